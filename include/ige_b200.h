@@ -1,0 +1,175 @@
+/*
+ * ige_b200.h -- C ABI of the B200-native post-physics step kernels for IsaacGymEnvs-MA.
+ *
+ * The reference has no FFI: its plug-in point for this path is the Python virtual method
+ * VecTask.post_physics_step (isaacgymenvs/tasks/base/vec_task.py:358-360), called from
+ * VecTask.step (vec_task.py:391).  Each entry point below replaces ONE task's implementation
+ * of that method (plus the fused step() epilogue, vec_task.py:396-404) with a single fused
+ * sm_100a CUDA kernel.  INTEGRATION.md shows the ctypes binding a maintainer adds.
+ *
+ * Conventions
+ *   - extern "C", plain pointers and sizes, no C++/torch types, never throws, never exits.
+ *   - All pointers are DEVICE pointers borrowed for the duration of the call; the launch is
+ *     asynchronous on `stream` (a cudaStream_t passed as void*); the callee never allocates,
+ *     frees or synchronises.  The call is CUDA-graph capturable.
+ *   - Layouts are the gymtorch layouts, unchanged: root / rigid-body rows = 13 floats
+ *     (pos3, quat xyzw 4, linvel3, angvel3), DOF rows = (pos, vel), force sensors = 6 floats,
+ *     contact forces = 3 floats; reset/progress/randomize flags are int64 (vec_task.py:317-324).
+ *   - Return value: 0 (IGE_OK), a negative IGE_E* code for bad arguments, or a positive
+ *     cudaError_t from the launch.  ige_last_error_string() describes the last failure of the
+ *     calling thread.
+ *   - The SAME structs (with host pointers) drive the CPU oracle in oracle/ige_oracle.c
+ *     (test infrastructure only).
+ */
+#ifndef IGE_B200_H
+#define IGE_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define IGE_ABI_VERSION 1
+
+#define IGE_OK 0
+#define IGE_ENULL (-1)   /* a required pointer is NULL */
+#define IGE_EALIGN (-2)  /* a pointer is not 16-byte aligned */
+#define IGE_ESIZE (-3)   /* a size / count is out of range */
+#define IGE_EPARAM (-4)  /* an inconsistent parameter combination */
+
+#define IGE_MAX_DOF 32
+#define IGE_NUM_STATS 16
+
+/* How reset_idx obtains its uniforms. */
+#define IGE_RAND_INJECTED 0 /* parity mode: caller pre-draws torch.rand(k, D) like the reference */
+#define IGE_RAND_PHILOX 1   /* production mode: Philox4x32-10 inside the kernel, no host sync */
+
+typedef struct IgeResetRand {
+    int32_t mode;              /* IGE_RAND_* */
+    int32_t _pad;
+    uint64_t seed;             /* PHILOX: key */
+    const uint64_t *step;      /* PHILOX: device word mixed into the counter (bumped once per step
+                                  by ige_compact_resets); NULL = 0 */
+    const int32_t *reset_rank; /* INJECTED: [N] exclusive prefix sum of (reset_buf != 0), i.e. the row
+                                  of env n in u0/u1 == its position in reset_buf.nonzero() */
+    const float *u0;           /* INJECTED: uniforms of the 1st torch.rand call of reset_idx, (k, D) */
+    const float *u1;           /* INJECTED: uniforms of the 2nd torch.rand call, (k, D) */
+} IgeResetRand;
+
+/* Episode-statistics accumulator slots (device float[IGE_NUM_STATS], atomically added to by
+ * every step kernel; all-reduced across GPUs once per horizon). */
+#define IGE_STAT_STEPS 0        /* env (or agent) rows stepped */
+#define IGE_STAT_REWARD 1       /* sum rew_buf */
+#define IGE_STAT_DONE 2         /* sum (reset_buf != 0) after the step */
+#define IGE_STAT_TIMEOUT 3      /* sum time_outs */
+#define IGE_STAT_DONE_LENGTH 4  /* sum progress_buf over done rows */
+#define IGE_STAT_TASK0 5        /* task specific, see each task */
+
+/* ------------------------------------------------------------------------------------------
+ * Reset compaction: reset_buf.nonzero() (ant.py:291, cartpole.py:168, franka_reach_MA.py:824)
+ * ------------------------------------------------------------------------------------------ */
+typedef struct IgeCompactArgs {
+    int32_t num_rows;          /* N (or N*A for the agent axis) */
+    int32_t group;             /* 1, or A: a row is emitted only if ALL `group` consecutive flags of
+                                  its env are set (franka_reach_MA.py:879-882); output ids are then
+                                  ENV ids */
+    const int64_t *reset_buf;  /* [num_rows] */
+    int32_t *reset_ids;        /* [num_rows/group] out: ascending ids, first *count entries valid */
+    int32_t *reset_rank;       /* [num_rows/group] out: exclusive prefix of the per-env flag */
+    int32_t *count;            /* [1] out */
+    uint64_t *step;            /* [1] in/out: incremented by one (Philox step word); may be NULL */
+    uint32_t *scratch;         /* [ige_compact_scratch_words(num_rows/group)] device words, zeroed ONCE by
+                                  the caller; every launch leaves them zero again (graph re-playable) */
+} IgeCompactArgs;
+
+int ige_compact_scratch_words(int32_t num_envs);
+int ige_compact_resets(const IgeCompactArgs *args, void *stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Cartpole -- replaces Cartpole.post_physics_step (tasks/cartpole.py:165-173) incl. reset_idx
+ * (:144-157), compute_observations (:131-142), compute_cartpole_reward (:180-196).
+ * ------------------------------------------------------------------------------------------ */
+typedef struct IgeCartpoleParams {
+    int32_t num_envs;
+    float reset_dist;          /* cfg env.resetDist, cartpole.py:41 */
+    float max_episode_length;  /* 500, cartpole.py:44 */
+    float clip_obs;            /* cfg env.clipObservations (vec_task.py:404); INFINITY = none */
+    IgeResetRand rand;         /* u0 = positions draw (k,2), u1 = velocities draw (k,2) */
+} IgeCartpoleParams;
+
+typedef struct IgeCartpoleBuffers {
+    float *dof_state;          /* (N*2, 2) in/out: reset rows rewritten */
+    float *obs_buf;            /* (N, 4) out */
+    float *rew_buf;            /* (N) out */
+    int64_t *reset_buf;        /* (N) in/out */
+    int64_t *progress_buf;     /* (N) in/out */
+    float *obs_clamped;        /* (N, 4) out, optional: clamp(obs_buf, +-clip_obs) (vec_task.py:404) */
+    uint8_t *timeout_buf;      /* (N) out, optional: bool time_outs (vec_task.py:396) */
+    float *stats;              /* [IGE_NUM_STATS] in/out, optional */
+} IgeCartpoleBuffers;
+
+int ige_cartpole_post_physics(const IgeCartpoleParams *p, const IgeCartpoleBuffers *b, void *stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Ant / Humanoid -- replace Ant.post_physics_step (tasks/ant.py:287-297) and
+ * Humanoid.post_physics_step (tasks/humanoid.py:287-296) incl. reset_idx, compute_*_observations,
+ * compute_*_reward.  One struct, two entry points (the tasks differ in obs layout and reward).
+ * ------------------------------------------------------------------------------------------ */
+typedef struct IgeLocomotionParams {
+    int32_t num_envs;
+    int32_t num_dof;               /* 8 (Ant) / 21 (Humanoid) */
+    int32_t num_sensor_floats;     /* 24 (4 feet x 6) / 12 (2 feet x 6) */
+    int32_t potentials_recip_mul;  /* 0: potentials = -|d| / dt (torch CPU semantics, parity default)
+                                      1: -|d| * (1/dt)  (torch CUDA div-by-scalar semantics) */
+    float dt;
+    float dof_vel_scale, contact_force_scale, angular_velocity_scale;
+    float up_weight, heading_weight;
+    float actions_cost_scale, energy_cost_scale, joints_at_limit_cost_scale;
+    float termination_height, death_cost;
+    float max_episode_length;
+    float clip_obs;
+    /* per-env constant rows of the reference (ant.py:103-114), identical for every env */
+    float targets[3], inv_start_rot[4], basis_vec0[3], basis_vec1[3];
+    float dof_limits_lower[IGE_MAX_DOF], dof_limits_upper[IGE_MAX_DOF];
+    float motor_effort_ratio[IGE_MAX_DOF]; /* Humanoid: motor_efforts / max_motor_effort (humanoid.py:355) */
+    IgeResetRand rand;             /* u0 = positions draw (k,D) in [0,1), u1 = velocities draw */
+} IgeLocomotionParams;
+
+typedef struct IgeLocomotionBuffers {
+    const float *root_states;         /* (N, 13) sim view */
+    float *dof_state;                 /* (N*D, 2) sim view, reset rows rewritten */
+    const float *vec_sensor_tensor;   /* (N, num_sensor_floats) sim view */
+    const float *dof_force_tensor;    /* (N, D) sim view; Humanoid only */
+    const float *actions;             /* (N, D) */
+    const float *initial_root_states; /* (N, 13) */
+    const float *initial_dof_pos;     /* (N, D) */
+    float *potentials;                /* (N) in/out */
+    float *prev_potentials;           /* (N) in/out */
+    float *up_vec;                    /* (N, 3) out */
+    float *heading_vec;               /* (N, 3) out */
+    float *obs_buf;                   /* (N, 60 | 108) out */
+    float *rew_buf;                   /* (N) out */
+    int64_t *reset_buf;               /* (N) in/out */
+    int64_t *progress_buf;            /* (N) in/out */
+    int64_t *randomize_buf;           /* (N) in/out, optional */
+    float *obs_clamped;               /* optional, see Cartpole */
+    uint8_t *timeout_buf;             /* optional */
+    float *stats;                     /* optional; TASK0 = sum root_states[:,7] (true_objective, ant.py:245-250) */
+} IgeLocomotionBuffers;
+
+int ige_ant_post_physics(const IgeLocomotionParams *p, const IgeLocomotionBuffers *b, void *stream);
+int ige_humanoid_post_physics(const IgeLocomotionParams *p, const IgeLocomotionBuffers *b, void *stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Library
+ * ------------------------------------------------------------------------------------------ */
+int ige_version(void);
+const char *ige_last_error_string(void);
+/* Kernel launches issued by this library since load (bench.py's gpu_launches claim). */
+uint64_t ige_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* IGE_B200_H */

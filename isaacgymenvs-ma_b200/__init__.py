@@ -1,0 +1,6 @@
+"""B200-native post-physics step kernels for IsaacGymEnvs-MA (hot path only)."""
+from . import synthetic  # noqa: F401
+
+__version__ = "0.1.0"
+from . import factory  # noqa: E402,F401
+from .factory import make  # noqa: E402,F401

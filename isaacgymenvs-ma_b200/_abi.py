@@ -1,0 +1,65 @@
+"""ctypes mirror of include/ige_b200.h (the C ABI).  Field order and types must match the header
+exactly; tests/test_abi.py cross-checks sizeof()/offsetof() against a compiled probe."""
+import ctypes as C
+
+IGE_MAX_DOF = 32
+IGE_NUM_STATS = 16
+IGE_RAND_INJECTED = 0
+IGE_RAND_PHILOX = 1
+
+IGE_OK, IGE_ENULL, IGE_EALIGN, IGE_ESIZE, IGE_EPARAM = 0, -1, -2, -3, -4
+
+STAT_STEPS, STAT_REWARD, STAT_DONE, STAT_TIMEOUT, STAT_DONE_LENGTH, STAT_TASK0 = 0, 1, 2, 3, 4, 5
+
+_p = C.c_void_p
+_f = C.c_float
+_i = C.c_int32
+
+
+class IgeResetRand(C.Structure):
+    _fields_ = [("mode", _i), ("_pad", _i), ("seed", C.c_uint64), ("step", _p),
+                ("reset_rank", _p), ("u0", _p), ("u1", _p)]
+
+
+class IgeCompactArgs(C.Structure):
+    _fields_ = [("num_rows", _i), ("group", _i), ("reset_buf", _p), ("reset_ids", _p),
+                ("reset_rank", _p), ("count", _p), ("step", _p), ("scratch", _p)]
+
+
+class IgeCartpoleParams(C.Structure):
+    _fields_ = [("num_envs", _i), ("reset_dist", _f), ("max_episode_length", _f), ("clip_obs", _f),
+                ("rand", IgeResetRand)]
+
+
+class IgeCartpoleBuffers(C.Structure):
+    _fields_ = [("dof_state", _p), ("obs_buf", _p), ("rew_buf", _p), ("reset_buf", _p),
+                ("progress_buf", _p), ("obs_clamped", _p), ("timeout_buf", _p), ("stats", _p)]
+
+
+class IgeLocomotionParams(C.Structure):
+    _fields_ = [("num_envs", _i), ("num_dof", _i), ("num_sensor_floats", _i),
+                ("potentials_recip_mul", _i),
+                ("dt", _f), ("dof_vel_scale", _f), ("contact_force_scale", _f),
+                ("angular_velocity_scale", _f), ("up_weight", _f), ("heading_weight", _f),
+                ("actions_cost_scale", _f), ("energy_cost_scale", _f),
+                ("joints_at_limit_cost_scale", _f), ("termination_height", _f), ("death_cost", _f),
+                ("max_episode_length", _f), ("clip_obs", _f),
+                ("targets", _f * 3), ("inv_start_rot", _f * 4), ("basis_vec0", _f * 3),
+                ("basis_vec1", _f * 3),
+                ("dof_limits_lower", _f * IGE_MAX_DOF), ("dof_limits_upper", _f * IGE_MAX_DOF),
+                ("motor_effort_ratio", _f * IGE_MAX_DOF),
+                ("rand", IgeResetRand)]
+
+
+class IgeLocomotionBuffers(C.Structure):
+    _fields_ = [("root_states", _p), ("dof_state", _p), ("vec_sensor_tensor", _p),
+                ("dof_force_tensor", _p), ("actions", _p), ("initial_root_states", _p),
+                ("initial_dof_pos", _p), ("potentials", _p), ("prev_potentials", _p),
+                ("up_vec", _p), ("heading_vec", _p), ("obs_buf", _p), ("rew_buf", _p),
+                ("reset_buf", _p), ("progress_buf", _p), ("randomize_buf", _p),
+                ("obs_clamped", _p), ("timeout_buf", _p), ("stats", _p)]
+
+
+def fill_array(carr, values):
+    for i, v in enumerate(values):
+        carr[i] = float(v)

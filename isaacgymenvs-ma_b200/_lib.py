@@ -1,0 +1,61 @@
+"""ctypes binding of libige_b200.so (the C ABI in include/ige_b200.h).
+
+There is NO fallback: if the library is missing or a call fails, this raises.  The product path
+never routes through the CPU oracle or eager torch.
+"""
+import ctypes as C
+import os
+
+from . import _abi
+from .build import SO_PATH
+
+_lib = None
+
+_SIGS = {
+    "ige_compact_resets": (_abi.IgeCompactArgs,),
+    "ige_cartpole_post_physics": (_abi.IgeCartpoleParams, _abi.IgeCartpoleBuffers),
+    "ige_ant_post_physics": (_abi.IgeLocomotionParams, _abi.IgeLocomotionBuffers),
+    "ige_humanoid_post_physics": (_abi.IgeLocomotionParams, _abi.IgeLocomotionBuffers),
+}
+
+
+class IgeError(RuntimeError):
+    pass
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(SO_PATH):
+            raise IgeError(
+                f"{SO_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                "(nvcc, sm_100a).  There is no CPU fallback for the post-physics kernels.")
+        l = C.CDLL(SO_PATH)
+        l.ige_version.restype = C.c_int
+        l.ige_last_error_string.restype = C.c_char_p
+        l.ige_launch_count.restype = C.c_uint64
+        for name, structs in _SIGS.items():
+            fn = getattr(l, name)
+            fn.restype = C.c_int
+            fn.argtypes = [C.POINTER(s) for s in structs] + [C.c_void_p]
+        if l.ige_version() != 1:
+            raise IgeError(f"ABI version mismatch: library {l.ige_version()}, binding 1")
+        _lib = l
+    return _lib
+
+
+def exported_symbols():
+    return ["ige_version", "ige_last_error_string", "ige_launch_count", *_SIGS.keys()]
+
+
+def call(name, *structs, stream=0):
+    """Invoke an entry point; raises IgeError with ige_last_error_string() on failure."""
+    l = lib()
+    rc = getattr(l, name)(*[C.byref(s) for s in structs], C.c_void_p(stream))
+    if rc != 0:
+        msg = l.ige_last_error_string().decode()
+        raise IgeError(f"{name} failed (rc={rc}): {msg}")
+
+
+def launch_count():
+    return int(lib().ige_launch_count())

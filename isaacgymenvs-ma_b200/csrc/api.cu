@@ -1,0 +1,30 @@
+// api.cu -- library-level entry points of the C ABI (include/ige_b200.h).
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+
+#include "ige_common.cuh"
+
+static thread_local char g_err[512] = "no error";
+static std::atomic<uint64_t> g_launches{0};
+
+int ige_fail(int code, const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+void ige_count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+
+int ige_check_launch(const char *what) {
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return ige_fail((int)e, "%s: launch failed: %s", what, cudaGetErrorString(e));
+    ige_count_launch();
+    return IGE_OK;
+}
+
+extern "C" int ige_version(void) { return IGE_ABI_VERSION; }
+extern "C" const char *ige_last_error_string(void) { return g_err; }
+extern "C" uint64_t ige_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }

@@ -1,0 +1,250 @@
+// ige_common.cuh -- shared host/device helpers for the post-physics kernels (sm_100a).
+//
+// Device math follows the reference's torch-CPU rounding op by op (the library is compiled with
+// -fmad=false, so only the explicit __fmaf_rn calls below fuse); see DESIGN.md "Numerics".
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "ige_b200.h"
+
+// ---------------------------------------------------------------------------------------------
+// host side: error reporting + launch accounting (api.cu)
+// ---------------------------------------------------------------------------------------------
+int ige_fail(int code, const char *fmt, ...);
+void ige_count_launch();
+int ige_check_launch(const char *what);
+
+#define IGE_REQUIRE_PTR(ptr)                                                       \
+    do {                                                                           \
+        if ((ptr) == nullptr) return ige_fail(IGE_ENULL, "%s is NULL", #ptr);      \
+        if ((reinterpret_cast<uintptr_t>(ptr) & 15u) != 0)                         \
+            return ige_fail(IGE_EALIGN, "%s is not 16-byte aligned", #ptr);        \
+    } while (0)
+#define IGE_OPTIONAL_PTR(ptr)                                                      \
+    do {                                                                           \
+        if ((ptr) != nullptr && (reinterpret_cast<uintptr_t>(ptr) & 15u) != 0)     \
+            return ige_fail(IGE_EALIGN, "%s is not 16-byte aligned", #ptr);        \
+    } while (0)
+
+static inline int ige_check_rand(const IgeResetRand &r) {
+    if (r.mode == IGE_RAND_INJECTED) {
+        if (r.reset_rank == nullptr) return ige_fail(IGE_ENULL, "rand.reset_rank is NULL (INJECTED mode)");
+        // u0/u1 may legitimately be NULL when no env resets (k == 0); the kernel never reads them then.
+    } else if (r.mode != IGE_RAND_PHILOX) {
+        return ige_fail(IGE_EPARAM, "rand.mode must be IGE_RAND_INJECTED or IGE_RAND_PHILOX");
+    }
+    return IGE_OK;
+}
+
+#ifdef __CUDACC__
+// ---------------------------------------------------------------------------------------------
+// device math (reference: isaacgymenvs/utils/torch_jit_utils.py)
+// ---------------------------------------------------------------------------------------------
+namespace ige {
+
+constexpr float kTwoPi = 6.28318530717958647692f;  // float(2*np.pi)
+constexpr float kHalfPi = 1.57079632679489661923f;
+
+// torch.norm(p=2, dim=-1) on CPU: sqrt of an fma chain
+__device__ __forceinline__ float norm3(float x, float y, float z) {
+    float s = __fmul_rn(x, x);
+    s = __fmaf_rn(y, y, s);
+    s = __fmaf_rn(z, z, s);
+    return __fsqrt_rn(s);
+}
+__device__ __forceinline__ float norm2(float x, float y) {
+    float s = __fmul_rn(x, x);
+    s = __fmaf_rn(y, y, s);
+    return __fsqrt_rn(s);
+}
+// torch.bmm (1x3)(3x1): unfused multiply-add chain (torch_jit_utils.py:88-89, :259-260)
+__device__ __forceinline__ float dot3(const float *a, const float *b) {
+    return __fadd_rn(__fadd_rn(__fmul_rn(a[0], b[0]), __fmul_rn(a[1], b[1])), __fmul_rn(a[2], b[2]));
+}
+// torch.remainder(Tensor, Scalar) (python %), torch_jit_utils.py:195
+__device__ __forceinline__ float py_remainder(float a, float b) {
+    float m = fmodf(a, b);
+    if (m != 0.0f && ((b < 0.0f) != (m < 0.0f))) m += b;
+    return m;
+}
+// torch_jit_utils.py:41-62, the 9-product form, xyzw
+__device__ __forceinline__ void quat_mul(const float *a, const float *b, float *out) {
+    const float x1 = a[0], y1 = a[1], z1 = a[2], w1 = a[3];
+    const float x2 = b[0], y2 = b[1], z2 = b[2], w2 = b[3];
+    const float ww = (z1 + x1) * (x2 + y2);
+    const float yy = (w1 - y1) * (w2 + z2);
+    const float zz = (w1 + y1) * (w2 - z2);
+    const float xx = ww + yy + zz;
+    const float qq = 0.5f * (xx + (z1 - x1) * (x2 - y2));
+    out[3] = qq - ww + (z1 - y1) * (y2 - z2);
+    out[0] = qq - xx + (x1 + w1) * (x2 + w2);
+    out[1] = qq - yy + (w1 - x1) * (y2 + z2);
+    out[2] = qq - zz + (z1 + y1) * (w2 - x2);
+}
+__device__ __forceinline__ void quat_conjugate(const float *a, float *out) {
+    out[0] = -a[0]; out[1] = -a[1]; out[2] = -a[2]; out[3] = a[3];
+}
+// torch_jit_utils.py:80-90 (INVERSE=false) / :93-103 (INVERSE=true)
+template <bool INVERSE>
+__device__ __forceinline__ void quat_rotate(const float *q, const float *v, float *out) {
+    const float qw = q[3];
+    const float s = 2.0f * (qw * qw) - 1.0f;
+    const float cr0 = q[1] * v[2] - q[2] * v[1];
+    const float cr1 = q[2] * v[0] - q[0] * v[2];
+    const float cr2 = q[0] * v[1] - q[1] * v[0];
+    const float d = dot3(q, v);
+    const float cr[3] = {cr0, cr1, cr2};
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        const float a = v[i] * s;
+        const float b = cr[i] * qw * 2.0f;
+        const float c = q[i] * d * 2.0f;
+        out[i] = INVERSE ? (a - b + c) : (a + b + c);
+    }
+}
+// torch_jit_utils.py:65-67
+__device__ __forceinline__ void normalize3(const float *x, float *out) {
+    float n = norm3(x[0], x[1], x[2]);
+    n = n < 1e-9f ? 1e-9f : n;
+    out[0] = x[0] / n; out[1] = x[1] / n; out[2] = x[2] / n;
+}
+// torch_jit_utils.py:175-195; pitch is never consumed on this path
+__device__ __forceinline__ void euler_roll_yaw(const float *q, float &roll, float &yaw) {
+    const float qx = q[0], qy = q[1], qz = q[2], qw = q[3];
+    const float sinr_cosp = 2.0f * (qw * qx + qy * qz);
+    const float cosr_cosp = qw * qw - qx * qx - qy * qy + qz * qz;
+    const float siny_cosp = 2.0f * (qw * qz + qx * qy);
+    const float cosy_cosp = qw * qw + qx * qx - qy * qy - qz * qz;
+    roll = py_remainder(atan2f(sinr_cosp, cosr_cosp), kTwoPi);
+    yaw = py_remainder(atan2f(siny_cosp, cosy_cosp), kTwoPi);
+}
+__device__ __forceinline__ float normalize_angle(float x) { return atan2f(sinf(x), cosf(x)); }
+
+// torch.sum(dim=-1) order of the CPU reference for a row of D < 32 floats held in registers:
+// 8 lanes over the full groups of 8, then the tail, then the lanes (see oracle row_sum()).
+template <int D, typename F>
+__device__ __forceinline__ float row_sum(F elem) {
+    constexpr int NV = D / 8;
+    static_assert(NV < 4, "row_sum: D >= 32 needs the 4-accumulator variant");
+    float lanes[8];
+#pragma unroll
+    for (int l = 0; l < 8; ++l) lanes[l] = 0.0f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i)
+#pragma unroll
+        for (int l = 0; l < 8; ++l) lanes[l] += elem(i * 8 + l);
+    float acc = 0.0f;
+#pragma unroll
+    for (int k = NV * 8; k < D; ++k) acc += elem(k);
+    if (NV > 0) {
+#pragma unroll
+        for (int l = 0; l < 8; ++l) acc += lanes[l];
+    }
+    return acc;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Philox4x32-10 counter-based RNG (production reset noise; the oracle has the same function)
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void philox4x32_10(uint32_t c[4], uint32_t k0, uint32_t k1) {
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        const uint32_t hi0 = __umulhi(0xD2511F53u, c[0]), lo0 = 0xD2511F53u * c[0];
+        const uint32_t hi1 = __umulhi(0xCD9E8D57u, c[2]), lo1 = 0xCD9E8D57u * c[2];
+        const uint32_t n0 = hi1 ^ c[1] ^ k0, n2 = hi0 ^ c[3] ^ k1;
+        c[0] = n0; c[1] = lo1; c[2] = n2; c[3] = lo0;
+        k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+    }
+}
+__device__ __forceinline__ float philox_uniform(const IgeResetRand &r, uint64_t step, uint32_t row,
+                                                uint32_t draw, uint32_t idx) {
+    uint32_t c[4] = {row, (draw << 16) | (idx >> 2), (uint32_t)step, (uint32_t)(step >> 32)};
+    philox4x32_10(c, (uint32_t)r.seed, (uint32_t)(r.seed >> 32));
+    return (float)(c[idx & 3] >> 8) * (1.0f / 16777216.0f);
+}
+// uniform `j` of torch.rand call `which` (0/1) for reset row `row` with `d` columns
+__device__ __forceinline__ float reset_uniform(const IgeResetRand &r, uint64_t step, int which, int row,
+                                               int d, int j) {
+    if (r.mode == IGE_RAND_PHILOX) return philox_uniform(r, step, (uint32_t)row, (uint32_t)which, (uint32_t)j);
+    const float *u = which ? r.u1 : r.u0;
+    return __ldg(u + (size_t)__ldg(r.reset_rank + row) * d + j);
+}
+
+// ---------------------------------------------------------------------------------------------
+// TMA 1-D bulk copies (cp.async.bulk) + mbarrier; SASS: UBLKCP / SYNCS
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void *p) {
+    return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void fence_mbar_init() {
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t phase) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(smem_u32(bar)),
+        "r"(phase)
+        : "memory");
+}
+// global -> shared, completes `bytes` on the mbarrier.  dst/src 16-B aligned, bytes % 16 == 0.
+__device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src_gmem, uint32_t bytes, uint64_t *bar) {
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+            smem_u32(dst_smem)),
+        "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
+        : "memory");
+}
+// shared -> global (bulk async-group)
+__device__ __forceinline__ void bulk_s2g(void *dst_gmem, const void *src_smem, uint32_t bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst_gmem),
+                 "r"(smem_u32(src_smem)), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read_all() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+// make generic-proxy smem writes visible to the async proxy (before bulk_s2g)
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+// ---------------------------------------------------------------------------------------------
+// episode statistics: block reduce -> one atomic per slot per CTA
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+// Every thread of the CTA calls this with its partials; `scratch` is >= NSTAT * (nthreads/32) floats.
+template <int NSTAT>
+__device__ __forceinline__ void block_stats_add(float *stats, const float (&v)[NSTAT], const int (&slot)[NSTAT],
+                                                float *scratch) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = (blockDim.x + 31) >> 5;
+#pragma unroll
+    for (int s = 0; s < NSTAT; ++s) {
+        const float w = warp_sum(v[s]);
+        if (lane == 0) scratch[s * nwarps + warp] = w;
+    }
+    __syncthreads();
+    if (threadIdx.x < NSTAT) {
+        float t = 0.0f;
+        for (int w = 0; w < nwarps; ++w) t += scratch[threadIdx.x * nwarps + w];
+        atomicAdd(stats + slot[threadIdx.x], t);
+    }
+}
+
+}  // namespace ige
+#endif  // __CUDACC__

@@ -1,0 +1,55 @@
+"""Build task mirrors on synthetic simulator state (the stand-in for isaacgymenvs.make(), whose
+hydra/isaacgym machinery is outside the hot path; signature kept close: seed, task, num_envs,
+sim_device, rl_device)."""
+import numpy as np
+import torch
+
+from . import synthetic
+from .tasks import SyntheticSim, task_map
+
+_SIM_TENSORS = {
+    "Cartpole": ["dof_state"],
+    "Ant": ["root_states", "dof_state", "vec_sensor_tensor"],
+    "Humanoid": ["root_states", "dof_state", "vec_sensor_tensor", "dof_force_tensor"],
+}
+_CFGS = {"Cartpole": synthetic.CARTPOLE_CFG, "Ant": synthetic.ANT_CFG, "Humanoid": synthetic.HUMANOID_CFG}
+
+
+def task_cfg(task):
+    return dict(_CFGS[task])
+
+
+def sim_tensor_names(task):
+    return list(_SIM_TENSORS[task])
+
+
+def from_state(task, st, sim_device, rl_device=None, **kw):
+    """Construct the mirror of `task` around an existing synthetic state dict (numpy arrays)."""
+    dev = torch.device(sim_device)
+    cfg = task_cfg(task)
+    cfg["num_envs"] = int(st["progress_buf"].shape[0])
+    tensors = {k: torch.from_numpy(np.ascontiguousarray(st[k])).to(dev) for k in _SIM_TENSORS[task]}
+    sim = SyntheticSim(tensors)
+    obj = task_map[task](cfg, sim, dev, rl_device=rl_device, **kw)
+    if hasattr(obj, "adopt_state"):
+        obj.adopt_state(st)
+    else:
+        for k in ("reset_buf", "progress_buf"):
+            getattr(obj, k).copy_(torch.from_numpy(st[k]).to(dev))
+    return obj
+
+
+def make(seed, task, num_envs, sim_device, rl_device=None, reset_prob=0.02, **kw):
+    """isaacgymenvs.make()-shaped entry point (isaacgymenvs/__init__.py:14-26) on synthetic state."""
+    st = synthetic.make_state(task.lower(), num_envs, seed=seed, reset_prob=reset_prob)
+    kw.setdefault("seed", seed)
+    return from_state(task, st, sim_device, rl_device=rl_device, **kw)
+
+
+def load_sim_inputs(obj, task, arrays):
+    """Overwrite the simulator-owned tensors (and actions) with new post-simulate values."""
+    for k, v in arrays.items():
+        t = obj.sim.tensors.get(k)
+        if t is None:
+            t = getattr(obj, k)
+        t.copy_(torch.from_numpy(np.ascontiguousarray(v)).to(t.device).view_as(t))

@@ -1,0 +1,12 @@
+"""Host-side mirrors of the reference task classes for the post-physics hot path.
+
+Same attribute names, buffer shapes / dtypes and ``step()`` contract as
+``isaacgymenvs/tasks/base/vec_task.py`` and the task modules; ``post_physics_step`` is one call
+into the C ABI (libige_b200.so).  ``task_map`` mirrors ``isaacgym_task_map``
+(isaacgymenvs/tasks/__init__.py:67-100) for the tasks on the path.
+"""
+from .base import SyntheticSim, VecTaskB200  # noqa: F401
+from .cartpole import Cartpole  # noqa: F401
+from .locomotion import Ant, Humanoid  # noqa: F401
+
+task_map = {"Cartpole": Cartpole, "Ant": Ant, "Humanoid": Humanoid}

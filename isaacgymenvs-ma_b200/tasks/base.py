@@ -1,0 +1,209 @@
+"""VecTask mirror: buffers + step() contract of isaacgymenvs/tasks/base/vec_task.py, with the
+post-physics work delegated to the fused CUDA kernels through the C ABI.
+
+What is kept from the reference (so callers cannot tell the difference):
+  * ``allocate_buffers`` shapes / dtypes (vec_task.py:302-326): obs_buf f32 (N, num_obs),
+    rew_buf f32, reset_buf i64 = 1, timeout_buf, progress_buf i64, randomize_buf i64, extras.
+  * ``step(actions) -> (obs_dict, rew, reset, extras)`` order of operations (vec_task.py:362-410).
+  * ``reset()`` / ``reset_done()`` (vec_task.py:428-457).
+What is different: the simulator.  Isaac Gym's PhysX binary is not available, so ``self.sim`` is a
+``SyntheticSim`` that owns the gymtorch-layout tensors and *records* the ``set_*_indexed`` calls
+(the same role ``gym`` plays in the reference).  A real integration binds the same
+``post_physics_step`` onto the reference classes -- see INTEGRATION.md.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+
+import numpy as np
+import torch
+
+from .. import _abi, _lib
+
+
+def _ptr(t):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+class SyntheticSim:
+    """Owns the simulator-side tensors (gymtorch layouts) and records indexed set calls.
+
+    ``tensors`` maps the reference attribute names (root_states, dof_state, ...) to torch tensors
+    on the sim device.  ``set_indexed(name, ids, count)`` plays the role of
+    ``gym.set_*_tensor_indexed(sim, tensor, ids_int32, count)``: recorded, never applied
+    (SURVEY.md section 8c FakeGym semantics)."""
+
+    def __init__(self, tensors):
+        self.tensors = tensors
+        self.calls = []
+        self.record = True
+
+    def set_indexed(self, name, tensor, ids, count):
+        if self.record:
+            self.calls.append((name, tensor, ids, count))
+
+    def simulate(self):
+        pass
+
+
+class VecTaskB200:
+    """Mirror of Env + VecTask (vec_task.py:67-133, 207-457) minus viewer / DR / sim creation."""
+
+    num_agents = 1
+
+    def __init__(self, cfg, sim: SyntheticSim, device, rl_device=None, rand_mode="philox", seed=0,
+                 fuse_epilogue=True, accumulate_stats=True):
+        self.cfg = cfg
+        self.sim = sim
+        self.gym = sim
+        self.device = torch.device(device)
+        self.rl_device = torch.device(rl_device) if rl_device is not None else self.device
+        self.num_environments = int(cfg["num_envs"])
+        self.num_observations = int(cfg["num_obs"])
+        self.num_states = int(cfg.get("num_states", 0))
+        self.num_actions = int(cfg["num_actions"])
+        self.control_freq_inv = int(cfg.get("control_freq_inv", 1))
+        self.clip_obs = float(cfg.get("clip_obs", math.inf))
+        self.clip_actions = float(cfg.get("clip_actions", math.inf))
+        self.control_steps = 0
+        self.rand_mode = rand_mode
+        self.seed = int(seed)
+        self.fuse_epilogue = fuse_epilogue
+        self.obs_dict = {}
+        self.allocate_buffers()
+        n_rows = self.num_envs * self.num_agents
+        dev = self.device
+        # outputs of the fused step() epilogue (vec_task.py:396,404)
+        self.timeout_bool = torch.zeros(n_rows, dtype=torch.bool, device=dev)
+        self.obs_clamped = torch.zeros_like(self.obs_buf) if fuse_epilogue else None
+        # reset compaction outputs (what gym.set_*_indexed consumes)
+        self.reset_env_ids = torch.zeros(self.num_envs, dtype=torch.int32, device=dev)
+        self.reset_rank = torch.zeros(self.num_envs, dtype=torch.int32, device=dev)
+        self.reset_count = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.rng_step = torch.zeros(1, dtype=torch.int64, device=dev)
+        words = 2 + (self.num_envs + 2047) // 2048
+        self._compact_scratch = torch.zeros(words, dtype=torch.int32, device=dev)
+        self.stats = torch.zeros(_abi.IGE_NUM_STATS, dtype=torch.float32, device=dev) if accumulate_stats else None
+        self._u0 = self._u1 = None
+
+    # -- vec_task.py:135-160 properties ------------------------------------------------------
+    @property
+    def num_envs(self):
+        return self.num_environments
+
+    @property
+    def num_obs(self):
+        return self.num_observations
+
+    @property
+    def num_acts(self):
+        return self.num_actions
+
+    # -- vec_task.py:302-326 -------------------------------------------------------------------
+    def allocate_buffers(self):
+        dev, n = self.device, self.num_envs * self.num_agents
+        self.obs_buf = torch.zeros((n, self.num_obs), device=dev, dtype=torch.float)
+        self.states_buf = torch.zeros((self.num_envs, self.num_states), device=dev, dtype=torch.float)
+        self.rew_buf = torch.zeros(n, device=dev, dtype=torch.float)
+        self.reset_buf = torch.ones(n, device=dev, dtype=torch.long)
+        self.timeout_buf = torch.zeros(n, device=dev, dtype=torch.long)
+        self.progress_buf = torch.zeros(n, device=dev, dtype=torch.long)
+        self.randomize_buf = torch.zeros(self.num_envs, device=dev, dtype=torch.long)
+        self.extras = {}
+
+    # -- stream / launch helpers ---------------------------------------------------------------
+    def _stream(self):
+        if self.device.type != "cuda":
+            raise _lib.IgeError(
+                f"post_physics_step needs CUDA tensors (device={self.device}); there is no CPU path")
+        return torch.cuda.current_stream(self.device).cuda_stream
+
+    def _rand_struct(self):
+        r = _abi.IgeResetRand()
+        if self.rand_mode == "philox":
+            r.mode = _abi.IGE_RAND_PHILOX
+            r.seed = self.seed
+            r.step = _ptr(self.rng_step)
+        else:
+            r.mode = _abi.IGE_RAND_INJECTED
+            r.reset_rank = _ptr(self.reset_rank)
+            r.u0 = _ptr(self._u0)
+            r.u1 = _ptr(self._u1)
+        return r
+
+    def compact_resets(self, group=1):
+        """reset_buf.nonzero() on the device: fills reset_env_ids / reset_rank / reset_count."""
+        a = _abi.IgeCompactArgs()
+        a.num_rows = self.reset_buf.numel()
+        a.group = group
+        a.reset_buf = _ptr(self.reset_buf)
+        a.reset_ids = _ptr(self.reset_env_ids)
+        a.reset_rank = _ptr(self.reset_rank)
+        a.count = _ptr(self.reset_count)
+        a.step = _ptr(self.rng_step)
+        a.scratch = _ptr(self._compact_scratch)
+        _lib.call("ige_compact_resets", a, stream=self._stream())
+
+    def draw_reset_uniforms(self, k):
+        """INJECTED mode: the torch.rand calls reset_idx would make, in order.  Subclasses override."""
+        raise NotImplementedError
+
+    def set_injected_uniforms(self, u0, u1):
+        self._u0, self._u1 = u0, u1
+
+    # -- abstract task hooks -------------------------------------------------------------------
+    def pre_physics_step(self, actions):
+        raise NotImplementedError
+
+    def post_physics_step(self):
+        raise NotImplementedError
+
+    # -- vec_task.py:362-410 -------------------------------------------------------------------
+    def step(self, actions):
+        action_tensor = torch.clamp(actions, -self.clip_actions, self.clip_actions)
+        self.pre_physics_step(action_tensor)
+        for _ in range(self.control_freq_inv):
+            self.sim.simulate()
+        self.post_physics_step()
+        self.control_steps += 1
+        if self.fuse_epilogue:
+            # produced by the same kernel launch (obs_clamped / timeout_bool outputs)
+            self.timeout_buf = self.timeout_bool
+            obs = self.obs_clamped
+        else:
+            self.timeout_buf = (self.progress_buf >= self.max_episode_length - 1) & (self.reset_buf != 0)
+            obs = torch.clamp(self.obs_buf, -self.clip_obs, self.clip_obs)
+        self.extras["time_outs"] = self.timeout_buf.to(self.rl_device)
+        self.obs_dict["obs"] = obs.to(self.rl_device)
+        if self.num_states > 0:
+            self.obs_dict["states"] = self.get_state()
+        return self.obs_dict, self.rew_buf.to(self.rl_device), self.reset_buf.to(self.rl_device), self.extras
+
+    def get_state(self):
+        return torch.clamp(self.states_buf, -self.clip_obs, self.clip_obs).to(self.rl_device)
+
+    def zero_actions(self):
+        return torch.zeros([self.num_envs, self.num_actions], dtype=torch.float32, device=self.rl_device)
+
+    def reset(self):
+        self.obs_dict["obs"] = torch.clamp(self.obs_buf, -self.clip_obs, self.clip_obs).to(self.rl_device)
+        if self.num_states > 0:
+            self.obs_dict["states"] = self.get_state()
+        return self.obs_dict
+
+    # -- helpers for subclasses ----------------------------------------------------------------
+    def _adopt(self, st, names):
+        """Move numpy state arrays onto the device under the reference attribute names."""
+        for k in names:
+            v = st[k]
+            t = torch.from_numpy(np.ascontiguousarray(v)).to(self.device) if isinstance(v, np.ndarray) else v
+            setattr(self, k, t)
+
+    @staticmethod
+    def _row_constant(t, name):
+        """The reference keeps per-env copies of constants (ant.py:103-114); the kernels take them as
+        scalars, so refuse anything that is not actually constant over envs."""
+        if t.dim() == 2 and t.shape[0] > 1 and not bool((t == t[0:1]).all()):
+            raise ValueError(f"{name} differs between envs; the fused kernel takes it as a per-task constant")
+        return [float(x) for x in (t[0] if t.dim() == 2 else t).tolist()]

@@ -1,0 +1,445 @@
+/*
+ * ige_oracle.c -- CPU restatement of the reference's post-physics hot path.
+ *
+ * TEST INFRASTRUCTURE ONLY.  Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
+ * --impl reference legs may call into this file; the product (isaacgymenvs-ma_b200/) never does.
+ *
+ * Parity status: PINNED.  The reference holds no golden vectors for this path (SURVEY.md
+ * section 4), so the oracle is pinned against outputs of the reference itself: the fixtures in
+ * tests/golden/*.npz are produced by importing the unmodified reference task classes in the
+ * build container (tests/golden/gen_golden.py) and tests/test_oracle_golden.py checks this file
+ * against them (flags / counters / reset ids bit-exact, floats <= 1e-5 relative; in practice
+ * bit-exact except where libm and torch's vectorised atan2/asin/exp differ in the last ulp).
+ *
+ * Every function cites the reference file:line it restates (paths relative to
+ * /root/reference/isaacgymenvs/).  Arithmetic is fp32 with the reference's (torch CPU) operation
+ * order; compile with -ffp-contract=off so that only the fmaf() calls written here fuse.
+ * The structs (include/ige_b200.h) are the product's C ABI, used here with HOST pointers.
+ */
+#include <math.h>
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "../include/ige_b200.h"
+
+#define TWO_PI_F 6.28318530717958647692f /* float(2*np.pi) */
+#define HALF_PI_F 1.57079632679489661923f
+
+/* ------------------------------------------------------------------------------------------
+ * torch-CPU primitive semantics (measured against torch 2.11 CPU in the build container)
+ * ------------------------------------------------------------------------------------------ */
+
+/* torch.norm(p=2, dim=-1) over 3 elements == sqrt of an fma chain (ATen norm kernel). */
+static inline float norm3(float x, float y, float z) {
+    float s = x * x;
+    s = fmaf(y, y, s);
+    s = fmaf(z, z, s);
+    return sqrtf(s);
+}
+static inline float norm2(float x, float y) {
+    float s = x * x;
+    s = fmaf(y, y, s);
+    return sqrtf(s);
+}
+/* torch.bmm (1x3)(3x1): plain multiply-add chain, no fma. utils/torch_jit_utils.py:88-89 */
+static inline float dot3(const float *a, const float *b) {
+    return (a[0] * b[0] + a[1] * b[1]) + a[2] * b[2];
+}
+/* torch.sum(dim=-1) of a contiguous row: 8 vector lanes accumulated over full groups of 8,
+ * then tail elements, then the lanes, all added sequentially (ATen SumKernel inner reduction). */
+static float row_sum(const float *x, int d) {
+    float lanes[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    int nv = d / 8;
+    if (nv >= 4) { /* 4 interleaved accumulators per lane; not reached for d <= 31 */
+        float p[4][8];
+        memset(p, 0, sizeof(p));
+        int q = nv / 4;
+        for (int i = 0; i < q; ++i)
+            for (int k = 0; k < 4; ++k)
+                for (int l = 0; l < 8; ++l) p[k][l] += x[(4 * i + k) * 8 + l];
+        for (int i = 4 * q; i < nv; ++i)
+            for (int l = 0; l < 8; ++l) p[0][l] += x[i * 8 + l];
+        for (int l = 0; l < 8; ++l) lanes[l] = ((p[0][l] + p[1][l]) + p[2][l]) + p[3][l];
+    } else {
+        for (int i = 0; i < nv; ++i)
+            for (int l = 0; l < 8; ++l) lanes[l] += x[i * 8 + l];
+    }
+    float acc = 0.0f;
+    for (int k = nv * 8; k < d; ++k) acc += x[k];
+    if (nv > 0)
+        for (int l = 0; l < 8; ++l) acc += lanes[l];
+    return acc;
+}
+/* python-style remainder, torch.remainder(Tensor, Scalar): torch_jit_utils.py:195 */
+static inline float py_remainder(float a, float b) {
+    float m = fmodf(a, b);
+    if (m != 0.0f && ((b < 0.0f) != (m < 0.0f))) m += b;
+    return m;
+}
+
+/* utils/torch_jit_utils.py:41-62 quat_mul (xyzw), the 9-product form */
+static void quat_mul(const float *a, const float *b, float *out) {
+    float x1 = a[0], y1 = a[1], z1 = a[2], w1 = a[3];
+    float x2 = b[0], y2 = b[1], z2 = b[2], w2 = b[3];
+    float ww = (z1 + x1) * (x2 + y2);
+    float yy = (w1 - y1) * (w2 + z2);
+    float zz = (w1 + y1) * (w2 - z2);
+    float xx = ww + yy + zz;
+    float qq = 0.5f * (xx + (z1 - x1) * (x2 - y2));
+    float w = qq - ww + (z1 - y1) * (y2 - z2);
+    float x = qq - xx + (x1 + w1) * (x2 + w2);
+    float y = qq - yy + (w1 - x1) * (y2 + z2);
+    float z = qq - zz + (z1 + y1) * (w2 - x2);
+    out[0] = x; out[1] = y; out[2] = z; out[3] = w;
+}
+/* utils/torch_jit_utils.py:106-110 */
+static void quat_conjugate(const float *a, float *out) {
+    out[0] = -a[0]; out[1] = -a[1]; out[2] = -a[2]; out[3] = a[3];
+}
+/* torch.cross(dim=-1) */
+static void cross3(const float *a, const float *b, float *o) {
+    o[0] = a[1] * b[2] - a[2] * b[1];
+    o[1] = a[2] * b[0] - a[0] * b[2];
+    o[2] = a[0] * b[1] - a[1] * b[0];
+}
+/* utils/torch_jit_utils.py:80-90 (sign=+1) and :93-103 (sign=-1, quat_rotate_inverse) */
+static void quat_rotate_impl(const float *q, const float *v, int inverse, float *out) {
+    float qw = q[3];
+    float s = 2.0f * (qw * qw) - 1.0f;
+    float cr[3];
+    cross3(q, v, cr);
+    float d = dot3(q, v);
+    for (int i = 0; i < 3; ++i) {
+        float a = v[i] * s;
+        float b = cr[i] * qw * 2.0f;
+        float c = q[i] * d * 2.0f;
+        out[i] = inverse ? (a - b + c) : (a + b + c);
+    }
+}
+/* utils/torch_jit_utils.py:65-67 normalize: x / clamp(norm, min=1e-9) */
+static void normalize3(const float *x, float *out) {
+    float n = norm3(x[0], x[1], x[2]);
+    if (n < 1e-9f) n = 1e-9f;
+    out[0] = x[0] / n; out[1] = x[1] / n; out[2] = x[2] / n;
+}
+/* utils/torch_jit_utils.py:175-195 get_euler_xyz; only roll and yaw are consumed by the tasks */
+static void euler_roll_yaw(const float *q, float *roll, float *yaw) {
+    float qx = q[0], qy = q[1], qz = q[2], qw = q[3];
+    float sinr_cosp = 2.0f * (qw * qx + qy * qz);
+    float cosr_cosp = qw * qw - qx * qx - qy * qy + qz * qz;
+    float r = atan2f(sinr_cosp, cosr_cosp);
+    float siny_cosp = 2.0f * (qw * qz + qx * qy);
+    float cosy_cosp = qw * qw + qx * qx - qy * qy - qz * qz;
+    float y = atan2f(siny_cosp, cosy_cosp);
+    *roll = py_remainder(r, TWO_PI_F);
+    *yaw = py_remainder(y, TWO_PI_F);
+}
+/* utils/torch_jit_utils.py:126-128 */
+static inline float normalize_angle(float x) { return atan2f(sinf(x), cosf(x)); }
+
+/* Philox4x32-10 (Salmon et al. 2011), the counter-based generator the production kernels use
+ * when IgeResetRand.mode == IGE_RAND_PHILOX.  counter = (row, draw, step_lo, step_hi), key = seed. */
+static void philox4x32_10(uint32_t c[4], uint32_t k0, uint32_t k1) {
+    for (int r = 0; r < 10; ++r) {
+        uint64_t p0 = (uint64_t)0xD2511F53u * c[0];
+        uint64_t p1 = (uint64_t)0xCD9E8D57u * c[2];
+        uint32_t n0 = (uint32_t)(p1 >> 32) ^ c[1] ^ k0;
+        uint32_t n1 = (uint32_t)p1;
+        uint32_t n2 = (uint32_t)(p0 >> 32) ^ c[3] ^ k1;
+        uint32_t n3 = (uint32_t)p0;
+        c[0] = n0; c[1] = n1; c[2] = n2; c[3] = n3;
+        k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+    }
+}
+/* uniform in [0,1) with 24 bits, element `idx` of draw `draw` for row `row` */
+static float philox_uniform(const IgeResetRand *r, uint32_t row, uint32_t draw, uint32_t idx) {
+    uint64_t step = r->step ? *r->step : 0;
+    uint32_t c[4] = {row, (draw << 16) | (idx >> 2), (uint32_t)step, (uint32_t)(step >> 32)};
+    philox4x32_10(c, (uint32_t)r->seed, (uint32_t)(r->seed >> 32));
+    return (float)(c[idx & 3] >> 8) * (1.0f / 16777216.0f);
+}
+static float reset_uniform(const IgeResetRand *r, int which, int row, int d, int j) {
+    if (r->mode == IGE_RAND_PHILOX) return philox_uniform(r, (uint32_t)row, (uint32_t)which, (uint32_t)j);
+    const float *u = which ? r->u1 : r->u0;
+    return u[(size_t)r->reset_rank[row] * d + j];
+}
+
+static void add_stat(float *stats, int slot, double v) {
+    if (stats) stats[slot] += (float)v;
+}
+
+/* ------------------------------------------------------------------------------------------
+ * Minimal pthread parallel-for (no OpenMP runtime in this image).  Env ranges are independent.
+ * ------------------------------------------------------------------------------------------ */
+#include <pthread.h>
+#define IGE_ORACLE_MAX_THREADS 256
+#define IGE_ORACLE_NACC 8
+static int g_threads = 1;
+void ige_oracle_set_threads(int n) { g_threads = n < 1 ? 1 : (n > IGE_ORACLE_MAX_THREADS ? IGE_ORACLE_MAX_THREADS : n); }
+int ige_oracle_get_threads(void) { return g_threads; }
+typedef void (*range_fn)(const void *p, const void *b, int e0, int e1, double *acc);
+typedef struct { range_fn fn; const void *p, *b; int e0, e1; double acc[IGE_ORACLE_NACC]; } range_job;
+static void *range_thread(void *arg) {
+    range_job *j = (range_job *)arg;
+    j->fn(j->p, j->b, j->e0, j->e1, j->acc);
+    return NULL;
+}
+static void parallel_ranges(range_fn fn, const void *p, const void *b, int n, double *acc) {
+    int t = g_threads;
+    if (t > n / 64) t = n / 64;
+    if (t < 1) t = 1;
+    range_job jobs[IGE_ORACLE_MAX_THREADS];
+    pthread_t th[IGE_ORACLE_MAX_THREADS];
+    int chunk = (n + t - 1) / t;
+    for (int i = 0; i < t; ++i) {
+        jobs[i].fn = fn; jobs[i].p = p; jobs[i].b = b;
+        jobs[i].e0 = i * chunk; jobs[i].e1 = (i + 1) * chunk < n ? (i + 1) * chunk : n;
+        memset(jobs[i].acc, 0, sizeof(jobs[i].acc));
+        if (i > 0) pthread_create(&th[i], NULL, range_thread, &jobs[i]);
+    }
+    range_thread(&jobs[0]);
+    for (int i = 1; i < t; ++i) pthread_join(th[i], NULL);
+    for (int k = 0; k < IGE_ORACLE_NACC; ++k) {
+        acc[k] = 0;
+        for (int i = 0; i < t; ++i) acc[k] += jobs[i].acc[k];
+    }
+}
+
+/* ------------------------------------------------------------------------------------------
+ * reset_buf.nonzero() with the multi-agent AND filter (franka_reach_MA.py:875-884)
+ * ------------------------------------------------------------------------------------------ */
+int ige_oracle_compact_resets(const IgeCompactArgs *a) {
+    int g = a->group < 1 ? 1 : a->group;
+    int n = a->num_rows / g;
+    int cnt = 0;
+    for (int e = 0; e < n; ++e) {
+        int all = 1;
+        for (int k = 0; k < g; ++k) all &= (a->reset_buf[(size_t)e * g + k] != 0);
+        if (a->reset_rank) a->reset_rank[e] = cnt;
+        if (all) a->reset_ids[cnt++] = e;
+    }
+    *a->count = cnt;
+    if (a->step) *a->step += 1;
+    return 0;
+}
+
+/* ------------------------------------------------------------------------------------------
+ * Cartpole: tasks/cartpole.py:165-173 post_physics_step
+ * ------------------------------------------------------------------------------------------ */
+static void cartpole_range(const void *vp, const void *vb, int e0, int e1, double *acc) {
+    const IgeCartpoleParams *p = (const IgeCartpoleParams *)vp;
+    const IgeCartpoleBuffers *b = (const IgeCartpoleBuffers *)vb;
+    double s_rew = 0, s_done = 0, s_to = 0, s_len = 0;
+    for (int e = e0; e < e1; ++e) {
+        float *ds = b->dof_state + (size_t)e * 4; /* (cart pos, cart vel, pole pos, pole vel) */
+        int64_t progress = b->progress_buf[e] + 1; /* :166 */
+        int64_t reset = b->reset_buf[e];
+        if (reset != 0) { /* reset_idx :144-157 */
+            for (int j = 0; j < 2; ++j) {
+                ds[2 * j + 0] = 0.2f * (reset_uniform(&p->rand, 0, e, 2, j) - 0.5f); /* :145 */
+                ds[2 * j + 1] = 0.5f * (reset_uniform(&p->rand, 1, e, 2, j) - 0.5f); /* :146 */
+            }
+            reset = 0; progress = 0; /* :156-157 */
+        }
+        /* compute_observations :137-140 */
+        float cart_pos = ds[0], cart_vel = ds[1], pole_angle = ds[2], pole_vel = ds[3];
+        float *obs = b->obs_buf + (size_t)e * 4;
+        obs[0] = cart_pos; obs[1] = cart_vel; obs[2] = pole_angle; obs[3] = pole_vel;
+        /* compute_cartpole_reward :180-196 */
+        float reward = 1.0f - pole_angle * pole_angle - 0.01f * fabsf(cart_vel) - 0.005f * fabsf(pole_vel);
+        if (fabsf(cart_pos) > p->reset_dist) reward = -2.0f;
+        if (fabsf(pole_angle) > HALF_PI_F) reward = -2.0f;
+        if (fabsf(cart_pos) > p->reset_dist) reset = 1;
+        if (fabsf(pole_angle) > HALF_PI_F) reset = 1;
+        if ((float)progress >= p->max_episode_length - 1.0f) reset = 1;
+        b->rew_buf[e] = reward;
+        b->reset_buf[e] = reset;
+        b->progress_buf[e] = progress;
+        /* VecTask.step epilogue, tasks/base/vec_task.py:396,404 */
+        int timeout = ((float)progress >= p->max_episode_length - 1.0f) && (reset != 0);
+        if (b->timeout_buf) b->timeout_buf[e] = (uint8_t)timeout;
+        if (b->obs_clamped)
+            for (int j = 0; j < 4; ++j) {
+                float v = obs[j];
+                v = v < -p->clip_obs ? -p->clip_obs : v;
+                v = v > p->clip_obs ? p->clip_obs : v;
+                b->obs_clamped[(size_t)e * 4 + j] = v;
+            }
+        s_rew += reward; s_done += (reset != 0); s_to += timeout; s_len += (reset != 0) ? (double)progress : 0.0;
+    }
+    acc[0] = s_rew; acc[1] = s_done; acc[2] = s_to; acc[3] = s_len;
+}
+int ige_oracle_cartpole_post_physics(const IgeCartpoleParams *p, const IgeCartpoleBuffers *b) {
+    double acc[IGE_ORACLE_NACC];
+    parallel_ranges(cartpole_range, p, b, p->num_envs, acc);
+    add_stat(b->stats, IGE_STAT_STEPS, p->num_envs); add_stat(b->stats, IGE_STAT_REWARD, acc[0]);
+    add_stat(b->stats, IGE_STAT_DONE, acc[1]); add_stat(b->stats, IGE_STAT_TIMEOUT, acc[2]);
+    add_stat(b->stats, IGE_STAT_DONE_LENGTH, acc[3]);
+    return 0;
+}
+
+/* ------------------------------------------------------------------------------------------
+ * Ant / Humanoid: tasks/ant.py:287-297, tasks/humanoid.py:287-296
+ * ------------------------------------------------------------------------------------------ */
+static inline float neg_norm_over_dt(const IgeLocomotionParams *p, float tx, float ty) {
+    float nn = -norm3(tx, ty, 0.0f);
+    return p->potentials_recip_mul ? nn * (1.0f / p->dt) : nn / p->dt;
+}
+
+static void locomotion_range(const IgeLocomotionParams *p, const IgeLocomotionBuffers *b, int humanoid,
+                             int e0, int e1, double *acc) {
+    const int d = p->num_dof, ns = p->num_sensor_floats;
+    const int num_obs = 12 + 3 * d + ns + (humanoid ? d : 0);
+    double s_rew = 0, s_done = 0, s_to = 0, s_len = 0, s_obj = 0;
+    for (int e = e0; e < e1; ++e) {
+        const float *root = b->root_states + (size_t)e * 13;
+        float *dof = b->dof_state + (size_t)e * d * 2;
+        const float *act = b->actions + (size_t)e * d;
+        float *obs = b->obs_buf + (size_t)e * num_obs;
+        int64_t progress = b->progress_buf[e] + 1; /* ant.py:288 */
+        if (b->randomize_buf) b->randomize_buf[e] += 1; /* ant.py:289 */
+        int64_t reset = b->reset_buf[e];
+        float potentials = b->potentials[e];
+
+        if (reset != 0) { /* reset_idx: ant.py:252-279, humanoid.py:253-279 */
+            for (int j = 0; j < d; ++j) {
+                /* torch_rand_float(-0.2, 0.2): (upper - lower) * rand + lower, torch_jit_utils.py:215-218 */
+                float pos = 0.4f * reset_uniform(&p->rand, 0, e, d, j) + (-0.2f);
+                float vel = 0.2f * reset_uniform(&p->rand, 1, e, d, j) + (-0.1f);
+                float v = b->initial_dof_pos[(size_t)e * d + j] + pos;
+                v = fminf(v, p->dof_limits_upper[j]); /* tensor_clamp, torch_jit_utils.py:228-230 */
+                v = fmaxf(v, p->dof_limits_lower[j]);
+                dof[2 * j + 0] = v;   /* ant.py:260 */
+                dof[2 * j + 1] = vel; /* ant.py:261 */
+            }
+            const float *init = b->initial_root_states + (size_t)e * 13;
+            float tx = p->targets[0] - init[0], ty = p->targets[1] - init[1]; /* ant.py:273-274 */
+            potentials = neg_norm_over_dt(p, tx, ty); /* ant.py:275-276 (prev == potentials) */
+            progress = 0; reset = 0; /* ant.py:278-279 */
+        }
+
+        /* compute_ant_observations ant.py:374-408 / compute_humanoid_observations humanoid.py:378-413 */
+        float to_target[3] = {p->targets[0] - root[0], p->targets[1] - root[1], 0.0f};
+        float prev_potentials = potentials;                             /* ant.py:390 */
+        potentials = neg_norm_over_dt(p, to_target[0], to_target[1]);   /* ant.py:391 */
+
+        /* compute_heading_and_up torch_jit_utils.py:247-262 */
+        float target_dirs[3], torso_quat[4], up_vec[3], heading_vec[3];
+        normalize3(to_target, target_dirs);
+        quat_mul(root + 3, p->inv_start_rot, torso_quat);
+        quat_rotate_impl(torso_quat, p->basis_vec1, 0, up_vec);
+        quat_rotate_impl(torso_quat, p->basis_vec0, 0, heading_vec);
+        float up_proj = up_vec[2];
+        float heading_proj = dot3(heading_vec, target_dirs);
+
+        /* compute_rot torch_jit_utils.py:265-276 */
+        float vel_loc[3], angvel_loc[3], roll, yaw;
+        quat_rotate_impl(torso_quat, root + 7, 1, vel_loc);
+        quat_rotate_impl(torso_quat, root + 10, 1, angvel_loc);
+        euler_roll_yaw(torso_quat, &roll, &yaw);
+        float walk_target_angle = atan2f(p->targets[2] - root[2], p->targets[0] - root[0]);
+        float angle_to_target = walk_target_angle - yaw;
+
+        obs[0] = root[2];
+        for (int i = 0; i < 3; ++i) obs[1 + i] = vel_loc[i];
+        if (humanoid) {
+            for (int i = 0; i < 3; ++i) obs[4 + i] = angvel_loc[i] * p->angular_velocity_scale;
+            obs[7] = normalize_angle(yaw);              /* humanoid.py:402-404 */
+            obs[8] = normalize_angle(roll);
+            obs[9] = normalize_angle(angle_to_target);
+        } else {
+            for (int i = 0; i < 3; ++i) obs[4 + i] = angvel_loc[i];
+            obs[7] = yaw; obs[8] = roll; obs[9] = angle_to_target; /* ant.py:403 */
+        }
+        obs[10] = up_proj;
+        obs[11] = heading_proj;
+        for (int j = 0; j < d; ++j) {
+            float lo = p->dof_limits_lower[j], hi = p->dof_limits_upper[j];
+            obs[12 + j] = (2.0f * dof[2 * j] - hi - lo) / (hi - lo); /* unscale torch_jit_utils.py:238-240 */
+            obs[12 + d + j] = dof[2 * j + 1] * p->dof_vel_scale;
+        }
+        int o = 12 + 2 * d;
+        if (humanoid) {
+            for (int j = 0; j < d; ++j) obs[o + j] = b->dof_force_tensor[(size_t)e * d + j] * p->contact_force_scale;
+            o += d;
+        }
+        for (int j = 0; j < ns; ++j) obs[o + j] = b->vec_sensor_tensor[(size_t)e * ns + j] * p->contact_force_scale;
+        o += ns;
+        for (int j = 0; j < d; ++j) obs[o + j] = act[j];
+
+        /* compute_ant_reward ant.py:325-371 / compute_humanoid_reward humanoid.py:323-375 */
+        float heading_reward = obs[11] > 0.8f ? p->heading_weight : p->heading_weight * obs[11] / 0.8f;
+        float up_reward = obs[10] > 0.93f ? 0.0f + p->up_weight : 0.0f;
+        float tmp[IGE_MAX_DOF];
+        for (int j = 0; j < d; ++j) tmp[j] = act[j] * act[j];
+        float actions_cost = row_sum(tmp, d);
+        float total;
+        float progress_reward = potentials - prev_potentials;
+        if (humanoid) {
+            for (int j = 0; j < d; ++j) {
+                float a = fabsf(obs[12 + j]);
+                float scaled = p->joints_at_limit_cost_scale * (a - 0.98f) / 0.02f; /* humanoid.py:356 */
+                tmp[j] = (a > 0.98f ? 1.0f : 0.0f) * scaled * p->motor_effort_ratio[j];
+            }
+            float dof_at_limit_cost = row_sum(tmp, d);
+            for (int j = 0; j < d; ++j) tmp[j] = fabsf(act[j] * obs[12 + d + j]) * p->motor_effort_ratio[j];
+            float electricity_cost = row_sum(tmp, d);
+            total = progress_reward + 2.0f + up_reward + heading_reward - p->actions_cost_scale * actions_cost -
+                    p->energy_cost_scale * electricity_cost - dof_at_limit_cost;
+        } else {
+            for (int j = 0; j < d; ++j) tmp[j] = fabsf(act[j] * obs[12 + d + j]);
+            float electricity_cost = row_sum(tmp, d);
+            int64_t dof_at_limit = 0;
+            for (int j = 0; j < d; ++j) dof_at_limit += obs[12 + j] > 0.99f;
+            total = progress_reward + 0.5f + up_reward + heading_reward - p->actions_cost_scale * actions_cost -
+                    p->energy_cost_scale * electricity_cost - (float)dof_at_limit * p->joints_at_limit_cost_scale;
+        }
+        if (obs[0] < p->termination_height) total = p->death_cost; /* ant.py:365 */
+        if (obs[0] < p->termination_height) reset = 1;             /* ant.py:368 */
+        if ((float)progress >= p->max_episode_length - 1.0f) reset = 1; /* ant.py:369 */
+
+        b->rew_buf[e] = total;
+        b->reset_buf[e] = reset;
+        b->progress_buf[e] = progress;
+        b->potentials[e] = potentials;
+        b->prev_potentials[e] = prev_potentials;
+        for (int i = 0; i < 3; ++i) {
+            b->up_vec[(size_t)e * 3 + i] = up_vec[i];
+            b->heading_vec[(size_t)e * 3 + i] = heading_vec[i];
+        }
+        int timeout = ((float)progress >= p->max_episode_length - 1.0f) && (reset != 0); /* vec_task.py:396 */
+        if (b->timeout_buf) b->timeout_buf[e] = (uint8_t)timeout;
+        if (b->obs_clamped)
+            for (int j = 0; j < num_obs; ++j) {
+                float v = obs[j];
+                v = v < -p->clip_obs ? -p->clip_obs : v;
+                v = v > p->clip_obs ? p->clip_obs : v;
+                b->obs_clamped[(size_t)e * num_obs + j] = v;
+            }
+        s_rew += total; s_done += (reset != 0); s_to += timeout;
+        s_len += (reset != 0) ? (double)progress : 0.0; s_obj += root[7];
+    }
+    acc[0] = s_rew; acc[1] = s_done; acc[2] = s_to; acc[3] = s_len; acc[4] = s_obj;
+}
+static void ant_range(const void *p, const void *b, int e0, int e1, double *acc) {
+    locomotion_range((const IgeLocomotionParams *)p, (const IgeLocomotionBuffers *)b, 0, e0, e1, acc);
+}
+static void humanoid_range(const void *p, const void *b, int e0, int e1, double *acc) {
+    locomotion_range((const IgeLocomotionParams *)p, (const IgeLocomotionBuffers *)b, 1, e0, e1, acc);
+}
+static int locomotion_post_physics(const IgeLocomotionParams *p, const IgeLocomotionBuffers *b, int humanoid) {
+    double acc[IGE_ORACLE_NACC];
+    parallel_ranges(humanoid ? humanoid_range : ant_range, p, b, p->num_envs, acc);
+    add_stat(b->stats, IGE_STAT_STEPS, p->num_envs); add_stat(b->stats, IGE_STAT_REWARD, acc[0]);
+    add_stat(b->stats, IGE_STAT_DONE, acc[1]); add_stat(b->stats, IGE_STAT_TIMEOUT, acc[2]);
+    add_stat(b->stats, IGE_STAT_DONE_LENGTH, acc[3]); add_stat(b->stats, IGE_STAT_TASK0, acc[4]);
+    return 0;
+}
+
+int ige_oracle_ant_post_physics(const IgeLocomotionParams *p, const IgeLocomotionBuffers *b) {
+    return locomotion_post_physics(p, b, 0);
+}
+int ige_oracle_humanoid_post_physics(const IgeLocomotionParams *p, const IgeLocomotionBuffers *b) {
+    return locomotion_post_physics(p, b, 1);
+}

@@ -1,0 +1,177 @@
+"""Shared test plumbing: drive the CPU oracle and the CUDA path through the SAME mirror classes
+(and therefore the same C-ABI structs), and compare buffers with the parity bars of the task
+(flags / counters / ids bit-exact, floats |d| <= 1e-5 * max(1, |ref|))."""
+import ctypes as C
+import glob
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from ige_loader import load_package  # noqa: E402
+
+pkg = load_package()
+from oracle import oracle  # noqa: E402
+
+GOLDEN_DIR = os.path.join(ROOT, "tests", "golden")
+RTOL = 1e-5   # north_star: observations and rewards within 1e-5 relative in fp32
+
+TASK_NAME = {"cartpole": "Cartpole", "ant": "Ant", "humanoid": "Humanoid"}
+ENTRY = {"cartpole": "cartpole_post_physics", "ant": "ant_post_physics", "humanoid": "humanoid_post_physics"}
+FLOAT_OUT = {
+    "cartpole": ["obs_buf", "rew_buf", "dof_state"],
+    "ant": ["obs_buf", "rew_buf", "dof_state", "potentials", "prev_potentials", "up_vec", "heading_vec"],
+    "humanoid": ["obs_buf", "rew_buf", "dof_state", "potentials", "prev_potentials", "up_vec", "heading_vec"],
+}
+INT_OUT = {
+    "cartpole": ["reset_buf", "progress_buf"],
+    "ant": ["reset_buf", "progress_buf", "randomize_buf"],
+    "humanoid": ["reset_buf", "progress_buf", "randomize_buf"],
+}
+BITEXACT_FLOAT = {"cartpole": ["dof_state"], "ant": ["potentials", "prev_potentials", "dof_state"],
+                  "humanoid": ["potentials", "prev_potentials", "dof_state"]}
+
+
+def golden_files(task):
+    return sorted(glob.glob(os.path.join(GOLDEN_DIR, f"{task}_n*.npz")))
+
+
+def load_golden(path):
+    z = np.load(path, allow_pickle=False)
+    return {k: z[k] for k in z.files}
+
+
+def init_state(blob):
+    return {k[len("init/"):]: v.copy() for k, v in blob.items() if k.startswith("init/")}
+
+
+def step_inputs(blob, s):
+    pre = f"step{s}/in/"
+    return {k[len(pre):]: v for k, v in blob.items() if k.startswith(pre)}
+
+
+def step_outputs(blob, s):
+    pre = f"step{s}/out/"
+    return {k[len(pre):]: v for k, v in blob.items() if k.startswith(pre)}
+
+
+def step_rands(blob, s):
+    out = []
+    i = 0
+    while f"step{s}/rand{i}" in blob:
+        out.append(blob[f"step{s}/rand{i}"])
+        i += 1
+    return out
+
+
+def step_call_indices(blob, s):
+    out = []
+    i = 0
+    while f"step{s}/call{i}/name" in blob:
+        if f"step{s}/call{i}/indices" in blob:
+            out.append((str(blob[f"step{s}/call{i}/name"]), blob[f"step{s}/call{i}/indices"]))
+        i += 1
+    return out
+
+
+def build(task, st, device, **kw):
+    kw.setdefault("rand_mode", "injected")
+    return pkg.factory.from_state(TASK_NAME[task], st, device, **kw)
+
+
+def oracle_compact(obj, group=1):
+    a = pkg._abi.IgeCompactArgs()
+    a.num_rows = obj.reset_buf.numel()
+    a.group = group
+    a.reset_buf = obj.reset_buf.data_ptr()
+    a.reset_ids = obj.reset_env_ids.data_ptr()
+    a.reset_rank = obj.reset_rank.data_ptr()
+    a.count = obj.reset_count.data_ptr()
+    a.step = obj.rng_step.data_ptr()
+    oracle.call("compact_resets", a)
+    return int(obj.reset_count.item())
+
+
+def oracle_step(task, obj, rands=None):
+    """One post_physics_step of the CPU oracle on a mirror object whose tensors live on the CPU."""
+    assert obj.device.type == "cpu"
+    k = oracle_compact(obj)
+    ids = obj.reset_env_ids[:k].clone()
+    if obj.rand_mode != "philox":
+        if rands:
+            obj.set_injected_uniforms(*[torch.from_numpy(np.ascontiguousarray(r)) for r in rands])
+        else:
+            assert k == 0, "injected mode needs the uniforms"
+    p, b = obj.abi_structs()
+    oracle.call(ENTRY[task], p, b)
+    obj._u0 = obj._u1 = None
+    return ids
+
+
+def cuda_step(task, obj, rands=None):
+    """One post_physics_step of the product CUDA path; returns the reset id list it emitted."""
+    if obj.rand_mode != "philox" and rands:
+        obj.set_injected_uniforms(*[torch.from_numpy(np.ascontiguousarray(r)).to(obj.device) for r in rands])
+    obj.post_physics_step()
+    k = int(obj.reset_count.item())
+    return obj.reset_env_ids[:k].clone()
+
+
+def get(obj, name):
+    if name == "obs_clamped":
+        return obj.obs_clamped.detach().cpu().numpy()
+    if name == "time_outs":
+        return obj.timeout_bool.detach().cpu().numpy()
+    return getattr(obj, name).detach().cpu().numpy()
+
+
+def assert_float_close(name, got, ref, rtol=RTOL):
+    got = np.asarray(got, dtype=np.float64).reshape(-1)
+    ref = np.asarray(ref, dtype=np.float64).reshape(-1)
+    assert got.shape == ref.shape, f"{name}: shape {got.shape} vs {ref.shape}"
+    err = np.abs(got - ref)
+    bound = rtol * np.maximum(1.0, np.abs(ref))
+    bad = ~(err <= bound)
+    if bad.any():
+        i = int(np.argmax(err / bound))
+        raise AssertionError(f"{name}: {int(bad.sum())}/{bad.size} outside 1e-5 rel; worst idx {i}: "
+                             f"got {got[i]!r} ref {ref[i]!r} |d|={err[i]:.3e}")
+
+
+def assert_equal(name, got, ref):
+    got, ref = np.asarray(got), np.asarray(ref)
+    assert got.shape == ref.shape, f"{name}: shape {got.shape} vs {ref.shape}"
+    if not np.array_equal(got, ref):
+        bad = np.flatnonzero(got.reshape(-1) != ref.reshape(-1))
+        raise AssertionError(f"{name}: {bad.size} mismatches, first idx {bad[0]}: "
+                             f"got {got.reshape(-1)[bad[0]]} ref {ref.reshape(-1)[bad[0]]}")
+
+
+def bitexact_fraction(got, ref):
+    g = np.ascontiguousarray(got, dtype=np.float32).view(np.uint32).reshape(-1)
+    r = np.ascontiguousarray(ref, dtype=np.float32).view(np.uint32).reshape(-1)
+    return float((g == r).mean())
+
+
+def compare_outputs(task, obj, ref_out, check_epilogue=True, bitexact=()):
+    """ref_out: dict name -> numpy array (golden fixture or another mirror's buffers)."""
+    for name in INT_OUT[task]:
+        assert_equal(name, get(obj, name), ref_out[name])
+    for name in FLOAT_OUT[task]:
+        assert_float_close(name, get(obj, name), ref_out[name])
+    for name in bitexact:
+        assert_equal(name + " (bit-exact)", get(obj, name).view(np.uint32), np.asarray(ref_out[name]).view(np.uint32))
+    if check_epilogue and obj.fuse_epilogue and "obs_clamped" in ref_out:
+        assert_float_close("obs_clamped", get(obj, "obs_clamped"), ref_out["obs_clamped"])
+        assert_equal("time_outs", get(obj, "time_outs").astype(bool), np.asarray(ref_out["time_outs"]).astype(bool))
+
+
+def snapshot(task, obj):
+    out = {n: get(obj, n).copy() for n in INT_OUT[task] + FLOAT_OUT[task]}
+    if obj.fuse_epilogue:
+        out["obs_clamped"] = get(obj, "obs_clamped").copy()
+        out["time_outs"] = get(obj, "time_outs").copy()
+    return out

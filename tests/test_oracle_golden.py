@@ -1,0 +1,35 @@
+"""Pin the CPU oracle (oracle/ige_oracle.c) against fixtures minted from the unmodified reference
+(tests/golden/gen_golden.py).  Runs anywhere (no GPU, no reference tree)."""
+import numpy as np
+import pytest
+
+import harness as H
+
+
+def _run_fixture(task, path):
+    blob = H.load_golden(path)
+    st = H.init_state(blob)
+    obj = H.build(task, st, "cpu")
+    steps = int(blob["meta_steps"])
+    worst = {}
+    for s in range(steps):
+        H.pkg.factory.load_sim_inputs(obj, H.TASK_NAME[task], H.step_inputs(blob, s))
+        ids = H.oracle_step(task, obj, H.step_rands(blob, s))
+        ref = H.step_outputs(blob, s)
+        H.assert_equal("reset_env_ids", ids.numpy(), ref["reset_env_ids"])
+        for cname, idx in H.step_call_indices(blob, s):
+            H.assert_equal(f"{cname} indices", ids.numpy(), idx)
+        H.compare_outputs(task, obj, ref, bitexact=H.BITEXACT_FLOAT[task])
+        for name in H.FLOAT_OUT[task]:
+            worst[name] = min(worst.get(name, 1.0), H.bitexact_fraction(H.get(obj, name), ref[name]))
+    return worst
+
+
+@pytest.mark.parametrize("task", ["cartpole", "ant", "humanoid"])
+def test_oracle_matches_reference_golden(task):
+    files = H.golden_files(task)
+    assert files, f"no golden fixtures for {task}"
+    for path in files:
+        worst = _run_fixture(task, path)
+        # the restatement is op-for-op: everything but libm-vs-sleef transcendentals is bit-exact
+        assert worst["rew_buf"] > 0.9, worst
