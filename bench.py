@@ -1,0 +1,403 @@
+#!/usr/bin/env python
+"""bench.py -- env-steps/sec of the fused post-physics step (obs + reward + done + reset).
+
+Contract (driver): `python bench.py --gpus N --steps K --warmup W [--impl reference]`, under
+torchrun for N > 1 (one rank per GPU); rank 0 prints ONE JSON line.
+
+Workload at every N: BASELINE.json configs[1] / configs[4] -- Ant post_physics_step, 16384 envs per
+GPU, synthetic post-simulate state (isaacgymenvs-ma_b200/synthetic.py), natural reset rate.
+A "step" is one pass of the hot path over all envs of a GPU: device-side `reset_buf.nonzero()`
+(ige_compact_resets) + ONE fused kernel (ige_ant_post_physics), replayed from a CUDA graph.
+
+L2 hygiene: the timed loop rotates through `replicas` independent copies of the whole env state
+whose total footprint exceeds 2x the 126 MB L2, so every step streams its tile from HBM.
+
+Keys beyond the base contract: `roofline` (dominant kernel, algorithmic bytes / measured launch
+duration vs MEASURED_PEAKS.json), `cpu_baseline` (CPU port on the host cores), `e2e` (host buffers
+in pinned memory -> H2D -> step -> D2H every step), `clocks`, `gpu_launches`, `sweep`.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+
+from ige_loader import load_package  # noqa: E402
+
+# frozen algorithmic bytes per env-step (SURVEY.md 8d / BASELINE.md section 2)
+ALGO_BYTES = {"Cartpole": 68, "Ant": 556, "Humanoid": 940}
+ALGO_BYTES_EPILOGUE = {"Cartpole": 85, "Ant": 797, "Humanoid": 1373}
+L2_BYTES = 126 * 1024 * 1024
+HORIZON = 16  # cfg/train/AntPPO.yaml:65 horizon_length -> one stats all-reduce per horizon
+
+
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured"
+    return 6650.0, "fallback"
+
+
+class ClockSampler:
+    """Samples nvidia-smi SM clocks / throttle reasons while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.idx, self.samples, self._stop, self._t = gpu_index, [], threading.Event(), None
+
+    def _once(self):
+        try:
+            out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i",
+                                  str(self.idx)], capture_output=True, text=True, timeout=5).stdout.strip()
+            if out:
+                self.samples.append([x.strip() for x in out.split(",")])
+        except Exception:
+            pass
+
+    def _run(self):
+        while not self._stop.is_set():
+            self._once()
+            self._stop.wait(0.1)
+
+    def __enter__(self):
+        self.t0 = time.time()
+        self._t = threading.Thread(target=self._run, daemon=True)
+        self._t.start()
+        return self
+
+    def __exit__(self, *a):
+        self._stop.set()
+        self._t.join(timeout=10)
+        if not self.samples:
+            self._once()
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        sm = sorted(float(s[0]) for s in self.samples if s[0].replace(".", "").isdigit())
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(s[2 + i].lower().startswith("active") for s in self.samples)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": float(self.samples[0][1]),
+                "reasons": reasons, "samples": len(self.samples)}
+
+
+def build_replicas(pkg, task, num_envs, replicas, device, seed, fall_frac, fuse_epilogue, rank):
+    envs = []
+    for r in range(replicas):
+        st = pkg.synthetic.make_state(task.lower(), num_envs, seed=seed + 1000 * rank + r, reset_prob=0.02,
+                                      fall_frac=fall_frac)
+        env = pkg.factory.from_state(task, st, device, rand_mode="philox", seed=seed + rank,
+                                     fuse_epilogue=fuse_epilogue)
+        env.sim.record = False
+        envs.append(env)
+    return envs
+
+
+def capture(envs, fn):
+    """Capture fn(env) for every env of `envs`, in order, into one CUDA graph."""
+    g = torch.cuda.CUDAGraph()
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        for e in envs:      # warm (module load etc.) outside capture
+            fn(e)
+    torch.cuda.current_stream().wait_stream(s)
+    torch.cuda.synchronize()
+    with torch.cuda.graph(g):
+        for e in envs:
+            fn(e)
+    return g
+
+
+def run_ours(args):
+    pkg = load_package()
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the post-physics kernels have no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    device = torch.device("cuda", local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=device)
+
+    task, n = args.task, args.num_envs
+    algo = ALGO_BYTES[task]
+    state_bytes = ALGO_BYTES_EPILOGUE[task] * n
+    replicas = args.replicas or max(2 * HORIZON, -(-2 * L2_BYTES // state_bytes))
+    replicas = -(-replicas // HORIZON) * HORIZON
+    envs = build_replicas(pkg, task, n, replicas, device, args.seed, args.fall_frac, False, rank)
+    lib = pkg._lib
+
+    # ---- graphs: chunks of HORIZON consecutive replicas (one stats all-reduce per chunk) ----
+    chunks = [(capture(envs[i:i + HORIZON], lambda e: e.post_physics_step()), HORIZON)
+              for i in range(0, replicas, HORIZON)]
+    single = [(capture([e], lambda e: e.post_physics_step()), 1) for e in envs[:HORIZON]]
+    stats_snap = torch.zeros_like(envs[0].stats)
+    pending = []
+
+    def allreduce_stats():
+        # episode statistics: <= 16 floats, once per horizon, off the critical path
+        if dist is None:
+            return
+        stats_snap.copy_(envs[0].stats)
+        pending.append(dist.all_reduce(stats_snap, async_op=True))
+
+    def timed(steps, warmup):
+        full, rem = divmod(steps, HORIZON)
+        def body():
+            for i in range(full):
+                chunks[i % len(chunks)][0].replay()
+                allreduce_stats()
+            for i in range(rem):
+                single[i][0].replay()
+        wfull = -(-warmup // HORIZON)
+        for i in range(max(wfull, 1)):
+            chunks[i % len(chunks)][0].replay()
+        allreduce_stats()
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+        t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0.record()
+        body()
+        t1.record()
+        torch.cuda.synchronize()
+        for w in pending:
+            w.wait()
+        pending.clear()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+        return t0.elapsed_time(t1) * 1e-3
+
+    clk = ClockSampler(local_rank)
+    clk.__enter__()
+    elapsed = timed(args.steps, args.warmup)
+    if dist is not None:
+        t = torch.tensor([elapsed], device=device, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        elapsed = float(t.item())
+    value = n * world * args.steps / elapsed
+    kernels_per_step = 2
+    gpu_launches = args.steps * kernels_per_step
+
+    # ---- dominant kernel alone (roofline): fused kernel only, same rotation, CUDA events ----
+    def kernel_only(e):
+        p, b = e.abi_structs()
+        lib.call(e.ENTRY, p, b, stream=torch.cuda.current_stream().cuda_stream)
+    kgraph = capture(envs, kernel_only)
+    for _ in range(3):
+        kgraph.replay()
+    torch.cuda.synchronize()
+    reps = max(1, 4096 // replicas)
+    k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    k0.record()
+    for _ in range(reps):
+        kgraph.replay()
+    k1.record()
+    torch.cuda.synchronize()
+    kernel_s = k0.elapsed_time(k1) * 1e-3 / (reps * replicas)
+    peak, peak_kind = measured_peaks()
+    achieved = algo * n / kernel_s / 1e9
+
+    out = {
+        "metric": "env-steps/sec (obs+reward+reset)", "value": value, "unit": "env-steps/s",
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": elapsed / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"{task} post_physics_step num_envs={n} per GPU (BASELINE.json configs[1])",
+                   "task": task, "num_envs_per_gpu": n, "global_envs": n * world,
+                   "parallelism": f"env-shard x{world}", "reset": "natural (2% fallen envs/step), in-kernel Philox",
+                   "l2": f"inputs larger than L2: rotating {replicas} state replicas = "
+                         f"{replicas * state_bytes / 2**20:.0f} MiB > 126 MiB L2",
+                   "launch": f"CUDA graph, {HORIZON} steps per graph; stats all-reduce every {HORIZON} steps"},
+        "gpu_launches": gpu_launches,
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "traffic": None, "peak_source": f"MEASURED_PEAKS.json hbm_gbs ({peak_kind})",
+                     "kernel": f"locomotion_post_physics_kernel<{task}>", "kernel_us": kernel_s * 1e6,
+                     "algorithmic_bytes_per_env": algo},
+    }
+    if not args.no_e2e:
+        out["e2e"] = run_e2e(pkg, args, device, dist=dist, world=world)   # collective: every rank runs it
+    if rank == 0 and world == 1 and not args.no_sweep:
+        out["sweep"] = run_sweep(pkg, args, device, peak)
+    # keep sampling for >= 1 s of GPU load so that short runs still see clocks under load
+    t_end = time.time() + max(0.0, 1.0 - (time.time() - clk.t0))
+    while time.time() < t_end:
+        chunks[0][0].replay()
+        torch.cuda.synchronize()
+    clk.__exit__()
+    out["clocks"] = clk.summary()
+    if rank == 0 and world == 1 and not args.no_cpu:
+        out["cpu_baseline"] = cpu_baseline(pkg, args, seconds=args.cpu_seconds)
+    if rank == 0:
+        print(json.dumps(out))
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def run_e2e(pkg, args, device, dist=None, world=1):
+    """Same metric through the public API with HOST buffers: every step copies the simulator
+    tensors + actions from pinned host memory, runs post_physics_step, and reads obs / rew / reset
+    back to pinned host memory."""
+    task, n = args.task, args.num_envs
+    st = pkg.synthetic.make_state(task.lower(), n, seed=args.seed + 77, reset_prob=0.02, fall_frac=args.fall_frac)
+    env = pkg.factory.from_state(task, st, device, rand_mode="philox", seed=args.seed, fuse_epilogue=False)
+    env.sim.record = False
+    names = pkg.factory.sim_tensor_names(task) + ["actions"]
+    dev_in = [env.sim.tensors[k] if k in env.sim.tensors else getattr(env, k) for k in names]
+    host_in = [torch.empty(t.shape, dtype=t.dtype).pin_memory().copy_(t.cpu()) for t in dev_in]
+    dev_out = [env.obs_buf, env.rew_buf, env.reset_buf]
+    host_out = [torch.empty(t.shape, dtype=t.dtype).pin_memory() for t in dev_out]
+    h2d = sum(t.numel() * t.element_size() for t in host_in)
+    d2h = sum(t.numel() * t.element_size() for t in host_out)
+
+    def step():
+        for d, h in zip(dev_in, host_in):
+            d.copy_(h, non_blocking=True)
+        env.post_physics_step()
+        for d, h in zip(dev_out, host_out):
+            h.copy_(d, non_blocking=True)
+
+    for _ in range(max(3, args.warmup)):
+        step()
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+    steps = args.steps
+    t0 = time.perf_counter()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        step()
+    e1.record()
+    torch.cuda.synchronize()
+    wall = time.perf_counter() - t0
+    el = max(e0.elapsed_time(e1) * 1e-3, 0.0)
+    el = max(el, wall * 0.0 + el)
+    if dist is not None:
+        t = torch.tensor([el], device=device, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        el = float(t.item())
+    return {"value": n * world * steps / el, "unit": "env-steps/s", "h2d_bytes_per_step": h2d,
+            "d2h_bytes_per_step": d2h, "ms_per_step": el / steps * 1e3, "wall_ms_per_step": wall / steps * 1e3,
+            "api": "Ant.post_physics_step() (ctypes -> ige_compact_resets + ige_ant_post_physics), pinned host buffers"}
+
+
+def run_sweep(pkg, args, device, peak):
+    """Roofline of the fused kernel vs num_envs: same kernel, larger batches."""
+    res = []
+    task = args.task
+    for n in (16384, 65536, 262144, 1048576):
+        per = ALGO_BYTES_EPILOGUE[task] * n
+        reps = max(2, min(32, -(-2 * L2_BYTES // per)))
+        envs = build_replicas(pkg, task, n, reps, device, args.seed + 5, args.fall_frac, False, 0)
+
+        def kernel_only(e):
+            p, b = e.abi_structs()
+            pkg._lib.call(e.ENTRY, p, b, stream=torch.cuda.current_stream().cuda_stream)
+        g = capture(envs, kernel_only)
+        for _ in range(3):
+            g.replay()
+        torch.cuda.synchronize()
+        loops = max(1, 512 // reps)
+        a, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(loops):
+            g.replay()
+        b_.record()
+        torch.cuda.synchronize()
+        t = a.elapsed_time(b_) * 1e-3 / (loops * reps)
+        gbs = ALGO_BYTES[task] * n / t / 1e9
+        res.append({"num_envs": n, "kernel_us": t * 1e6, "achieved_gbs": gbs, "frac": gbs / peak,
+                    "env_steps_per_s": n / t})
+        del envs, g
+        torch.cuda.empty_cache()
+    return res
+
+
+def cpu_baseline(pkg, args, seconds=6.0, steps=None, warmup=3):
+    """The CPU port (oracle/ige_oracle.c, plain C + pthreads) of the same step on the host cores."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import harness as H
+    from oracle import oracle
+    task, n = args.task, args.num_envs
+    cores = os.cpu_count() or 1
+    oracle.lib().ige_oracle_set_threads(cores)
+    st = pkg.synthetic.make_state(task.lower(), n, seed=args.seed, reset_prob=0.02, fall_frac=args.fall_frac)
+    obj = H.build(task.lower(), st, "cpu", rand_mode="philox", fuse_epilogue=False)
+    for _ in range(warmup):
+        H.oracle_step(task.lower(), obj)
+    done, t0 = 0, time.perf_counter()
+    while True:
+        H.oracle_step(task.lower(), obj)
+        done += 1
+        if steps is not None:
+            if done >= steps:
+                break
+        elif time.perf_counter() - t0 >= seconds:
+            break
+    el = time.perf_counter() - t0
+    return {"value": n * done / el, "unit": "env-steps/s", "cores": cores, "kind": "port",
+            "sample": f"{done} steps of {task} num_envs={n} (oracle/ige_oracle.c, {cores} pthreads), "
+                      f"{el:.1f} s", "ms_per_step": el / done * 1e3}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    pkg = load_package()
+    cb = cpu_baseline(pkg, args, steps=args.steps, warmup=max(args.warmup, 1))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    out = {"impl": "reference", "metric": "env-steps/sec (obs+reward+reset)", "value": cb["value"],
+           "unit": "env-steps/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+           "ms_per_step": cb["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+           "dtype": "f32", "data": "synthetic",
+           "config": {"workload": f"{args.task} post_physics_step num_envs={args.num_envs} (CPU, host cores)",
+                      "task": args.task, "num_envs_per_gpu": args.num_envs},
+           "cpu_baseline": cb,
+           "e2e": {"value": cb["value"], "unit": "env-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+           "gpu_launches": 0}
+    print(json.dumps(out))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=2048)
+    ap.add_argument("--warmup", type=int, default=64)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--task", default="Ant", choices=list(ALGO_BYTES))
+    ap.add_argument("--num-envs", type=int, default=16384)
+    ap.add_argument("--replicas", type=int, default=0)
+    ap.add_argument("--seed", type=int, default=0)
+    ap.add_argument("--fall-frac", type=float, default=0.02)
+    ap.add_argument("--cpu-seconds", type=float, default=6.0)
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-sweep", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -168,6 +168,9 @@ int ige_version(void);
 const char *ige_last_error_string(void);
 /* Kernel launches issued by this library since load (bench.py's gpu_launches claim). */
 uint64_t ige_launch_count(void);
+/* Debug knob: 0 = stage tiles with plain coalesced loads/stores instead of TMA bulk copies
+ * (also settable with the environment variable IGE_NO_TMA=1).  Results are identical. */
+void ige_set_use_tma(int on);
 
 #ifdef __cplusplus
 }

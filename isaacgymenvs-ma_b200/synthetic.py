@@ -88,7 +88,7 @@ def _resets(rng, n, prob):
 # ---------------------------------------------------------------------------------------------
 # Cartpole
 # ---------------------------------------------------------------------------------------------
-def make_cartpole(num_envs, seed=0, reset_prob=0.02):
+def make_cartpole(num_envs, seed=0, reset_prob=0.02, fall_frac=None):
     rng = _rng(seed)
     n = num_envs
     st = {}
@@ -110,14 +110,24 @@ def advance_cartpole(st, rng):
 # ---------------------------------------------------------------------------------------------
 # Ant / Humanoid (same structure)
 # ---------------------------------------------------------------------------------------------
-def _make_locomotion(cfg, lower, upper, num_envs, seed, reset_prob, with_dof_force):
+def _heights(rng, n, th, fall_frac):
+    """Torso heights straddling the termination height; `fall_frac` pins the fallen fraction."""
+    if fall_frac is None:
+        return rng.uniform(th - 0.15, th + 0.5, n)
+    z = rng.uniform(th + 1e-3, th + 0.5, n)
+    fallen = rng.random(n) < fall_frac
+    z[fallen] = rng.uniform(th - 0.15, th - 1e-3, int(fallen.sum()))
+    return z
+
+
+def _make_locomotion(cfg, lower, upper, num_envs, seed, reset_prob, with_dof_force, fall_frac=None):
     rng = _rng(seed)
     n, d = num_envs, cfg["num_dof"]
     th, dt = cfg["termination_height"], cfg["dt"]
     st = {}
     root = np.zeros((n, 13), F32)
     root[:, 0:2] = rng.normal(0.0, 3.0, (n, 2))
-    root[:, 2] = rng.uniform(th - 0.15, th + 0.5, n)
+    root[:, 2] = _heights(rng, n, th, fall_frac)
     root[:, 3:7] = _unit_quats(rng, n)
     root[:, 7:13] = rng.standard_normal((n, 6))
     st["root_states"] = root
@@ -180,17 +190,17 @@ def _advance_locomotion(cfg, st, rng, with_dof_force):
     st["actions"][:] = rng.uniform(-1.0, 1.0, (n, d))
 
 
-def make_ant(num_envs, seed=0, reset_prob=0.02):
-    return _make_locomotion(ANT_CFG, ANT_DOF_LOWER, ANT_DOF_UPPER, num_envs, seed, reset_prob, False)
+def make_ant(num_envs, seed=0, reset_prob=0.02, fall_frac=None):
+    return _make_locomotion(ANT_CFG, ANT_DOF_LOWER, ANT_DOF_UPPER, num_envs, seed, reset_prob, False, fall_frac)
 
 
 def advance_ant(st, rng):
     _advance_locomotion(ANT_CFG, st, rng, False)
 
 
-def make_humanoid(num_envs, seed=0, reset_prob=0.02):
+def make_humanoid(num_envs, seed=0, reset_prob=0.02, fall_frac=None):
     st = _make_locomotion(HUMANOID_CFG, HUMANOID_DOF_LOWER, HUMANOID_DOF_UPPER, num_envs, seed,
-                          reset_prob, True)
+                          reset_prob, True, fall_frac)
     st["motor_efforts"] = HUMANOID_MOTOR_EFFORTS.astype(F32)
     return st
 

@@ -82,7 +82,7 @@ class VecTaskB200:
         self.reset_rank = torch.zeros(self.num_envs, dtype=torch.int32, device=dev)
         self.reset_count = torch.zeros(1, dtype=torch.int32, device=dev)
         self.rng_step = torch.zeros(1, dtype=torch.int64, device=dev)
-        words = 2 + (self.num_envs + 2047) // 2048
+        words = 2 + (self.num_envs + 2047) // 2048   # == ige_compact_scratch_words(num_envs)
         self._compact_scratch = torch.zeros(words, dtype=torch.int32, device=dev)
         self.stats = torch.zeros(_abi.IGE_NUM_STATS, dtype=torch.float32, device=dev) if accumulate_stats else None
         self._u0 = self._u1 = None

@@ -1,0 +1,136 @@
+"""GPU parity tests proper: the CUDA path, called through the C ABI, against (a) the committed
+reference goldens and (b) the CPU oracle on the same seeded inputs at BASELINE.json's full sizes.
+Bars (north_star): done flags, reset indices, progress counters bit-exact; obs / rewards within
+1e-5 relative (|d| <= 1e-5 * max(1, |ref|)); potentials and reset DOF rows bit-exact."""
+import ctypes as C
+
+import numpy as np
+import pytest
+import torch
+
+import harness as H
+
+pytestmark = pytest.mark.gpu
+DOFS = {"cartpole": 2, "ant": 8, "humanoid": 21}
+
+
+def _set_tma(on):
+    lib = H.pkg._lib.lib()
+    lib.ige_set_use_tma(C.c_int(1 if on else 0))
+
+
+@pytest.mark.parametrize("task", ["cartpole", "ant", "humanoid"])
+def test_cuda_matches_reference_golden(task):
+    for path in H.golden_files(task):
+        blob = H.load_golden(path)
+        obj = H.build(task, H.init_state(blob), "cuda:0")
+        for s in range(int(blob["meta_steps"])):
+            H.pkg.factory.load_sim_inputs(obj, H.TASK_NAME[task], H.step_inputs(blob, s))
+            ids = H.cuda_step(task, obj, H.step_rands(blob, s))
+            ref = H.step_outputs(blob, s)
+            H.assert_equal("reset_env_ids", ids.cpu().numpy(), ref["reset_env_ids"])
+            H.compare_outputs(task, obj, ref, bitexact=H.BITEXACT_FLOAT[task])
+
+
+def _oracle_vs_cuda(task, n, seed, reset_prob, steps=3, tma=True, rand_mode="injected"):
+    _set_tma(tma)
+    try:
+        st = H.pkg.synthetic.make_state(task, n, seed=seed, reset_prob=reset_prob)
+        ref = H.build(task, {k: v.copy() for k, v in st.items()}, "cpu", rand_mode=rand_mode, seed=seed)
+        gpu = H.build(task, {k: v.copy() for k, v in st.items()}, "cuda:0", rand_mode=rand_mode, seed=seed)
+        rng = np.random.Generator(np.random.PCG64(seed + 1))
+        phys = np.random.Generator(np.random.PCG64(seed + 2))
+        d = DOFS[task]
+        for s in range(steps):
+            if s > 0:
+                cur = {k: H.get(ref, k) for k in H.pkg.factory.sim_tensor_names(H.TASK_NAME[task])}
+                cur.update({k: st[k] for k in st if k not in cur})
+                cur["progress_buf"] = H.get(ref, "progress_buf")
+                H.pkg.synthetic.advance_physics(task, cur, phys)
+                names = H.pkg.factory.sim_tensor_names(H.TASK_NAME[task]) + (["actions"] if task != "cartpole" else [])
+                for o in (ref, gpu):
+                    H.pkg.factory.load_sim_inputs(o, H.TASK_NAME[task], {k: cur[k] for k in names})
+            k = int((H.get(ref, "reset_buf") != 0).sum())
+            rands = [rng.random((k, d), dtype=np.float32) for _ in range(2)] if rand_mode == "injected" else None
+            ids_ref = H.oracle_step(task, ref, rands)
+            ids_gpu = H.cuda_step(task, gpu, rands)
+            H.assert_equal(f"step{s} reset ids", ids_gpu.cpu().numpy(), ids_ref.numpy())
+            H.compare_outputs(task, gpu, H.snapshot(task, ref), bitexact=H.BITEXACT_FLOAT[task])
+        # episode statistics accumulate the same sums (float atomics: order differs -> loose bar)
+        np.testing.assert_allclose(gpu.stats.cpu().numpy(), ref.stats.numpy(), rtol=2e-3, atol=1e-2)
+    finally:
+        _set_tma(True)
+
+
+# BASELINE.json configs at full size
+def test_cartpole_c1_512():
+    _oracle_vs_cuda("cartpole", 512, 0, 0.02)
+
+
+def test_ant_c2_16384():
+    _oracle_vs_cuda("ant", 16384, 0, 0.02)
+
+
+def test_humanoid_c3_32768():
+    _oracle_vs_cuda("humanoid", 32768, 0, 0.02)
+
+
+@pytest.mark.parametrize("task", ["cartpole", "ant", "humanoid"])
+@pytest.mark.parametrize("n", [1, 37, 1000, 4100])
+@pytest.mark.parametrize("tma", [True, False])
+def test_ragged_sizes(task, n, tma):
+    """N not a multiple of the tile / of 4: partial tiles take the non-bulk path."""
+    _oracle_vs_cuda(task, n, 5, 0.3, steps=2, tma=tma)
+
+
+@pytest.mark.parametrize("task", ["cartpole", "ant", "humanoid"])
+@pytest.mark.parametrize("reset_prob", [0.0, 1.0])
+def test_reset_extremes(task, reset_prob):
+    _oracle_vs_cuda(task, 2048, 9, reset_prob, steps=2)
+
+
+@pytest.mark.parametrize("task", ["cartpole", "ant", "humanoid"])
+def test_philox_mode_matches_oracle_philox(task):
+    """Production (sync-free) reset noise: same counter-based generator in kernel and oracle."""
+    _oracle_vs_cuda(task, 4096, 21, 0.25, steps=3, rand_mode="philox")
+
+
+def test_empty_env_set():
+    p, b = H.pkg._abi.IgeCartpoleParams(), H.pkg._abi.IgeCartpoleBuffers()
+    t = torch.zeros(16, device="cuda:0")
+    for f in ("dof_state", "obs_buf", "rew_buf", "reset_buf", "progress_buf"):
+        setattr(b, f, t.data_ptr())
+    p.num_envs = 0
+    p.rand.mode = H.pkg._abi.IGE_RAND_PHILOX
+    H.pkg._lib.call("ige_cartpole_post_physics", p, b)   # no launch, no error
+
+
+@pytest.mark.parametrize("n,group,prob", [(1, 1, 1.0), (2047, 1, 0.5), (2048, 1, 0.02), (100000, 1, 0.3),
+                                          (1 << 20, 1, 0.02), (8192 * 2, 2, 0.7), (3 * 1000, 3, 0.9)])
+def test_compact_resets(n, group, prob):
+    """reset_buf.nonzero() (+ multi-agent AND filter) bit-exact vs numpy, incl. multi-chunk look-back
+    and graph-style re-launch on the same scratch."""
+    rng = np.random.Generator(np.random.PCG64(n))
+    env = H.pkg.make(0, "Cartpole", 8, "cuda:0")
+    for trial in range(3):
+        flags = (rng.random(n) < prob).astype(np.int64) * rng.integers(1, 5, n)
+        reset = torch.from_numpy(flags).cuda()
+        ne = n // group
+        ids = torch.full((ne,), -1, dtype=torch.int32, device="cuda")
+        rank = torch.full((ne,), -1, dtype=torch.int32, device="cuda")
+        count = torch.zeros(1, dtype=torch.int32, device="cuda")
+        if trial == 0:
+            scratch = torch.zeros(H.pkg._lib.lib().ige_compact_scratch_words(ne), dtype=torch.int32, device="cuda")
+        a = H.pkg._abi.IgeCompactArgs()
+        a.num_rows, a.group = n, group
+        a.reset_buf, a.reset_ids, a.reset_rank = reset.data_ptr(), ids.data_ptr(), rank.data_ptr()
+        a.count, a.scratch = count.data_ptr(), scratch.data_ptr()
+        H.pkg._lib.call("ige_compact_resets", a, stream=torch.cuda.current_stream().cuda_stream)
+        torch.cuda.synchronize()
+        env_flag = (flags.reshape(ne, group) != 0).all(axis=1)
+        want = np.flatnonzero(env_flag).astype(np.int32)
+        k = int(count.item())
+        assert k == want.size
+        np.testing.assert_array_equal(ids[:k].cpu().numpy(), want)
+        np.testing.assert_array_equal(rank.cpu().numpy(), np.cumsum(env_flag) - env_flag)
+        assert int(scratch.abs().sum().item()) == 0, "scratch not restored to zero"
