@@ -145,7 +145,7 @@ def run_ours(args):
     chunks = [(capture(envs[i:i + HORIZON], lambda e: e.post_physics_step()), HORIZON)
               for i in range(0, replicas, HORIZON)]
     single = [(capture([e], lambda e: e.post_physics_step()), 1) for e in envs[:HORIZON]]
-    stats_snap = torch.zeros_like(envs[0].stats)
+    stats_snap = torch.zeros(16, device=device)
     pending = []
 
     def allreduce_stats():

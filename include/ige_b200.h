@@ -40,6 +40,12 @@ extern "C" {
 
 #define IGE_MAX_DOF 32
 #define IGE_NUM_STATS 16
+/* The statistics accumulator is IGE_STATS_ROWS rows of IGE_STATS_STRIDE floats (first IGE_NUM_STATS
+ * of each row used), one 128-byte line per row: a CTA adds to row (blockIdx % ROWS) so the L2
+ * atomics of a launch spread over 32 lines instead of serialising on one.  The statistic is the
+ * column sum over rows. */
+#define IGE_STATS_ROWS 32
+#define IGE_STATS_STRIDE 32
 
 /* How reset_idx obtains its uniforms. */
 #define IGE_RAND_INJECTED 0 /* parity mode: caller pre-draws torch.rand(k, D) like the reference */
@@ -57,8 +63,8 @@ typedef struct IgeResetRand {
     const float *u1;           /* INJECTED: uniforms of the 2nd torch.rand call, (k, D) */
 } IgeResetRand;
 
-/* Episode-statistics accumulator slots (device float[IGE_NUM_STATS], atomically added to by
- * every step kernel; all-reduced across GPUs once per horizon). */
+/* Episode-statistics accumulator slots (device float[IGE_STATS_ROWS * IGE_STATS_STRIDE], atomically
+ * added to by every step kernel; column sums all-reduced across GPUs once per horizon). */
 #define IGE_STAT_STEPS 0        /* env (or agent) rows stepped */
 #define IGE_STAT_REWARD 1       /* sum rew_buf */
 #define IGE_STAT_DONE 2         /* sum (reset_buf != 0) after the step */
@@ -106,7 +112,7 @@ typedef struct IgeCartpoleBuffers {
     int64_t *progress_buf;     /* (N) in/out */
     float *obs_clamped;        /* (N, 4) out, optional: clamp(obs_buf, +-clip_obs) (vec_task.py:404) */
     uint8_t *timeout_buf;      /* (N) out, optional: bool time_outs (vec_task.py:396) */
-    float *stats;              /* [IGE_NUM_STATS] in/out, optional */
+    float *stats;              /* [IGE_STATS_ROWS * IGE_STATS_STRIDE] in/out, optional */
 } IgeCartpoleBuffers;
 
 int ige_cartpole_post_physics(const IgeCartpoleParams *p, const IgeCartpoleBuffers *b, void *stream);

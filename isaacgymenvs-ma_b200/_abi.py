@@ -4,6 +4,8 @@ import ctypes as C
 
 IGE_MAX_DOF = 32
 IGE_NUM_STATS = 16
+IGE_STATS_ROWS = 32
+IGE_STATS_STRIDE = 32
 IGE_RAND_INJECTED = 0
 IGE_RAND_PHILOX = 1
 

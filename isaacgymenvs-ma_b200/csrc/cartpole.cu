@@ -10,7 +10,6 @@ namespace {
 constexpr int kThreads = 128;
 
 __global__ void __launch_bounds__(kThreads) cartpole_post_physics_kernel(IgeCartpoleParams p, IgeCartpoleBuffers b) {
-    __shared__ float s_red[5 * (kThreads / 32)];
     const int e = blockIdx.x * kThreads + threadIdx.x;
     const uint64_t step = (p.rand.mode == IGE_RAND_PHILOX && p.rand.step) ? __ldg(p.rand.step) : 0ull;
     float st_rew = 0.f, st_done = 0.f, st_to = 0.f, st_len = 0.f, st_n = 0.f;
@@ -56,7 +55,7 @@ __global__ void __launch_bounds__(kThreads) cartpole_post_physics_kernel(IgeCart
     if (b.stats) {
         const float v[5] = {st_n, st_rew, st_done, st_to, st_len};
         const int slot[5] = {IGE_STAT_STEPS, IGE_STAT_REWARD, IGE_STAT_DONE, IGE_STAT_TIMEOUT, IGE_STAT_DONE_LENGTH};
-        ige::block_stats_add<5>(b.stats, v, slot, s_red);
+        ige::warp_stats_add<5>(b.stats, v, slot);
     }
 }
 

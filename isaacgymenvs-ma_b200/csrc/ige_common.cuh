@@ -228,22 +228,19 @@ __device__ __forceinline__ float warp_sum(float v) {
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
     return v;
 }
-// Every thread of the CTA calls this with its partials; `scratch` is >= NSTAT * (nthreads/32) floats.
+// One warp holds NSTAT per-lane partials: reduce them and add to this CTA's statistics row with a
+// single multi-lane atomic instruction (one L2 transaction on one 128-B line).
 template <int NSTAT>
-__device__ __forceinline__ void block_stats_add(float *stats, const float (&v)[NSTAT], const int (&slot)[NSTAT],
-                                                float *scratch) {
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = (blockDim.x + 31) >> 5;
+__device__ __forceinline__ void warp_stats_add(float *stats, const float (&v)[NSTAT], const int (&slot)[NSTAT]) {
+    const int lane = threadIdx.x & 31;
+    float mine = 0.0f;
+    int my_slot = 0;
 #pragma unroll
     for (int s = 0; s < NSTAT; ++s) {
-        const float w = warp_sum(v[s]);
-        if (lane == 0) scratch[s * nwarps + warp] = w;
+        const float t = warp_sum(v[s]);
+        if (lane == s) { mine = t; my_slot = slot[s]; }
     }
-    __syncthreads();
-    if (threadIdx.x < NSTAT) {
-        float t = 0.0f;
-        for (int w = 0; w < nwarps; ++w) t += scratch[threadIdx.x * nwarps + w];
-        atomicAdd(stats + slot[threadIdx.x], t);
-    }
+    if (lane < NSTAT) atomicAdd(stats + (blockIdx.x % IGE_STATS_ROWS) * IGE_STATS_STRIDE + my_slot, mine);
 }
 
 }  // namespace ige

@@ -84,8 +84,16 @@ class VecTaskB200:
         self.rng_step = torch.zeros(1, dtype=torch.int64, device=dev)
         words = 2 + (self.num_envs + 2047) // 2048   # == ige_compact_scratch_words(num_envs)
         self._compact_scratch = torch.zeros(words, dtype=torch.int32, device=dev)
-        self.stats = torch.zeros(_abi.IGE_NUM_STATS, dtype=torch.float32, device=dev) if accumulate_stats else None
+        self.stats_rows = (torch.zeros(_abi.IGE_STATS_ROWS * _abi.IGE_STATS_STRIDE, dtype=torch.float32, device=dev)
+                           if accumulate_stats else None)
         self._u0 = self._u1 = None
+
+    @property
+    def stats(self):
+        """Episode statistics accumulated by the step kernels: [IGE_NUM_STATS] column sums."""
+        if self.stats_rows is None:
+            return None
+        return self.stats_rows.view(_abi.IGE_STATS_ROWS, _abi.IGE_STATS_STRIDE)[:, :_abi.IGE_NUM_STATS].sum(0)
 
     # -- vec_task.py:135-160 properties ------------------------------------------------------
     @property

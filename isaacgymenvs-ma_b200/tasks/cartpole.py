@@ -34,7 +34,7 @@ class Cartpole(VecTaskB200):
         b.progress_buf = _ptr(self.progress_buf)
         b.obs_clamped = _ptr(self.obs_clamped) if self.fuse_epilogue else None
         b.timeout_buf = _ptr(self.timeout_bool) if self.fuse_epilogue else None
-        b.stats = _ptr(self.stats)
+        b.stats = _ptr(self.stats_rows)
         return p, b
 
     def draw_reset_uniforms(self, k):

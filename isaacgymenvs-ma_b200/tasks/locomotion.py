@@ -91,7 +91,7 @@ class _Locomotion(VecTaskB200):
         b.dof_force_tensor = _ptr(self.dof_force_tensor) if self.HAS_DOF_FORCE else None
         b.obs_clamped = _ptr(self.obs_clamped) if self.fuse_epilogue else None
         b.timeout_buf = _ptr(self.timeout_bool) if self.fuse_epilogue else None
-        b.stats = _ptr(self.stats)
+        b.stats = _ptr(self.stats_rows)
         return p, b
 
     def draw_reset_uniforms(self, k):

@@ -57,7 +57,7 @@ def _oracle_vs_cuda(task, n, seed, reset_prob, steps=3, tma=True, rand_mode="inj
             H.assert_equal(f"step{s} reset ids", ids_gpu.cpu().numpy(), ids_ref.numpy())
             H.compare_outputs(task, gpu, H.snapshot(task, ref), bitexact=H.BITEXACT_FLOAT[task])
         # episode statistics accumulate the same sums (float atomics: order differs -> loose bar)
-        np.testing.assert_allclose(gpu.stats.cpu().numpy(), ref.stats.numpy(), rtol=2e-3, atol=1e-2)
+        np.testing.assert_allclose(gpu.stats.cpu().numpy(), ref.stats.numpy(), rtol=2e-3, atol=2e-2)
     finally:
         _set_tma(True)
 
