@@ -50,7 +50,7 @@ struct Layout {
     static constexpr bool VEC4 = !HUM && (D % 4 == 0) && (NS % 4 == 0) && (NUM_OBS % 4 == 0);
 };
 
-// one tile of inputs as it lies in shared memory (each member a multiple of 16 B)
+// one tile of the large inputs as it lies in shared memory (each member a multiple of 16 B)
 template <int D, int NS, bool HUM>
 struct __align__(128) InTile {
     float root[TE * 13];
@@ -58,25 +58,15 @@ struct __align__(128) InTile {
     float sens[TE * NS];
     float force[HUM ? TE * D : 4];
     float act[TE * D];
-    float pot[TE];
-    long long reset[TE];
-    long long progress[TE];
-    long long randomize[TE];
 };
 template <int NUM_OBS>
 struct __align__(128) OutTile {
     float obs[TE * NUM_OBS];
-    float rew[TE];
-    float pot[TE];
-    float prev[TE];
-    float up[TE * 3];
-    float head[TE * 3];
-    long long reset[TE];
-    long long progress[TE];
-    long long randomize[TE];
 };
+// per-tile hand-off from the role warps to the REWARD warp
 template <int D>
-struct Terms {
+struct Handoff {
+    float pot[TE], prev[TE], obj[TE];
     float t0[D * TS], t1[D * TS], t2[D * TS];  // reward terms [dof][env], padded: conflict-free both ways
 };
 
@@ -104,24 +94,26 @@ __device__ __forceinline__ float neg_norm_over_dt(const IgeLocomotionParams &p, 
 }
 
 // ---------------------------------------------------------------------------------------------
-// roles (lane == env); `in`/`out`/`terms` are shared-memory tiles, e0 the first env of the tile
+// roles (lane == env `e` of the tile); `root` points at the env's 13-float row in shared memory
 // ---------------------------------------------------------------------------------------------
-template <int D, int NS, bool HUM>
+// HEADING: potentials (+ reset potentials), up / heading vectors, projections.  Writes the final
+// potentials / prev_potentials / up_vec / heading_vec rows straight to global (coalesced per warp).
+template <int D, int NUM_OBS>
 __device__ __forceinline__ void role_heading(const IgeLocomotionParams &p, const IgeLocomotionBuffers &b,
-                                             const InTile<D, NS, HUM> &in,
-                                             OutTile<Layout<D, NS, HUM>::NUM_OBS> &out, int lane, int e0) {
-    constexpr int NUM_OBS = Layout<D, NS, HUM>::NUM_OBS;
-    const float *root = in.root + lane * 13;
-    float potentials = in.pot[lane];
-    if (in.reset[lane] != 0) {  // ant.py:273-276
-        const float *init = b.initial_root_states + (size_t)(e0 + lane) * 13;
+                                             const float *root, bool was_reset, float potentials, int e,
+                                             float *obs_row, Handoff<D> &h, int lane) {
+    if (was_reset) {  // ant.py:273-276
+        const float *init = b.initial_root_states + (size_t)e * 13;
         potentials = neg_norm_over_dt(p, ige::norm3(p.targets[0] - __ldg(init), p.targets[1] - __ldg(init + 1), 0.0f));
     }
     // compute_*_observations ant.py:384-391
     const float to_target[3] = {p.targets[0] - root[0], p.targets[1] - root[1], 0.0f};
-    out.prev[lane] = potentials;
     float n = ige::norm3(to_target[0], to_target[1], 0.0f);
-    out.pot[lane] = neg_norm_over_dt(p, n);
+    const float new_pot = neg_norm_over_dt(p, n);
+    h.prev[lane] = potentials;
+    h.pot[lane] = new_pot;
+    b.prev_potentials[e] = potentials;
+    b.potentials[e] = new_pot;
     // compute_heading_and_up torch_jit_utils.py:247-262
     n = n < 1e-9f ? 1e-9f : n;  // normalize(), torch_jit_utils.py:65-67
     const float target_dirs[3] = {to_target[0] / n, to_target[1] / n, to_target[2] / n};
@@ -129,35 +121,29 @@ __device__ __forceinline__ void role_heading(const IgeLocomotionParams &p, const
     ige::quat_mul(root + 3, p.inv_start_rot, torso_quat);
     ige::quat_rotate<false>(torso_quat, p.basis_vec1, up_vec);
     ige::quat_rotate<false>(torso_quat, p.basis_vec0, heading_vec);
-    float *o = out.obs + lane * NUM_OBS;
-    o[10] = up_vec[2];
-    o[11] = ige::dot3(heading_vec, target_dirs);
-    out.up[lane * 3 + 0] = up_vec[0]; out.up[lane * 3 + 1] = up_vec[1]; out.up[lane * 3 + 2] = up_vec[2];
-    out.head[lane * 3 + 0] = heading_vec[0]; out.head[lane * 3 + 1] = heading_vec[1];
-    out.head[lane * 3 + 2] = heading_vec[2];
+    obs_row[10] = up_vec[2];
+    obs_row[11] = ige::dot3(heading_vec, target_dirs);
+    float *up = b.up_vec + (size_t)e * 3, *hd = b.heading_vec + (size_t)e * 3;
+    up[0] = up_vec[0]; up[1] = up_vec[1]; up[2] = up_vec[2];
+    hd[0] = heading_vec[0]; hd[1] = heading_vec[1]; hd[2] = heading_vec[2];
 }
 
-template <int D, int NS, bool HUM>
-__device__ __forceinline__ void role_velocity(const IgeLocomotionParams &p, const InTile<D, NS, HUM> &in,
-                                              OutTile<Layout<D, NS, HUM>::NUM_OBS> &out, int lane) {
-    constexpr int NUM_OBS = Layout<D, NS, HUM>::NUM_OBS;
-    const float *root = in.root + lane * 13;
+template <int D, bool HUM>
+__device__ __forceinline__ void role_velocity(const IgeLocomotionParams &p, const float *root, float *obs_row,
+                                              Handoff<D> &h, int lane) {
     float torso_quat[4], vel_loc[3], angvel_loc[3];
     ige::quat_mul(root + 3, p.inv_start_rot, torso_quat);
     ige::quat_rotate<true>(torso_quat, root + 7, vel_loc);  // compute_rot torch_jit_utils.py:265-267
     ige::quat_rotate<true>(torso_quat, root + 10, angvel_loc);
-    float *o = out.obs + lane * NUM_OBS;
-    o[0] = root[2];
-    o[1] = vel_loc[0]; o[2] = vel_loc[1]; o[3] = vel_loc[2];
+    obs_row[0] = root[2];
+    obs_row[1] = vel_loc[0]; obs_row[2] = vel_loc[1]; obs_row[3] = vel_loc[2];
     const float s = HUM ? p.angular_velocity_scale : 1.0f;  // x * 1.0f is exact
-    o[4] = angvel_loc[0] * s; o[5] = angvel_loc[1] * s; o[6] = angvel_loc[2] * s;
+    obs_row[4] = angvel_loc[0] * s; obs_row[5] = angvel_loc[1] * s; obs_row[6] = angvel_loc[2] * s;
+    h.obj[lane] = root[7];  // true_objective statistic (ant.py:245-250)
 }
 
-template <int D, int NS, bool HUM>
-__device__ __forceinline__ void role_angles(const IgeLocomotionParams &p, const InTile<D, NS, HUM> &in,
-                                            OutTile<Layout<D, NS, HUM>::NUM_OBS> &out, int lane) {
-    constexpr int NUM_OBS = Layout<D, NS, HUM>::NUM_OBS;
-    const float *root = in.root + lane * 13;
+template <bool HUM>
+__device__ __forceinline__ void role_angles(const IgeLocomotionParams &p, const float *root, float *obs_row) {
     float q[4];
     ige::quat_mul(root + 3, p.inv_start_rot, q);
     // get_euler_xyz torch_jit_utils.py:175-195 (pitch is never consumed on this path)
@@ -170,44 +156,66 @@ __device__ __forceinline__ void role_angles(const IgeLocomotionParams &p, const 
     const float yaw = mod_two_pi(atan2f(siny_cosp, cosy_cosp));
     const float walk_target_angle = atan2f(p.targets[2] - root[2], p.targets[0] - root[0]);  // :272-273
     const float angle_to_target = walk_target_angle - yaw;
-    float *o = out.obs + lane * NUM_OBS;
     if (HUM) {  // humanoid.py:402-404 normalize_angle
-        o[7] = wrap_pi(yaw); o[8] = wrap_pi(roll); o[9] = wrap_pi(angle_to_target);
+        obs_row[7] = wrap_pi(yaw); obs_row[8] = wrap_pi(roll); obs_row[9] = wrap_pi(angle_to_target);
     } else {  // ant.py:403
-        o[7] = yaw; o[8] = roll; o[9] = angle_to_target;
+        obs_row[7] = yaw; obs_row[8] = roll; obs_row[9] = angle_to_target;
     }
 }
 
-// reset_idx for one DOF (ant.py:257-261): returns the new (pos, vel) row
-__device__ __forceinline__ float2 reset_dof(const IgeLocomotionParams &p, const IgeLocomotionBuffers &b, uint64_t step,
-                                            int e, int d, int j) {
-    // torch_rand_float(lo, hi): (hi - lo) * rand + lo (torch_jit_utils.py:215-218)
-    const float pos = 0.4f * ige::reset_uniform(p.rand, step, 0, e, d, j) + (-0.2f);
-    const float vel = 0.2f * ige::reset_uniform(p.rand, step, 1, e, d, j) + (-0.1f);
+// reset_idx noise for DOF j of env e (ant.py:257-258): torch_rand_float(lo, hi) = (hi - lo) * rand + lo
+__device__ __forceinline__ float2 finish_reset_dof(const IgeLocomotionParams &p, const IgeLocomotionBuffers &b, int e,
+                                                   int d, int j, float u_pos, float u_vel) {
+    const float pos = 0.4f * u_pos + (-0.2f);
+    const float vel = 0.2f * u_vel + (-0.1f);
     float v = __ldg(b.initial_dof_pos + (size_t)e * d + j) + pos;
     v = fminf(v, p.dof_limits_upper[j]);  // tensor_clamp torch_jit_utils.py:228-230
     v = fmaxf(v, p.dof_limits_lower[j]);
-    return make_float2(v, vel);
+    return make_float2(v, vel);  // ant.py:260-261
+}
+// four consecutive uniforms (columns 4g .. 4g+3) of draw `which` for env row `e`: ONE Philox call
+__device__ __forceinline__ void reset_uniform4(const IgeResetRand &r, uint64_t step, int which, int e, int d, int g,
+                                               float (&u)[4]) {
+    if (r.mode == IGE_RAND_PHILOX) {
+        uint32_t c[4] = {(uint32_t)e, ((uint32_t)which << 16) | (uint32_t)g, (uint32_t)step, (uint32_t)(step >> 32)};
+        ige::philox4x32_10(c, (uint32_t)r.seed, (uint32_t)(r.seed >> 32));
+#pragma unroll
+        for (int k = 0; k < 4; ++k) u[k] = (float)(c[k] >> 8) * (1.0f / 16777216.0f);
+    } else {
+        const float *src = (which ? r.u1 : r.u0) + (size_t)__ldg(r.reset_rank + e) * d + g * 4;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) u[k] = __ldg(src + k);
+    }
 }
 
-// element-wise columns + reset DOF scatter + per-DOF reward terms; `share` of `nshares` warps
+// ELEM: element-wise columns + reset DOF scatter + per-DOF reward terms; `share` of `nshares` warps.
+// `my_flag` is the reset flag of env (e0 + lane); items fetch their env's flag with a shuffle.
 template <int D, int NS, bool HUM>
 __device__ __forceinline__ void role_elem(const IgeLocomotionParams &p, const IgeLocomotionBuffers &b,
-                                          InTile<D, NS, HUM> &in, OutTile<Layout<D, NS, HUM>::NUM_OBS> &out,
-                                          Terms<D> &tm, int lane, int share, int nshares, int ne, int e0,
-                                          uint64_t step) {
+                                          const InTile<D, NS, HUM> &in, float *obs, Handoff<D> &h, int lane,
+                                          int share, int nshares, int ne, int e0, uint64_t step, bool my_flag) {
     using L = Layout<D, NS, HUM>;
     constexpr int NUM_OBS = L::NUM_OBS;
     const int stride = 32 * nshares;
     if (L::VEC4) {
-        for (int it = share * 32 + lane; it < ne * (D / 4); it += stride) {
-            const int le = it / (D / 4), g = it - le * (D / 4);
+        constexpr int G = D / 4;
+        for (int base = share * 32; base < ne * G; base += stride) {
+            const int it = base + lane;
+            const bool valid = it < ne * G;
+            const int le = valid ? it / G : 0, g = it - le * G;
+            const bool was_reset = __shfl_sync(0xffffffffu, my_flag, le);
+            if (!valid) continue;
             float4 a = reinterpret_cast<const float4 *>(in.dof)[it * 2];      // p0 v0 p1 v1
             float4 c = reinterpret_cast<const float4 *>(in.dof)[it * 2 + 1];  // p2 v2 p3 v3
-            if (in.reset[le] != 0) {  // reset_idx: rewrite this env's DOF rows (global + local copy)
+            if (was_reset) {  // reset_idx: rewrite this env's DOF rows (global copy + the values used below)
                 const int e = e0 + le;
-                const float2 r0 = reset_dof(p, b, step, e, D, g * 4 + 0), r1 = reset_dof(p, b, step, e, D, g * 4 + 1);
-                const float2 r2 = reset_dof(p, b, step, e, D, g * 4 + 2), r3 = reset_dof(p, b, step, e, D, g * 4 + 3);
+                float up[4], uv[4];
+                reset_uniform4(p.rand, step, 0, e, D, g, up);
+                reset_uniform4(p.rand, step, 1, e, D, g, uv);
+                const float2 r0 = finish_reset_dof(p, b, e, D, g * 4 + 0, up[0], uv[0]);
+                const float2 r1 = finish_reset_dof(p, b, e, D, g * 4 + 1, up[1], uv[1]);
+                const float2 r2 = finish_reset_dof(p, b, e, D, g * 4 + 2, up[2], uv[2]);
+                const float2 r3 = finish_reset_dof(p, b, e, D, g * 4 + 3, up[3], uv[3]);
                 a = make_float4(r0.x, r0.y, r1.x, r1.y);
                 c = make_float4(r2.x, r2.y, r3.x, r3.y);
                 float4 *row = reinterpret_cast<float4 *>(b.dof_state + ((size_t)e * D + g * 4) * 2);
@@ -224,54 +232,61 @@ __device__ __forceinline__ void role_elem(const IgeLocomotionParams &p, const Ig
                 const float lo = p.dof_limits_lower[j], hi = p.dof_limits_upper[j];
                 ps[k] = (2.0f * pos[k] - hi - lo) / (hi - lo);  // unscale torch_jit_utils.py:238-240
                 vs[k] = vel[k] * p.dof_vel_scale;
-                tm.t0[j * TS + le] = av[k] * av[k];                // actions ** 2        ant.py:353
-                tm.t1[j * TS + le] = fabsf(av[k] * vs[k]);         // |a * dof_vel_obs|   ant.py:354
-                tm.t2[j * TS + le] = ps[k] > 0.99f ? 1.0f : 0.0f;  // dof at limit        ant.py:355
+                h.t0[j * TS + le] = av[k] * av[k];                // actions ** 2        ant.py:353
+                h.t1[j * TS + le] = fabsf(av[k] * vs[k]);         // |a * dof_vel_obs|   ant.py:354
+                h.t2[j * TS + le] = ps[k] > 0.99f ? 1.0f : 0.0f;  // dof at limit        ant.py:355
             }
-            float *o = out.obs + le * NUM_OBS;
+            float *o = obs + le * NUM_OBS;
             reinterpret_cast<float4 *>(o + L::O_DOFPOS)[g] = make_float4(ps[0], ps[1], ps[2], ps[3]);
             reinterpret_cast<float4 *>(o + L::O_DOFVEL)[g] = make_float4(vs[0], vs[1], vs[2], vs[3]);
             reinterpret_cast<float4 *>(o + L::O_ACT)[g] = act;
         }
-        for (int it = share * 32 + lane; it < ne * (NS / 4); it += stride) {
-            const int le = it / (NS / 4), g = it - le * (NS / 4);
+        constexpr int GS = NS / 4;
+        for (int it = share * 32 + lane; it < ne * GS; it += stride) {
+            const int le = it / GS, g = it - le * GS;
             float4 s = reinterpret_cast<const float4 *>(in.sens)[it];
             s.x *= p.contact_force_scale; s.y *= p.contact_force_scale;
             s.z *= p.contact_force_scale; s.w *= p.contact_force_scale;
-            reinterpret_cast<float4 *>(out.obs + le * NUM_OBS + L::O_SENS)[g] = s;
+            reinterpret_cast<float4 *>(obs + le * NUM_OBS + L::O_SENS)[g] = s;
         }
     } else {
-        for (int it = share * 32 + lane; it < ne * D; it += stride) {
-            const int le = it / D, j = it - le * D;
+        for (int base = share * 32; base < ne * D; base += stride) {
+            const int it = base + lane;
+            const bool valid = it < ne * D;
+            const int le = valid ? it / D : 0, j = it - le * D;
+            const bool was_reset = __shfl_sync(0xffffffffu, my_flag, le);
+            if (!valid) continue;
             float2 pv = reinterpret_cast<const float2 *>(in.dof)[it];
-            if (in.reset[le] != 0) {
-                pv = reset_dof(p, b, step, e0 + le, D, j);
+            if (was_reset) {
+                const int e = e0 + le;
+                pv = finish_reset_dof(p, b, e, D, j, ige::reset_uniform(p.rand, step, 0, e, D, j),
+                                      ige::reset_uniform(p.rand, step, 1, e, D, j));
                 reinterpret_cast<float2 *>(b.dof_state)[(size_t)e0 * D + it] = pv;
             }
             const float lo = p.dof_limits_lower[j], hi = p.dof_limits_upper[j];
             const float ps = (2.0f * pv.x - hi - lo) / (hi - lo);
             const float vs = pv.y * p.dof_vel_scale;
             const float a = in.act[it];
-            float *o = out.obs + le * NUM_OBS;
+            float *o = obs + le * NUM_OBS;
             o[L::O_DOFPOS + j] = ps;
             o[L::O_DOFVEL + j] = vs;
             o[L::O_ACT + j] = a;
-            tm.t0[j * TS + le] = a * a;
+            h.t0[j * TS + le] = a * a;
             if (HUM) {
                 o[L::O_FORCE + j] = in.force[it] * p.contact_force_scale;
                 const float ratio = p.motor_effort_ratio[j];
-                tm.t1[j * TS + le] = fabsf(a * vs) * ratio;  // humanoid.py:359
+                h.t1[j * TS + le] = fabsf(a * vs) * ratio;  // humanoid.py:359
                 const float ap = fabsf(ps);
                 const float scaled = p.joints_at_limit_cost_scale * (ap - 0.98f) / 0.02f;  // humanoid.py:356
-                tm.t2[j * TS + le] = (ap > 0.98f ? 1.0f : 0.0f) * scaled * ratio;           // humanoid.py:357
+                h.t2[j * TS + le] = (ap > 0.98f ? 1.0f : 0.0f) * scaled * ratio;            // humanoid.py:357
             } else {
-                tm.t1[j * TS + le] = fabsf(a * vs);
-                tm.t2[j * TS + le] = ps > 0.99f ? 1.0f : 0.0f;
+                h.t1[j * TS + le] = fabsf(a * vs);
+                h.t2[j * TS + le] = ps > 0.99f ? 1.0f : 0.0f;
             }
         }
         for (int it = share * 32 + lane; it < ne * NS; it += stride) {
             const int le = it / NS, j = it - le * NS;
-            out.obs[le * NUM_OBS + L::O_SENS + j] = in.sens[it] * p.contact_force_scale;
+            obs[le * NUM_OBS + L::O_SENS + j] = in.sens[it] * p.contact_force_scale;
         }
     }
 }
@@ -280,31 +295,29 @@ struct StatAcc {
     float rew = 0.f, len = 0.f, obj = 0.f, n = 0.f, done = 0.f, to = 0.f;
 };
 
-// reward + termination for env `lane` of a tile (ant.py:325-371, humanoid.py:323-375, vec_task.py:396)
-template <int D, int NS, bool HUM>
+// REWARD: reward + termination for env e (ant.py:325-371, humanoid.py:323-375, vec_task.py:396).
+// Writes rew / reset / progress / randomize / time_out straight to global (coalesced per warp).
+template <int D, bool HUM>
 __device__ __forceinline__ void role_reward(const IgeLocomotionParams &p, const IgeLocomotionBuffers &b,
-                                            const InTile<D, NS, HUM> &in, OutTile<Layout<D, NS, HUM>::NUM_OBS> &out,
-                                            const Terms<D> &tm, int lane, int e0, bool has_rnd, StatAcc &st) {
-    constexpr int NUM_OBS = Layout<D, NS, HUM>::NUM_OBS;
-    const float *o = out.obs + lane * NUM_OBS;
-    const float z = o[0];
-    long long progress = in.progress[lane] + 1;  // ant.py:288
-    long long reset = in.reset[lane];
+                                            const float *obs_row, const Handoff<D> &h, int lane, int e,
+                                            long long reset, long long progress, long long randomize, StatAcc &st) {
+    const float z = obs_row[0];
+    progress += 1;  // ant.py:288
     if (reset != 0) { progress = 0; reset = 0; }  // ant.py:278-279
-    const float heading_reward = o[11] > 0.8f ? p.heading_weight : p.heading_weight * o[11] / 0.8f;
-    const float up_reward = o[10] > 0.93f ? 0.0f + p.up_weight : 0.0f;
-    const float actions_cost = ige::row_sum<D>([&](int j) { return tm.t0[j * TS + lane]; });
-    const float electricity_cost = ige::row_sum<D>([&](int j) { return tm.t1[j * TS + lane]; });
-    const float progress_reward = out.pot[lane] - out.prev[lane];
+    const float heading_reward = obs_row[11] > 0.8f ? p.heading_weight : p.heading_weight * obs_row[11] / 0.8f;
+    const float up_reward = obs_row[10] > 0.93f ? 0.0f + p.up_weight : 0.0f;
+    const float actions_cost = ige::row_sum<D>([&](int j) { return h.t0[j * TS + lane]; });
+    const float electricity_cost = ige::row_sum<D>([&](int j) { return h.t1[j * TS + lane]; });
+    const float progress_reward = h.pot[lane] - h.prev[lane];
     float total;
     if (HUM) {
-        const float dof_at_limit_cost = ige::row_sum<D>([&](int j) { return tm.t2[j * TS + lane]; });
+        const float dof_at_limit_cost = ige::row_sum<D>([&](int j) { return h.t2[j * TS + lane]; });
         total = progress_reward + 2.0f + up_reward + heading_reward - p.actions_cost_scale * actions_cost -
                 p.energy_cost_scale * electricity_cost - dof_at_limit_cost;
     } else {
         float at_limit = 0.0f;  // integer count <= 8: exact in fp32 (ant.py:355 sums int64)
 #pragma unroll
-        for (int j = 0; j < D; ++j) at_limit += tm.t2[j * TS + lane];
+        for (int j = 0; j < D; ++j) at_limit += h.t2[j * TS + lane];
         total = progress_reward + 0.5f + up_reward + heading_reward - p.actions_cost_scale * actions_cost -
                 p.energy_cost_scale * electricity_cost - at_limit * p.joints_at_limit_cost_scale;
     }
@@ -312,14 +325,14 @@ __device__ __forceinline__ void role_reward(const IgeLocomotionParams &p, const 
     const bool late = (float)progress >= p.max_episode_length - 1.0f;
     if (fallen) total = p.death_cost;
     if (fallen || late) reset = 1;
-    out.rew[lane] = total;
-    out.reset[lane] = reset;
-    out.progress[lane] = progress;
-    if (has_rnd) out.randomize[lane] = in.randomize[lane] + 1;  // ant.py:289
+    b.rew_buf[e] = total;
+    b.reset_buf[e] = reset;
+    b.progress_buf[e] = progress;
+    if (b.randomize_buf) b.randomize_buf[e] = randomize + 1;  // ant.py:289
     const bool timeout = late && reset != 0;  // vec_task.py:396
-    if (b.timeout_buf) b.timeout_buf[e0 + lane] = timeout ? 1 : 0;
+    if (b.timeout_buf) b.timeout_buf[e] = timeout ? 1 : 0;
     st.n += 1.f; st.rew += total; st.done += reset != 0 ? 1.f : 0.f; st.to += timeout ? 1.f : 0.f;
-    st.len += reset != 0 ? (float)progress : 0.f; st.obj += in.root[lane * 13 + 7];
+    st.len += reset != 0 ? (float)progress : 0.f; st.obj += h.obj[lane];
 }
 
 __device__ __forceinline__ void flush_stats(float *stats, const StatAcc &st) {
@@ -329,42 +342,6 @@ __device__ __forceinline__ void flush_stats(float *stats, const StatAcc &st) {
     ige::warp_stats_add<6>(stats, v, slot);
 }
 
-template <int D, int NS, bool HUM>
-__device__ __forceinline__ void issue_tile_loads(const IgeLocomotionBuffers &b, InTile<D, NS, HUM> &in, uint64_t *bar,
-                                                 int e0, int ne, bool has_rnd) {
-    const uint32_t une = (uint32_t)ne;
-    uint32_t bytes = une * (13 * 4 + D * 8 + NS * 4 + D * 4 + 4 + 8 + 8);
-    if (HUM) bytes += une * D * 4;
-    if (has_rnd) bytes += une * 8;
-    ige::mbar_expect_tx(bar, bytes);
-    ige::bulk_g2s(in.root, b.root_states + (size_t)e0 * 13, une * 52, bar);
-    ige::bulk_g2s(in.dof, b.dof_state + (size_t)e0 * D * 2, une * D * 8, bar);
-    ige::bulk_g2s(in.sens, b.vec_sensor_tensor + (size_t)e0 * NS, une * NS * 4, bar);
-    if (HUM) ige::bulk_g2s(in.force, b.dof_force_tensor + (size_t)e0 * D, une * D * 4, bar);
-    ige::bulk_g2s(in.act, b.actions + (size_t)e0 * D, une * D * 4, bar);
-    ige::bulk_g2s(in.pot, b.potentials + e0, une * 4, bar);
-    ige::bulk_g2s(in.reset, b.reset_buf + e0, une * 8, bar);
-    ige::bulk_g2s(in.progress, b.progress_buf + e0, une * 8, bar);
-    if (has_rnd) ige::bulk_g2s(in.randomize, b.randomize_buf + e0, une * 8, bar);
-}
-
-template <int NUM_OBS>
-__device__ __forceinline__ void issue_tile_stores(const IgeLocomotionBuffers &b, OutTile<NUM_OBS> &out, int e0, int ne,
-                                                  bool has_rnd, bool second_obs_copy) {
-    const uint32_t une = (uint32_t)ne;
-    ige::bulk_s2g(b.obs_buf + (size_t)e0 * NUM_OBS, out.obs, une * NUM_OBS * 4);
-    if (second_obs_copy) ige::bulk_s2g(b.obs_clamped + (size_t)e0 * NUM_OBS, out.obs, une * NUM_OBS * 4);
-    ige::bulk_s2g(b.rew_buf + e0, out.rew, une * 4);
-    ige::bulk_s2g(b.potentials + e0, out.pot, une * 4);
-    ige::bulk_s2g(b.prev_potentials + e0, out.prev, une * 4);
-    ige::bulk_s2g(b.up_vec + (size_t)e0 * 3, out.up, une * 12);
-    ige::bulk_s2g(b.heading_vec + (size_t)e0 * 3, out.head, une * 12);
-    ige::bulk_s2g(b.reset_buf + e0, out.reset, une * 8);
-    ige::bulk_s2g(b.progress_buf + e0, out.progress, une * 8);
-    if (has_rnd) ige::bulk_s2g(b.randomize_buf + e0, out.randomize, une * 8);
-    ige::bulk_commit();
-}
-
 template <int N>
 __device__ __forceinline__ void bulk_wait_read() {
     asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
@@ -372,11 +349,33 @@ __device__ __forceinline__ void bulk_wait_read() {
 
 enum Role { HEADING = 0, VELOCITY = 1, ANGLES = 2, REWARD = 3, ELEM0 = 4 };
 
+// Bulk loads of one tile, split over the lane 0s of the four role warps so they issue in parallel.
+// HEADING also arms the barrier (expect_tx may legally trail the first complete_tx: the phase
+// cannot flip before the single expected arrival).
+template <int D, int NS, bool HUM>
+__device__ __forceinline__ void issue_tile_loads(int role, const IgeLocomotionBuffers &b, InTile<D, NS, HUM> &in,
+                                                 uint64_t *bar, int e0, int ne) {
+    const uint32_t une = (uint32_t)ne;
+    if (role == HEADING) {
+        uint32_t bytes = une * (13 * 4 + D * 8 + NS * 4 + D * 4);
+        if (HUM) bytes += une * D * 4;
+        ige::mbar_expect_tx(bar, bytes);
+        ige::bulk_g2s(in.root, b.root_states + (size_t)e0 * 13, une * 52, bar);
+    } else if (role == VELOCITY) {
+        ige::bulk_g2s(in.dof, b.dof_state + (size_t)e0 * D * 2, une * D * 8, bar);
+    } else if (role == ANGLES) {
+        ige::bulk_g2s(in.sens, b.vec_sensor_tensor + (size_t)e0 * NS, une * NS * 4, bar);
+        if (HUM) ige::bulk_g2s(in.force, b.dof_force_tensor + (size_t)e0 * D, une * D * 4, bar);
+    } else if (role == ELEM0) {
+        ige::bulk_g2s(in.act, b.actions + (size_t)e0 * D, une * D * 4, bar);
+    }
+}
+
 // ---------------------------------------------------------------------------------------------
 // main kernel: persistent, pipelined, TMA in / TMA out.  Handles tiles [0, num_tiles); every tile
 // has ne % 4 == 0 envs (only the last may be partial).
 // ---------------------------------------------------------------------------------------------
-template <int D, int NS, bool HUM, int NW_ELEM, int IN_STAGES, int OUT_STAGES>
+template <int D, int NS, bool HUM, int NW_ELEM, int IN_STAGES>
 __global__ void __launch_bounds__(32 * (4 + NW_ELEM))
 locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p,
                             const __grid_constant__ IgeLocomotionBuffers b, const int num_tiles) {
@@ -389,18 +388,19 @@ locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p,
     extern __shared__ __align__(128) unsigned char smem_raw[];
     In *in = reinterpret_cast<In *>(smem_raw);
     Out *out = reinterpret_cast<Out *>(smem_raw + sizeof(In) * IN_STAGES);
-    Terms<D> *terms = reinterpret_cast<Terms<D> *>(smem_raw + sizeof(In) * IN_STAGES + sizeof(Out) * OUT_STAGES);
-    uint64_t *full = reinterpret_cast<uint64_t *>(smem_raw + sizeof(In) * IN_STAGES + sizeof(Out) * OUT_STAGES +
-                                                  sizeof(Terms<D>) * 2);
+    uint64_t *full = reinterpret_cast<uint64_t *>(smem_raw + sizeof(In) * IN_STAGES + sizeof(Out) * 2);
+    Handoff<D> *hand = reinterpret_cast<Handoff<D> *>(smem_raw + sizeof(In) * IN_STAGES + sizeof(Out) * 2 +
+                                                      sizeof(uint64_t) * IN_STAGES);
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int role = (warp + (int)blockIdx.x) % NW;
     const int first = blockIdx.x, stride = gridDim.x;
     const int my_tiles = (num_tiles - first + stride - 1) / stride;
-    const bool has_rnd = b.randomize_buf != nullptr;
     const bool clamp_copy = b.obs_clamped != nullptr && p.clip_obs < INFINITY;
     const bool second_obs_copy = b.obs_clamped != nullptr && !clamp_copy;
     const uint64_t step = (p.rand.mode == IGE_RAND_PHILOX && p.rand.step) ? __ldg(p.rand.step) : 0ull;
+    auto tile_e0 = [&](int it) { return (first + it * stride) * TE; };
+    auto tile_ne = [&](int it) { return min(TE, p.num_envs - tile_e0(it)); };
 
     if (tid == 0) {
 #pragma unroll
@@ -408,63 +408,88 @@ locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p,
         ige::fence_mbar_init();
     }
     __syncthreads();
+    // prologue: the first IN_STAGES tiles
+    if (lane == 0 && role != REWARD)
+        for (int k = 0; k < IN_STAGES && k < my_tiles; ++k)
+            issue_tile_loads<D, NS, HUM>(role, b, in[k], &full[k], tile_e0(k), tile_ne(k));
 
     if (role == REWARD) {
-        if (lane == 0) {
-            for (int k = 0; k < IN_STAGES && k < my_tiles; ++k) {
-                const int e0 = (first + k * stride) * TE;
-                issue_tile_loads<D, NS, HUM>(b, in[k], &full[k], e0, min(TE, p.num_envs - e0), has_rnd);
-            }
+        // small per-env inputs are prefetched one tile ahead into registers (coalesced 8-B loads)
+        long long n_reset = 0, n_progress = 0, n_rand = 0;
+        if (lane < tile_ne(0)) {
+            const int e = tile_e0(0) + lane;
+            n_reset = b.reset_buf[e]; n_progress = b.progress_buf[e];
+            if (b.randomize_buf) n_rand = b.randomize_buf[e];
         }
         StatAcc st;
         for (int it = 0; it < my_tiles; ++it) {
-            const int s = it % IN_STAGES, o = it % OUT_STAGES;
-            const int e0 = (first + it * stride) * TE;
-            const int ne = min(TE, p.num_envs - e0);
-            // out[(it + 1) % OUT_STAGES] is written by the role warps right after the next barrier:
-            // its previous store (tile it + 1 - OUT_STAGES) must have finished reading shared memory.
-            if (lane == 0) bulk_wait_read<OUT_STAGES - 2>();
-            __syncthreads();  // barrier #it: the role warps have produced tile `it`
-            ige::mbar_wait(&full[s], (it / IN_STAGES) & 1);  // already complete: orders the TMA writes for us
-            if (lane < ne) role_reward<D, NS, HUM>(p, b, in[s], out[o], terms[it & 1], lane, e0, has_rnd, st);
-            ige::fence_proxy_async();
-            __syncwarp();
-            if (lane == 0) {
-                issue_tile_stores<NUM_OBS>(b, out[o], e0, ne, has_rnd, second_obs_copy);
-                if (it + IN_STAGES < my_tiles) {
-                    const int n0 = (first + (it + IN_STAGES) * stride) * TE;
-                    issue_tile_loads<D, NS, HUM>(b, in[s], &full[s], n0, min(TE, p.num_envs - n0), has_rnd);
-                }
+            const long long reset = n_reset, progress = n_progress, randomize = n_rand;
+            if (it + 1 < my_tiles && lane < tile_ne(it + 1)) {
+                const int e = tile_e0(it + 1) + lane;
+                n_reset = b.reset_buf[e]; n_progress = b.progress_buf[e];
+                if (b.randomize_buf) n_rand = b.randomize_buf[e];
             }
-            __syncwarp();
+            __syncthreads();  // barrier #it: the role warps have produced tile `it`
+            if (lane < tile_ne(it))
+                role_reward<D, HUM>(p, b, out[it & 1].obs + lane * NUM_OBS, hand[it & 1], lane, tile_e0(it) + lane,
+                                    reset, progress, randomize, st);
         }
-        if (lane == 0) bulk_wait_read<0>();  // shared memory must outlive the async reads
         if (b.stats) flush_stats(b.stats, st);
     } else {
+        // reset flag (+ potentials for HEADING) of env (tile, lane), prefetched one tile ahead
+        long long n_flag = 0;
+        float n_pot = 0.f;
+        if (lane < tile_ne(0)) {
+            n_flag = b.reset_buf[tile_e0(0) + lane];
+            if (role == HEADING) n_pot = b.potentials[tile_e0(0) + lane];
+        }
         for (int it = 0; it < my_tiles; ++it) {
-            const int s = it % IN_STAGES, o = it % OUT_STAGES;
-            const int e0 = (first + it * stride) * TE;
-            const int ne = min(TE, p.num_envs - e0);
-            ige::mbar_wait(&full[s], (it / IN_STAGES) & 1);
-            if (role == HEADING) {
-                if (lane < ne) role_heading<D, NS, HUM>(p, b, in[s], out[o], lane, e0);
-            } else if (role == VELOCITY) {
-                if (lane < ne) role_velocity<D, NS, HUM>(p, in[s], out[o], lane);
-            } else if (role == ANGLES) {
-                if (lane < ne) role_angles<D, NS, HUM>(p, in[s], out[o], lane);
+            const int s = it % IN_STAGES, o = it & 1;
+            const int e0 = tile_e0(it), ne = tile_ne(it);
+            const bool was_reset = n_flag != 0;
+            const float pot_in = n_pot;
+            if (it + 1 < my_tiles && lane < tile_ne(it + 1)) {
+                n_flag = b.reset_buf[tile_e0(it + 1) + lane];
+                if (role == HEADING) n_pot = b.potentials[tile_e0(it + 1) + lane];
             } else {
-                role_elem<D, NS, HUM>(p, b, in[s], out[o], terms[it & 1], lane, role - ELEM0, NW_ELEM, ne, e0, step);
+                n_flag = 0;
+            }
+            ige::mbar_wait(&full[s], (it / IN_STAGES) & 1);
+            float *obs_row = out[o].obs + lane * NUM_OBS;
+            const float *root = in[s].root + lane * 13;
+            if (role == HEADING) {
+                if (lane < ne) role_heading<D, NUM_OBS>(p, b, root, was_reset, pot_in, e0 + lane, obs_row, hand[o], lane);
+            } else if (role == VELOCITY) {
+                if (lane < ne) role_velocity<D, HUM>(p, root, obs_row, hand[o], lane);
+            } else if (role == ANGLES) {
+                if (lane < ne) role_angles<HUM>(p, root, obs_row);
+            } else {
+                role_elem<D, NS, HUM>(p, b, in[s], out[o].obs, hand[o], lane, role - ELEM0, NW_ELEM, ne, e0, step,
+                                      was_reset);
             }
             ige::fence_proxy_async();  // obs tile -> visible to the bulk-store (async) proxy
-            __syncthreads();           // barrier #it
-            if (clamp_copy) {          // finite clip: second, clamped copy with plain coalesced stores
-                // (reads out[o] concurrently with the bulk store; it is not rewritten before barrier
-                //  #(it + OUT_STAGES - 1), and every role warp passes through here first)
+            // out[o ^ 1] is rewritten right after this barrier: its store (tile it - 1, issued by this
+            // same thread one iteration ago) must have finished reading shared memory
+            if (role == ELEM0 && lane == 0) bulk_wait_read<0>();
+            __syncthreads();  // barrier #it
+            if (lane == 0) {
+                if (role == ELEM0) {  // tile `it` is complete in out[o]: one bulk store (two with the epilogue copy)
+                    ige::bulk_s2g(b.obs_buf + (size_t)e0 * NUM_OBS, out[o].obs, (uint32_t)ne * NUM_OBS * 4);
+                    if (second_obs_copy)
+                        ige::bulk_s2g(b.obs_clamped + (size_t)e0 * NUM_OBS, out[o].obs, (uint32_t)ne * NUM_OBS * 4);
+                    ige::bulk_commit();
+                }
+                if (it + IN_STAGES < my_tiles)  // in[s] is free again: refill it
+                    issue_tile_loads<D, NS, HUM>(role, b, in[s], &full[s], tile_e0(it + IN_STAGES),
+                                                 tile_ne(it + IN_STAGES));
+            }
+            if (clamp_copy) {  // finite clip: second, clamped copy with plain coalesced stores
                 const int reward_warp = (REWARD + NW - (int)(blockIdx.x % NW)) % NW;
                 for (int i = (warp > reward_warp ? tid - 32 : tid); i < ne * NUM_OBS; i += 32 * (NW - 1))
                     b.obs_clamped[(size_t)e0 * NUM_OBS + i] = clampf(out[o].obs[i], p.clip_obs);
             }
         }
+        if (role == ELEM0 && lane == 0) bulk_wait_read<0>();  // shared memory must outlive the async reads
     }
 }
 
@@ -480,13 +505,12 @@ locomotion_tile_kernel(const __grid_constant__ IgeLocomotionParams p, const __gr
     constexpr int NW = 4 + NW_ELEM;
     __shared__ InTile<D, NS, HUM> in;
     __shared__ OutTile<NUM_OBS> out;
-    __shared__ Terms<D> tm;
+    __shared__ Handoff<D> hand;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int role = (warp + (int)blockIdx.x) % NW;
     const int e0 = (blockIdx.x + tile_offset) * TE;
     const int ne = min(TE, p.num_envs - e0);
-    const bool has_rnd = b.randomize_buf != nullptr;
     const uint64_t step = (p.rand.mode == IGE_RAND_PHILOX && p.rand.step) ? __ldg(p.rand.step) : 0ull;
 
     coop_copy(in.root, b.root_states + (size_t)e0 * 13, ne * 13);
@@ -494,40 +518,39 @@ locomotion_tile_kernel(const __grid_constant__ IgeLocomotionParams p, const __gr
     coop_copy(in.sens, b.vec_sensor_tensor + (size_t)e0 * NS, ne * NS);
     if (HUM) coop_copy(in.force, b.dof_force_tensor + (size_t)e0 * D, ne * D);
     coop_copy(in.act, b.actions + (size_t)e0 * D, ne * D);
-    coop_copy(in.pot, (const float *)b.potentials + e0, ne);
-    coop_copy(in.reset, (const long long *)b.reset_buf + e0, ne);
-    coop_copy(in.progress, (const long long *)b.progress_buf + e0, ne);
-    if (has_rnd) coop_copy(in.randomize, (const long long *)b.randomize_buf + e0, ne);
+    long long reset = 0, progress = 0, randomize = 0;
+    float pot_in = 0.f;
+    if (lane < ne) {
+        reset = b.reset_buf[e0 + lane];
+        if (role == HEADING) pot_in = b.potentials[e0 + lane];
+        if (role == REWARD) {
+            progress = b.progress_buf[e0 + lane];
+            if (b.randomize_buf) randomize = b.randomize_buf[e0 + lane];
+        }
+    }
     __syncthreads();
 
+    float *obs_row = out.obs + lane * NUM_OBS;
+    const float *root = in.root + lane * 13;
     if (role == HEADING) {
-        if (lane < ne) role_heading<D, NS, HUM>(p, b, in, out, lane, e0);
+        if (lane < ne) role_heading<D, NUM_OBS>(p, b, root, reset != 0, pot_in, e0 + lane, obs_row, hand, lane);
     } else if (role == VELOCITY) {
-        if (lane < ne) role_velocity<D, NS, HUM>(p, in, out, lane);
+        if (lane < ne) role_velocity<D, HUM>(p, root, obs_row, hand, lane);
     } else if (role == ANGLES) {
-        if (lane < ne) role_angles<D, NS, HUM>(p, in, out, lane);
+        if (lane < ne) role_angles<HUM>(p, root, obs_row);
     } else if (role >= ELEM0) {
-        role_elem<D, NS, HUM>(p, b, in, out, tm, lane, role - ELEM0, NW_ELEM, ne, e0, step);
+        role_elem<D, NS, HUM>(p, b, in, out.obs, hand, lane, role - ELEM0, NW_ELEM, ne, e0, step, reset != 0);
     }
     __syncthreads();
     if (role == REWARD) {
         StatAcc st;
-        if (lane < ne) role_reward<D, NS, HUM>(p, b, in, out, tm, lane, e0, has_rnd, st);
+        if (lane < ne) role_reward<D, HUM>(p, b, obs_row, hand, lane, e0 + lane, reset, progress, randomize, st);
         if (b.stats) flush_stats(b.stats, st);
     }
-    __syncthreads();
     coop_copy(b.obs_buf + (size_t)e0 * NUM_OBS, (const float *)out.obs, ne * NUM_OBS);
     if (b.obs_clamped)
         for (int i = tid; i < ne * NUM_OBS; i += blockDim.x)
             b.obs_clamped[(size_t)e0 * NUM_OBS + i] = clampf(out.obs[i], p.clip_obs);
-    coop_copy(b.rew_buf + e0, (const float *)out.rew, ne);
-    coop_copy(b.potentials + e0, (const float *)out.pot, ne);
-    coop_copy(b.prev_potentials + e0, (const float *)out.prev, ne);
-    coop_copy(b.up_vec + (size_t)e0 * 3, (const float *)out.up, ne * 3);
-    coop_copy(b.heading_vec + (size_t)e0 * 3, (const float *)out.head, ne * 3);
-    coop_copy((long long *)b.reset_buf + e0, (const long long *)out.reset, ne);
-    coop_copy((long long *)b.progress_buf + e0, (const long long *)out.progress, ne);
-    if (has_rnd) coop_copy((long long *)b.randomize_buf + e0, (const long long *)out.randomize, ne);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -568,13 +591,13 @@ int check(const IgeLocomotionParams *p, const IgeLocomotionBuffers *b, int d, in
     return ige_check_rand(p->rand);
 }
 
-template <int D, int NS, bool HUM, int NW_ELEM, int IN_STAGES, int OUT_STAGES>
+template <int D, int NS, bool HUM, int NW_ELEM, int IN_STAGES>
 int launch(const IgeLocomotionParams *p, const IgeLocomotionBuffers *b, cudaStream_t stream, const char *name) {
     constexpr int NT = 32 * (4 + NW_ELEM);
     constexpr int NUM_OBS = Layout<D, NS, HUM>::NUM_OBS;
-    constexpr size_t smem = sizeof(InTile<D, NS, HUM>) * IN_STAGES + sizeof(OutTile<NUM_OBS>) * OUT_STAGES +
-                            sizeof(Terms<D>) * 2 + sizeof(uint64_t) * IN_STAGES;
-    auto kern = locomotion_pipelined_kernel<D, NS, HUM, NW_ELEM, IN_STAGES, OUT_STAGES>;
+    constexpr size_t smem = sizeof(InTile<D, NS, HUM>) * IN_STAGES + sizeof(OutTile<NUM_OBS>) * 2 +
+                            sizeof(Handoff<D>) * 2 + sizeof(uint64_t) * IN_STAGES;
+    auto kern = locomotion_pipelined_kernel<D, NS, HUM, NW_ELEM, IN_STAGES>;
     static int max_ctas = 0;  // resident CTAs on the current device (per template instance)
     if (max_ctas == 0) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -617,11 +640,11 @@ extern "C" void ige_set_use_tma(int on) { g_use_tma = on ? 1 : 0; }
 extern "C" int ige_ant_post_physics(const IgeLocomotionParams *p, const IgeLocomotionBuffers *b, void *stream) {
     if (int rc = check(p, b, 8, 24, false)) return rc;
     if (p->num_envs == 0) return IGE_OK;
-    return launch<8, 24, false, 1, 2, 3>(p, b, (cudaStream_t)stream, "ige_ant_post_physics");
+    return launch<8, 24, false, 1, 2>(p, b, (cudaStream_t)stream, "ige_ant_post_physics");
 }
 
 extern "C" int ige_humanoid_post_physics(const IgeLocomotionParams *p, const IgeLocomotionBuffers *b, void *stream) {
     if (int rc = check(p, b, 21, 12, true)) return rc;
     if (p->num_envs == 0) return IGE_OK;
-    return launch<21, 12, true, 3, 2, 3>(p, b, (cudaStream_t)stream, "ige_humanoid_post_physics");
+    return launch<21, 12, true, 3, 2>(p, b, (cudaStream_t)stream, "ige_humanoid_post_physics");
 }
