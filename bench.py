@@ -7,7 +7,7 @@ torchrun for N > 1 (one rank per GPU); rank 0 prints ONE JSON line.
 Workload at every N: BASELINE.json configs[1] / configs[4] -- Ant post_physics_step, 16384 envs per
 GPU, synthetic post-simulate state (isaacgymenvs-ma_b200/synthetic.py), natural reset rate.
 A "step" is one pass of the hot path over all envs of a GPU: device-side `reset_buf.nonzero()`
-(ige_compact_resets) + ONE fused kernel (ige_ant_post_physics), replayed from a CUDA graph.
+inside ONE fused kernel (ige_ant_post_physics), replayed from a CUDA graph.
 
 L2 hygiene: the timed loop rotates through `replicas` independent copies of the whole env state
 whose total footprint exceeds 2x the 126 MB L2, so every step streams its tile from HBM.
@@ -192,7 +192,7 @@ def run_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         elapsed = float(t.item())
     value = n * world * args.steps / elapsed
-    kernels_per_step = 2
+    kernels_per_step = 1
     gpu_launches = args.steps * kernels_per_step
 
     # ---- dominant kernel alone (roofline): fused kernel only, same rotation, CUDA events ----
@@ -296,7 +296,7 @@ def run_e2e(pkg, args, device, dist=None, world=1):
         el = float(t.item())
     return {"value": n * world * steps / el, "unit": "env-steps/s", "h2d_bytes_per_step": h2d,
             "d2h_bytes_per_step": d2h, "ms_per_step": el / steps * 1e3, "wall_ms_per_step": wall / steps * 1e3,
-            "api": "Ant.post_physics_step() (ctypes -> ige_compact_resets + ige_ant_post_physics), pinned host buffers"}
+            "api": "Ant.post_physics_step() (ctypes -> ige_ant_post_physics), pinned host buffers"}
 
 
 def run_sweep(pkg, args, device, peak):

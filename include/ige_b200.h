@@ -55,8 +55,9 @@ typedef struct IgeResetRand {
     int32_t mode;              /* IGE_RAND_* */
     int32_t _pad;
     uint64_t seed;             /* PHILOX: key */
-    const uint64_t *step;      /* PHILOX: device word mixed into the counter (bumped once per step
-                                  by ige_compact_resets); NULL = 0 */
+    uint64_t *step;            /* PHILOX: device word mixed into the counter; read at kernel entry and
+                                  incremented by one at kernel exit by every step kernel that is given a
+                                  reset list (IgeResetList.scratch != NULL); NULL = 0 */
     const int32_t *reset_rank; /* INJECTED: [N] exclusive prefix sum of (reset_buf != 0), i.e. the row
                                   of env n in u0/u1 == its position in reset_buf.nonzero() */
     const float *u0;           /* INJECTED: uniforms of the 1st torch.rand call of reset_idx, (k, D) */
@@ -72,6 +73,22 @@ typedef struct IgeResetRand {
 #define IGE_STAT_DONE_LENGTH 4  /* sum progress_buf over done rows */
 #define IGE_STAT_TASK0 5        /* task specific, see each task */
 
+/* Reset index list emitted by every step kernel: the ids of the envs that were reset IN this step
+ * (== reset_buf.nonzero() at entry; for agent-axis tasks the envs whose agents were ALL flagged),
+ * ascending int32 -- what gym.set_*_tensor_indexed consumes (ant.py:263-271).  Produced inside the
+ * fused kernel (persistent kernels: contiguous tile ranges per CTA + a CTA-level look-back over the
+ * per-CTA counts, fully overlapped with the step; small kernels: ballot masks expanded by the CTA that
+ * retires last).  Optional as a whole (scratch == NULL: no list, rand.step is not advanced). */
+typedef struct IgeResetList {
+    int32_t *ids;      /* [num_envs] out; the first *count entries are valid */
+    int32_t *count;    /* [1] out */
+    uint32_t *scratch; /* [ige_reset_list_scratch_words(num_envs)] device words, 16-B aligned, zeroed ONCE by
+                          the caller and then owned by the kernels (launch epoch, per-CTA look-back slots,
+                          retirement counters, tile masks) */
+} IgeResetList;
+
+int ige_reset_list_scratch_words(int32_t num_envs);
+
 /* ------------------------------------------------------------------------------------------
  * Reset compaction: reset_buf.nonzero() (ant.py:291, cartpole.py:168, franka_reach_MA.py:824)
  * ------------------------------------------------------------------------------------------ */
@@ -84,7 +101,6 @@ typedef struct IgeCompactArgs {
     int32_t *reset_ids;        /* [num_rows/group] out: ascending ids, first *count entries valid */
     int32_t *reset_rank;       /* [num_rows/group] out: exclusive prefix of the per-env flag */
     int32_t *count;            /* [1] out */
-    uint64_t *step;            /* [1] in/out: incremented by one (Philox step word); may be NULL */
     uint32_t *scratch;         /* [ige_compact_scratch_words(num_rows/group)] device words, zeroed ONCE by
                                   the caller; every launch leaves them zero again (graph re-playable) */
 } IgeCompactArgs;
@@ -113,6 +129,7 @@ typedef struct IgeCartpoleBuffers {
     float *obs_clamped;        /* (N, 4) out, optional: clamp(obs_buf, +-clip_obs) (vec_task.py:404) */
     uint8_t *timeout_buf;      /* (N) out, optional: bool time_outs (vec_task.py:396) */
     float *stats;              /* [IGE_STATS_ROWS * IGE_STATS_STRIDE] in/out, optional */
+    IgeResetList list;         /* optional */
 } IgeCartpoleBuffers;
 
 int ige_cartpole_post_physics(const IgeCartpoleParams *p, const IgeCartpoleBuffers *b, void *stream);
@@ -162,6 +179,7 @@ typedef struct IgeLocomotionBuffers {
     float *obs_clamped;               /* optional, see Cartpole */
     uint8_t *timeout_buf;             /* optional */
     float *stats;                     /* optional; TASK0 = sum root_states[:,7] (true_objective, ant.py:245-250) */
+    IgeResetList list;                /* optional */
 } IgeLocomotionBuffers;
 
 int ige_ant_post_physics(const IgeLocomotionParams *p, const IgeLocomotionBuffers *b, void *stream);

@@ -23,9 +23,13 @@ class IgeResetRand(C.Structure):
                 ("reset_rank", _p), ("u0", _p), ("u1", _p)]
 
 
+class IgeResetList(C.Structure):
+    _fields_ = [("ids", _p), ("count", _p), ("scratch", _p)]
+
+
 class IgeCompactArgs(C.Structure):
     _fields_ = [("num_rows", _i), ("group", _i), ("reset_buf", _p), ("reset_ids", _p),
-                ("reset_rank", _p), ("count", _p), ("step", _p), ("scratch", _p)]
+                ("reset_rank", _p), ("count", _p), ("scratch", _p)]
 
 
 class IgeCartpoleParams(C.Structure):
@@ -35,7 +39,8 @@ class IgeCartpoleParams(C.Structure):
 
 class IgeCartpoleBuffers(C.Structure):
     _fields_ = [("dof_state", _p), ("obs_buf", _p), ("rew_buf", _p), ("reset_buf", _p),
-                ("progress_buf", _p), ("obs_clamped", _p), ("timeout_buf", _p), ("stats", _p)]
+                ("progress_buf", _p), ("obs_clamped", _p), ("timeout_buf", _p), ("stats", _p),
+                ("list", IgeResetList)]
 
 
 class IgeLocomotionParams(C.Structure):
@@ -59,9 +64,14 @@ class IgeLocomotionBuffers(C.Structure):
                 ("initial_dof_pos", _p), ("potentials", _p), ("prev_potentials", _p),
                 ("up_vec", _p), ("heading_vec", _p), ("obs_buf", _p), ("rew_buf", _p),
                 ("reset_buf", _p), ("progress_buf", _p), ("randomize_buf", _p),
-                ("obs_clamped", _p), ("timeout_buf", _p), ("stats", _p)]
+                ("obs_clamped", _p), ("timeout_buf", _p), ("stats", _p), ("list", IgeResetList)]
 
 
 def fill_array(carr, values):
     for i, v in enumerate(values):
         carr[i] = float(v)
+
+
+def reset_list_scratch_words(num_envs):
+    """== ige_reset_list_scratch_words(): look-back slots + retirement counter + one mask word per 32 envs."""
+    return 2 * (2 + 2040) + 4 + (((num_envs + 31) // 32 + 3) // 4) * 4

@@ -36,6 +36,8 @@ def lib():
         l.ige_launch_count.restype = C.c_uint64
         l.ige_compact_scratch_words.restype = C.c_int
         l.ige_compact_scratch_words.argtypes = [C.c_int32]
+        l.ige_reset_list_scratch_words.restype = C.c_int
+        l.ige_reset_list_scratch_words.argtypes = [C.c_int32]
         l.ige_set_use_tma.restype = None
         l.ige_set_use_tma.argtypes = [C.c_int]
         for name, structs in _SIGS.items():
@@ -50,7 +52,7 @@ def lib():
 
 def exported_symbols():
     return ["ige_version", "ige_last_error_string", "ige_launch_count", "ige_compact_scratch_words",
-            "ige_set_use_tma", *_SIGS.keys()]
+            "ige_reset_list_scratch_words", "ige_set_use_tma", *_SIGS.keys()]
 
 
 def call(name, *structs, stream=0):

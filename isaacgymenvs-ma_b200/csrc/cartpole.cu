@@ -11,12 +11,14 @@ constexpr int kThreads = 128;
 
 __global__ void __launch_bounds__(kThreads) cartpole_post_physics_kernel(IgeCartpoleParams p, IgeCartpoleBuffers b) {
     const int e = blockIdx.x * kThreads + threadIdx.x;
-    const uint64_t step = (p.rand.mode == IGE_RAND_PHILOX && p.rand.step) ? __ldg(p.rand.step) : 0ull;
+    const uint64_t step = ige::load_step(p.rand);
     float st_rew = 0.f, st_done = 0.f, st_to = 0.f, st_len = 0.f, st_n = 0.f;
+    bool was_reset = false;
     if (e < p.num_envs) {
         float4 ds = reinterpret_cast<const float4 *>(b.dof_state)[e];  // (x, xd, th, thd)
         long long progress = b.progress_buf[e] + 1;                   // cartpole.py:166
         long long reset = b.reset_buf[e];
+        was_reset = reset != 0;
         if (reset != 0) {                                              // reset_idx cartpole.py:144-157
             ds.x = 0.2f * (ige::reset_uniform(p.rand, step, 0, e, 2, 0) - 0.5f);
             ds.z = 0.2f * (ige::reset_uniform(p.rand, step, 0, e, 2, 1) - 0.5f);
@@ -52,11 +54,16 @@ __global__ void __launch_bounds__(kThreads) cartpole_post_physics_kernel(IgeCart
         st_n = 1.f; st_rew = reward; st_done = reset != 0 ? 1.f : 0.f; st_to = timeout ? 1.f : 0.f;
         st_len = reset != 0 ? (float)progress : 0.f;
     }
+    if (b.list.scratch) {  // warp == one 32-env tile of the reset list
+        const uint32_t mask = __ballot_sync(0xffffffffu, was_reset);
+        if ((threadIdx.x & 31) == 0 && e < p.num_envs) ige::publish_tile_mask(b.list, e >> 5, mask);
+    }
     if (b.stats) {
         const float v[5] = {st_n, st_rew, st_done, st_to, st_len};
         const int slot[5] = {IGE_STAT_STEPS, IGE_STAT_REWARD, IGE_STAT_DONE, IGE_STAT_TIMEOUT, IGE_STAT_DONE_LENGTH};
         ige::warp_stats_add<5>(b.stats, v, slot);
     }
+    if (b.list.scratch) ige::finish_reset_list(b.list, p.num_envs, p.rand.step, (threadIdx.x & 31) == 0);
 }
 
 }  // namespace
@@ -70,6 +77,7 @@ extern "C" int ige_cartpole_post_physics(const IgeCartpoleParams *p, const IgeCa
     IGE_REQUIRE_PTR(b->reset_buf);
     IGE_REQUIRE_PTR(b->progress_buf);
     IGE_OPTIONAL_PTR(b->obs_clamped);
+    if (int rc = ige_check_list(b->list)) return rc;
     if (int rc = ige_check_rand(p->rand)) return rc;
     if (p->num_envs == 0) return IGE_OK;
     const int grid = (p->num_envs + kThreads - 1) / kThreads;

@@ -102,7 +102,6 @@ __global__ void __launch_bounds__(kThreads) compact_resets_kernel(IgeCompactArgs
         if (tid == 0) {
             scratch[0] = 0u;
             scratch[1] = 0u;
-            if (a.step) *a.step += 1ull;
         }
     }
 }
@@ -124,3 +123,5 @@ extern "C" int ige_compact_resets(const IgeCompactArgs *a, void *stream) {
     compact_resets_kernel<<<num_chunks, kThreads, 0, (cudaStream_t)stream>>>(*a, num_chunks);
     return ige_check_launch("ige_compact_resets");
 }
+
+extern "C" int ige_reset_list_scratch_words(int32_t num_envs) { return ige::reset_list_scratch_words(num_envs); }

@@ -38,6 +38,13 @@ static inline int ige_check_rand(const IgeResetRand &r) {
     return IGE_OK;
 }
 
+static inline int ige_check_list(const IgeResetList &l) {
+    if (l.scratch == nullptr) return IGE_OK;
+    if (l.ids == nullptr || l.count == nullptr) return ige_fail(IGE_ENULL, "list.ids / list.count is NULL");
+    if ((reinterpret_cast<uintptr_t>(l.scratch) & 15u) != 0) return ige_fail(IGE_EALIGN, "list.scratch is not 16-byte aligned");
+    return IGE_OK;
+}
+
 #ifdef __CUDACC__
 // ---------------------------------------------------------------------------------------------
 // device math (reference: isaacgymenvs/utils/torch_jit_utils.py)
@@ -164,6 +171,10 @@ __device__ __forceinline__ float philox_uniform(const IgeResetRand &r, uint64_t 
     philox4x32_10(c, (uint32_t)r.seed, (uint32_t)(r.seed >> 32));
     return (float)(c[idx & 3] >> 8) * (1.0f / 16777216.0f);
 }
+// Philox step word at kernel entry (plain load: the CTA that retires last advances it)
+__device__ __forceinline__ uint64_t load_step(const IgeResetRand &r) {
+    return (r.mode == IGE_RAND_PHILOX && r.step) ? *reinterpret_cast<const volatile uint64_t *>(r.step) : 0ull;
+}
 // uniform `j` of torch.rand call `which` (0/1) for reset row `row` with `d` columns
 __device__ __forceinline__ float reset_uniform(const IgeResetRand &r, uint64_t step, int which, int row,
                                                int d, int j) {
@@ -241,6 +252,100 @@ __device__ __forceinline__ void warp_stats_add(float *stats, const float (&v)[NS
         if (lane == s) { mine = t; my_slot = slot[s]; }
     }
     if (lane < NSTAT) atomicAdd(stats + (blockIdx.x % IGE_STATS_ROWS) * IGE_STATS_STRIDE + my_slot, mine);
+}
+
+// ---------------------------------------------------------------------------------------------
+// reset index list (IgeResetList): tile masks -> ascending ids, by the CTA that retires last
+// ---------------------------------------------------------------------------------------------
+// Scratch layout (uint32 words, zeroed once by the caller).  Two emission schemes share it:
+//   persistent kernels (blocked tiles, CTA-level look-back):
+//     64-bit word 0 = launch epoch, word 1 = {unused, retirement counter}, words 2.. = per-CTA slots
+//     {epoch + 1 : count}, kListMaxCtas of them;
+//   one-tile-per-warp kernels (masks + last-CTA expansion): uint32 word kListCounterWord = retirement
+//     counter, ballot masks from kListMaskBase on.
+constexpr int kListMaxCtas = 2040;
+constexpr int kListCounterWord = 2 * (2 + kListMaxCtas);  // 4084
+constexpr int kListMaskBase = kListCounterWord + 4;       // 16-B aligned
+
+__host__ __device__ inline int reset_list_scratch_words(int num_envs) {
+    return kListMaskBase + (((num_envs + 31) / 32 + 3) / 4) * 4;
+}
+// One thread publishes the ballot mask of 32-env tile `tile` (bit i = env tile*32+i was reset).
+// No fence here: finish_reset_list() fences once per publishing thread.
+__device__ __forceinline__ void publish_tile_mask(const IgeResetList &L, int tile, uint32_t mask) {
+    L.scratch[kListMaskBase + tile] = mask;
+}
+// finish_reset_list() is called by EVERY thread of EVERY CTA once, after the CTA's masks are published
+// (`i_published`: this thread wrote masks).  The CTA that arrives last expands all masks (blocked
+// partition, batched vector loads, block scan) into L.ids / L.count, re-zeroes the counter and
+// advances the Philox step word.
+// (kept out of line: it runs in ONE CTA per launch and must not inflate the step kernels' registers)
+static __device__ __noinline__ void expand_reset_list(const IgeResetList L, const int num_envs, uint64_t *step) {
+    __shared__ int s_wtot[32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nthr = blockDim.x, nwarps = (nthr + 31) >> 5;
+    __threadfence();
+    const int tiles4 = ((num_envs + 31) / 32 + 3) / 4;
+    const uint4 *m4 = reinterpret_cast<const uint4 *>(L.scratch + kListMaskBase);
+    const int per = (tiles4 + nthr - 1) / nthr;
+    const int lo = min(tiles4, tid * per), hi = min(tiles4, lo + per);
+    constexpr int B = 4;  // loads in flight per thread
+    int cnt = 0;
+    for (int i0 = lo; i0 < hi; i0 += B) {
+        uint4 m[B];
+#pragma unroll
+        for (int k = 0; k < B; ++k) m[k] = (i0 + k < hi) ? __ldcg(m4 + i0 + k) : make_uint4(0, 0, 0, 0);
+#pragma unroll
+        for (int k = 0; k < B; ++k) cnt += __popc(m[k].x) + __popc(m[k].y) + __popc(m[k].z) + __popc(m[k].w);
+    }
+    int incl = cnt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
+    }
+    if (lane == 31) s_wtot[warp] = incl;
+    __syncthreads();
+    int woff = 0, total = 0;
+    for (int w = 0; w < nwarps; ++w) {
+        const int t = s_wtot[w];
+        if (w < warp) woff += t;
+        total += t;
+    }
+    int off = woff + incl - cnt;
+    if (cnt > 0) {
+        for (int i0 = lo; i0 < hi; i0 += B) {
+            uint4 m[B];
+#pragma unroll
+            for (int k = 0; k < B; ++k) m[k] = (i0 + k < hi) ? __ldcg(m4 + i0 + k) : make_uint4(0, 0, 0, 0);
+#pragma unroll
+            for (int k = 0; k < B; ++k) {
+                const uint32_t w4[4] = {m[k].x, m[k].y, m[k].z, m[k].w};
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    uint32_t mw = w4[q];
+                    const int base = ((i0 + k) * 4 + q) * 32;
+                    while (mw) {
+                        L.ids[off++] = base + __ffs(mw) - 1;
+                        mw &= mw - 1;
+                    }
+                }
+            }
+        }
+    }
+    if (tid == 0) {
+        *L.count = total;
+        L.scratch[kListCounterWord] = 0u;
+        if (step) *step += 1ull;
+    }
+}
+__device__ __forceinline__ void finish_reset_list(const IgeResetList &L, int num_envs, uint64_t *step,
+                                                  bool i_published) {
+    __shared__ int s_last;
+    if (i_published) __threadfence();  // my masks are visible device-wide before this CTA counts as retired
+    __syncthreads();
+    if (threadIdx.x == 0) s_last = atomicAdd(&L.scratch[kListCounterWord], 1u) == gridDim.x - 1;
+    __syncthreads();
+    if (s_last) expand_reset_list(L, num_envs, step);
 }
 
 }  // namespace ige

@@ -348,6 +348,7 @@ __device__ __forceinline__ void bulk_wait_read() {
 }
 
 enum Role { HEADING = 0, VELOCITY = 1, ANGLES = 2, REWARD = 3, ELEM0 = 4 };
+enum EmitMode { EMIT_NONE = 0, EMIT_MASKS = 1, EMIT_APPEND = 2 };
 
 // Bulk loads of one tile, split over the lane 0s of the four role warps so they issue in parallel.
 // HEADING also arms the barrier (expect_tx may legally trail the first complete_tx: the phase
@@ -376,9 +377,10 @@ __device__ __forceinline__ void issue_tile_loads(int role, const IgeLocomotionBu
 // has ne % 4 == 0 envs (only the last may be partial).
 // ---------------------------------------------------------------------------------------------
 template <int D, int NS, bool HUM, int NW_ELEM, int IN_STAGES>
-__global__ void __launch_bounds__(32 * (4 + NW_ELEM))
+__global__ void __launch_bounds__(32 * (4 + NW_ELEM), HUM ? 3 : 6)  // caps registers: 6 (Ant) / 3 (Humanoid) CTAs per SM
 locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p,
-                            const __grid_constant__ IgeLocomotionBuffers b, const int num_tiles) {
+                            const __grid_constant__ IgeLocomotionBuffers b, const int num_tiles,
+                            const int tiles_per_cta) {
     using L = Layout<D, NS, HUM>;
     constexpr int NUM_OBS = L::NUM_OBS;
     constexpr int NW = 4 + NW_ELEM;
@@ -391,15 +393,18 @@ locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p,
     uint64_t *full = reinterpret_cast<uint64_t *>(smem_raw + sizeof(In) * IN_STAGES + sizeof(Out) * 2);
     Handoff<D> *hand = reinterpret_cast<Handoff<D> *>(smem_raw + sizeof(In) * IN_STAGES + sizeof(Out) * 2 +
                                                       sizeof(uint64_t) * IN_STAGES);
+    uint32_t *tile_masks = reinterpret_cast<uint32_t *>(hand + 2);  // [tiles_per_cta] reset ballots of my tiles
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int role = (warp + (int)blockIdx.x) % NW;
-    const int first = blockIdx.x, stride = gridDim.x;
-    const int my_tiles = (num_tiles - first + stride - 1) / stride;
+    // blocked assignment: CTA c owns the contiguous tiles [c*K, c*K + my_tiles) -- its reset ids are then
+    // one contiguous run of the output list
+    const int first = blockIdx.x * tiles_per_cta;
+    const int my_tiles = min(tiles_per_cta, num_tiles - first);
     const bool clamp_copy = b.obs_clamped != nullptr && p.clip_obs < INFINITY;
     const bool second_obs_copy = b.obs_clamped != nullptr && !clamp_copy;
-    const uint64_t step = (p.rand.mode == IGE_RAND_PHILOX && p.rand.step) ? __ldg(p.rand.step) : 0ull;
-    auto tile_e0 = [&](int it) { return (first + it * stride) * TE; };
+    const uint64_t step = ige::load_step(p.rand);
+    auto tile_e0 = [&](int it) { return (first + it) * TE; };
     auto tile_ne = [&](int it) { return min(TE, p.num_envs - tile_e0(it)); };
 
     if (tid == 0) {
@@ -421,6 +426,27 @@ locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p,
             n_reset = b.reset_buf[e]; n_progress = b.progress_buf[e];
             if (b.randomize_buf) n_rand = b.randomize_buf[e];
         }
+        // ---- reset index list, part 1 (while the role warps work on the first tile): count my resets
+        //      and publish the count early, so nobody has to wait for it later ----
+        const bool emit = b.list.scratch != nullptr;
+        volatile uint64_t *sc = reinterpret_cast<volatile uint64_t *>(b.list.scratch);
+        uint64_t tag = 0;
+        int cnt = 0;
+        if (emit) {
+            tag = sc[0] + 1;  // launch epoch + 1 (the scratch starts zeroed)
+            constexpr int PB = 8;            // flag loads in flight
+            for (int it0 = 0; it0 < my_tiles; it0 += PB) {
+                long long f[PB];
+#pragma unroll
+                for (int k = 0; k < PB; ++k) {
+                    const int e = tile_e0(it0 + k) + lane;
+                    f[k] = (it0 + k < my_tiles && e < p.num_envs) ? b.reset_buf[e] : 0;
+                }
+#pragma unroll
+                for (int k = 0; k < PB; ++k) cnt += __popc(__ballot_sync(0xffffffffu, f[k] != 0));
+            }
+            if (lane == 0) sc[2 + blockIdx.x] = (tag << 32) | (uint32_t)cnt;
+        }
         StatAcc st;
         for (int it = 0; it < my_tiles; ++it) {
             const long long reset = n_reset, progress = n_progress, randomize = n_rand;
@@ -428,6 +454,12 @@ locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p,
                 const int e = tile_e0(it + 1) + lane;
                 n_reset = b.reset_buf[e]; n_progress = b.progress_buf[e];
                 if (b.randomize_buf) n_rand = b.randomize_buf[e];
+            } else {
+                n_reset = 0;  // lanes past the end of a partial tile must not leak stale flags
+            }
+            if (emit) {
+                const uint32_t mask = __ballot_sync(0xffffffffu, reset != 0);
+                if (lane == 0) tile_masks[it] = mask;
             }
             __syncthreads();  // barrier #it: the role warps have produced tile `it`
             if (lane < tile_ne(it))
@@ -435,6 +467,61 @@ locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p,
                                     reset, progress, randomize, st);
         }
         if (b.stats) flush_stats(b.stats, st);
+        // ---- reset index list, part 2 (last thing this warp does): offset = sum of the predecessor CTAs'
+        //      counts, published long ago; then the ascending ids of my tiles ----
+        if (emit) {
+            // Predecessors have lower block ids, so they were dispatched before this CTA: the wait cannot
+            // deadlock.  Loads go out in batches (no dependent chain); only unpublished slots are re-polled.
+            // Retirement ticket, issued now so that its round trip overlaps the polling below.  Every role
+            // warp of this CTA has passed its last barrier, i.e. has long consumed the epoch / Philox step.
+            unsigned ticket = 0;
+            if (lane == 0) ticket = atomicInc(b.list.scratch + 2, gridDim.x - 1);
+            int sum = 0;
+            constexpr int LB = 8;
+            for (int c0 = lane; c0 < (int)blockIdx.x; c0 += 32 * LB) {
+                uint64_t v[LB];
+                bool ok;
+                do {
+                    ok = true;
+#pragma unroll
+                    for (int k = 0; k < LB; ++k) {
+                        const int c = c0 + 32 * k;
+                        v[k] = c < (int)blockIdx.x ? sc[2 + c] : (tag << 32);
+                        ok &= (v[k] >> 32) == tag;
+                    }
+                } while (!ok);
+#pragma unroll
+                for (int k = 0; k < LB; ++k) sum += (int)(uint32_t)v[k];
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+            if (blockIdx.x == gridDim.x - 1 && lane == 0) *b.list.count = sum + cnt;
+            __syncwarp();
+            // lane l expands tiles l, l + 32, ...: exclusive scan of the tile counts, then the set bits
+            for (int t0 = 0; t0 < my_tiles; t0 += 32) {
+                const int t = t0 + lane;
+                uint32_t m = t < my_tiles ? tile_masks[t] : 0u;
+                const int c = __popc(m);
+                int incl = c;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const int u = __shfl_up_sync(0xffffffffu, incl, o);
+                    if (lane >= o) incl += u;
+                }
+                int off = sum + incl - c;
+                const int base = tile_e0(t);
+                while (m) {
+                    b.list.ids[off++] = base + __ffs(m) - 1;
+                    m &= m - 1;
+                }
+                sum += __shfl_sync(0xffffffffu, incl, 31);
+            }
+            // the CTA that retires last opens the next launch epoch and advances the Philox step word
+            if (lane == 0 && ticket == gridDim.x - 1) {
+                sc[0] = sc[0] + 1;
+                if (p.rand.step) *p.rand.step += 1ull;
+            }
+        }
     } else {
         // reset flag (+ potentials for HEADING) of env (tile, lane), prefetched one tile ahead
         long long n_flag = 0;
@@ -499,7 +586,7 @@ locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p,
 template <int D, int NS, bool HUM, int NW_ELEM>
 __global__ void __launch_bounds__(32 * (4 + NW_ELEM))
 locomotion_tile_kernel(const __grid_constant__ IgeLocomotionParams p, const __grid_constant__ IgeLocomotionBuffers b,
-                       const int tile_offset) {
+                       const int tile_offset, const int emit_mode) {
     using L = Layout<D, NS, HUM>;
     constexpr int NUM_OBS = L::NUM_OBS;
     constexpr int NW = 4 + NW_ELEM;
@@ -511,7 +598,7 @@ locomotion_tile_kernel(const __grid_constant__ IgeLocomotionParams p, const __gr
     const int role = (warp + (int)blockIdx.x) % NW;
     const int e0 = (blockIdx.x + tile_offset) * TE;
     const int ne = min(TE, p.num_envs - e0);
-    const uint64_t step = (p.rand.mode == IGE_RAND_PHILOX && p.rand.step) ? __ldg(p.rand.step) : 0ull;
+    const uint64_t step = ige::load_step(p.rand);
 
     coop_copy(in.root, b.root_states + (size_t)e0 * 13, ne * 13);
     coop_copy(in.dof, (const float *)b.dof_state + (size_t)e0 * D * 2, ne * D * 2);
@@ -543,6 +630,17 @@ locomotion_tile_kernel(const __grid_constant__ IgeLocomotionParams p, const __gr
     }
     __syncthreads();
     if (role == REWARD) {
+        if (b.list.scratch && emit_mode == EMIT_MASKS) {  // sole kernel of the step: masks, expanded below
+            const uint32_t mask = __ballot_sync(0xffffffffu, reset != 0);
+            if (lane == 0) ige::publish_tile_mask(b.list, blockIdx.x + tile_offset, mask);
+        }
+        if (b.list.scratch && emit_mode == EMIT_APPEND) {  // the one ragged tile after the pipelined kernel
+            const uint32_t mask = __ballot_sync(0xffffffffu, reset != 0);
+            const int base = *b.list.count;
+            __syncwarp();
+            if (reset != 0) b.list.ids[base + __popc(mask & ((1u << lane) - 1u))] = e0 + lane;
+            if (lane == 0) *b.list.count = base + __popc(mask);
+        }
         StatAcc st;
         if (lane < ne) role_reward<D, HUM>(p, b, obs_row, hand, lane, e0 + lane, reset, progress, randomize, st);
         if (b.stats) flush_stats(b.stats, st);
@@ -551,6 +649,8 @@ locomotion_tile_kernel(const __grid_constant__ IgeLocomotionParams p, const __gr
     if (b.obs_clamped)
         for (int i = tid; i < ne * NUM_OBS; i += blockDim.x)
             b.obs_clamped[(size_t)e0 * NUM_OBS + i] = clampf(out.obs[i], p.clip_obs);
+    if (b.list.scratch && emit_mode == EMIT_MASKS)
+        ige::finish_reset_list(b.list, p.num_envs, p.rand.step, role == REWARD && lane == 0);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -588,6 +688,7 @@ int check(const IgeLocomotionParams *p, const IgeLocomotionBuffers *b, int d, in
     IGE_REQUIRE_PTR(b->progress_buf);
     IGE_OPTIONAL_PTR(b->randomize_buf);
     IGE_OPTIONAL_PTR(b->obs_clamped);
+    if (int rc = ige_check_list(b->list)) return rc;
     return ige_check_rand(p->rand);
 }
 
@@ -595,8 +696,9 @@ template <int D, int NS, bool HUM, int NW_ELEM, int IN_STAGES>
 int launch(const IgeLocomotionParams *p, const IgeLocomotionBuffers *b, cudaStream_t stream, const char *name) {
     constexpr int NT = 32 * (4 + NW_ELEM);
     constexpr int NUM_OBS = Layout<D, NS, HUM>::NUM_OBS;
+    constexpr int kMaxTilesPerCta = 1024;  // per-CTA reset-ballot scratch (4 KB): covers 24 M envs on a B200
     constexpr size_t smem = sizeof(InTile<D, NS, HUM>) * IN_STAGES + sizeof(OutTile<NUM_OBS>) * 2 +
-                            sizeof(Handoff<D>) * 2 + sizeof(uint64_t) * IN_STAGES;
+                            sizeof(Handoff<D>) * 2 + sizeof(uint64_t) * IN_STAGES + sizeof(uint32_t) * kMaxTilesPerCta;
     auto kern = locomotion_pipelined_kernel<D, NS, HUM, NW_ELEM, IN_STAGES>;
     static int max_ctas = 0;  // resident CTAs on the current device (per template instance)
     if (max_ctas == 0) {
@@ -609,6 +711,7 @@ int launch(const IgeLocomotionParams *p, const IgeLocomotionBuffers *b, cudaStre
         if (e != cudaSuccess || per_sm < 1 || sms < 1)
             return ige_fail(e != cudaSuccess ? (int)e : IGE_EPARAM, "%s: occupancy query failed", name);
         max_ctas = sms * per_sm;
+        if (max_ctas > ige::kListMaxCtas) max_ctas = ige::kListMaxCtas;
     }
     const int n = p->num_envs;
     const int full_tiles = n / TE, rem = n % TE;
@@ -622,12 +725,15 @@ int launch(const IgeLocomotionParams *p, const IgeLocomotionBuffers *b, cudaStre
         fallback_tiles = full_tiles + (rem > 0 ? 1 : 0);
     }
     if (pipelined_tiles > 0) {
-        const int grid = pipelined_tiles < max_ctas ? pipelined_tiles : max_ctas;
-        kern<<<grid, NT, smem, stream>>>(*p, *b, pipelined_tiles);
+        const int per_cta = (pipelined_tiles + max_ctas - 1) / max_ctas;   // contiguous tiles per CTA
+        if (per_cta > kMaxTilesPerCta) return ige_fail(IGE_ESIZE, "%s: num_envs=%d too large for one launch", name, n);
+        const int grid = (pipelined_tiles + per_cta - 1) / per_cta;        // <= max_ctas: all CTAs co-resident
+        kern<<<grid, NT, smem, stream>>>(*p, *b, pipelined_tiles, per_cta);
         if (int rc = ige_check_launch(name)) return rc;
     }
-    if (fallback_tiles > 0) {
-        locomotion_tile_kernel<D, NS, HUM, NW_ELEM><<<fallback_tiles, NT, 0, stream>>>(*p, *b, fallback_offset);
+    if (fallback_tiles > 0) {  // TMA mode: at most the one ragged tile, whose ids come last -> append
+        locomotion_tile_kernel<D, NS, HUM, NW_ELEM><<<fallback_tiles, NT, 0, stream>>>(
+            *p, *b, fallback_offset, pipelined_tiles == 0 ? EMIT_MASKS : EMIT_APPEND);
         if (int rc = ige_check_launch(name)) return rc;
     }
     return IGE_OK;

@@ -15,6 +15,7 @@ from __future__ import annotations
 
 import ctypes as C
 import math
+import os
 
 import numpy as np
 import torch
@@ -70,6 +71,7 @@ class VecTaskB200:
         self.rand_mode = rand_mode
         self.seed = int(seed)
         self.fuse_epilogue = fuse_epilogue
+        self.emit_reset_list = os.environ.get("IGE_NO_LIST", "0") != "1"   # debug knob
         self.obs_dict = {}
         self.allocate_buffers()
         n_rows = self.num_envs * self.num_agents
@@ -84,6 +86,7 @@ class VecTaskB200:
         self.rng_step = torch.zeros(1, dtype=torch.int64, device=dev)
         words = 2 + (self.num_envs + 2047) // 2048   # == ige_compact_scratch_words(num_envs)
         self._compact_scratch = torch.zeros(words, dtype=torch.int32, device=dev)
+        self._list_scratch = torch.zeros(_abi.reset_list_scratch_words(self.num_envs), dtype=torch.int32, device=dev)
         self.stats_rows = (torch.zeros(_abi.IGE_STATS_ROWS * _abi.IGE_STATS_STRIDE, dtype=torch.float32, device=dev)
                            if accumulate_stats else None)
         self._u0 = self._u1 = None
@@ -140,6 +143,16 @@ class VecTaskB200:
             r.u1 = _ptr(self._u1)
         return r
 
+    def _list_struct(self):
+        """Reset index list emitted by the fused kernel itself (ids ascending + device count)."""
+        l = _abi.IgeResetList()
+        if not self.emit_reset_list:
+            return l
+        l.ids = _ptr(self.reset_env_ids)
+        l.count = _ptr(self.reset_count)
+        l.scratch = _ptr(self._list_scratch)
+        return l
+
     def compact_resets(self, group=1):
         """reset_buf.nonzero() on the device: fills reset_env_ids / reset_rank / reset_count."""
         a = _abi.IgeCompactArgs()
@@ -149,7 +162,6 @@ class VecTaskB200:
         a.reset_ids = _ptr(self.reset_env_ids)
         a.reset_rank = _ptr(self.reset_rank)
         a.count = _ptr(self.reset_count)
-        a.step = _ptr(self.rng_step)
         a.scratch = _ptr(self._compact_scratch)
         _lib.call("ige_compact_resets", a, stream=self._stream())
 

@@ -35,6 +35,7 @@ class Cartpole(VecTaskB200):
         b.obs_clamped = _ptr(self.obs_clamped) if self.fuse_epilogue else None
         b.timeout_buf = _ptr(self.timeout_bool) if self.fuse_epilogue else None
         b.stats = _ptr(self.stats_rows)
+        b.list = self._list_struct()
         return p, b
 
     def draw_reset_uniforms(self, k):
@@ -52,8 +53,10 @@ class Cartpole(VecTaskB200):
     def post_physics_step(self):
         """cartpole.py:165-173 as: device-side nonzero() + ONE fused kernel."""
         stream = self._stream()
-        self.compact_resets()
         if self.rand_mode != "philox":
+            # parity mode: the uniforms are drawn on the host side in the reference's order, which needs
+            # len(env_ids) first -- the same host sync the reference has
+            self.compact_resets()
             k = int(self.reset_count.item())          # same host sync as `len(env_ids)` cartpole.py:169
             if k > 0 and self._u0 is None:
                 self._u0, self._u1 = self.draw_reset_uniforms(k)

@@ -220,8 +220,24 @@ int ige_oracle_compact_resets(const IgeCompactArgs *a) {
         if (all) a->reset_ids[cnt++] = e;
     }
     *a->count = cnt;
-    if (a->step) *a->step += 1;
     return 0;
+}
+
+/* IgeResetList: ids of the envs reset in this step == reset_buf.nonzero() at entry, ascending
+ * (group > 1: envs whose agent rows are all flagged).  Must run BEFORE the step rewrites reset_buf. */
+static void emit_reset_list(const IgeResetList *l, const int64_t *reset_buf, int num_envs, int group) {
+    if (!l->scratch) return;
+    int cnt = 0;
+    for (int e = 0; e < num_envs; ++e) {
+        int all = 1;
+        for (int k = 0; k < group; ++k) all &= (reset_buf[(size_t)e * group + k] != 0);
+        if (all) l->ids[cnt++] = e;
+    }
+    *l->count = cnt;
+}
+/* every step kernel that is given a reset list advances the Philox step word on exit */
+static void advance_step(const IgeResetList *l, const IgeResetRand *r) {
+    if (l->scratch && r->step) *r->step += 1;
 }
 
 /* ------------------------------------------------------------------------------------------
@@ -272,7 +288,9 @@ static void cartpole_range(const void *vp, const void *vb, int e0, int e1, doubl
 }
 int ige_oracle_cartpole_post_physics(const IgeCartpoleParams *p, const IgeCartpoleBuffers *b) {
     double acc[IGE_ORACLE_NACC];
+    emit_reset_list(&b->list, b->reset_buf, p->num_envs, 1);
     parallel_ranges(cartpole_range, p, b, p->num_envs, acc);
+    advance_step(&b->list, &p->rand);
     add_stat(b->stats, IGE_STAT_STEPS, p->num_envs); add_stat(b->stats, IGE_STAT_REWARD, acc[0]);
     add_stat(b->stats, IGE_STAT_DONE, acc[1]); add_stat(b->stats, IGE_STAT_TIMEOUT, acc[2]);
     add_stat(b->stats, IGE_STAT_DONE_LENGTH, acc[3]);
@@ -430,7 +448,9 @@ static void humanoid_range(const void *p, const void *b, int e0, int e1, double 
 }
 static int locomotion_post_physics(const IgeLocomotionParams *p, const IgeLocomotionBuffers *b, int humanoid) {
     double acc[IGE_ORACLE_NACC];
+    emit_reset_list(&b->list, b->reset_buf, p->num_envs, 1);
     parallel_ranges(humanoid ? humanoid_range : ant_range, p, b, p->num_envs, acc);
+    advance_step(&b->list, &p->rand);
     add_stat(b->stats, IGE_STAT_STEPS, p->num_envs); add_stat(b->stats, IGE_STAT_REWARD, acc[0]);
     add_stat(b->stats, IGE_STAT_DONE, acc[1]); add_stat(b->stats, IGE_STAT_TIMEOUT, acc[2]);
     add_stat(b->stats, IGE_STAT_DONE_LENGTH, acc[3]); add_stat(b->stats, IGE_STAT_TASK0, acc[4]);

@@ -90,7 +90,6 @@ def oracle_compact(obj, group=1):
     a.reset_ids = obj.reset_env_ids.data_ptr()
     a.reset_rank = obj.reset_rank.data_ptr()
     a.count = obj.reset_count.data_ptr()
-    a.step = obj.rng_step.data_ptr()
     oracle.call("compact_resets", a)
     return int(obj.reset_count.item())
 
