@@ -186,6 +186,98 @@ int ige_ant_post_physics(const IgeLocomotionParams *p, const IgeLocomotionBuffer
 int ige_humanoid_post_physics(const IgeLocomotionParams *p, const IgeLocomotionBuffers *b, void *stream);
 
 /* ------------------------------------------------------------------------------------------
+ * ShadowHand -- replaces the reset section of ShadowHand.pre_physics_step (tasks/shadow_hand.py:670-682:
+ * reset_target_pose :586-602, reset_idx :604-668, randomize_rotation :803-806) and
+ * ShadowHand.post_physics_step (:710-715: compute_observations :437-584 for the four observation
+ * types + the asymmetric states_buf, compute_hand_reward :746-800 incl. the global
+ * consecutive_successes update).
+ * ------------------------------------------------------------------------------------------ */
+#define IGE_HAND_OBS_OPENAI 0       /* 42  (shadow_hand.py:473-485) */
+#define IGE_HAND_OBS_FULL_NO_VEL 1  /* 77  (:499-510) */
+#define IGE_HAND_OBS_FULL 2         /* 157 (:511-526) */
+#define IGE_HAND_OBS_FULL_STATE 3   /* 211 (:557-584) */
+#define IGE_HAND_NUM_FINGERTIPS 5
+
+/* Uniforms of the four torch.rand draws of the pre-physics reset, in the reference's order:
+ *   A (kg, 4)      reset_target_pose(goal_env_ids)                    shadow_hand.py:587
+ *   B (k, 2*24+5)  reset_idx(env_ids)                                 shadow_hand.py:610
+ *   C (k, 4)       reset_target_pose(env_ids) nested in reset_idx     shadow_hand.py:613
+ *   D (k)          random_force_prob                                  shadow_hand.py:644
+ * kg = #(reset_goal_buf != 0), k = #(reset_buf != 0); rows follow nonzero() order. */
+typedef struct IgeHandResetRand {
+    int32_t mode;             /* IGE_RAND_INJECTED | IGE_RAND_PHILOX */
+    int32_t _pad;
+    uint64_t seed;
+    uint64_t *step;           /* PHILOX: step word, advanced by ige_shadow_hand_post_physics (needs list.scratch) */
+    const int32_t *goal_rank; /* INJECTED: [N] exclusive prefix of (reset_goal_buf != 0) */
+    const int32_t *env_rank;  /* INJECTED: [N] exclusive prefix of (reset_buf != 0) */
+    const float *uA, *uB, *uC, *uD;
+} IgeHandResetRand;
+
+typedef struct IgeShadowHandParams {
+    int32_t num_envs;
+    int32_t num_hand_dofs;     /* 24 */
+    int32_t num_dofs_per_env;  /* rows of dof_state / columns of prev_targets per env (>= num_hand_dofs) */
+    int32_t num_bodies;        /* rigid bodies per env in rigid_body_states / rb_forces */
+    int32_t num_actions;       /* 20 */
+    int32_t obs_type;          /* IGE_HAND_OBS_* */
+    int32_t asymmetric_obs;    /* also write the 211-wide states_buf (shadow_hand.py:470-471) */
+    int32_t ignore_z_rot;      /* object_type == "pen" doubles the success tolerance (:758-759) */
+    int32_t max_consecutive_successes;
+    int32_t fingertip_handles[IGE_HAND_NUM_FINGERTIPS];
+    float max_episode_length;
+    float dist_reward_scale, rot_reward_scale, rot_eps, action_penalty_scale;
+    float success_tolerance, reach_goal_bonus, fall_dist, fall_penalty, av_factor;
+    float vel_obs_scale, force_torque_obs_scale, clip_obs;
+    float reset_position_noise, reset_dof_pos_noise, reset_dof_vel_noise;
+    float goal_displacement[3];
+    float force_prob_range[2];
+    float dof_lower[IGE_MAX_DOF], dof_upper[IGE_MAX_DOF];
+    float dof_default_pos[IGE_MAX_DOF];   /* shadow_hand_dof_default_pos (limits delta base, :648-649) */
+    float dof_default_vel[IGE_MAX_DOF];   /* shadow_hand_dof_default_vel (:654) */
+    float dof_reset_base[IGE_MAX_DOF];    /* shadow_hand_default_dof_pos (:652; zeros in the reference) */
+    IgeHandResetRand rand;
+} IgeShadowHandParams;
+
+typedef struct IgeShadowHandBuffers {
+    /* simulator views */
+    float *dof_state;                 /* (N*num_dofs_per_env, 2) reset rows rewritten */
+    float *root_state_tensor;         /* (num_actors, 13) object / goal rows rewritten by the reset */
+    const float *rigid_body_states;   /* (N, num_bodies, 13) */
+    const float *vec_sensor_tensor;   /* (N, 30); full_state / asymmetric only */
+    const float *dof_force_tensor;    /* (N, 24); full_state / asymmetric only */
+    /* task state */
+    const float *actions;             /* (N, 20) */
+    const int64_t *hand_indices, *object_indices, *goal_object_indices; /* (N) actor rows */
+    float *goal_states;               /* (N, 13) */
+    const float *goal_init_state;     /* (N, 13) */
+    const float *object_init_state;   /* (N, 13) */
+    float *prev_targets, *cur_targets;/* (N, num_dofs_per_env) */
+    float *rb_forces;                 /* (N, num_bodies, 3) */
+    float *random_force_prob;         /* (N) */
+    float *successes;                 /* (N) */
+    float *consecutive_successes;     /* (1) */
+    float *obs_buf;                   /* (N, 42|77|157|211) */
+    float *states_buf;                /* (N, 211) when asymmetric_obs */
+    float *rew_buf;
+    int64_t *reset_buf, *reset_goal_buf, *progress_buf, *randomize_buf;
+    /* outputs for the simulator calls of the reset (optional) */
+    int64_t *actor_dirty;             /* (num_actors) 0/1: root rows to hand to set_actor_root_state_tensor_indexed
+                                         (== the sorted unique() of shadow_hand.py:634-636 once compacted) */
+    /* fused step() epilogue (optional) */
+    float *obs_clamped, *states_clamped;
+    uint8_t *timeout_buf;
+    float *stats;                     /* TASK0 = sum resets, TASK0+1 = sum successes*resets */
+    uint32_t *reduce_scratch;         /* [4] zeroed once: global reduction of compute_hand_reward */
+    IgeResetList list;                /* envs reset by ige_shadow_hand_reset (== reset_buf.nonzero()) */
+} IgeShadowHandBuffers;
+
+/* pre-physics position: resets for (reset_goal_buf != 0) and (reset_buf != 0) */
+int ige_shadow_hand_reset(const IgeShadowHandParams *p, const IgeShadowHandBuffers *b, void *stream);
+/* post-physics position: progress++, observations, reward, termination, consecutive_successes */
+int ige_shadow_hand_post_physics(const IgeShadowHandParams *p, const IgeShadowHandBuffers *b, void *stream);
+
+/* ------------------------------------------------------------------------------------------
  * Library
  * ------------------------------------------------------------------------------------------ */
 int ige_version(void);

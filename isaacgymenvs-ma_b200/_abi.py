@@ -67,9 +67,43 @@ class IgeLocomotionBuffers(C.Structure):
                 ("obs_clamped", _p), ("timeout_buf", _p), ("stats", _p), ("list", IgeResetList)]
 
 
+IGE_HAND_OBS = {"openai": 0, "full_no_vel": 1, "full": 2, "full_state": 3}
+
+
+class IgeHandResetRand(C.Structure):
+    _fields_ = [("mode", _i), ("_pad", _i), ("seed", C.c_uint64), ("step", _p), ("goal_rank", _p),
+                ("env_rank", _p), ("uA", _p), ("uB", _p), ("uC", _p), ("uD", _p)]
+
+
+class IgeShadowHandParams(C.Structure):
+    _fields_ = [("num_envs", _i), ("num_hand_dofs", _i), ("num_dofs_per_env", _i), ("num_bodies", _i),
+                ("num_actions", _i), ("obs_type", _i), ("asymmetric_obs", _i), ("ignore_z_rot", _i),
+                ("max_consecutive_successes", _i), ("fingertip_handles", _i * 5),
+                ("max_episode_length", _f), ("dist_reward_scale", _f), ("rot_reward_scale", _f), ("rot_eps", _f),
+                ("action_penalty_scale", _f), ("success_tolerance", _f), ("reach_goal_bonus", _f),
+                ("fall_dist", _f), ("fall_penalty", _f), ("av_factor", _f), ("vel_obs_scale", _f),
+                ("force_torque_obs_scale", _f), ("clip_obs", _f), ("reset_position_noise", _f),
+                ("reset_dof_pos_noise", _f), ("reset_dof_vel_noise", _f), ("goal_displacement", _f * 3),
+                ("force_prob_range", _f * 2), ("dof_lower", _f * IGE_MAX_DOF), ("dof_upper", _f * IGE_MAX_DOF),
+                ("dof_default_pos", _f * IGE_MAX_DOF), ("dof_default_vel", _f * IGE_MAX_DOF),
+                ("dof_reset_base", _f * IGE_MAX_DOF), ("rand", IgeHandResetRand)]
+
+
+class IgeShadowHandBuffers(C.Structure):
+    _fields_ = [("dof_state", _p), ("root_state_tensor", _p), ("rigid_body_states", _p),
+                ("vec_sensor_tensor", _p), ("dof_force_tensor", _p), ("actions", _p), ("hand_indices", _p),
+                ("object_indices", _p), ("goal_object_indices", _p), ("goal_states", _p),
+                ("goal_init_state", _p), ("object_init_state", _p), ("prev_targets", _p), ("cur_targets", _p),
+                ("rb_forces", _p), ("random_force_prob", _p), ("successes", _p),
+                ("consecutive_successes", _p), ("obs_buf", _p), ("states_buf", _p), ("rew_buf", _p),
+                ("reset_buf", _p), ("reset_goal_buf", _p), ("progress_buf", _p), ("randomize_buf", _p),
+                ("actor_dirty", _p), ("obs_clamped", _p), ("states_clamped", _p), ("timeout_buf", _p),
+                ("stats", _p), ("reduce_scratch", _p), ("list", IgeResetList)]
+
+
 def fill_array(carr, values):
     for i, v in enumerate(values):
-        carr[i] = float(v)
+        carr[i] = type(carr[0])(v) if isinstance(carr[0], int) else float(v)
 
 
 def reset_list_scratch_words(num_envs):

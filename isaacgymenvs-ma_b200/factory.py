@@ -11,8 +11,11 @@ _SIM_TENSORS = {
     "Cartpole": ["dof_state"],
     "Ant": ["root_states", "dof_state", "vec_sensor_tensor"],
     "Humanoid": ["root_states", "dof_state", "vec_sensor_tensor", "dof_force_tensor"],
+    "ShadowHand": ["dof_state", "root_state_tensor", "rigid_body_states", "vec_sensor_tensor", "dof_force_tensor"],
 }
-_CFGS = {"Cartpole": synthetic.CARTPOLE_CFG, "Ant": synthetic.ANT_CFG, "Humanoid": synthetic.HUMANOID_CFG}
+_CFGS = {"Cartpole": synthetic.CARTPOLE_CFG, "Ant": synthetic.ANT_CFG, "Humanoid": synthetic.HUMANOID_CFG,
+         "ShadowHand": synthetic.SHADOW_HAND_CFG}
+_SYN_NAME = {"Cartpole": "cartpole", "Ant": "ant", "Humanoid": "humanoid", "ShadowHand": "shadow_hand"}
 
 
 def task_cfg(task):
@@ -28,6 +31,10 @@ def from_state(task, st, sim_device, rl_device=None, **kw):
     dev = torch.device(sim_device)
     cfg = task_cfg(task)
     cfg["num_envs"] = int(st["progress_buf"].shape[0])
+    for k in list(st):                      # per-state config overrides travel with the state dict
+        if k.startswith("cfg_"):
+            v = st[k]
+            cfg[k[4:]] = v.item() if v.shape == () and v.dtype.kind in "iuf" else str(v)
     tensors = {k: torch.from_numpy(np.ascontiguousarray(st[k])).to(dev) for k in _SIM_TENSORS[task]}
     sim = SyntheticSim(tensors)
     obj = task_map[task](cfg, sim, dev, rl_device=rl_device, **kw)
@@ -41,7 +48,7 @@ def from_state(task, st, sim_device, rl_device=None, **kw):
 
 def make(seed, task, num_envs, sim_device, rl_device=None, reset_prob=0.02, **kw):
     """isaacgymenvs.make()-shaped entry point (isaacgymenvs/__init__.py:14-26) on synthetic state."""
-    st = synthetic.make_state(task.lower(), num_envs, seed=seed, reset_prob=reset_prob)
+    st = synthetic.make_state(_SYN_NAME[task], num_envs, seed=seed, reset_prob=reset_prob)
     kw.setdefault("seed", seed)
     return from_state(task, st, sim_device, rl_device=rl_device, **kw)
 

@@ -219,3 +219,135 @@ def make_state(task, num_envs, seed=0, reset_prob=0.02, **kw):
 
 def advance_physics(task, st, rng):
     ADVANCERS[task](st, rng)
+
+
+# ---------------------------------------------------------------------------------------------
+# ShadowHand (reference: tasks/shadow_hand.py; cfg/task/ShadowHand.yaml)
+# ---------------------------------------------------------------------------------------------
+SHADOW_HAND_CFG = dict(
+    max_episode_length=600, dist_reward_scale=-10.0, rot_reward_scale=1.0, rot_eps=0.1,
+    action_penalty_scale=-0.0002, reach_goal_bonus=250.0, fall_dist=0.24, fall_penalty=0.0,
+    success_tolerance=0.1, max_consecutive_successes=0, av_factor=0.1, vel_obs_scale=0.2,
+    force_torque_obs_scale=10.0, reset_position_noise=0.01, reset_dof_pos_noise=0.2,
+    reset_dof_vel_noise=0.0, clip_obs=5.0, clip_actions=1.0, dt=0.0166, ignore_z_rot=False,
+    use_relative_control=False, dof_speed_scale=20.0, act_moving_average=1.0,
+    force_prob_range=(0.001, 0.1), goal_displacement=(-0.2, -0.06, 0.12),
+    num_hand_dofs=24, num_actions=20, num_fingertips=5, num_bodies=28,
+    fingertip_handles=(7, 11, 15, 20, 25),
+    obs_type="full_state", asymmetric_obs=False)
+SHADOW_HAND_NUM_OBS = {"openai": 42, "full_no_vel": 77, "full": 157, "full_state": 211}
+# the 20 actuated of the 24 hand DOFs (coupled distal joints are passive in the MJCF)
+SHADOW_HAND_ACTUATED = (0, 1, 2, 3, 4, 6, 7, 8, 10, 11, 12, 14, 15, 16, 17, 19, 20, 21, 22, 23)
+
+
+def _shadow_limits():
+    r = _rng(424242)
+    lo = r.uniform(-0.8, 0.0, 24).astype(F32)
+    hi = r.uniform(0.5, 1.6, 24).astype(F32)
+    return lo, hi
+
+
+def _quat_mul_np(a, b):
+    x1, y1, z1, w1 = a[..., 0], a[..., 1], a[..., 2], a[..., 3]
+    x2, y2, z2, w2 = b[..., 0], b[..., 1], b[..., 2], b[..., 3]
+    return np.stack([w1 * x2 + x1 * w2 + y1 * z2 - z1 * y2, w1 * y2 - x1 * z2 + y1 * w2 + z1 * x2,
+                     w1 * z2 + x1 * y2 - y1 * x2 + z1 * w2, w1 * w2 - x1 * x2 - y1 * y2 - z1 * z2], -1)
+
+
+def _rand_unit_quats(rng, n):
+    q = rng.standard_normal((n, 4))
+    return q / np.linalg.norm(q, axis=-1, keepdims=True)
+
+
+def _shadow_sim_draw(st, rng, cfg):
+    """(Re)draw everything the simulator owns for one step."""
+    n, d, b = st["progress_buf"].shape[0], cfg["num_hand_dofs"], cfg["num_bodies"]
+    lo, hi = st["shadow_hand_dof_lower_limits"], st["shadow_hand_dof_upper_limits"]
+    span = (hi - lo).astype(np.float64)
+    dof = np.zeros((n, d, 2), F32)
+    dof[:, :, 0] = rng.uniform(lo - 0.05 * span, hi + 0.05 * span, (n, d))
+    dof[:, :, 1] = rng.normal(0.0, 2.0, (n, d))
+    st["dof_state"] = dof.reshape(n * d, 2)
+    root = st["root_state_tensor"].reshape(n, 3, 13)
+    goal = st["goal_states"]
+    # object near the goal: straddles fall_dist = 0.24 and, for 5 % of envs, the success tolerance
+    root[:, 1, 0:3] = goal[:, 0:3] + rng.normal(0.0, 0.1, (n, 3))
+    q = _rand_unit_quats(rng, n)
+    close = rng.random(n) < 0.05
+    ang = rng.uniform(-0.04, 0.04, n)
+    small = np.stack([np.sin(ang / 2), np.zeros(n), np.zeros(n), np.cos(ang / 2)], -1)
+    q[close] = _quat_mul_np(goal[close, 3:7].astype(np.float64), small[close])
+    root[:, 1, 3:7] = q
+    root[:, 1, 7:13] = rng.standard_normal((n, 6))
+    root[:, 0, 7:13] = 0.0
+    rb = np.zeros((n, b, 13), F32)
+    rb[:, :, 0:3] = rng.normal(0.0, 0.3, (n, b, 3))
+    rb[:, :, 3:7] = _rand_unit_quats(rng, n * b).reshape(n, b, 4)
+    rb[:, :, 7:13] = rng.standard_normal((n, b, 6))
+    st["rigid_body_states"] = rb
+    st["vec_sensor_tensor"] = rng.normal(0.0, 0.3, (n, cfg["num_fingertips"] * 6)).astype(F32)
+    st["dof_force_tensor"] = rng.normal(0.0, 0.3, (n, d)).astype(F32)
+    st["actions"] = rng.uniform(-1.0, 1.0, (n, cfg["num_actions"])).astype(F32)
+
+
+def make_shadow_hand(num_envs, seed=0, reset_prob=0.02, fall_frac=None, obs_type=None, asymmetric_obs=None,
+                     max_consecutive_successes=None, goal_reset_prob=0.05):
+    cfg = dict(SHADOW_HAND_CFG)
+    if obs_type is not None:
+        cfg["obs_type"] = obs_type
+    if asymmetric_obs is not None:
+        cfg["asymmetric_obs"] = asymmetric_obs
+    if max_consecutive_successes is not None:
+        cfg["max_consecutive_successes"] = max_consecutive_successes
+    rng = _rng(seed)
+    n, d = num_envs, cfg["num_hand_dofs"]
+    st = {"cfg_obs_type": np.array(cfg["obs_type"]), "cfg_asymmetric_obs": np.array(int(cfg["asymmetric_obs"])),
+          "cfg_max_consecutive_successes": np.array(int(cfg["max_consecutive_successes"]))}
+    lo, hi = _shadow_limits()
+    st["shadow_hand_dof_lower_limits"], st["shadow_hand_dof_upper_limits"] = lo, hi
+    st["shadow_hand_dof_default_pos"] = np.zeros(d, F32)
+    st["shadow_hand_dof_default_vel"] = np.zeros(d, F32)
+    obj_init = np.zeros((n, 13), F32)
+    obj_init[:, 0:3] = np.array([0.0, -0.39, 0.54], F32) + rng.normal(0, 0.5, (n, 3)).astype(F32)
+    obj_init[:, 6] = 1.0
+    st["object_init_state"] = obj_init
+    goal = obj_init.copy()
+    goal[:, 2] -= F32(0.04)                       # shadow_hand.py:402-404
+    st["goal_init_state"] = goal.copy()
+    goal[:, 3:7] = _rand_unit_quats(rng, n)
+    st["goal_states"] = goal
+    root = np.zeros((n, 3, 13), F32)
+    root[:, 0, 0:3] = obj_init[:, 0:3] + np.array([0.0, 0.39, -0.04], F32)
+    root[:, 0, 6] = 1.0
+    root[:, 2, 0:3] = goal[:, 0:3] + np.array(cfg["goal_displacement"], F32)
+    root[:, 2, 3:7] = goal[:, 3:7]
+    st["root_state_tensor"] = root.reshape(n * 3, 13)
+    st["hand_indices"] = (3 * np.arange(n)).astype(I64)
+    st["object_indices"] = (3 * np.arange(n) + 1).astype(I64)
+    st["goal_object_indices"] = (3 * np.arange(n) + 2).astype(I64)
+    st["fingertip_handles"] = np.array(cfg["fingertip_handles"], I64)
+    st["actuated_dof_indices"] = np.array(SHADOW_HAND_ACTUATED, I64)
+    st["progress_buf"] = _progress(rng, n, cfg["max_episode_length"])
+    st["reset_buf"] = _resets(rng, n, reset_prob)
+    st["reset_goal_buf"] = _resets(rng, n, goal_reset_prob if reset_prob < 1.0 else 1.0)
+    st["randomize_buf"] = np.zeros(n, I64)
+    st["successes"] = rng.integers(0, 6, n).astype(F32)
+    st["consecutive_successes"] = np.array([1.5], F32)
+    st["prev_targets"] = rng.uniform(lo, hi, (n, d)).astype(F32)
+    st["cur_targets"] = st["prev_targets"].copy()
+    st["rb_forces"] = rng.normal(0, 1, (n, cfg["num_bodies"], 3)).astype(F32)
+    st["random_force_prob"] = rng.uniform(0.001, 0.1, n).astype(F32)
+    _shadow_sim_draw(st, rng, cfg)
+    nobs = SHADOW_HAND_NUM_OBS[cfg["obs_type"]]
+    st["obs_buf"] = np.zeros((n, nobs), F32)
+    st["states_buf"] = np.zeros((n, 211 if cfg["asymmetric_obs"] else 0), F32)
+    st["rew_buf"] = np.zeros(n, F32)
+    return st
+
+
+def advance_shadow_hand(st, rng):
+    _shadow_sim_draw(st, rng, SHADOW_HAND_CFG)
+
+
+MAKERS["shadow_hand"] = make_shadow_hand
+ADVANCERS["shadow_hand"] = advance_shadow_hand

@@ -8,5 +8,6 @@ into the C ABI (libige_b200.so).  ``task_map`` mirrors ``isaacgym_task_map``
 from .base import SyntheticSim, VecTaskB200  # noqa: F401
 from .cartpole import Cartpole  # noqa: F401
 from .locomotion import Ant, Humanoid  # noqa: F401
+from .shadow_hand import ShadowHand  # noqa: F401
 
-task_map = {"Cartpole": Cartpole, "Ant": Ant, "Humanoid": Humanoid}
+task_map = {"Cartpole": Cartpole, "Ant": Ant, "Humanoid": Humanoid, "ShadowHand": ShadowHand}

@@ -463,3 +463,235 @@ int ige_oracle_ant_post_physics(const IgeLocomotionParams *p, const IgeLocomotio
 int ige_oracle_humanoid_post_physics(const IgeLocomotionParams *p, const IgeLocomotionBuffers *b) {
     return locomotion_post_physics(p, b, 1);
 }
+
+/* ------------------------------------------------------------------------------------------
+ * ShadowHand: tasks/shadow_hand.py
+ * ------------------------------------------------------------------------------------------ */
+static float hand_uniform(const IgeHandResetRand *r, int draw, int row_rank, int env, int cols, int j) {
+    /* draw: 0 = A (goal ids), 1 = B, 2 = C, 3 = D (env ids) */
+    if (r->mode == IGE_RAND_PHILOX) {
+        IgeResetRand q = {IGE_RAND_PHILOX, 0, r->seed, r->step, 0, 0, 0};
+        return philox_uniform(&q, (uint32_t)env, (uint32_t)draw, (uint32_t)j);
+    }
+    const float *u = draw == 0 ? r->uA : draw == 1 ? r->uB : draw == 2 ? r->uC : r->uD;
+    return u[(size_t)row_rank * cols + j];
+}
+/* torch_rand_float(-1, 1): (upper - lower) * rand + lower, torch_jit_utils.py:215-218 */
+static inline float sym_uniform(float u) { return 2.0f * u + (-1.0f); }
+
+/* randomize_rotation shadow_hand.py:803-806 with quat_from_angle_axis torch_jit_utils.py:118-123:
+ * quat_mul(aa(rand0 * pi, x), aa(rand1 * pi, y)); each aa() result goes through quat_unit(). */
+static void quat_from_angle_axis_unit(float angle, int axis, float *q) {
+    float theta = angle / 2.0f;
+    float s = sinf(theta), c = cosf(theta);
+    float v[4] = {0, 0, 0, c};
+    v[axis] = 1.0f * s; /* normalize(axis) * sin: the unit axis has norm exactly 1 */
+    float n2 = v[0] * v[0];
+    n2 = fmaf(v[1], v[1], n2); n2 = fmaf(v[2], v[2], n2); n2 = fmaf(v[3], v[3], n2);
+    float n = sqrtf(n2);
+    if (n < 1e-9f) n = 1e-9f;
+    for (int i = 0; i < 4; ++i) q[i] = v[i] / n;
+}
+static void randomize_rotation(float rand0, float rand1, float *out) {
+    const float PI_F = 3.14159265358979323846f;
+    float qa[4], qb[4];
+    quat_from_angle_axis_unit(rand0 * PI_F, 0, qa);
+    quat_from_angle_axis_unit(rand1 * PI_F, 1, qb);
+    quat_mul(qa, qb, out);
+}
+
+/* reset_target_pose shadow_hand.py:586-602 for one env */
+static void hand_reset_target(const IgeShadowHandParams *p, const IgeShadowHandBuffers *b, int e, float r0, float r1) {
+    float rot[4];
+    randomize_rotation(r0, r1, rot);
+    float *gs = b->goal_states + (size_t)e * 13;
+    const float *gi = b->goal_init_state + (size_t)e * 13;
+    float *root = b->root_state_tensor + (size_t)b->goal_object_indices[e] * 13;
+    for (int i = 0; i < 3; ++i) { gs[i] = gi[i]; root[i] = gs[i] + p->goal_displacement[i]; }
+    for (int i = 0; i < 4; ++i) { gs[3 + i] = rot[i]; root[3 + i] = rot[i]; }
+    for (int i = 7; i < 13; ++i) root[i] = 0.0f;
+    if (b->actor_dirty) b->actor_dirty[b->goal_object_indices[e]] = 1;
+    b->reset_goal_buf[e] = 0;
+}
+
+/* the reset section of pre_physics_step, shadow_hand.py:670-682 */
+int ige_oracle_shadow_hand_reset(const IgeShadowHandParams *p, const IgeShadowHandBuffers *b) {
+    const int n = p->num_envs, d = p->num_hand_dofs, dpe = p->num_dofs_per_env;
+    const IgeHandResetRand *r = &p->rand;
+    emit_reset_list(&b->list, b->reset_buf, n, 1);
+    for (int e = 0; e < n; ++e) {
+        const int goal = b->reset_goal_buf[e] != 0, env = b->reset_buf[e] != 0;
+        if (goal) { /* :675-679 reset_target_pose(goal_env_ids) */
+            const int rk = r->goal_rank ? r->goal_rank[e] : 0;
+            hand_reset_target(p, b, e, sym_uniform(hand_uniform(r, 0, rk, e, 4, 0)), sym_uniform(hand_uniform(r, 0, rk, e, 4, 1)));
+        }
+        if (!env) continue;
+        /* reset_idx :604-668 */
+        const int rk = r->env_rank ? r->env_rank[e] : 0;
+        const int cols = 2 * d + 5;
+        float rf[2 * IGE_MAX_DOF + 5];
+        for (int j = 0; j < cols; ++j) rf[j] = sym_uniform(hand_uniform(r, 1, rk, e, cols, j));
+        hand_reset_target(p, b, e, sym_uniform(hand_uniform(r, 2, rk, e, 4, 0)), sym_uniform(hand_uniform(r, 2, rk, e, 4, 1))); /* :613 */
+        for (int i = 0; i < p->num_bodies * 3; ++i) b->rb_forces[(size_t)e * p->num_bodies * 3 + i] = 0.0f; /* :616 */
+        float *obj = b->root_state_tensor + (size_t)b->object_indices[e] * 13;
+        const float *oi = b->object_init_state + (size_t)e * 13;
+        for (int i = 0; i < 13; ++i) obj[i] = oi[i];                               /* :619 */
+        obj[0] = oi[0] + p->reset_position_noise * rf[0];                          /* :620-621 */
+        obj[1] = oi[1] + p->reset_position_noise * rf[1];
+        obj[2] = oi[2] + p->reset_position_noise * rf[2];                          /* :622-623 (up axis z) */
+        float rot[4];
+        randomize_rotation(rf[3], rf[4], rot);                                     /* :625 */
+        for (int i = 0; i < 4; ++i) obj[3 + i] = rot[i];
+        for (int i = 7; i < 13; ++i) obj[i] = 0.0f;
+        if (b->actor_dirty) b->actor_dirty[b->object_indices[e]] = 1;
+        /* :644-645 */
+        float l0 = logf(p->force_prob_range[0]), l1 = logf(p->force_prob_range[1]);
+        b->random_force_prob[e] = expf((l0 - l1) * hand_uniform(r, 3, rk, e, 1, 0) + l1);
+        for (int j = 0; j < d; ++j) { /* :647-657 */
+            float delta_max = p->dof_upper[j] - p->dof_default_pos[j];
+            float delta_min = p->dof_lower[j] - p->dof_default_pos[j];
+            float rand_delta = delta_min + (delta_max - delta_min) * 0.5f * (rf[5 + j] + 1.0f);
+            float pos = p->dof_reset_base[j] + p->reset_dof_pos_noise * rand_delta;
+            float vel = p->dof_default_vel[j] + p->reset_dof_vel_noise * rf[5 + d + j];
+            b->dof_state[((size_t)e * dpe + j) * 2 + 0] = pos;
+            b->dof_state[((size_t)e * dpe + j) * 2 + 1] = vel;
+            b->prev_targets[(size_t)e * dpe + j] = pos;
+            b->cur_targets[(size_t)e * dpe + j] = pos;
+        }
+        b->progress_buf[e] = 0; b->reset_buf[e] = 0; b->successes[e] = 0.0f; /* :666-668 */
+    }
+    return 0;
+}
+
+/* observation row layouts, shadow_hand.py:473-584 */
+enum { SEG_DOF_POS, SEG_DOF_VEL, SEG_DOF_FORCE, SEG_OBJ_POSE, SEG_OBJ_POS, SEG_OBJ_LINVEL, SEG_OBJ_ANGVEL,
+       SEG_GOAL_POSE, SEG_QUAT_DIFF, SEG_FT_STATE, SEG_FT_POS, SEG_SENSORS, SEG_ACTIONS, SEG_END };
+static const int HAND_LAYOUT[4][12][2] = {
+    /* openai 42 */ {{SEG_FT_POS, 0}, {SEG_OBJ_POS, 15}, {SEG_QUAT_DIFF, 18}, {SEG_ACTIONS, 22}, {SEG_END, 42}},
+    /* full_no_vel 77 */ {{SEG_DOF_POS, 0}, {SEG_OBJ_POSE, 24}, {SEG_GOAL_POSE, 31}, {SEG_QUAT_DIFF, 38}, {SEG_FT_POS, 42},
+                          {SEG_ACTIONS, 57}, {SEG_END, 77}},
+    /* full 157 */ {{SEG_DOF_POS, 0}, {SEG_DOF_VEL, 24}, {SEG_OBJ_POSE, 48}, {SEG_OBJ_LINVEL, 55}, {SEG_OBJ_ANGVEL, 58},
+                    {SEG_GOAL_POSE, 61}, {SEG_QUAT_DIFF, 68}, {SEG_FT_STATE, 72}, {SEG_ACTIONS, 137}, {SEG_END, 157}},
+    /* full_state 211 */ {{SEG_DOF_POS, 0}, {SEG_DOF_VEL, 24}, {SEG_DOF_FORCE, 48}, {SEG_OBJ_POSE, 72}, {SEG_OBJ_LINVEL, 79},
+                          {SEG_OBJ_ANGVEL, 82}, {SEG_GOAL_POSE, 85}, {SEG_QUAT_DIFF, 92}, {SEG_FT_STATE, 96}, {SEG_SENSORS, 161},
+                          {SEG_ACTIONS, 191}, {SEG_END, 211}}};
+
+static void hand_fill_row(const IgeShadowHandParams *p, const IgeShadowHandBuffers *b, int e, int layout, float *row,
+                          const float *quat_diff) {
+    const int d = p->num_hand_dofs, dpe = p->num_dofs_per_env;
+    const float *obj = b->root_state_tensor + (size_t)b->object_indices[e] * 13;
+    const float *goal = b->goal_states + (size_t)e * 13;
+    for (int s = 0; HAND_LAYOUT[layout][s][0] != SEG_END; ++s) {
+        float *o = row + HAND_LAYOUT[layout][s][1];
+        switch (HAND_LAYOUT[layout][s][0]) {
+        case SEG_DOF_POS:
+            for (int j = 0; j < d; ++j) {
+                float lo = p->dof_lower[j], hi = p->dof_upper[j];
+                o[j] = (2.0f * b->dof_state[((size_t)e * dpe + j) * 2] - hi - lo) / (hi - lo);
+            }
+            break;
+        case SEG_DOF_VEL: for (int j = 0; j < d; ++j) o[j] = p->vel_obs_scale * b->dof_state[((size_t)e * dpe + j) * 2 + 1]; break;
+        case SEG_DOF_FORCE: for (int j = 0; j < d; ++j) o[j] = p->force_torque_obs_scale * b->dof_force_tensor[(size_t)e * d + j]; break;
+        case SEG_OBJ_POSE: for (int i = 0; i < 7; ++i) o[i] = obj[i]; break;
+        case SEG_OBJ_POS: for (int i = 0; i < 3; ++i) o[i] = obj[i]; break;
+        case SEG_OBJ_LINVEL: for (int i = 0; i < 3; ++i) o[i] = obj[7 + i]; break;
+        case SEG_OBJ_ANGVEL: for (int i = 0; i < 3; ++i) o[i] = p->vel_obs_scale * obj[10 + i]; break;
+        case SEG_GOAL_POSE: for (int i = 0; i < 7; ++i) o[i] = goal[i]; break;
+        case SEG_QUAT_DIFF: for (int i = 0; i < 4; ++i) o[i] = quat_diff[i]; break;
+        case SEG_FT_STATE:
+            for (int f = 0; f < IGE_HAND_NUM_FINGERTIPS; ++f)
+                for (int i = 0; i < 13; ++i)
+                    o[f * 13 + i] = b->rigid_body_states[((size_t)e * p->num_bodies + p->fingertip_handles[f]) * 13 + i];
+            break;
+        case SEG_FT_POS:
+            for (int f = 0; f < IGE_HAND_NUM_FINGERTIPS; ++f)
+                for (int i = 0; i < 3; ++i)
+                    o[f * 3 + i] = b->rigid_body_states[((size_t)e * p->num_bodies + p->fingertip_handles[f]) * 13 + i];
+            break;
+        case SEG_SENSORS: for (int i = 0; i < 30; ++i) o[i] = p->force_torque_obs_scale * b->vec_sensor_tensor[(size_t)e * 30 + i]; break;
+        case SEG_ACTIONS: for (int i = 0; i < p->num_actions; ++i) o[i] = b->actions[(size_t)e * p->num_actions + i]; break;
+        }
+    }
+}
+static int hand_num_obs(int layout) {
+    int s = 0;
+    while (HAND_LAYOUT[layout][s][0] != SEG_END) ++s;
+    return HAND_LAYOUT[layout][s][1];
+}
+
+/* post_physics_step shadow_hand.py:710-715 */
+int ige_oracle_shadow_hand_post_physics(const IgeShadowHandParams *p, const IgeShadowHandBuffers *b) {
+    const int n = p->num_envs, na = p->num_actions;
+    const int num_obs = hand_num_obs(p->obs_type);
+    float tol = p->success_tolerance;
+    if (p->ignore_z_rot) tol = 2.0f * tol; /* :758-759 */
+    int64_t num_resets = 0;
+    float finished = 0.0f;
+    double s_rew = 0, s_done = 0, s_to = 0, s_len = 0;
+    for (int e = 0; e < n; ++e) {
+        int64_t progress = b->progress_buf[e] + 1; /* :711 */
+        if (b->randomize_buf) b->randomize_buf[e] += 1;
+        const float *obj = b->root_state_tensor + (size_t)b->object_indices[e] * 13;
+        const float *goal = b->goal_states + (size_t)e * 13;
+        const float *act = b->actions + (size_t)e * na;
+        /* compute_observations :437-471 */
+        float conj[4], quat_diff[4];
+        quat_conjugate(goal + 3, conj);
+        quat_mul(obj + 3, conj, quat_diff);
+        float *obs = b->obs_buf + (size_t)e * num_obs;
+        hand_fill_row(p, b, e, p->obs_type, obs, quat_diff);
+        if (p->asymmetric_obs) hand_fill_row(p, b, e, IGE_HAND_OBS_FULL_STATE, b->states_buf + (size_t)e * 211, quat_diff);
+        /* compute_hand_reward :746-800 */
+        float goal_dist = norm3(obj[0] - goal[0], obj[1] - goal[1], obj[2] - goal[2]);
+        float qn = norm3(quat_diff[0], quat_diff[1], quat_diff[2]);
+        float rot_dist = 2.0f * asinf(qn > 1.0f ? 1.0f : qn);
+        float dist_rew = goal_dist * p->dist_reward_scale;
+        float rot_rew = 1.0f / (fabsf(rot_dist) + p->rot_eps) * p->rot_reward_scale;
+        float sq[IGE_MAX_DOF];
+        for (int j = 0; j < na; ++j) sq[j] = act[j] * act[j];
+        float action_penalty = row_sum(sq, na);
+        float reward = dist_rew + rot_rew + action_penalty * p->action_penalty_scale;
+        int64_t goal_resets = fabsf(rot_dist) <= tol ? 1 : b->reset_goal_buf[e];
+        float successes = b->successes[e] + (float)goal_resets;
+        if (goal_resets == 1) reward = reward + p->reach_goal_bonus;
+        if (goal_dist >= p->fall_dist) reward = reward + p->fall_penalty;
+        int64_t resets = goal_dist >= p->fall_dist ? 1 : b->reset_buf[e];
+        if (p->max_consecutive_successes > 0) {
+            if (fabsf(rot_dist) <= tol) progress = 0;
+            if (successes >= (float)p->max_consecutive_successes) resets = 1;
+        }
+        const int late = (float)progress >= p->max_episode_length - 1.0f;
+        if (late) resets = 1;
+        if (p->max_consecutive_successes > 0 && late) reward = reward + 0.5f * p->fall_penalty;
+        num_resets += resets;
+        finished += successes * (float)resets;
+        b->rew_buf[e] = reward; b->reset_buf[e] = resets; b->reset_goal_buf[e] = goal_resets;
+        b->progress_buf[e] = progress; b->successes[e] = successes;
+        /* VecTask.step epilogue vec_task.py:396-408 */
+        int timeout = late && resets != 0;
+        if (b->timeout_buf) b->timeout_buf[e] = (uint8_t)timeout;
+        if (b->obs_clamped)
+            for (int j = 0; j < num_obs; ++j) {
+                float v = obs[j];
+                v = v < -p->clip_obs ? -p->clip_obs : v; v = v > p->clip_obs ? p->clip_obs : v;
+                b->obs_clamped[(size_t)e * num_obs + j] = v;
+            }
+        if (b->states_clamped && p->asymmetric_obs)
+            for (int j = 0; j < 211; ++j) {
+                float v = b->states_buf[(size_t)e * 211 + j];
+                v = v < -p->clip_obs ? -p->clip_obs : v; v = v > p->clip_obs ? p->clip_obs : v;
+                b->states_clamped[(size_t)e * 211 + j] = v;
+            }
+        s_rew += reward; s_done += resets != 0; s_to += timeout; s_len += resets != 0 ? (double)progress : 0.0;
+    }
+    /* :795-798 */
+    if (num_resets > 0)
+        b->consecutive_successes[0] = p->av_factor * finished / (float)num_resets +
+                                      (float)(1.0 - (double)p->av_factor) * b->consecutive_successes[0];
+    add_stat(b->stats, IGE_STAT_STEPS, n); add_stat(b->stats, IGE_STAT_REWARD, s_rew);
+    add_stat(b->stats, IGE_STAT_DONE, s_done); add_stat(b->stats, IGE_STAT_TIMEOUT, s_to);
+    add_stat(b->stats, IGE_STAT_DONE_LENGTH, s_len); add_stat(b->stats, IGE_STAT_TASK0, (double)num_resets);
+    add_stat(b->stats, IGE_STAT_TASK0 + 1, finished);
+    if (b->list.scratch && p->rand.step) *p->rand.step += 1;
+    return 0;
+}

@@ -22,7 +22,8 @@ from ige_loader import load_package  # noqa: E402
 pkg = load_package()
 syn = pkg.synthetic
 
-CFGS = {"cartpole": syn.CARTPOLE_CFG, "ant": syn.ANT_CFG, "humanoid": syn.HUMANOID_CFG}
+CFGS = {"cartpole": syn.CARTPOLE_CFG, "ant": syn.ANT_CFG, "humanoid": syn.HUMANOID_CFG,
+        "shadow_hand": syn.SHADOW_HAND_CFG}
 
 # (task, num_envs, seed, reset_prob of step 0, steps)
 FIXTURES = [
@@ -32,6 +33,12 @@ FIXTURES = [
     ("ant", 64, 1234, 1.0, 2),
     ("humanoid", 96, 0, 0.05, 3),
     ("humanoid", 64, 1234, 1.0, 2),
+    ("shadow_hand", 64, 0, 0.05, 3, dict(obs_type="full_state")),
+    ("shadow_hand", 48, 1, 1.0, 2, dict(obs_type="full_state")),            # first step: everything resets
+    ("shadow_hand", 48, 2, 0.1, 2, dict(obs_type="openai", asymmetric_obs=True)),
+    ("shadow_hand", 48, 3, 0.1, 2, dict(obs_type="full_no_vel")),
+    ("shadow_hand", 48, 4, 0.1, 2, dict(obs_type="full", max_consecutive_successes=3)),
+    ("shadow_hand", 48, 5, 0.0, 2, dict(obs_type="full_state", goal_reset_prob=0.2)),   # goal-only resets
 ]
 
 
@@ -55,8 +62,12 @@ def generate(task, n, seed, reset_prob, steps, **kw):
         out, rands, calls = ref_harness.run_reference_step(task, obj, st, cfg, torch_seed=1000 + s)
         for name, v in out.items():
             blob[f"step{s}/out/{name}"] = v
-        for i, r in enumerate(rands):
-            blob[f"step{s}/rand{i}"] = r
+        if isinstance(rands, dict):
+            for name, r in rands.items():
+                blob[f"step{s}/rand{name}"] = r
+        else:
+            for i, r in enumerate(rands):
+                blob[f"step{s}/rand{i}"] = r
         for i, (cname, args) in enumerate(calls):
             blob[f"step{s}/call{i}/name"] = cname
             idx = [a for a in args if isinstance(a, np.ndarray) and a.dtype == np.int32]
@@ -66,8 +77,13 @@ def generate(task, n, seed, reset_prob, steps, **kw):
 
 
 def main():
-    for task, n, seed, p, steps in FIXTURES:
-        blob = generate(task, n, seed, p, steps)
+    only = sys.argv[1:]
+    for fx in FIXTURES:
+        task, n, seed, p, steps = fx[:5]
+        kw = fx[5] if len(fx) > 5 else {}
+        if only and task not in only:
+            continue
+        blob = generate(task, n, seed, p, steps, **kw)
         path = os.path.join(HERE, f"{task}_n{n}_s{seed}.npz")
         np.savez_compressed(path, **blob)
         print(f"wrote {path}  ({os.path.getsize(path) / 1024:.0f} KiB)")

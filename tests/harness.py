@@ -19,7 +19,7 @@ from oracle import oracle  # noqa: E402
 GOLDEN_DIR = os.path.join(ROOT, "tests", "golden")
 RTOL = 1e-5   # north_star: observations and rewards within 1e-5 relative in fp32
 
-TASK_NAME = {"cartpole": "Cartpole", "ant": "Ant", "humanoid": "Humanoid"}
+TASK_NAME = {"cartpole": "Cartpole", "ant": "Ant", "humanoid": "Humanoid", "shadow_hand": "ShadowHand"}
 ENTRY = {"cartpole": "cartpole_post_physics", "ant": "ant_post_physics", "humanoid": "humanoid_post_physics"}
 FLOAT_OUT = {
     "cartpole": ["obs_buf", "rew_buf", "dof_state"],
@@ -31,8 +31,13 @@ INT_OUT = {
     "ant": ["reset_buf", "progress_buf", "randomize_buf"],
     "humanoid": ["reset_buf", "progress_buf", "randomize_buf"],
 }
+_HAND_FLOAT = ["obs_buf", "rew_buf", "successes", "consecutive_successes", "goal_states", "root_state_tensor",
+               "dof_state", "prev_targets", "cur_targets", "rb_forces", "random_force_prob"]
+FLOAT_OUT["shadow_hand"] = _HAND_FLOAT
+INT_OUT["shadow_hand"] = ["reset_buf", "reset_goal_buf", "progress_buf", "randomize_buf"]
 BITEXACT_FLOAT = {"cartpole": ["dof_state"], "ant": ["potentials", "prev_potentials", "dof_state"],
-                  "humanoid": ["potentials", "prev_potentials", "dof_state"]}
+                  "humanoid": ["potentials", "prev_potentials", "dof_state"],
+                  "shadow_hand": ["successes", "rb_forces"]}
 
 
 def golden_files(task):
@@ -59,6 +64,9 @@ def step_outputs(blob, s):
 
 
 def step_rands(blob, s):
+    named = {k.split("/rand")[1]: blob[k] for k in blob if k.startswith(f"step{s}/rand") and k[-1] in "ABCD"}
+    if named or str(blob.get("meta_task", "")) == "shadow_hand":
+        return named
     out = []
     i = 0
     while f"step{s}/rand{i}" in blob:
@@ -94,9 +102,47 @@ def oracle_compact(obj, group=1):
     return int(obj.reset_count.item())
 
 
+def _hand_uniforms(rands, device):
+    return {k: torch.from_numpy(np.ascontiguousarray(v)).to(device) for k, v in (rands or {}).items()}
+
+
+def oracle_step_hand(obj, rands=None):
+    """ShadowHand: reset section of pre_physics_step + action targets + post_physics_step (oracle)."""
+    assert obj.device.type == "cpu"
+    k = oracle_compact(obj)
+    ids = obj.reset_env_ids[:k].clone()
+    a = pkg._abi.IgeCompactArgs()
+    a.num_rows, a.group = obj.reset_goal_buf.numel(), 1
+    a.reset_buf, a.reset_ids = obj.reset_goal_buf.data_ptr(), obj.goal_env_ids.data_ptr()
+    a.reset_rank, a.count = obj.goal_rank.data_ptr(), obj.goal_count.data_ptr()
+    oracle.call("compact_resets", a)
+    if obj.rand_mode != "philox":
+        obj.set_injected_uniforms(**_hand_uniforms(rands, "cpu"))
+    obj.actor_dirty.zero_()
+    p, b = obj.abi_structs()
+    oracle.call("shadow_hand_reset", p, b)
+    obj._u = {}
+    obj.apply_actions(obj.actions.clone())
+    p, b = obj.abi_structs()
+    oracle.call("shadow_hand_post_physics", p, b)
+    return ids
+
+
+def cuda_step_hand(obj, rands=None):
+    if obj.rand_mode != "philox":
+        obj.set_injected_uniforms(**_hand_uniforms(rands, obj.device))
+    obj.pre_physics_step(obj.actions.clone())
+    k = int(obj.reset_count.item())
+    ids = obj.reset_env_ids[:k].clone()
+    obj.post_physics_step()
+    return ids
+
+
 def oracle_step(task, obj, rands=None):
     """One post_physics_step of the CPU oracle on a mirror object whose tensors live on the CPU."""
     assert obj.device.type == "cpu"
+    if task == "shadow_hand":
+        return oracle_step_hand(obj, rands)
     k = oracle_compact(obj)
     ids = obj.reset_env_ids[:k].clone()
     if obj.rand_mode != "philox":
@@ -112,6 +158,8 @@ def oracle_step(task, obj, rands=None):
 
 def cuda_step(task, obj, rands=None):
     """One post_physics_step of the product CUDA path; returns the reset id list it emitted."""
+    if task == "shadow_hand":
+        return cuda_step_hand(obj, rands)
     if obj.rand_mode != "philox" and rands:
         obj.set_injected_uniforms(*[torch.from_numpy(np.ascontiguousarray(r)).to(obj.device) for r in rands])
     obj.post_physics_step()
@@ -163,6 +211,10 @@ def compare_outputs(task, obj, ref_out, check_epilogue=True, bitexact=()):
         assert_float_close(name, get(obj, name), ref_out[name])
     for name in bitexact:
         assert_equal(name + " (bit-exact)", get(obj, name).view(np.uint32), np.asarray(ref_out[name]).view(np.uint32))
+    if task == "shadow_hand" and obj.asymmetric_obs:
+        assert_float_close("states_buf", get(obj, "states_buf"), ref_out["states_buf"])
+        if check_epilogue and obj.fuse_epilogue and "states_clamped" in ref_out:
+            assert_float_close("states_clamped", obj.states_clamped.detach().cpu().numpy(), ref_out["states_clamped"])
     if check_epilogue and obj.fuse_epilogue and "obs_clamped" in ref_out:
         assert_float_close("obs_clamped", get(obj, "obs_clamped"), ref_out["obs_clamped"])
         assert_equal("time_outs", get(obj, "time_outs").astype(bool), np.asarray(ref_out["time_outs"]).astype(bool))
@@ -170,6 +222,10 @@ def compare_outputs(task, obj, ref_out, check_epilogue=True, bitexact=()):
 
 def snapshot(task, obj):
     out = {n: get(obj, n).copy() for n in INT_OUT[task] + FLOAT_OUT[task]}
+    if task == "shadow_hand" and obj.asymmetric_obs:
+        out["states_buf"] = get(obj, "states_buf").copy()
+        if obj.fuse_epilogue:
+            out["states_clamped"] = obj.states_clamped.detach().cpu().numpy().copy()
     if obj.fuse_epilogue:
         out["obs_clamped"] = get(obj, "obs_clamped").copy()
         out["time_outs"] = get(obj, "time_outs").copy()

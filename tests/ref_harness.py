@@ -102,7 +102,53 @@ def build_humanoid(st, cfg):
     return obj
 
 
-BUILDERS = {"cartpole": build_cartpole, "ant": build_ant, "humanoid": build_humanoid}
+def build_shadow_hand(st, cfg):
+    mod = ref_shim.ref_module("tasks.shadow_hand")
+    n = st["progress_buf"].shape[0]
+    d = cfg["num_hand_dofs"]
+    obs_type = str(st["cfg_obs_type"])
+    asym = bool(int(st["cfg_asymmetric_obs"]))
+    obj = mod.ShadowHand.__new__(mod.ShadowHand)
+    _common(obj, cfg, n, st["obs_buf"].shape[1], cfg["num_actions"], num_states=211 if asym else 0)
+    obj.obs_type, obj.asymmetric_obs = obs_type, asym
+    obj.object_type = "block"
+    obj.up_axis_idx = 2
+    obj.num_shadow_hand_dofs = d
+    obj.num_fingertips = cfg["num_fingertips"]
+    obj.dt = cfg["dt"]
+    for k in ("dist_reward_scale", "rot_reward_scale", "rot_eps", "action_penalty_scale", "reach_goal_bonus",
+              "fall_dist", "fall_penalty", "success_tolerance", "vel_obs_scale", "force_torque_obs_scale",
+              "reset_position_noise", "reset_dof_pos_noise", "reset_dof_vel_noise", "use_relative_control",
+              "act_moving_average"):
+        setattr(obj, k, cfg[k])
+    obj.shadow_hand_dof_speed_scale = cfg["dof_speed_scale"]
+    obj.max_consecutive_successes = int(st["cfg_max_consecutive_successes"])
+    obj.av_factor = torch.tensor(cfg["av_factor"], dtype=torch.float)       # shadow_hand.py:196
+    obj.force_scale = 0.0
+    obj.print_success_stat = False
+    obj.force_prob_range = torch.tensor(cfg["force_prob_range"], dtype=torch.float)
+    obj.goal_displacement_tensor = torch.tensor(cfg["goal_displacement"], dtype=torch.float)
+    for k in ("dof_state", "root_state_tensor", "vec_sensor_tensor", "dof_force_tensor", "goal_states",
+              "goal_init_state", "object_init_state", "hand_indices", "object_indices", "goal_object_indices",
+              "fingertip_handles", "actuated_dof_indices", "shadow_hand_dof_lower_limits",
+              "shadow_hand_dof_upper_limits", "shadow_hand_dof_default_pos", "shadow_hand_dof_default_vel",
+              "progress_buf", "reset_buf", "reset_goal_buf", "randomize_buf", "successes", "consecutive_successes",
+              "prev_targets", "cur_targets", "rb_forces", "random_force_prob", "obs_buf", "states_buf", "rew_buf"):
+        setattr(obj, k, _t(st[k]))
+    obj.rigid_body_states = _t(st["rigid_body_states"])                      # (N, B, 13) view, shadow_hand.py:173
+    obj.shadow_hand_default_dof_pos = torch.zeros(d)                         # shadow_hand.py:166
+    obj.shadow_hand_dof_state = obj.dof_state.view(n, -1, 2)[:, :d]
+    obj.shadow_hand_dof_pos = obj.shadow_hand_dof_state[..., 0]
+    obj.shadow_hand_dof_vel = obj.shadow_hand_dof_state[..., 1]
+    obj.x_unit_tensor = torch.tensor([1.0, 0, 0]).repeat((n, 1))
+    obj.y_unit_tensor = torch.tensor([0, 1.0, 0]).repeat((n, 1))
+    obj.z_unit_tensor = torch.tensor([0, 0, 1.0]).repeat((n, 1))
+    obj.actions = _t(st["actions"])
+    return obj
+
+
+BUILDERS = {"cartpole": build_cartpole, "ant": build_ant, "humanoid": build_humanoid,
+            "shadow_hand": build_shadow_hand}
 
 # buffers the path mutates / produces, per task (captured after every step)
 OUTPUTS = {
@@ -112,12 +158,19 @@ OUTPUTS = {
     "humanoid": ["obs_buf", "rew_buf", "reset_buf", "progress_buf", "randomize_buf", "dof_state",
                  "potentials", "prev_potentials", "up_vec", "heading_vec"],
 }
+OUTPUTS["shadow_hand"] = ["obs_buf", "states_buf", "rew_buf", "reset_buf", "reset_goal_buf", "progress_buf",
+                          "randomize_buf", "successes", "consecutive_successes", "goal_states", "root_state_tensor",
+                          "dof_state", "prev_targets", "cur_targets", "rb_forces", "random_force_prob"]
 # sim-owned tensors refreshed by the synthetic "physics" before every step
 SIM_INPUTS = {
     "cartpole": ["dof_state"],
     "ant": ["root_states", "dof_state", "vec_sensor_tensor", "actions"],
     "humanoid": ["root_states", "dof_state", "vec_sensor_tensor", "dof_force_tensor", "actions"],
 }
+
+
+SIM_INPUTS["shadow_hand"] = ["dof_state", "root_state_tensor", "rigid_body_states", "vec_sensor_tensor",
+                             "dof_force_tensor", "actions"]
 
 
 def reset_rand_shapes(task, k, cfg):
@@ -129,6 +182,18 @@ def reset_rand_shapes(task, k, cfg):
     raise KeyError(task)
 
 
+def shadow_hand_rand_shapes(k_goal, k_env, cfg):
+    """pre_physics_step draw order (shadow_hand.py:670-682): reset_target_pose(goal ids) -> (kg, 4);
+    reset_idx -> (k, 2*24+5), its nested reset_target_pose(env ids) -> (k, 4), force prob -> (k,)."""
+    shapes = []
+    if k_goal > 0:
+        shapes.append(("A", (k_goal, 4)))
+    if k_env > 0:
+        d = cfg["num_hand_dofs"]
+        shapes += [("B", (k_env, 2 * d + 5)), ("C", (k_env, 4)), ("D", (k_env,))]
+    return shapes
+
+
 def run_reference_step(task, obj, st, cfg, torch_seed):
     """Copy the sim-owned tensors of ``st`` into the reference object, run one reference
     ``VecTask.step`` and return (outputs dict, reset-rand list, recorded sim calls)."""
@@ -138,6 +203,7 @@ def run_reference_step(task, obj, st, cfg, torch_seed):
             continue
         getattr(obj, k).copy_(_t(st[k]))
     reset_ids = obj.reset_buf.nonzero(as_tuple=False).flatten().clone()
+    goal_ids = obj.reset_goal_buf.nonzero(as_tuple=False).flatten().clone() if task == "shadow_hand" else None
     if task == "cartpole":
         actions = torch.zeros(n, 1)
     else:
@@ -148,13 +214,21 @@ def run_reference_step(task, obj, st, cfg, torch_seed):
     # regenerate the uniforms reset_idx consumed (same seed, same call shapes, same order)
     k = int(reset_ids.numel())
     rands = []
-    if k > 0:
+    if task == "shadow_hand":
+        torch.manual_seed(torch_seed)
+        rands = {name: torch.rand(*shape).numpy() for name, shape in
+                 shadow_hand_rand_shapes(int(goal_ids.numel()), k, cfg)}
+    elif k > 0:
         torch.manual_seed(torch_seed)
         rands = [torch.rand(*s).numpy() for s in reset_rand_shapes(task, k, cfg)]
     out = {name: getattr(obj, name).detach().clone().numpy() for name in OUTPUTS[task]}
     out["obs_clamped"] = obs_dict["obs"].detach().clone().numpy()
     out["time_outs"] = extras["time_outs"].detach().clone().numpy()
     out["reset_env_ids"] = reset_ids.to(torch.int32).numpy()
+    if goal_ids is not None:
+        out["goal_env_ids"] = goal_ids.to(torch.int32).numpy()
+    if "states" in obs_dict:
+        out["states_clamped"] = obs_dict["states"].detach().clone().numpy()
     calls = [(name, [a.numpy() if isinstance(a, torch.Tensor) else a for a in args])
              for name, args in obj.gym.calls]
     return out, rands, calls

@@ -17,19 +17,21 @@ def _run_fixture(task, path):
         ids = H.oracle_step(task, obj, H.step_rands(blob, s))
         ref = H.step_outputs(blob, s)
         H.assert_equal("reset_env_ids", ids.numpy(), ref["reset_env_ids"])
-        for cname, idx in H.step_call_indices(blob, s):
-            H.assert_equal(f"{cname} indices", ids.numpy(), idx)
+        if task != "shadow_hand":   # (the hand's sim-call lists are actor ids: tests/test_shadow_hand.py)
+            for cname, idx in H.step_call_indices(blob, s):
+                H.assert_equal(f"{cname} indices", ids.numpy(), idx)
         H.compare_outputs(task, obj, ref, bitexact=H.BITEXACT_FLOAT[task])
         for name in H.FLOAT_OUT[task]:
             worst[name] = min(worst.get(name, 1.0), H.bitexact_fraction(H.get(obj, name), ref[name]))
     return worst
 
 
-@pytest.mark.parametrize("task", ["cartpole", "ant", "humanoid"])
+@pytest.mark.parametrize("task", ["cartpole", "ant", "humanoid", "shadow_hand"])
 def test_oracle_matches_reference_golden(task):
     files = H.golden_files(task)
     assert files, f"no golden fixtures for {task}"
     for path in files:
         worst = _run_fixture(task, path)
         # the restatement is op-for-op: everything but libm-vs-sleef transcendentals is bit-exact
-        assert worst["rew_buf"] > 0.9, worst
+        # (ShadowHand's reward goes through asin(): libm and torch's vectorised asin differ in the last ulp)
+        assert worst["rew_buf"] > (0.5 if task == "shadow_hand" else 0.9), worst
