@@ -16,6 +16,8 @@ _SIGS = {
     "ige_cartpole_post_physics": (_abi.IgeCartpoleParams, _abi.IgeCartpoleBuffers),
     "ige_ant_post_physics": (_abi.IgeLocomotionParams, _abi.IgeLocomotionBuffers),
     "ige_humanoid_post_physics": (_abi.IgeLocomotionParams, _abi.IgeLocomotionBuffers),
+    "ige_shadow_hand_reset": (_abi.IgeShadowHandParams, _abi.IgeShadowHandBuffers),
+    "ige_shadow_hand_post_physics": (_abi.IgeShadowHandParams, _abi.IgeShadowHandBuffers),
 }
 
 

@@ -742,6 +742,7 @@ int launch(const IgeLocomotionParams *p, const IgeLocomotionBuffers *b, cudaStre
 }  // namespace
 
 extern "C" void ige_set_use_tma(int on) { g_use_tma = on ? 1 : 0; }
+extern "C" int ige_use_tma() { return use_tma(); }
 
 extern "C" int ige_ant_post_physics(const IgeLocomotionParams *p, const IgeLocomotionBuffers *b, void *stream) {
     if (int rc = check(p, b, 8, 24, false)) return rc;

@@ -1,0 +1,445 @@
+// shadow_hand.cu -- fused ShadowHand reset (pre-physics position) and post_physics_step for sm_100a.
+//
+// Replaces (reference, isaacgymenvs/tasks/shadow_hand.py):
+//   reset section of pre_physics_step :670-682  (reset_target_pose :586-602, reset_idx :604-668,
+//                                                randomize_rotation :803-806)
+//   post_physics_step :710-715                   (compute_observations :437-584 -- four observation
+//                                                types + asymmetric states_buf --, compute_hand_reward
+//                                                :746-800 incl. the global consecutive_successes update)
+//   + the VecTask.step epilogue base/vec_task.py:396-408 when requested.
+//
+// Post-physics kernel (HBM-bound, 1732 B/env for full_state): a CTA owns a tile of 32 consecutive
+// envs.  Every observation column is a function of ONE input element, so the tile's (32 x num_obs)
+// rows are assembled in shared memory by element-parallel loops that read the contiguous input
+// spans (dof_state, dof_force, sensors, actions) with fully coalesced loads, gather the 5 fingertip
+// rows per env (52-B segments) and are written back with one TMA bulk store (rows are 844 B: only a
+// tile of >= 4 envs is 16-B aligned, which is exactly why the row-major tile goes through shared
+// memory).  Warp 0 (lane == env) does the per-env object/goal quaternion math, the reward and the
+// flags, and feeds the two global sums of compute_hand_reward into a last-CTA reduction.
+#include "ige_common.cuh"
+
+namespace {
+
+constexpr int TE = 32;
+constexpr int NT = 256;
+constexpr int MAX_OBS = 211;
+constexpr float kPiF = 3.14159265358979323846f;
+
+enum Seg { SEG_DOF_POS, SEG_DOF_VEL, SEG_DOF_FORCE, SEG_OBJ_POSE, SEG_OBJ_POS, SEG_OBJ_LINVEL, SEG_OBJ_ANGVEL,
+           SEG_GOAL_POSE, SEG_QUAT_DIFF, SEG_FT_STATE, SEG_FT_POS, SEG_SENSORS, SEG_ACTIONS, SEG_END };
+struct SegEntry { int kind, off; };
+// shadow_hand.py:473-584
+__constant__ SegEntry kLayout[4][12] = {
+    {{SEG_FT_POS, 0}, {SEG_OBJ_POS, 15}, {SEG_QUAT_DIFF, 18}, {SEG_ACTIONS, 22}, {SEG_END, 42}},
+    {{SEG_DOF_POS, 0}, {SEG_OBJ_POSE, 24}, {SEG_GOAL_POSE, 31}, {SEG_QUAT_DIFF, 38}, {SEG_FT_POS, 42}, {SEG_ACTIONS, 57},
+     {SEG_END, 77}},
+    {{SEG_DOF_POS, 0}, {SEG_DOF_VEL, 24}, {SEG_OBJ_POSE, 48}, {SEG_OBJ_LINVEL, 55}, {SEG_OBJ_ANGVEL, 58},
+     {SEG_GOAL_POSE, 61}, {SEG_QUAT_DIFF, 68}, {SEG_FT_STATE, 72}, {SEG_ACTIONS, 137}, {SEG_END, 157}},
+    {{SEG_DOF_POS, 0}, {SEG_DOF_VEL, 24}, {SEG_DOF_FORCE, 48}, {SEG_OBJ_POSE, 72}, {SEG_OBJ_LINVEL, 79},
+     {SEG_OBJ_ANGVEL, 82}, {SEG_GOAL_POSE, 85}, {SEG_QUAT_DIFF, 92}, {SEG_FT_STATE, 96}, {SEG_SENSORS, 161},
+     {SEG_ACTIONS, 191}, {SEG_END, 211}}};
+__host__ __device__ inline int hand_num_obs(int type) { return type == 0 ? 42 : type == 1 ? 77 : type == 2 ? 157 : 211; }
+
+__device__ __forceinline__ float clampf(float x, float c) { return x < -c ? -c : (x > c ? c : x); }
+
+// ---------------------------------------------------------------------------------------------
+// reset (pre-physics): one thread per env; only flagged envs do work
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ float hand_uniform(const IgeHandResetRand &r, uint64_t step, int draw, int rank, int env,
+                                              int cols, int j) {
+    if (r.mode == IGE_RAND_PHILOX) {
+        uint32_t c[4] = {(uint32_t)env, ((uint32_t)draw << 16) | ((uint32_t)j >> 2), (uint32_t)step, (uint32_t)(step >> 32)};
+        ige::philox4x32_10(c, (uint32_t)r.seed, (uint32_t)(r.seed >> 32));
+        return (float)(c[j & 3] >> 8) * (1.0f / 16777216.0f);
+    }
+    const float *u = draw == 0 ? r.uA : draw == 1 ? r.uB : draw == 2 ? r.uC : r.uD;
+    return __ldg(u + (size_t)rank * cols + j);
+}
+__device__ __forceinline__ float sym_uniform(float u) { return 2.0f * u + (-1.0f); }  // torch_rand_float(-1, 1)
+
+// quat_from_angle_axis (torch_jit_utils.py:118-123) for a unit coordinate axis, incl. quat_unit()
+__device__ __forceinline__ void quat_from_angle_axis_unit(float angle, int axis, float *q) {
+    const float theta = angle / 2.0f;
+    const float s = sinf(theta), c = cosf(theta);
+    float v[4] = {0.f, 0.f, 0.f, c};
+    v[axis] = 1.0f * s;
+    float n2 = __fmul_rn(v[0], v[0]);
+    n2 = __fmaf_rn(v[1], v[1], n2); n2 = __fmaf_rn(v[2], v[2], n2); n2 = __fmaf_rn(v[3], v[3], n2);
+    float n = __fsqrt_rn(n2);
+    n = n < 1e-9f ? 1e-9f : n;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) q[i] = v[i] / n;
+}
+__device__ __forceinline__ void randomize_rotation(float rand0, float rand1, float *out) {  // shadow_hand.py:803-806
+    float qa[4], qb[4];
+    quat_from_angle_axis_unit(rand0 * kPiF, 0, qa);
+    quat_from_angle_axis_unit(rand1 * kPiF, 1, qb);
+    ige::quat_mul(qa, qb, out);
+}
+__device__ __forceinline__ void reset_target(const IgeShadowHandParams &p, const IgeShadowHandBuffers &b, int e, float r0,
+                                             float r1) {  // reset_target_pose shadow_hand.py:586-602
+    float rot[4];
+    randomize_rotation(r0, r1, rot);
+    float *gs = b.goal_states + (size_t)e * 13;
+    const float *gi = b.goal_init_state + (size_t)e * 13;
+    const long long gidx = b.goal_object_indices[e];
+    float *root = b.root_state_tensor + (size_t)gidx * 13;
+#pragma unroll
+    for (int i = 0; i < 3; ++i) { const float v = gi[i]; gs[i] = v; root[i] = v + p.goal_displacement[i]; }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { gs[3 + i] = rot[i]; root[3 + i] = rot[i]; }
+#pragma unroll
+    for (int i = 7; i < 13; ++i) root[i] = 0.0f;
+    if (b.actor_dirty) b.actor_dirty[gidx] = 1;
+    b.reset_goal_buf[e] = 0;
+}
+
+__global__ void __launch_bounds__(128) shadow_hand_reset_kernel(const __grid_constant__ IgeShadowHandParams p,
+                                                                const __grid_constant__ IgeShadowHandBuffers b) {
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    const IgeHandResetRand &r = p.rand;
+    const uint64_t step = (r.mode == IGE_RAND_PHILOX && r.step) ? *reinterpret_cast<const volatile uint64_t *>(r.step) : 0ull;
+    bool env = false;
+    if (e < p.num_envs) {
+        const bool goal = b.reset_goal_buf[e] != 0;
+        env = b.reset_buf[e] != 0;
+        if (goal) {  // :675-679
+            const int rk = r.goal_rank ? __ldg(r.goal_rank + e) : 0;
+            reset_target(p, b, e, sym_uniform(hand_uniform(r, step, 0, rk, e, 4, 0)),
+                         sym_uniform(hand_uniform(r, step, 0, rk, e, 4, 1)));
+        }
+        if (env) {  // reset_idx :604-668
+            const int d = p.num_hand_dofs, dpe = p.num_dofs_per_env, cols = 2 * d + 5;
+            const int rk = r.env_rank ? __ldg(r.env_rank + e) : 0;
+            float rf[5];
+#pragma unroll
+            for (int j = 0; j < 5; ++j) rf[j] = sym_uniform(hand_uniform(r, step, 1, rk, e, cols, j));
+            reset_target(p, b, e, sym_uniform(hand_uniform(r, step, 2, rk, e, 4, 0)),
+                         sym_uniform(hand_uniform(r, step, 2, rk, e, 4, 1)));  // :613
+            float *rbf = b.rb_forces + (size_t)e * p.num_bodies * 3;
+            for (int i = 0; i < p.num_bodies * 3; ++i) rbf[i] = 0.0f;  // :616
+            const long long oidx = b.object_indices[e];
+            float *obj = b.root_state_tensor + (size_t)oidx * 13;
+            const float *oi = b.object_init_state + (size_t)e * 13;
+            obj[0] = oi[0] + p.reset_position_noise * rf[0];  // :619-623
+            obj[1] = oi[1] + p.reset_position_noise * rf[1];
+            obj[2] = oi[2] + p.reset_position_noise * rf[2];
+            float rot[4];
+            randomize_rotation(rf[3], rf[4], rot);  // :625
+#pragma unroll
+            for (int i = 0; i < 4; ++i) obj[3 + i] = rot[i];
+#pragma unroll
+            for (int i = 7; i < 13; ++i) obj[i] = 0.0f;
+            if (b.actor_dirty) b.actor_dirty[oidx] = 1;
+            const float l0 = logf(p.force_prob_range[0]), l1 = logf(p.force_prob_range[1]);  // :644-645
+            b.random_force_prob[e] = expf((l0 - l1) * hand_uniform(r, step, 3, rk, e, 1, 0) + l1);
+            for (int j = 0; j < d; ++j) {  // :647-657
+                const float delta_max = p.dof_upper[j] - p.dof_default_pos[j];
+                const float delta_min = p.dof_lower[j] - p.dof_default_pos[j];
+                const float rj = sym_uniform(hand_uniform(r, step, 1, rk, e, cols, 5 + j));
+                const float rv = sym_uniform(hand_uniform(r, step, 1, rk, e, cols, 5 + d + j));
+                const float rand_delta = delta_min + (delta_max - delta_min) * 0.5f * (rj + 1.0f);
+                const float pos = p.dof_reset_base[j] + p.reset_dof_pos_noise * rand_delta;
+                const float vel = p.dof_default_vel[j] + p.reset_dof_vel_noise * rv;
+                reinterpret_cast<float2 *>(b.dof_state)[(size_t)e * dpe + j] = make_float2(pos, vel);
+                b.prev_targets[(size_t)e * dpe + j] = pos;
+                b.cur_targets[(size_t)e * dpe + j] = pos;
+            }
+            b.progress_buf[e] = 0;  // :666-668
+            b.reset_buf[e] = 0;
+            b.successes[e] = 0.0f;
+        }
+    }
+    if (b.list.scratch) {  // reset list == reset_buf.nonzero() at entry
+        const uint32_t mask = __ballot_sync(0xffffffffu, env);
+        if ((threadIdx.x & 31) == 0 && e < p.num_envs) ige::publish_tile_mask(b.list, e >> 5, mask);
+        ige::finish_reset_list(b.list, p.num_envs, nullptr, (threadIdx.x & 31) == 0);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// post-physics
+// ---------------------------------------------------------------------------------------------
+// Fill the element-parallel segments of one (TE x num_obs) tile held in shared memory.
+__device__ __forceinline__ void fill_tile(const IgeShadowHandParams &p, const IgeShadowHandBuffers &b, int layout, int nobs,
+                                          float *tile, int e0, int ne) {
+    const int d = p.num_hand_dofs, dpe = p.num_dofs_per_env, na = p.num_actions, tid = threadIdx.x;
+    for (int s = 0; kLayout[layout][s].kind != SEG_END; ++s) {
+        const int kind = kLayout[layout][s].kind, off = kLayout[layout][s].off;
+        if (kind == SEG_DOF_POS || kind == SEG_DOF_VEL) {
+            const bool pos = kind == SEG_DOF_POS;
+            for (int i = tid; i < ne * d; i += NT) {
+                const int le = i / d, j = i - le * d;
+                const float2 pv = __ldg(reinterpret_cast<const float2 *>(b.dof_state) + (size_t)(e0 + le) * dpe + j);
+                const float lo = p.dof_lower[j], hi = p.dof_upper[j];
+                tile[le * nobs + off + j] = pos ? (2.0f * pv.x - hi - lo) / (hi - lo)   // unscale :499-500
+                                                : p.vel_obs_scale * pv.y;                // :514
+            }
+        } else if (kind == SEG_DOF_FORCE) {
+            for (int i = tid; i < ne * d; i += NT) {
+                const int le = i / d, j = i - le * d;
+                tile[le * nobs + off + j] = p.force_torque_obs_scale * __ldg(b.dof_force_tensor + (size_t)e0 * d + i);
+            }
+        } else if (kind == SEG_SENSORS) {
+            for (int i = tid; i < ne * 30; i += NT) {
+                const int le = i / 30, j = i - le * 30;
+                tile[le * nobs + off + j] = p.force_torque_obs_scale * __ldg(b.vec_sensor_tensor + (size_t)e0 * 30 + i);
+            }
+        } else if (kind == SEG_ACTIONS) {
+            for (int i = tid; i < ne * na; i += NT) {
+                const int le = i / na, j = i - le * na;
+                tile[le * nobs + off + j] = __ldg(b.actions + (size_t)e0 * na + i);
+            }
+        } else if (kind == SEG_FT_STATE) {
+            for (int i = tid; i < ne * 65; i += NT) {
+                const int le = i / 65, j = i - le * 65, f = j / 13, k = j - f * 13;
+                tile[le * nobs + off + j] =
+                    __ldg(b.rigid_body_states + ((size_t)(e0 + le) * p.num_bodies + p.fingertip_handles[f]) * 13 + k);
+            }
+        } else if (kind == SEG_FT_POS) {
+            for (int i = tid; i < ne * 15; i += NT) {
+                const int le = i / 15, j = i - le * 15, f = j / 3, k = j - f * 3;
+                tile[le * nobs + off + j] =
+                    __ldg(b.rigid_body_states + ((size_t)(e0 + le) * p.num_bodies + p.fingertip_handles[f]) * 13 + k);
+            }
+        }
+    }
+}
+// The per-env segments (object / goal rows, quat diff), by the thread that owns env `le`.
+__device__ __forceinline__ void fill_env_segments(const IgeShadowHandParams &p, int layout, int nobs, float *row,
+                                                  const float *obj, const float *goal, const float *qd) {
+    for (int s = 0; kLayout[layout][s].kind != SEG_END; ++s) {
+        float *o = row + kLayout[layout][s].off;
+        switch (kLayout[layout][s].kind) {
+        case SEG_OBJ_POSE:
+#pragma unroll
+            for (int i = 0; i < 7; ++i) o[i] = obj[i];
+            break;
+        case SEG_OBJ_POS: o[0] = obj[0]; o[1] = obj[1]; o[2] = obj[2]; break;
+        case SEG_OBJ_LINVEL: o[0] = obj[7]; o[1] = obj[8]; o[2] = obj[9]; break;
+        case SEG_OBJ_ANGVEL:
+            o[0] = p.vel_obs_scale * obj[10]; o[1] = p.vel_obs_scale * obj[11]; o[2] = p.vel_obs_scale * obj[12];
+            break;
+        case SEG_GOAL_POSE:
+#pragma unroll
+            for (int i = 0; i < 7; ++i) o[i] = goal[i];
+            break;
+        case SEG_QUAT_DIFF: o[0] = qd[0]; o[1] = qd[1]; o[2] = qd[2]; o[3] = qd[3]; break;
+        default: break;
+        }
+    }
+}
+
+__device__ __forceinline__ void store_tile(float *dst, float *dst_clamped, const float *tile, int count, float clip,
+                                           bool bulk) {
+    // `count` floats, contiguous in global.  bulk: one TMA store by thread 0 (after fence + barrier).
+    if (bulk) {
+        if (threadIdx.x == 0) {
+            ige::bulk_s2g(dst, tile, (uint32_t)count * 4);
+            ige::bulk_commit();
+        }
+    } else {
+        for (int i = threadIdx.x; i < count; i += NT) dst[i] = tile[i];
+    }
+    if (dst_clamped)  // vec_task.py:404 (clip_obs is finite for this task: a real second pass)
+        for (int i = threadIdx.x; i < count; i += NT) dst_clamped[i] = clampf(tile[i], clip);
+}
+
+__global__ void __launch_bounds__(NT) shadow_hand_post_physics_kernel(const __grid_constant__ IgeShadowHandParams p,
+                                                                      const __grid_constant__ IgeShadowHandBuffers b,
+                                                                      const int use_tma) {
+    extern __shared__ __align__(128) float smem[];
+    const int nobs = hand_num_obs(p.obs_type);
+    float *obs_tile = smem;                                             // TE * nobs
+    float *st_tile = smem + ((TE * nobs + 31) / 32) * 32;               // TE * 211 when asymmetric
+    __shared__ int s_last;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int e0 = blockIdx.x * TE;
+    const int ne = min(TE, p.num_envs - e0);
+    const bool bulk = use_tma && (ne % 4 == 0);
+
+    fill_tile(p, b, p.obs_type, nobs, obs_tile, e0, ne);
+    if (p.asymmetric_obs) fill_tile(p, b, IGE_HAND_OBS_FULL_STATE, MAX_OBS, st_tile, e0, ne);
+
+    // ---- warp 0: per-env object / goal math, reward, flags (compute_hand_reward :746-800) ----
+    int my_resets = 0;
+    float my_finished = 0.f, st_rew = 0.f, st_len = 0.f;
+    int st_to = 0;
+    if (warp == 0) {
+        if (lane < ne) {
+            const int e = e0 + lane;
+            float obj[13], goal[7];
+            const float *op = b.root_state_tensor + (size_t)b.object_indices[e] * 13;
+            const float *gp = b.goal_states + (size_t)e * 13;
+#pragma unroll
+            for (int i = 0; i < 13; ++i) obj[i] = op[i];
+#pragma unroll
+            for (int i = 0; i < 7; ++i) goal[i] = gp[i];
+            float conj[4], qd[4];
+            ige::quat_conjugate(goal + 3, conj);
+            ige::quat_mul(obj + 3, conj, qd);
+            fill_env_segments(p, p.obs_type, nobs, obs_tile + lane * nobs, obj, goal, qd);
+            if (p.asymmetric_obs) fill_env_segments(p, IGE_HAND_OBS_FULL_STATE, MAX_OBS, st_tile + lane * MAX_OBS, obj, goal, qd);
+
+            long long progress = b.progress_buf[e] + 1;  // :711
+            if (b.randomize_buf) b.randomize_buf[e] += 1;
+            const float tol = p.ignore_z_rot ? 2.0f * p.success_tolerance : p.success_tolerance;  // :758-759
+            const float goal_dist = ige::norm3(obj[0] - goal[0], obj[1] - goal[1], obj[2] - goal[2]);
+            const float qn = ige::norm3(qd[0], qd[1], qd[2]);
+            const float rot_dist = 2.0f * asinf(qn > 1.0f ? 1.0f : qn);
+            const float dist_rew = goal_dist * p.dist_reward_scale;
+            const float rot_rew = 1.0f / (fabsf(rot_dist) + p.rot_eps) * p.rot_reward_scale;
+            // torch.sum(actions ** 2, dim=-1) for 20 columns: 8 vector lanes over 16, tail 4, then lanes
+            const float *act = b.actions + (size_t)e * p.num_actions;
+            float lanes8[8];
+#pragma unroll
+            for (int l = 0; l < 8; ++l) lanes8[l] = 0.f;
+            const int na = p.num_actions, nv = na / 8;
+            for (int i = 0; i < nv; ++i)
+#pragma unroll
+                for (int l = 0; l < 8; ++l) { const float a = __ldg(act + i * 8 + l); lanes8[l] += a * a; }
+            float action_penalty = 0.f;
+            for (int k = nv * 8; k < na; ++k) { const float a = __ldg(act + k); action_penalty += a * a; }
+            if (nv > 0)
+#pragma unroll
+                for (int l = 0; l < 8; ++l) action_penalty += lanes8[l];
+            float reward = dist_rew + rot_rew + action_penalty * p.action_penalty_scale;
+            const bool hit = fabsf(rot_dist) <= tol;
+            const long long goal_resets = hit ? 1 : b.reset_goal_buf[e];
+            const float successes = b.successes[e] + (float)goal_resets;
+            if (goal_resets == 1) reward = reward + p.reach_goal_bonus;
+            const bool fell = goal_dist >= p.fall_dist;
+            if (fell) reward = reward + p.fall_penalty;
+            long long resets = fell ? 1 : b.reset_buf[e];
+            if (p.max_consecutive_successes > 0) {
+                if (hit) progress = 0;
+                if (successes >= (float)p.max_consecutive_successes) resets = 1;
+            }
+            const bool late = (float)progress >= p.max_episode_length - 1.0f;
+            if (late) resets = 1;
+            if (p.max_consecutive_successes > 0 && late) reward = reward + 0.5f * p.fall_penalty;
+            b.rew_buf[e] = reward;
+            b.reset_buf[e] = resets;
+            b.reset_goal_buf[e] = goal_resets;
+            b.progress_buf[e] = progress;
+            b.successes[e] = successes;
+            const bool timeout = late && resets != 0;  // vec_task.py:396
+            if (b.timeout_buf) b.timeout_buf[e] = timeout ? 1 : 0;
+            my_resets = (int)resets;
+            my_finished = successes * (float)resets;
+            st_rew = reward; st_to = timeout; st_len = resets != 0 ? (float)progress : 0.f;
+        }
+        // global sums of compute_hand_reward (:795-796): exact (integer-valued terms)
+        const int tile_resets = __reduce_add_sync(0xffffffffu, my_resets);
+        const float tile_finished = ige::warp_sum(my_finished);
+        if (lane == 0) {
+            atomicAdd(b.reduce_scratch + 0, (unsigned)tile_resets);
+            atomicAdd(reinterpret_cast<float *>(b.reduce_scratch) + 2, tile_finished);
+        }
+        if (b.stats) {
+            const float v[7] = {lane < ne ? 1.f : 0.f, st_rew, (float)(my_resets != 0), (float)st_to, st_len,
+                                (float)my_resets, my_finished};
+            const int slot[7] = {IGE_STAT_STEPS, IGE_STAT_REWARD, IGE_STAT_DONE, IGE_STAT_TIMEOUT, IGE_STAT_DONE_LENGTH,
+                                 IGE_STAT_TASK0, IGE_STAT_TASK0 + 1};
+            ige::warp_stats_add<7>(b.stats, v, slot);
+        }
+    }
+    if (bulk) ige::fence_proxy_async();
+    __syncthreads();
+
+    // ---- tile stores ----
+    store_tile(b.obs_buf + (size_t)e0 * nobs, b.obs_clamped ? b.obs_clamped + (size_t)e0 * nobs : nullptr, obs_tile,
+               ne * nobs, p.clip_obs, bulk);
+    if (p.asymmetric_obs)
+        store_tile(b.states_buf + (size_t)e0 * MAX_OBS, b.states_clamped ? b.states_clamped + (size_t)e0 * MAX_OBS : nullptr,
+                   st_tile, ne * MAX_OBS, p.clip_obs, bulk);
+    if (bulk && tid == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+
+    // ---- last CTA: consecutive_successes (:798), re-arm the scratch, advance the Philox step ----
+    __syncthreads();
+    if (tid == 0) {
+        __threadfence();
+        s_last = atomicAdd(b.reduce_scratch + 1, 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (s_last && tid == 0) {
+        __threadfence();
+        const unsigned num_resets = *reinterpret_cast<volatile unsigned *>(b.reduce_scratch + 0);
+        const float finished = *reinterpret_cast<volatile float *>(b.reduce_scratch + 2);
+        if (num_resets > 0)
+            b.consecutive_successes[0] = p.av_factor * finished / (float)num_resets +
+                                         (float)(1.0 - (double)p.av_factor) * b.consecutive_successes[0];
+        b.reduce_scratch[0] = 0u; b.reduce_scratch[1] = 0u; b.reduce_scratch[2] = 0u;
+        if (b.list.scratch && p.rand.step) *p.rand.step += 1ull;
+    }
+}
+
+int check(const IgeShadowHandParams *p, const IgeShadowHandBuffers *b) {
+    if (!p || !b) return ige_fail(IGE_ENULL, "params / buffers is NULL");
+    if (p->num_envs < 0) return ige_fail(IGE_ESIZE, "num_envs < 0");
+    if (p->num_hand_dofs < 1 || p->num_hand_dofs > IGE_MAX_DOF || p->num_dofs_per_env < p->num_hand_dofs)
+        return ige_fail(IGE_ESIZE, "num_hand_dofs=%d num_dofs_per_env=%d invalid", p->num_hand_dofs, p->num_dofs_per_env);
+    if (p->num_actions < 1 || p->num_actions > IGE_MAX_DOF) return ige_fail(IGE_ESIZE, "num_actions=%d invalid", p->num_actions);
+    if (p->obs_type < 0 || p->obs_type > 3) return ige_fail(IGE_EPARAM, "obs_type=%d invalid", p->obs_type);
+    for (int f = 0; f < IGE_HAND_NUM_FINGERTIPS; ++f)
+        if (p->fingertip_handles[f] < 0 || p->fingertip_handles[f] >= p->num_bodies)
+            return ige_fail(IGE_ESIZE, "fingertip_handles[%d]=%d outside [0, %d)", f, p->fingertip_handles[f], p->num_bodies);
+    IGE_REQUIRE_PTR(b->dof_state);
+    IGE_REQUIRE_PTR(b->root_state_tensor);
+    IGE_REQUIRE_PTR(b->goal_states);
+    IGE_REQUIRE_PTR(b->reset_buf);
+    IGE_REQUIRE_PTR(b->reset_goal_buf);
+    IGE_REQUIRE_PTR(b->progress_buf);
+    IGE_REQUIRE_PTR(b->successes);
+    if (!b->object_indices || !b->goal_object_indices) return ige_fail(IGE_ENULL, "object / goal index tensors are NULL");
+    return ige_check_list(b->list);
+}
+
+}  // namespace
+
+extern "C" int ige_shadow_hand_reset(const IgeShadowHandParams *p, const IgeShadowHandBuffers *b, void *stream) {
+    if (int rc = check(p, b)) return rc;
+    IGE_REQUIRE_PTR(b->goal_init_state);
+    IGE_REQUIRE_PTR(b->object_init_state);
+    IGE_REQUIRE_PTR(b->prev_targets);
+    IGE_REQUIRE_PTR(b->cur_targets);
+    IGE_REQUIRE_PTR(b->rb_forces);
+    IGE_REQUIRE_PTR(b->random_force_prob);
+    if (p->rand.mode == IGE_RAND_INJECTED && (!p->rand.goal_rank || !p->rand.env_rank))
+        return ige_fail(IGE_ENULL, "rand.goal_rank / rand.env_rank is NULL (INJECTED mode)");
+    if (p->rand.mode != IGE_RAND_INJECTED && p->rand.mode != IGE_RAND_PHILOX) return ige_fail(IGE_EPARAM, "rand.mode invalid");
+    if (p->num_envs == 0) return IGE_OK;
+    const int grid = (p->num_envs + 127) / 128;
+    shadow_hand_reset_kernel<<<grid, 128, 0, (cudaStream_t)stream>>>(*p, *b);
+    return ige_check_launch("ige_shadow_hand_reset");
+}
+
+extern "C" int ige_shadow_hand_post_physics(const IgeShadowHandParams *p, const IgeShadowHandBuffers *b, void *stream) {
+    if (int rc = check(p, b)) return rc;
+    IGE_REQUIRE_PTR(b->rigid_body_states);
+    IGE_REQUIRE_PTR(b->actions);
+    IGE_REQUIRE_PTR(b->obs_buf);
+    IGE_REQUIRE_PTR(b->rew_buf);
+    IGE_REQUIRE_PTR(b->consecutive_successes);
+    if (!b->reduce_scratch) return ige_fail(IGE_ENULL, "reduce_scratch is NULL");
+    const bool need_full = p->obs_type == IGE_HAND_OBS_FULL_STATE || p->asymmetric_obs;
+    if (need_full) {
+        IGE_REQUIRE_PTR(b->vec_sensor_tensor);
+        IGE_REQUIRE_PTR(b->dof_force_tensor);
+    }
+    if (p->asymmetric_obs) IGE_REQUIRE_PTR(b->states_buf);
+    IGE_OPTIONAL_PTR(b->obs_clamped);
+    if (p->num_envs == 0) return IGE_OK;
+    const int nobs = hand_num_obs(p->obs_type);
+    const size_t smem = (size_t)(((TE * nobs + 31) / 32) * 32 + (p->asymmetric_obs ? TE * MAX_OBS : 0)) * sizeof(float);
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(shadow_hand_post_physics_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)((TE * MAX_OBS + 32 + TE * MAX_OBS) * sizeof(float)));
+        if (e != cudaSuccess) return ige_fail((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+        attr_set = true;
+    }
+    const int grid = (p->num_envs + TE - 1) / TE;
+    shadow_hand_post_physics_kernel<<<grid, NT, smem, (cudaStream_t)stream>>>(*p, *b, ige_use_tma());
+    return ige_check_launch("ige_shadow_hand_post_physics");
+}

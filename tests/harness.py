@@ -175,12 +175,34 @@ def get(obj, name):
     return getattr(obj, name).detach().cpu().numpy()
 
 
-def assert_float_close(name, got, ref, rtol=RTOL):
+HAND_QD_OFFSET = {"openai": 18, "full_no_vel": 38, "full": 68, "full_state": 92}
+
+
+def hand_reward_slack(obj, ref_obs):
+    """compute_hand_reward (shadow_hand.py:761-764) is ill-conditioned where the rotation distance
+    approaches pi: rot_dist = 2*asin(|q_xyz|) has an unbounded derivative at |q_xyz| -> 1, so a 1-ulp
+    difference in the object quaternion (e.g. libm vs CUDA sinf/cosf in the reset of THIS step -- torch
+    CPU vs torch CUDA differ the same way) moves the reward by more than 1e-5.  The slack is the change
+    of the rotation term under a +-2 ulp perturbation of |q_xyz|; it is ~0 everywhere else."""
+    off = HAND_QD_OFFSET[obj.obs_type]
+    qd = np.asarray(ref_obs, dtype=np.float64)[:, off:off + 3]
+    qn = np.sqrt((qd ** 2).sum(-1))
+    eps, scale = obj.rot_eps, abs(obj.rot_reward_scale)
+
+    def rot_rew(q):
+        return scale / (np.abs(2.0 * np.arcsin(np.clip(q, 0.0, 1.0))) + eps)
+    d = 2.4e-7 * np.maximum(qn, 1e-3)
+    return np.maximum(np.abs(rot_rew(qn + d) - rot_rew(qn)), np.abs(rot_rew(qn - d) - rot_rew(qn)))
+
+
+def assert_float_close(name, got, ref, rtol=RTOL, slack=None):
     got = np.asarray(got, dtype=np.float64).reshape(-1)
     ref = np.asarray(ref, dtype=np.float64).reshape(-1)
     assert got.shape == ref.shape, f"{name}: shape {got.shape} vs {ref.shape}"
     err = np.abs(got - ref)
     bound = rtol * np.maximum(1.0, np.abs(ref))
+    if slack is not None:
+        bound = bound + np.asarray(slack, dtype=np.float64).reshape(-1)
     bad = ~(err <= bound)
     if bad.any():
         i = int(np.argmax(err / bound))
@@ -208,7 +230,8 @@ def compare_outputs(task, obj, ref_out, check_epilogue=True, bitexact=()):
     for name in INT_OUT[task]:
         assert_equal(name, get(obj, name), ref_out[name])
     for name in FLOAT_OUT[task]:
-        assert_float_close(name, get(obj, name), ref_out[name])
+        slack = hand_reward_slack(obj, ref_out["obs_buf"]) if (task == "shadow_hand" and name == "rew_buf") else None
+        assert_float_close(name, get(obj, name), ref_out[name], slack=slack)
     for name in bitexact:
         assert_equal(name + " (bit-exact)", get(obj, name).view(np.uint32), np.asarray(ref_out[name]).view(np.uint32))
     if task == "shadow_hand" and obj.asymmetric_obs:

@@ -14,12 +14,28 @@ pytestmark = pytest.mark.gpu
 DOFS = {"cartpole": 2, "ant": 8, "humanoid": 21}
 
 
+def _make_rands(task, ref, rng):
+    """Uniforms for one step in the shapes / order the reference's reset path draws them."""
+    k = int((H.get(ref, "reset_buf") != 0).sum())
+    if task == "shadow_hand":
+        kg = int((H.get(ref, "reset_goal_buf") != 0).sum())
+        out = {}
+        if kg:
+            out["A"] = rng.random((kg, 4), dtype=np.float32)
+        if k:
+            out["B"] = rng.random((k, 53), dtype=np.float32)
+            out["C"] = rng.random((k, 4), dtype=np.float32)
+            out["D"] = rng.random((k,), dtype=np.float32)
+        return out
+    return [rng.random((k, DOFS[task]), dtype=np.float32) for _ in range(2)]
+
+
 def _set_tma(on):
     lib = H.pkg._lib.lib()
     lib.ige_set_use_tma(C.c_int(1 if on else 0))
 
 
-@pytest.mark.parametrize("task", ["cartpole", "ant", "humanoid"])
+@pytest.mark.parametrize("task", ["cartpole", "ant", "humanoid", "shadow_hand"])
 def test_cuda_matches_reference_golden(task):
     for path in H.golden_files(task):
         blob = H.load_golden(path)
@@ -32,26 +48,26 @@ def test_cuda_matches_reference_golden(task):
             H.compare_outputs(task, obj, ref, bitexact=H.BITEXACT_FLOAT[task])
 
 
-def _oracle_vs_cuda(task, n, seed, reset_prob, steps=3, tma=True, rand_mode="injected"):
+def _oracle_vs_cuda(task, n, seed, reset_prob, steps=3, tma=True, rand_mode="injected", **make_kw):
     _set_tma(tma)
     try:
-        st = H.pkg.synthetic.make_state(task, n, seed=seed, reset_prob=reset_prob)
+        st = H.pkg.synthetic.make_state(task, n, seed=seed, reset_prob=reset_prob, **make_kw)
         ref = H.build(task, {k: v.copy() for k, v in st.items()}, "cpu", rand_mode=rand_mode, seed=seed)
         gpu = H.build(task, {k: v.copy() for k, v in st.items()}, "cuda:0", rand_mode=rand_mode, seed=seed)
         rng = np.random.Generator(np.random.PCG64(seed + 1))
         phys = np.random.Generator(np.random.PCG64(seed + 2))
-        d = DOFS[task]
         for s in range(steps):
             if s > 0:
                 cur = {k: H.get(ref, k) for k in H.pkg.factory.sim_tensor_names(H.TASK_NAME[task])}
                 cur.update({k: st[k] for k in st if k not in cur})
                 cur["progress_buf"] = H.get(ref, "progress_buf")
                 H.pkg.synthetic.advance_physics(task, cur, phys)
+                if task == "shadow_hand":
+                    cur["goal_states"] = H.get(ref, "goal_states")
                 names = H.pkg.factory.sim_tensor_names(H.TASK_NAME[task]) + (["actions"] if task != "cartpole" else [])
                 for o in (ref, gpu):
                     H.pkg.factory.load_sim_inputs(o, H.TASK_NAME[task], {k: cur[k] for k in names})
-            k = int((H.get(ref, "reset_buf") != 0).sum())
-            rands = [rng.random((k, d), dtype=np.float32) for _ in range(2)] if rand_mode == "injected" else None
+            rands = _make_rands(task, ref, rng) if rand_mode == "injected" else None
             ids_ref = H.oracle_step(task, ref, rands)
             ids_gpu = H.cuda_step(task, gpu, rands)
             H.assert_equal(f"step{s} reset ids", ids_gpu.cpu().numpy(), ids_ref.numpy())
@@ -93,6 +109,48 @@ def test_reset_extremes(task, reset_prob):
 def test_philox_mode_matches_oracle_philox(task):
     """Production (sync-free) reset noise: same counter-based generator in kernel and oracle."""
     _oracle_vs_cuda(task, 4096, 21, 0.25, steps=3, rand_mode="philox")
+
+
+# ShadowHand (SURVEY.md 8a a13-a15): default cfg size, every observation type, asymmetric states
+def test_shadow_hand_16384_full_state():
+    _oracle_vs_cuda("shadow_hand", 16384, 0, 0.02)
+
+
+@pytest.mark.parametrize("obs_type", ["openai", "full_no_vel", "full", "full_state"])
+@pytest.mark.parametrize("asym", [False, True])
+def test_shadow_hand_obs_types(obs_type, asym):
+    _oracle_vs_cuda("shadow_hand", 2052, 3, 0.2, steps=2, obs_type=obs_type, asymmetric_obs=asym)
+
+
+@pytest.mark.parametrize("n", [1, 37, 1000])
+@pytest.mark.parametrize("tma", [True, False])
+def test_shadow_hand_ragged(n, tma):
+    _oracle_vs_cuda("shadow_hand", n, 5, 0.3, steps=2, tma=tma)
+
+
+def test_shadow_hand_max_consecutive_successes_and_extremes():
+    _oracle_vs_cuda("shadow_hand", 2048, 7, 1.0, steps=2, max_consecutive_successes=3)
+    _oracle_vs_cuda("shadow_hand", 2048, 8, 0.0, steps=2, goal_reset_prob=0.3)     # goal-only resets
+
+
+def test_shadow_hand_philox():
+    _oracle_vs_cuda("shadow_hand", 4096, 21, 0.25, steps=3, rand_mode="philox")
+
+
+def test_shadow_hand_sim_call_lists():
+    """The id lists handed to gym.set_*_indexed: sorted unique() of object/goal actor rows (:634-636)."""
+    st = H.pkg.synthetic.make_state("shadow_hand", 3000, seed=4, reset_prob=0.1, goal_reset_prob=0.2)
+    gpu = H.build("shadow_hand", st, "cuda:0", rand_mode="philox")
+    env = np.flatnonzero(st["reset_buf"] != 0)
+    goal = np.flatnonzero(st["reset_goal_buf"] != 0)
+    want = np.unique(np.concatenate([st["object_indices"][env], st["goal_object_indices"][env],
+                                     st["goal_object_indices"][goal]])).astype(np.int32)
+    gpu.pre_physics_step(gpu.actions.clone())
+    calls = {name: (ids, cnt) for name, _, ids, cnt in gpu.sim.calls if ids is not None}
+    ids, cnt = calls["set_actor_root_state_tensor_indexed"]
+    np.testing.assert_array_equal(ids[:int(cnt.item())].cpu().numpy(), want)
+    ids, cnt = calls["set_dof_state_tensor_indexed"]
+    np.testing.assert_array_equal(ids[:int(cnt.item())].cpu().numpy(), st["hand_indices"][env].astype(np.int32))
 
 
 def test_empty_env_set():
