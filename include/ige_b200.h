@@ -278,6 +278,88 @@ int ige_shadow_hand_reset(const IgeShadowHandParams *p, const IgeShadowHandBuffe
 int ige_shadow_hand_post_physics(const IgeShadowHandParams *p, const IgeShadowHandBuffers *b, void *stream);
 
 /* ------------------------------------------------------------------------------------------
+ * Franka multi-agent tasks (the fork's agent axis: obs/rew/reset/progress rows = env * A + agent).
+ * Replaces <Task>.post_physics_step incl. reset_idx (+ _agent_ids_to_env_ids AND filter,
+ * _reset_init_cube_state, _reset_dest_cube_state / _reset_stack_base_cube_state), _update_states,
+ * compute_FSM, compute_global_FSM, compute_observations and compute_franka_reward of
+ *   FrankaReachMA   tasks/franka_reach_MA.py:519-612, :616-704, :821-828, :875-889, :928-960
+ *   FrankaCollectMA tasks/franka_collect_MA.py:549-734, :737-860, :1082-1174
+ *   FrankaCombineMA tasks/franka_combine_MA.py:565-789, :793-908, :1080-1166
+ *   FrankaPPMA      tasks/franka_PPMA.py:561-772, :776-895, :958-966, :1082-1167
+ * Reach / Collect accept 1..4 agents and targets; Combine / PP are written for exactly two
+ * (franka_PPMA.py:599, :606 hard-code the pair).
+ * ------------------------------------------------------------------------------------------ */
+#define IGE_FRANKA_REACH 0
+#define IGE_FRANKA_COLLECT 1
+#define IGE_FRANKA_COMBINE 2
+#define IGE_FRANKA_PP 3
+#define IGE_MA_MAX_AGENTS 4
+#define IGE_MA_NUM_COMPONENTS 10
+
+/* Uniforms of reset_idx, in the reference's torch.rand order (k = #envs whose agents are ALL flagged):
+ *   u[0] (k, T)     cube z         u[1] (k, T, 2)  cube xy      (_reset_init_cube_state)
+ *   u[2] (k, T)|(k) dest / stack-base z   u[3] (k, T, 2)|(k, 2) dest / stack-base xy   (PP | Combine only)
+ *   u[4] (k, 9)     franka DOF noise, shared by the A arms of the env (franka_reach_MA.py:638-647) */
+typedef struct IgeMAResetRand {
+    int32_t mode;
+    int32_t _pad;
+    uint64_t seed;
+    uint64_t *step;
+    const int32_t *env_rank;  /* INJECTED: [N] exclusive prefix of the per-env AND flag */
+    const float *u[5];
+} IgeMAResetRand;
+
+typedef struct IgeFrankaMAParams {
+    int32_t variant;          /* IGE_FRANKA_* */
+    int32_t num_envs, num_agents, num_targets;
+    int32_t num_actions;      /* 6 (Reach) / 7 */
+    int32_t num_obs;          /* 19 / 28 / 48 / 50 for A = T = 2 */
+    int32_t num_bodies, num_actors, num_dofs; /* per env: rigid bodies, actors, DOFs (= 9 A) */
+    /* strided slices of the reference (franka_reach_MA.py:463-469, :509; franka_PPMA.py:489-517) */
+    int32_t eef_body_start, eef_body_step;
+    int32_t base_body_start, base_body_step;
+    int32_t hand_body_start, hand_body_step;
+    int32_t cube_actor_start, cube_actor_step;
+    int32_t dest_actor_start, dest_actor_step; /* PP */
+    int32_t stack_base_actor;                  /* Combine */
+    float max_episode_length, clip_obs;
+    float cubeA_size, dest_size, wall_pos_y, wall_height;
+    /* reset constants, pre-folded by the host exactly as the reference's Python expressions do */
+    float cube_z_base;        /* table z + cube size / 2 (fp32 ops in Reach/Collect, double in Combine/PP) */
+    float cube_z_range;       /* rand_z_range: 0.5 (Reach) / 0.2 */
+    float cube_xy_center[2];
+    float cube_xy_mult;       /* 2 * startPositionNoise */
+    float aux_z_base;         /* dest / stack-base z */
+    float aux_xy_center_x[IGE_MA_MAX_AGENTS], aux_xy_center_y;
+    float aux_xy_mult;        /* 2 * startPositionNoise (PP) / 2 * 0.15 (Combine) */
+    float dof_noise_mult;     /* frankaDofNoise * 2 */
+    float franka_default_dof_pos[9], franka_dof_lower[9], franka_dof_upper[9];
+    IgeMAResetRand rand;
+} IgeFrankaMAParams;
+
+typedef struct IgeFrankaMABuffers {
+    const float *rigid_body_state; /* (N, num_bodies, 13) */
+    float *root_state;             /* (N, num_actors, 13) cube (+dest / stack-base) rows rewritten on reset */
+    float *dof_state;              /* (N, num_dofs, 2) */
+    const float *contact_forces;   /* (N, num_bodies, 3); Reach only */
+    const float *actions;          /* (N*A, num_actions) */
+    float *pos_control, *effort_control; /* (N, num_dofs) */
+    float *init_cubeA_state;       /* (N, T, 13) */
+    float *obs_buf;                /* (N*A, num_obs) */
+    float *rew_buf;                /* (N*A) */
+    int64_t *reset_buf, *progress_buf; /* (N*A) */
+    float *reward_components;      /* [IGE_MA_NUM_COMPONENTS] out: the .mean()s logged in extras
+                                      (state0..6, BSR, gBSR, side_rule; unused slots = 0) */
+    float *obs_clamped;            /* optional */
+    uint8_t *timeout_buf;          /* optional */
+    float *stats;                  /* optional; TASK0.. = component SUMS (what the multi-GPU all-reduce needs) */
+    float *reduce_scratch;         /* [IGE_MA_NUM_COMPONENTS + 2] zeroed once: component sums + retirement counter */
+    IgeResetList list;             /* ENV ids that were reset (all agents flagged) */
+} IgeFrankaMABuffers;
+
+int ige_franka_ma_post_physics(const IgeFrankaMAParams *p, const IgeFrankaMABuffers *b, void *stream);
+
+/* ------------------------------------------------------------------------------------------
  * Library
  * ------------------------------------------------------------------------------------------ */
 int ige_version(void);

@@ -101,6 +101,37 @@ class IgeShadowHandBuffers(C.Structure):
                 ("stats", _p), ("reduce_scratch", _p), ("list", IgeResetList)]
 
 
+IGE_FRANKA_VARIANT = {"reach": 0, "collect": 1, "combine": 2, "pp": 3}
+IGE_MA_MAX_AGENTS = 4
+IGE_MA_NUM_COMPONENTS = 10
+
+
+class IgeMAResetRand(C.Structure):
+    _fields_ = [("mode", _i), ("_pad", _i), ("seed", C.c_uint64), ("step", _p), ("env_rank", _p), ("u", _p * 5)]
+
+
+class IgeFrankaMAParams(C.Structure):
+    _fields_ = [("variant", _i), ("num_envs", _i), ("num_agents", _i), ("num_targets", _i), ("num_actions", _i),
+                ("num_obs", _i), ("num_bodies", _i), ("num_actors", _i), ("num_dofs", _i),
+                ("eef_body_start", _i), ("eef_body_step", _i), ("base_body_start", _i), ("base_body_step", _i),
+                ("hand_body_start", _i), ("hand_body_step", _i), ("cube_actor_start", _i), ("cube_actor_step", _i),
+                ("dest_actor_start", _i), ("dest_actor_step", _i), ("stack_base_actor", _i),
+                ("max_episode_length", _f), ("clip_obs", _f), ("cubeA_size", _f), ("dest_size", _f),
+                ("wall_pos_y", _f), ("wall_height", _f), ("cube_z_base", _f), ("cube_z_range", _f),
+                ("cube_xy_center", _f * 2), ("cube_xy_mult", _f), ("aux_z_base", _f),
+                ("aux_xy_center_x", _f * IGE_MA_MAX_AGENTS), ("aux_xy_center_y", _f), ("aux_xy_mult", _f),
+                ("dof_noise_mult", _f), ("franka_default_dof_pos", _f * 9), ("franka_dof_lower", _f * 9),
+                ("franka_dof_upper", _f * 9), ("rand", IgeMAResetRand)]
+
+
+class IgeFrankaMABuffers(C.Structure):
+    _fields_ = [("rigid_body_state", _p), ("root_state", _p), ("dof_state", _p), ("contact_forces", _p),
+                ("actions", _p), ("pos_control", _p), ("effort_control", _p), ("init_cubeA_state", _p),
+                ("obs_buf", _p), ("rew_buf", _p), ("reset_buf", _p), ("progress_buf", _p),
+                ("reward_components", _p), ("obs_clamped", _p), ("timeout_buf", _p), ("stats", _p),
+                ("reduce_scratch", _p), ("list", IgeResetList)]
+
+
 def fill_array(carr, values):
     for i, v in enumerate(values):
         carr[i] = type(carr[0])(v) if isinstance(carr[0], int) else float(v)

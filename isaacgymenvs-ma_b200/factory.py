@@ -13,12 +13,19 @@ _SIM_TENSORS = {
     "Humanoid": ["root_states", "dof_state", "vec_sensor_tensor", "dof_force_tensor"],
     "ShadowHand": ["dof_state", "root_state_tensor", "rigid_body_states", "vec_sensor_tensor", "dof_force_tensor"],
 }
+_MA_TASKS = {"FrankaReachMA": "reach", "FrankaCollectMA": "collect", "FrankaCombineMA": "combine", "FrankaPPMA": "pp"}
+for _t in _MA_TASKS:
+    _SIM_TENSORS[_t] = ["_rigid_body_state", "_root_state", "_dof_state", "_contact_forces"]
 _CFGS = {"Cartpole": synthetic.CARTPOLE_CFG, "Ant": synthetic.ANT_CFG, "Humanoid": synthetic.HUMANOID_CFG,
          "ShadowHand": synthetic.SHADOW_HAND_CFG}
 _SYN_NAME = {"Cartpole": "cartpole", "Ant": "ant", "Humanoid": "humanoid", "ShadowHand": "shadow_hand"}
+for _t, _v in _MA_TASKS.items():
+    _SYN_NAME[_t] = "franka_" + _v
 
 
 def task_cfg(task):
+    if task in _MA_TASKS:
+        return synthetic.franka_ma_cfg(_MA_TASKS[task])
     return dict(_CFGS[task])
 
 
@@ -30,11 +37,16 @@ def from_state(task, st, sim_device, rl_device=None, **kw):
     """Construct the mirror of `task` around an existing synthetic state dict (numpy arrays)."""
     dev = torch.device(sim_device)
     cfg = task_cfg(task)
-    cfg["num_envs"] = int(st["progress_buf"].shape[0])
+    if task in _MA_TASKS:
+        cfg = synthetic.franka_ma_cfg(_MA_TASKS[task], int(st["cfg_num_agents"]), int(st["cfg_num_targets"]))
+        cfg["num_envs"] = int(st["progress_buf"].shape[0]) // cfg["num_agents"]
+    else:
+        cfg["num_envs"] = int(st["progress_buf"].shape[0])
     for k in list(st):                      # per-state config overrides travel with the state dict
         if k.startswith("cfg_"):
             v = st[k]
-            cfg[k[4:]] = v.item() if v.shape == () and v.dtype.kind in "iuf" else str(v)
+            if task not in _MA_TASKS:
+                cfg[k[4:]] = v.item() if v.shape == () and v.dtype.kind in "iuf" else str(v)
     tensors = {k: torch.from_numpy(np.ascontiguousarray(st[k])).to(dev) for k in _SIM_TENSORS[task]}
     sim = SyntheticSim(tensors)
     obj = task_map[task](cfg, sim, dev, rl_device=rl_device, **kw)

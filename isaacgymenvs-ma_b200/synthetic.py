@@ -351,3 +351,136 @@ def advance_shadow_hand(st, rng):
 
 MAKERS["shadow_hand"] = make_shadow_hand
 ADVANCERS["shadow_hand"] = advance_shadow_hand
+
+
+# ---------------------------------------------------------------------------------------------
+# Franka multi-agent tasks (reference: tasks/franka_{reach,collect,combine}_MA.py, franka_PPMA.py)
+# ---------------------------------------------------------------------------------------------
+FRANKA_VARIANTS = ("reach", "collect", "combine", "pp")
+FRANKA_DEFAULT_DOF_POS = np.array([0, 0.1963, 0, -2.6180, 0, 2.9416, 0.7854, 0.035, 0.035], F32)
+# franka_panda_gripper.urdf joint limits (7 arm joints + 2 fingers)
+FRANKA_DOF_LOWER = np.array([-2.8973, -1.7628, -2.8973, -3.0718, -2.8973, -0.0175, -2.8973, 0.0, 0.0], F32)
+FRANKA_DOF_UPPER = np.array([2.8973, 1.7628, 2.8973, -0.0698, 2.8973, 3.7525, 2.8973, 0.04, 0.04], F32)
+FRANKA_LINKS = 17          # rigid bodies per arm (franka_panda_gripper.urdf)
+FRANKA_LINK_BASE, FRANKA_LINK_HAND, FRANKA_LINK_GRIP_SITE = 0, 9, 14
+
+
+def franka_ma_cfg(variant, num_agents=2, num_targets=None):
+    """Layout + parameters of one Franka MA variant.  Actor / body order (one env):
+    table, stand, [wall | stack_base], cubes x T, frankas x A (17 links each), [dests x T]."""
+    a = num_agents
+    t = a if num_targets is None else num_targets
+    extra_front = 1 if variant in ("collect", "combine") else 0
+    extra_back = t if variant == "pp" else 0
+    cube0 = 2 + extra_front
+    franka0 = cube0 + t
+    body_franka0 = cube0 + t
+    num_obs = {"reach": 10 + 3 * t + 3 * (a - 1), "collect": 3 * t + 17 + 3 * (a - 1) + 2,
+               "combine": 7 * t + 3 + 7 * a + 13 + 2 + 1 + 1, "pp": 7 * t + 3 * t + 7 * a + 13 + 2 + 1}[variant]
+    return dict(
+        variant=variant, num_agents=a, num_targets=t,
+        num_actions=6 if variant == "reach" else 7, num_obs=num_obs,
+        max_episode_length=150 if variant == "reach" else 300, clip_obs=5.0, clip_actions=1.0,
+        start_position_noise=0.25, franka_dof_noise=0.25, cubeA_size=0.05, dest_size=0.05,
+        table_surface_pos=(0.0, 0.0, 1.025), wall_pos_y=0.3, wall_height=0.3,
+        rand_z_range={"reach": 0.5, "collect": 0.2, "combine": 0.2, "pp": 0.2}[variant],
+        num_actors=2 + extra_front + t + a + extra_back, num_bodies=2 + extra_front + t + FRANKA_LINKS * a + extra_back,
+        num_dofs=9 * a,
+        cube_actor_start=cube0, cube_actor_step=1,
+        franka_actor_start=franka0,
+        dest_actor_start=franka0 + a, dest_actor_step=1,
+        stack_base_actor=2,
+        eef_body_start=body_franka0 + FRANKA_LINK_GRIP_SITE, eef_body_step=FRANKA_LINKS,
+        base_body_start=body_franka0 + FRANKA_LINK_BASE, base_body_step=FRANKA_LINKS,
+        hand_body_start=body_franka0 + FRANKA_LINK_HAND, hand_body_step=FRANKA_LINKS)
+
+
+def _franka_sim_draw(st, rng, cfg):
+    n, a, t = st["progress_buf"].shape[0] // cfg["num_agents"], cfg["num_agents"], cfg["num_targets"]
+    nb, na = cfg["num_bodies"], cfg["num_actors"]
+    v = cfg["variant"]
+    rb = np.zeros((n, nb, 13), F32)
+    rb[:, :, 0] = rng.uniform(-0.7, 0.7, (n, nb))
+    rb[:, :, 1] = rng.uniform(-0.5, 0.8, (n, nb))
+    rb[:, :, 2] = rng.uniform(1.0, 1.6, (n, nb))
+    rb[:, :, 3:7] = _rand_unit_quats(rng, n * nb).reshape(n, nb, 4)
+    rb[:, :, 7:13] = rng.standard_normal((n, nb, 6))
+    root = np.zeros((n, na, 13), F32)
+    root[:, :, 6] = 1.0
+    cs, fs = cfg["cube_actor_start"], cfg["franka_actor_start"]
+    cubes = root[:, cs:cs + t]
+    if v == "collect":     # straddle every FSM threshold of franka_collect_MA.py:549-606
+        cubes[:, :, 0] = rng.uniform(-0.8, 0.8, (n, t))
+        cubes[:, :, 1] = rng.uniform(-0.3, 0.7, (n, t))
+        cubes[:, :, 2] = rng.uniform(1.0, 1.6, (n, t))
+    else:
+        cubes[:, :, 0:2] = rng.uniform(-0.25, 0.25, (n, t, 2))
+        cubes[:, :, 2] = 1.05 + rng.uniform(0.0, cfg["rand_z_range"], (n, t))
+    cubes[:, :, 3:7] = _rand_unit_quats(rng, n * t).reshape(n, t, 4)
+    cubes[:, :, 7:13] = rng.normal(0, 0.2, (n, t, 6))
+    if v == "pp":
+        ds = cfg["dest_actor_start"]
+        dests = root[:, ds:ds + t]
+        dests[:, :, 0] = np.array([-0.25, 0.25] * (t // 2 + 1), F32)[:t] + rng.uniform(-0.25, 0.25, (n, t))
+        dests[:, :, 1] = 0.3 + rng.uniform(-0.25, 0.25, (n, t))
+        dests[:, :, 2] = 1.01875
+        near = rng.random((n, t)) < 0.4     # cube hovering over / next to its destination (states 3..6)
+        off = np.zeros((n, t, 3), F32)
+        off[:, :, 0:2] = rng.uniform(-0.04, 0.04, (n, t, 2))
+        off[:, :, 2] = rng.uniform(-0.12, 0.12, (n, t))
+        dests[near, 0:3] = (cubes[:, :, 0:3] + off)[near]
+    if v == "combine":
+        sb = root[:, cfg["stack_base_actor"]]
+        sb[:, 0:2] = rng.uniform(-0.15, 0.15, (n, 2))
+        sb[:, 2] = 1.01875 + rng.uniform(-0.05, 0.08, n)
+    # a fraction of the grippers sits on a cube (own cube for combine/pp, any cube otherwise)
+    es, est = cfg["eef_body_start"], cfg["eef_body_step"]
+    for ag in range(a):
+        on = rng.random(n) < 0.3
+        tgt = cubes[:, ag % t, 0:3] + rng.uniform(-0.02, 0.02, (n, 3)).astype(F32)
+        rb[on, es + ag * est, 0:3] = tgt[on]
+    # two grippers of an env sometimes too close (gFSM of combine / pp, franka_PPMA.py:597-611)
+    if a >= 2:
+        close = rng.random(n) < 0.15
+        rb[close, es + est, 0:3] = rb[close, es, 0:3] + rng.uniform(-0.1, 0.1, (int(close.sum()), 3)).astype(F32)
+    st["_rigid_body_state"] = rb
+    st["_root_state"] = root
+    st["_contact_forces"] = rng.normal(0.0, 0.1, (n, nb, 3)).astype(F32)
+    dof = np.zeros((n, cfg["num_dofs"], 2), F32)
+    dof[:, :, 0] = rng.uniform(np.tile(FRANKA_DOF_LOWER, a), np.tile(FRANKA_DOF_UPPER, a), (n, cfg["num_dofs"]))
+    dof[:, :, 1] = rng.normal(0, 1, (n, cfg["num_dofs"]))
+    st["_dof_state"] = dof
+    st["actions"] = rng.uniform(-1.0, 1.0, (n * a, cfg["num_actions"])).astype(F32)
+
+
+def make_franka_ma(variant, num_envs, seed=0, reset_prob=0.02, fall_frac=None, num_agents=2, num_targets=None,
+                   ragged_flags=False):
+    cfg = franka_ma_cfg(variant, num_agents, num_targets)
+    rng = _rng(seed)
+    n, a, t = num_envs, cfg["num_agents"], cfg["num_targets"]
+    st = {"cfg_variant": np.array(variant), "cfg_num_agents": np.array(a), "cfg_num_targets": np.array(t)}
+    env_prog = _progress(rng, n, cfg["max_episode_length"])
+    st["progress_buf"] = np.repeat(env_prog, a)           # lock-step across an env's agents
+    env_reset = _resets(rng, n, reset_prob)
+    st["reset_buf"] = np.repeat(env_reset, a)
+    if ragged_flags:                                      # exercise the AND filter (franka_reach_MA.py:879-882)
+        flip = rng.random(n * a) < 0.2
+        st["reset_buf"] = np.where(flip, 1 - st["reset_buf"], st["reset_buf"]).astype(I64)
+    _franka_sim_draw(st, rng, cfg)
+    st["_pos_control"] = rng.normal(0, 1, (n, cfg["num_dofs"])).astype(F32)
+    st["_effort_control"] = rng.normal(0, 1, (n, cfg["num_dofs"])).astype(F32)
+    st["_init_cubeA_state"] = np.zeros((n, t, 13), F32)
+    st["obs_buf"] = np.zeros((n * a, cfg["num_obs"]), F32)
+    st["rew_buf"] = np.zeros(n * a, F32)
+    return st
+
+
+def _advance_franka(st, rng):
+    cfg = franka_ma_cfg(str(st["cfg_variant"]), int(st["cfg_num_agents"]), int(st["cfg_num_targets"]))
+    _franka_sim_draw(st, rng, cfg)
+
+
+for _v in FRANKA_VARIANTS:
+    MAKERS["franka_" + _v] = (lambda v: (lambda num_envs, seed=0, reset_prob=0.02, **kw: make_franka_ma(
+        v, num_envs, seed=seed, reset_prob=reset_prob, **kw)))(_v)
+    ADVANCERS["franka_" + _v] = _advance_franka

@@ -49,6 +49,14 @@ static inline float dot3(const float *a, const float *b) {
 /* torch.sum(dim=-1) of a contiguous row: 8 vector lanes accumulated over full groups of 8,
  * then tail elements, then the lanes, all added sequentially (ATen SumKernel inner reduction). */
 static float row_sum(const float *x, int d) {
+    if (d < 8) { /* scalar path: 4 interleaved accumulators, remainder into the first, then a chain */
+        float p[4] = {0, 0, 0, 0};
+        int q = d / 4;
+        for (int i = 0; i < q; ++i)
+            for (int k = 0; k < 4; ++k) p[k] += x[4 * i + k];
+        for (int i = 4 * q; i < d; ++i) p[0] += x[i];
+        return ((p[0] + p[1]) + p[2]) + p[3];
+    }
     float lanes[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     int nv = d / 8;
     if (nv >= 4) { /* 4 interleaved accumulators per lane; not reached for d <= 31 */
@@ -692,6 +700,297 @@ int ige_oracle_shadow_hand_post_physics(const IgeShadowHandParams *p, const IgeS
     add_stat(b->stats, IGE_STAT_DONE, s_done); add_stat(b->stats, IGE_STAT_TIMEOUT, s_to);
     add_stat(b->stats, IGE_STAT_DONE_LENGTH, s_len); add_stat(b->stats, IGE_STAT_TASK0, (double)num_resets);
     add_stat(b->stats, IGE_STAT_TASK0 + 1, finished);
+    if (b->list.scratch && p->rand.step) *p->rand.step += 1;
+    return 0;
+}
+
+
+/* ------------------------------------------------------------------------------------------
+ * Franka multi-agent tasks: tasks/franka_{reach,collect,combine}_MA.py, tasks/franka_PPMA.py
+ * ------------------------------------------------------------------------------------------ */
+static float ma_uniform(const IgeMAResetRand *r, int draw, int rank, int env, int cols, int j) {
+    if (r->mode == IGE_RAND_PHILOX) {
+        IgeResetRand q = {IGE_RAND_PHILOX, 0, r->seed, r->step, 0, 0, 0};
+        return philox_uniform(&q, (uint32_t)env, (uint32_t)draw, (uint32_t)j);
+    }
+    return r->u[draw][(size_t)rank * cols + j];
+}
+static const float *ma_body(const IgeFrankaMAParams *p, const IgeFrankaMABuffers *b, int e, int start, int step, int i) {
+    return b->rigid_body_state + ((size_t)e * p->num_bodies + start + step * i) * 13;
+}
+static float *ma_actor(const IgeFrankaMAParams *p, const IgeFrankaMABuffers *b, int e, int actor) {
+    return b->root_state + ((size_t)e * p->num_actors + actor) * 13;
+}
+
+/* reset_idx for one env whose agents are all flagged (franka_reach_MA.py:616-704 and siblings) */
+static void ma_reset_env(const IgeFrankaMAParams *p, const IgeFrankaMABuffers *b, int e) {
+    const int A = p->num_agents, T = p->num_targets;
+    const IgeMAResetRand *r = &p->rand;
+    const int rk = r->env_rank ? r->env_rank[e] : 0;
+    for (int c = 0; c < T; ++c) { /* _reset_init_cube_state */
+        float *init = b->init_cubeA_state + ((size_t)e * T + c) * 13;
+        for (int i = 0; i < 13; ++i) init[i] = 0.0f;
+        init[2] = p->cube_z_base + ma_uniform(r, 0, rk, e, T, c) * p->cube_z_range;
+        init[0] = p->cube_xy_center[0] + p->cube_xy_mult * (ma_uniform(r, 1, rk, e, T * 2, c * 2 + 0) - 0.5f);
+        init[1] = p->cube_xy_center[1] + p->cube_xy_mult * (ma_uniform(r, 1, rk, e, T * 2, c * 2 + 1) - 0.5f);
+        init[6] = 1.0f;
+        float *cube = ma_actor(p, b, e, p->cube_actor_start + p->cube_actor_step * c);
+        for (int i = 0; i < 13; ++i) cube[i] = init[i]; /* _cubeA_state[env_ids] = _init_cubeA_state[env_ids] */
+    }
+    if (p->variant == IGE_FRANKA_PP) { /* _reset_dest_cube_state franka_PPMA.py:867-895 */
+        for (int c = 0; c < T; ++c) {
+            float *d = ma_actor(p, b, e, p->dest_actor_start + p->dest_actor_step * c);
+            for (int i = 0; i < 13; ++i) d[i] = 0.0f;
+            d[2] = p->aux_z_base + ma_uniform(r, 2, rk, e, T, c) * 0.0f;
+            d[0] = p->aux_xy_center_x[c] + p->aux_xy_mult * (ma_uniform(r, 3, rk, e, T * 2, c * 2 + 0) - 0.5f);
+            d[1] = p->aux_xy_center_y + p->aux_xy_mult * (ma_uniform(r, 3, rk, e, T * 2, c * 2 + 1) - 0.5f);
+            d[6] = 1.0f;
+        }
+    }
+    if (p->variant == IGE_FRANKA_COMBINE) { /* _reset_stack_base_cube_state franka_combine_MA.py:880-908 */
+        float *d = ma_actor(p, b, e, p->stack_base_actor);
+        for (int i = 0; i < 13; ++i) d[i] = 0.0f;
+        d[2] = p->aux_z_base + ma_uniform(r, 2, rk, e, 1, 0) * 0.0f;
+        d[0] = p->aux_xy_center_x[0] + p->aux_xy_mult * (ma_uniform(r, 3, rk, e, 2, 0) - 0.5f);
+        d[1] = p->aux_xy_center_y + p->aux_xy_mult * (ma_uniform(r, 3, rk, e, 2, 1) - 0.5f);
+        d[6] = 1.0f;
+    }
+    float pos[9];
+    for (int j = 0; j < 9; ++j) { /* :638-644 */
+        float v = p->franka_default_dof_pos[j] + p->dof_noise_mult * (ma_uniform(r, 4, rk, e, 9, j) - 0.5f);
+        v = fminf(v, p->franka_dof_upper[j]);
+        v = fmaxf(v, p->franka_dof_lower[j]);
+        pos[j] = j >= 7 ? p->franka_default_dof_pos[j] : v;
+    }
+    for (int a = 0; a < A; ++a)
+        for (int j = 0; j < 9; ++j) { /* :646-656: the same sample tiled over the A arms */
+            size_t k = (size_t)e * p->num_dofs + a * 9 + j;
+            b->dof_state[k * 2 + 0] = pos[j];
+            b->dof_state[k * 2 + 1] = 0.0f;
+            b->pos_control[k] = pos[j];
+            b->effort_control[k] = 0.0f;
+        }
+    for (int a = 0; a < A; ++a) { b->progress_buf[(size_t)e * A + a] = 0; b->reset_buf[(size_t)e * A + a] = 0; }
+}
+
+static inline float pow2_small(int s) { return s >= 0 ? (float)(1 << s) : 0.5f; } /* torch.pow(2.0, FSM) */
+
+int ige_oracle_franka_ma_post_physics(const IgeFrankaMAParams *p, const IgeFrankaMABuffers *b) {
+    const int N = p->num_envs, A = p->num_agents, T = p->num_targets, NA = p->num_actions, NO = p->num_obs, V = p->variant;
+    /* post_physics_step :821-826: progress++, agent flags -> reset_idx (AND filter) */
+    for (size_t i = 0; i < (size_t)N * A; ++i) b->progress_buf[i] += 1;
+    emit_reset_list(&b->list, b->reset_buf, N, A);
+    for (int e = 0; e < N; ++e) {
+        int all = 1;
+        for (int a = 0; a < A; ++a) all &= b->reset_buf[(size_t)e * A + a] != 0;
+        if (all) ma_reset_env(p, b, e);
+    }
+    double comp[IGE_MA_NUM_COMPONENTS] = {0};
+    double s_rew = 0, s_done = 0, s_to = 0, s_len = 0;
+    for (int e = 0; e < N; ++e) {
+        const float *eef[IGE_MA_MAX_AGENTS], *base[IGE_MA_MAX_AGENTS], *cube[IGE_MA_MAX_AGENTS];
+        for (int a = 0; a < A; ++a) {
+            eef[a] = ma_body(p, b, e, p->eef_body_start, p->eef_body_step, a);
+            base[a] = ma_body(p, b, e, p->base_body_start, p->base_body_step, a);
+        }
+        for (int c = 0; c < T; ++c) cube[c] = ma_actor(p, b, e, p->cube_actor_start + p->cube_actor_step * c);
+        /* _get_min_relative_pos (franka_reach_MA.py:521-531) */
+        int nearest[IGE_MA_MAX_AGENTS];
+        float min_rel[IGE_MA_MAX_AGENTS][3];
+        for (int a = 0; a < A; ++a) {
+            float best = 0.0f;
+            int bi = 0;
+            for (int c = 0; c < T; ++c) {
+                float d = norm3(cube[c][0] - eef[a][0], cube[c][1] - eef[a][1], cube[c][2] - eef[a][2]);
+                if (c == 0 || d < best) { best = d; bi = c; }
+            }
+            nearest[a] = bi;
+            for (int i = 0; i < 3; ++i) min_rel[a][i] = cube[bi][i] - eef[a][i];
+        }
+        /* per-agent FSM */
+        int fsm[IGE_MA_MAX_AGENTS] = {0, 0, 0, 0};
+        float md[IGE_MA_MAX_AGENTS];
+        const float on_cube_th = (float)(0.05 * 0.5 * 0.9); /* cubeA_size * 0.5 * 0.9 with cubeA_size = 0.05 */
+        const float on_th = (float)((double)p->cubeA_size * 0.5 * 0.9);
+        (void)on_cube_th;
+        for (int a = 0; a < A; ++a) {
+            const float *act = b->actions + ((size_t)e * A + a) * NA;
+            const int closed = act[NA - 1] < 0.0f;
+            if (V == IGE_FRANKA_REACH) {
+                md[a] = norm3(min_rel[a][0], min_rel[a][1], min_rel[a][2]);
+            } else if (V == IGE_FRANKA_COLLECT) { /* franka_collect_MA.py:549-606 */
+                md[a] = norm3(min_rel[a][0], min_rel[a][1], min_rel[a][2]);
+                const float *hc = cube[nearest[a]];
+                const int close = md[a] <= on_th;
+                const int holding = close && closed;
+                const int high = (hc[2] - 1.05f) > (float)((double)p->wall_height + (double)p->cubeA_size / 2);
+                const int in_area = (hc[1] > (float)((double)p->wall_pos_y + (double)p->cubeA_size * 1.)) && (fabsf(hc[0]) < 0.6f);
+                const int low = (hc[2] - 1.05f) < (float)((double)p->wall_height / 2.);
+                int s = 0;
+                if (close) s = 1;
+                if (holding) s = 2;
+                if (holding && high) s = 3;
+                if (holding && in_area) s = 4;
+                if (holding && in_area && low) s = 5;
+                if (holding && in_area && low && !closed) s = 6;
+                fsm[a] = s;
+            } else { /* Combine :565-611 / PP :561-595: own cube */
+                md[a] = norm3(cube[a][0] - eef[a][0], cube[a][1] - eef[a][1], cube[a][2] - eef[a][2]);
+                const int on = md[a] <= on_th;
+                int s = 0;
+                if (on) s = 1;
+                if (on && closed) s = 2;
+                if (V == IGE_FRANKA_PP) {
+                    const float *dest = ma_actor(p, b, e, p->dest_actor_start + p->dest_actor_step * a);
+                    const float dz = dest[2] - cube[a][2];
+                    const int lifted = fabsf(dz) >= (float)(((double)p->dest_size + (double)p->cubeA_size) / 2.);
+                    const int align = norm2(dest[0] - cube[a][0], dest[1] - cube[a][1]) < (float)((0.05) * 0.5);
+                    const int stackable = fabsf(dz) <= (float)((double)p->cubeA_size * 0.8660 + (double)p->dest_size / 2.);
+                    if (on && lifted) s = 3;
+                    if (align) s = 4;
+                    if (align && stackable) s = 5;
+                    if (align && stackable && !closed) s = 6;
+                }
+                fsm[a] = s;
+            }
+        }
+        /* rows */
+        for (int a = 0; a < A; ++a) {
+            const size_t row = (size_t)e * A + a;
+            const float *act = b->actions + row * NA;
+            float *o = b->obs_buf + row * NO;
+            int gfsm = 0;
+            if (V == IGE_FRANKA_COMBINE || V == IGE_FRANKA_PP) {
+                /* compute_global_FSM franka_PPMA.py:597-611: d_ecp is stack([..]).flatten(), i.e. laid out
+                 * [all envs | all envs]; flat row k pairs d_ep[k // 2] with d_ecp[k] */
+                const float *e0 = eef[0], *e1 = eef[1];
+                const int too_close_grip = norm3(e1[0] - e0[0], e1[1] - e0[1], e1[2] - e0[2]) <= 0.18f;
+                const size_t k = row;
+                const int j = k < (size_t)N ? (int)k : (int)(k - N);
+                const float *je = ma_body(p, b, j, p->eef_body_start, p->eef_body_step, k < (size_t)N ? 0 : 1);
+                const float *jc = ma_actor(p, b, j, p->cube_actor_start + p->cube_actor_step * (k < (size_t)N ? 1 : 0));
+                const int too_close_cube = norm3(je[0] - jc[0], je[1] - jc[1], je[2] - jc[2]) <= 0.18f;
+                gfsm = (too_close_grip || too_close_cube) ? -1 : 0;
+            }
+            int n = 0;
+            if (V == IGE_FRANKA_REACH || V == IGE_FRANKA_COLLECT) {
+                for (int c = 0; c < T; ++c) for (int i = 0; i < 3; ++i) o[n++] = cube[c][i];
+                for (int i = 0; i < 4; ++i) o[n++] = eef[a][3 + i];
+                for (int i = 0; i < 3; ++i) o[n++] = eef[a][i];
+                for (int i = 0; i < 3; ++i) o[n++] = min_rel[a][i];
+                if (V == IGE_FRANKA_COLLECT) {
+                    for (int i = 0; i < 3; ++i) o[n++] = base[a][i];
+                    for (int i = 0; i < 4; ++i) o[n++] = base[a][3 + i];
+                }
+                for (int s = 1; s < A; ++s) for (int i = 0; i < 3; ++i) o[n++] = eef[(a + s) % A][i];
+                if (V == IGE_FRANKA_COLLECT) { o[n++] = (float)fsm[a]; o[n++] = (float)fsm[a]; }
+            } else {
+                for (int s = 0; s < T; ++s) for (int i = 0; i < 4; ++i) o[n++] = cube[(a + s) % T][3 + i];
+                for (int s = 0; s < T; ++s) for (int i = 0; i < 3; ++i) o[n++] = cube[(a + s) % T][i];
+                const float *aux = NULL;
+                if (V == IGE_FRANKA_COMBINE) {
+                    aux = ma_actor(p, b, e, p->stack_base_actor);
+                    for (int i = 0; i < 3; ++i) o[n++] = aux[i];
+                } else {
+                    for (int s = 0; s < T; ++s) {
+                        const float *d = ma_actor(p, b, e, p->dest_actor_start + p->dest_actor_step * ((a + s) % T));
+                        for (int i = 0; i < 3; ++i) o[n++] = d[i];
+                    }
+                    aux = ma_actor(p, b, e, p->dest_actor_start + p->dest_actor_step * a);
+                }
+                for (int i = 0; i < 3; ++i) o[n++] = cube[a][i] - eef[a][i];
+                for (int i = 0; i < 3; ++i) o[n++] = aux[i] - cube[a][i];
+                for (int i = 0; i < 3; ++i) o[n++] = base[a][i];
+                for (int i = 0; i < 4; ++i) o[n++] = base[a][3 + i];
+                for (int s = 0; s < A; ++s) for (int i = 0; i < 3; ++i) o[n++] = eef[(a + s) % A][i];
+                for (int s = 0; s < A; ++s) for (int i = 0; i < 4; ++i) o[n++] = eef[(a + s) % A][3 + i];
+                for (int s = 0; s < A; ++s) o[n++] = pow2_small(fsm[(a + s) % A]);
+                o[n++] = pow2_small(gfsm);
+                if (V == IGE_FRANKA_COMBINE) o[n++] = (a == A - 1) ? 1.0f : 0.0f; /* agent_idx :526-527 */
+            }
+            /* compute_franka_reward */
+            float rewards;
+            float c10[IGE_MA_NUM_COMPONENTS] = {0};
+            const float alast = act[NA - 1];
+            if (V == IGE_FRANKA_REACH) { /* franka_reach_MA.py:928-960 */
+                const float d = md[a];
+                const float dist_reward = 1.0f / (0.5f + d * d);
+                float sq[8];
+                for (int j = 0; j < NA; ++j) sq[j] = act[j] * act[j];
+                const float actions_cost = row_sum(sq, NA) * 0.01f;
+                rewards = dist_reward - actions_cost;
+                int64_t distinct = 0;
+                for (int c = 0; c < T; ++c) { int hit = 0; for (int q = 0; q < A; ++q) hit |= nearest[q] == c; distinct += hit; }
+                const float all_touched = ((float)distinct / (float)A) * 1.0f;
+                const float *cf = b->contact_forces + ((size_t)e * p->num_bodies + p->hand_body_start + p->hand_body_step * a) * 3;
+                const float colliding = (norm3(cf[0], cf[1], cf[2]) >= 0.1f ? 1.0f : 0.0f) * -10.0f;
+                rewards = rewards + (all_touched + colliding);
+            } else {
+                const float m = md[a];
+                const int s = fsm[a];
+                c10[0] = s == 0 ? expf(-5.0f * (m * m)) : 0.0f;
+                c10[1] = s == 1 ? expf(-1.0f * alast) : 0.0f;
+                if (V == IGE_FRANKA_COLLECT) { /* franka_collect_MA.py:1082-1174 */
+                    const float *hc = cube[nearest[a]];
+                    c10[2] = s == 2 ? (hc[2] - 1.05f) / (float)(0.3 + 0.025) : 0.0f;
+                    const float dy = fabsf(hc[1] - (float)(0.3 + 0.05 * 2.));
+                    c10[3] = s == 3 ? expf(-5.0f * (dy * dy)) : 0.0f;
+                    const float dz = fabsf(hc[2] - (float)(0.3 / 2. + 1.05));
+                    c10[4] = s == 4 ? expf(-5.0f * (dz * dz)) : 0.0f;
+                    c10[5] = s == 5 ? expf(4.0f * alast) : 0.0f;
+                    c10[6] = s == 6 ? 1.0f * 3.0f : 0.0f;
+                    c10[7] = (float)s; /* BSR */
+                    c10[8] = 0.0f;     /* gBSR */
+                    rewards = c10[0] + c10[1] + c10[2] + c10[3] + c10[4] + c10[5] + c10[6] + c10[7] + c10[8] + 0.0f;
+                } else if (V == IGE_FRANKA_COMBINE) { /* franka_combine_MA.py:1080-1166 */
+                    const float *sb = ma_actor(p, b, e, p->stack_base_actor);
+                    float lift = fabsf(sb[2] - cube[a][2]) / (float)((0.05 + 0.05) * 0.5);
+                    lift = lift < 0.0f ? 0.0f : (lift > 1.0f ? 1.0f : lift);
+                    c10[2] = s == 2 ? lift : 0.0f;
+                    c10[7] = (float)s;
+                    rewards = c10[0] + c10[1] + c10[7];
+                } else { /* franka_PPMA.py:1082-1167 */
+                    const float *dest = ma_actor(p, b, e, p->dest_actor_start + p->dest_actor_step * a);
+                    const float rx = dest[0] - cube[a][0], ry = dest[1] - cube[a][1], rz = dest[2] - cube[a][2];
+                    float lift = fabsf(rz) / (float)((0.05 + 0.05) * 0.5);
+                    lift = lift < 0.0f ? 0.0f : (lift > 1.0f ? 1.0f : lift);
+                    c10[2] = s == 2 ? lift : 0.0f;
+                    const float dt = norm3(rx + 0.0f, ry + 0.0f, rz + 0.05f);
+                    c10[3] = s == 3 ? expf(-3.0f * dt) : 0.0f;
+                    c10[4] = s == 4 ? expf(-10.0f * dt) : 0.0f;
+                    c10[5] = s == 5 ? expf(5.0f * alast) : 0.0f;
+                    c10[6] = s == 6 ? tanhf(m) : 0.0f;
+                    c10[7] = (float)s;
+                    c10[8] = (float)gfsm * 0.5f;
+                    c10[9] = 0.0f;
+                    rewards = c10[0] + c10[1] + c10[2] + c10[3] + c10[4] + c10[5] + c10[6] + c10[7] + c10[8] + c10[9];
+                }
+            }
+            rewards = rewards < 0.0f ? 0.0f : rewards; /* torch.clip(rewards, 0., None) */
+            for (int i = 0; i < IGE_MA_NUM_COMPONENTS; ++i) comp[i] += c10[i];
+            int64_t reset = b->reset_buf[row];
+            const int64_t progress = b->progress_buf[row];
+            const int late = (float)progress >= p->max_episode_length - 1.0f;
+            if (late) reset = 1;
+            b->rew_buf[row] = rewards;
+            b->reset_buf[row] = reset;
+            const int timeout = late && reset != 0;
+            if (b->timeout_buf) b->timeout_buf[row] = (uint8_t)timeout;
+            if (b->obs_clamped)
+                for (int j = 0; j < NO; ++j) {
+                    float v = o[j];
+                    v = v < -p->clip_obs ? -p->clip_obs : v; v = v > p->clip_obs ? p->clip_obs : v;
+                    b->obs_clamped[row * NO + j] = v;
+                }
+            s_rew += rewards; s_done += reset != 0; s_to += timeout; s_len += reset != 0 ? (double)progress : 0.0;
+        }
+    }
+    if (b->reward_components)
+        for (int i = 0; i < IGE_MA_NUM_COMPONENTS; ++i) b->reward_components[i] = (float)(comp[i] / ((double)N * A));
+    add_stat(b->stats, IGE_STAT_STEPS, (double)N * A); add_stat(b->stats, IGE_STAT_REWARD, s_rew);
+    add_stat(b->stats, IGE_STAT_DONE, s_done); add_stat(b->stats, IGE_STAT_TIMEOUT, s_to);
+    add_stat(b->stats, IGE_STAT_DONE_LENGTH, s_len);
+    for (int i = 0; i < IGE_MA_NUM_COMPONENTS; ++i) add_stat(b->stats, IGE_STAT_TASK0 + i, comp[i]);
     if (b->list.scratch && p->rand.step) *p->rand.step += 1;
     return 0;
 }

@@ -24,6 +24,8 @@ syn = pkg.synthetic
 
 CFGS = {"cartpole": syn.CARTPOLE_CFG, "ant": syn.ANT_CFG, "humanoid": syn.HUMANOID_CFG,
         "shadow_hand": syn.SHADOW_HAND_CFG}
+for _v in syn.FRANKA_VARIANTS:
+    CFGS["franka_" + _v] = None     # built per fixture: synthetic.franka_ma_cfg(variant, A, T)
 
 # (task, num_envs, seed, reset_prob of step 0, steps)
 FIXTURES = [
@@ -39,12 +41,25 @@ FIXTURES = [
     ("shadow_hand", 48, 3, 0.1, 2, dict(obs_type="full_no_vel")),
     ("shadow_hand", 48, 4, 0.1, 2, dict(obs_type="full", max_consecutive_successes=3)),
     ("shadow_hand", 48, 5, 0.0, 2, dict(obs_type="full_state", goal_reset_prob=0.2)),   # goal-only resets
+    ("franka_reach", 64, 0, 0.1, 3, {}),
+    ("franka_reach", 32, 1, 1.0, 2, {}),                          # first step resets every env (vec_task.py:317)
+    ("franka_reach", 32, 2, 0.3, 2, dict(ragged_flags=True)),     # AND filter: partially flagged envs do not reset
+    ("franka_reach", 24, 3, 0.2, 2, dict(num_agents=3)),          # numAgents override (cfg/task/FrankaReachMA.yaml:9)
+    ("franka_collect", 64, 0, 0.1, 3, {}),
+    ("franka_collect", 32, 1, 1.0, 2, {}),
+    ("franka_combine", 64, 0, 0.1, 3, {}),
+    ("franka_combine", 32, 1, 1.0, 2, {}),
+    ("franka_pp", 64, 0, 0.1, 3, {}),
+    ("franka_pp", 32, 1, 1.0, 2, {}),
+    ("franka_pp", 32, 2, 0.3, 2, dict(ragged_flags=True)),
 ]
 
 
 def generate(task, n, seed, reset_prob, steps, **kw):
-    cfg = CFGS[task]
     st = syn.make_state(task, n, seed=seed, reset_prob=reset_prob, **kw)
+    cfg = CFGS[task]
+    if task.startswith("franka_"):
+        cfg = syn.franka_ma_cfg(task[len("franka_"):], int(st["cfg_num_agents"]), int(st["cfg_num_targets"]))
     obj = ref_harness.BUILDERS[task](st, cfg)
     rng = np.random.Generator(np.random.PCG64(seed + 7919))
     blob = {"meta_task": task, "meta_num_envs": n, "meta_seed": seed, "meta_steps": steps,

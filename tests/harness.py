@@ -19,7 +19,10 @@ from oracle import oracle  # noqa: E402
 GOLDEN_DIR = os.path.join(ROOT, "tests", "golden")
 RTOL = 1e-5   # north_star: observations and rewards within 1e-5 relative in fp32
 
-TASK_NAME = {"cartpole": "Cartpole", "ant": "Ant", "humanoid": "Humanoid", "shadow_hand": "ShadowHand"}
+TASK_NAME = {"cartpole": "Cartpole", "ant": "Ant", "humanoid": "Humanoid", "shadow_hand": "ShadowHand",
+             "franka_reach": "FrankaReachMA", "franka_collect": "FrankaCollectMA",
+             "franka_combine": "FrankaCombineMA", "franka_pp": "FrankaPPMA"}
+MA_TASKS = ["franka_reach", "franka_collect", "franka_combine", "franka_pp"]
 ENTRY = {"cartpole": "cartpole_post_physics", "ant": "ant_post_physics", "humanoid": "humanoid_post_physics"}
 FLOAT_OUT = {
     "cartpole": ["obs_buf", "rew_buf", "dof_state"],
@@ -35,9 +38,15 @@ _HAND_FLOAT = ["obs_buf", "rew_buf", "successes", "consecutive_successes", "goal
                "dof_state", "prev_targets", "cur_targets", "rb_forces", "random_force_prob"]
 FLOAT_OUT["shadow_hand"] = _HAND_FLOAT
 INT_OUT["shadow_hand"] = ["reset_buf", "reset_goal_buf", "progress_buf", "randomize_buf"]
+for _t in MA_TASKS:
+    FLOAT_OUT[_t] = ["obs_buf", "rew_buf", "_root_state", "_dof_state", "_pos_control", "_effort_control",
+                     "_init_cubeA_state"]
+    INT_OUT[_t] = ["reset_buf", "progress_buf"]
 BITEXACT_FLOAT = {"cartpole": ["dof_state"], "ant": ["potentials", "prev_potentials", "dof_state"],
                   "humanoid": ["potentials", "prev_potentials", "dof_state"],
                   "shadow_hand": ["successes", "rb_forces"]}
+for _t in MA_TASKS:
+    BITEXACT_FLOAT[_t] = ["_root_state", "_dof_state", "_pos_control", "_effort_control", "_init_cubeA_state"]
 
 
 def golden_files(task):
@@ -138,11 +147,40 @@ def cuda_step_hand(obj, rands=None):
     return ids
 
 
+def _ma_set_uniforms(obj, rands, device):
+    if obj.rand_mode == "philox" or not rands:
+        return
+    u = [None] * 5
+    for (slot, _), r in zip(obj.rand_shapes(0), rands):
+        u[slot] = torch.from_numpy(np.ascontiguousarray(r)).to(device)
+    obj.set_injected_uniforms(*u)
+
+
+def oracle_step_ma(obj, rands=None):
+    assert obj.device.type == "cpu"
+    k = oracle_compact(obj, group=obj.num_agents)
+    ids = obj.reset_env_ids[:k].clone()
+    _ma_set_uniforms(obj, rands, "cpu")
+    p, b = obj.abi_structs()
+    oracle.call("franka_ma_post_physics", p, b)
+    obj._u = [None] * 5
+    return ids
+
+
+def cuda_step_ma(obj, rands=None):
+    _ma_set_uniforms(obj, rands, obj.device)
+    obj.post_physics_step()
+    k = int(obj.reset_count.item())
+    return obj.reset_env_ids[:k].clone()
+
+
 def oracle_step(task, obj, rands=None):
     """One post_physics_step of the CPU oracle on a mirror object whose tensors live on the CPU."""
     assert obj.device.type == "cpu"
     if task == "shadow_hand":
         return oracle_step_hand(obj, rands)
+    if task in MA_TASKS:
+        return oracle_step_ma(obj, rands)
     k = oracle_compact(obj)
     ids = obj.reset_env_ids[:k].clone()
     if obj.rand_mode != "philox":
@@ -160,6 +198,8 @@ def cuda_step(task, obj, rands=None):
     """One post_physics_step of the product CUDA path; returns the reset id list it emitted."""
     if task == "shadow_hand":
         return cuda_step_hand(obj, rands)
+    if task in MA_TASKS:
+        return cuda_step_ma(obj, rands)
     if obj.rand_mode != "philox" and rands:
         obj.set_injected_uniforms(*[torch.from_numpy(np.ascontiguousarray(r)).to(obj.device) for r in rands])
     obj.post_physics_step()
@@ -238,6 +278,12 @@ def compare_outputs(task, obj, ref_out, check_epilogue=True, bitexact=()):
         assert_float_close("states_buf", get(obj, "states_buf"), ref_out["states_buf"])
         if check_epilogue and obj.fuse_epilogue and "states_clamped" in ref_out:
             assert_float_close("states_clamped", obj.states_clamped.detach().cpu().numpy(), ref_out["states_clamped"])
+    if task in MA_TASKS and "reward_components" in ref_out:
+        from isaacgymenvs_ma_b200.tasks.franka_ma import COMPONENT_NAMES
+        names = [str(x) for x in ref_out.get("reward_component_names", COMPONENT_NAMES)]
+        got = obj.reward_components.detach().cpu().numpy()
+        sel = np.array([got[COMPONENT_NAMES.index(nm)] for nm in names])
+        assert_float_close("reward_components", sel, ref_out["reward_components"])
     if check_epilogue and obj.fuse_epilogue and "obs_clamped" in ref_out:
         assert_float_close("obs_clamped", get(obj, "obs_clamped"), ref_out["obs_clamped"])
         assert_equal("time_outs", get(obj, "time_outs").astype(bool), np.asarray(ref_out["time_outs"]).astype(bool))
@@ -249,6 +295,8 @@ def snapshot(task, obj):
         out["states_buf"] = get(obj, "states_buf").copy()
         if obj.fuse_epilogue:
             out["states_clamped"] = obj.states_clamped.detach().cpu().numpy().copy()
+    if task in MA_TASKS:
+        out["reward_components"] = obj.reward_components.detach().cpu().numpy().copy()
     if obj.fuse_epilogue:
         out["obs_clamped"] = get(obj, "obs_clamped").copy()
         out["time_outs"] = get(obj, "time_outs").copy()

@@ -147,8 +147,86 @@ def build_shadow_hand(st, cfg):
     return obj
 
 
+_MA_MODULE = {"reach": ("tasks.franka_reach_MA", "FrankaReachMA"), "collect": ("tasks.franka_collect_MA", "FrankaCollectMA"),
+              "combine": ("tasks.franka_combine_MA", "FrankaCombineMA"), "pp": ("tasks.franka_PPMA", "FrankaPPMA")}
+
+
+def build_franka_ma(st, cfg):
+    """cfg = synthetic.franka_ma_cfg(variant, A, T).  pre_physics_step is replaced by `self.actions = actions`
+    (its OSC torque controller needs PhysX Jacobians / mass matrices and is out of the hot path)."""
+    v = cfg["variant"]
+    modname, clsname = _MA_MODULE[v]
+    cls = getattr(ref_shim.ref_module(modname), clsname)
+    a, t = cfg["num_agents"], cfg["num_targets"]
+    n = st["progress_buf"].shape[0] // a
+    obj = cls.__new__(cls)
+    _common(obj, cfg, n, cfg["num_obs"], cfg["num_actions"], num_agents=a)
+    obj.num_targets = t
+    obj.num_dofs = cfg["num_dofs"]
+    obj.states, obj.handles = {}, {}
+    obj.cubeA_size, obj.dest_size = cfg["cubeA_size"], cfg["dest_size"]
+    obj.start_position_noise, obj.start_rotation_noise = cfg["start_position_noise"], 0.785
+    obj.franka_dof_noise = cfg["franka_dof_noise"]
+    obj._table_surface_pos = np.array(cfg["table_surface_pos"])
+    obj.reward_settings = {"r_dist_scale": 0.1, "r_lift_scale": 1.5, "r_align_scale": 2.0, "r_stack_scale": 16.0,
+                           "table_height": obj._table_surface_pos[2]}
+    obj.wall_pos, obj.wall_height = [0.0, cfg["wall_pos_y"], 1.175], cfg["wall_height"]
+    from ige_loader import load_package
+    syn = load_package().synthetic
+    FRANKA_DEFAULT_DOF_POS, FRANKA_DOF_LOWER, FRANKA_DOF_UPPER = (syn.FRANKA_DEFAULT_DOF_POS, syn.FRANKA_DOF_LOWER,
+                                                                  syn.FRANKA_DOF_UPPER)
+    obj.franka_default_dof_pos = _t(FRANKA_DEFAULT_DOF_POS)
+    obj.franka_dof_lower_limits, obj.franka_dof_upper_limits = _t(FRANKA_DOF_LOWER), _t(FRANKA_DOF_UPPER)
+    for k in ("_rigid_body_state", "_root_state", "_dof_state", "_contact_forces", "_pos_control", "_effort_control",
+              "_init_cubeA_state", "obs_buf", "rew_buf", "reset_buf", "progress_buf"):
+        setattr(obj, k, _t(st[k]))
+    obj._q, obj._qd = obj._dof_state[..., 0], obj._dof_state[..., 1]
+    rb = obj._rigid_body_state
+
+    def strided(tensor, start, step, count):
+        return tensor[:, start:start + step * count:step, :]
+    obj._eef_state = strided(rb, cfg["eef_body_start"], cfg["eef_body_step"], a)
+    obj._base_state = strided(rb, cfg["base_body_start"], cfg["base_body_step"], a)
+    obj._eef_lf_state = obj._eef_state.clone()
+    obj._eef_rf_state = obj._eef_state.clone()
+    obj._hands_contact_forces = strided(obj._contact_forces, cfg["hand_body_start"], cfg["hand_body_step"], a)
+    cs = cfg["cube_actor_start"]
+    obj._cubeA_ids = list(range(cs, cs + t))
+    obj._cubeA_state = strided(obj._root_state, cs, cfg["cube_actor_step"], t)
+    obj.frankas = [list(range(cfg["franka_actor_start"], cfg["franka_actor_start"] + a))]
+    obj._global_indices = torch.arange(n * cfg["num_actors"], dtype=torch.int32).view(n, -1)
+    obj.states["cubeA_size"] = torch.ones(n, 1) * cfg["cubeA_size"]
+    if v == "pp":
+        ds = cfg["dest_actor_start"]
+        obj._dest_ids = list(range(ds, ds + t))
+        obj._dest_state = strided(obj._root_state, ds, cfg["dest_actor_step"], t)
+    if v == "combine":
+        obj._stack_base_id = cfg["stack_base_actor"]
+        obj._stack_base_state = obj._root_state[:, obj._stack_base_id, :]
+        obj.agent_idx = torch.zeros(n * a, 1, dtype=torch.long)             # franka_combine_MA.py:526-527
+        obj.agent_idx[a - 1::a, :] = 1
+        obj.states["agent_idx"] = obj.agent_idx
+    obj.actions = _t(st["actions"])
+    obj.pre_physics_step = lambda act: setattr(obj, "actions", act.clone())
+    return obj
+
+
 BUILDERS = {"cartpole": build_cartpole, "ant": build_ant, "humanoid": build_humanoid,
             "shadow_hand": build_shadow_hand}
+for _v in ("reach", "collect", "combine", "pp"):
+    BUILDERS["franka_" + _v] = build_franka_ma
+
+
+def franka_rand_shapes(variant, k, a, t):
+    """torch.rand call shapes of reset_idx, in order (franka_reach_MA.py:616-704, franka_PPMA.py:776-895,
+    franka_combine_MA.py:793-908)."""
+    shapes = [(k, t), (k, t, 2)]                 # _reset_init_cube_state: z then xy
+    if variant == "pp":
+        shapes += [(k, t), (k, t, 2)]            # _reset_dest_cube_state
+    if variant == "combine":
+        shapes += [(k,), (k, 2)]                 # _reset_stack_base_cube_state
+    shapes.append((k, 9))                        # franka dof noise
+    return shapes
 
 # buffers the path mutates / produces, per task (captured after every step)
 OUTPUTS = {
@@ -171,6 +249,10 @@ SIM_INPUTS = {
 
 SIM_INPUTS["shadow_hand"] = ["dof_state", "root_state_tensor", "rigid_body_states", "vec_sensor_tensor",
                              "dof_force_tensor", "actions"]
+for _v in ("reach", "collect", "combine", "pp"):
+    OUTPUTS["franka_" + _v] = ["obs_buf", "rew_buf", "reset_buf", "progress_buf", "_root_state", "_dof_state",
+                               "_pos_control", "_effort_control", "_init_cubeA_state"]
+    SIM_INPUTS["franka_" + _v] = ["_rigid_body_state", "_root_state", "_dof_state", "_contact_forces", "actions"]
 
 
 def reset_rand_shapes(task, k, cfg):
@@ -202,6 +284,8 @@ def run_reference_step(task, obj, st, cfg, torch_seed):
         if k == "actions":
             continue
         getattr(obj, k).copy_(_t(st[k]))
+    if task.startswith("franka_"):
+        return _run_reference_step_ma(task, obj, st, cfg, torch_seed)
     reset_ids = obj.reset_buf.nonzero(as_tuple=False).flatten().clone()
     goal_ids = obj.reset_goal_buf.nonzero(as_tuple=False).flatten().clone() if task == "shadow_hand" else None
     if task == "cartpole":
@@ -231,4 +315,32 @@ def run_reference_step(task, obj, st, cfg, torch_seed):
         out["states_clamped"] = obs_dict["states"].detach().clone().numpy()
     calls = [(name, [a.numpy() if isinstance(a, torch.Tensor) else a for a in args])
              for name, args in obj.gym.calls]
+    return out, rands, calls
+
+
+def _run_reference_step_ma(task, obj, st, cfg, torch_seed):
+    a, t, v = cfg["num_agents"], cfg["num_targets"], cfg["variant"]
+    for k in SIM_INPUTS[task]:
+        if k != "actions":
+            getattr(obj, k).copy_(_t(st[k]))
+    flags = (obj.reset_buf != 0).view(-1, a).all(dim=1)
+    env_ids = flags.nonzero(as_tuple=False).flatten().clone()
+    any_flag = bool((obj.reset_buf != 0).any())
+    obj.gym.calls.clear()
+    torch.manual_seed(torch_seed)
+    obs_dict, rew, reset, extras = obj.step(_t(st["actions"]))
+    k = int(env_ids.numel())
+    rands = []
+    if any_flag:      # reset_idx runs (and draws, possibly with k == 0 rows) whenever ANY agent row is flagged
+        torch.manual_seed(torch_seed)
+        rands = [torch.rand(*s).numpy() for s in franka_rand_shapes(v, k, a, t)]
+    out = {name: getattr(obj, name).detach().clone().numpy() for name in OUTPUTS[task]}
+    out["obs_clamped"] = obs_dict["obs"].detach().clone().numpy()
+    out["time_outs"] = extras["time_outs"].detach().clone().numpy()
+    out["reset_env_ids"] = env_ids.to(torch.int32).numpy()
+    comps = sorted(k2 for k2 in extras if k2.startswith("r/"))
+    if comps:
+        out["reward_component_names"] = np.array(comps)
+        out["reward_components"] = np.array([float(extras[c]) for c in comps], np.float32)
+    calls = [(name, [x.numpy() if isinstance(x, torch.Tensor) else x for x in args]) for name, args in obj.gym.calls]
     return out, rands, calls
