@@ -18,6 +18,7 @@ _SIGS = {
     "ige_humanoid_post_physics": (_abi.IgeLocomotionParams, _abi.IgeLocomotionBuffers),
     "ige_shadow_hand_reset": (_abi.IgeShadowHandParams, _abi.IgeShadowHandBuffers),
     "ige_shadow_hand_post_physics": (_abi.IgeShadowHandParams, _abi.IgeShadowHandBuffers),
+    "ige_franka_ma_post_physics": (_abi.IgeFrankaMAParams, _abi.IgeFrankaMABuffers),
 }
 
 

@@ -1,0 +1,477 @@
+// franka_ma.cu -- fused post_physics_step of the fork's multi-agent Franka tasks for sm_100a.
+//
+// Replaces (reference, isaacgymenvs/tasks/): FrankaReachMA (franka_reach_MA.py:519-612, :616-704,
+// :821-828, :875-889, :928-960), FrankaCollectMA (franka_collect_MA.py:549-734, :737-860, :1082-1174),
+// FrankaCombineMA (franka_combine_MA.py:565-789, :793-908, :1080-1166), FrankaPPMA (franka_PPMA.py:
+// 561-772, :776-895, :958-966, :1082-1167): progress++, agent flags -> AND-filtered env resets
+// (cube / destination / stack-base root rows, arm DOF rows, controls), nearest-cube argmin, the
+// per-agent FSM, the global FSM, the agent-axis observation rows (cyclic shift: every agent sees
+// itself first), the FSM-gated reward, the time-out reset flag and the logged reward-component means.
+//
+// One thread per ENV (it owns the env's A agent rows: the per-env quantities -- distance matrix,
+// nearest ids, FSM of every agent -- are shared by the rows, so nothing is exchanged between
+// threads).  The gathers from the rigid-body / root tensors are 28-byte pieces of 52-byte rows
+// (sector granular by nature); the (envs x A x num_obs) observation tile is assembled in shared
+// memory and leaves with one TMA bulk store, so the dominant write stream is fully coalesced.
+//
+// Combine / PP: compute_global_FSM pairs flat row k with d_ecp[k] of a (2, N)-shaped stack that was
+// flatten()ed (franka_PPMA.py:606), i.e. row k reads the gripper / cube of env k or k - N.  Those
+// cube rows may be rewritten by that other env's reset, so these two variants run the reset as its
+// own launch first (grid-wide ordering by the stream); Reach / Collect are a single launch.
+#include "ige_common.cuh"
+
+namespace {
+
+constexpr int TE = 64;   // envs per CTA (two 32-env list tiles)
+constexpr int NT = 64;
+constexpr int MAXA = IGE_MA_MAX_AGENTS;
+constexpr int NC = IGE_MA_NUM_COMPONENTS;
+enum Phase { PH_FUSED = 0, PH_RESET = 1, PH_COMPUTE = 2 };
+
+__device__ __forceinline__ float clampf(float x, float c) { return x < -c ? -c : (x > c ? c : x); }
+
+__device__ __forceinline__ float ma_uniform(const IgeMAResetRand &r, uint64_t step, int draw, int rank, int env, int cols,
+                                            int j) {
+    if (r.mode == IGE_RAND_PHILOX) {
+        uint32_t c[4] = {(uint32_t)env, ((uint32_t)draw << 16) | ((uint32_t)j >> 2), (uint32_t)step, (uint32_t)(step >> 32)};
+        ige::philox4x32_10(c, (uint32_t)r.seed, (uint32_t)(r.seed >> 32));
+        return (float)(c[j & 3] >> 8) * (1.0f / 16777216.0f);
+    }
+    return __ldg(r.u[draw] + (size_t)rank * cols + j);
+}
+__device__ __forceinline__ const float *body_row(const IgeFrankaMAParams &p, const IgeFrankaMABuffers &b, int e, int start,
+                                                 int step, int i) {
+    return b.rigid_body_state + ((size_t)e * p.num_bodies + start + step * i) * 13;
+}
+__device__ __forceinline__ float *actor_row(const IgeFrankaMAParams &p, const IgeFrankaMABuffers &b, int e, int actor) {
+    return b.root_state + ((size_t)e * p.num_actors + actor) * 13;
+}
+
+// reset_idx for one env whose agents are all flagged (franka_reach_MA.py:616-704 and siblings)
+__device__ void reset_env(const IgeFrankaMAParams &p, const IgeFrankaMABuffers &b, uint64_t step, int e) {
+    const int A = p.num_agents, T = p.num_targets;
+    const IgeMAResetRand &r = p.rand;
+    const int rk = r.env_rank ? __ldg(r.env_rank + e) : 0;
+    for (int c = 0; c < T; ++c) {  // _reset_init_cube_state
+        float v[13];
+#pragma unroll
+        for (int i = 0; i < 13; ++i) v[i] = 0.0f;
+        v[2] = p.cube_z_base + ma_uniform(r, step, 0, rk, e, T, c) * p.cube_z_range;
+        v[0] = p.cube_xy_center[0] + p.cube_xy_mult * (ma_uniform(r, step, 1, rk, e, T * 2, c * 2 + 0) - 0.5f);
+        v[1] = p.cube_xy_center[1] + p.cube_xy_mult * (ma_uniform(r, step, 1, rk, e, T * 2, c * 2 + 1) - 0.5f);
+        v[6] = 1.0f;
+        float *init = b.init_cubeA_state + ((size_t)e * T + c) * 13;
+        float *cube = actor_row(p, b, e, p.cube_actor_start + p.cube_actor_step * c);
+#pragma unroll
+        for (int i = 0; i < 13; ++i) { init[i] = v[i]; cube[i] = v[i]; }
+    }
+    if (p.variant == IGE_FRANKA_PP) {  // _reset_dest_cube_state franka_PPMA.py:867-895
+        for (int c = 0; c < T; ++c) {
+            float *d = actor_row(p, b, e, p.dest_actor_start + p.dest_actor_step * c);
+#pragma unroll
+            for (int i = 0; i < 13; ++i) d[i] = 0.0f;
+            d[2] = p.aux_z_base + ma_uniform(r, step, 2, rk, e, T, c) * 0.0f;
+            d[0] = p.aux_xy_center_x[c] + p.aux_xy_mult * (ma_uniform(r, step, 3, rk, e, T * 2, c * 2 + 0) - 0.5f);
+            d[1] = p.aux_xy_center_y + p.aux_xy_mult * (ma_uniform(r, step, 3, rk, e, T * 2, c * 2 + 1) - 0.5f);
+            d[6] = 1.0f;
+        }
+    }
+    if (p.variant == IGE_FRANKA_COMBINE) {  // _reset_stack_base_cube_state franka_combine_MA.py:880-908
+        float *d = actor_row(p, b, e, p.stack_base_actor);
+#pragma unroll
+        for (int i = 0; i < 13; ++i) d[i] = 0.0f;
+        d[2] = p.aux_z_base + ma_uniform(r, step, 2, rk, e, 1, 0) * 0.0f;
+        d[0] = p.aux_xy_center_x[0] + p.aux_xy_mult * (ma_uniform(r, step, 3, rk, e, 2, 0) - 0.5f);
+        d[1] = p.aux_xy_center_y + p.aux_xy_mult * (ma_uniform(r, step, 3, rk, e, 2, 1) - 0.5f);
+        d[6] = 1.0f;
+    }
+    float pos[9];
+#pragma unroll
+    for (int j = 0; j < 9; ++j) {  // :638-644
+        float v = p.franka_default_dof_pos[j] + p.dof_noise_mult * (ma_uniform(r, step, 4, rk, e, 9, j) - 0.5f);
+        v = fminf(v, p.franka_dof_upper[j]);
+        v = fmaxf(v, p.franka_dof_lower[j]);
+        pos[j] = j >= 7 ? p.franka_default_dof_pos[j] : v;
+    }
+    for (int a = 0; a < A; ++a)
+#pragma unroll
+        for (int j = 0; j < 9; ++j) {  // :646-656: the same sample tiled over the A arms
+            const size_t k = (size_t)e * p.num_dofs + a * 9 + j;
+            reinterpret_cast<float2 *>(b.dof_state)[k] = make_float2(pos[j], 0.0f);
+            b.pos_control[k] = pos[j];
+            b.effort_control[k] = 0.0f;
+        }
+}
+
+__device__ __forceinline__ float pow2_small(int s) { return s >= 0 ? (float)(1 << s) : 0.5f; }  // torch.pow(2.0, FSM)
+
+// torch.sum(actions ** 2, dim=-1) for fewer than 8 columns: ATen's scalar path (4 interleaved
+// accumulators, remainder into the first)
+__device__ __forceinline__ float sum_sq_small(const float *act, int d) {
+    float p4[4] = {0.f, 0.f, 0.f, 0.f};
+    const int q = d / 4;
+    for (int i = 0; i < q; ++i)
+#pragma unroll
+        for (int k = 0; k < 4; ++k) { const float a = act[4 * i + k]; p4[k] += a * a; }
+    for (int i = 4 * q; i < d; ++i) { const float a = act[i]; p4[0] += a * a; }
+    return ((p4[0] + p4[1]) + p4[2]) + p4[3];
+}
+
+__global__ void __launch_bounds__(NT) franka_ma_kernel(const __grid_constant__ IgeFrankaMAParams p,
+                                                       const __grid_constant__ IgeFrankaMABuffers b, const int phase,
+                                                       const int use_tma) {
+    extern __shared__ __align__(128) float obs_tile[];  // TE * A * num_obs
+    __shared__ int s_last;
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int N = p.num_envs, A = p.num_agents, T = p.num_targets, NA = p.num_actions, NO = p.num_obs, V = p.variant;
+    const int e0 = blockIdx.x * TE;
+    const int ne = min(TE, N - e0);
+    const int e = e0 + tid;
+    const bool valid = tid < ne;
+    const uint64_t step = (p.rand.mode == IGE_RAND_PHILOX && p.rand.step)
+                              ? *reinterpret_cast<const volatile uint64_t *>(p.rand.step) : 0ull;
+
+    // ---- post_physics_step :821-826: progress++, agent flags -> reset_idx (AND filter) ----
+    bool did_reset = false;
+    if (phase != PH_COMPUTE && valid) {
+        bool all = true;
+        for (int a = 0; a < A; ++a) {
+            const size_t row = (size_t)e * A + a;
+            b.progress_buf[row] += 1;
+            all &= b.reset_buf[row] != 0;
+        }
+        if (all) {
+            reset_env(p, b, step, e);
+            for (int a = 0; a < A; ++a) { b.progress_buf[(size_t)e * A + a] = 0; b.reset_buf[(size_t)e * A + a] = 0; }
+            did_reset = true;
+        }
+    }
+    if (phase != PH_COMPUTE && b.list.scratch) {
+        const uint32_t mask = __ballot_sync(0xffffffffu, did_reset);
+        if (lane == 0 && e < N) ige::publish_tile_mask(b.list, e >> 5, mask);
+    }
+    if (phase == PH_RESET) {
+        if (b.list.scratch) ige::finish_reset_list(b.list, N, nullptr, lane == 0);
+        return;
+    }
+
+    // ---- _update_states / compute_FSM / compute_observations / compute_franka_reward ----
+    float comp[NC];
+#pragma unroll
+    for (int i = 0; i < NC; ++i) comp[i] = 0.0f;
+    float st_rew = 0.f, st_done = 0.f, st_to = 0.f, st_len = 0.f;
+    if (valid) {
+        float eef[MAXA][7], cube[MAXA][7];
+        for (int a = 0; a < A; ++a) {
+            const float *r = body_row(p, b, e, p.eef_body_start, p.eef_body_step, a);
+#pragma unroll
+            for (int i = 0; i < 7; ++i) eef[a][i] = __ldg(r + i);
+        }
+        for (int c = 0; c < T; ++c) {
+            const float *r = actor_row(p, b, e, p.cube_actor_start + p.cube_actor_step * c);
+#pragma unroll
+            for (int i = 0; i < 7; ++i) cube[c][i] = r[i];
+        }
+        // _get_min_relative_pos (franka_reach_MA.py:521-531)
+        float ncube[MAXA][3];   // nearest cube position per agent, kept by value
+        unsigned touched = 0u;   // bit c set <=> cube c is some agent's nearest cube
+        for (int a = 0; a < MAXA; ++a) { ncube[a][0] = ncube[a][1] = ncube[a][2] = 0.f; }
+        for (int a = 0; a < A; ++a) {
+            float best = 0.0f, bx = 0.f, by = 0.f, bz = 0.f;
+            int bi = 0;
+            for (int c = 0; c < T; ++c) {
+                const float d = ige::norm3(cube[c][0] - eef[a][0], cube[c][1] - eef[a][1], cube[c][2] - eef[a][2]);
+                if (c == 0 || d < best) { best = d; bi = c; bx = cube[c][0]; by = cube[c][1]; bz = cube[c][2]; }
+            }
+            ncube[a][0] = bx; ncube[a][1] = by; ncube[a][2] = bz;
+            touched |= 1u << bi;
+        }
+        int fsm[MAXA] = {0, 0, 0, 0};
+        float md[MAXA] = {0.f, 0.f, 0.f, 0.f};
+        const float on_th = (float)((double)p.cubeA_size * 0.5 * 0.9);
+        for (int a = 0; a < A; ++a) {
+            const float alast = __ldg(b.actions + ((size_t)e * A + a) * NA + NA - 1);
+            const bool closed = alast < 0.0f;
+            int s = 0;
+            if (V == IGE_FRANKA_REACH || V == IGE_FRANKA_COLLECT) {
+                const float *nc = ncube[a];
+                md[a] = ige::norm3(nc[0] - eef[a][0], nc[1] - eef[a][1], nc[2] - eef[a][2]);
+                if (V == IGE_FRANKA_COLLECT) {  // franka_collect_MA.py:549-606
+                    const bool close = md[a] <= on_th;
+                    const bool holding = close && closed;
+                    const bool high = (nc[2] - 1.05f) > (float)((double)p.wall_height + (double)p.cubeA_size / 2);
+                    const bool in_area = (nc[1] > (float)((double)p.wall_pos_y + (double)p.cubeA_size * 1.)) && (fabsf(nc[0]) < 0.6f);
+                    const bool low = (nc[2] - 1.05f) < (float)((double)p.wall_height / 2.);
+                    if (close) s = 1;
+                    if (holding) s = 2;
+                    if (holding && high) s = 3;
+                    if (holding && in_area) s = 4;
+                    if (holding && in_area && low) s = 5;
+                    if (holding && in_area && low && !closed) s = 6;
+                }
+            } else {  // Combine :565-611 / PP :561-595: own cube
+                md[a] = ige::norm3(cube[a][0] - eef[a][0], cube[a][1] - eef[a][1], cube[a][2] - eef[a][2]);
+                const bool on = md[a] <= on_th;
+                if (on) s = 1;
+                if (on && closed) s = 2;
+                if (V == IGE_FRANKA_PP) {
+                    const float *dest = actor_row(p, b, e, p.dest_actor_start + p.dest_actor_step * a);
+                    const float dz = dest[2] - cube[a][2];
+                    const bool lifted = fabsf(dz) >= (float)(((double)p.dest_size + (double)p.cubeA_size) / 2.);
+                    const bool align = ige::norm2(dest[0] - cube[a][0], dest[1] - cube[a][1]) < (float)((0.05) * 0.5);
+                    const bool stackable = fabsf(dz) <= (float)((double)p.cubeA_size * 0.8660 + (double)p.dest_size / 2.);
+                    if (on && lifted) s = 3;
+                    if (align) s = 4;
+                    if (align && stackable) s = 5;
+                    if (align && stackable && !closed) s = 6;
+                }
+            }
+            fsm[a] = s;
+        }
+        for (int a = 0; a < A; ++a) {
+            const size_t row = (size_t)e * A + a;
+            const float *act = b.actions + row * NA;
+            float *o = obs_tile + ((size_t)tid * A + a) * NO;
+            int gfsm = 0;
+            if (V == IGE_FRANKA_COMBINE || V == IGE_FRANKA_PP) {
+                // compute_global_FSM franka_PPMA.py:597-611 (the flatten() of a (2, N) stack, see header)
+                const bool grip = ige::norm3(eef[1][0] - eef[0][0], eef[1][1] - eef[0][1], eef[1][2] - eef[0][2]) <= 0.18f;
+                const bool first_half = row < (size_t)N;
+                const int j = first_half ? (int)row : (int)(row - N);
+                const float *je = body_row(p, b, j, p.eef_body_start, p.eef_body_step, first_half ? 0 : 1);
+                const float *jc = actor_row(p, b, j, p.cube_actor_start + p.cube_actor_step * (first_half ? 1 : 0));
+                const bool cub = ige::norm3(__ldg(je) - jc[0], __ldg(je + 1) - jc[1], __ldg(je + 2) - jc[2]) <= 0.18f;
+                gfsm = (grip || cub) ? -1 : 0;
+            }
+            int n = 0;
+            if (V == IGE_FRANKA_REACH || V == IGE_FRANKA_COLLECT) {
+                for (int c = 0; c < T; ++c) { o[n++] = cube[c][0]; o[n++] = cube[c][1]; o[n++] = cube[c][2]; }
+#pragma unroll
+                for (int i = 0; i < 4; ++i) o[n++] = eef[a][3 + i];
+#pragma unroll
+                for (int i = 0; i < 3; ++i) o[n++] = eef[a][i];
+#pragma unroll
+                for (int i = 0; i < 3; ++i) o[n++] = ncube[a][i] - eef[a][i];
+                if (V == IGE_FRANKA_COLLECT) {
+                    const float *bs = body_row(p, b, e, p.base_body_start, p.base_body_step, a);
+#pragma unroll
+                    for (int i = 0; i < 7; ++i) o[n++] = __ldg(bs + i);
+                }
+                for (int s = 1; s < A; ++s) {
+                    const int q = (a + s) % A;
+                    o[n++] = eef[q][0]; o[n++] = eef[q][1]; o[n++] = eef[q][2];
+                }
+                if (V == IGE_FRANKA_COLLECT) { o[n++] = (float)fsm[a]; o[n++] = (float)fsm[a]; }
+            } else {
+                for (int s = 0; s < T; ++s) { const int q = (a + s) % T;
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) o[n++] = cube[q][3 + i]; }
+                for (int s = 0; s < T; ++s) { const int q = (a + s) % T; o[n++] = cube[q][0]; o[n++] = cube[q][1]; o[n++] = cube[q][2]; }
+                const float *aux;
+                if (V == IGE_FRANKA_COMBINE) {
+                    aux = actor_row(p, b, e, p.stack_base_actor);
+                    o[n++] = aux[0]; o[n++] = aux[1]; o[n++] = aux[2];
+                } else {
+                    for (int s = 0; s < T; ++s) {
+                        const float *d = actor_row(p, b, e, p.dest_actor_start + p.dest_actor_step * ((a + s) % T));
+                        o[n++] = d[0]; o[n++] = d[1]; o[n++] = d[2];
+                    }
+                    aux = actor_row(p, b, e, p.dest_actor_start + p.dest_actor_step * a);
+                }
+#pragma unroll
+                for (int i = 0; i < 3; ++i) o[n++] = cube[a][i] - eef[a][i];
+#pragma unroll
+                for (int i = 0; i < 3; ++i) o[n++] = aux[i] - cube[a][i];
+                const float *bs = body_row(p, b, e, p.base_body_start, p.base_body_step, a);
+#pragma unroll
+                for (int i = 0; i < 7; ++i) o[n++] = __ldg(bs + i);
+                for (int s = 0; s < A; ++s) { const int q = (a + s) % A; o[n++] = eef[q][0]; o[n++] = eef[q][1]; o[n++] = eef[q][2]; }
+                for (int s = 0; s < A; ++s) { const int q = (a + s) % A;
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) o[n++] = eef[q][3 + i]; }
+                for (int s = 0; s < A; ++s) o[n++] = pow2_small(fsm[(a + s) % A]);
+                o[n++] = pow2_small(gfsm);
+                if (V == IGE_FRANKA_COMBINE) o[n++] = (a == A - 1) ? 1.0f : 0.0f;  // agent_idx :526-527
+            }
+            // ---- compute_franka_reward ----
+            float rewards;
+            float c10[NC];
+#pragma unroll
+            for (int i = 0; i < NC; ++i) c10[i] = 0.0f;
+            const float alast = __ldg(act + NA - 1);
+            if (V == IGE_FRANKA_REACH) {  // franka_reach_MA.py:928-960
+                const float d = md[a];
+                const float dist_reward = 1.0f / (0.5f + d * d);
+                float av[8];
+                for (int j = 0; j < NA; ++j) av[j] = __ldg(act + j);
+                const float actions_cost = sum_sq_small(av, NA) * 0.01f;
+                rewards = dist_reward - actions_cost;
+                const int distinct = __popc(touched);  // mask.sum(dim=-1), franka_reach_MA.py:944-948
+                const float all_touched = ((float)distinct / (float)A) * 1.0f;
+                const float *cf = b.contact_forces + ((size_t)e * p.num_bodies + p.hand_body_start + p.hand_body_step * a) * 3;
+                const float colliding = (ige::norm3(__ldg(cf), __ldg(cf + 1), __ldg(cf + 2)) >= 0.1f ? 1.0f : 0.0f) * -10.0f;
+                rewards = rewards + (all_touched + colliding);
+            } else {
+                const float m = md[a];
+                const int s = fsm[a];
+                c10[0] = s == 0 ? expf(-5.0f * (m * m)) : 0.0f;
+                c10[1] = s == 1 ? expf(-1.0f * alast) : 0.0f;
+                if (V == IGE_FRANKA_COLLECT) {  // franka_collect_MA.py:1082-1174
+                    const float *hc = ncube[a];
+                    c10[2] = s == 2 ? (hc[2] - 1.05f) / (float)(0.3 + 0.025) : 0.0f;
+                    const float dy = fabsf(hc[1] - (float)(0.3 + 0.05 * 2.));
+                    c10[3] = s == 3 ? expf(-5.0f * (dy * dy)) : 0.0f;
+                    const float dz = fabsf(hc[2] - (float)(0.3 / 2. + 1.05));
+                    c10[4] = s == 4 ? expf(-5.0f * (dz * dz)) : 0.0f;
+                    c10[5] = s == 5 ? expf(4.0f * alast) : 0.0f;
+                    c10[6] = s == 6 ? 1.0f * 3.0f : 0.0f;
+                    c10[7] = (float)s;
+                    rewards = c10[0] + c10[1] + c10[2] + c10[3] + c10[4] + c10[5] + c10[6] + c10[7] + c10[8] + 0.0f;
+                } else if (V == IGE_FRANKA_COMBINE) {  // franka_combine_MA.py:1080-1166
+                    const float *sb = actor_row(p, b, e, p.stack_base_actor);
+                    float lift = fabsf(sb[2] - cube[a][2]) / (float)((0.05 + 0.05) * 0.5);
+                    lift = lift < 0.0f ? 0.0f : (lift > 1.0f ? 1.0f : lift);
+                    c10[2] = s == 2 ? lift : 0.0f;
+                    c10[7] = (float)s;
+                    rewards = c10[0] + c10[1] + c10[7];
+                } else {  // franka_PPMA.py:1082-1167
+                    const float *dest = actor_row(p, b, e, p.dest_actor_start + p.dest_actor_step * a);
+                    const float rx = dest[0] - cube[a][0], ry = dest[1] - cube[a][1], rz = dest[2] - cube[a][2];
+                    float lift = fabsf(rz) / (float)((0.05 + 0.05) * 0.5);
+                    lift = lift < 0.0f ? 0.0f : (lift > 1.0f ? 1.0f : lift);
+                    c10[2] = s == 2 ? lift : 0.0f;
+                    const float dt = ige::norm3(rx + 0.0f, ry + 0.0f, rz + 0.05f);
+                    c10[3] = s == 3 ? expf(-3.0f * dt) : 0.0f;
+                    c10[4] = s == 4 ? expf(-10.0f * dt) : 0.0f;
+                    c10[5] = s == 5 ? expf(5.0f * alast) : 0.0f;
+                    c10[6] = s == 6 ? tanhf(m) : 0.0f;
+                    c10[7] = (float)s;
+                    c10[8] = (float)gfsm * 0.5f;
+                    rewards = c10[0] + c10[1] + c10[2] + c10[3] + c10[4] + c10[5] + c10[6] + c10[7] + c10[8] + c10[9];
+                }
+            }
+            rewards = rewards < 0.0f ? 0.0f : rewards;  // torch.clip(rewards, 0., None)
+#pragma unroll
+            for (int i = 0; i < NC; ++i) comp[i] += c10[i];
+            long long reset = b.reset_buf[row];
+            const long long progress = b.progress_buf[row];
+            const bool late = (float)progress >= p.max_episode_length - 1.0f;
+            if (late) reset = 1;
+            b.rew_buf[row] = rewards;
+            b.reset_buf[row] = reset;
+            const bool timeout = late && reset != 0;  // vec_task.py:396
+            if (b.timeout_buf) b.timeout_buf[row] = timeout ? 1 : 0;
+            st_rew += rewards; st_done += reset != 0 ? 1.f : 0.f; st_to += timeout ? 1.f : 0.f;
+            st_len += reset != 0 ? (float)progress : 0.f;
+        }
+    }
+
+    // ---- observation tile out: one bulk store (or a coalesced loop for ragged tiles) ----
+    const int count = ne * A * NO;
+    const bool bulk = use_tma && (count % 4 == 0);
+    if (bulk) ige::fence_proxy_async();
+    __syncthreads();
+    float *dst = b.obs_buf + (size_t)e0 * A * NO;
+    if (bulk) {
+        if (tid == 0) { ige::bulk_s2g(dst, obs_tile, (uint32_t)count * 4); ige::bulk_commit(); }
+    } else {
+        for (int i = tid; i < count; i += NT) dst[i] = obs_tile[i];
+    }
+    if (b.obs_clamped) {  // vec_task.py:404
+        float *dc = b.obs_clamped + (size_t)e0 * A * NO;
+        for (int i = tid; i < count; i += NT) dc[i] = clampf(obs_tile[i], p.clip_obs);
+    }
+    if (bulk && tid == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+
+    // ---- reward-component sums (the .mean()s of extras) + statistics ----
+#pragma unroll
+    for (int i = 0; i < NC; ++i) comp[i] = ige::warp_sum(comp[i]);
+    if (lane < NC) {
+        float mine = 0.f;
+#pragma unroll
+        for (int i = 0; i < NC; ++i) if (lane == i) mine = comp[i];
+        atomicAdd(b.reduce_scratch + lane, mine);
+        if (b.stats) atomicAdd(b.stats + (blockIdx.x % IGE_STATS_ROWS) * IGE_STATS_STRIDE + IGE_STAT_TASK0 + lane, mine);
+    }
+    if (b.stats) {
+        const float v[5] = {valid ? (float)A : 0.f, st_rew, st_done, st_to, st_len};
+        const int slot[5] = {IGE_STAT_STEPS, IGE_STAT_REWARD, IGE_STAT_DONE, IGE_STAT_TIMEOUT, IGE_STAT_DONE_LENGTH};
+        ige::warp_stats_add<5>(b.stats, v, slot);
+    }
+    if (phase == PH_FUSED && b.list.scratch) ige::finish_reset_list(b.list, N, nullptr, lane == 0);
+    __syncthreads();
+    if (tid == 0) {
+        __threadfence();
+        unsigned *cnt = reinterpret_cast<unsigned *>(b.reduce_scratch + NC);
+        s_last = atomicAdd(cnt, 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (s_last && tid == 0) {
+        __threadfence();
+        const float denom = (float)((long long)N * A);
+        for (int i = 0; i < NC; ++i) {
+            const float s = *reinterpret_cast<volatile float *>(b.reduce_scratch + i);
+            if (b.reward_components) b.reward_components[i] = s / denom;
+            b.reduce_scratch[i] = 0.0f;
+        }
+        b.reduce_scratch[NC] = 0.0f;
+        if (b.list.scratch && p.rand.step) *p.rand.step += 1ull;
+    }
+}
+
+}  // namespace
+
+extern "C" int ige_franka_ma_post_physics(const IgeFrankaMAParams *p, const IgeFrankaMABuffers *b, void *stream) {
+    if (!p || !b) return ige_fail(IGE_ENULL, "params / buffers is NULL");
+    if (p->variant < 0 || p->variant > 3) return ige_fail(IGE_EPARAM, "variant=%d invalid", p->variant);
+    if (p->num_envs < 0) return ige_fail(IGE_ESIZE, "num_envs < 0");
+    if (p->num_agents < 1 || p->num_agents > MAXA || p->num_targets < 1 || p->num_targets > MAXA)
+        return ige_fail(IGE_ESIZE, "num_agents=%d num_targets=%d outside 1..%d", p->num_agents, p->num_targets, MAXA);
+    const bool pair_only = p->variant == IGE_FRANKA_COMBINE || p->variant == IGE_FRANKA_PP;
+    if (pair_only && (p->num_agents != 2 || p->num_targets != 2))
+        return ige_fail(IGE_EPARAM, "Combine / PP need exactly 2 agents and 2 targets");
+    if (!pair_only && p->variant != IGE_FRANKA_REACH && p->num_targets < 1) return ige_fail(IGE_EPARAM, "bad targets");
+    if (p->num_actions < 1 || p->num_actions > 7) return ige_fail(IGE_ESIZE, "num_actions=%d invalid", p->num_actions);
+    if (p->num_dofs != 9 * p->num_agents) return ige_fail(IGE_ESIZE, "num_dofs=%d != 9 * num_agents", p->num_dofs);
+    const int last_eef = p->eef_body_start + p->eef_body_step * (p->num_agents - 1);
+    const int last_base = p->base_body_start + p->base_body_step * (p->num_agents - 1);
+    const int last_hand = p->hand_body_start + p->hand_body_step * (p->num_agents - 1);
+    if (last_eef >= p->num_bodies || last_base >= p->num_bodies || last_hand >= p->num_bodies || p->eef_body_start < 0 ||
+        p->base_body_start < 0 || p->hand_body_start < 0)
+        return ige_fail(IGE_ESIZE, "rigid-body slice outside [0, %d)", p->num_bodies);
+    if (p->cube_actor_start + p->cube_actor_step * (p->num_targets - 1) >= p->num_actors)
+        return ige_fail(IGE_ESIZE, "cube actor slice outside [0, %d)", p->num_actors);
+    IGE_REQUIRE_PTR(b->rigid_body_state);
+    IGE_REQUIRE_PTR(b->root_state);
+    IGE_REQUIRE_PTR(b->dof_state);
+    IGE_REQUIRE_PTR(b->actions);
+    IGE_REQUIRE_PTR(b->pos_control);
+    IGE_REQUIRE_PTR(b->effort_control);
+    IGE_REQUIRE_PTR(b->init_cubeA_state);
+    IGE_REQUIRE_PTR(b->obs_buf);
+    IGE_REQUIRE_PTR(b->rew_buf);
+    IGE_REQUIRE_PTR(b->reset_buf);
+    IGE_REQUIRE_PTR(b->progress_buf);
+    if (p->variant == IGE_FRANKA_REACH) IGE_REQUIRE_PTR(b->contact_forces);
+    if (!b->reduce_scratch) return ige_fail(IGE_ENULL, "reduce_scratch is NULL");
+    IGE_OPTIONAL_PTR(b->obs_clamped);
+    if (int rc = ige_check_list(b->list)) return rc;
+    if (p->rand.mode == IGE_RAND_INJECTED && !p->rand.env_rank) return ige_fail(IGE_ENULL, "rand.env_rank is NULL (INJECTED mode)");
+    if (p->rand.mode != IGE_RAND_INJECTED && p->rand.mode != IGE_RAND_PHILOX) return ige_fail(IGE_EPARAM, "rand.mode invalid");
+    if (p->num_envs == 0) return IGE_OK;
+    const size_t smem = (size_t)TE * p->num_agents * p->num_obs * sizeof(float);
+    if (smem > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(franka_ma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return ige_fail((int)e, "cudaFuncSetAttribute(%zu): %s", smem, cudaGetErrorString(e));
+    }
+    const int grid = (p->num_envs + TE - 1) / TE;
+    cudaStream_t s = (cudaStream_t)stream;
+    if (pair_only) {
+        franka_ma_kernel<<<grid, NT, 0, s>>>(*p, *b, PH_RESET, ige_use_tma());
+        if (int rc = ige_check_launch("ige_franka_ma_post_physics(reset)")) return rc;
+        franka_ma_kernel<<<grid, NT, smem, s>>>(*p, *b, PH_COMPUTE, ige_use_tma());
+    } else {
+        franka_ma_kernel<<<grid, NT, smem, s>>>(*p, *b, PH_FUSED, ige_use_tma());
+    }
+    return ige_check_launch("ige_franka_ma_post_physics");
+}

@@ -27,6 +27,12 @@ def _make_rands(task, ref, rng):
             out["C"] = rng.random((k, 4), dtype=np.float32)
             out["D"] = rng.random((k,), dtype=np.float32)
         return out
+    if task in H.MA_TASKS:
+        flags = (H.get(ref, "reset_buf") != 0)
+        if not flags.any():
+            return []
+        k = int(flags.reshape(-1, ref.num_agents).all(axis=1).sum())
+        return [rng.random(shape, dtype=np.float32) for _, shape in ref.rand_shapes(k)]
     return [rng.random((k, DOFS[task]), dtype=np.float32) for _ in range(2)]
 
 
@@ -35,7 +41,7 @@ def _set_tma(on):
     lib.ige_set_use_tma(C.c_int(1 if on else 0))
 
 
-@pytest.mark.parametrize("task", ["cartpole", "ant", "humanoid", "shadow_hand"])
+@pytest.mark.parametrize("task", ["cartpole", "ant", "humanoid", "shadow_hand"] + H.MA_TASKS)
 def test_cuda_matches_reference_golden(task):
     for path in H.golden_files(task):
         blob = H.load_golden(path)
@@ -64,6 +70,9 @@ def _oracle_vs_cuda(task, n, seed, reset_prob, steps=3, tma=True, rand_mode="inj
                 H.pkg.synthetic.advance_physics(task, cur, phys)
                 if task == "shadow_hand":
                     cur["goal_states"] = H.get(ref, "goal_states")
+                if task in H.MA_TASKS:
+                    for kk in ("cfg_variant", "cfg_num_agents", "cfg_num_targets"):
+                        cur[kk] = st[kk]
                 names = H.pkg.factory.sim_tensor_names(H.TASK_NAME[task]) + (["actions"] if task != "cartpole" else [])
                 for o in (ref, gpu):
                     H.pkg.factory.load_sim_inputs(o, H.TASK_NAME[task], {k: cur[k] for k in names})
@@ -151,6 +160,46 @@ def test_shadow_hand_sim_call_lists():
     np.testing.assert_array_equal(ids[:int(cnt.item())].cpu().numpy(), want)
     ids, cnt = calls["set_dof_state_tensor_indexed"]
     np.testing.assert_array_equal(ids[:int(cnt.item())].cpu().numpy(), st["hand_indices"][env].astype(np.int32))
+
+
+# Franka multi-agent family (BASELINE.json configs[3]: 8192 envs x 2 agents)
+@pytest.mark.parametrize("task", H.MA_TASKS)
+def test_franka_ma_c4_8192x2(task):
+    _oracle_vs_cuda(task, 8192, 0, 0.05)
+
+
+@pytest.mark.parametrize("task", H.MA_TASKS)
+@pytest.mark.parametrize("n", [1, 37, 1000])
+def test_franka_ma_ragged_sizes_and_flags(task, n):
+    _oracle_vs_cuda(task, n, 5, 0.3, steps=2, ragged_flags=True)
+
+
+@pytest.mark.parametrize("task", ["franka_reach", "franka_collect"])
+@pytest.mark.parametrize("agents", [1, 3, 4])
+def test_franka_ma_agent_counts(task, agents):
+    _oracle_vs_cuda(task, 1500, 6, 0.2, steps=2, num_agents=agents)
+
+
+@pytest.mark.parametrize("task", H.MA_TASKS)
+def test_franka_ma_philox_and_full_reset(task):
+    _oracle_vs_cuda(task, 4096, 21, 0.25, steps=3, rand_mode="philox")
+    _oracle_vs_cuda(task, 2048, 9, 1.0, steps=2)
+
+
+def test_franka_ma_sim_call_lists():
+    """Global actor ids handed to gym.set_*_indexed (franka_PPMA.py:813-836)."""
+    st = H.pkg.synthetic.make_state("franka_pp", 3000, seed=4, reset_prob=0.1)
+    gpu = H.build("franka_pp", st, "cuda:0", rand_mode="philox")
+    env = np.flatnonzero((st["reset_buf"] != 0).reshape(-1, 2).all(axis=1))
+    cfg = gpu.cfg
+    gpu.post_physics_step()
+    calls = {name: ids for name, _, ids, _ in gpu.sim.calls}
+    want_f = (env[:, None] * cfg["num_actors"] + np.arange(cfg["franka_actor_start"], cfg["franka_actor_start"] + 2)).reshape(-1)
+    cols = list(range(cfg["cube_actor_start"], cfg["cube_actor_start"] + 2)) + \
+        list(range(cfg["dest_actor_start"], cfg["dest_actor_start"] + 2))
+    want_r = (env[:, None] * cfg["num_actors"] + np.array(cols)).reshape(-1)
+    np.testing.assert_array_equal(calls["set_dof_state_tensor_indexed"].cpu().numpy(), want_f.astype(np.int32))
+    np.testing.assert_array_equal(calls["set_actor_root_state_tensor_indexed"].cpu().numpy(), want_r.astype(np.int32))
 
 
 def test_empty_env_set():
