@@ -33,8 +33,15 @@ import torch  # noqa: E402
 from ige_loader import load_package  # noqa: E402
 
 # frozen algorithmic bytes per env-step (SURVEY.md 8d / BASELINE.md section 2)
-ALGO_BYTES = {"Cartpole": 68, "Ant": 556, "Humanoid": 940}
-ALGO_BYTES_EPILOGUE = {"Cartpole": 85, "Ant": 797, "Humanoid": 1373}
+ALGO_BYTES = {"Cartpole": 68, "Ant": 556, "Humanoid": 940, "ShadowHand": 1732, "FrankaReachMA": 376,
+              "FrankaCollectMA": 488, "FrankaCombineMA": 692, "FrankaPPMA": 720}
+ALGO_BYTES_EPILOGUE = {"Cartpole": 85, "Ant": 797, "Humanoid": 1373, "ShadowHand": 2577, "FrankaReachMA": 530,
+                       "FrankaCollectMA": 714, "FrankaCombineMA": 1078, "FrankaPPMA": 1122}
+KERNEL_NAME = {"Cartpole": "cartpole_post_physics_kernel", "Ant": "locomotion_pipelined_kernel<Ant>",
+               "Humanoid": "locomotion_pipelined_kernel<Humanoid>",
+               "ShadowHand": "shadow_hand_post_physics_kernel (+ shadow_hand_reset_kernel)",
+               "FrankaReachMA": "franka_ma_kernel", "FrankaCollectMA": "franka_ma_kernel",
+               "FrankaCombineMA": "franka_ma_kernel (reset + compute)", "FrankaPPMA": "franka_ma_kernel (reset + compute)"}
 L2_BYTES = 126 * 1024 * 1024
 HORIZON = 16  # cfg/train/AntPPO.yaml:65 horizon_length -> one stats all-reduce per horizon
 
@@ -94,8 +101,8 @@ class ClockSampler:
 def build_replicas(pkg, task, num_envs, replicas, device, seed, fall_frac, fuse_epilogue, rank):
     envs = []
     for r in range(replicas):
-        st = pkg.synthetic.make_state(task.lower(), num_envs, seed=seed + 1000 * rank + r, reset_prob=0.02,
-                                      fall_frac=fall_frac)
+        st = pkg.synthetic.make_state(pkg.factory._SYN_NAME[task], num_envs, seed=seed + 1000 * rank + r,
+                                      reset_prob=0.02, fall_frac=fall_frac)
         env = pkg.factory.from_state(task, st, device, rand_mode="philox", seed=seed + rank,
                                      fuse_epilogue=fuse_epilogue)
         env.sim.record = False
@@ -142,9 +149,9 @@ def run_ours(args):
     lib = pkg._lib
 
     # ---- graphs: chunks of HORIZON consecutive replicas (one stats all-reduce per chunk) ----
-    chunks = [(capture(envs[i:i + HORIZON], lambda e: e.post_physics_step()), HORIZON)
+    chunks = [(capture(envs[i:i + HORIZON], lambda e: e.hot_step()), HORIZON)
               for i in range(0, replicas, HORIZON)]
-    single = [(capture([e], lambda e: e.post_physics_step()), 1) for e in envs[:HORIZON]]
+    single = [(capture([e], lambda e: e.hot_step()), 1) for e in envs[:HORIZON]]
     reducer = pkg.distributed.StatsReducer(device)
 
     def allreduce_stats():
@@ -193,10 +200,7 @@ def run_ours(args):
     gpu_launches = args.steps * kernels_per_step
 
     # ---- dominant kernel alone (roofline): fused kernel only, same rotation, CUDA events ----
-    def kernel_only(e):
-        p, b = e.abi_structs()
-        lib.call(e.ENTRY, p, b, stream=torch.cuda.current_stream().cuda_stream)
-    kgraph = capture(envs, kernel_only)
+    kgraph = capture(envs, lambda e: e.hot_step())
     for _ in range(3):
         kgraph.replay()
     torch.cuda.synchronize()
@@ -216,7 +220,8 @@ def run_ours(args):
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": elapsed / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"{task} post_physics_step num_envs={n} per GPU (BASELINE.json configs[1])",
+        "config": {"workload": f"{task} post_physics_step num_envs={n} per GPU" +
+                               (" (BASELINE.json configs[1])" if task == "Ant" and n == 16384 else ""),
                    "task": task, "num_envs_per_gpu": n, "global_envs": n * world,
                    "parallelism": f"env-shard x{world}", "reset": "natural (2% fallen envs/step), in-kernel Philox",
                    "l2": f"inputs larger than L2: rotating {replicas} state replicas = "
@@ -225,7 +230,7 @@ def run_ours(args):
         "gpu_launches": gpu_launches,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": None, "peak_source": f"MEASURED_PEAKS.json hbm_gbs ({peak_kind})",
-                     "kernel": f"locomotion_pipelined_kernel<{task}>", "kernel_us": kernel_s * 1e6,
+                     "kernel": KERNEL_NAME[task], "kernel_us": kernel_s * 1e6,
                      "algorithmic_bytes_per_env": algo},
     }
     if not args.no_e2e:
@@ -253,10 +258,11 @@ def run_e2e(pkg, args, device, dist=None, world=1):
     tensors + actions from pinned host memory, runs post_physics_step, and reads obs / rew / reset
     back to pinned host memory."""
     task, n = args.task, args.num_envs
-    st = pkg.synthetic.make_state(task.lower(), n, seed=args.seed + 77, reset_prob=0.02, fall_frac=args.fall_frac)
+    st = pkg.synthetic.make_state(pkg.factory._SYN_NAME[task], n, seed=args.seed + 77, reset_prob=0.02,
+                                  fall_frac=args.fall_frac)
     env = pkg.factory.from_state(task, st, device, rand_mode="philox", seed=args.seed, fuse_epilogue=False)
     env.sim.record = False
-    names = pkg.factory.sim_tensor_names(task) + ["actions"]
+    names = pkg.factory.sim_tensor_names(task) + (["actions"] if hasattr(env, "actions") else [])
     dev_in = [env.sim.tensors[k] if k in env.sim.tensors else getattr(env, k) for k in names]
     host_in = [torch.empty(t.shape, dtype=t.dtype).pin_memory().copy_(t.cpu()) for t in dev_in]
     dev_out = [env.obs_buf, env.rew_buf, env.reset_buf]
@@ -267,7 +273,7 @@ def run_e2e(pkg, args, device, dist=None, world=1):
     def step():
         for d, h in zip(dev_in, host_in):
             d.copy_(h, non_blocking=True)
-        env.post_physics_step()
+        env.hot_step()
         for d, h in zip(dev_out, host_out):
             h.copy_(d, non_blocking=True)
 
@@ -293,7 +299,7 @@ def run_e2e(pkg, args, device, dist=None, world=1):
         el = float(t.item())
     return {"value": n * world * steps / el, "unit": "env-steps/s", "h2d_bytes_per_step": h2d,
             "d2h_bytes_per_step": d2h, "ms_per_step": el / steps * 1e3, "wall_ms_per_step": wall / steps * 1e3,
-            "api": "Ant.post_physics_step() (ctypes -> ige_ant_post_physics), pinned host buffers"}
+            "api": f"{task}.post_physics_step() (ctypes -> C ABI), pinned host buffers"}
 
 
 def run_sweep(pkg, args, device, peak):
@@ -305,10 +311,7 @@ def run_sweep(pkg, args, device, peak):
         reps = max(2, min(32, -(-2 * L2_BYTES // per)))
         envs = build_replicas(pkg, task, n, reps, device, args.seed + 5, args.fall_frac, False, 0)
 
-        def kernel_only(e):
-            p, b = e.abi_structs()
-            pkg._lib.call(e.ENTRY, p, b, stream=torch.cuda.current_stream().cuda_stream)
-        g = capture(envs, kernel_only)
+        g = capture(envs, lambda e: e.hot_step())
         for _ in range(3):
             g.replay()
         torch.cuda.synchronize()
@@ -336,13 +339,14 @@ def cpu_baseline(pkg, args, seconds=6.0, steps=None, warmup=3):
     task, n = args.task, args.num_envs
     cores = os.cpu_count() or 1
     oracle.lib().ige_oracle_set_threads(cores)
-    st = pkg.synthetic.make_state(task.lower(), n, seed=args.seed, reset_prob=0.02, fall_frac=args.fall_frac)
-    obj = H.build(task.lower(), st, "cpu", rand_mode="philox", fuse_epilogue=False)
+    syn = pkg.factory._SYN_NAME[task]
+    st = pkg.synthetic.make_state(syn, n, seed=args.seed, reset_prob=0.02, fall_frac=args.fall_frac)
+    obj = H.build(syn, st, "cpu", rand_mode="philox", fuse_epilogue=False)
     for _ in range(warmup):
-        H.oracle_step(task.lower(), obj)
+        H.oracle_step(syn, obj)
     done, t0 = 0, time.perf_counter()
     while True:
-        H.oracle_step(task.lower(), obj)
+        H.oracle_step(syn, obj)
         done += 1
         if steps is not None:
             if done >= steps:

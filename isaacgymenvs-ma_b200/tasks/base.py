@@ -179,6 +179,11 @@ class VecTaskB200:
     def post_physics_step(self):
         raise NotImplementedError
 
+    def hot_step(self):
+        """Exactly the hot path of one control step (what bench.py times): the reset + obs + reward +
+        done work, nothing else.  Tasks that reset in pre-physics position override this."""
+        self.post_physics_step()
+
     # -- vec_task.py:362-410 -------------------------------------------------------------------
     def step(self, actions):
         action_tensor = torch.clamp(actions, -self.clip_actions, self.clip_actions)

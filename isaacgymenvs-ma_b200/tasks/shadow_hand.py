@@ -70,7 +70,12 @@ class ShadowHand(VecTaskB200):
         for k in ("reset_buf", "reset_goal_buf", "progress_buf", "randomize_buf", "actions"):
             getattr(self, k).copy_(torch.from_numpy(st[k]).to(self.device))
         self.shadow_hand_default_dof_pos = torch.zeros(self.num_shadow_hand_dofs, device=self.device)  # :166
-        self._p_cache = None
+        # host copies of the small constant tensors (read once: no D2H inside a step / graph capture)
+        self._consts = dict(
+            fingertips=[int(h) for h in self.fingertip_handles.tolist()],
+            lower=self.shadow_hand_dof_lower_limits.tolist(), upper=self.shadow_hand_dof_upper_limits.tolist(),
+            default_pos=self.shadow_hand_dof_default_pos.tolist(), default_vel=self.shadow_hand_dof_default_vel.tolist(),
+            reset_base=self.shadow_hand_default_dof_pos.tolist())
 
     # ------------------------------------------------------------------------------------------
     def abi_structs(self):
@@ -82,8 +87,9 @@ class ShadowHand(VecTaskB200):
         p.asymmetric_obs = int(self.asymmetric_obs)
         p.ignore_z_rot = int(self.ignore_z)
         p.max_consecutive_successes = self.max_consecutive_successes
-        for i, h in enumerate(self.fingertip_handles.tolist()):
-            p.fingertip_handles[i] = int(h)
+        c = self._consts
+        for i, h in enumerate(c["fingertips"]):
+            p.fingertip_handles[i] = h
         p.max_episode_length = float(self.max_episode_length)
         for k in ("dist_reward_scale", "rot_reward_scale", "rot_eps", "action_penalty_scale", "success_tolerance",
                   "reach_goal_bonus", "fall_dist", "fall_penalty", "av_factor", "vel_obs_scale",
@@ -92,11 +98,11 @@ class ShadowHand(VecTaskB200):
         p.clip_obs = self.clip_obs
         _abi.fill_array(p.goal_displacement, self.goal_displacement)
         _abi.fill_array(p.force_prob_range, self.force_prob_range_f)
-        _abi.fill_array(p.dof_lower, self.shadow_hand_dof_lower_limits.tolist())
-        _abi.fill_array(p.dof_upper, self.shadow_hand_dof_upper_limits.tolist())
-        _abi.fill_array(p.dof_default_pos, self.shadow_hand_dof_default_pos.tolist())
-        _abi.fill_array(p.dof_default_vel, self.shadow_hand_dof_default_vel.tolist())
-        _abi.fill_array(p.dof_reset_base, self.shadow_hand_default_dof_pos.tolist())
+        _abi.fill_array(p.dof_lower, c["lower"])
+        _abi.fill_array(p.dof_upper, c["upper"])
+        _abi.fill_array(p.dof_default_pos, c["default_pos"])
+        _abi.fill_array(p.dof_default_vel, c["default_vel"])
+        _abi.fill_array(p.dof_reset_base, c["reset_base"])
         r = p.rand
         if self.rand_mode == "philox":
             r.mode, r.seed, r.step = _abi.IGE_RAND_PHILOX, self.seed, _ptr(self.rng_step)
@@ -188,6 +194,10 @@ class ShadowHand(VecTaskB200):
             self.cur_targets[:, idx] = torch.max(torch.min(self.cur_targets[:, idx], hi), lo)
         self.prev_targets[:, idx] = self.cur_targets[:, idx]
         self.sim.set_indexed("set_dof_position_target_tensor", self.cur_targets, None, None)
+
+    def hot_step(self):
+        self.reset_resolved()          # pre-physics position (shadow_hand.py:670-682)
+        self.post_physics_step()       # post-physics position (:710-715)
 
     def post_physics_step(self):
         """shadow_hand.py:710-715 as ONE fused kernel."""
