@@ -67,7 +67,7 @@ struct __align__(128) OutTile {
 template <int D>
 struct Handoff {
     float pot[TE], prev[TE], obj[TE];
-    float t0[D * TS], t1[D * TS], t2[D * TS];  // reward terms [dof][env], padded: conflict-free both ways
+    float t2[D * TS];  // joints-at-limit reward term [dof][env] (the one with a division), padded: conflict-free
 };
 
 __device__ __forceinline__ float clampf(float x, float c) { return x < -c ? -c : (x > c ? c : x); }
@@ -224,7 +224,6 @@ __device__ __forceinline__ void role_elem(const IgeLocomotionParams &p, const Ig
             }
             const float4 act = reinterpret_cast<const float4 *>(in.act)[it];
             const float pos[4] = {a.x, a.z, c.x, c.z}, vel[4] = {a.y, a.w, c.y, c.w};
-            const float av[4] = {act.x, act.y, act.z, act.w};
             float ps[4], vs[4];
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
@@ -232,8 +231,6 @@ __device__ __forceinline__ void role_elem(const IgeLocomotionParams &p, const Ig
                 const float lo = p.dof_limits_lower[j], hi = p.dof_limits_upper[j];
                 ps[k] = (2.0f * pos[k] - hi - lo) / (hi - lo);  // unscale torch_jit_utils.py:238-240
                 vs[k] = vel[k] * p.dof_vel_scale;
-                h.t0[j * TS + le] = av[k] * av[k];                // actions ** 2        ant.py:353
-                h.t1[j * TS + le] = fabsf(av[k] * vs[k]);         // |a * dof_vel_obs|   ant.py:354
                 h.t2[j * TS + le] = ps[k] > 0.99f ? 1.0f : 0.0f;  // dof at limit        ant.py:355
             }
             float *o = obs + le * NUM_OBS;
@@ -250,12 +247,20 @@ __device__ __forceinline__ void role_elem(const IgeLocomotionParams &p, const Ig
             reinterpret_cast<float4 *>(obs + le * NUM_OBS + L::O_SENS)[g] = s;
         }
     } else {
-        for (int base = share * 32; base < ne * D; base += stride) {
-            const int it = base + lane;
-            const bool valid = it < ne * D;
-            const int le = valid ? it / D : 0, j = it - le * D;
-            const bool was_reset = __shfl_sync(0xffffffffu, my_flag, le);
-            if (!valid) continue;
+        // Fixed-column mapping: lane L of the ELEM warps owns DOF column j = L % D for the envs
+        // g, g + GROUPS, ... (g = L / D), so every per-DOF constant lives in a register; the lanes left
+        // over (32 * nshares - GROUPS * D) stream the force-sensor columns.
+        const int L = share * 32 + lane, lanes = 32 * nshares;
+        const int groups = lanes / D, sens_lanes = lanes - groups * D;
+        const bool dof_lane = L < groups * D;
+        const int g = dof_lane ? L / D : 0, j = dof_lane ? L - g * D : 0;
+        const float lo = p.dof_limits_lower[j], hi = p.dof_limits_upper[j], den = hi - lo;
+        const float ratio = HUM ? p.motor_effort_ratio[j] : 1.0f;
+        for (int le0 = 0; le0 < TE; le0 += groups) {   // uniform trip count: the shuffle needs the whole warp
+            const int le = le0 + g;
+            const bool was_reset = __shfl_sync(0xffffffffu, my_flag, le & 31);
+            if (!dof_lane || le >= ne) continue;
+            const int it = le * D + j;
             float2 pv = reinterpret_cast<const float2 *>(in.dof)[it];
             if (was_reset) {
                 const int e = e0 + le;
@@ -263,30 +268,31 @@ __device__ __forceinline__ void role_elem(const IgeLocomotionParams &p, const Ig
                                       ige::reset_uniform(p.rand, step, 1, e, D, j));
                 reinterpret_cast<float2 *>(b.dof_state)[(size_t)e0 * D + it] = pv;
             }
-            const float lo = p.dof_limits_lower[j], hi = p.dof_limits_upper[j];
-            const float ps = (2.0f * pv.x - hi - lo) / (hi - lo);
-            const float vs = pv.y * p.dof_vel_scale;
-            const float a = in.act[it];
+            const float ps = (2.0f * pv.x - hi - lo) / den;   // unscale torch_jit_utils.py:238-240
             float *o = obs + le * NUM_OBS;
             o[L::O_DOFPOS + j] = ps;
-            o[L::O_DOFVEL + j] = vs;
-            o[L::O_ACT + j] = a;
-            h.t0[j * TS + le] = a * a;
+            o[L::O_DOFVEL + j] = pv.y * p.dof_vel_scale;
+            o[L::O_ACT + j] = in.act[it];
             if (HUM) {
                 o[L::O_FORCE + j] = in.force[it] * p.contact_force_scale;
-                const float ratio = p.motor_effort_ratio[j];
-                h.t1[j * TS + le] = fabsf(a * vs) * ratio;  // humanoid.py:359
                 const float ap = fabsf(ps);
                 const float scaled = p.joints_at_limit_cost_scale * (ap - 0.98f) / 0.02f;  // humanoid.py:356
                 h.t2[j * TS + le] = (ap > 0.98f ? 1.0f : 0.0f) * scaled * ratio;            // humanoid.py:357
             } else {
-                h.t1[j * TS + le] = fabsf(a * vs);
                 h.t2[j * TS + le] = ps > 0.99f ? 1.0f : 0.0f;
             }
         }
-        for (int it = share * 32 + lane; it < ne * NS; it += stride) {
-            const int le = it / NS, j = it - le * NS;
-            obs[le * NUM_OBS + L::O_SENS + j] = in.sens[it] * p.contact_force_scale;
+        if (sens_lanes > 0) {
+            if (!dof_lane)
+                for (int it = L - groups * D; it < ne * NS; it += sens_lanes) {
+                    const int le = it / NS, c = it - le * NS;
+                    obs[le * NUM_OBS + L::O_SENS + c] = in.sens[it] * p.contact_force_scale;
+                }
+        } else {
+            for (int it = L; it < ne * NS; it += lanes) {
+                const int le = it / NS, c = it - le * NS;
+                obs[le * NUM_OBS + L::O_SENS + c] = in.sens[it] * p.contact_force_scale;
+            }
         }
     }
 }
@@ -297,7 +303,7 @@ struct StatAcc {
 
 // REWARD: reward + termination for env e (ant.py:325-371, humanoid.py:323-375, vec_task.py:396).
 // Writes rew / reset / progress / randomize / time_out straight to global (coalesced per warp).
-template <int D, bool HUM>
+template <int D, int NS, bool HUM>
 __device__ __forceinline__ void role_reward(const IgeLocomotionParams &p, const IgeLocomotionBuffers &b,
                                             const float *obs_row, const Handoff<D> &h, int lane, int e,
                                             long long reset, long long progress, long long randomize, StatAcc &st) {
@@ -306,8 +312,12 @@ __device__ __forceinline__ void role_reward(const IgeLocomotionParams &p, const 
     if (reset != 0) { progress = 0; reset = 0; }  // ant.py:278-279
     const float heading_reward = obs_row[11] > 0.8f ? p.heading_weight : p.heading_weight * obs_row[11] / 0.8f;
     const float up_reward = obs_row[10] > 0.93f ? 0.0f + p.up_weight : 0.0f;
-    const float actions_cost = ige::row_sum<D>([&](int j) { return h.t0[j * TS + lane]; });
-    const float electricity_cost = ige::row_sum<D>([&](int j) { return h.t1[j * TS + lane]; });
+    using L = Layout<D, NS, HUM>;
+    const float actions_cost = ige::row_sum<D>([&](int j) { const float a = obs_row[L::O_ACT + j]; return a * a; });
+    const float electricity_cost = ige::row_sum<D>([&](int j) {
+        const float t = fabsf(obs_row[L::O_ACT + j] * obs_row[L::O_DOFVEL + j]);   // ant.py:354 / humanoid.py:359
+        return HUM ? t * p.motor_effort_ratio[j] : t;
+    });
     const float progress_reward = h.pot[lane] - h.prev[lane];
     float total;
     if (HUM) {
@@ -463,7 +473,7 @@ locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p,
             }
             __syncthreads();  // barrier #it: the role warps have produced tile `it`
             if (lane < tile_ne(it))
-                role_reward<D, HUM>(p, b, out[it & 1].obs + lane * NUM_OBS, hand[it & 1], lane, tile_e0(it) + lane,
+                role_reward<D, NS, HUM>(p, b, out[it & 1].obs + lane * NUM_OBS, hand[it & 1], lane, tile_e0(it) + lane,
                                     reset, progress, randomize, st);
         }
         if (b.stats) flush_stats(b.stats, st);
@@ -642,7 +652,7 @@ locomotion_tile_kernel(const __grid_constant__ IgeLocomotionParams p, const __gr
             if (lane == 0) *b.list.count = base + __popc(mask);
         }
         StatAcc st;
-        if (lane < ne) role_reward<D, HUM>(p, b, obs_row, hand, lane, e0 + lane, reset, progress, randomize, st);
+        if (lane < ne) role_reward<D, NS, HUM>(p, b, obs_row, hand, lane, e0 + lane, reset, progress, randomize, st);
         if (b.stats) flush_stats(b.stats, st);
     }
     coop_copy(b.obs_buf + (size_t)e0 * NUM_OBS, (const float *)out.obs, ne * NUM_OBS);
