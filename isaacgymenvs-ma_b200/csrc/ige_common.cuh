@@ -130,6 +130,19 @@ __device__ __forceinline__ void euler_roll_yaw(const float *q, float &roll, floa
 }
 __device__ __forceinline__ float normalize_angle(float x) { return atan2f(sinf(x), cosf(x)); }
 
+// a / b for a loop-invariant divisor b whose reciprocal y = 1.0f / b (IEEE division) the caller hoisted.
+// Two Markstein corrections (exact fma residual, then refine) make the quotient the correctly rounded
+// a / b for normal-range operands -- bit for bit the `/` of the reference -- in 5 instructions instead
+// of the ~15 + slow-path branch of the division sequence.  tests/test_gpu_parity.py compares the columns
+// computed with it bit-exactly against the oracle's plain `/`.
+__device__ __forceinline__ float div_by(float a, float b, float y) {
+    float q = __fmul_rn(a, y);
+    float r = __fmaf_rn(-b, q, a);
+    q = __fmaf_rn(r, y, q);
+    r = __fmaf_rn(-b, q, a);
+    return __fmaf_rn(r, y, q);
+}
+
 // torch.sum(dim=-1) order of the CPU reference for a row of D < 32 floats held in registers:
 // 8 lanes over the full groups of 8, then the tail, then the lanes (see oracle row_sum()).
 template <int D, typename F>

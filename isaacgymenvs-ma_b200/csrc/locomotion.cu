@@ -188,79 +188,87 @@ __device__ __forceinline__ void reset_uniform4(const IgeResetRand &r, uint64_t s
     }
 }
 
-// ELEM: element-wise columns + reset DOF scatter + per-DOF reward terms; `share` of `nshares` warps.
-// `my_flag` is the reset flag of env (e0 + lane); items fetch their env's flag with a shuffle.
-template <int D, int NS, bool HUM>
+// Per-lane constants of an ELEM lane.  A lane owns FIXED DOF column(s) -- one float4 group (VEC4 layouts)
+// or one column -- for the envs g, g + GROUPS, ... of every tile, so the limits, the hoisted reciprocal of
+// the unscale divisor and the motor-effort ratio live in registers for the whole kernel.
+template <int D, int NS, bool HUM, int NW_ELEM>
+struct ElemLane {
+    static constexpr bool VEC4 = Layout<D, NS, HUM>::VEC4;
+    static constexpr int LANES = 32 * NW_ELEM;
+    static constexpr int G = D / 4;                              // float4 groups per env row (VEC4)
+    static constexpr int GROUPS = VEC4 ? LANES / G : LANES / D;  // envs per pass over the tile
+    static constexpr int K = VEC4 ? 4 : 1;                       // DOF columns per lane
+    static_assert(!VEC4 || LANES % G == 0, "VEC4 mapping needs LANES % (D / 4) == 0");
+    bool active;
+    int g, j;  // first env of the lane, first DOF column
+    float lo[K], hi[K], den[K], rden[K], ratio[K];
+    __device__ __forceinline__ void init(const IgeLocomotionParams &p, int L) {
+        if (VEC4) {
+            active = true; g = L / G; j = (L - g * G) * 4;
+        } else {
+            active = L < GROUPS * D; g = active ? L / D : 0; j = active ? L - g * D : 0;
+        }
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+            lo[k] = p.dof_limits_lower[j + k]; hi[k] = p.dof_limits_upper[j + k];
+            den[k] = hi[k] - lo[k];
+            rden[k] = 1.0f / den[k];
+            ratio[k] = HUM ? p.motor_effort_ratio[j + k] : 1.0f;
+        }
+    }
+};
+
+// ELEM: DOF observation columns (unscaled position, scaled velocity; VEC4 layouts: actions too), the
+// reset_idx DOF scatter for flagged envs and the joints-at-limit reward term.  `my_flag` is the reset flag
+// of env (e0 + lane); items fetch their env's flag with a shuffle.
+template <int D, int NS, bool HUM, int NW_ELEM>
 __device__ __forceinline__ void role_elem(const IgeLocomotionParams &p, const IgeLocomotionBuffers &b,
-                                          const InTile<D, NS, HUM> &in, float *obs, Handoff<D> &h, int lane,
-                                          int share, int nshares, int ne, int e0, uint64_t step, bool my_flag) {
+                                          const InTile<D, NS, HUM> &in, float *obs, Handoff<D> &h,
+                                          const ElemLane<D, NS, HUM, NW_ELEM> &c, int ne, int e0, uint64_t step,
+                                          bool my_flag) {
     using L = Layout<D, NS, HUM>;
+    using EL = ElemLane<D, NS, HUM, NW_ELEM>;
     constexpr int NUM_OBS = L::NUM_OBS;
-    const int stride = 32 * nshares;
-    if (L::VEC4) {
-        constexpr int G = D / 4;
-        for (int base = share * 32; base < ne * G; base += stride) {
-            const int it = base + lane;
-            const bool valid = it < ne * G;
-            const int le = valid ? it / G : 0, g = it - le * G;
-            const bool was_reset = __shfl_sync(0xffffffffu, my_flag, le);
-            if (!valid) continue;
-            float4 a = reinterpret_cast<const float4 *>(in.dof)[it * 2];      // p0 v0 p1 v1
-            float4 c = reinterpret_cast<const float4 *>(in.dof)[it * 2 + 1];  // p2 v2 p3 v3
+    constexpr float kInv002 = 1.0f / 0.02f;
+#pragma unroll
+    for (int le0 = 0; le0 < TE; le0 += EL::GROUPS) {  // uniform trip count: the shuffle needs the whole warp
+        const int le = le0 + c.g;
+        const bool was_reset = __shfl_sync(0xffffffffu, my_flag, le & 31);
+        if (!c.active || le >= ne) continue;
+        float *o = obs + le * NUM_OBS;
+        if (L::VEC4) {
+            const int g = c.j >> 2, it = le * EL::G + g;
+            float4 a = reinterpret_cast<const float4 *>(in.dof)[it * 2];       // p0 v0 p1 v1
+            float4 d = reinterpret_cast<const float4 *>(in.dof)[it * 2 + 1];   // p2 v2 p3 v3
             if (was_reset) {  // reset_idx: rewrite this env's DOF rows (global copy + the values used below)
                 const int e = e0 + le;
                 float up[4], uv[4];
                 reset_uniform4(p.rand, step, 0, e, D, g, up);
                 reset_uniform4(p.rand, step, 1, e, D, g, uv);
-                const float2 r0 = finish_reset_dof(p, b, e, D, g * 4 + 0, up[0], uv[0]);
-                const float2 r1 = finish_reset_dof(p, b, e, D, g * 4 + 1, up[1], uv[1]);
-                const float2 r2 = finish_reset_dof(p, b, e, D, g * 4 + 2, up[2], uv[2]);
-                const float2 r3 = finish_reset_dof(p, b, e, D, g * 4 + 3, up[3], uv[3]);
+                const float2 r0 = finish_reset_dof(p, b, e, D, c.j + 0, up[0], uv[0]);
+                const float2 r1 = finish_reset_dof(p, b, e, D, c.j + 1, up[1], uv[1]);
+                const float2 r2 = finish_reset_dof(p, b, e, D, c.j + 2, up[2], uv[2]);
+                const float2 r3 = finish_reset_dof(p, b, e, D, c.j + 3, up[3], uv[3]);
                 a = make_float4(r0.x, r0.y, r1.x, r1.y);
-                c = make_float4(r2.x, r2.y, r3.x, r3.y);
-                float4 *row = reinterpret_cast<float4 *>(b.dof_state + ((size_t)e * D + g * 4) * 2);
+                d = make_float4(r2.x, r2.y, r3.x, r3.y);
+                float4 *row = reinterpret_cast<float4 *>(b.dof_state + ((size_t)e * D + c.j) * 2);
                 row[0] = a;
-                row[1] = c;
+                row[1] = d;
             }
             const float4 act = reinterpret_cast<const float4 *>(in.act)[it];
-            const float pos[4] = {a.x, a.z, c.x, c.z}, vel[4] = {a.y, a.w, c.y, c.w};
+            const float pos[4] = {a.x, a.z, d.x, d.z}, vel[4] = {a.y, a.w, d.y, d.w};
             float ps[4], vs[4];
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
-                const int j = g * 4 + k;
-                const float lo = p.dof_limits_lower[j], hi = p.dof_limits_upper[j];
-                ps[k] = (2.0f * pos[k] - hi - lo) / (hi - lo);  // unscale torch_jit_utils.py:238-240
+                ps[k] = ige::div_by(2.0f * pos[k] - c.hi[k] - c.lo[k], c.den[k], c.rden[k]);  // unscale torch_jit_utils.py:238-240
                 vs[k] = vel[k] * p.dof_vel_scale;
-                h.t2[j * TS + le] = ps[k] > 0.99f ? 1.0f : 0.0f;  // dof at limit        ant.py:355
+                h.t2[(c.j + k) * TS + le] = ps[k] > 0.99f ? 1.0f : 0.0f;  // dof at limit        ant.py:355
             }
-            float *o = obs + le * NUM_OBS;
             reinterpret_cast<float4 *>(o + L::O_DOFPOS)[g] = make_float4(ps[0], ps[1], ps[2], ps[3]);
             reinterpret_cast<float4 *>(o + L::O_DOFVEL)[g] = make_float4(vs[0], vs[1], vs[2], vs[3]);
             reinterpret_cast<float4 *>(o + L::O_ACT)[g] = act;
-        }
-        constexpr int GS = NS / 4;
-        for (int it = share * 32 + lane; it < ne * GS; it += stride) {
-            const int le = it / GS, g = it - le * GS;
-            float4 s = reinterpret_cast<const float4 *>(in.sens)[it];
-            s.x *= p.contact_force_scale; s.y *= p.contact_force_scale;
-            s.z *= p.contact_force_scale; s.w *= p.contact_force_scale;
-            reinterpret_cast<float4 *>(obs + le * NUM_OBS + L::O_SENS)[g] = s;
-        }
-    } else {
-        // Fixed-column mapping: lane L of the ELEM warps owns DOF column j = L % D for the envs
-        // g, g + GROUPS, ... (g = L / D), so every per-DOF constant lives in a register; the lanes left
-        // over (32 * nshares - GROUPS * D) stream the force-sensor columns.
-        const int L = share * 32 + lane, lanes = 32 * nshares;
-        const int groups = lanes / D, sens_lanes = lanes - groups * D;
-        const bool dof_lane = L < groups * D;
-        const int g = dof_lane ? L / D : 0, j = dof_lane ? L - g * D : 0;
-        const float lo = p.dof_limits_lower[j], hi = p.dof_limits_upper[j], den = hi - lo;
-        const float ratio = HUM ? p.motor_effort_ratio[j] : 1.0f;
-        for (int le0 = 0; le0 < TE; le0 += groups) {   // uniform trip count: the shuffle needs the whole warp
-            const int le = le0 + g;
-            const bool was_reset = __shfl_sync(0xffffffffu, my_flag, le & 31);
-            if (!dof_lane || le >= ne) continue;
-            const int it = le * D + j;
+        } else {
+            const int j = c.j, it = le * D + j;
             float2 pv = reinterpret_cast<const float2 *>(in.dof)[it];
             if (was_reset) {
                 const int e = e0 + le;
@@ -268,31 +276,48 @@ __device__ __forceinline__ void role_elem(const IgeLocomotionParams &p, const Ig
                                       ige::reset_uniform(p.rand, step, 1, e, D, j));
                 reinterpret_cast<float2 *>(b.dof_state)[(size_t)e0 * D + it] = pv;
             }
-            const float ps = (2.0f * pv.x - hi - lo) / den;   // unscale torch_jit_utils.py:238-240
-            float *o = obs + le * NUM_OBS;
+            const float ps = ige::div_by(2.0f * pv.x - c.hi[0] - c.lo[0], c.den[0], c.rden[0]);  // unscale :238-240
             o[L::O_DOFPOS + j] = ps;
             o[L::O_DOFVEL + j] = pv.y * p.dof_vel_scale;
-            o[L::O_ACT + j] = in.act[it];
             if (HUM) {
-                o[L::O_FORCE + j] = in.force[it] * p.contact_force_scale;
                 const float ap = fabsf(ps);
-                const float scaled = p.joints_at_limit_cost_scale * (ap - 0.98f) / 0.02f;  // humanoid.py:356
-                h.t2[j * TS + le] = (ap > 0.98f ? 1.0f : 0.0f) * scaled * ratio;            // humanoid.py:357
+                const float scaled = ige::div_by(p.joints_at_limit_cost_scale * (ap - 0.98f), 0.02f, kInv002);  // humanoid.py:356
+                h.t2[j * TS + le] = (ap > 0.98f ? 1.0f : 0.0f) * scaled * c.ratio[0];                            // humanoid.py:357
             } else {
                 h.t2[j * TS + le] = ps > 0.99f ? 1.0f : 0.0f;
             }
         }
-        if (sens_lanes > 0) {
-            if (!dof_lane)
-                for (int it = L - groups * D; it < ne * NS; it += sens_lanes) {
-                    const int le = it / NS, c = it - le * NS;
-                    obs[le * NUM_OBS + L::O_SENS + c] = in.sens[it] * p.contact_force_scale;
-                }
-        } else {
-            for (int it = L; it < ne * NS; it += lanes) {
-                const int le = it / NS, c = it - le * NS;
-                obs[le * NUM_OBS + L::O_SENS + c] = in.sens[it] * p.contact_force_scale;
-            }
+    }
+}
+
+// STREAM: the observation columns that are a copy / scaling of ONE input element (force sensors, DOF
+// forces, and -- scalar layouts -- the actions).  Shared by the three torso warps, which run their slice
+// after their own short role, so the ELEM warps keep only the division-heavy DOF columns.
+template <int D, int NS, bool HUM>
+__device__ __forceinline__ void stream_columns(const IgeLocomotionParams &p, const InTile<D, NS, HUM> &in, float *obs,
+                                               int part, int nparts, int lane, int ne) {
+    using L = Layout<D, NS, HUM>;
+    constexpr int NUM_OBS = L::NUM_OBS;
+    const int first = part * 32 + lane, stride = 32 * nparts;
+    if (L::VEC4) {
+        constexpr int GS = NS / 4;
+        for (int it = first; it < ne * GS; it += stride) {
+            const int le = it / GS, g = it - le * GS;
+            float4 s = reinterpret_cast<const float4 *>(in.sens)[it];
+            s.x *= p.contact_force_scale; s.y *= p.contact_force_scale;
+            s.z *= p.contact_force_scale; s.w *= p.contact_force_scale;
+            reinterpret_cast<float4 *>(obs + le * NUM_OBS + L::O_SENS)[g] = s;
+        }
+    } else {
+        for (int it = first; it < ne * D; it += stride) {
+            const int le = it / D, j = it - le * D;
+            float *o = obs + le * NUM_OBS;
+            o[L::O_ACT + j] = in.act[it];
+            if (HUM) o[L::O_FORCE + j] = in.force[it] * p.contact_force_scale;
+        }
+        for (int it = first; it < ne * NS; it += stride) {
+            const int le = it / NS, cix = it - le * NS;
+            obs[le * NUM_OBS + L::O_SENS + cix] = in.sens[it] * p.contact_force_scale;
         }
     }
 }
@@ -536,6 +561,8 @@ locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p,
         // reset flag (+ potentials for HEADING) of env (tile, lane), prefetched one tile ahead
         long long n_flag = 0;
         float n_pot = 0.f;
+        ElemLane<D, NS, HUM, NW_ELEM> elem;
+        elem.init(p, role >= ELEM0 ? (role - ELEM0) * 32 + lane : 0);
         if (lane < tile_ne(0)) {
             n_flag = b.reset_buf[tile_e0(0) + lane];
             if (role == HEADING) n_pot = b.potentials[tile_e0(0) + lane];
@@ -561,9 +588,9 @@ locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p,
             } else if (role == ANGLES) {
                 if (lane < ne) role_angles<HUM>(p, root, obs_row);
             } else {
-                role_elem<D, NS, HUM>(p, b, in[s], out[o].obs, hand[o], lane, role - ELEM0, NW_ELEM, ne, e0, step,
-                                      was_reset);
+                role_elem<D, NS, HUM, NW_ELEM>(p, b, in[s], out[o].obs, hand[o], elem, ne, e0, step, was_reset);
             }
+            if (role < REWARD) stream_columns<D, NS, HUM>(p, in[s], out[o].obs, role, 3, lane, ne);
             ige::fence_proxy_async();  // obs tile -> visible to the bulk-store (async) proxy
             // out[o ^ 1] is rewritten right after this barrier: its store (tile it - 1, issued by this
             // same thread one iteration ago) must have finished reading shared memory
@@ -636,8 +663,11 @@ locomotion_tile_kernel(const __grid_constant__ IgeLocomotionParams p, const __gr
     } else if (role == ANGLES) {
         if (lane < ne) role_angles<HUM>(p, root, obs_row);
     } else if (role >= ELEM0) {
-        role_elem<D, NS, HUM>(p, b, in, out.obs, hand, lane, role - ELEM0, NW_ELEM, ne, e0, step, reset != 0);
+        ElemLane<D, NS, HUM, NW_ELEM> elem;
+        elem.init(p, (role - ELEM0) * 32 + lane);
+        role_elem<D, NS, HUM, NW_ELEM>(p, b, in, out.obs, hand, elem, ne, e0, step, reset != 0);
     }
+    if (role < REWARD) stream_columns<D, NS, HUM>(p, in, out.obs, role, 3, lane, ne);
     __syncthreads();
     if (role == REWARD) {
         if (b.list.scratch && emit_mode == EMIT_MASKS) {  // sole kernel of the step: masks, expanded below

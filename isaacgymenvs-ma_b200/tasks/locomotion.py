@@ -54,7 +54,10 @@ class _Locomotion(VecTaskB200):
             c["lo"] = self.dof_limits_lower.tolist()
             c["hi"] = self.dof_limits_upper.tolist()
             if hasattr(self, "motor_efforts"):
-                c["ratio"] = (self.motor_efforts / self.max_motor_effort).tolist()  # humanoid.py:355
+                # humanoid.py:355.  Divided on the host: torch-CUDA turns `tensor / python_float` into a
+                # multiply by the reciprocal (1/3 -> 0.33333331 instead of 0.33333334), which would move
+                # the reward by an ulp against the CPU-pinned reference.
+                c["ratio"] = (self.motor_efforts.detach().cpu() / self.max_motor_effort).tolist()
             self._consts = c
         return self._consts
 
