@@ -37,6 +37,22 @@
 
 namespace {
 
+#ifdef IGE_ROLE_CLOCKS  // debug build only (tools/role_clocks.py): where does each role warp spend its cycles
+__device__ unsigned long long g_role_clk[8][8];
+__device__ __forceinline__ long long clk_now() {
+    long long t;
+    asm volatile("mov.u64 %0, %%clock64;" : "=l"(t)::"memory");
+    return t;
+}
+#define CLK(var) const long long var = clk_now()
+#define CLK_ADD(acc, a, b) acc += (b) - (a)
+#define CLK_FLUSH(role, slot, v) do { if (lane == 0) atomicAdd(&g_role_clk[role][slot], (unsigned long long)(v)); } while (0)
+#else
+#define CLK(var)
+#define CLK_ADD(acc, a, b)
+#define CLK_FLUSH(role, slot, v)
+#endif
+
 constexpr int TE = 32;       // envs per tile == warp size (lane == env for the torso roles)
 constexpr int TS = TE + 1;   // padded stride of the transposed reward-term scratch
 
@@ -70,6 +86,8 @@ struct Handoff {
     float t2[D * TS];  // joints-at-limit reward term [dof][env] (the one with a division), padded: conflict-free
 };
 
+enum Role { HEADING = 0, VELOCITY = 1, ANGLES = 2, REWARD = 3, ELEM0 = 4 };
+
 __device__ __forceinline__ float clampf(float x, float c) { return x < -c ? -c : (x > c ? c : x); }
 
 template <typename T>
@@ -100,12 +118,10 @@ __device__ __forceinline__ float neg_norm_over_dt(const IgeLocomotionParams &p, 
 // potentials / prev_potentials / up_vec / heading_vec rows straight to global (coalesced per warp).
 template <int D, int NUM_OBS>
 __device__ __forceinline__ void role_heading(const IgeLocomotionParams &p, const IgeLocomotionBuffers &b,
-                                             const float *root, bool was_reset, float potentials, int e,
-                                             float *obs_row, Handoff<D> &h, int lane) {
-    if (was_reset) {  // ant.py:273-276
-        const float *init = b.initial_root_states + (size_t)e * 13;
-        potentials = neg_norm_over_dt(p, ige::norm3(p.targets[0] - __ldg(init), p.targets[1] - __ldg(init + 1), 0.0f));
-    }
+                                             const float *root, bool was_reset, float init_x, float init_y,
+                                             float potentials, int e, float *obs_row, Handoff<D> &h, int lane) {
+    if (was_reset)  // ant.py:273-276; (init_x, init_y) = initial_root_states[e, 0:2], prefetched a tile ahead
+        potentials = neg_norm_over_dt(p, ige::norm3(p.targets[0] - init_x, p.targets[1] - init_y, 0.0f));
     // compute_*_observations ant.py:384-391
     const float to_target[3] = {p.targets[0] - root[0], p.targets[1] - root[1], 0.0f};
     float n = ige::norm3(to_target[0], to_target[1], 0.0f);
@@ -164,13 +180,12 @@ __device__ __forceinline__ void role_angles(const IgeLocomotionParams &p, const 
 }
 
 // reset_idx noise for DOF j of env e (ant.py:257-258): torch_rand_float(lo, hi) = (hi - lo) * rand + lo
-__device__ __forceinline__ float2 finish_reset_dof(const IgeLocomotionParams &p, const IgeLocomotionBuffers &b, int e,
-                                                   int d, int j, float u_pos, float u_vel) {
+__device__ __forceinline__ float2 finish_reset_dof(float init_pos, float lo, float hi, float u_pos, float u_vel) {
     const float pos = 0.4f * u_pos + (-0.2f);
     const float vel = 0.2f * u_vel + (-0.1f);
-    float v = __ldg(b.initial_dof_pos + (size_t)e * d + j) + pos;
-    v = fminf(v, p.dof_limits_upper[j]);  // tensor_clamp torch_jit_utils.py:228-230
-    v = fmaxf(v, p.dof_limits_lower[j]);
+    float v = init_pos + pos;
+    v = fminf(v, hi);  // tensor_clamp torch_jit_utils.py:228-230
+    v = fmaxf(v, lo);
     return make_float2(v, vel);  // ant.py:260-261
 }
 // four consecutive uniforms (columns 4g .. 4g+3) of draw `which` for env row `e`: ONE Philox call
@@ -198,7 +213,10 @@ struct ElemLane {
     static constexpr int G = D / 4;                              // float4 groups per env row (VEC4)
     static constexpr int GROUPS = VEC4 ? LANES / G : LANES / D;  // envs per pass over the tile
     static constexpr int K = VEC4 ? 4 : 1;                       // DOF columns per lane
+    static constexpr int P = (TE + GROUPS - 1) / GROUPS;         // passes over a tile
+    static constexpr int NPF = P * K;                            // prefetched reset words per lane (>= 2: HEADING)
     static_assert(!VEC4 || LANES % G == 0, "VEC4 mapping needs LANES % (D / 4) == 0");
+    static_assert(NPF >= 2, "the HEADING warp keeps initial root x / y in the same registers");
     bool active;
     int g, j;  // first env of the lane, first DOF column
     float lo[K], hi[K], den[K], rden[K], ratio[K];
@@ -218,6 +236,38 @@ struct ElemLane {
     }
 };
 
+// Reset-path inputs of one tile, fetched ONE TILE AHEAD so that the (rare, scattered, DRAM-latency) reads of
+// reset_idx never sit on a role's critical path: `mask` is the tile's reset ballot; pf[] holds, per role,
+//   HEADING  pf[0], pf[1] = initial_root_states[e, 0:2] of env `lane`          (ant.py:273)
+//   ELEM     pf[k * K + i] = initial_dof_pos[e_k, j + i], e_k the lane's env of pass k   (ant.py:260)
+template <int D, int NS, bool HUM, int NW_ELEM>
+__device__ __forceinline__ void prefetch_reset(const IgeLocomotionBuffers &b, const ElemLane<D, NS, HUM, NW_ELEM> &c,
+                                               int role, int lane, int e0, uint32_t mask,
+                                               float (&pf)[ElemLane<D, NS, HUM, NW_ELEM>::NPF]) {
+    using EL = ElemLane<D, NS, HUM, NW_ELEM>;
+    if (mask == 0u) return;
+    if (role == HEADING) {
+        if ((mask >> lane) & 1u) {
+            const float *init = b.initial_root_states + (size_t)(e0 + lane) * 13;
+            pf[0] = __ldg(init); pf[1] = __ldg(init + 1);
+        }
+    } else if (role >= ELEM0 && c.active) {
+#pragma unroll
+        for (int k = 0; k < EL::P; ++k) {
+            const int le = k * EL::GROUPS + c.g;
+            if (le < TE && ((mask >> le) & 1u)) {
+                const float *src = b.initial_dof_pos + (size_t)(e0 + le) * D + c.j;
+                if (EL::VEC4) {
+                    const float4 v = __ldg(reinterpret_cast<const float4 *>(src));
+                    pf[k * 4 + 0] = v.x; pf[k * 4 + 1] = v.y; pf[k * 4 + 2] = v.z; pf[k * 4 + 3] = v.w;
+                } else {
+                    pf[k] = __ldg(src);
+                }
+            }
+        }
+    }
+}
+
 // ELEM: DOF observation columns (unscaled position, scaled velocity; VEC4 layouts: actions too), the
 // reset_idx DOF scatter for flagged envs and the joints-at-limit reward term.  `my_flag` is the reset flag
 // of env (e0 + lane); items fetch their env's flag with a shuffle.
@@ -225,16 +275,17 @@ template <int D, int NS, bool HUM, int NW_ELEM>
 __device__ __forceinline__ void role_elem(const IgeLocomotionParams &p, const IgeLocomotionBuffers &b,
                                           const InTile<D, NS, HUM> &in, float *obs, Handoff<D> &h,
                                           const ElemLane<D, NS, HUM, NW_ELEM> &c, int ne, int e0, uint64_t step,
-                                          bool my_flag) {
+                                          uint32_t mask, const float (&pf)[ElemLane<D, NS, HUM, NW_ELEM>::NPF]) {
     using L = Layout<D, NS, HUM>;
     using EL = ElemLane<D, NS, HUM, NW_ELEM>;
     constexpr int NUM_OBS = L::NUM_OBS;
     constexpr float kInv002 = 1.0f / 0.02f;
+    if (!c.active) return;
 #pragma unroll
-    for (int le0 = 0; le0 < TE; le0 += EL::GROUPS) {  // uniform trip count: the shuffle needs the whole warp
-        const int le = le0 + c.g;
-        const bool was_reset = __shfl_sync(0xffffffffu, my_flag, le & 31);
-        if (!c.active || le >= ne) continue;
+    for (int k = 0; k < EL::P; ++k) {
+        const int le = k * EL::GROUPS + c.g;
+        if (le >= ne) continue;
+        const bool was_reset = (mask >> le) & 1u;
         float *o = obs + le * NUM_OBS;
         if (L::VEC4) {
             const int g = c.j >> 2, it = le * EL::G + g;
@@ -245,10 +296,10 @@ __device__ __forceinline__ void role_elem(const IgeLocomotionParams &p, const Ig
                 float up[4], uv[4];
                 reset_uniform4(p.rand, step, 0, e, D, g, up);
                 reset_uniform4(p.rand, step, 1, e, D, g, uv);
-                const float2 r0 = finish_reset_dof(p, b, e, D, c.j + 0, up[0], uv[0]);
-                const float2 r1 = finish_reset_dof(p, b, e, D, c.j + 1, up[1], uv[1]);
-                const float2 r2 = finish_reset_dof(p, b, e, D, c.j + 2, up[2], uv[2]);
-                const float2 r3 = finish_reset_dof(p, b, e, D, c.j + 3, up[3], uv[3]);
+                const float2 r0 = finish_reset_dof(pf[k * EL::K + 0], c.lo[0], c.hi[0], up[0], uv[0]);
+                const float2 r1 = finish_reset_dof(pf[k * EL::K + 1], c.lo[1], c.hi[1], up[1], uv[1]);
+                const float2 r2 = finish_reset_dof(pf[k * EL::K + 2], c.lo[2], c.hi[2], up[2], uv[2]);
+                const float2 r3 = finish_reset_dof(pf[k * EL::K + 3], c.lo[3], c.hi[3], up[3], uv[3]);
                 a = make_float4(r0.x, r0.y, r1.x, r1.y);
                 d = make_float4(r2.x, r2.y, r3.x, r3.y);
                 float4 *row = reinterpret_cast<float4 *>(b.dof_state + ((size_t)e * D + c.j) * 2);
@@ -259,10 +310,10 @@ __device__ __forceinline__ void role_elem(const IgeLocomotionParams &p, const Ig
             const float pos[4] = {a.x, a.z, d.x, d.z}, vel[4] = {a.y, a.w, d.y, d.w};
             float ps[4], vs[4];
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                ps[k] = ige::div_by(2.0f * pos[k] - c.hi[k] - c.lo[k], c.den[k], c.rden[k]);  // unscale torch_jit_utils.py:238-240
-                vs[k] = vel[k] * p.dof_vel_scale;
-                h.t2[(c.j + k) * TS + le] = ps[k] > 0.99f ? 1.0f : 0.0f;  // dof at limit        ant.py:355
+            for (int i = 0; i < 4; ++i) {
+                ps[i] = ige::div_by(2.0f * pos[i] - c.hi[i] - c.lo[i], c.den[i], c.rden[i]);  // unscale torch_jit_utils.py:238-240
+                vs[i] = vel[i] * p.dof_vel_scale;
+                h.t2[(c.j + i) * TS + le] = ps[i] > 0.99f ? 1.0f : 0.0f;  // dof at limit        ant.py:355
             }
             reinterpret_cast<float4 *>(o + L::O_DOFPOS)[g] = make_float4(ps[0], ps[1], ps[2], ps[3]);
             reinterpret_cast<float4 *>(o + L::O_DOFVEL)[g] = make_float4(vs[0], vs[1], vs[2], vs[3]);
@@ -272,7 +323,7 @@ __device__ __forceinline__ void role_elem(const IgeLocomotionParams &p, const Ig
             float2 pv = reinterpret_cast<const float2 *>(in.dof)[it];
             if (was_reset) {
                 const int e = e0 + le;
-                pv = finish_reset_dof(p, b, e, D, j, ige::reset_uniform(p.rand, step, 0, e, D, j),
+                pv = finish_reset_dof(pf[k], c.lo[0], c.hi[0], ige::reset_uniform(p.rand, step, 0, e, D, j),
                                       ige::reset_uniform(p.rand, step, 1, e, D, j));
                 reinterpret_cast<float2 *>(b.dof_state)[(size_t)e0 * D + it] = pv;
             }
@@ -382,7 +433,6 @@ __device__ __forceinline__ void bulk_wait_read() {
     asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
 }
 
-enum Role { HEADING = 0, VELOCITY = 1, ANGLES = 2, REWARD = 3, ELEM0 = 4 };
 enum EmitMode { EMIT_NONE = 0, EMIT_MASKS = 1, EMIT_APPEND = 2 };
 
 // Bulk loads of one tile, split over the lane 0s of the four role warps so they issue in parallel.
@@ -412,7 +462,7 @@ __device__ __forceinline__ void issue_tile_loads(int role, const IgeLocomotionBu
 // has ne % 4 == 0 envs (only the last may be partial).
 // ---------------------------------------------------------------------------------------------
 template <int D, int NS, bool HUM, int NW_ELEM, int IN_STAGES>
-__global__ void __launch_bounds__(32 * (4 + NW_ELEM), HUM ? 3 : 6)  // caps registers: 6 (Ant) / 3 (Humanoid) CTAs per SM
+__global__ void __launch_bounds__(32 * (4 + NW_ELEM), HUM ? 3 : 5)  // shared memory allows 5 (Ant) / 3 (Humanoid) CTAs per SM
 locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p,
                             const __grid_constant__ IgeLocomotionBuffers b, const int num_tiles,
                             const int tiles_per_cta) {
@@ -442,6 +492,7 @@ locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p,
     auto tile_e0 = [&](int it) { return (first + it) * TE; };
     auto tile_ne = [&](int it) { return min(TE, p.num_envs - tile_e0(it)); };
 
+    CLK(kstart);
     if (tid == 0) {
 #pragma unroll
         for (int s = 0; s < IN_STAGES; ++s) ige::mbar_init(&full[s], 1);
@@ -483,6 +534,9 @@ locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p,
             if (lane == 0) sc[2 + blockIdx.x] = (tag << 32) | (uint32_t)cnt;
         }
         StatAcc st;
+        long long k_work = 0, k_bar = 0;
+        (void)k_work; (void)k_bar;
+        CLK(rp);
         for (int it = 0; it < my_tiles; ++it) {
             const long long reset = n_reset, progress = n_progress, randomize = n_rand;
             if (it + 1 < my_tiles && lane < tile_ne(it + 1)) {
@@ -496,11 +550,16 @@ locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p,
                 const uint32_t mask = __ballot_sync(0xffffffffu, reset != 0);
                 if (lane == 0) tile_masks[it] = mask;
             }
+            CLK(r0);
             __syncthreads();  // barrier #it: the role warps have produced tile `it`
+            CLK(r1);
             if (lane < tile_ne(it))
                 role_reward<D, NS, HUM>(p, b, out[it & 1].obs + lane * NUM_OBS, hand[it & 1], lane, tile_e0(it) + lane,
                                     reset, progress, randomize, st);
+            CLK(r2);
+            CLK_ADD(k_bar, r0, r1); CLK_ADD(k_work, r1, r2);
         }
+        CLK(r3);
         if (b.stats) flush_stats(b.stats, st);
         // ---- reset index list, part 2 (last thing this warp does): offset = sum of the predecessor CTAs'
         //      counts, published long ago; then the ascending ids of my tiles ----
@@ -557,45 +616,63 @@ locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p,
                 if (p.rand.step) *p.rand.step += 1ull;
             }
         }
+        CLK(r4);
+        CLK_FLUSH(REWARD, 1, k_work); CLK_FLUSH(REWARD, 2, k_bar); CLK_FLUSH(REWARD, 3, r4 - r3);
+        CLK_FLUSH(REWARD, 0, rp - kstart); CLK_FLUSH(REWARD, 4, r4 - kstart); CLK_FLUSH(REWARD, 7, my_tiles);
     } else {
-        // reset flag (+ potentials for HEADING) of env (tile, lane), prefetched one tile ahead
-        long long n_flag = 0;
-        float n_pot = 0.f;
-        ElemLane<D, NS, HUM, NW_ELEM> elem;
+        // Look-ahead of the small per-env inputs: reset flags two tiles ahead, the reset-path rows
+        // (prefetch_reset) and HEADING's potentials one tile ahead -- all in registers.
+        using EL = ElemLane<D, NS, HUM, NW_ELEM>;
+        EL elem;
         elem.init(p, role >= ELEM0 ? (role - ELEM0) * 32 + lane : 0);
-        if (lane < tile_ne(0)) {
-            n_flag = b.reset_buf[tile_e0(0) + lane];
-            if (role == HEADING) n_pot = b.potentials[tile_e0(0) + lane];
-        }
+        auto load_flag = [&](int t) -> long long {
+            return (role != VELOCITY && role != ANGLES && t < my_tiles && lane < tile_ne(t)) ? b.reset_buf[tile_e0(t) + lane]
+                                                                                             : 0ll;
+        };
+        long long f_next = load_flag(1);
+        float n_pot = 0.f;
+        if (role == HEADING && lane < tile_ne(0)) n_pot = b.potentials[tile_e0(0) + lane];
+        uint32_t m_cur = __ballot_sync(0xffffffffu, load_flag(0) != 0), m_next = 0u;
+        float pf_cur[EL::NPF], pf_next[EL::NPF];
+#pragma unroll
+        for (int i = 0; i < EL::NPF; ++i) pf_cur[i] = pf_next[i] = 0.f;
+        prefetch_reset<D, NS, HUM, NW_ELEM>(b, elem, role, lane, tile_e0(0), m_cur, pf_cur);
+        long long k_load = 0, k_work = 0, k_bar = 0, k_issue = 0;
+        (void)k_load; (void)k_work; (void)k_bar; (void)k_issue;
+        CLK(cbeg);
         for (int it = 0; it < my_tiles; ++it) {
             const int s = it % IN_STAGES, o = it & 1;
             const int e0 = tile_e0(it), ne = tile_ne(it);
-            const bool was_reset = n_flag != 0;
+            const bool was_reset = (m_cur >> lane) & 1u;
             const float pot_in = n_pot;
-            if (it + 1 < my_tiles && lane < tile_ne(it + 1)) {
-                n_flag = b.reset_buf[tile_e0(it + 1) + lane];
-                if (role == HEADING) n_pot = b.potentials[tile_e0(it + 1) + lane];
-            } else {
-                n_flag = 0;
-            }
+            m_next = __ballot_sync(0xffffffffu, f_next != 0);  // tile it + 1 (flags loaded one iteration ago)
+            f_next = load_flag(it + 2);
+            if (role == HEADING && it + 1 < my_tiles && lane < tile_ne(it + 1)) n_pot = b.potentials[tile_e0(it + 1) + lane];
+            if (it + 1 < my_tiles) prefetch_reset<D, NS, HUM, NW_ELEM>(b, elem, role, lane, tile_e0(it + 1), m_next, pf_next);
+            CLK(c0);
             ige::mbar_wait(&full[s], (it / IN_STAGES) & 1);
+            CLK(c1);
             float *obs_row = out[o].obs + lane * NUM_OBS;
             const float *root = in[s].root + lane * 13;
             if (role == HEADING) {
-                if (lane < ne) role_heading<D, NUM_OBS>(p, b, root, was_reset, pot_in, e0 + lane, obs_row, hand[o], lane);
+                if (lane < ne)
+                    role_heading<D, NUM_OBS>(p, b, root, was_reset, pf_cur[0], pf_cur[1], pot_in, e0 + lane, obs_row, hand[o], lane);
             } else if (role == VELOCITY) {
                 if (lane < ne) role_velocity<D, HUM>(p, root, obs_row, hand[o], lane);
             } else if (role == ANGLES) {
                 if (lane < ne) role_angles<HUM>(p, root, obs_row);
             } else {
-                role_elem<D, NS, HUM, NW_ELEM>(p, b, in[s], out[o].obs, hand[o], elem, ne, e0, step, was_reset);
+                role_elem<D, NS, HUM, NW_ELEM>(p, b, in[s], out[o].obs, hand[o], elem, ne, e0, step, m_cur, pf_cur);
             }
             if (role < REWARD) stream_columns<D, NS, HUM>(p, in[s], out[o].obs, role, 3, lane, ne);
             ige::fence_proxy_async();  // obs tile -> visible to the bulk-store (async) proxy
             // out[o ^ 1] is rewritten right after this barrier: its store (tile it - 1, issued by this
             // same thread one iteration ago) must have finished reading shared memory
+            CLK(c2);
             if (role == ELEM0 && lane == 0) bulk_wait_read<0>();
             __syncthreads();  // barrier #it
+            CLK(c3);
+            CLK_ADD(k_load, c0, c1); CLK_ADD(k_work, c1, c2); CLK_ADD(k_bar, c2, c3);
             if (lane == 0) {
                 if (role == ELEM0) {  // tile `it` is complete in out[o]: one bulk store (two with the epilogue copy)
                     ige::bulk_s2g(b.obs_buf + (size_t)e0 * NUM_OBS, out[o].obs, (uint32_t)ne * NUM_OBS * 4);
@@ -612,8 +689,18 @@ locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p,
                 for (int i = (warp > reward_warp ? tid - 32 : tid); i < ne * NUM_OBS; i += 32 * (NW - 1))
                     b.obs_clamped[(size_t)e0 * NUM_OBS + i] = clampf(out[o].obs[i], p.clip_obs);
             }
+            m_cur = m_next;
+#pragma unroll
+            for (int i = 0; i < EL::NPF; ++i) pf_cur[i] = pf_next[i];
+            CLK(c6);
+            CLK_ADD(k_issue, c3, c6);
         }
+        CLK(c4);
         if (role == ELEM0 && lane == 0) bulk_wait_read<0>();  // shared memory must outlive the async reads
+        CLK(c5);
+        CLK_FLUSH(min(role, 4), 0, k_load); CLK_FLUSH(min(role, 4), 1, k_work); CLK_FLUSH(min(role, 4), 2, k_bar);
+        CLK_FLUSH(min(role, 4), 3, c5 - c4); CLK_FLUSH(min(role, 4), 7, my_tiles);
+        CLK_FLUSH(min(role, 4), 4, k_issue); CLK_FLUSH(min(role, 4), 5, c5 - cbeg); CLK_FLUSH(min(role, 4), 6, cbeg - kstart);
     }
 }
 
@@ -656,16 +743,22 @@ locomotion_tile_kernel(const __grid_constant__ IgeLocomotionParams p, const __gr
 
     float *obs_row = out.obs + lane * NUM_OBS;
     const float *root = in.root + lane * 13;
+    using EL = ElemLane<D, NS, HUM, NW_ELEM>;
+    EL elem;
+    elem.init(p, role >= ELEM0 ? (role - ELEM0) * 32 + lane : 0);
+    const uint32_t mask = __ballot_sync(0xffffffffu, reset != 0);
+    float pf[EL::NPF];
+#pragma unroll
+    for (int i = 0; i < EL::NPF; ++i) pf[i] = 0.f;
+    prefetch_reset<D, NS, HUM, NW_ELEM>(b, elem, role, lane, e0, mask, pf);
     if (role == HEADING) {
-        if (lane < ne) role_heading<D, NUM_OBS>(p, b, root, reset != 0, pot_in, e0 + lane, obs_row, hand, lane);
+        if (lane < ne) role_heading<D, NUM_OBS>(p, b, root, reset != 0, pf[0], pf[1], pot_in, e0 + lane, obs_row, hand, lane);
     } else if (role == VELOCITY) {
         if (lane < ne) role_velocity<D, HUM>(p, root, obs_row, hand, lane);
     } else if (role == ANGLES) {
         if (lane < ne) role_angles<HUM>(p, root, obs_row);
     } else if (role >= ELEM0) {
-        ElemLane<D, NS, HUM, NW_ELEM> elem;
-        elem.init(p, (role - ELEM0) * 32 + lane);
-        role_elem<D, NS, HUM, NW_ELEM>(p, b, in, out.obs, hand, elem, ne, e0, step, reset != 0);
+        role_elem<D, NS, HUM, NW_ELEM>(p, b, in, out.obs, hand, elem, ne, e0, step, mask, pf);
     }
     if (role < REWARD) stream_columns<D, NS, HUM>(p, in, out.obs, role, 3, lane, ne);
     __syncthreads();
@@ -780,6 +873,15 @@ int launch(const IgeLocomotionParams *p, const IgeLocomotionBuffers *b, cudaStre
 }
 
 }  // namespace
+
+#ifdef IGE_ROLE_CLOCKS
+extern "C" int ige_debug_role_clocks(unsigned long long *out, int reset) {
+    cudaDeviceSynchronize();
+    if (out) cudaMemcpyFromSymbol(out, g_role_clk, sizeof(unsigned long long) * 64);
+    if (reset) { unsigned long long z[64] = {0}; cudaMemcpyToSymbol(g_role_clk, z, sizeof(z)); }
+    return 0;
+}
+#endif
 
 extern "C" void ige_set_use_tma(int on) { g_use_tma = on ? 1 : 0; }
 extern "C" int ige_use_tma() { return use_tma(); }
