@@ -116,10 +116,23 @@ __device__ __forceinline__ float neg_norm_over_dt(const IgeLocomotionParams &p, 
 // ---------------------------------------------------------------------------------------------
 // HEADING: potentials (+ reset potentials), up / heading vectors, projections.  Writes the final
 // potentials / prev_potentials / up_vec / heading_vec rows straight to global (coalesced per warp).
+// HEADING's per-env global outputs.  They are written AFTER the tile barrier (store_heading): the
+// fence.proxy.async every producer executes before the barrier would otherwise wait for these stores.
+struct HeadingOut {
+    float prev, pot, up[3], hd[3];
+};
+__device__ __forceinline__ void store_heading(const IgeLocomotionBuffers &b, int e, const HeadingOut &r) {
+    b.prev_potentials[e] = r.prev;
+    b.potentials[e] = r.pot;
+    float *up = b.up_vec + (size_t)e * 3, *hd = b.heading_vec + (size_t)e * 3;
+    up[0] = r.up[0]; up[1] = r.up[1]; up[2] = r.up[2];
+    hd[0] = r.hd[0]; hd[1] = r.hd[1]; hd[2] = r.hd[2];
+}
+
 template <int D, int NUM_OBS>
-__device__ __forceinline__ void role_heading(const IgeLocomotionParams &p, const IgeLocomotionBuffers &b,
-                                             const float *root, bool was_reset, float init_x, float init_y,
-                                             float potentials, int e, float *obs_row, Handoff<D> &h, int lane) {
+__device__ __forceinline__ void role_heading(const IgeLocomotionParams &p, const float *root, bool was_reset,
+                                             float init_x, float init_y, float potentials, float *obs_row,
+                                             Handoff<D> &h, int lane, HeadingOut &r) {
     if (was_reset)  // ant.py:273-276; (init_x, init_y) = initial_root_states[e, 0:2], prefetched a tile ahead
         potentials = neg_norm_over_dt(p, ige::norm3(p.targets[0] - init_x, p.targets[1] - init_y, 0.0f));
     // compute_*_observations ant.py:384-391
@@ -128,8 +141,8 @@ __device__ __forceinline__ void role_heading(const IgeLocomotionParams &p, const
     const float new_pot = neg_norm_over_dt(p, n);
     h.prev[lane] = potentials;
     h.pot[lane] = new_pot;
-    b.prev_potentials[e] = potentials;
-    b.potentials[e] = new_pot;
+    r.prev = potentials;
+    r.pot = new_pot;
     // compute_heading_and_up torch_jit_utils.py:247-262
     n = n < 1e-9f ? 1e-9f : n;  // normalize(), torch_jit_utils.py:65-67
     const float target_dirs[3] = {to_target[0] / n, to_target[1] / n, to_target[2] / n};
@@ -139,9 +152,8 @@ __device__ __forceinline__ void role_heading(const IgeLocomotionParams &p, const
     ige::quat_rotate<false>(torso_quat, p.basis_vec0, heading_vec);
     obs_row[10] = up_vec[2];
     obs_row[11] = ige::dot3(heading_vec, target_dirs);
-    float *up = b.up_vec + (size_t)e * 3, *hd = b.heading_vec + (size_t)e * 3;
-    up[0] = up_vec[0]; up[1] = up_vec[1]; up[2] = up_vec[2];
-    hd[0] = heading_vec[0]; hd[1] = heading_vec[1]; hd[2] = heading_vec[2];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) { r.up[i] = up_vec[i]; r.hd[i] = heading_vec[i]; }
 }
 
 template <int D, bool HUM>
@@ -214,9 +226,7 @@ struct ElemLane {
     static constexpr int GROUPS = VEC4 ? LANES / G : LANES / D;  // envs per pass over the tile
     static constexpr int K = VEC4 ? 4 : 1;                       // DOF columns per lane
     static constexpr int P = (TE + GROUPS - 1) / GROUPS;         // passes over a tile
-    static constexpr int NPF = P * K;                            // prefetched reset words per lane (>= 2: HEADING)
     static_assert(!VEC4 || LANES % G == 0, "VEC4 mapping needs LANES % (D / 4) == 0");
-    static_assert(NPF >= 2, "the HEADING warp keeps initial root x / y in the same registers");
     bool active;
     int g, j;  // first env of the lane, first DOF column
     float lo[K], hi[K], den[K], rden[K], ratio[K];
@@ -236,36 +246,50 @@ struct ElemLane {
     }
 };
 
-// Reset-path inputs of one tile, fetched ONE TILE AHEAD so that the (rare, scattered, DRAM-latency) reads of
-// reset_idx never sit on a role's critical path: `mask` is the tile's reset ballot; pf[] holds, per role,
-//   HEADING  pf[0], pf[1] = initial_root_states[e, 0:2] of env `lane`          (ant.py:273)
-//   ELEM     pf[k * K + i] = initial_dof_pos[e_k, j + i], e_k the lane's env of pass k   (ant.py:260)
+// Reset-path inputs of one tile (reset_idx reads them for the few flagged envs: scattered rows, a full DRAM
+// latency each), staged ONE TILE AHEAD in shared memory with cp.async (LDGSTS): no register holds an
+// in-flight load, and the consumer -- the very thread that issued the copy -- only does a wait_group.
+//   xy[le * 2 + {0, 1}] = initial_root_states[e, 0:2]      (HEADING, ant.py:273)
+//   pos[le * D + j]     = initial_dof_pos[e, j]            (ELEM, ant.py:260; same [TE][D] layout as global)
+template <int D>
+struct ResetStage {
+    float xy[TE * 2];
+    float pos[TE * D];
+};
+__device__ __forceinline__ void cp_async4(float *dst_smem, const float *src) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(ige::smem_u32(dst_smem)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async16(float *dst_smem, const float *src) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(ige::smem_u32(dst_smem)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
 template <int D, int NS, bool HUM, int NW_ELEM>
 __device__ __forceinline__ void prefetch_reset(const IgeLocomotionBuffers &b, const ElemLane<D, NS, HUM, NW_ELEM> &c,
-                                               int role, int lane, int e0, uint32_t mask,
-                                               float (&pf)[ElemLane<D, NS, HUM, NW_ELEM>::NPF]) {
+                                               int role, int lane, int e0, uint32_t mask, ResetStage<D> &st) {
     using EL = ElemLane<D, NS, HUM, NW_ELEM>;
-    if (mask == 0u) return;
-    if (role == HEADING) {
-        if ((mask >> lane) & 1u) {
-            const float *init = b.initial_root_states + (size_t)(e0 + lane) * 13;
-            pf[0] = __ldg(init); pf[1] = __ldg(init + 1);
-        }
-    } else if (role >= ELEM0 && c.active) {
+    if (mask != 0u) {
+        if (role == HEADING) {
+            if ((mask >> lane) & 1u) {
+                const float *init = b.initial_root_states + (size_t)(e0 + lane) * 13;
+                cp_async4(st.xy + lane * 2, init);
+                cp_async4(st.xy + lane * 2 + 1, init + 1);
+            }
+        } else if (role >= ELEM0 && c.active) {
 #pragma unroll
-        for (int k = 0; k < EL::P; ++k) {
-            const int le = k * EL::GROUPS + c.g;
-            if (le < TE && ((mask >> le) & 1u)) {
-                const float *src = b.initial_dof_pos + (size_t)(e0 + le) * D + c.j;
-                if (EL::VEC4) {
-                    const float4 v = __ldg(reinterpret_cast<const float4 *>(src));
-                    pf[k * 4 + 0] = v.x; pf[k * 4 + 1] = v.y; pf[k * 4 + 2] = v.z; pf[k * 4 + 3] = v.w;
-                } else {
-                    pf[k] = __ldg(src);
+            for (int k = 0; k < EL::P; ++k) {
+                const int le = k * EL::GROUPS + c.g;
+                if (le < TE && ((mask >> le) & 1u)) {
+                    const float *src = b.initial_dof_pos + (size_t)(e0 + le) * D + c.j;
+                    if (EL::VEC4) cp_async16(st.pos + le * D + c.j, src);
+                    else cp_async4(st.pos + le * D + c.j, src);
                 }
             }
         }
     }
+    cp_async_commit();  // one group per tile, empty or not: wait_group<1> then always means "the previous tile's"
 }
 
 // ELEM: DOF observation columns (unscaled position, scaled velocity; VEC4 layouts: actions too), the
@@ -275,7 +299,7 @@ template <int D, int NS, bool HUM, int NW_ELEM>
 __device__ __forceinline__ void role_elem(const IgeLocomotionParams &p, const IgeLocomotionBuffers &b,
                                           const InTile<D, NS, HUM> &in, float *obs, Handoff<D> &h,
                                           const ElemLane<D, NS, HUM, NW_ELEM> &c, int ne, int e0, uint64_t step,
-                                          uint32_t mask, const float (&pf)[ElemLane<D, NS, HUM, NW_ELEM>::NPF]) {
+                                          uint32_t mask, const float *init_pos /* [TE][D] rows of this tile */) {
     using L = Layout<D, NS, HUM>;
     using EL = ElemLane<D, NS, HUM, NW_ELEM>;
     constexpr int NUM_OBS = L::NUM_OBS;
@@ -294,12 +318,13 @@ __device__ __forceinline__ void role_elem(const IgeLocomotionParams &p, const Ig
             if (was_reset) {  // reset_idx: rewrite this env's DOF rows (global copy + the values used below)
                 const int e = e0 + le;
                 float up[4], uv[4];
+                const float4 ip = *reinterpret_cast<const float4 *>(init_pos + le * D + c.j);
                 reset_uniform4(p.rand, step, 0, e, D, g, up);
                 reset_uniform4(p.rand, step, 1, e, D, g, uv);
-                const float2 r0 = finish_reset_dof(pf[k * EL::K + 0], c.lo[0], c.hi[0], up[0], uv[0]);
-                const float2 r1 = finish_reset_dof(pf[k * EL::K + 1], c.lo[1], c.hi[1], up[1], uv[1]);
-                const float2 r2 = finish_reset_dof(pf[k * EL::K + 2], c.lo[2], c.hi[2], up[2], uv[2]);
-                const float2 r3 = finish_reset_dof(pf[k * EL::K + 3], c.lo[3], c.hi[3], up[3], uv[3]);
+                const float2 r0 = finish_reset_dof(ip.x, c.lo[0], c.hi[0], up[0], uv[0]);
+                const float2 r1 = finish_reset_dof(ip.y, c.lo[1], c.hi[1], up[1], uv[1]);
+                const float2 r2 = finish_reset_dof(ip.z, c.lo[2], c.hi[2], up[2], uv[2]);
+                const float2 r3 = finish_reset_dof(ip.w, c.lo[3], c.hi[3], up[3], uv[3]);
                 a = make_float4(r0.x, r0.y, r1.x, r1.y);
                 d = make_float4(r2.x, r2.y, r3.x, r3.y);
                 float4 *row = reinterpret_cast<float4 *>(b.dof_state + ((size_t)e * D + c.j) * 2);
@@ -323,7 +348,7 @@ __device__ __forceinline__ void role_elem(const IgeLocomotionParams &p, const Ig
             float2 pv = reinterpret_cast<const float2 *>(in.dof)[it];
             if (was_reset) {
                 const int e = e0 + le;
-                pv = finish_reset_dof(pf[k], c.lo[0], c.hi[0], ige::reset_uniform(p.rand, step, 0, e, D, j),
+                pv = finish_reset_dof(init_pos[it], c.lo[0], c.hi[0], ige::reset_uniform(p.rand, step, 0, e, D, j),
                                       ige::reset_uniform(p.rand, step, 1, e, D, j));
                 reinterpret_cast<float2 *>(b.dof_state)[(size_t)e0 * D + it] = pv;
             }
@@ -475,9 +500,10 @@ locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p,
     extern __shared__ __align__(128) unsigned char smem_raw[];
     In *in = reinterpret_cast<In *>(smem_raw);
     Out *out = reinterpret_cast<Out *>(smem_raw + sizeof(In) * IN_STAGES);
+    constexpr size_t kBarBytes = (sizeof(uint64_t) * IN_STAGES + 15) / 16 * 16;
     uint64_t *full = reinterpret_cast<uint64_t *>(smem_raw + sizeof(In) * IN_STAGES + sizeof(Out) * 2);
-    Handoff<D> *hand = reinterpret_cast<Handoff<D> *>(smem_raw + sizeof(In) * IN_STAGES + sizeof(Out) * 2 +
-                                                      sizeof(uint64_t) * IN_STAGES);
+    ResetStage<D> *stage = reinterpret_cast<ResetStage<D> *>(smem_raw + sizeof(In) * IN_STAGES + sizeof(Out) * 2 + kBarBytes);
+    Handoff<D> *hand = reinterpret_cast<Handoff<D> *>(stage + 2);
     uint32_t *tile_masks = reinterpret_cast<uint32_t *>(hand + 2);  // [tiles_per_cta] reset ballots of my tiles
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -621,7 +647,7 @@ locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p,
         CLK_FLUSH(REWARD, 0, rp - kstart); CLK_FLUSH(REWARD, 4, r4 - kstart); CLK_FLUSH(REWARD, 7, my_tiles);
     } else {
         // Look-ahead of the small per-env inputs: reset flags two tiles ahead, the reset-path rows
-        // (prefetch_reset) and HEADING's potentials one tile ahead -- all in registers.
+        // (prefetch_reset, cp.async into stage[]) and HEADING's potentials one tile ahead.
         using EL = ElemLane<D, NS, HUM, NW_ELEM>;
         EL elem;
         elem.init(p, role >= ELEM0 ? (role - ELEM0) * 32 + lane : 0);
@@ -633,10 +659,7 @@ locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p,
         float n_pot = 0.f;
         if (role == HEADING && lane < tile_ne(0)) n_pot = b.potentials[tile_e0(0) + lane];
         uint32_t m_cur = __ballot_sync(0xffffffffu, load_flag(0) != 0), m_next = 0u;
-        float pf_cur[EL::NPF], pf_next[EL::NPF];
-#pragma unroll
-        for (int i = 0; i < EL::NPF; ++i) pf_cur[i] = pf_next[i] = 0.f;
-        prefetch_reset<D, NS, HUM, NW_ELEM>(b, elem, role, lane, tile_e0(0), m_cur, pf_cur);
+        prefetch_reset<D, NS, HUM, NW_ELEM>(b, elem, role, lane, tile_e0(0), m_cur, stage[0]);
         long long k_load = 0, k_work = 0, k_bar = 0, k_issue = 0;
         (void)k_load; (void)k_work; (void)k_bar; (void)k_issue;
         CLK(cbeg);
@@ -648,21 +671,25 @@ locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p,
             m_next = __ballot_sync(0xffffffffu, f_next != 0);  // tile it + 1 (flags loaded one iteration ago)
             f_next = load_flag(it + 2);
             if (role == HEADING && it + 1 < my_tiles && lane < tile_ne(it + 1)) n_pot = b.potentials[tile_e0(it + 1) + lane];
-            if (it + 1 < my_tiles) prefetch_reset<D, NS, HUM, NW_ELEM>(b, elem, role, lane, tile_e0(it + 1), m_next, pf_next);
+            // m_next == 0 past the last tile; stage[(it + 1) & 1] was last read two tiles ago by this same thread
+            prefetch_reset<D, NS, HUM, NW_ELEM>(b, elem, role, lane, tile_e0(it + 1), m_next, stage[(it + 1) & 1]);
+            HeadingOut hout;
             CLK(c0);
             ige::mbar_wait(&full[s], (it / IN_STAGES) & 1);
+            cp_async_wait<1>();  // my staged reset rows of tile `it` (the group of tile it + 1 may still fly)
             CLK(c1);
             float *obs_row = out[o].obs + lane * NUM_OBS;
             const float *root = in[s].root + lane * 13;
             if (role == HEADING) {
                 if (lane < ne)
-                    role_heading<D, NUM_OBS>(p, b, root, was_reset, pf_cur[0], pf_cur[1], pot_in, e0 + lane, obs_row, hand[o], lane);
+                    role_heading<D, NUM_OBS>(p, root, was_reset, stage[o].xy[lane * 2], stage[o].xy[lane * 2 + 1], pot_in,
+                                             obs_row, hand[o], lane, hout);
             } else if (role == VELOCITY) {
                 if (lane < ne) role_velocity<D, HUM>(p, root, obs_row, hand[o], lane);
             } else if (role == ANGLES) {
                 if (lane < ne) role_angles<HUM>(p, root, obs_row);
             } else {
-                role_elem<D, NS, HUM, NW_ELEM>(p, b, in[s], out[o].obs, hand[o], elem, ne, e0, step, m_cur, pf_cur);
+                role_elem<D, NS, HUM, NW_ELEM>(p, b, in[s], out[o].obs, hand[o], elem, ne, e0, step, m_cur, stage[o].pos);
             }
             if (role < REWARD) stream_columns<D, NS, HUM>(p, in[s], out[o].obs, role, 3, lane, ne);
             ige::fence_proxy_async();  // obs tile -> visible to the bulk-store (async) proxy
@@ -673,6 +700,7 @@ locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p,
             __syncthreads();  // barrier #it
             CLK(c3);
             CLK_ADD(k_load, c0, c1); CLK_ADD(k_work, c1, c2); CLK_ADD(k_bar, c2, c3);
+            if (role == HEADING && lane < ne) store_heading(b, e0 + lane, hout);
             if (lane == 0) {
                 if (role == ELEM0) {  // tile `it` is complete in out[o]: one bulk store (two with the epilogue copy)
                     ige::bulk_s2g(b.obs_buf + (size_t)e0 * NUM_OBS, out[o].obs, (uint32_t)ne * NUM_OBS * 4);
@@ -690,8 +718,6 @@ locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p,
                     b.obs_clamped[(size_t)e0 * NUM_OBS + i] = clampf(out[o].obs[i], p.clip_obs);
             }
             m_cur = m_next;
-#pragma unroll
-            for (int i = 0; i < EL::NPF; ++i) pf_cur[i] = pf_next[i];
             CLK(c6);
             CLK_ADD(k_issue, c3, c6);
         }
@@ -747,18 +773,23 @@ locomotion_tile_kernel(const __grid_constant__ IgeLocomotionParams p, const __gr
     EL elem;
     elem.init(p, role >= ELEM0 ? (role - ELEM0) * 32 + lane : 0);
     const uint32_t mask = __ballot_sync(0xffffffffu, reset != 0);
-    float pf[EL::NPF];
-#pragma unroll
-    for (int i = 0; i < EL::NPF; ++i) pf[i] = 0.f;
-    prefetch_reset<D, NS, HUM, NW_ELEM>(b, elem, role, lane, e0, mask, pf);
+    float init_x = 0.f, init_y = 0.f;
+    if (role == HEADING && reset != 0) {
+        init_x = __ldg(b.initial_root_states + (size_t)(e0 + lane) * 13);
+        init_y = __ldg(b.initial_root_states + (size_t)(e0 + lane) * 13 + 1);
+    }
     if (role == HEADING) {
-        if (lane < ne) role_heading<D, NUM_OBS>(p, b, root, reset != 0, pf[0], pf[1], pot_in, e0 + lane, obs_row, hand, lane);
+        if (lane < ne) {
+            HeadingOut hout;
+            role_heading<D, NUM_OBS>(p, root, reset != 0, init_x, init_y, pot_in, obs_row, hand, lane, hout);
+            store_heading(b, e0 + lane, hout);
+        }
     } else if (role == VELOCITY) {
         if (lane < ne) role_velocity<D, HUM>(p, root, obs_row, hand, lane);
     } else if (role == ANGLES) {
         if (lane < ne) role_angles<HUM>(p, root, obs_row);
     } else if (role >= ELEM0) {
-        role_elem<D, NS, HUM, NW_ELEM>(p, b, in, out.obs, hand, elem, ne, e0, step, mask, pf);
+        role_elem<D, NS, HUM, NW_ELEM>(p, b, in, out.obs, hand, elem, ne, e0, step, mask, b.initial_dof_pos + (size_t)e0 * D);
     }
     if (role < REWARD) stream_columns<D, NS, HUM>(p, in, out.obs, role, 3, lane, ne);
     __syncthreads();
@@ -831,7 +862,8 @@ int launch(const IgeLocomotionParams *p, const IgeLocomotionBuffers *b, cudaStre
     constexpr int NUM_OBS = Layout<D, NS, HUM>::NUM_OBS;
     constexpr int kMaxTilesPerCta = 1024;  // per-CTA reset-ballot scratch (4 KB): covers 24 M envs on a B200
     constexpr size_t smem = sizeof(InTile<D, NS, HUM>) * IN_STAGES + sizeof(OutTile<NUM_OBS>) * 2 +
-                            sizeof(Handoff<D>) * 2 + sizeof(uint64_t) * IN_STAGES + sizeof(uint32_t) * kMaxTilesPerCta;
+                            (sizeof(uint64_t) * IN_STAGES + 15) / 16 * 16 + sizeof(ResetStage<D>) * 2 +
+                            sizeof(Handoff<D>) * 2 + sizeof(uint32_t) * kMaxTilesPerCta;
     auto kern = locomotion_pipelined_kernel<D, NS, HUM, NW_ELEM, IN_STAGES>;
     static int max_ctas = 0;  // resident CTAs on the current device (per template instance)
     if (max_ctas == 0) {
