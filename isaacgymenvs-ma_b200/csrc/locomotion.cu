@@ -487,7 +487,7 @@ __device__ __forceinline__ void issue_tile_loads(int role, const IgeLocomotionBu
 // has ne % 4 == 0 envs (only the last may be partial).
 // ---------------------------------------------------------------------------------------------
 template <int D, int NS, bool HUM, int NW_ELEM, int IN_STAGES>
-__global__ void __launch_bounds__(32 * (4 + NW_ELEM), HUM ? 3 : 5)  // shared memory allows 5 (Ant) / 3 (Humanoid) CTAs per SM
+__global__ void __launch_bounds__(32 * (4 + NW_ELEM), HUM ? 3 : 6)  // shared memory allows 6 (Ant) / 3 (Humanoid) CTAs per SM
 locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p,
                             const __grid_constant__ IgeLocomotionBuffers b, const int num_tiles,
                             const int tiles_per_cta) {
@@ -497,6 +497,9 @@ locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p,
     using In = InTile<D, NS, HUM>;
     using Out = OutTile<NUM_OBS>;
 
+#ifdef IGE_ROLE_CLOCKS
+    __shared__ long long dbg_arrive[2][8];
+#endif
     extern __shared__ __align__(128) unsigned char smem_raw[];
     In *in = reinterpret_cast<In *>(smem_raw);
     Out *out = reinterpret_cast<Out *>(smem_raw + sizeof(In) * IN_STAGES);
@@ -504,7 +507,9 @@ locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p,
     uint64_t *full = reinterpret_cast<uint64_t *>(smem_raw + sizeof(In) * IN_STAGES + sizeof(Out) * 2);
     ResetStage<D> *stage = reinterpret_cast<ResetStage<D> *>(smem_raw + sizeof(In) * IN_STAGES + sizeof(Out) * 2 + kBarBytes);
     Handoff<D> *hand = reinterpret_cast<Handoff<D> *>(stage + 2);
-    uint32_t *tile_masks = reinterpret_cast<uint32_t *>(hand + 2);  // [tiles_per_cta] reset ballots of my tiles
+    // reset ballots of my tiles: the mask words of the list scratch (global; written and read back by the
+    // REWARD warp only, so they need no shared memory)
+    uint32_t *tile_masks = b.list.scratch ? b.list.scratch + ige::kListMaskBase + blockIdx.x * tiles_per_cta : nullptr;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int role = (warp + (int)blockIdx.x) % NW;
@@ -560,6 +565,7 @@ locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p,
             if (lane == 0) sc[2 + blockIdx.x] = (tag << 32) | (uint32_t)cnt;
         }
         StatAcc st;
+        uint32_t reg_mask = 0u;  // lane t: reset ballot of my tile t (t < 32)
         long long k_work = 0, k_bar = 0;
         (void)k_work; (void)k_bar;
         CLK(rp);
@@ -574,11 +580,23 @@ locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p,
             }
             if (emit) {
                 const uint32_t mask = __ballot_sync(0xffffffffu, reset != 0);
-                if (lane == 0) tile_masks[it] = mask;
+                if (it < 32) { if (lane == it) reg_mask = mask; }  // the first 32 ballots never leave the warp
+                else if (lane == 0) tile_masks[it] = mask;
             }
             CLK(r0);
             __syncthreads();  // barrier #it: the role warps have produced tile `it`
             CLK(r1);
+#ifdef IGE_ROLE_CLOCKS
+            if (lane == 0) {  // rows 5 / 6 of g_role_clk: [role] = times last to arrive / sum of (last - own arrival)
+                long long last = 0; int who = 0;
+                for (int r = 0; r < NW; ++r) { if (r == REWARD) continue; const long long t = dbg_arrive[it & 1][r]; if (t > last) { last = t; who = r; } }
+                atomicAdd(&g_role_clk[5][min(who, 4)], 1ull);
+                for (int r = 0; r < NW; ++r) { if (r == REWARD) continue; atomicAdd(&g_role_clk[6][min(r, 4)], (unsigned long long)(last - dbg_arrive[it & 1][r])); }
+                atomicAdd(&g_role_clk[5][REWARD], (unsigned long long)(r0 > last ? 1 : 0));          // REWARD arrived last
+                atomicAdd(&g_role_clk[6][REWARD], (unsigned long long)(r0 > last ? r0 - last : 0));  // ... by this much
+                atomicAdd(&g_role_clk[5][7], (unsigned long long)(last > r0 ? last - r0 : 0));       // REWARD idle before the barrier
+            }
+#endif
             if (lane < tile_ne(it))
                 role_reward<D, NS, HUM>(p, b, out[it & 1].obs + lane * NUM_OBS, hand[it & 1], lane, tile_e0(it) + lane,
                                     reset, progress, randomize, st);
@@ -620,7 +638,7 @@ locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p,
             // lane l expands tiles l, l + 32, ...: exclusive scan of the tile counts, then the set bits
             for (int t0 = 0; t0 < my_tiles; t0 += 32) {
                 const int t = t0 + lane;
-                uint32_t m = t < my_tiles ? tile_masks[t] : 0u;
+                uint32_t m = t >= my_tiles ? 0u : (t0 == 0 ? reg_mask : __ldcg(tile_masks + t));
                 const int c = __popc(m);
                 int incl = c;
 #pragma unroll
@@ -696,6 +714,9 @@ locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p,
             // out[o ^ 1] is rewritten right after this barrier: its store (tile it - 1, issued by this
             // same thread one iteration ago) must have finished reading shared memory
             CLK(c2);
+#ifdef IGE_ROLE_CLOCKS
+            if (lane == 0) dbg_arrive[o][min(role, 4) + (role > ELEM0 ? role - ELEM0 : 0)] = c2;
+#endif
             if (role == ELEM0 && lane == 0) bulk_wait_read<0>();
             __syncthreads();  // barrier #it
             CLK(c3);
@@ -860,10 +881,9 @@ template <int D, int NS, bool HUM, int NW_ELEM, int IN_STAGES>
 int launch(const IgeLocomotionParams *p, const IgeLocomotionBuffers *b, cudaStream_t stream, const char *name) {
     constexpr int NT = 32 * (4 + NW_ELEM);
     constexpr int NUM_OBS = Layout<D, NS, HUM>::NUM_OBS;
-    constexpr int kMaxTilesPerCta = 1024;  // per-CTA reset-ballot scratch (4 KB): covers 24 M envs on a B200
     constexpr size_t smem = sizeof(InTile<D, NS, HUM>) * IN_STAGES + sizeof(OutTile<NUM_OBS>) * 2 +
                             (sizeof(uint64_t) * IN_STAGES + 15) / 16 * 16 + sizeof(ResetStage<D>) * 2 +
-                            sizeof(Handoff<D>) * 2 + sizeof(uint32_t) * kMaxTilesPerCta;
+                            sizeof(Handoff<D>) * 2;
     auto kern = locomotion_pipelined_kernel<D, NS, HUM, NW_ELEM, IN_STAGES>;
     static int max_ctas = 0;  // resident CTAs on the current device (per template instance)
     if (max_ctas == 0) {
@@ -891,7 +911,6 @@ int launch(const IgeLocomotionParams *p, const IgeLocomotionBuffers *b, cudaStre
     }
     if (pipelined_tiles > 0) {
         const int per_cta = (pipelined_tiles + max_ctas - 1) / max_ctas;   // contiguous tiles per CTA
-        if (per_cta > kMaxTilesPerCta) return ige_fail(IGE_ESIZE, "%s: num_envs=%d too large for one launch", name, n);
         const int grid = (pipelined_tiles + per_cta - 1) / per_cta;        // <= max_ctas: all CTAs co-resident
         kern<<<grid, NT, smem, stream>>>(*p, *b, pipelined_tiles, per_cta);
         if (int rc = ige_check_launch(name)) return rc;

@@ -53,5 +53,21 @@ def main():
                   f"issue {v[r][4] / tiles:8.0f}  loop-total {v[r][5] / tiles:8.0f}  tiles {tiles}")
 
 
+    # appended by the arrival-time instrumentation
+    return v, names
+
+
+def report_arrivals(v, names):
+    tiles = max(v[3][7], 1)
+    print("  last to arrive at the tile barrier (share of tiles) / mean wait for the last arrival (cycles):")
+    for r, nm in enumerate(names):
+        if nm == "REWARD":
+            print(f"    {nm:9s} last on {100.0 * v[5][r] / tiles:5.1f}% of tiles, late by {v[6][r] / tiles:7.0f} cyc/tile on average; "
+                  f"idle before the barrier {v[5][7] / tiles:7.0f} cyc/tile")
+        else:
+            n = 1 if nm != "ELEM*" else max(1, round(v[4][7] / tiles))
+            print(f"    {nm:9s} last on {100.0 * v[5][r] / tiles:5.1f}% of tiles, waits {v[6][r] / tiles / n:7.0f} cyc/tile")
+
+
 if __name__ == "__main__":
-    main()
+    report_arrivals(*main())
