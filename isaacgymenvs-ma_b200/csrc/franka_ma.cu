@@ -47,60 +47,65 @@ __device__ __forceinline__ float *actor_row(const IgeFrankaMAParams &p, const Ig
     return b.root_state + ((size_t)e * p.num_actors + actor) * 13;
 }
 
-// reset_idx for one env whose agents are all flagged (franka_reach_MA.py:616-704 and siblings)
-__device__ void reset_env(const IgeFrankaMAParams &p, const IgeFrankaMABuffers &b, uint64_t step, int e) {
-    const int A = p.num_agents, T = p.num_targets;
+// reset_idx for one env whose agents are all flagged (franka_reach_MA.py:616-704 and siblings), done by a
+// whole warp: one uniform (one Philox call) per lane, then the rows are written item-parallel.  A single
+// thread doing this serially (~25 Philox calls) used to hold its whole CTA back for microseconds.
+// us[]: per-warp shared scratch (>= 32 floats).  Draw 2 (the z noise of the destination / stack-base cube)
+// is multiplied by 0.0 in the reference (franka_PPMA.py:880), so its value never matters and is not drawn.
+__device__ void reset_env_coop(const IgeFrankaMAParams &p, const IgeFrankaMABuffers &b, uint64_t step, int e, int lane,
+                               float *us) {
+    const int A = p.num_agents, T = p.num_targets, V = p.variant;
     const IgeMAResetRand &r = p.rand;
     const int rk = r.env_rank ? __ldg(r.env_rank + e) : 0;
-    for (int c = 0; c < T; ++c) {  // _reset_init_cube_state
-        float v[13];
-#pragma unroll
-        for (int i = 0; i < 13; ++i) v[i] = 0.0f;
-        v[2] = p.cube_z_base + ma_uniform(r, step, 0, rk, e, T, c) * p.cube_z_range;
-        v[0] = p.cube_xy_center[0] + p.cube_xy_mult * (ma_uniform(r, step, 1, rk, e, T * 2, c * 2 + 0) - 0.5f);
-        v[1] = p.cube_xy_center[1] + p.cube_xy_mult * (ma_uniform(r, step, 1, rk, e, T * 2, c * 2 + 1) - 0.5f);
-        v[6] = 1.0f;
-        float *init = b.init_cubeA_state + ((size_t)e * T + c) * 13;
-        float *cube = actor_row(p, b, e, p.cube_actor_start + p.cube_actor_step * c);
-#pragma unroll
-        for (int i = 0; i < 13; ++i) { init[i] = v[i]; cube[i] = v[i]; }
-    }
-    if (p.variant == IGE_FRANKA_PP) {  // _reset_dest_cube_state franka_PPMA.py:867-895
-        for (int c = 0; c < T; ++c) {
-            float *d = actor_row(p, b, e, p.dest_actor_start + p.dest_actor_step * c);
-#pragma unroll
-            for (int i = 0; i < 13; ++i) d[i] = 0.0f;
-            d[2] = p.aux_z_base + ma_uniform(r, step, 2, rk, e, T, c) * 0.0f;
-            d[0] = p.aux_xy_center_x[c] + p.aux_xy_mult * (ma_uniform(r, step, 3, rk, e, T * 2, c * 2 + 0) - 0.5f);
-            d[1] = p.aux_xy_center_y + p.aux_xy_mult * (ma_uniform(r, step, 3, rk, e, T * 2, c * 2 + 1) - 0.5f);
-            d[6] = 1.0f;
+    const int naux = V == IGE_FRANKA_PP ? T : (V == IGE_FRANKA_COMBINE ? 1 : 0);
+    // uniform table: [0, T) draw 0 | [T, 3T) draw 1 | [3T, 3T + 2 naux) draw 3 | then 9 of draw 4
+    const int o1 = T, o3 = 3 * T, o4 = o3 + 2 * naux, nu = o4 + 9;
+    if (lane < nu) {
+        int draw, cols, j;
+        if (lane < o1) { draw = 0; cols = T; j = lane; }
+        else if (lane < o3) { draw = 1; cols = 2 * T; j = lane - o1; }
+        else if (lane < o4) { draw = 3; cols = 2 * naux; j = lane - o3; }
+        else { draw = 4; cols = 9; j = lane - o4; }
+        float u = ma_uniform(r, step, draw, rk, e, cols, j);
+        if (draw == 4) {  // :638-644: the arm's joint sample (the same one is tiled over the A arms)
+            float v = p.franka_default_dof_pos[j] + p.dof_noise_mult * (u - 0.5f);
+            v = fminf(v, p.franka_dof_upper[j]);
+            v = fmaxf(v, p.franka_dof_lower[j]);
+            u = j >= 7 ? p.franka_default_dof_pos[j] : v;
         }
+        us[lane] = u;
     }
-    if (p.variant == IGE_FRANKA_COMBINE) {  // _reset_stack_base_cube_state franka_combine_MA.py:880-908
-        float *d = actor_row(p, b, e, p.stack_base_actor);
-#pragma unroll
-        for (int i = 0; i < 13; ++i) d[i] = 0.0f;
-        d[2] = p.aux_z_base + ma_uniform(r, step, 2, rk, e, 1, 0) * 0.0f;
-        d[0] = p.aux_xy_center_x[0] + p.aux_xy_mult * (ma_uniform(r, step, 3, rk, e, 2, 0) - 0.5f);
-        d[1] = p.aux_xy_center_y + p.aux_xy_mult * (ma_uniform(r, step, 3, rk, e, 2, 1) - 0.5f);
-        d[6] = 1.0f;
+    __syncwarp();
+    for (int it = lane; it < T * 13; it += 32) {  // _reset_init_cube_state
+        const int c = it / 13, i = it - c * 13;
+        float v = 0.0f;
+        if (i == 0) v = p.cube_xy_center[0] + p.cube_xy_mult * (us[o1 + 2 * c] - 0.5f);
+        else if (i == 1) v = p.cube_xy_center[1] + p.cube_xy_mult * (us[o1 + 2 * c + 1] - 0.5f);
+        else if (i == 2) v = p.cube_z_base + us[c] * p.cube_z_range;
+        else if (i == 6) v = 1.0f;
+        b.init_cubeA_state[((size_t)e * T + c) * 13 + i] = v;
+        actor_row(p, b, e, p.cube_actor_start + p.cube_actor_step * c)[i] = v;
     }
-    float pos[9];
-#pragma unroll
-    for (int j = 0; j < 9; ++j) {  // :638-644
-        float v = p.franka_default_dof_pos[j] + p.dof_noise_mult * (ma_uniform(r, step, 4, rk, e, 9, j) - 0.5f);
-        v = fminf(v, p.franka_dof_upper[j]);
-        v = fmaxf(v, p.franka_dof_lower[j]);
-        pos[j] = j >= 7 ? p.franka_default_dof_pos[j] : v;
+    for (int it = lane; it < naux * 13; it += 32) {  // _reset_dest_cube_state / _reset_stack_base_cube_state
+        const int c = it / 13, i = it - c * 13;
+        float v = 0.0f;
+        if (i == 0) v = p.aux_xy_center_x[c] + p.aux_xy_mult * (us[o3 + 2 * c] - 0.5f);
+        else if (i == 1) v = p.aux_xy_center_y + p.aux_xy_mult * (us[o3 + 2 * c + 1] - 0.5f);
+        else if (i == 2) v = p.aux_z_base + 0.0f;
+        else if (i == 6) v = 1.0f;
+        const int actor = V == IGE_FRANKA_PP ? p.dest_actor_start + p.dest_actor_step * c : p.stack_base_actor;
+        actor_row(p, b, e, actor)[i] = v;
     }
-    for (int a = 0; a < A; ++a)
-#pragma unroll
-        for (int j = 0; j < 9; ++j) {  // :646-656: the same sample tiled over the A arms
-            const size_t k = (size_t)e * p.num_dofs + a * 9 + j;
-            reinterpret_cast<float2 *>(b.dof_state)[k] = make_float2(pos[j], 0.0f);
-            b.pos_control[k] = pos[j];
-            b.effort_control[k] = 0.0f;
-        }
+    for (int it = lane; it < A * 9; it += 32) {  // :646-656
+        const int j = it % 9;
+        const size_t k = (size_t)e * p.num_dofs + it;
+        const float pos = us[o4 + j];
+        reinterpret_cast<float2 *>(b.dof_state)[k] = make_float2(pos, 0.0f);
+        b.pos_control[k] = pos;
+        b.effort_control[k] = 0.0f;
+    }
+    if (lane < A) { b.progress_buf[(size_t)e * A + lane] = 0; b.reset_buf[(size_t)e * A + lane] = 0; }
+    __syncwarp();
 }
 
 __device__ __forceinline__ float pow2_small(int s) { return s >= 0 ? (float)(1 << s) : 0.5f; }  // torch.pow(2.0, FSM)
@@ -122,6 +127,7 @@ __global__ void __launch_bounds__(NT) franka_ma_kernel(const __grid_constant__ I
                                                        const int use_tma) {
     extern __shared__ __align__(128) float obs_tile[];  // TE * A * num_obs
     __shared__ int s_last;
+    __shared__ float s_u[NT / 32][32];
     const int tid = threadIdx.x, lane = tid & 31;
     const int N = p.num_envs, A = p.num_agents, T = p.num_targets, NA = p.num_actions, NO = p.num_obs, V = p.variant;
     const int e0 = blockIdx.x * TE;
@@ -140,15 +146,13 @@ __global__ void __launch_bounds__(NT) franka_ma_kernel(const __grid_constant__ I
             b.progress_buf[row] += 1;
             all &= b.reset_buf[row] != 0;
         }
-        if (all) {
-            reset_env(p, b, step, e);
-            for (int a = 0; a < A; ++a) { b.progress_buf[(size_t)e * A + a] = 0; b.reset_buf[(size_t)e * A + a] = 0; }
-            did_reset = true;
-        }
+        did_reset = all;
     }
-    if (phase != PH_COMPUTE && b.list.scratch) {
+    if (phase != PH_COMPUTE) {
         const uint32_t mask = __ballot_sync(0xffffffffu, did_reset);
-        if (lane == 0 && e < N) ige::publish_tile_mask(b.list, e >> 5, mask);
+        if (b.list.scratch && lane == 0 && e < N) ige::publish_tile_mask(b.list, e >> 5, mask);
+        for (uint32_t m = mask; m; m &= m - 1)  // the warp resets its flagged envs one after the other, together
+            reset_env_coop(p, b, step, e - lane + __ffs(m) - 1, lane, s_u[tid >> 5]);
     }
     if (phase == PH_RESET) {
         if (b.list.scratch) ige::finish_reset_list(b.list, N, nullptr, lane == 0);
