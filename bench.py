@@ -255,13 +255,44 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
+def _time_steps(step, steps, warmup, device, dist):
+    for _ in range(max(3, warmup)):
+        step()
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+    t0 = time.perf_counter()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(steps):
+        step()
+    e1.record()
+    torch.cuda.synchronize()
+    wall = time.perf_counter() - t0
+    el = max(e0.elapsed_time(e1) * 1e-3, 0.0)
+    if dist is not None:
+        t = torch.tensor([el, wall], device=device, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        el, wall = float(t[0].item()), float(t[1].item())
+    return el, wall
+
+
+def _nbytes(ts):
+    return sum(t.numel() * t.element_size() for t in ts)
+
+
 def run_e2e(pkg, args, device, dist=None, world=1):
-    """Same metric through the public API with HOST buffers: every step copies the simulator
-    tensors + actions from pinned host memory, runs post_physics_step, and reads obs / rew / reset
-    back to pinned host memory."""
+    """Same metric through the public API with HOST buffers (the reference's sim_device=cpu pipeline=cpu
+    situation): every step the simulator tensors + actions start in pinned host memory and obs / rew /
+    reset end in pinned host memory.  Two ways to get them across PCIe, both timed, the faster reported:
+      staged : cudaMemcpyAsync H2D of every input, the fused kernel, cudaMemcpyAsync D2H of the results;
+      mapped : env.map_host_sim() -- the fused kernel itself streams the pinned host tensors in and the
+               results out (reads and writes overlap on the duplex link, one launch, no staging pass)."""
     task, n = args.task, args.num_envs
-    st = pkg.synthetic.make_state(pkg.factory._SYN_NAME[task], n, seed=args.seed + 77, reset_prob=0.02,
-                                  fall_frac=args.fall_frac)
+    syn = pkg.factory._SYN_NAME[task]
+    res = {}
+    # ---- staged copies ----
+    st = pkg.synthetic.make_state(syn, n, seed=args.seed + 77, reset_prob=0.02, fall_frac=args.fall_frac)
     env = pkg.factory.from_state(task, st, device, rand_mode="philox", seed=args.seed, fuse_epilogue=False)
     env.sim.record = False
     names = pkg.factory.sim_tensor_names(task) + (["actions"] if hasattr(env, "actions") else [])
@@ -269,39 +300,50 @@ def run_e2e(pkg, args, device, dist=None, world=1):
     host_in = [torch.empty(t.shape, dtype=t.dtype).pin_memory().copy_(t.cpu()) for t in dev_in]
     dev_out = [env.obs_buf, env.rew_buf, env.reset_buf]
     host_out = [torch.empty(t.shape, dtype=t.dtype).pin_memory() for t in dev_out]
-    h2d = sum(t.numel() * t.element_size() for t in host_in)
-    d2h = sum(t.numel() * t.element_size() for t in host_out)
 
-    def step():
+    def step_staged():
         for d, h in zip(dev_in, host_in):
             d.copy_(h, non_blocking=True)
         env.hot_step()
         for d, h in zip(dev_out, host_out):
             h.copy_(d, non_blocking=True)
 
-    for _ in range(max(3, args.warmup)):
-        step()
-    torch.cuda.synchronize()
-    if dist is not None:
-        dist.barrier()
-    steps = args.steps
-    t0 = time.perf_counter()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(steps):
-        step()
-    e1.record()
-    torch.cuda.synchronize()
-    wall = time.perf_counter() - t0
-    el = max(e0.elapsed_time(e1) * 1e-3, 0.0)
-    el = max(el, wall * 0.0 + el)
-    if dist is not None:
-        t = torch.tensor([el], device=device, dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        el = float(t.item())
-    return {"value": n * world * steps / el, "unit": "env-steps/s", "h2d_bytes_per_step": h2d,
-            "d2h_bytes_per_step": d2h, "ms_per_step": el / steps * 1e3, "wall_ms_per_step": wall / steps * 1e3,
-            "api": f"{task}.post_physics_step() (ctypes -> C ABI), pinned host buffers"}
+    el, wall = _time_steps(step_staged, args.steps, args.warmup, device, dist)
+    res["staged"] = {"value": n * world * args.steps / el, "ms_per_step": el / args.steps * 1e3,
+                     "wall_ms_per_step": wall / args.steps * 1e3, "h2d_bytes_per_step": _nbytes(host_in),
+                     "d2h_bytes_per_step": _nbytes(host_out)}
+    del env
+    # ---- mapped: rotating host-resident replicas so no step re-reads lines a previous step left in L2 ----
+    if hasattr(pkg.tasks.task_map[task], "HOST_SIM_ATTRS") and pkg.tasks.task_map[task].HOST_SIM_ATTRS:
+        reps = 8
+        envs, h2d, d2h = [], 0, 0
+        for r in range(reps):
+            st = pkg.synthetic.make_state(syn, n, seed=args.seed + 177 + r, reset_prob=0.02, fall_frac=args.fall_frac)
+            e = pkg.factory.from_state(task, st, device, rand_mode="philox", seed=args.seed, fuse_epilogue=False)
+            e.sim.record = False
+            moved = e.map_host_sim()
+            h2d = _nbytes([moved[k] for k in moved if k not in ("obs_buf", "rew_buf")])  # reset_buf is read too
+            d2h = _nbytes([moved[k] for k in ("obs_buf", "rew_buf", "reset_buf")])
+            envs.append(e)
+        it = [0]
+
+        def step_mapped():
+            envs[it[0] % reps].hot_step()
+            it[0] += 1
+
+        el, wall = _time_steps(step_mapped, args.steps, args.warmup, device, dist)
+        ok = all(bool(torch.isfinite(e.obs_buf).all()) and float(e.obs_buf.abs().sum()) > 0 for e in envs)
+        res["mapped"] = {"value": n * world * args.steps / el, "ms_per_step": el / args.steps * 1e3,
+                         "wall_ms_per_step": wall / args.steps * 1e3, "h2d_bytes_per_step": h2d,
+                         "d2h_bytes_per_step": d2h, "results_on_host_ok": ok}
+        del envs
+    best = max(res, key=lambda k: res[k]["value"])
+    out = dict(res[best])
+    out.update({"unit": "env-steps/s", "mode": best, "modes": res,
+                "api": f"{task}.post_physics_step() (ctypes -> C ABI), pinned host buffers; "
+                       + ("map_host_sim(): the kernel reads/writes pinned host memory over PCIe"
+                          if best == "mapped" else "cudaMemcpyAsync H2D + kernel + D2H")})
+    return out
 
 
 def run_sweep(pkg, args, device, peak):

@@ -369,6 +369,9 @@ uint64_t ige_launch_count(void);
 /* Debug knob: 0 = stage tiles with plain coalesced loads/stores instead of TMA bulk copies
  * (also settable with the environment variable IGE_NO_TMA=1).  Results are identical. */
 void ige_set_use_tma(int on);
+/* Debug knob: 0 = take the generic any-shape kernels instead of the shape-specialised fast paths (ShadowHand with
+ * 24 DOFs / 20 actions, Franka MA with 2 agents / 2 targets); also IGE_GENERIC=1.  Results are identical. */
+void ige_set_fast_paths(int on);
 
 #ifdef __cplusplus
 }

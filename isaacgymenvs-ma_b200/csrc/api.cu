@@ -2,6 +2,7 @@
 #include <atomic>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 
 #include "ige_common.cuh"
 
@@ -28,3 +29,15 @@ int ige_check_launch(const char *what) {
 extern "C" int ige_version(void) { return IGE_ABI_VERSION; }
 extern "C" const char *ige_last_error_string(void) { return g_err; }
 extern "C" uint64_t ige_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+
+// Debug knob: 0 = always take the generic (any-shape) kernels instead of the shape-specialised fast paths
+// (ShadowHand 24/20, Franka MA pairs).  Also IGE_GENERIC=1.  Results are identical; tests run both.
+static int g_fast_paths = -1;
+extern "C" void ige_set_fast_paths(int on) { g_fast_paths = on ? 1 : 0; }
+extern "C" int ige_fast_paths() {
+    if (g_fast_paths < 0) {
+        const char *e = getenv("IGE_GENERIC");
+        g_fast_paths = (e && e[0] == '1') ? 0 : 1;
+    }
+    return g_fast_paths;
+}

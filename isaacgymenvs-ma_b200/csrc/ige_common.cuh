@@ -16,6 +16,7 @@ int ige_fail(int code, const char *fmt, ...);
 void ige_count_launch();
 int ige_check_launch(const char *what);
 extern "C" int ige_use_tma();  // 1 unless IGE_NO_TMA=1 / ige_set_use_tma(0)
+extern "C" int ige_fast_paths();  // 1 unless IGE_GENERIC=1 / ige_set_fast_paths(0)
 
 #define IGE_REQUIRE_PTR(ptr)                                                       \
     do {                                                                           \

@@ -38,7 +38,7 @@ __constant__ SegEntry kLayout[4][12] = {
     {{SEG_DOF_POS, 0}, {SEG_DOF_VEL, 24}, {SEG_DOF_FORCE, 48}, {SEG_OBJ_POSE, 72}, {SEG_OBJ_LINVEL, 79},
      {SEG_OBJ_ANGVEL, 82}, {SEG_GOAL_POSE, 85}, {SEG_QUAT_DIFF, 92}, {SEG_FT_STATE, 96}, {SEG_SENSORS, 161},
      {SEG_ACTIONS, 191}, {SEG_END, 211}}};
-__host__ __device__ inline int hand_num_obs(int type) { return type == 0 ? 42 : type == 1 ? 77 : type == 2 ? 157 : 211; }
+__host__ __device__ constexpr int hand_num_obs(int type) { return type == 0 ? 42 : type == 1 ? 77 : type == 2 ? 157 : 211; }
 
 __device__ __forceinline__ float clampf(float x, float c) { return x < -c ? -c : (x > c ? c : x); }
 
@@ -245,16 +245,40 @@ __device__ __forceinline__ void store_tile(float *dst, float *dst_clamped, const
         for (int i = threadIdx.x; i < count; i += NT) dst_clamped[i] = clampf(tile[i], clip);
 }
 
+// Called by every thread of every CTA (of all launches of one step) after its partial sums were added to
+// reduce_scratch: the CTA that arrives last (`expected_ctas` arrivals) finishes compute_hand_reward's global
+// part -- consecutive_successes (:795-798) --, re-arms the scratch and advances the Philox step.
+__device__ __forceinline__ void finish_hand_reduction(const IgeShadowHandParams &p, const IgeShadowHandBuffers &b,
+                                                      int expected_ctas, int *s_last) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        *s_last = atomicAdd(b.reduce_scratch + 1, 1u) == (unsigned)expected_ctas - 1u;
+    }
+    __syncthreads();
+    if (*s_last && threadIdx.x == 0) {
+        __threadfence();
+        const unsigned num_resets = *reinterpret_cast<volatile unsigned *>(b.reduce_scratch + 0);
+        const float finished = *reinterpret_cast<volatile float *>(b.reduce_scratch + 2);
+        if (num_resets > 0)
+            b.consecutive_successes[0] = p.av_factor * finished / (float)num_resets +
+                                         (float)(1.0 - (double)p.av_factor) * b.consecutive_successes[0];
+        b.reduce_scratch[0] = 0u; b.reduce_scratch[1] = 0u; b.reduce_scratch[2] = 0u;
+        if (b.list.scratch && p.rand.step) *p.rand.step += 1ull;
+    }
+}
+
 __global__ void __launch_bounds__(NT) shadow_hand_post_physics_kernel(const __grid_constant__ IgeShadowHandParams p,
                                                                       const __grid_constant__ IgeShadowHandBuffers b,
-                                                                      const int use_tma) {
+                                                                      const int use_tma, const int tile0,
+                                                                      const int expected_ctas) {
     extern __shared__ __align__(128) float smem[];
     const int nobs = hand_num_obs(p.obs_type);
     float *obs_tile = smem;                                             // TE * nobs
     float *st_tile = smem + ((TE * nobs + 31) / 32) * 32;               // TE * 211 when asymmetric
     __shared__ int s_last;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int e0 = blockIdx.x * TE;
+    const int e0 = (tile0 + blockIdx.x) * TE;
     const int ne = min(TE, p.num_envs - e0);
     const bool bulk = use_tma && (ne % 4 == 0);
 
@@ -355,23 +379,285 @@ __global__ void __launch_bounds__(NT) shadow_hand_post_physics_kernel(const __gr
                    st_tile, ne * MAX_OBS, p.clip_obs, bulk);
     if (bulk && tid == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
 
-    // ---- last CTA: consecutive_successes (:798), re-arm the scratch, advance the Philox step ----
-    __syncthreads();
-    if (tid == 0) {
-        __threadfence();
-        s_last = atomicAdd(b.reduce_scratch + 1, 1u) == gridDim.x - 1;
+    finish_hand_reduction(p, b, expected_ctas, &s_last);
+}
+
+// ---------------------------------------------------------------------------------------------
+// post-physics, standard hand (24 DOFs == DOFs per env, 20 actions, 5 fingertips x 6 sensor floats):
+// persistent CTAs over 32-env tiles, every global load of a tile issued before the first use.
+// ---------------------------------------------------------------------------------------------
+// The generic kernel above walks the layout segment by segment (one DRAM round trip per segment,
+// runtime divisions); here the element -> (env, column) maps are compile-time, each thread first
+// issues ALL of its loads for the tile (3 float2 DOF rows, one float4 each of dof_force / sensors /
+// actions, <= 9 fingertip floats; warp 0 also the object / goal rows and the flags of its env) and
+// only then scatters them into the shared (32 x num_obs) tile, so a tile costs two dependent DRAM
+// round trips (object_indices -> object row is the second) instead of ~12.  Per-CTA partial sums stay in
+// registers across tiles: 3 global atomics per CTA, not per tile.
+constexpr int FD = 24, FA = 20, FS = 30, FT_N = 5;
+constexpr int kFastCtasPerSm = 2;
+constexpr int FNT = 512;       // threads per CTA of the fast kernel
+constexpr int CT = FNT - 32;   // element threads (warp 0 is the env warp)
+constexpr int KD = (TE * FD + CT - 1) / CT, KS = (TE * FS / 4 + CT - 1) / CT, KF = (TE * 65 + CT - 1) / CT,
+              KP = (TE * 15 + CT - 1) / CT;   // loads per element thread: DOF rows, sensor vectors, fingertip floats
+static_assert(TE * FD / 4 <= CT && TE * FA / 4 <= CT && KS <= 2, "fast kernel: one vector per thread for force / actions");
+struct SegOff { int dof_pos, dof_vel, dof_force, ft_state, ft_pos, sensors, actions; };
+// element-segment offsets of the four layouts (shadow_hand.py:473-584; same numbers as kLayout), compile-time
+__host__ __device__ constexpr SegOff seg_offsets(int layout) {
+    return layout == 0 ? SegOff{-1, -1, -1, -1, 0, -1, 22}
+         : layout == 1 ? SegOff{0, -1, -1, -1, 42, -1, 57}
+         : layout == 2 ? SegOff{0, 24, -1, 72, -1, -1, 137}
+                       : SegOff{0, 24, 48, 96, -1, 161, 191};
+}
+
+template <int LAYOUT, bool ASYM>
+__global__ void __launch_bounds__(FNT, kFastCtasPerSm)
+shadow_hand_post_physics_fast_kernel(const __grid_constant__ IgeShadowHandParams p,
+                                     const __grid_constant__ IgeShadowHandBuffers b, const int num_tiles,
+                                     const int expected_ctas) {
+    extern __shared__ __align__(128) float smem[];
+    constexpr int nobs = hand_num_obs(LAYOUT);
+    float *obs_tile = smem;                                   // TE * nobs
+    float *st_tile = smem + ((TE * nobs + 31) / 32) * 32;     // TE * 211 when asymmetric
+    __shared__ int s_last;
+    __shared__ float s_lo[FD], s_hi[FD], s_rspan[FD];
+    __shared__ int s_ft[FT_N];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    constexpr bool asym = ASYM;
+    constexpr SegOff oo = seg_offsets(LAYOUT);
+    constexpr SegOff so = seg_offsets(IGE_HAND_OBS_FULL_STATE);   // states_buf
+    constexpr bool need_dof = oo.dof_pos >= 0 || oo.dof_vel >= 0 || asym;
+    constexpr bool need_force = oo.dof_force >= 0 || asym;
+    constexpr bool need_sens = oo.sensors >= 0 || asym;
+    constexpr bool ft_full = oo.ft_state >= 0 || asym;
+    if (tid < FD) {
+        const float lo = p.dof_lower[tid], hi = p.dof_upper[tid];
+        s_lo[tid] = lo; s_hi[tid] = hi; s_rspan[tid] = 1.0f / (hi - lo);
     }
+    if (tid < FT_N) s_ft[tid] = p.fingertip_handles[tid];
     __syncthreads();
-    if (s_last && tid == 0) {
-        __threadfence();
-        const unsigned num_resets = *reinterpret_cast<volatile unsigned *>(b.reduce_scratch + 0);
-        const float finished = *reinterpret_cast<volatile float *>(b.reduce_scratch + 2);
-        if (num_resets > 0)
-            b.consecutive_successes[0] = p.av_factor * finished / (float)num_resets +
-                                         (float)(1.0 - (double)p.av_factor) * b.consecutive_successes[0];
-        b.reduce_scratch[0] = 0u; b.reduce_scratch[1] = 0u; b.reduce_scratch[2] = 0u;
-        if (b.list.scratch && p.rand.step) *p.rand.step += 1ull;
+
+    int acc_resets = 0;                      // warp 0, lane == env: partial sums over this CTA's tiles
+    float acc_finished = 0.f, acc_n = 0.f, acc_rew = 0.f, acc_done = 0.f, acc_to = 0.f, acc_len = 0.f;
+
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int e0 = tile * TE;
+        const int e = e0 + lane;             // warp 0 only
+        float obj[13], goal[7], qd[4];
+        long long progress = 0, resets_in = 0, goal_in = 0;
+        float succ_in = 0.f;
+        if (warp == 0) {
+            // ---- env warp (lane == env): object / goal rows, flags, quaternion difference ----
+            const long long oidx = b.object_indices[e];
+            const float *gp = b.goal_states + (size_t)e * 13;
+#pragma unroll
+            for (int i = 0; i < 7; ++i) goal[i] = gp[i];
+            progress = b.progress_buf[e];
+            resets_in = b.reset_buf[e];
+            goal_in = b.reset_goal_buf[e];
+            succ_in = b.successes[e];
+            const float *op = b.root_state_tensor + (size_t)oidx * 13;
+#pragma unroll
+            for (int i = 0; i < 13; ++i) obj[i] = op[i];
+            if (b.randomize_buf) b.randomize_buf[e] += 1;
+            float conj[4];
+            ige::quat_conjugate(goal + 3, conj);
+            ige::quat_mul(obj + 3, conj, qd);
+            fill_env_segments(p, LAYOUT, nobs, obs_tile + lane * nobs, obj, goal, qd);
+            if (asym) fill_env_segments(p, IGE_HAND_OBS_FULL_STATE, MAX_OBS, st_tile + lane * MAX_OBS, obj, goal, qd);
+        } else {
+            // ---- element warps: every load of the tile first, then the scatter into the row-major tile(s) ----
+            const int ct = tid - 32;
+            float2 dv[KD];
+            float4 fo = make_float4(0.f, 0.f, 0.f, 0.f), se0 = fo, se1 = fo, ac = fo;
+            float ft[KF];
+            if (need_dof) {
+                const float2 *src = reinterpret_cast<const float2 *>(b.dof_state) + (size_t)e0 * FD;
+#pragma unroll
+                for (int k = 0; k < KD; ++k) { const int i = ct + k * CT; if (i < TE * FD) dv[k] = __ldg(src + i); }
+            }
+            if (need_force && ct < TE * FD / 4) fo = __ldg(reinterpret_cast<const float4 *>(b.dof_force_tensor + (size_t)e0 * FD) + ct);
+            if (need_sens) {
+                const float4 *src = reinterpret_cast<const float4 *>(b.vec_sensor_tensor + (size_t)e0 * FS);
+                if (ct < TE * FS / 4) se0 = __ldg(src + ct);
+                if (KS > 1 && ct + CT < TE * FS / 4) se1 = __ldg(src + ct + CT);
+            }
+            if (ct < TE * FA / 4) ac = __ldg(reinterpret_cast<const float4 *>(b.actions + (size_t)e0 * FA) + ct);
+            const float *rb = b.rigid_body_states + (size_t)e0 * p.num_bodies * 13;
+            if (ft_full) {
+#pragma unroll
+                for (int k = 0; k < KF; ++k) {
+                    const int i = ct + k * CT;
+                    if (i < TE * 65) {
+                        const int le = i / 65, r = i - le * 65, f = r / 13, kk = r - f * 13;
+                        ft[k] = __ldg(rb + ((size_t)le * p.num_bodies + s_ft[f]) * 13 + kk);
+                    }
+                }
+            } else {
+#pragma unroll
+                for (int k = 0; k < KP; ++k) {
+                    const int i = ct + k * CT;
+                    if (i < TE * 15) {
+                        const int le = i / 15, r = i - le * 15, f = r / 3, kk = r - f * 3;
+                        ft[k] = __ldg(rb + ((size_t)le * p.num_bodies + s_ft[f]) * 13 + kk);
+                    }
+                }
+            }
+            if (need_dof) {
+#pragma unroll
+                for (int k = 0; k < KD; ++k) {
+                    const int i = ct + k * CT;
+                    if (i < TE * FD) {
+                        const int le = i / FD, j = i - le * FD;
+                        // unscale :499-500; the divisor is loop-invariant per column -> exact reciprocal division
+                        const float up = ige::div_by(2.0f * dv[k].x - s_hi[j] - s_lo[j], s_hi[j] - s_lo[j], s_rspan[j]);
+                        const float uv = p.vel_obs_scale * dv[k].y;
+                        if (oo.dof_pos >= 0) obs_tile[le * nobs + oo.dof_pos + j] = up;
+                        if (oo.dof_vel >= 0) obs_tile[le * nobs + oo.dof_vel + j] = uv;
+                        if (asym) { st_tile[le * MAX_OBS + so.dof_pos + j] = up; st_tile[le * MAX_OBS + so.dof_vel + j] = uv; }
+                    }
+                }
+            }
+            if (need_force && ct < TE * FD / 4) {
+                const float v[4] = {fo.x, fo.y, fo.z, fo.w};
+                const int i = ct * 4, le = i / FD, j = i - le * FD;   // 24 % 4 == 0: one env per vector
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const float x = p.force_torque_obs_scale * v[q];
+                    if (oo.dof_force >= 0) obs_tile[le * nobs + oo.dof_force + j + q] = x;
+                    if (asym) st_tile[le * MAX_OBS + so.dof_force + j + q] = x;
+                }
+            }
+            if (need_sens) {
+#pragma unroll
+                for (int h = 0; h < KS; ++h) {
+                    const int i4 = ct + h * CT;
+                    if (i4 < TE * FS / 4) {
+                        const float4 sv = h ? se1 : se0;
+                        const float v[4] = {sv.x, sv.y, sv.z, sv.w};
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) {   // 30 % 4 != 0: a vector may straddle two envs
+                            const int i = i4 * 4 + q, le = i / FS, j = i - le * FS;
+                            const float x = p.force_torque_obs_scale * v[q];
+                            if (oo.sensors >= 0) obs_tile[le * nobs + oo.sensors + j] = x;
+                            if (asym) st_tile[le * MAX_OBS + so.sensors + j] = x;
+                        }
+                    }
+                }
+            }
+            if (ct < TE * FA / 4) {
+                const float v[4] = {ac.x, ac.y, ac.z, ac.w};
+                const int i = ct * 4, le = i / FA, j = i - le * FA;
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    obs_tile[le * nobs + oo.actions + j + q] = v[q];
+                    if (asym) st_tile[le * MAX_OBS + so.actions + j + q] = v[q];
+                }
+            }
+            if (ft_full) {
+#pragma unroll
+                for (int k = 0; k < KF; ++k) {
+                    const int i = ct + k * CT;
+                    if (i < TE * 65) {
+                        const int le = i / 65, r = i - le * 65;
+                        if (oo.ft_state >= 0) obs_tile[le * nobs + oo.ft_state + r] = ft[k];
+                        if (oo.ft_pos >= 0) {
+                            const int f = r / 13, kk = r - f * 13;
+                            if (kk < 3) obs_tile[le * nobs + oo.ft_pos + f * 3 + kk] = ft[k];
+                        }
+                        if (asym) st_tile[le * MAX_OBS + so.ft_state + r] = ft[k];
+                    }
+                }
+            } else {
+#pragma unroll
+                for (int k = 0; k < KP; ++k) {
+                    const int i = ct + k * CT;
+                    if (i < TE * 15) { const int le = i / 15, r = i - le * 15; obs_tile[le * nobs + oo.ft_pos + r] = ft[k]; }
+                }
+            }
+        }
+        ige::fence_proxy_async();
+        __syncthreads();
+        // ---- tile out (warp 1 issues the bulk stores; warp 0 goes on with the reward) ----
+        if (tid == 32) {
+            ige::bulk_s2g(b.obs_buf + (size_t)e0 * nobs, obs_tile, (uint32_t)(TE * nobs) * 4);
+            if (asym) ige::bulk_s2g(b.states_buf + (size_t)e0 * MAX_OBS, st_tile, (uint32_t)(TE * MAX_OBS) * 4);
+            ige::bulk_commit();
+        }
+        if (warp == 0) {  // compute_hand_reward :746-800
+            progress += 1;  // :711
+            const float tol = p.ignore_z_rot ? 2.0f * p.success_tolerance : p.success_tolerance;  // :758-759
+            const float goal_dist = ige::norm3(obj[0] - goal[0], obj[1] - goal[1], obj[2] - goal[2]);
+            const float qn = ige::norm3(qd[0], qd[1], qd[2]);
+            const float rot_dist = 2.0f * asinf(qn > 1.0f ? 1.0f : qn);
+            const float dist_rew = goal_dist * p.dist_reward_scale;
+            const float rot_rew = 1.0f / (fabsf(rot_dist) + p.rot_eps) * p.rot_reward_scale;
+            const float *arow = obs_tile + lane * nobs + oo.actions;
+            const float action_penalty = ige::row_sum<FA>([&](int k) { const float a = arow[k]; return a * a; });
+            float reward = dist_rew + rot_rew + action_penalty * p.action_penalty_scale;
+            const bool hit = fabsf(rot_dist) <= tol;
+            const long long goal_resets = hit ? 1 : goal_in;
+            const float successes = succ_in + (float)goal_resets;
+            if (goal_resets == 1) reward = reward + p.reach_goal_bonus;
+            const bool fell = goal_dist >= p.fall_dist;
+            if (fell) reward = reward + p.fall_penalty;
+            long long resets = fell ? 1 : resets_in;
+            if (p.max_consecutive_successes > 0) {
+                if (hit) progress = 0;
+                if (successes >= (float)p.max_consecutive_successes) resets = 1;
+            }
+            const bool late = (float)progress >= p.max_episode_length - 1.0f;
+            if (late) resets = 1;
+            if (p.max_consecutive_successes > 0 && late) reward = reward + 0.5f * p.fall_penalty;
+            b.rew_buf[e] = reward;
+            b.reset_buf[e] = resets;
+            b.reset_goal_buf[e] = goal_resets;
+            b.progress_buf[e] = progress;
+            b.successes[e] = successes;
+            const bool timeout = late && resets != 0;  // vec_task.py:396
+            if (b.timeout_buf) b.timeout_buf[e] = timeout ? 1 : 0;
+            acc_resets += (int)resets;
+            acc_finished += successes * (float)resets;
+            acc_n += 1.f; acc_rew += reward; acc_done += resets != 0 ? 1.f : 0.f; acc_to += timeout ? 1.f : 0.f;
+            acc_len += resets != 0 ? (float)progress : 0.f;
+        }
+        if (b.obs_clamped) {  // vec_task.py:404
+            float *dc = b.obs_clamped + (size_t)e0 * nobs;
+            for (int i = tid; i < TE * nobs; i += FNT) dc[i] = clampf(obs_tile[i], p.clip_obs);
+        }
+        if (asym && b.states_clamped) {
+            float *dc = b.states_clamped + (size_t)e0 * MAX_OBS;
+            for (int i = tid; i < TE * MAX_OBS; i += FNT) dc[i] = clampf(st_tile[i], p.clip_obs);
+        }
+        if (tid == 32) ige::bulk_wait_read_all();
+        __syncthreads();  // the tile may be overwritten
     }
+
+    // ---- per-CTA sums -> global; last CTA: consecutive_successes (:798), re-arm, advance Philox ----
+    if (warp == 0) {
+        const int cta_resets = __reduce_add_sync(0xffffffffu, acc_resets);
+        const float cta_finished = ige::warp_sum(acc_finished);   // integer-valued terms: exact in any order
+        if (lane == 0) {
+            atomicAdd(b.reduce_scratch + 0, (unsigned)cta_resets);
+            atomicAdd(reinterpret_cast<float *>(b.reduce_scratch) + 2, cta_finished);
+        }
+        if (b.stats) {
+            const float v[7] = {acc_n, acc_rew, acc_done, acc_to, acc_len, (float)acc_resets, acc_finished};
+            const int slot[7] = {IGE_STAT_STEPS, IGE_STAT_REWARD, IGE_STAT_DONE, IGE_STAT_TIMEOUT, IGE_STAT_DONE_LENGTH,
+                                 IGE_STAT_TASK0, IGE_STAT_TASK0 + 1};
+            ige::warp_stats_add<7>(b.stats, v, slot);
+        }
+    }
+    finish_hand_reduction(p, b, expected_ctas, &s_last);
+}
+
+typedef void (*HandFastKernel)(const IgeShadowHandParams, const IgeShadowHandBuffers, const int, const int);
+HandFastKernel fast_kernel(int layout, bool asym) {
+    static const HandFastKernel table[8] = {
+        shadow_hand_post_physics_fast_kernel<0, false>, shadow_hand_post_physics_fast_kernel<0, true>,
+        shadow_hand_post_physics_fast_kernel<1, false>, shadow_hand_post_physics_fast_kernel<1, true>,
+        shadow_hand_post_physics_fast_kernel<2, false>, shadow_hand_post_physics_fast_kernel<2, true>,
+        shadow_hand_post_physics_fast_kernel<3, false>, shadow_hand_post_physics_fast_kernel<3, true>};
+    return table[layout * 2 + (asym ? 1 : 0)];
 }
 
 int check(const IgeShadowHandParams *p, const IgeShadowHandBuffers *b) {
@@ -439,7 +725,31 @@ extern "C" int ige_shadow_hand_post_physics(const IgeShadowHandParams *p, const 
         if (e != cudaSuccess) return ige_fail((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
         attr_set = true;
     }
-    const int grid = (p->num_envs + TE - 1) / TE;
-    shadow_hand_post_physics_kernel<<<grid, NT, smem, (cudaStream_t)stream>>>(*p, *b, ige_use_tma());
+    static bool fast_attr_set = false;
+    if (!fast_attr_set) {
+        for (int i = 0; i < 8; ++i) {
+            cudaError_t e = cudaFuncSetAttribute(fast_kernel(i >> 1, i & 1), cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                 (int)((TE * MAX_OBS + 32 + TE * MAX_OBS) * sizeof(float)));
+            if (e != cudaSuccess) return ige_fail((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+        }
+        fast_attr_set = true;
+    }
+    const int tiles = (p->num_envs + TE - 1) / TE;
+    cudaStream_t s = (cudaStream_t)stream;
+    const bool standard = p->num_hand_dofs == FD && p->num_dofs_per_env == FD && p->num_actions == FA && ige_use_tma() &&
+                          ige_fast_paths();
+    if (standard) {
+        // full tiles: persistent fast kernel; a ragged last tile (num_envs % 32) goes through the generic one
+        const int full = p->num_envs / TE, ragged = tiles - full;
+        const int grid = full < 148 * kFastCtasPerSm ? full : 148 * kFastCtasPerSm;
+        if (full > 0) {
+            fast_kernel(p->obs_type, p->asymmetric_obs != 0)<<<grid, FNT, smem, s>>>(*p, *b, full, grid + ragged);
+            if (int rc = ige_check_launch("ige_shadow_hand_post_physics(fast)")) return rc;
+        }
+        if (ragged == 0) return IGE_OK;
+        shadow_hand_post_physics_kernel<<<ragged, NT, smem, s>>>(*p, *b, ige_use_tma(), full, grid + ragged);
+    } else {
+        shadow_hand_post_physics_kernel<<<tiles, NT, smem, s>>>(*p, *b, ige_use_tma(), 0, tiles);
+    }
     return ige_check_launch("ige_shadow_hand_post_physics");
 }

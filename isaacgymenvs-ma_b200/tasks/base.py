@@ -217,6 +217,40 @@ class VecTaskB200:
             self.obs_dict["states"] = self.get_state()
         return self.obs_dict
 
+    # -- pipeline=cpu: simulator state lives in pinned host memory ------------------------------
+    HOST_SIM_ATTRS = ()      # task attributes that alias simulator / policy memory (set by subclasses)
+    HOST_OUT_ATTRS = ("obs_buf", "rew_buf", "reset_buf")
+
+    def map_host_sim(self, extra=()):
+        """``sim_device=cpu pipeline=cpu`` (vec_task.py:82-88) without a staging copy: the simulator
+        tensors, the actions and the three step() results are re-homed in PINNED host memory and the
+        fused kernel reads / writes them over PCIe itself (pinned allocations are device-addressable
+        under UVA; the TMA / coalesced accesses of the kernel become the PCIe transactions, reads and
+        writes overlap on the full-duplex link).  Task-owned state (progress, potentials, targets ...)
+        stays in HBM.  Returns {name: pinned tensor}; the tensors stay ordinary CPU tensors for the host
+        side.  Only the kernel launch touches them afterwards -- there is still no CPU compute path."""
+        if self.device.type != "cuda":
+            raise _lib.IgeError("map_host_sim() needs a CUDA device to run the kernels on")
+        moved = {}
+        for name in tuple(self.HOST_SIM_ATTRS) + tuple(self.HOST_OUT_ATTRS) + tuple(extra):
+            t = getattr(self, name, None)
+            if t is None:
+                continue
+            h = torch.empty(t.shape, dtype=t.dtype, pin_memory=True)
+            h.copy_(t)
+            setattr(self, name, h)
+            for k, v in list(self.sim.tensors.items()):
+                if v is t:
+                    self.sim.tensors[k] = h
+            moved[name] = h
+        torch.cuda.synchronize(self.device)
+        self.host_mapped = moved
+        self._on_remap()
+        return moved
+
+    def _on_remap(self):
+        pass
+
     # -- helpers for subclasses ----------------------------------------------------------------
     def _adopt(self, st, names):
         """Move numpy state arrays onto the device under the reference attribute names."""

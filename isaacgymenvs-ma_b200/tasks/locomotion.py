@@ -9,6 +9,12 @@ class _Locomotion(VecTaskB200):
     ENTRY = None
     HAS_DOF_FORCE = False
     SENSORS = 0
+    HOST_SIM_ATTRS = ("root_states", "dof_state", "vec_sensor_tensor", "dof_force_tensor", "actions")
+
+    def _on_remap(self):
+        n, d = self.num_envs, self.num_dof
+        self.dof_pos = self.dof_state.view(n, d, 2)[..., 0]
+        self.dof_vel = self.dof_state.view(n, d, 2)[..., 1]
 
     def __init__(self, cfg, sim, device, **kw):
         cfg = dict(cfg)

@@ -249,3 +249,44 @@ def test_compact_resets(n, group, prob):
         np.testing.assert_array_equal(ids[:k].cpu().numpy(), want)
         np.testing.assert_array_equal(rank.cpu().numpy(), np.cumsum(env_flag) - env_flag)
         assert int(scratch.abs().sum().item()) == 0, "scratch not restored to zero"
+
+
+@pytest.mark.parametrize("task,n", [("Ant", 4096), ("Humanoid", 2048 + 36)])
+@pytest.mark.parametrize("tma", [True, False])
+def test_host_mapped_sim_matches_device_resident(task, n, tma):
+    """pipeline=cpu mode (VecTaskB200.map_host_sim): the kernel reading / writing pinned host memory
+    gives bit for bit what it gives on HBM-resident tensors, incl. the reset rows scattered back."""
+    _set_tma(tma)
+    try:
+        syn = H.pkg.factory._SYN_NAME[task]
+        st = H.pkg.synthetic.make_state(syn, n, seed=21, reset_prob=0.1)
+        a = H.pkg.factory.from_state(task, {k: v.copy() for k, v in st.items()}, "cuda:0", rand_mode="philox", seed=5)
+        b = H.pkg.factory.from_state(task, {k: v.copy() for k, v in st.items()}, "cuda:0", rand_mode="philox", seed=5)
+        moved = b.map_host_sim()
+        assert all(t.device.type == "cpu" and t.is_pinned() for t in moved.values())
+        for _ in range(2):
+            a.post_physics_step()
+            b.post_physics_step()
+        torch.cuda.synchronize()
+        for name in ("obs_buf", "rew_buf", "reset_buf", "progress_buf", "dof_state", "potentials", "obs_clamped"):
+            H.assert_equal(name, getattr(b, name).cpu().numpy(), getattr(a, name).cpu().numpy())
+        H.assert_equal("reset ids", b.reset_env_ids.cpu().numpy(), a.reset_env_ids.cpu().numpy())
+    finally:
+        _set_tma(True)
+
+
+def _set_fast(on):
+    H.pkg._lib.lib().ige_set_fast_paths(C.c_int(1 if on else 0))
+
+
+@pytest.mark.parametrize("task", ["shadow_hand"] + H.MA_TASKS)
+def test_generic_kernels_match_oracle(task):
+    """The any-shape kernels (taken for non-standard dimensions) stay parity-green when forced."""
+    _set_fast(False)
+    try:
+        _oracle_vs_cuda(task, 2052, 3, 0.2, steps=2)
+        if task == "shadow_hand":
+            for obs_type in ("openai", "full_no_vel", "full"):
+                _oracle_vs_cuda(task, 1030, 4, 0.2, steps=2, obs_type=obs_type, asymmetric_obs=(obs_type == "full"))
+    finally:
+        _set_fast(True)

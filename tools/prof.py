@@ -25,7 +25,7 @@ def main():
     pkg = load_package()
     envs = []
     for r in range(a.replicas):
-        st = pkg.synthetic.make_state(a.task.lower(), a.num_envs, seed=r, reset_prob=0.02, fall_frac=a.fall_frac)
+        st = pkg.synthetic.make_state(pkg.factory._SYN_NAME[a.task], a.num_envs, seed=r, reset_prob=0.02, **({"fall_frac": a.fall_frac} if a.task in ("Ant", "Humanoid") else {}))
         e = pkg.factory.from_state(a.task, st, "cuda:0", rand_mode="philox", seed=1, fuse_epilogue=a.epilogue)
         e.sim.record = False
         envs.append(e)
