@@ -5,3 +5,4 @@ __version__ = "0.1.0"
 from . import factory  # noqa: E402,F401
 from .factory import make  # noqa: E402,F401
 from . import distributed  # noqa: E402,F401
+from . import host_pipeline  # noqa: E402,F401

@@ -122,6 +122,72 @@ __device__ __forceinline__ float sum_sq_small(const float *act, int d) {
     return ((p4[0] + p4[1]) + p4[2]) + p4[3];
 }
 
+// Common tail of both kernels: the CTA's observation tile leaves with one bulk store (or a coalesced loop for
+// ragged tiles), then the reward-component sums / statistics / reset list / last-CTA means.
+__device__ __forceinline__ void franka_tile_out_and_reduce(const IgeFrankaMAParams &p, const IgeFrankaMABuffers &b,
+                                                           const float *obs_tile, int *s_last_p, float (&comp)[NC],
+                                                           float st_rew, float st_done, float st_to, float st_len,
+                                                           bool valid, int phase, int use_tma, int A, int num_obs_) {
+    const int tid = threadIdx.x, lane = tid & 31, N = p.num_envs;
+    const int e0 = blockIdx.x * TE;
+    const int ne = min(TE, N - e0);
+    int &s_last = *s_last_p;
+    // ---- observation tile out: one bulk store (or a coalesced loop for ragged tiles) ----
+    const int count = ne * A * num_obs_;
+    const bool bulk = use_tma && (count % 4 == 0);
+    if (bulk) ige::fence_proxy_async();
+    __syncthreads();
+    float *dst = b.obs_buf + (size_t)e0 * A * num_obs_;
+    if (bulk) {
+        if (tid == 0) { ige::bulk_s2g(dst, obs_tile, (uint32_t)count * 4); ige::bulk_commit(); }
+    } else {
+        for (int i = tid; i < count; i += NT) dst[i] = obs_tile[i];
+    }
+    if (b.obs_clamped) {  // vec_task.py:404
+        float *dc = b.obs_clamped + (size_t)e0 * A * num_obs_;
+        for (int i = tid; i < count; i += NT) dc[i] = clampf(obs_tile[i], p.clip_obs);
+    }
+
+    // ---- reward-component sums (the .mean()s of extras) + statistics ----
+#pragma unroll
+    for (int i = 0; i < NC; ++i) comp[i] = ige::warp_sum(comp[i]);
+    if (lane < NC) {
+        float mine = 0.f;
+#pragma unroll
+        for (int i = 0; i < NC; ++i) if (lane == i) mine = comp[i];
+        atomicAdd(b.reduce_scratch + lane, mine);
+        if (b.stats) atomicAdd(b.stats + (blockIdx.x % IGE_STATS_ROWS) * IGE_STATS_STRIDE + IGE_STAT_TASK0 + lane, mine);
+    }
+    if (b.stats) {
+        const float v[5] = {valid ? (float)A : 0.f, st_rew, st_done, st_to, st_len};
+        const int slot[5] = {IGE_STAT_STEPS, IGE_STAT_REWARD, IGE_STAT_DONE, IGE_STAT_TIMEOUT, IGE_STAT_DONE_LENGTH};
+        ige::warp_stats_add<5>(b.stats, v, slot);
+    }
+    // ---- ONE retirement ticket per CTA: the CTA that arrives last expands the reset list (single-launch
+    //      variants) and turns the component sums into the logged means, lane-parallel ----
+    if (lane < NC) __threadfence();  // the lanes that published (ballot mask by lane 0, sums by lanes < NC)
+    __syncthreads();
+    if (tid == 0) {
+        unsigned *cnt = reinterpret_cast<unsigned *>(b.reduce_scratch + NC);
+        s_last = atomicAdd(cnt, 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (s_last) {
+        __threadfence();
+        if (phase == PH_FUSED && b.list.scratch) ige::expand_reset_list(b.list, N, nullptr);
+        if (tid < NC) {
+            const float sum = __ldcg(b.reduce_scratch + tid);
+            if (b.reward_components) b.reward_components[tid] = sum / (float)((long long)N * A);
+            b.reduce_scratch[tid] = 0.0f;
+        }
+        if (tid == 0) {
+            b.reduce_scratch[NC] = 0.0f;
+            if (b.list.scratch && p.rand.step) *p.rand.step += 1ull;
+        }
+    }
+    if (bulk && tid == 0) ige::bulk_wait_read_all();  // the tile must outlive the bulk store's reads
+}
+
 __global__ void __launch_bounds__(NT) franka_ma_kernel(const __grid_constant__ IgeFrankaMAParams p,
                                                        const __grid_constant__ IgeFrankaMABuffers b, const int phase,
                                                        const int use_tma) {
@@ -370,59 +436,322 @@ __global__ void __launch_bounds__(NT) franka_ma_kernel(const __grid_constant__ I
         }
     }
 
-    // ---- observation tile out: one bulk store (or a coalesced loop for ragged tiles) ----
-    const int count = ne * A * NO;
-    const bool bulk = use_tma && (count % 4 == 0);
-    if (bulk) ige::fence_proxy_async();
-    __syncthreads();
-    float *dst = b.obs_buf + (size_t)e0 * A * NO;
-    if (bulk) {
-        if (tid == 0) { ige::bulk_s2g(dst, obs_tile, (uint32_t)count * 4); ige::bulk_commit(); }
-    } else {
-        for (int i = tid; i < count; i += NT) dst[i] = obs_tile[i];
-    }
-    if (b.obs_clamped) {  // vec_task.py:404
-        float *dc = b.obs_clamped + (size_t)e0 * A * NO;
-        for (int i = tid; i < count; i += NT) dc[i] = clampf(obs_tile[i], p.clip_obs);
-    }
-    if (bulk && tid == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
-
-    // ---- reward-component sums (the .mean()s of extras) + statistics ----
-#pragma unroll
-    for (int i = 0; i < NC; ++i) comp[i] = ige::warp_sum(comp[i]);
-    if (lane < NC) {
-        float mine = 0.f;
-#pragma unroll
-        for (int i = 0; i < NC; ++i) if (lane == i) mine = comp[i];
-        atomicAdd(b.reduce_scratch + lane, mine);
-        if (b.stats) atomicAdd(b.stats + (blockIdx.x % IGE_STATS_ROWS) * IGE_STATS_STRIDE + IGE_STAT_TASK0 + lane, mine);
-    }
-    if (b.stats) {
-        const float v[5] = {valid ? (float)A : 0.f, st_rew, st_done, st_to, st_len};
-        const int slot[5] = {IGE_STAT_STEPS, IGE_STAT_REWARD, IGE_STAT_DONE, IGE_STAT_TIMEOUT, IGE_STAT_DONE_LENGTH};
-        ige::warp_stats_add<5>(b.stats, v, slot);
-    }
-    if (phase == PH_FUSED && b.list.scratch) ige::finish_reset_list(b.list, N, nullptr, lane == 0);
-    __syncthreads();
-    if (tid == 0) {
-        __threadfence();
-        unsigned *cnt = reinterpret_cast<unsigned *>(b.reduce_scratch + NC);
-        s_last = atomicAdd(cnt, 1u) == gridDim.x - 1;
-    }
-    __syncthreads();
-    if (s_last && tid == 0) {
-        __threadfence();
-        const float denom = (float)((long long)N * A);
-        for (int i = 0; i < NC; ++i) {
-            const float s = *reinterpret_cast<volatile float *>(b.reduce_scratch + i);
-            if (b.reward_components) b.reward_components[i] = s / denom;
-            b.reduce_scratch[i] = 0.0f;
-        }
-        b.reduce_scratch[NC] = 0.0f;
-        if (b.list.scratch && p.rand.step) *p.rand.step += 1ull;
-    }
+    franka_tile_out_and_reduce(p, b, obs_tile, &s_last, comp, st_rew, st_done, st_to, st_len, valid, phase, use_tma, A, NO);
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// Pair kernel: the shipped configuration of all four tasks (numAgents = numTargets = 2,
+// cfg/task/Franka*MA.yaml) with every per-env quantity in registers.
+// ---------------------------------------------------------------------------------------------
+// Same thread-per-env ownership as franka_ma_kernel, but V / A / T / num_actions are compile-time: the
+// agent and cube loops unroll, nothing is indexed dynamically (the generic kernel keeps eef / cube /
+// fsm in local memory), and every load whose address depends only on the env index -- gripper, base and
+// contact rows, actions, the flags as 16-B vectors, the cross-env rows of compute_global_FSM -- is issued
+// before the reset section, so a step costs two dependent DRAM round trips (flags + state, then the cube
+// rows a reset may have rewritten) instead of one per stage.
+template <int V>
+__global__ void __launch_bounds__(NT) franka_ma_pair_kernel(const __grid_constant__ IgeFrankaMAParams p,
+                                                            const __grid_constant__ IgeFrankaMABuffers b, const int phase,
+                                                            const int use_tma) {
+    constexpr int A = 2, T = 2;
+    constexpr int NA = V == IGE_FRANKA_REACH ? 6 : 7;
+    constexpr int NO = V == IGE_FRANKA_REACH ? 19 : V == IGE_FRANKA_COLLECT ? 28 : V == IGE_FRANKA_COMBINE ? 48 : 50;
+    constexpr bool PAIRED = V == IGE_FRANKA_COMBINE || V == IGE_FRANKA_PP;
+    extern __shared__ __align__(128) float obs_tile[];  // TE * A * NO
+    __shared__ int s_last;
+    __shared__ float s_u[NT / 32][32];
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int N = p.num_envs;
+    const int e0 = blockIdx.x * TE;
+    const int ne = min(TE, N - e0);
+    const int e = e0 + tid;
+    const bool valid = tid < ne;
+    const int ec = valid ? e : N - 1;   // clamped: invalid lanes load a real row and discard it
+    const uint64_t step = (p.rand.mode == IGE_RAND_PHILOX && p.rand.step)
+                              ? *reinterpret_cast<const volatile uint64_t *>(p.rand.step) : 0ull;
+
+    // ---- loads that no reset can change ----
+    longlong2 prog = *reinterpret_cast<const longlong2 *>(b.progress_buf + (size_t)ec * A);
+    longlong2 rst = *reinterpret_cast<const longlong2 *>(b.reset_buf + (size_t)ec * A);
+    float eef[A][7], base[A][7], act[A][NA], cf[A][3], je[A][3];
+    if (phase != PH_RESET) {
+#pragma unroll
+        for (int a = 0; a < A; ++a) {
+            const float *r = body_row(p, b, ec, p.eef_body_start, p.eef_body_step, a);
+#pragma unroll
+            for (int i = 0; i < 7; ++i) eef[a][i] = __ldg(r + i);
+            if (V != IGE_FRANKA_REACH) {
+                const float *bs = body_row(p, b, ec, p.base_body_start, p.base_body_step, a);
+#pragma unroll
+                for (int i = 0; i < 7; ++i) base[a][i] = __ldg(bs + i);
+            }
+            const float *ap = b.actions + ((size_t)ec * A + a) * NA;
+#pragma unroll
+            for (int j = 0; j < NA; ++j) act[a][j] = __ldg(ap + j);
+            if (V == IGE_FRANKA_REACH) {
+                const float *c = b.contact_forces + ((size_t)ec * p.num_bodies + p.hand_body_start + p.hand_body_step * a) * 3;
+#pragma unroll
+                for (int i = 0; i < 3; ++i) cf[a][i] = __ldg(c + i);
+            }
+            if (PAIRED) {  // compute_global_FSM's partner rows (franka_PPMA.py:597-611, see the header)
+                const size_t row = (size_t)ec * A + a;
+                const bool first_half = row < (size_t)N;
+                const int j = first_half ? (int)row : (int)(row - N);
+                const float *r2 = body_row(p, b, j, p.eef_body_start, p.eef_body_step, first_half ? 0 : 1);
+#pragma unroll
+                for (int i = 0; i < 3; ++i) je[a][i] = __ldg(r2 + i);
+            }
+        }
+    }
+
+    // ---- post_physics_step :821-826: progress++, agent flags -> reset_idx (AND filter) ----
+    if (phase != PH_COMPUTE) {
+        const bool did_reset = valid && rst.x != 0 && rst.y != 0;
+        const uint32_t mask = __ballot_sync(0xffffffffu, did_reset);
+        if (b.list.scratch && lane == 0 && e < N) ige::publish_tile_mask(b.list, e >> 5, mask);
+        for (uint32_t m = mask; m; m &= m - 1)  // the warp resets its flagged envs one after the other, together
+            reset_env_coop(p, b, step, e - lane + __ffs(m) - 1, lane, s_u[tid >> 5]);
+        if (did_reset) { prog = make_longlong2(0, 0); rst = make_longlong2(0, 0); }
+        else { prog.x += 1; prog.y += 1; }
+        if (valid) *reinterpret_cast<longlong2 *>(b.progress_buf + (size_t)e * A) = prog;
+    }
+    if (phase == PH_RESET) {
+        if (b.list.scratch) ige::finish_reset_list(b.list, N, nullptr, lane == 0);
+        return;
+    }
+
+
+    // ---- rows a reset may have rewritten (own warp's writes are ordered by reset_env_coop's __syncwarp) ----
+    float cube[T][7], dest[A][3], sb[3], jc[A][3];
+#pragma unroll
+    for (int c = 0; c < T; ++c) {
+        const float *r = actor_row(p, b, ec, p.cube_actor_start + p.cube_actor_step * c);
+#pragma unroll
+        for (int i = 0; i < 7; ++i) cube[c][i] = r[i];
+    }
+    if (V == IGE_FRANKA_PP) {
+#pragma unroll
+        for (int a = 0; a < A; ++a) {
+            const float *d = actor_row(p, b, ec, p.dest_actor_start + p.dest_actor_step * a);
+#pragma unroll
+            for (int i = 0; i < 3; ++i) dest[a][i] = d[i];
+        }
+    }
+    if (V == IGE_FRANKA_COMBINE) {
+        const float *r = actor_row(p, b, ec, p.stack_base_actor);
+#pragma unroll
+        for (int i = 0; i < 3; ++i) sb[i] = r[i];
+    }
+    if (PAIRED) {
+#pragma unroll
+        for (int a = 0; a < A; ++a) {
+            const size_t row = (size_t)ec * A + a;
+            const bool first_half = row < (size_t)N;
+            const int j = first_half ? (int)row : (int)(row - N);
+            const float *r = actor_row(p, b, j, p.cube_actor_start + p.cube_actor_step * (first_half ? 1 : 0));
+#pragma unroll
+            for (int i = 0; i < 3; ++i) jc[a][i] = r[i];
+        }
+    }
+
+    float comp[NC];
+#pragma unroll
+    for (int i = 0; i < NC; ++i) comp[i] = 0.0f;
+    float st_rew = 0.f, st_done = 0.f, st_to = 0.f, st_len = 0.f;
+    if (valid) {
+        // _get_min_relative_pos (franka_reach_MA.py:521-531)
+        float ncube[A][3];
+        unsigned touched = 0u;
+#pragma unroll
+        for (int a = 0; a < A; ++a) {
+            float best = 0.0f, bx = 0.f, by = 0.f, bz = 0.f;
+            int bi = 0;
+#pragma unroll
+            for (int c = 0; c < T; ++c) {
+                const float d = ige::norm3(cube[c][0] - eef[a][0], cube[c][1] - eef[a][1], cube[c][2] - eef[a][2]);
+                if (c == 0 || d < best) { best = d; bi = c; bx = cube[c][0]; by = cube[c][1]; bz = cube[c][2]; }
+            }
+            ncube[a][0] = bx; ncube[a][1] = by; ncube[a][2] = bz;
+            touched |= 1u << bi;
+        }
+        int fsm[A];
+        float md[A];
+        const float on_th = (float)((double)p.cubeA_size * 0.5 * 0.9);
+#pragma unroll
+        for (int a = 0; a < A; ++a) {
+            const bool closed = act[a][NA - 1] < 0.0f;
+            int sx = 0;
+            if (V == IGE_FRANKA_REACH || V == IGE_FRANKA_COLLECT) {
+                const float *nc = ncube[a];
+                md[a] = ige::norm3(nc[0] - eef[a][0], nc[1] - eef[a][1], nc[2] - eef[a][2]);
+                if (V == IGE_FRANKA_COLLECT) {  // franka_collect_MA.py:549-606
+                    const bool close = md[a] <= on_th;
+                    const bool holding = close && closed;
+                    const bool high = (nc[2] - 1.05f) > (float)((double)p.wall_height + (double)p.cubeA_size / 2);
+                    const bool in_area = (nc[1] > (float)((double)p.wall_pos_y + (double)p.cubeA_size * 1.)) && (fabsf(nc[0]) < 0.6f);
+                    const bool low = (nc[2] - 1.05f) < (float)((double)p.wall_height / 2.);
+                    if (close) sx = 1;
+                    if (holding) sx = 2;
+                    if (holding && high) sx = 3;
+                    if (holding && in_area) sx = 4;
+                    if (holding && in_area && low) sx = 5;
+                    if (holding && in_area && low && !closed) sx = 6;
+                }
+            } else {  // Combine :565-611 / PP :561-595: own cube
+                md[a] = ige::norm3(cube[a][0] - eef[a][0], cube[a][1] - eef[a][1], cube[a][2] - eef[a][2]);
+                const bool on = md[a] <= on_th;
+                if (on) sx = 1;
+                if (on && closed) sx = 2;
+                if (V == IGE_FRANKA_PP) {
+                    const float dz = dest[a][2] - cube[a][2];
+                    const bool lifted = fabsf(dz) >= (float)(((double)p.dest_size + (double)p.cubeA_size) / 2.);
+                    const bool align = ige::norm2(dest[a][0] - cube[a][0], dest[a][1] - cube[a][1]) < (float)((0.05) * 0.5);
+                    const bool stackable = fabsf(dz) <= (float)((double)p.cubeA_size * 0.8660 + (double)p.dest_size / 2.);
+                    if (on && lifted) sx = 3;
+                    if (align) sx = 4;
+                    if (align && stackable) sx = 5;
+                    if (align && stackable && !closed) sx = 6;
+                }
+            }
+            fsm[a] = sx;
+        }
+#pragma unroll
+        for (int a = 0; a < A; ++a) {
+            const size_t row = (size_t)e * A + a;
+            float *o = obs_tile + ((size_t)tid * A + a) * NO;
+            int gfsm = 0;
+            if (PAIRED) {  // compute_global_FSM franka_PPMA.py:597-611
+                const bool grip = ige::norm3(eef[1][0] - eef[0][0], eef[1][1] - eef[0][1], eef[1][2] - eef[0][2]) <= 0.18f;
+                const bool cub = ige::norm3(je[a][0] - jc[a][0], je[a][1] - jc[a][1], je[a][2] - jc[a][2]) <= 0.18f;
+                gfsm = (grip || cub) ? -1 : 0;
+            }
+            int n = 0;
+            if (V == IGE_FRANKA_REACH || V == IGE_FRANKA_COLLECT) {
+#pragma unroll
+                for (int c = 0; c < T; ++c) { o[n++] = cube[c][0]; o[n++] = cube[c][1]; o[n++] = cube[c][2]; }
+#pragma unroll
+                for (int i = 0; i < 4; ++i) o[n++] = eef[a][3 + i];
+#pragma unroll
+                for (int i = 0; i < 3; ++i) o[n++] = eef[a][i];
+#pragma unroll
+                for (int i = 0; i < 3; ++i) o[n++] = ncube[a][i] - eef[a][i];
+                if (V == IGE_FRANKA_COLLECT) {
+#pragma unroll
+                    for (int i = 0; i < 7; ++i) o[n++] = base[a][i];
+                }
+#pragma unroll
+                for (int sft = 1; sft < A; ++sft) {
+                    const int q = (a + sft) % A;
+                    o[n++] = eef[q][0]; o[n++] = eef[q][1]; o[n++] = eef[q][2];
+                }
+                if (V == IGE_FRANKA_COLLECT) { o[n++] = (float)fsm[a]; o[n++] = (float)fsm[a]; }
+            } else {
+#pragma unroll
+                for (int sft = 0; sft < T; ++sft) { const int q = (a + sft) % T;
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) o[n++] = cube[q][3 + i]; }
+#pragma unroll
+                for (int sft = 0; sft < T; ++sft) { const int q = (a + sft) % T; o[n++] = cube[q][0]; o[n++] = cube[q][1]; o[n++] = cube[q][2]; }
+                float aux[3];
+                if (V == IGE_FRANKA_COMBINE) {
+                    aux[0] = sb[0]; aux[1] = sb[1]; aux[2] = sb[2];
+                    o[n++] = aux[0]; o[n++] = aux[1]; o[n++] = aux[2];
+                } else {
+#pragma unroll
+                    for (int sft = 0; sft < T; ++sft) {
+                        const int q = (a + sft) % T;
+                        o[n++] = dest[q][0]; o[n++] = dest[q][1]; o[n++] = dest[q][2];
+                    }
+                    aux[0] = dest[a][0]; aux[1] = dest[a][1]; aux[2] = dest[a][2];
+                }
+#pragma unroll
+                for (int i = 0; i < 3; ++i) o[n++] = cube[a][i] - eef[a][i];
+#pragma unroll
+                for (int i = 0; i < 3; ++i) o[n++] = aux[i] - cube[a][i];
+#pragma unroll
+                for (int i = 0; i < 7; ++i) o[n++] = base[a][i];
+#pragma unroll
+                for (int sft = 0; sft < A; ++sft) { const int q = (a + sft) % A; o[n++] = eef[q][0]; o[n++] = eef[q][1]; o[n++] = eef[q][2]; }
+#pragma unroll
+                for (int sft = 0; sft < A; ++sft) { const int q = (a + sft) % A;
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) o[n++] = eef[q][3 + i]; }
+#pragma unroll
+                for (int sft = 0; sft < A; ++sft) o[n++] = pow2_small(fsm[(a + sft) % A]);
+                o[n++] = pow2_small(gfsm);
+                if (V == IGE_FRANKA_COMBINE) o[n++] = (a == A - 1) ? 1.0f : 0.0f;  // agent_idx :526-527
+            }
+            // ---- compute_franka_reward ----
+            float rewards;
+            float c10[NC];
+#pragma unroll
+            for (int i = 0; i < NC; ++i) c10[i] = 0.0f;
+            const float alast = act[a][NA - 1];
+            if (V == IGE_FRANKA_REACH) {  // franka_reach_MA.py:928-960
+                const float d = md[a];
+                const float dist_reward = 1.0f / (0.5f + d * d);
+                const float actions_cost = sum_sq_small(act[a], NA) * 0.01f;
+                rewards = dist_reward - actions_cost;
+                const int distinct = __popc(touched);  // mask.sum(dim=-1), franka_reach_MA.py:944-948
+                const float all_touched = ((float)distinct / (float)A) * 1.0f;
+                const float colliding = (ige::norm3(cf[a][0], cf[a][1], cf[a][2]) >= 0.1f ? 1.0f : 0.0f) * -10.0f;
+                rewards = rewards + (all_touched + colliding);
+            } else {
+                const float m = md[a];
+                const int sx = fsm[a];
+                c10[0] = sx == 0 ? expf(-5.0f * (m * m)) : 0.0f;
+                c10[1] = sx == 1 ? expf(-1.0f * alast) : 0.0f;
+                if (V == IGE_FRANKA_COLLECT) {  // franka_collect_MA.py:1082-1174
+                    const float *hc = ncube[a];
+                    c10[2] = sx == 2 ? (hc[2] - 1.05f) / (float)(0.3 + 0.025) : 0.0f;
+                    const float dy = fabsf(hc[1] - (float)(0.3 + 0.05 * 2.));
+                    c10[3] = sx == 3 ? expf(-5.0f * (dy * dy)) : 0.0f;
+                    const float dz = fabsf(hc[2] - (float)(0.3 / 2. + 1.05));
+                    c10[4] = sx == 4 ? expf(-5.0f * (dz * dz)) : 0.0f;
+                    c10[5] = sx == 5 ? expf(4.0f * alast) : 0.0f;
+                    c10[6] = sx == 6 ? 1.0f * 3.0f : 0.0f;
+                    c10[7] = (float)sx;
+                    rewards = c10[0] + c10[1] + c10[2] + c10[3] + c10[4] + c10[5] + c10[6] + c10[7] + c10[8] + 0.0f;
+                } else if (V == IGE_FRANKA_COMBINE) {  // franka_combine_MA.py:1080-1166
+                    float lift = fabsf(sb[2] - cube[a][2]) / (float)((0.05 + 0.05) * 0.5);
+                    lift = lift < 0.0f ? 0.0f : (lift > 1.0f ? 1.0f : lift);
+                    c10[2] = sx == 2 ? lift : 0.0f;
+                    c10[7] = (float)sx;
+                    rewards = c10[0] + c10[1] + c10[7];
+                } else {  // franka_PPMA.py:1082-1167
+                    const float rx = dest[a][0] - cube[a][0], ry = dest[a][1] - cube[a][1], rz = dest[a][2] - cube[a][2];
+                    float lift = fabsf(rz) / (float)((0.05 + 0.05) * 0.5);
+                    lift = lift < 0.0f ? 0.0f : (lift > 1.0f ? 1.0f : lift);
+                    c10[2] = sx == 2 ? lift : 0.0f;
+                    const float dt = ige::norm3(rx + 0.0f, ry + 0.0f, rz + 0.05f);
+                    c10[3] = sx == 3 ? expf(-3.0f * dt) : 0.0f;
+                    c10[4] = sx == 4 ? expf(-10.0f * dt) : 0.0f;
+                    c10[5] = sx == 5 ? expf(5.0f * alast) : 0.0f;
+                    c10[6] = sx == 6 ? tanhf(m) : 0.0f;
+                    c10[7] = (float)sx;
+                    c10[8] = (float)gfsm * 0.5f;
+                    rewards = c10[0] + c10[1] + c10[2] + c10[3] + c10[4] + c10[5] + c10[6] + c10[7] + c10[8] + c10[9];
+                }
+            }
+            rewards = rewards < 0.0f ? 0.0f : rewards;  // torch.clip(rewards, 0., None)
+#pragma unroll
+            for (int i = 0; i < NC; ++i) comp[i] += c10[i];
+            long long reset = a == 0 ? rst.x : rst.y;
+            const long long progress = a == 0 ? prog.x : prog.y;
+            const bool late = (float)progress >= p.max_episode_length - 1.0f;
+            if (late) reset = 1;
+            if (a == 0) rst.x = reset; else rst.y = reset;
+            b.rew_buf[row] = rewards;
+            const bool timeout = late && reset != 0;  // vec_task.py:396
+            if (b.timeout_buf) b.timeout_buf[row] = timeout ? 1 : 0;
+            st_rew += rewards; st_done += reset != 0 ? 1.f : 0.f; st_to += timeout ? 1.f : 0.f;
+            st_len += reset != 0 ? (float)progress : 0.f;
+        }
+        *reinterpret_cast<longlong2 *>(b.reset_buf + (size_t)e * A) = rst;
+    }
+    franka_tile_out_and_reduce(p, b, obs_tile, &s_last, comp, st_rew, st_done, st_to, st_len, valid, phase, use_tma, A, NO);
+}
 }  // namespace
 
 extern "C" int ige_franka_ma_post_physics(const IgeFrankaMAParams *p, const IgeFrankaMABuffers *b, void *stream) {
@@ -470,12 +799,21 @@ extern "C" int ige_franka_ma_post_physics(const IgeFrankaMAParams *p, const IgeF
     }
     const int grid = (p->num_envs + TE - 1) / TE;
     cudaStream_t s = (cudaStream_t)stream;
+    typedef void (*Kernel)(const IgeFrankaMAParams, const IgeFrankaMABuffers, const int, const int);
+    Kernel k = franka_ma_kernel;
+    static const int kPairObs[4] = {19, 28, 48, 50}, kPairActions[4] = {6, 7, 7, 7};
+    if (ige_fast_paths() && p->num_agents == 2 && p->num_targets == 2 && p->num_obs == kPairObs[p->variant] &&
+        p->num_actions == kPairActions[p->variant]) {
+        static const Kernel pair[4] = {franka_ma_pair_kernel<IGE_FRANKA_REACH>, franka_ma_pair_kernel<IGE_FRANKA_COLLECT>,
+                                       franka_ma_pair_kernel<IGE_FRANKA_COMBINE>, franka_ma_pair_kernel<IGE_FRANKA_PP>};
+        k = pair[p->variant];
+    }
     if (pair_only) {
-        franka_ma_kernel<<<grid, NT, 0, s>>>(*p, *b, PH_RESET, ige_use_tma());
+        k<<<grid, NT, 0, s>>>(*p, *b, PH_RESET, ige_use_tma());
         if (int rc = ige_check_launch("ige_franka_ma_post_physics(reset)")) return rc;
-        franka_ma_kernel<<<grid, NT, smem, s>>>(*p, *b, PH_COMPUTE, ige_use_tma());
+        k<<<grid, NT, smem, s>>>(*p, *b, PH_COMPUTE, ige_use_tma());
     } else {
-        franka_ma_kernel<<<grid, NT, smem, s>>>(*p, *b, PH_FUSED, ige_use_tma());
+        k<<<grid, NT, smem, s>>>(*p, *b, PH_FUSED, ige_use_tma());
     }
     return ige_check_launch("ige_franka_ma_post_physics");
 }

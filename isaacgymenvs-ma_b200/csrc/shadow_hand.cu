@@ -94,66 +94,89 @@ __device__ __forceinline__ void reset_target(const IgeShadowHandParams &p, const
     b.reset_goal_buf[e] = 0;
 }
 
+// reset_idx (shadow_hand.py:604-668) for ONE env, by a whole warp: the 2*d + 5 + 2 + 1 uniforms are drawn one
+// (Philox call) per lane and parked in shared memory, then the rows are written item-parallel (DOF j by lane j,
+// rb_forces strided, the object row / goal pose / force probability by one lane each).  A single thread doing
+// this serially (~60 Philox calls) used to set the latency of the whole launch.
+__device__ void hand_reset_env_coop(const IgeShadowHandParams &p, const IgeShadowHandBuffers &b, uint64_t step, int e, int rk,
+                                    int lane, float *us) {
+    const IgeHandResetRand &r = p.rand;
+    const int d = p.num_hand_dofs, dpe = p.num_dofs_per_env, cols = 2 * d + 5;
+    // us[0 .. cols) draw 1 | us[cols], us[cols + 1] draw 2 | us[cols + 2] draw 3
+    for (int j = lane; j < cols + 3; j += 32) {
+        float u;
+        if (j < cols) u = hand_uniform(r, step, 1, rk, e, cols, j);
+        else if (j < cols + 2) u = hand_uniform(r, step, 2, rk, e, 4, j - cols);
+        else u = hand_uniform(r, step, 3, rk, e, 1, 0);
+        us[j] = u;
+    }
+    __syncwarp();
+    if (lane == 31) reset_target(p, b, e, sym_uniform(us[cols]), sym_uniform(us[cols + 1]));  // :613
+    float *rbf = b.rb_forces + (size_t)e * p.num_bodies * 3;
+    for (int i = lane; i < p.num_bodies * 3; i += 32) rbf[i] = 0.0f;  // :616
+    if (lane == 30) {
+        const long long oidx = b.object_indices[e];
+        float *obj = b.root_state_tensor + (size_t)oidx * 13;
+        const float *oi = b.object_init_state + (size_t)e * 13;
+        obj[0] = oi[0] + p.reset_position_noise * sym_uniform(us[0]);  // :619-623
+        obj[1] = oi[1] + p.reset_position_noise * sym_uniform(us[1]);
+        obj[2] = oi[2] + p.reset_position_noise * sym_uniform(us[2]);
+        float rot[4];
+        randomize_rotation(sym_uniform(us[3]), sym_uniform(us[4]), rot);  // :625
+#pragma unroll
+        for (int i = 0; i < 4; ++i) obj[3 + i] = rot[i];
+#pragma unroll
+        for (int i = 7; i < 13; ++i) obj[i] = 0.0f;
+        if (b.actor_dirty) b.actor_dirty[oidx] = 1;
+    }
+    if (lane == 29) {
+        const float l0 = logf(p.force_prob_range[0]), l1 = logf(p.force_prob_range[1]);  // :644-645
+        b.random_force_prob[e] = expf((l0 - l1) * us[cols + 2] + l1);
+        b.progress_buf[e] = 0;  // :666-668
+        b.reset_buf[e] = 0;
+        b.successes[e] = 0.0f;
+    }
+    for (int j = lane; j < d; j += 32) {  // :647-657
+        const float delta_max = p.dof_upper[j] - p.dof_default_pos[j];
+        const float delta_min = p.dof_lower[j] - p.dof_default_pos[j];
+        const float rj = sym_uniform(us[5 + j]);
+        const float rv = sym_uniform(us[5 + d + j]);
+        const float rand_delta = delta_min + (delta_max - delta_min) * 0.5f * (rj + 1.0f);
+        const float pos = p.dof_reset_base[j] + p.reset_dof_pos_noise * rand_delta;
+        const float vel = p.dof_default_vel[j] + p.reset_dof_vel_noise * rv;
+        reinterpret_cast<float2 *>(b.dof_state)[(size_t)e * dpe + j] = make_float2(pos, vel);
+        b.prev_targets[(size_t)e * dpe + j] = pos;
+        b.cur_targets[(size_t)e * dpe + j] = pos;
+    }
+    __syncwarp();
+}
+
 __global__ void __launch_bounds__(128) shadow_hand_reset_kernel(const __grid_constant__ IgeShadowHandParams p,
                                                                 const __grid_constant__ IgeShadowHandBuffers b) {
-    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    __shared__ float s_u[4][2 * IGE_MAX_DOF + 8];
+    const int e = blockIdx.x * blockDim.x + threadIdx.x, lane = threadIdx.x & 31;
     const IgeHandResetRand &r = p.rand;
     const uint64_t step = (r.mode == IGE_RAND_PHILOX && r.step) ? *reinterpret_cast<const volatile uint64_t *>(r.step) : 0ull;
     bool env = false;
+    int rk = 0;
     if (e < p.num_envs) {
         const bool goal = b.reset_goal_buf[e] != 0;
         env = b.reset_buf[e] != 0;
-        if (goal) {  // :675-679
-            const int rk = r.goal_rank ? __ldg(r.goal_rank + e) : 0;
-            reset_target(p, b, e, sym_uniform(hand_uniform(r, step, 0, rk, e, 4, 0)),
-                         sym_uniform(hand_uniform(r, step, 0, rk, e, 4, 1)));
-        }
-        if (env) {  // reset_idx :604-668
-            const int d = p.num_hand_dofs, dpe = p.num_dofs_per_env, cols = 2 * d + 5;
-            const int rk = r.env_rank ? __ldg(r.env_rank + e) : 0;
-            float rf[5];
-#pragma unroll
-            for (int j = 0; j < 5; ++j) rf[j] = sym_uniform(hand_uniform(r, step, 1, rk, e, cols, j));
-            reset_target(p, b, e, sym_uniform(hand_uniform(r, step, 2, rk, e, 4, 0)),
-                         sym_uniform(hand_uniform(r, step, 2, rk, e, 4, 1)));  // :613
-            float *rbf = b.rb_forces + (size_t)e * p.num_bodies * 3;
-            for (int i = 0; i < p.num_bodies * 3; ++i) rbf[i] = 0.0f;  // :616
-            const long long oidx = b.object_indices[e];
-            float *obj = b.root_state_tensor + (size_t)oidx * 13;
-            const float *oi = b.object_init_state + (size_t)e * 13;
-            obj[0] = oi[0] + p.reset_position_noise * rf[0];  // :619-623
-            obj[1] = oi[1] + p.reset_position_noise * rf[1];
-            obj[2] = oi[2] + p.reset_position_noise * rf[2];
-            float rot[4];
-            randomize_rotation(rf[3], rf[4], rot);  // :625
-#pragma unroll
-            for (int i = 0; i < 4; ++i) obj[3 + i] = rot[i];
-#pragma unroll
-            for (int i = 7; i < 13; ++i) obj[i] = 0.0f;
-            if (b.actor_dirty) b.actor_dirty[oidx] = 1;
-            const float l0 = logf(p.force_prob_range[0]), l1 = logf(p.force_prob_range[1]);  // :644-645
-            b.random_force_prob[e] = expf((l0 - l1) * hand_uniform(r, step, 3, rk, e, 1, 0) + l1);
-            for (int j = 0; j < d; ++j) {  // :647-657
-                const float delta_max = p.dof_upper[j] - p.dof_default_pos[j];
-                const float delta_min = p.dof_lower[j] - p.dof_default_pos[j];
-                const float rj = sym_uniform(hand_uniform(r, step, 1, rk, e, cols, 5 + j));
-                const float rv = sym_uniform(hand_uniform(r, step, 1, rk, e, cols, 5 + d + j));
-                const float rand_delta = delta_min + (delta_max - delta_min) * 0.5f * (rj + 1.0f);
-                const float pos = p.dof_reset_base[j] + p.reset_dof_pos_noise * rand_delta;
-                const float vel = p.dof_default_vel[j] + p.reset_dof_vel_noise * rv;
-                reinterpret_cast<float2 *>(b.dof_state)[(size_t)e * dpe + j] = make_float2(pos, vel);
-                b.prev_targets[(size_t)e * dpe + j] = pos;
-                b.cur_targets[(size_t)e * dpe + j] = pos;
-            }
-            b.progress_buf[e] = 0;  // :666-668
-            b.reset_buf[e] = 0;
-            b.successes[e] = 0.0f;
+        if (env) rk = r.env_rank ? __ldg(r.env_rank + e) : 0;
+        if (goal && !env) {  // :675-679 (for an env that also resets, reset_idx's own reset_target_pose :613 overwrites it)
+            const int grk = r.goal_rank ? __ldg(r.goal_rank + e) : 0;
+            reset_target(p, b, e, sym_uniform(hand_uniform(r, step, 0, grk, e, 4, 0)),
+                         sym_uniform(hand_uniform(r, step, 0, grk, e, 4, 1)));
         }
     }
+    const uint32_t mask = __ballot_sync(0xffffffffu, env);
+    for (uint32_t m = mask; m; m &= m - 1) {  // the warp resets its flagged envs one after the other, together
+        const int src = __ffs(m) - 1;
+        hand_reset_env_coop(p, b, step, e - lane + src, __shfl_sync(0xffffffffu, rk, src), lane, s_u[threadIdx.x >> 5]);
+    }
     if (b.list.scratch) {  // reset list == reset_buf.nonzero() at entry
-        const uint32_t mask = __ballot_sync(0xffffffffu, env);
-        if ((threadIdx.x & 31) == 0 && e < p.num_envs) ige::publish_tile_mask(b.list, e >> 5, mask);
-        ige::finish_reset_list(b.list, p.num_envs, nullptr, (threadIdx.x & 31) == 0);
+        if (lane == 0 && e < p.num_envs) ige::publish_tile_mask(b.list, e >> 5, mask);
+        ige::finish_reset_list(b.list, p.num_envs, nullptr, lane == 0);
     }
 }
 

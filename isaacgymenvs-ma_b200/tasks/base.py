@@ -220,6 +220,7 @@ class VecTaskB200:
     # -- pipeline=cpu: simulator state lives in pinned host memory ------------------------------
     HOST_SIM_ATTRS = ()      # task attributes that alias simulator / policy memory (set by subclasses)
     HOST_OUT_ATTRS = ("obs_buf", "rew_buf", "reset_buf")
+    HOST_INOUT_ATTRS = ()    # subset of HOST_SIM_ATTRS that reset_idx rewrites in place
 
     def map_host_sim(self, extra=()):
         """``sim_device=cpu pipeline=cpu`` (vec_task.py:82-88) without a staging copy: the simulator
@@ -231,12 +232,19 @@ class VecTaskB200:
         side.  Only the kernel launch touches them afterwards -- there is still no CPU compute path."""
         if self.device.type != "cuda":
             raise _lib.IgeError("map_host_sim() needs a CUDA device to run the kernels on")
+        names = [n for n in tuple(self.HOST_SIM_ATTRS) + tuple(self.HOST_OUT_ATTRS) + tuple(extra)
+                 if getattr(self, n, None) is not None]
+        moved = self._rehome(names, lambda t: torch.empty(t.shape, dtype=t.dtype, pin_memory=True))
+        self.host_mapped = moved
+        return moved
+
+    def _rehome(self, names, make):
+        """Replace the tensors behind the attributes `names` (and their entries in sim.tensors) by
+        ``make(old_tensor)`` holding the same values.  Returns {name: new tensor}."""
         moved = {}
-        for name in tuple(self.HOST_SIM_ATTRS) + tuple(self.HOST_OUT_ATTRS) + tuple(extra):
-            t = getattr(self, name, None)
-            if t is None:
-                continue
-            h = torch.empty(t.shape, dtype=t.dtype, pin_memory=True)
+        for name in names:
+            t = getattr(self, name)
+            h = make(t)
             h.copy_(t)
             setattr(self, name, h)
             for k, v in list(self.sim.tensors.items()):
@@ -244,7 +252,6 @@ class VecTaskB200:
                     self.sim.tensors[k] = h
             moved[name] = h
         torch.cuda.synchronize(self.device)
-        self.host_mapped = moved
         self._on_remap()
         return moved
 

@@ -10,6 +10,7 @@ class _Locomotion(VecTaskB200):
     HAS_DOF_FORCE = False
     SENSORS = 0
     HOST_SIM_ATTRS = ("root_states", "dof_state", "vec_sensor_tensor", "dof_force_tensor", "actions")
+    HOST_INOUT_ATTRS = ("dof_state",)
 
     def _on_remap(self):
         n, d = self.num_envs, self.num_dof

@@ -203,4 +203,5 @@ class ShadowHand(VecTaskB200):
         """shadow_hand.py:710-715 as ONE fused kernel."""
         p, b = self.abi_structs()
         _lib.call("ige_shadow_hand_post_physics", p, b, stream=self._stream())
-        self.extras["consecutive_successes"] = self.consecutive_successes.mean()   # shadow_hand.py:424
+        # shadow_hand.py:424 `.mean()` of the 1-element tensor == the element: a 0-dim view, no extra kernel
+        self.extras["consecutive_successes"] = self.consecutive_successes.reshape(())
