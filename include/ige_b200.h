@@ -360,6 +360,36 @@ typedef struct IgeFrankaMABuffers {
 int ige_franka_ma_post_physics(const IgeFrankaMAParams *p, const IgeFrankaMABuffers *b, void *stream);
 
 /* ------------------------------------------------------------------------------------------
+ * pre_physics_step action scaling: the clamp of VecTask.step
+ * (tasks/base/vec_task.py:373) fused with the task's action -> actuation map.  One launch each.
+ * actions_in must not alias actions.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct IgeActionForceArgs {        /* Ant tasks/ant.py:281-285, Humanoid tasks/humanoid.py:281-285 */
+    int32_t num_envs, num_dof;
+    float clip_actions;                    /* cfg env.clipActions; INFINITY = no clamp */
+    float power_scale;
+    float gears[IGE_MAX_DOF];              /* Ant joint_gears / Humanoid motor_efforts */
+    const float *actions_in;               /* (N, D) policy output */
+    float *actions;                        /* (N, D) self.actions = clamp(actions_in) */
+    float *forces;                         /* (N, D) actions * gears * power_scale -> set_dof_actuation_force_tensor */
+} IgeActionForceArgs;
+int ige_locomotion_pre_physics(const IgeActionForceArgs *a, void *stream);
+
+typedef struct IgeHandTargetArgs {         /* ShadowHand tasks/shadow_hand.py:684-698 */
+    int32_t num_envs, num_actions, num_dofs_per_env;
+    int32_t use_relative_control;
+    float clip_actions;
+    float speed_scale_dt;                  /* float32(shadow_hand_dof_speed_scale * dt), the Python product */
+    float act_moving_average, one_minus_mavg; /* float32(a), float32(1.0 - a) */
+    int32_t actuated[IGE_MAX_DOF];         /* actuated_dof_indices, by action column */
+    float lower[IGE_MAX_DOF], upper[IGE_MAX_DOF]; /* DOF limits of the actuated DOFs, by action column */
+    const float *actions_in;               /* (N, num_actions) */
+    float *actions;                        /* (N, num_actions) */
+    float *prev_targets, *cur_targets;     /* (N, num_dofs_per_env) */
+} IgeHandTargetArgs;
+int ige_shadow_hand_pre_physics_targets(const IgeHandTargetArgs *a, void *stream);
+
+/* ------------------------------------------------------------------------------------------
  * Library
  * ------------------------------------------------------------------------------------------ */
 int ige_version(void);

@@ -132,6 +132,18 @@ class IgeFrankaMABuffers(C.Structure):
                 ("reduce_scratch", _p), ("list", IgeResetList)]
 
 
+class IgeActionForceArgs(C.Structure):
+    _fields_ = [("num_envs", _i), ("num_dof", _i), ("clip_actions", _f), ("power_scale", _f),
+                ("gears", _f * IGE_MAX_DOF), ("actions_in", _p), ("actions", _p), ("forces", _p)]
+
+
+class IgeHandTargetArgs(C.Structure):
+    _fields_ = [("num_envs", _i), ("num_actions", _i), ("num_dofs_per_env", _i), ("use_relative_control", _i),
+                ("clip_actions", _f), ("speed_scale_dt", _f), ("act_moving_average", _f), ("one_minus_mavg", _f),
+                ("actuated", _i * IGE_MAX_DOF), ("lower", _f * IGE_MAX_DOF), ("upper", _f * IGE_MAX_DOF),
+                ("actions_in", _p), ("actions", _p), ("prev_targets", _p), ("cur_targets", _p)]
+
+
 def fill_array(carr, values):
     for i, v in enumerate(values):
         carr[i] = type(carr[0])(v) if isinstance(carr[0], int) else float(v)

@@ -19,6 +19,8 @@ _SIGS = {
     "ige_shadow_hand_reset": (_abi.IgeShadowHandParams, _abi.IgeShadowHandBuffers),
     "ige_shadow_hand_post_physics": (_abi.IgeShadowHandParams, _abi.IgeShadowHandBuffers),
     "ige_franka_ma_post_physics": (_abi.IgeFrankaMAParams, _abi.IgeFrankaMABuffers),
+    "ige_locomotion_pre_physics": (_abi.IgeActionForceArgs,),
+    "ige_shadow_hand_pre_physics_targets": (_abi.IgeHandTargetArgs,),
 }
 
 

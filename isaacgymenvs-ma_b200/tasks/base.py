@@ -186,7 +186,8 @@ class VecTaskB200:
 
     # -- vec_task.py:362-410 -------------------------------------------------------------------
     def step(self, actions):
-        action_tensor = torch.clamp(actions, -self.clip_actions, self.clip_actions)
+        # vec_task.py:373; tasks whose pre-physics kernel clamps itself (FUSED_ACTION_CLAMP) skip the extra pass
+        action_tensor = actions if self.FUSED_ACTION_CLAMP else torch.clamp(actions, -self.clip_actions, self.clip_actions)
         self.pre_physics_step(action_tensor)
         for _ in range(self.control_freq_inv):
             self.sim.simulate()
@@ -218,6 +219,7 @@ class VecTaskB200:
         return self.obs_dict
 
     # -- pipeline=cpu: simulator state lives in pinned host memory ------------------------------
+    FUSED_ACTION_CLAMP = False
     HOST_SIM_ATTRS = ()      # task attributes that alias simulator / policy memory (set by subclasses)
     HOST_OUT_ATTRS = ("obs_buf", "rew_buf", "reset_buf")
     HOST_INOUT_ATTRS = ()    # subset of HOST_SIM_ATTRS that reset_idx rewrites in place

@@ -11,6 +11,7 @@ class _Locomotion(VecTaskB200):
     SENSORS = 0
     HOST_SIM_ATTRS = ("root_states", "dof_state", "vec_sensor_tensor", "dof_force_tensor", "actions")
     HOST_INOUT_ATTRS = ("dof_state",)
+    FUSED_ACTION_CLAMP = True
 
     def _on_remap(self):
         n, d = self.num_envs, self.num_dof
@@ -40,6 +41,7 @@ class _Locomotion(VecTaskB200):
         self.dof_pos = self.dof_state.view(n, d, 2)[..., 0]
         self.dof_vel = self.dof_state.view(n, d, 2)[..., 1]
         self.actions = torch.zeros((n, d), device=self.device)
+        self.forces = None
 
     def adopt_state(self, st):
         """Task-owned tensors that the reference builds in __init__ (ant.py:88-114)."""
@@ -112,11 +114,22 @@ class _Locomotion(VecTaskB200):
         return u0, u1
 
     def pre_physics_step(self, actions):
-        # ant.py:281-285 / humanoid.py:281-285 (out of the hot path; plain torch)
-        self.actions.copy_(actions.to(self.device))
+        """ant.py:281-285 / humanoid.py:281-285 (+ the clamp of VecTask.step, vec_task.py:373) as one launch:
+        self.actions = clamp(actions), forces = actions * gears * power_scale."""
+        if self.forces is None:
+            self.forces = torch.zeros_like(self.actions)
+        src = actions.to(self.device, dtype=torch.float32).contiguous()
+        if src.data_ptr() == self.actions.data_ptr():
+            src = src.clone()
+        a = _abi.IgeActionForceArgs()
+        a.num_envs, a.num_dof = self.num_envs, self.num_dof
+        a.clip_actions, a.power_scale = self.clip_actions, self.power_scale
         gears = getattr(self, "motor_efforts", None)
-        forces = self.actions * (gears.unsqueeze(0) if gears is not None else 15.0) * self.power_scale
-        self.sim.set_indexed("set_dof_actuation_force_tensor", forces, None, None)
+        _abi.fill_array(a.gears, gears.tolist() if gears is not None else [15.0] * self.num_dof)  # ant.py joint_gears
+        a.actions_in, a.actions, a.forces = _ptr(src), _ptr(self.actions), _ptr(self.forces)
+        _lib.call("ige_locomotion_pre_physics", a, stream=self._stream())
+        self._actions_in = src          # keep the source alive until the stream has consumed it
+        self.sim.set_indexed("set_dof_actuation_force_tensor", self.forces, None, None)
 
     def post_physics_step(self):
         """ant.py:287-297 / humanoid.py:287-296 as: device-side nonzero() + ONE fused kernel."""

@@ -13,6 +13,8 @@ NUM_OBS = {"openai": 42, "full_no_vel": 77, "full": 157, "full_state": 211}
 
 
 class ShadowHand(VecTaskB200):
+    FUSED_ACTION_CLAMP = True
+
     def __init__(self, cfg, sim, device, **kw):
         cfg = dict(cfg)
         self.obs_type = cfg["obs_type"]
@@ -179,20 +181,34 @@ class ShadowHand(VecTaskB200):
             self.sim_reset_calls()
         self.apply_actions(actions)
 
+    def target_args(self, actions):
+        """IgeHandTargetArgs for `actions` (kept separate so that tests can hand the same struct to the oracle)."""
+        src = actions.to(self.device, dtype=torch.float32).contiguous()
+        if src.data_ptr() == self.actions.data_ptr():
+            src = src.clone()
+        a = _abi.IgeHandTargetArgs()
+        a.num_envs, a.num_actions = self.num_envs, self.num_actions
+        a.num_dofs_per_env = self.cur_targets.shape[1]
+        a.use_relative_control = int(self.use_relative_control)
+        a.clip_actions = self.clip_actions
+        a.speed_scale_dt = self.shadow_hand_dof_speed_scale * self.dt      # the Python-float product, then fp32
+        a.act_moving_average = self.act_moving_average
+        a.one_minus_mavg = 1.0 - self.act_moving_average
+        idx = self.actuated_dof_indices.tolist()
+        _abi.fill_array(a.actuated, idx)
+        _abi.fill_array(a.lower, self.shadow_hand_dof_lower_limits[self.actuated_dof_indices].tolist())
+        _abi.fill_array(a.upper, self.shadow_hand_dof_upper_limits[self.actuated_dof_indices].tolist())
+        a.actions_in, a.actions = _ptr(src), _ptr(self.actions)
+        a.prev_targets, a.cur_targets = _ptr(self.prev_targets), _ptr(self.cur_targets)
+        return a, src
+
     def apply_actions(self, actions):
-        """shadow_hand.py:684-698: actions -> position targets (outside the hot path, plain torch)."""
-        self.actions.copy_(actions.to(self.device))
-        idx = self.actuated_dof_indices
-        lo, hi = self.shadow_hand_dof_lower_limits[idx], self.shadow_hand_dof_upper_limits[idx]
-        if self.use_relative_control:
-            targets = self.prev_targets[:, idx] + self.shadow_hand_dof_speed_scale * self.dt * self.actions
-            self.cur_targets[:, idx] = torch.max(torch.min(targets, hi), lo)
-        else:
-            self.cur_targets[:, idx] = 0.5 * (self.actions + 1.0) * (hi - lo) + lo
-            self.cur_targets[:, idx] = self.act_moving_average * self.cur_targets[:, idx] + \
-                (1.0 - self.act_moving_average) * self.prev_targets[:, idx]
-            self.cur_targets[:, idx] = torch.max(torch.min(self.cur_targets[:, idx], hi), lo)
-        self.prev_targets[:, idx] = self.cur_targets[:, idx]
+        """shadow_hand.py:684-698 (+ the clamp of VecTask.step, vec_task.py:373) as one launch: actions ->
+        position targets of the actuated DOFs (absolute + moving average, or relative), limit clamp,
+        prev_targets update."""
+        a, src = self.target_args(actions)
+        _lib.call("ige_shadow_hand_pre_physics_targets", a, stream=self._stream())
+        self._actions_in = src
         self.sim.set_indexed("set_dof_position_target_tensor", self.cur_targets, None, None)
 
     def hot_step(self):

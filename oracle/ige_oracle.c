@@ -994,3 +994,53 @@ int ige_oracle_franka_ma_post_physics(const IgeFrankaMAParams *p, const IgeFrank
     if (b->list.scratch && p->rand.step) *p->rand.step += 1;
     return 0;
 }
+
+/* ------------------------------------------------------------------------------------------
+ * pre_physics_step action scaling
+ * ------------------------------------------------------------------------------------------ */
+static float clamp_sym(float x, float c) { /* torch.clamp(x, -c, c), tasks/base/vec_task.py:373 */
+    x = x < -c ? -c : x;
+    return x > c ? c : x;
+}
+
+/* Ant.pre_physics_step tasks/ant.py:281-285 / Humanoid tasks/humanoid.py:281-285:
+ * forces = self.actions * gears * self.power_scale (left to right), after the clamp of VecTask.step. */
+int ige_oracle_locomotion_pre_physics(const IgeActionForceArgs *a) {
+    const int D = a->num_dof;
+    for (long long i = 0; i < (long long)a->num_envs * D; ++i) {
+        const float x = clamp_sym(a->actions_in[i], a->clip_actions);
+        a->actions[i] = x;
+        const float t = x * a->gears[i % D];
+        a->forces[i] = t * a->power_scale;
+    }
+    return 0;
+}
+
+/* ShadowHand.pre_physics_step tasks/shadow_hand.py:684-698 (targets part; utils/torch_jit_utils.py:229-235
+ * scale / tensor_clamp). */
+int ige_oracle_shadow_hand_pre_physics_targets(const IgeHandTargetArgs *a) {
+    const int NA = a->num_actions, DPE = a->num_dofs_per_env;
+    for (int e = 0; e < a->num_envs; ++e)
+        for (int j = 0; j < NA; ++j) {
+            const float x = clamp_sym(a->actions_in[(size_t)e * NA + j], a->clip_actions);
+            a->actions[(size_t)e * NA + j] = x;
+            const size_t t = (size_t)e * DPE + a->actuated[j];
+            const float lo = a->lower[j], hi = a->upper[j], prev = a->prev_targets[t];
+            float cur;
+            if (a->use_relative_control) {
+                const float d = a->speed_scale_dt * x; /* :686 */
+                cur = prev + d;
+            } else {
+                const float s0 = 0.5f * (x + 1.0f);    /* scale(): 0.5 * (x + 1.0) * (upper - lower) + lower */
+                const float s1 = s0 * (hi - lo);
+                cur = s1 + lo;
+                const float m0 = a->act_moving_average * cur, m1 = a->one_minus_mavg * prev; /* :692-693 */
+                cur = m0 + m1;
+            }
+            cur = cur < hi ? cur : hi;                   /* torch.max(torch.min(t, upper), lower) */
+            cur = cur > lo ? cur : lo;
+            a->cur_targets[t] = cur;
+            a->prev_targets[t] = cur;                    /* :697 */
+        }
+    return 0;
+}

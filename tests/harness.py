@@ -131,7 +131,8 @@ def oracle_step_hand(obj, rands=None):
     p, b = obj.abi_structs()
     oracle.call("shadow_hand_reset", p, b)
     obj._u = {}
-    obj.apply_actions(obj.actions.clone())
+    a, src = obj.target_args(obj.actions.clone())        # shadow_hand.py:684-698
+    oracle.call("shadow_hand_pre_physics_targets", a)
     p, b = obj.abi_structs()
     oracle.call("shadow_hand_post_physics", p, b)
     return ids

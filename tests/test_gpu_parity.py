@@ -318,3 +318,63 @@ def test_host_staged_pipeline_matches_plain_envs(task, n, graph):
         for name in ("obs_buf", "rew_buf", "reset_buf"):
             H.assert_equal(f"group {g} {name}", pipe.host_out[g][name].numpy(), getattr(e, name).cpu().numpy())
         H.assert_equal(f"group {g} dof_state", pipe.host_in[g]["dof_state"].numpy(), e.dof_state.cpu().numpy())
+
+
+# ---- pre_physics_step action scaling -----------------------------------------------------
+def _oracle_call(name, args):
+    from oracle import oracle
+    oracle.call(name, args)
+
+
+@pytest.mark.parametrize("task,n", [("Ant", 16384), ("Humanoid", 1001)])
+def test_locomotion_pre_physics_forces(task, n):
+    """clamp + actions * gears * power_scale: bit-exact against the oracle and against the reference's own torch
+    expression (ant.py:283 / humanoid.py:283) evaluated on the CPU."""
+    env = H.pkg.make(3, task, n, "cuda:0")
+    env.clip_actions, env.power_scale = 1.0, 0.75
+    g = torch.Generator().manual_seed(5)
+    raw = (torch.rand((n, env.num_dof), generator=g) * 3.0 - 1.5)
+    env.pre_physics_step(raw.to("cuda:0"))
+    torch.cuda.synchronize()
+    act = torch.clamp(raw, -1.0, 1.0)
+    gears = env.motor_efforts.cpu() if hasattr(env, "motor_efforts") else torch.full((env.num_dof,), 15.0)
+    want = act * gears.unsqueeze(0) * 0.75
+    H.assert_equal("actions", env.actions.cpu().numpy(), act.numpy())
+    H.assert_equal("forces", env.forces.cpu().numpy(), want.numpy())
+    a = H.pkg._abi.IgeActionForceArgs()
+    a.num_envs, a.num_dof, a.clip_actions, a.power_scale = n, env.num_dof, 1.0, 0.75
+    H.pkg._abi.fill_array(a.gears, gears.tolist())
+    src, o_act, o_f = raw.numpy().copy(), np.zeros((n, env.num_dof), np.float32), np.zeros((n, env.num_dof), np.float32)
+    a.actions_in, a.actions, a.forces = src.ctypes.data, o_act.ctypes.data, o_f.ctypes.data
+    _oracle_call("locomotion_pre_physics", a)
+    H.assert_equal("oracle forces", env.forces.cpu().numpy(), o_f)
+
+
+@pytest.mark.parametrize("relative", [False, True])
+@pytest.mark.parametrize("mavg", [1.0, 0.3])
+def test_shadow_hand_pre_physics_targets(relative, mavg):
+    """shadow_hand.py:684-698 on the device == the same lines in torch on the CPU == the oracle."""
+    n = 2050
+    st = H.pkg.synthetic.make_state("shadow_hand", n, seed=2, reset_prob=0.0, goal_reset_prob=0.0)
+    env = H.build("shadow_hand", st, "cuda:0", rand_mode="philox")
+    env.use_relative_control, env.act_moving_average = relative, mavg
+    g = torch.Generator().manual_seed(6)
+    raw = torch.rand((n, 20), generator=g) * 3.0 - 1.5
+    prev = env.prev_targets.cpu().clone()
+    cur = env.cur_targets.cpu().clone()
+    env.apply_actions(raw.to("cuda:0"))
+    torch.cuda.synchronize()
+    act = torch.clamp(raw, -1.0, 1.0)
+    idx = env.actuated_dof_indices.cpu()
+    lo, hi = env.shadow_hand_dof_lower_limits.cpu()[idx], env.shadow_hand_dof_upper_limits.cpu()[idx]
+    if relative:
+        targets = prev[:, idx] + env.shadow_hand_dof_speed_scale * env.dt * act
+        cur[:, idx] = torch.max(torch.min(targets, hi), lo)
+    else:
+        cur[:, idx] = 0.5 * (act + 1.0) * (hi - lo) + lo
+        cur[:, idx] = mavg * cur[:, idx] + (1.0 - mavg) * prev[:, idx]
+        cur[:, idx] = torch.max(torch.min(cur[:, idx], hi), lo)
+    prev[:, idx] = cur[:, idx]
+    H.assert_equal("actions", env.actions.cpu().numpy(), act.numpy())
+    H.assert_equal("cur_targets", env.cur_targets.cpu().numpy(), cur.numpy())
+    H.assert_equal("prev_targets", env.prev_targets.cpu().numpy(), prev.numpy())
