@@ -158,8 +158,7 @@ def run_ours(args):
         # episode statistics: <= 16 floats, once per horizon, off the critical path
         if dist is None:
             return
-        reducer.wait()
-        reducer.start(envs[0].stats)
+        reducer.start(lambda: envs[0].stats)      # side stream: the step stream never waits for the collective
 
     def timed(steps, warmup):
         full, rem = divmod(steps, HORIZON)
@@ -169,6 +168,8 @@ def run_ours(args):
                 allreduce_stats()
             for i in range(rem):
                 single[i][0].replay()
+            if dist is not None:
+                reducer.wait()          # the last horizon's collective ends inside the timed region
         wfull = -(-warmup // HORIZON)
         for i in range(max(wfull, 1)):
             chunks[i % len(chunks)][0].replay()

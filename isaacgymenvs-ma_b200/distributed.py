@@ -51,22 +51,40 @@ def rank_seed(seed, rank):
 
 class StatsReducer:
     """Sum all-reduce of the episode-statistics vector, off the step's critical path: the step
-    kernels keep adding into the env's accumulator while a snapshot is being reduced."""
+    kernels keep adding into the env's accumulator while a snapshot is being reduced.
+
+    On CUDA the snapshot and the NCCL all-reduce are issued on a SIDE stream that only waits for the step
+    stream's work up to now; the step stream never waits for the collective (a `work.wait()` on the step
+    stream put the ~15 us all-reduce latency into every horizon: 89 % weak-scaling efficiency at 2 GPUs).
+    ``wait()`` joins the side stream when the reduced numbers are actually needed."""
 
     def __init__(self, device):
+        self.device = torch.device(device)
         self.snap = torch.zeros(_abi.IGE_NUM_STATS, dtype=torch.float32, device=device)
+        self.side = torch.cuda.Stream(self.device) if self.device.type == "cuda" else None
         self._work = None
 
     def start(self, stats_vector):
+        """`stats_vector`: the [IGE_NUM_STATS] tensor, or a callable returning it (evaluated on the side stream)."""
         import torch.distributed as dist
-        self.snap.copy_(stats_vector)
-        if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
-            self._work = dist.all_reduce(self.snap, op=dist.ReduceOp.SUM, async_op=True)
+        multi = dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
+        if self.side is None:
+            self.snap.copy_(stats_vector() if callable(stats_vector) else stats_vector)
+            if multi:
+                self._work = dist.all_reduce(self.snap, op=dist.ReduceOp.SUM, async_op=True)
+            return
+        self.side.wait_stream(torch.cuda.current_stream(self.device))
+        with torch.cuda.stream(self.side):
+            self.snap.copy_(stats_vector() if callable(stats_vector) else stats_vector)
+            if multi:
+                dist.all_reduce(self.snap, op=dist.ReduceOp.SUM, async_op=True).wait()   # side stream waits, not the step's
 
     def wait(self):
         if self._work is not None:
             self._work.wait()
             self._work = None
+        if self.side is not None:
+            torch.cuda.current_stream(self.device).wait_stream(self.side)
         return self.snap
 
     def result(self):
