@@ -98,6 +98,16 @@ class ClockSampler:
                 "reasons": reasons, "samples": len(self.samples)}
 
 
+def ncu_traffic(task, n):
+    """DRAM bytes per launch of the dominant kernel from the committed ncu --set full capture (profiles/traffic.json),
+    or None when this (task, num_envs) was not captured."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            return json.load(f).get(task, {}).get(str(n))
+    except (OSError, ValueError):
+        return None
+
+
 def build_replicas(pkg, task, num_envs, replicas, device, seed, fall_frac, fuse_epilogue, rank):
     envs = []
     for r in range(replicas):
@@ -232,7 +242,7 @@ def run_ours(args):
                    "launch": f"CUDA graph, {HORIZON} steps per graph; stats all-reduce every {HORIZON} steps"},
         "gpu_launches": gpu_launches,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": None, "peak_source": f"MEASURED_PEAKS.json hbm_gbs ({peak_kind})",
+                     "traffic": ncu_traffic(task, n), "peak_source": f"MEASURED_PEAKS.json hbm_gbs ({peak_kind})",
                      "kernel": KERNEL_NAME[task], "kernel_us": kernel_s * 1e6,
                      "algorithmic_bytes_per_env": algo},
     }

@@ -417,12 +417,13 @@ __global__ void __launch_bounds__(NT) shadow_hand_post_physics_kernel(const __gr
 // round trips (object_indices -> object row is the second) instead of ~12.  Per-CTA partial sums stay in
 // registers across tiles: 3 global atomics per CTA, not per tile.
 constexpr int FD = 24, FA = 20, FS = 30, FT_N = 5;
-constexpr int kFastCtasPerSm = 2;
-constexpr int FNT = 512;       // threads per CTA of the fast kernel
+constexpr int kFastCtasPerSm = 4;
+constexpr int FNT = 256;       // threads per CTA of the fast kernel
 constexpr int CT = FNT - 32;   // element threads (warp 0 is the env warp)
-constexpr int KD = (TE * FD + CT - 1) / CT, KS = (TE * FS / 4 + CT - 1) / CT, KF = (TE * 65 + CT - 1) / CT,
-              KP = (TE * 15 + CT - 1) / CT;   // loads per element thread: DOF rows, sensor vectors, fingertip floats
-static_assert(TE * FD / 4 <= CT && TE * FA / 4 <= CT && KS <= 2, "fast kernel: one vector per thread for force / actions");
+// column-owner mapping: SUB threads share a column and split the 32 envs of the tile between them
+constexpr int DSUB = CT / FD, SSUB = CT / FS;
+constexpr int KD = (TE + DSUB - 1) / DSUB, KS = (TE + SSUB - 1) / SSUB;   // loads per thread: DOF rows, sensor floats
+static_assert(TE * FD / 4 <= CT && TE * FA / 4 <= CT, "fast kernel: one vector per thread for force / actions");
 struct SegOff { int dof_pos, dof_vel, dof_force, ft_state, ft_pos, sensors, actions; };
 // element-segment offsets of the four layouts (shadow_hand.py:473-584; same numbers as kLayout), compile-time
 __host__ __device__ constexpr SegOff seg_offsets(int layout) {
@@ -452,6 +453,8 @@ shadow_hand_post_physics_fast_kernel(const __grid_constant__ IgeShadowHandParams
     constexpr bool need_force = oo.dof_force >= 0 || asym;
     constexpr bool need_sens = oo.sensors >= 0 || asym;
     constexpr bool ft_full = oo.ft_state >= 0 || asym;
+    constexpr int FTW = ft_full ? 65 : 15, FTC = ft_full ? 13 : 3;   // fingertip block: 5 x (13 | 3) floats per env
+    constexpr int FSUB = CT / FTW, KF = (TE + FSUB - 1) / FSUB;
     if (tid < FD) {
         const float lo = p.dof_lower[tid], hi = p.dof_upper[tid];
         s_lo[tid] = lo; s_hi[tid] = hi; s_rspan[tid] = 1.0f / (hi - lo);
@@ -488,55 +491,49 @@ shadow_hand_post_physics_fast_kernel(const __grid_constant__ IgeShadowHandParams
             fill_env_segments(p, LAYOUT, nobs, obs_tile + lane * nobs, obj, goal, qd);
             if (asym) fill_env_segments(p, IGE_HAND_OBS_FULL_STATE, MAX_OBS, st_tile + lane * MAX_OBS, obj, goal, qd);
         } else {
-            // ---- element warps: every load of the tile first, then the scatter into the row-major tile(s) ----
+            // ---- element warps: every load of the tile first, then the scatter into the row-major tile(s).
+            //      Each thread owns ONE column of a segment and walks the envs with a fixed stride, so addresses
+            //      and tile offsets are a base + one add per element (no per-element divisions) ----
             const int ct = tid - 32;
             float2 dv[KD];
-            float4 fo = make_float4(0.f, 0.f, 0.f, 0.f), se0 = fo, se1 = fo, ac = fo;
-            float ft[KF];
-            if (need_dof) {
-                const float2 *src = reinterpret_cast<const float2 *>(b.dof_state) + (size_t)e0 * FD;
+            float sv[KS], ft[KF];
+            float4 fo = make_float4(0.f, 0.f, 0.f, 0.f), ac = fo;
+            // DOF rows: column j = ct % 24, envs sub, sub + DSUB, ...
+            const int dj = ct % FD, dsub = ct / FD;
+            // sensors: column ct % 30; fingertips: column ct % FTW of the (5 x 13 | 5 x 3) block
+            const int sj = ct % FS, ssub = ct / FS;
+            const int fc = ct % FTW, fsub = ct / FTW;
+            if (need_dof && dsub < DSUB) {
+                const float2 *src = reinterpret_cast<const float2 *>(b.dof_state) + (size_t)e0 * FD + dj;
 #pragma unroll
-                for (int k = 0; k < KD; ++k) { const int i = ct + k * CT; if (i < TE * FD) dv[k] = __ldg(src + i); }
+                for (int k = 0; k < KD; ++k) { const int le = dsub + k * DSUB; if (le < TE) dv[k] = __ldg(src + le * FD); }
             }
             if (need_force && ct < TE * FD / 4) fo = __ldg(reinterpret_cast<const float4 *>(b.dof_force_tensor + (size_t)e0 * FD) + ct);
-            if (need_sens) {
-                const float4 *src = reinterpret_cast<const float4 *>(b.vec_sensor_tensor + (size_t)e0 * FS);
-                if (ct < TE * FS / 4) se0 = __ldg(src + ct);
-                if (KS > 1 && ct + CT < TE * FS / 4) se1 = __ldg(src + ct + CT);
+            if (need_sens && ssub < SSUB) {
+                const float *src = b.vec_sensor_tensor + (size_t)e0 * FS + sj;
+#pragma unroll
+                for (int k = 0; k < KS; ++k) { const int le = ssub + k * SSUB; if (le < TE) sv[k] = __ldg(src + le * FS); }
             }
             if (ct < TE * FA / 4) ac = __ldg(reinterpret_cast<const float4 *>(b.actions + (size_t)e0 * FA) + ct);
-            const float *rb = b.rigid_body_states + (size_t)e0 * p.num_bodies * 13;
-            if (ft_full) {
+            if (fsub < FSUB) {
+                const int f = fc / FTC, kk = fc - f * FTC;
+                const int estride = p.num_bodies * 13;
+                const float *src = b.rigid_body_states + (size_t)e0 * estride + s_ft[f] * 13 + kk;
 #pragma unroll
-                for (int k = 0; k < KF; ++k) {
-                    const int i = ct + k * CT;
-                    if (i < TE * 65) {
-                        const int le = i / 65, r = i - le * 65, f = r / 13, kk = r - f * 13;
-                        ft[k] = __ldg(rb + ((size_t)le * p.num_bodies + s_ft[f]) * 13 + kk);
-                    }
-                }
-            } else {
-#pragma unroll
-                for (int k = 0; k < KP; ++k) {
-                    const int i = ct + k * CT;
-                    if (i < TE * 15) {
-                        const int le = i / 15, r = i - le * 15, f = r / 3, kk = r - f * 3;
-                        ft[k] = __ldg(rb + ((size_t)le * p.num_bodies + s_ft[f]) * 13 + kk);
-                    }
-                }
+                for (int k = 0; k < KF; ++k) { const int le = fsub + k * FSUB; if (le < TE) ft[k] = __ldg(src + (size_t)le * estride); }
             }
-            if (need_dof) {
+            if (need_dof && dsub < DSUB) {
+                const float lo = s_lo[dj], hi = s_hi[dj], rs = s_rspan[dj];
 #pragma unroll
                 for (int k = 0; k < KD; ++k) {
-                    const int i = ct + k * CT;
-                    if (i < TE * FD) {
-                        const int le = i / FD, j = i - le * FD;
+                    const int le = dsub + k * DSUB;
+                    if (le < TE) {
                         // unscale :499-500; the divisor is loop-invariant per column -> exact reciprocal division
-                        const float up = ige::div_by(2.0f * dv[k].x - s_hi[j] - s_lo[j], s_hi[j] - s_lo[j], s_rspan[j]);
+                        const float up = ige::div_by(2.0f * dv[k].x - hi - lo, hi - lo, rs);
                         const float uv = p.vel_obs_scale * dv[k].y;
-                        if (oo.dof_pos >= 0) obs_tile[le * nobs + oo.dof_pos + j] = up;
-                        if (oo.dof_vel >= 0) obs_tile[le * nobs + oo.dof_vel + j] = uv;
-                        if (asym) { st_tile[le * MAX_OBS + so.dof_pos + j] = up; st_tile[le * MAX_OBS + so.dof_vel + j] = uv; }
+                        if (oo.dof_pos >= 0) obs_tile[le * nobs + oo.dof_pos + dj] = up;
+                        if (oo.dof_vel >= 0) obs_tile[le * nobs + oo.dof_vel + dj] = uv;
+                        if (asym) { st_tile[le * MAX_OBS + so.dof_pos + dj] = up; st_tile[le * MAX_OBS + so.dof_vel + dj] = uv; }
                     }
                 }
             }
@@ -550,20 +547,14 @@ shadow_hand_post_physics_fast_kernel(const __grid_constant__ IgeShadowHandParams
                     if (asym) st_tile[le * MAX_OBS + so.dof_force + j + q] = x;
                 }
             }
-            if (need_sens) {
+            if (need_sens && ssub < SSUB) {
 #pragma unroll
-                for (int h = 0; h < KS; ++h) {
-                    const int i4 = ct + h * CT;
-                    if (i4 < TE * FS / 4) {
-                        const float4 sv = h ? se1 : se0;
-                        const float v[4] = {sv.x, sv.y, sv.z, sv.w};
-#pragma unroll
-                        for (int q = 0; q < 4; ++q) {   // 30 % 4 != 0: a vector may straddle two envs
-                            const int i = i4 * 4 + q, le = i / FS, j = i - le * FS;
-                            const float x = p.force_torque_obs_scale * v[q];
-                            if (oo.sensors >= 0) obs_tile[le * nobs + oo.sensors + j] = x;
-                            if (asym) st_tile[le * MAX_OBS + so.sensors + j] = x;
-                        }
+                for (int k = 0; k < KS; ++k) {
+                    const int le = ssub + k * SSUB;
+                    if (le < TE) {
+                        const float x = p.force_torque_obs_scale * sv[k];
+                        if (oo.sensors >= 0) obs_tile[le * nobs + oo.sensors + sj] = x;
+                        if (asym) st_tile[le * MAX_OBS + so.sensors + sj] = x;
                     }
                 }
             }
@@ -576,25 +567,20 @@ shadow_hand_post_physics_fast_kernel(const __grid_constant__ IgeShadowHandParams
                     if (asym) st_tile[le * MAX_OBS + so.actions + j + q] = v[q];
                 }
             }
-            if (ft_full) {
+            if (fsub < FSUB) {
+                const int f = fc / FTC, kk = fc - f * FTC;
 #pragma unroll
                 for (int k = 0; k < KF; ++k) {
-                    const int i = ct + k * CT;
-                    if (i < TE * 65) {
-                        const int le = i / 65, r = i - le * 65;
-                        if (oo.ft_state >= 0) obs_tile[le * nobs + oo.ft_state + r] = ft[k];
-                        if (oo.ft_pos >= 0) {
-                            const int f = r / 13, kk = r - f * 13;
-                            if (kk < 3) obs_tile[le * nobs + oo.ft_pos + f * 3 + kk] = ft[k];
+                    const int le = fsub + k * FSUB;
+                    if (le < TE) {
+                        if (ft_full) {
+                            if (oo.ft_state >= 0) obs_tile[le * nobs + oo.ft_state + fc] = ft[k];
+                            if (oo.ft_pos >= 0 && kk < 3) obs_tile[le * nobs + oo.ft_pos + f * 3 + kk] = ft[k];
+                            if (asym) st_tile[le * MAX_OBS + so.ft_state + fc] = ft[k];
+                        } else {
+                            obs_tile[le * nobs + oo.ft_pos + fc] = ft[k];
                         }
-                        if (asym) st_tile[le * MAX_OBS + so.ft_state + r] = ft[k];
                     }
-                }
-            } else {
-#pragma unroll
-                for (int k = 0; k < KP; ++k) {
-                    const int i = ct + k * CT;
-                    if (i < TE * 15) { const int le = i / 15, r = i - le * 15; obs_tile[le * nobs + oo.ft_pos + r] = ft[k]; }
                 }
             }
         }

@@ -20,6 +20,7 @@ def main():
     ap.add_argument("--steps", type=int, default=4)
     ap.add_argument("--replicas", type=int, default=4)
     ap.add_argument("--epilogue", action="store_true")
+    ap.add_argument("--hot", action="store_true", help="hot_step() (incl. the pre-physics reset of ShadowHand)")
     ap.add_argument("--fall-frac", type=float, default=0.02)
     a = ap.parse_args()
     pkg = load_package()
@@ -31,7 +32,7 @@ def main():
         envs.append(e)
     torch.cuda.synchronize()
     for s in range(a.steps):
-        envs[s % a.replicas].post_physics_step()
+        (envs[s % a.replicas].hot_step if a.hot else envs[s % a.replicas].post_physics_step)()
     torch.cuda.synchronize()
     print("ok", a.task, a.num_envs, a.steps)
 
