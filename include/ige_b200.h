@@ -390,6 +390,60 @@ typedef struct IgeHandTargetArgs {         /* ShadowHand tasks/shadow_hand.py:68
 int ige_shadow_hand_pre_physics_targets(const IgeHandTargetArgs *a, void *stream);
 
 /* ------------------------------------------------------------------------------------------
+ * Agent-side per-step bookkeeping of A2CAgentMA.play_steps: the immediate
+ * consumer of rew_buf / reset_buf / time_outs.  ONE launch replaces learning/A2CAgent_MA.py:35-56
+ * (rewards_shaper, time-out value bootstrap, experience_buffer 'rewards'[n] and next 'dones',
+ * current_rewards / current_shaped_rewards / current_lengths accumulate + done masking,
+ * env_done_indices = dones.nonzero()[::num_agents], the three AverageMeter updates) -- about 15 torch
+ * launches and one host sync (len(env_done_indices)) in the reference.
+ * rl_games (setup.py:23 "rl-games>=1.6.0", not vendored) supplies DefaultRewardsShaper
+ * ((r + shift) * scale, clamp) and AverageMeter (windowed mean); their published algorithms are
+ * restated here and in the oracle.
+ * ------------------------------------------------------------------------------------------ */
+#define IGE_METER_REWARDS 0        /* game_rewards         <- current_rewards[env_done_indices] */
+#define IGE_METER_SHAPED_REWARDS 1 /* game_shaped_rewards  <- current_shaped_rewards[...] */
+#define IGE_METER_LENGTHS 2        /* game_lengths         <- current_lengths[...] */
+typedef struct IgeRolloutStepArgs {
+    int32_t num_rows;              /* batch rows = num_envs * num_agents (row = env*A + agent) */
+    int32_t num_agents;            /* A: every A-th entry of dones.nonzero() is kept (:45) */
+    int32_t value_bootstrap;       /* config value_bootstrap and 'time_outs' in infos (:36) */
+    int32_t meter_max_size;        /* games_to_track */
+    float gamma;
+    float shaper_shift, shaper_scale; /* DefaultRewardsShaper: (r + shift_value) * scale_value */
+    float shaper_min, shaper_max;  /* then clamp; -INFINITY / INFINITY = none */
+    const float *rewards;          /* (rows) rew_buf as returned by env.step */
+    const int64_t *dones;          /* (rows) reset_buf as returned by env.step */
+    const uint8_t *time_outs;      /* (rows) extras["time_outs"]; may be NULL when !value_bootstrap */
+    const float *values;           /* (rows) res_dict['values']; may be NULL when !value_bootstrap */
+    float *mb_rewards;             /* (rows) experience_buffer 'rewards'[n] out */
+    uint8_t *dones_out;            /* (rows) optional out: dones as uint8 == what update_data('dones', n+1, self.dones)
+                                      stores at the next step (:23) */
+    float *current_rewards, *current_shaped_rewards, *current_lengths; /* (rows) in/out */
+    int32_t *done_rows;            /* (rows) out: env_done_indices (ROW ids, ascending); first *done_count valid */
+    int32_t *done_count;           /* [1] out */
+    float *meter_mean;             /* [3] in/out: AverageMeter.mean of IGE_METER_* */
+    int32_t *meter_size;           /* [3] in/out: AverageMeter.current_size */
+    double *reduce_scratch;        /* [4] zeroed ONCE by the caller; left zero by every launch */
+    uint32_t *scratch;             /* [ige_compact_scratch_words(num_rows)] zeroed ONCE; left zero by every launch */
+} IgeRolloutStepArgs;
+int ige_ma_rollout_step(const IgeRolloutStepArgs *a, void *stream);
+
+/* A2CBase.discount_values (rl_games GAE) as called from learning/A2CAgent_MA.py:60-66, plus
+ * mb_returns = mb_advs + mb_values (:67).  Thread per row walks the horizon backwards. */
+typedef struct IgeDiscountArgs {
+    int32_t num_rows, horizon;
+    float gamma, gamma_tau;        /* float32(gamma), float32(gamma * tau) (the Python double product) */
+    const uint8_t *dones;          /* (rows) self.dones after the last step */
+    const float *last_values;      /* (rows) */
+    const uint8_t *mb_dones;       /* (horizon, rows) */
+    const float *mb_values;        /* (horizon, rows) */
+    const float *mb_rewards;       /* (horizon, rows) */
+    float *mb_advs;                /* (horizon, rows) out, optional */
+    float *mb_returns;             /* (horizon, rows) out */
+} IgeDiscountArgs;
+int ige_ma_discount_values(const IgeDiscountArgs *a, void *stream);
+
+/* ------------------------------------------------------------------------------------------
  * Library
  * ------------------------------------------------------------------------------------------ */
 int ige_version(void);

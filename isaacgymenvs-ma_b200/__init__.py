@@ -6,3 +6,4 @@ from . import factory  # noqa: E402,F401
 from .factory import make  # noqa: E402,F401
 from . import distributed  # noqa: E402,F401
 from . import host_pipeline  # noqa: E402,F401
+from . import rollout  # noqa: E402,F401

@@ -144,6 +144,21 @@ class IgeHandTargetArgs(C.Structure):
                 ("actions_in", _p), ("actions", _p), ("prev_targets", _p), ("cur_targets", _p)]
 
 
+class IgeRolloutStepArgs(C.Structure):
+    _fields_ = [("num_rows", _i), ("num_agents", _i), ("value_bootstrap", _i), ("meter_max_size", _i),
+                ("gamma", _f), ("shaper_shift", _f), ("shaper_scale", _f), ("shaper_min", _f), ("shaper_max", _f),
+                ("rewards", _p), ("dones", _p), ("time_outs", _p), ("values", _p), ("mb_rewards", _p),
+                ("dones_out", _p), ("current_rewards", _p), ("current_shaped_rewards", _p),
+                ("current_lengths", _p), ("done_rows", _p), ("done_count", _p), ("meter_mean", _p),
+                ("meter_size", _p), ("reduce_scratch", _p), ("scratch", _p)]
+
+
+class IgeDiscountArgs(C.Structure):
+    _fields_ = [("num_rows", _i), ("horizon", _i), ("gamma", _f), ("gamma_tau", _f), ("dones", _p),
+                ("last_values", _p), ("mb_dones", _p), ("mb_values", _p), ("mb_rewards", _p), ("mb_advs", _p),
+                ("mb_returns", _p)]
+
+
 def fill_array(carr, values):
     for i, v in enumerate(values):
         carr[i] = type(carr[0])(v) if isinstance(carr[0], int) else float(v)

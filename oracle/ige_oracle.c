@@ -1044,3 +1044,81 @@ int ige_oracle_shadow_hand_pre_physics_targets(const IgeHandTargetArgs *a) {
         }
     return 0;
 }
+
+/* ------------------------------------------------------------------------------------------
+ * Agent-side bookkeeping of A2CAgentMA.play_steps, learning/A2CAgent_MA.py:35-56.
+ * rl_games pieces (setup.py:23 "rl-games>=1.6.0", not vendored) restated from their published source:
+ * DefaultRewardsShaper.__call__ = clamp((r + shift_value) * scale_value, min_val, max_val);
+ * AverageMeter.update(values): new_mean = mean(values); size = clip(len, 0, max_size);
+ * old_size = min(max_size - size, current_size); mean = (mean*old_size + new_mean*size) / (old_size+size).
+ * ------------------------------------------------------------------------------------------ */
+int ige_oracle_ma_rollout_step(const IgeRolloutStepArgs *a) {
+    const int n = a->num_rows, A = a->num_agents;
+    int rank = 0, kept = 0;
+    double sum[3] = {0.0, 0.0, 0.0};
+    for (int r = 0; r < n; ++r) {
+        float s = a->rewards[r] + a->shaper_shift;          /* :34 self.rewards_shaper(rewards) */
+        s = s * a->shaper_scale;
+        s = s < a->shaper_min ? a->shaper_min : s;
+        s = s > a->shaper_max ? a->shaper_max : s;
+        if (a->value_bootstrap) {                            /* :35-36 */
+            const float gv = a->gamma * a->values[r];
+            s = s + gv * (float)a->time_outs[r];
+        }
+        a->mb_rewards[r] = s;                                /* :38 */
+        const float cr = a->current_rewards[r] + a->rewards[r]; /* :40-42 */
+        const float cs = a->current_shaped_rewards[r] + s;
+        const float cl = a->current_lengths[r] + 1.0f;
+        const int done = a->dones[r] != 0;
+        if (done) {                                          /* :43-44 all_done_indices[::num_agents] */
+            if (rank % A == 0) {
+                a->done_rows[kept++] = r;
+                sum[0] += cr, sum[1] += cs, sum[2] += cl;    /* :46-48 (values before the masking below) */
+            }
+            ++rank;
+        }
+        const float nd = 1.0f - (float)a->dones[r];          /* :51 */
+        a->current_rewards[r] = cr * nd;                     /* :53-55 */
+        a->current_shaped_rewards[r] = cs * nd;
+        a->current_lengths[r] = cl * nd;
+        if (a->dones_out) a->dones_out[r] = (uint8_t)a->dones[r];
+    }
+    *a->done_count = kept;
+    if (kept > 0)
+        for (int m = 0; m < 3; ++m) {                        /* AverageMeter.update */
+            const float new_mean = (float)sum[m] / (float)kept;
+            const int size = kept < a->meter_max_size ? kept : a->meter_max_size;
+            int old_size = a->meter_max_size - size;
+            if (a->meter_size[m] < old_size) old_size = a->meter_size[m];
+            const int size_sum = old_size + size;
+            a->meter_size[m] = size_sum;
+            const float x = a->meter_mean[m] * (float)old_size, y = new_mean * (float)size;
+            a->meter_mean[m] = (x + y) / (float)size_sum;
+        }
+    return 0;
+}
+
+/* rl_games A2CBase.discount_values as called from learning/A2CAgent_MA.py:60-66, and :67
+ * mb_returns = mb_advs + mb_values. */
+int ige_oracle_ma_discount_values(const IgeDiscountArgs *a) {
+    const size_t n = (size_t)a->num_rows;
+    for (size_t r = 0; r < n; ++r) {
+        float lastgaelam = 0.0f, nextvalues = a->last_values[r], nnt = 1.0f - (float)a->dones[r];
+        for (int t = a->horizon - 1; t >= 0; --t) {
+            const size_t i = (size_t)t * n + r;
+            const float v = a->mb_values[i];
+            const float gv = a->gamma * nextvalues;
+            const float t1 = gv * nnt;
+            const float t2 = a->mb_rewards[i] + t1;
+            const float delta = t2 - v;
+            const float gl = a->gamma_tau * nnt;
+            const float t3 = gl * lastgaelam;
+            lastgaelam = delta + t3;
+            if (a->mb_advs) a->mb_advs[i] = lastgaelam;
+            a->mb_returns[i] = lastgaelam + v;
+            nextvalues = v;
+            nnt = 1.0f - (float)a->mb_dones[i];
+        }
+    }
+    return 0;
+}

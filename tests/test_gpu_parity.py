@@ -4,6 +4,8 @@ Bars (north_star): done flags, reset indices, progress counters bit-exact; obs /
 1e-5 relative (|d| <= 1e-5 * max(1, |ref|)); potentials and reset DOF rows bit-exact."""
 import ctypes as C
 
+import os
+
 import numpy as np
 import pytest
 import torch
@@ -378,3 +380,44 @@ def test_shadow_hand_pre_physics_targets(relative, mavg):
     H.assert_equal("actions", env.actions.cpu().numpy(), act.numpy())
     H.assert_equal("cur_targets", env.cur_targets.cpu().numpy(), cur.numpy())
     H.assert_equal("prev_targets", env.prev_targets.cpu().numpy(), prev.numpy())
+
+
+# ---- agent-side rollout bookkeeping (A2CAgent_MA.py:35-67) ---------------------------------
+def _rollout_blob(num_rows, A, Hz, seed, done_prob, paired, boot=True, track=100):
+    g = torch.Generator().manual_seed(seed)
+    if paired:
+        d = (torch.rand((Hz, num_rows // A), generator=g) < done_prob).repeat_interleave(A, dim=1)
+    else:
+        d = torch.rand((Hz, num_rows), generator=g) < done_prob
+    blob = {
+        "rewards": torch.randn((Hz, num_rows), generator=g) * 3.0, "values": torch.randn((Hz, num_rows), generator=g),
+        "dones": d.to(torch.long), "time_outs": (d & (torch.rand((Hz, num_rows), generator=g) < 0.3)).to(torch.uint8),
+        "last_values": torch.randn((num_rows,), generator=g),
+        "init_current_rewards": torch.randn((num_rows,), generator=g) * 5.0,
+        "init_current_shaped_rewards": torch.randn((num_rows,), generator=g) * 0.05,
+        "init_current_lengths": torch.randint(0, 50, (num_rows,), generator=g).float(),
+        "init_dones": (torch.rand((num_rows,), generator=g) < 0.1).to(torch.uint8),
+    }
+    blob = {k: v.numpy() for k, v in blob.items()}
+    blob.update(cfg_num_agents=A, cfg_horizon=Hz, cfg_value_bootstrap=int(boot), cfg_games_to_track=track,
+                cfg_gamma=0.99, cfg_tau=0.95, cfg_scale=0.01, cfg_shift=0.0, cfg_min=-np.inf, cfg_max=np.inf)
+    return blob
+
+
+def test_rollout_step_matches_reference_golden():
+    """ige_ma_rollout_step + ige_ma_discount_values on the device == what the reference's own play_steps wrote."""
+    import rollout_harness as R
+    for path in R.golden_files():
+        blob = H.load_golden(path)
+        R.compare(R.gpu_rollout(blob), blob, os.path.basename(path))
+
+
+@pytest.mark.parametrize("rows,A,paired,done_prob", [
+    (8192 * 2, 2, True, 0.02),      # BASELINE.json configs[3]: 8192 envs x 2 agents
+    (16384 * 2 + 6, 2, False, 0.3), # ragged tail chunk, ragged done list (the [::A] stride runs over the list)
+    (262144 * 2, 2, True, 1.0),     # every row done: 256 chunks of look-back, meter window saturates
+    (5, 1, True, 0.5), (2049 * 3, 3, False, 0.0)])
+def test_rollout_step_matches_oracle(rows, A, paired, done_prob):
+    import rollout_harness as R
+    blob = _rollout_blob(rows, A, 3, seed=rows % 97, done_prob=done_prob, paired=paired, boot=(rows % 2 == 0))
+    R.compare(R.gpu_rollout(blob), R.oracle_rollout(blob), f"rows={rows}")

@@ -1,5 +1,7 @@
 """Pin the CPU oracle (oracle/ige_oracle.c) against fixtures minted from the unmodified reference
 (tests/golden/gen_golden.py).  Runs anywhere (no GPU, no reference tree)."""
+import os
+
 import numpy as np
 import pytest
 
@@ -35,3 +37,14 @@ def test_oracle_matches_reference_golden(task):
         # the restatement is op-for-op: everything but libm-vs-sleef transcendentals is bit-exact
         # (ShadowHand's reward goes through asin(): libm and torch's vectorised asin differ in the last ulp)
         assert worst["rew_buf"] > (0.5 if task == "shadow_hand" else 0.9), worst
+
+
+def test_oracle_rollout_matches_reference_play_steps():
+    """the oracle's restatement of A2CAgent_MA.py:35-67 against what the reference's own
+    play_steps wrote on a scripted environment (tests/golden/gen_golden_rollout.py)."""
+    import rollout_harness as R
+    files = R.golden_files()
+    assert len(files) >= 4
+    for path in files:
+        blob = H.load_golden(path)
+        R.compare(R.oracle_rollout(blob), blob, os.path.basename(path))
