@@ -424,8 +424,9 @@ typedef struct IgeRolloutStepArgs {
     float *meter_mean;             /* [3] in/out: AverageMeter.mean of IGE_METER_* */
     int32_t *meter_size;           /* [3] in/out: AverageMeter.current_size */
     double *reduce_scratch;        /* [4] zeroed ONCE by the caller; left zero by every launch */
-    uint32_t *scratch;             /* [ige_compact_scratch_words(num_rows)] zeroed ONCE; left zero by every launch */
+    uint32_t *scratch;             /* [ige_rollout_scratch_words(num_rows)] zeroed ONCE; left zero by every launch */
 } IgeRolloutStepArgs;
+int ige_rollout_scratch_words(int32_t num_rows);
 int ige_ma_rollout_step(const IgeRolloutStepArgs *a, void *stream);
 
 /* A2CBase.discount_values (rl_games GAE) as called from learning/A2CAgent_MA.py:60-66, plus

@@ -45,6 +45,8 @@ def lib():
         l.ige_compact_scratch_words.argtypes = [C.c_int32]
         l.ige_reset_list_scratch_words.restype = C.c_int
         l.ige_reset_list_scratch_words.argtypes = [C.c_int32]
+        l.ige_rollout_scratch_words.restype = C.c_int
+        l.ige_rollout_scratch_words.argtypes = [C.c_int32]
         l.ige_set_use_tma.restype = None
         l.ige_set_use_tma.argtypes = [C.c_int]
         l.ige_set_fast_paths.restype = None
@@ -61,7 +63,7 @@ def lib():
 
 def exported_symbols():
     return ["ige_version", "ige_last_error_string", "ige_launch_count", "ige_compact_scratch_words",
-            "ige_reset_list_scratch_words", "ige_set_use_tma", "ige_set_fast_paths", *_SIGS.keys()]
+            "ige_reset_list_scratch_words", "ige_rollout_scratch_words", "ige_set_use_tma", "ige_set_fast_paths", *_SIGS.keys()]
 
 
 def call(name, *structs, stream=0):

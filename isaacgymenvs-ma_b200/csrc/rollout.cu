@@ -6,10 +6,10 @@
 // updates -- sync-free (the reference reads len(env_done_indices) on the host).
 //
 // HBM-bound, 45 B/row (R rewards 4 + dones 8 + time_outs 1 + values 4 + current_* 12; W mb_rewards 4
-// + dones_out 1 + current_* 12 minus nothing re-read) -> thread owns 8 consecutive rows so every stream
-// moves as 16-B (8-B for the byte streams) vectors.  The `[::A]` stride is over the LIST of done rows, so
-// a row is kept iff its rank in nonzero() is a multiple of A: single-pass chained scan with decoupled
-// look-back over chunk counts (same protocol as compact.cu); all element-wise stores are issued before
+// + dones_out 1 + current_* 12 minus nothing re-read) -> thread owns 4 consecutive rows so every stream
+// moves as 16-B (4-B for the byte streams) vectors.  The `[::A]` stride is over the LIST of done rows, so
+// a row is kept iff its rank in nonzero() is a multiple of A: single-pass chained scan with decoupled,
+// warp-wide look-back over chunk counts; all element-wise stores are issued before
 // the look-back so they overlap it.  Meter sums: per-CTA fp32 partials -> fp64 atomics; the CTA that
 // retires last applies the AverageMeter recurrence and restores the scratch (graph re-playable).
 //
@@ -19,57 +19,60 @@
 namespace {
 
 constexpr int kThreads = 256;
-constexpr int kItems = 8;
+constexpr int kItems = 4;  // rows per thread: one 16-B vector per float stream, two per int64 stream, 4 B per byte stream
 constexpr int kChunk = kThreads * kItems;
 constexpr uint32_t kFlagAgg = 1u << 30, kFlagPrefix = 2u << 30, kValMask = (1u << 30) - 1;
 
-__device__ __forceinline__ void load8(const float *p, float (&v)[kItems]) {
+__device__ __forceinline__ void load4(const float *p, float (&v)[kItems]) {
     const float4 a = __ldg(reinterpret_cast<const float4 *>(p));
-    const float4 b = __ldg(reinterpret_cast<const float4 *>(p) + 1);
-    v[0] = a.x, v[1] = a.y, v[2] = a.z, v[3] = a.w, v[4] = b.x, v[5] = b.y, v[6] = b.z, v[7] = b.w;
+    v[0] = a.x, v[1] = a.y, v[2] = a.z, v[3] = a.w;
 }
-__device__ __forceinline__ void load8_rw(const float *p, float (&v)[kItems]) {  // buffers this kernel rewrites
-    const float4 a = reinterpret_cast<const float4 *>(p)[0], b = reinterpret_cast<const float4 *>(p)[1];
-    v[0] = a.x, v[1] = a.y, v[2] = a.z, v[3] = a.w, v[4] = b.x, v[5] = b.y, v[6] = b.z, v[7] = b.w;
+__device__ __forceinline__ void load4_rw(const float *p, float (&v)[kItems]) {  // buffers this kernel rewrites
+    const float4 a = *reinterpret_cast<const float4 *>(p);
+    v[0] = a.x, v[1] = a.y, v[2] = a.z, v[3] = a.w;
 }
-__device__ __forceinline__ void store8(float *p, const float (&v)[kItems]) {
-    reinterpret_cast<float4 *>(p)[0] = make_float4(v[0], v[1], v[2], v[3]);
-    reinterpret_cast<float4 *>(p)[1] = make_float4(v[4], v[5], v[6], v[7]);
+__device__ __forceinline__ void store4(float *p, const float (&v)[kItems]) {
+    *reinterpret_cast<float4 *>(p) = make_float4(v[0], v[1], v[2], v[3]);
 }
+__device__ __forceinline__ uint32_t poll(const uint32_t *p) { return *reinterpret_cast<const volatile uint32_t *>(p); }
 
+// Chunk c is CTA c (CTAs are dispatched in block-index order, so a CTA's predecessors are always running or done --
+// the same assumption as the reset list of the locomotion kernel); slots: scratch[2 + c], retirement counter: scratch[1].
 __global__ void __launch_bounds__(kThreads) ma_rollout_step_kernel(IgeRolloutStepArgs a, int num_chunks, int vec) {
     uint32_t *scratch = a.scratch;
-    __shared__ int s_chunk;
+    __shared__ int s_last;
     __shared__ int s_warp[kThreads / 32];
     __shared__ int s_prefix;
     __shared__ float s_sum[kThreads / 32][3];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (tid == 0) s_chunk = (int)atomicAdd(&scratch[0], 1u);
-    __syncthreads();
-    const int chunk = s_chunk;
+    const int chunk = blockIdx.x;
     const int n = a.num_rows;
     const int base = chunk * kChunk + tid * kItems;
     const bool full = vec && base + kItems <= n;  // vec: every stream is 16-B aligned (host-checked)
     const bool boot = a.value_bootstrap != 0;
+    // meter state: fetched now by the three threads that may need it at the very end (hides a cold DRAM round trip)
+    float mt_mean = 0.0f;
+    int mt_size = 0;
+    if (tid < 3) mt_mean = a.meter_mean[tid], mt_size = a.meter_size[tid];
 
     float rew[kItems], val[kItems], cr[kItems], cs[kItems], cl[kItems];
     long long dn[kItems];
     uint8_t to[kItems];
     if (full) {
-        load8(a.rewards + base, rew);
-        load8_rw(a.current_rewards + base, cr);
-        load8_rw(a.current_shaped_rewards + base, cs);
-        load8_rw(a.current_lengths + base, cl);
+        load4(a.rewards + base, rew);
+        load4_rw(a.current_rewards + base, cr);
+        load4_rw(a.current_shaped_rewards + base, cs);
+        load4_rw(a.current_lengths + base, cl);
 #pragma unroll
         for (int i = 0; i < kItems; i += 2) {
             const longlong2 d = __ldg(reinterpret_cast<const longlong2 *>(a.dones + base + i));
             dn[i] = d.x, dn[i + 1] = d.y;
         }
         if (boot) {
-            load8(a.values + base, val);
-            const uint2 t = __ldg(reinterpret_cast<const uint2 *>(a.time_outs + base));
+            load4(a.values + base, val);
+            const uint32_t t = __ldg(reinterpret_cast<const uint32_t *>(a.time_outs + base));
 #pragma unroll
-            for (int i = 0; i < 4; ++i) to[i] = (t.x >> (8 * i)) & 0xffu, to[4 + i] = (t.y >> (8 * i)) & 0xffu;
+            for (int i = 0; i < kItems; ++i) to[i] = (t >> (8 * i)) & 0xffu;
         }
     } else {
 #pragma unroll
@@ -109,18 +112,15 @@ __global__ void __launch_bounds__(kThreads) ma_rollout_step_kernel(IgeRolloutSte
         bits |= (dn[i] != 0 ? 1u : 0u) << i;
     }
     if (full) {
-        store8(a.mb_rewards + base, shaped);
-        store8(a.current_rewards + base, m_cr);
-        store8(a.current_shaped_rewards + base, m_cs);
-        store8(a.current_lengths + base, m_cl);
+        store4(a.mb_rewards + base, shaped);
+        store4(a.current_rewards + base, m_cr);
+        store4(a.current_shaped_rewards + base, m_cs);
+        store4(a.current_lengths + base, m_cl);
         if (a.dones_out) {
-            uint2 o = make_uint2(0u, 0u);
+            uint32_t o = 0u;
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                o.x |= (uint32_t)(uint8_t)dn[i] << (8 * i);
-                o.y |= (uint32_t)(uint8_t)dn[4 + i] << (8 * i);
-            }
-            *reinterpret_cast<uint2 *>(a.dones_out + base) = o;
+            for (int i = 0; i < kItems; ++i) o |= (uint32_t)(uint8_t)dn[i] << (8 * i);
+            *reinterpret_cast<uint32_t *>(a.dones_out + base) = o;
         }
     } else {
 #pragma unroll
@@ -154,23 +154,30 @@ __global__ void __launch_bounds__(kThreads) ma_rollout_step_kernel(IgeRolloutSte
         total += c;
     }
     const int local_excl = warp_off + incl - mine;
-    if (tid == 0) {
+    if (warp == 0) {  // warp-wide look-back: lane l polls predecessor (window start - l)
         uint32_t prefix = 0;
         if (chunk > 0) {
-            atomicExch(&scratch[2 + chunk], kFlagAgg | (uint32_t)total);
-            int j = chunk - 1;
-            while (true) {
-                uint32_t s;
-                do { s = atomicAdd(&scratch[2 + j], 0u); } while ((s >> 30) == 0u);
-                prefix += s & kValMask;
-                if ((s >> 30) == 2u) break;
-                --j;
+            if (lane == 0) atomicExch(&scratch[2 + chunk], kFlagAgg | (uint32_t)total);
+            for (int j0 = chunk - 1;; j0 -= 32) {
+                const int j = j0 - lane;
+                uint32_t s = kFlagPrefix;  // before chunk 0: an inclusive prefix of zero
+                if (j >= 0)
+                    do { s = poll(&scratch[2 + j]); } while ((s >> 30) == 0u);
+                const unsigned pm = __ballot_sync(0xffffffffu, (s >> 30) == 2u);
+                const int first = pm ? __ffs(pm) - 1 : 32;
+                uint32_t v = lane <= first ? (s & kValMask) : 0u;
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+                prefix += v;
+                if (pm) break;
             }
         }
-        atomicExch(&scratch[2 + chunk], kFlagPrefix | (prefix + (uint32_t)total));
-        s_prefix = (int)prefix;
-        if (chunk == num_chunks - 1)  // :45  len(all_done_indices[::A]) = ceil(total / A)
-            *a.done_count = ((int)prefix + total + a.num_agents - 1) / a.num_agents;
+        if (lane == 0) {
+            atomicExch(&scratch[2 + chunk], kFlagPrefix | (prefix + (uint32_t)total));
+            s_prefix = (int)prefix;
+            if (chunk == num_chunks - 1)  // :45  len(all_done_indices[::A]) = ceil(total / A)
+                *a.done_count = ((int)prefix + total + a.num_agents - 1) / a.num_agents;
+        }
     }
     __syncthreads();
     int rank = s_prefix + local_excl;
@@ -193,20 +200,18 @@ __global__ void __launch_bounds__(kThreads) ma_rollout_step_kernel(IgeRolloutSte
     }
     if (lane == 0) s_sum[warp][0] = p0, s_sum[warp][1] = p1, s_sum[warp][2] = p2;
     __syncthreads();
-    if (tid == 0) {
-        if (total > 0) {
-            double t0 = 0.0, t1 = 0.0, t2 = 0.0;
-            for (int w = 0; w < kThreads / 32; ++w) t0 += s_sum[w][0], t1 += s_sum[w][1], t2 += s_sum[w][2];
-            atomicAdd(&a.reduce_scratch[0], t0);
-            atomicAdd(&a.reduce_scratch[1], t1);
-            atomicAdd(&a.reduce_scratch[2], t2);
-        }
+    if (tid < 3 && total > 0) {  // three lanes, one fp64 atomic each
+        double t = 0.0;
+        for (int w = 0; w < kThreads / 32; ++w) t += s_sum[w][tid];
+        atomicAdd(&a.reduce_scratch[tid], t);
+    }
+    if (tid < 32) {
         __threadfence();
-        const uint32_t d = atomicAdd(&scratch[1], 1u);
-        s_chunk = (d == (uint32_t)num_chunks - 1u);
+        __syncwarp();
+        if (tid == 0) s_last = (atomicAdd(&scratch[1], 1u) == (uint32_t)num_chunks - 1u);
     }
     __syncthreads();
-    if (s_chunk) {  // last CTA to retire: AverageMeter.update x3 (:47-49), restore the scratch
+    if (s_last) {  // last CTA to retire: AverageMeter.update x3 (:47-49), restore the scratch
         __threadfence();
         if (tid < 3) {
             const int k = __ldcg(a.done_count);
@@ -214,19 +219,16 @@ __global__ void __launch_bounds__(kThreads) ma_rollout_step_kernel(IgeRolloutSte
             if (k > 0) {
                 const float new_mean = (float)sum / (float)k;  // torch.mean(values.float(), dim=0)
                 const int size = min(k, a.meter_max_size);     // np.clip(size, 0, max_size)
-                const int old_size = min(a.meter_max_size - size, a.meter_size[tid]);
+                const int old_size = min(a.meter_max_size - size, mt_size);
                 const int size_sum = old_size + size;
                 a.meter_size[tid] = size_sum;
-                const float x = a.meter_mean[tid] * (float)old_size, y = new_mean * (float)size;
+                const float x = mt_mean * (float)old_size, y = new_mean * (float)size;
                 a.meter_mean[tid] = (x + y) / (float)size_sum;
             }
             a.reduce_scratch[tid] = 0.0;
         }
         for (int i = tid; i < num_chunks; i += kThreads) scratch[2 + i] = 0u;
-        if (tid == 0) {
-            scratch[0] = 0u;
-            scratch[1] = 0u;
-        }
+        if (tid == 0) scratch[1] = 0u;
     }
 }
 
@@ -255,6 +257,9 @@ __global__ void __launch_bounds__(256) ma_discount_values_kernel(IgeDiscountArgs
 
 }  // namespace
 
+// scratch words for `num_rows` rows: retirement counter + one look-back slot per chunk
+extern "C" int ige_rollout_scratch_words(int32_t num_rows) { return 4 + (num_rows + kChunk - 1) / kChunk; }
+
 extern "C" int ige_ma_rollout_step(const IgeRolloutStepArgs *a, void *stream) {
     if (!a) return ige_fail(IGE_ENULL, "args is NULL");
     if (a->num_rows < 0 || a->num_rows > (1 << 30) - 1) return ige_fail(IGE_ESIZE, "num_rows=%d out of range", a->num_rows);
@@ -274,8 +279,8 @@ extern "C" int ige_ma_rollout_step(const IgeRolloutStepArgs *a, void *stream) {
     nat |= reinterpret_cast<uintptr_t>(a->dones) & 7u;
     if (nat) return ige_fail(IGE_EALIGN, "a float / int64 stream is not naturally aligned");
     int vec = (all & 15u) == 0;
-    if (a->dones_out && (reinterpret_cast<uintptr_t>(a->dones_out) & 7u)) vec = 0;
-    if (a->value_bootstrap && (reinterpret_cast<uintptr_t>(a->time_outs) & 7u)) vec = 0;
+    if (a->dones_out && (reinterpret_cast<uintptr_t>(a->dones_out) & 3u)) vec = 0;
+    if (a->value_bootstrap && (reinterpret_cast<uintptr_t>(a->time_outs) & 3u)) vec = 0;
     if (!a->done_rows || !a->done_count || !a->meter_mean || !a->meter_size || !a->reduce_scratch || !a->scratch)
         return ige_fail(IGE_ENULL, "done_rows / done_count / meter_* / reduce_scratch / scratch must be non-NULL");
     const int num_chunks = a->num_rows == 0 ? 1 : (a->num_rows + kChunk - 1) / kChunk;

@@ -57,8 +57,8 @@ class RolloutBookkeeperMA:
         self.meter_size = torch.zeros((4,), device=dev, dtype=torch.int32)
         self.game_rewards, self.game_shaped_rewards, self.game_lengths = (_Meter(self, i) for i in range(3))
         self._reduce = torch.zeros((4,), device=dev, dtype=torch.float64)
-        words = _lib.lib().ige_compact_scratch_words(max(num_rows, 1))
-        self._scratch = torch.zeros((words + 4,), device=dev, dtype=torch.int32)
+        words = _lib.lib().ige_rollout_scratch_words(max(num_rows, 1))
+        self._scratch = torch.zeros((words,), device=dev, dtype=torch.int32)
         self._n = 0
 
     # -- views with the reference's names --------------------------------------------------------------------
