@@ -445,6 +445,42 @@ typedef struct IgeDiscountArgs {
 int ige_ma_discount_values(const IgeDiscountArgs *a, void *stream);
 
 /* ------------------------------------------------------------------------------------------
+ * MA Franka pre_physics_step with the operational-space torque controller:
+ * Franka*MA.pre_physics_step + _compute_osc_torques (tasks/franka_reach_MA.py:770-818,
+ * franka_collect_MA.py:892-951, franka_combine_MA.py:910-969, franka_PPMA.py:897-956) fused with the
+ * action clamp of VecTask.step (vec_task.py:373).  One launch, one thread per agent row
+ * (row = env*A + agent): mm^-1 (7x7) and (J mm^-1 J^T)^-1 (6x6) are inverted in registers.  Both matrices
+ * are symmetric positive definite for a physical mass matrix and a full-row-rank Jacobian, so the inverses
+ * use Gauss-Jordan without pivoting (torch.inverse = LAPACK LU with partial pivoting: results agree to
+ * rounding x condition number, not bit-exact).  mm / j_eef are the tensors _get_mm / _get_j_eef return
+ * (franka_PPMA.py:1041-1061), already stacked over agents.  controlType "osc" only ("joint_tor" cannot run
+ * in the reference: (rows,6) * (1,7) does not broadcast, franka_PPMA.py:235,939).
+ * ------------------------------------------------------------------------------------------ */
+typedef struct IgeFrankaOscArgs {
+    int32_t num_envs, num_agents;
+    int32_t num_actions;           /* 6 (Reach: arm only) or 7 (7th column = gripper command) */
+    int32_t has_gripper;           /* Collect / Combine / PP: franka_PPMA.py:946-953 */
+    int32_t num_bodies;            /* rigid bodies per env */
+    int32_t eef_body_start, eef_body_step; /* agent a's end-effector body = start + a*step (its [7:13] = eef_vel) */
+    float clip_actions;            /* cfg env.clipActions; INFINITY = none */
+    float action_scale;            /* u_arm = actions[:, :6] * cmd_limit / action_scale */
+    float cmd_limit[6];
+    float kp[6], kd[6], kp_null[7], kd_null[7];
+    float default_dof_pos[7];      /* franka_default_dof_pos[:7] */
+    float effort_limits[7];        /* _franka_effort_limits[:7] */
+    float gripper_lower[2], gripper_upper[2]; /* franka_dof_{lower,upper}_limits[-2:] */
+    const float *actions_in;       /* (N*A, num_actions) policy output */
+    float *actions;                /* (N*A, num_actions) out: self.actions (clamped copy); may alias actions_in */
+    const float *mm;               /* (N*A, 7, 7) */
+    const float *j_eef;            /* (N*A, 6, 7) */
+    const float *dof_state;        /* (N, 9*A, 2): q / qd = [..., 0] / [..., 1], 9 DOFs per agent */
+    const float *rigid_body_state; /* (N, num_bodies, 13) */
+    float *effort_control;         /* (N, 9*A) in/out: columns 0..5 of each agent written (:944 assigns [:, :6]) */
+    float *pos_control;            /* (N, 9*A) in/out: columns 7..8 of each agent written when has_gripper */
+} IgeFrankaOscArgs;
+int ige_franka_ma_pre_physics(const IgeFrankaOscArgs *a, void *stream);
+
+/* ------------------------------------------------------------------------------------------
  * Library
  * ------------------------------------------------------------------------------------------ */
 int ige_version(void);

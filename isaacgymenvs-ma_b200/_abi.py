@@ -159,6 +159,15 @@ class IgeDiscountArgs(C.Structure):
                 ("mb_returns", _p)]
 
 
+class IgeFrankaOscArgs(C.Structure):
+    _fields_ = [("num_envs", _i), ("num_agents", _i), ("num_actions", _i), ("has_gripper", _i), ("num_bodies", _i),
+                ("eef_body_start", _i), ("eef_body_step", _i), ("clip_actions", _f), ("action_scale", _f),
+                ("cmd_limit", _f * 6), ("kp", _f * 6), ("kd", _f * 6), ("kp_null", _f * 7), ("kd_null", _f * 7),
+                ("default_dof_pos", _f * 7), ("effort_limits", _f * 7), ("gripper_lower", _f * 2),
+                ("gripper_upper", _f * 2), ("actions_in", _p), ("actions", _p), ("mm", _p), ("j_eef", _p),
+                ("dof_state", _p), ("rigid_body_state", _p), ("effort_control", _p), ("pos_control", _p)]
+
+
 def fill_array(carr, values):
     for i, v in enumerate(values):
         carr[i] = type(carr[0])(v) if isinstance(carr[0], int) else float(v)

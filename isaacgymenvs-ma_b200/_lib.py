@@ -21,6 +21,7 @@ _SIGS = {
     "ige_franka_ma_post_physics": (_abi.IgeFrankaMAParams, _abi.IgeFrankaMABuffers),
     "ige_locomotion_pre_physics": (_abi.IgeActionForceArgs,),
     "ige_shadow_hand_pre_physics_targets": (_abi.IgeHandTargetArgs,),
+    "ige_franka_ma_pre_physics": (_abi.IgeFrankaOscArgs,),
     "ige_ma_rollout_step": (_abi.IgeRolloutStepArgs,),
     "ige_ma_discount_values": (_abi.IgeDiscountArgs,),
 }

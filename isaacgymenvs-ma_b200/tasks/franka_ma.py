@@ -1,8 +1,9 @@
 """Franka multi-agent mirrors: FrankaReachMA / FrankaCollectMA / FrankaCombineMA / FrankaPPMA
 (reference: isaacgymenvs/tasks/franka_reach_MA.py, franka_collect_MA.py, franka_combine_MA.py,
 franka_PPMA.py).  Buffers carry the fork's flattened agent axis: row = env * num_agents + agent
-(franka_reach_MA.py:22-38).  ``post_physics_step`` is one C-ABI call; the OSC torque controller of
-``pre_physics_step`` needs PhysX Jacobians / mass matrices and is outside the hot path."""
+(franka_reach_MA.py:22-38).  ``post_physics_step`` is one C-ABI call;
+``pre_physics_step`` (the OSC torque controller) is the fused ``ige_franka_ma_pre_physics``
+kernel once the simulator's mass-matrix / Jacobian tensors are bound with ``attach_dynamics``."""
 import numpy as np
 import torch
 
@@ -166,8 +167,57 @@ class FrankaMA(VecTaskB200):
             u[slot] = torch.rand(shape, device=self.device)
         return u
 
+    # -- pre_physics_step: operational-space torque controller --------------------------------
+    EFFORT_LIMITS = [87.0, 87.0, 87.0, 87.0, 12.0, 12.0, 12.0]   # franka_description panda.urdf efforts (:339)
+
+    def attach_dynamics(self, mm, j_eef, action_scale=1.0, cmd_limit=0.55, kp=150.0, kp_null=10.0,
+                        effort_limits=None):
+        """Bind the tensors ``_get_mm()`` / ``_get_j_eef()`` return (franka_PPMA.py:1041-1061: PhysX mass matrices
+        (N*A, 7, 7) and end-effector Jacobians (N*A, 6, 7), stacked over agents) and the controller gains
+        (franka_PPMA.py:226-235).  Afterwards ``pre_physics_step`` is the fused OSC kernel."""
+        rows = self.num_envs * self.num_agents
+        for name, t, shape in (("mm", mm, (rows, 7, 7)), ("j_eef", j_eef, (rows, 6, 7))):
+            if tuple(t.shape) != shape or t.dtype != torch.float32 or t.device != self.device or not t.is_contiguous():
+                raise _lib.IgeError(f"{name}: expected a contiguous float32 tensor {shape} on {self.device}")
+        if self.num_dofs != 9 * self.num_agents:
+            raise _lib.IgeError("OSC pre-physics expects 9 DOFs per Franka (7 arm + 2 fingers)")
+        self._mm, self._j_eef = mm, j_eef
+        self.action_scale = float(action_scale)
+        self.cmd_limit = [float(cmd_limit)] * 6
+        self.kp = [float(kp)] * 6
+        self.kd = (2 * torch.sqrt(torch.tensor(self.kp))).tolist()            # :227
+        self.kp_null = [float(kp_null)] * 7
+        self.kd_null = (2 * torch.sqrt(torch.tensor(self.kp_null))).tolist()  # :229
+        self._franka_effort_limits = list(effort_limits or self.EFFORT_LIMITS)
+
     def pre_physics_step(self, actions):
-        self.actions.copy_(actions.to(self.device))       # franka_reach_MA.py:806 (OSC torques: out of scope)
+        """franka_PPMA.py:931-956 (and the same method of the other three tasks) as one C-ABI call; without
+        attached dynamics only ``self.actions = actions.clone()`` (:933) happens."""
+        actions = actions.to(self.device)
+        if getattr(self, "_mm", None) is None:
+            self.actions.copy_(actions)
+            return
+        if actions.dtype != torch.float32 or not actions.is_contiguous() or tuple(actions.shape) != tuple(self.actions.shape):
+            raise _lib.IgeError(f"actions: expected contiguous float32 {tuple(self.actions.shape)}")
+        from ..synthetic import FRANKA_DEFAULT_DOF_POS, FRANKA_DOF_LOWER, FRANKA_DOF_UPPER
+        c = self.cfg
+        a = _abi.IgeFrankaOscArgs()
+        a.num_envs, a.num_agents, a.num_actions = self.num_envs, self.num_agents, self.num_actions
+        a.has_gripper = int(self.variant != "reach")
+        a.num_bodies = self._rigid_body_state.shape[1]
+        a.eef_body_start, a.eef_body_step = c["eef_body_start"], c["eef_body_step"]
+        a.clip_actions, a.action_scale = self.clip_actions, self.action_scale
+        for name, vals in (("cmd_limit", self.cmd_limit), ("kp", self.kp), ("kd", self.kd), ("kp_null", self.kp_null),
+                           ("kd_null", self.kd_null), ("effort_limits", self._franka_effort_limits),
+                           ("default_dof_pos", list(c.get("franka_default_dof_pos", FRANKA_DEFAULT_DOF_POS))[:7]),
+                           ("gripper_lower", list(c.get("franka_dof_lower_limits", FRANKA_DOF_LOWER))[-2:]),
+                           ("gripper_upper", list(c.get("franka_dof_upper_limits", FRANKA_DOF_UPPER))[-2:])):
+            _abi.fill_array(getattr(a, name), vals)
+        a.actions_in, a.actions = _ptr(actions), _ptr(self.actions)
+        a.mm, a.j_eef = _ptr(self._mm), _ptr(self._j_eef)
+        a.dof_state, a.rigid_body_state = _ptr(self._dof_state), _ptr(self._rigid_body_state)
+        a.effort_control, a.pos_control = _ptr(self._effort_control), _ptr(self._pos_control)
+        _lib.call("ige_franka_ma_pre_physics", a, stream=self._stream())
 
     def post_physics_step(self):
         """franka_reach_MA.py:821-828 etc. as one C-ABI call (Combine / PP launch a reset kernel first)."""

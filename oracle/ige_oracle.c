@@ -1122,3 +1122,106 @@ int ige_oracle_ma_discount_values(const IgeDiscountArgs *a) {
     }
     return 0;
 }
+
+/* ------------------------------------------------------------------------------------------
+ * MA Franka pre_physics_step + _compute_osc_torques, tasks/franka_PPMA.py:897-956
+ * (same text in franka_reach_MA.py:770-818, franka_collect_MA.py:892-951, franka_combine_MA.py:910-969).
+ * torch.inverse is LAPACK LU; mm and J mm^-1 J^T are SPD, so Gauss-Jordan without pivoting is used here and
+ * in the kernel (agreement with the reference: rounding x condition number, see tests/test_oracle_golden.py).
+ * Products are re-associated where mathematically identical: j_eef_inv = m_eef @ (J @ mm_inv),
+ * J^T @ (m_eef @ v) instead of (J^T @ m_eef) @ v.
+ * ------------------------------------------------------------------------------------------ */
+static void gj_inverse(float *A, int n) { /* in place, row-major n x n */
+    for (int k = 0; k < n; ++k) {
+        const float p = 1.0f / A[k * n + k];
+        A[k * n + k] = 1.0f;
+        for (int j = 0; j < n; ++j) A[k * n + j] = A[k * n + j] * p;
+        for (int i = 0; i < n; ++i) {
+            if (i == k) continue;
+            const float f = A[i * n + k];
+            A[i * n + k] = 0.0f;
+            for (int j = 0; j < n; ++j) A[i * n + j] = fmaf(-f, A[k * n + j], A[i * n + j]);
+        }
+    }
+}
+
+int ige_oracle_franka_ma_pre_physics(const IgeFrankaOscArgs *a) {
+    const int A = a->num_agents, NA = a->num_actions;
+    const float PI = 3.14159265358979323846f, TWO_PI = 6.28318530717958647692f;
+    for (int e = 0; e < a->num_envs; ++e)
+        for (int g = 0; g < A; ++g) {
+            const size_t r = (size_t)e * A + g;
+            float act[8];
+            for (int i = 0; i < NA; ++i) { /* vec_task.py:373 + :933 self.actions = actions.clone() */
+                float x = a->actions_in[r * NA + i];
+                x = x < -a->clip_actions ? -a->clip_actions : x;
+                x = x > a->clip_actions ? a->clip_actions : x;
+                act[i] = x;
+                a->actions[r * NA + i] = x;
+            }
+            const float *ds = a->dof_state + r * 18;
+            const float *ev = a->rigid_body_state + ((size_t)e * a->num_bodies + a->eef_body_start + (size_t)g * a->eef_body_step) * 13 + 7;
+            float M[49], J[42], JM[42], E[36], v[6], un[7], w[7], t[6], y[6], z[6], u[7];
+            for (int i = 0; i < 49; ++i) M[i] = a->mm[r * 49 + i];
+            for (int i = 0; i < 42; ++i) J[i] = a->j_eef[r * 42 + i];
+            for (int i = 0; i < 6; ++i) {          /* :939, :913 kp * dpose - kd * eef_vel */
+                const float dpose = (act[i] * a->cmd_limit[i]) / a->action_scale;
+                const float x0 = a->kp[i] * dpose, x1 = a->kd[i] * ev[i];
+                v[i] = x0 - x1;
+            }
+            for (int k = 0; k < 7; ++k) {          /* :920 */
+                const float q = ds[2 * k], qd = ds[2 * k + 1];
+                const float d0 = (a->default_dof_pos[k] - q) + PI;
+                const float wrap = py_remainder(d0, TWO_PI) - PI;
+                const float x0 = a->kd_null[k] * (-qd), x1 = a->kp_null[k] * wrap;
+                un[k] = x0 + x1;
+            }
+            for (int i = 0; i < 7; ++i) {          /* :922 u_null = mm @ u_null */
+                float s = 0.0f;
+                for (int k = 0; k < 7; ++k) s = fmaf(M[i * 7 + k], un[k], s);
+                w[i] = s;
+            }
+            gj_inverse(M, 7);                      /* :907 */
+            for (int i = 0; i < 6; ++i)            /* J @ mm_inv */
+                for (int j = 0; j < 7; ++j) {
+                    float s = 0.0f;
+                    for (int k = 0; k < 7; ++k) s = fmaf(J[i * 7 + k], M[k * 7 + j], s);
+                    JM[i * 7 + j] = s;
+                }
+            for (int i = 0; i < 6; ++i)            /* :908 m_eef_inv */
+                for (int j = 0; j < 6; ++j) {
+                    float s = 0.0f;
+                    for (int k = 0; k < 7; ++k) s = fmaf(JM[i * 7 + k], J[j * 7 + k], s);
+                    E[i * 6 + j] = s;
+                }
+            gj_inverse(E, 6);                      /* :909 m_eef */
+            for (int i = 0; i < 6; ++i) {
+                float s = 0.0f, s2 = 0.0f;
+                for (int k = 0; k < 6; ++k) s = fmaf(E[i * 6 + k], v[k], s);
+                t[i] = s;
+                for (int k = 0; k < 7; ++k) s2 = fmaf(JM[i * 7 + k], w[k], s2);
+                y[i] = s2;
+            }
+            for (int i = 0; i < 6; ++i) {
+                float s = 0.0f;
+                for (int k = 0; k < 6; ++k) s = fmaf(E[i * 6 + k], y[k], s);
+                z[i] = s;
+            }
+            for (int k = 0; k < 7; ++k) {          /* :913 + :923, :926 clamp */
+                float s = 0.0f, s2 = 0.0f;
+                for (int i = 0; i < 6; ++i) s = fmaf(J[i * 7 + k], t[i], s);
+                for (int i = 0; i < 6; ++i) s2 = fmaf(J[i * 7 + k], z[i], s2);
+                float x = s + (w[k] - s2);
+                const float lim = a->effort_limits[k];
+                x = x < -lim ? -lim : x;
+                u[k] = x > lim ? lim : x;
+            }
+            for (int k = 0; k < 6; ++k) a->effort_control[r * 9 + k] = u[k]; /* :944 _arm_control[:, :6] = u_arm[:, :6] */
+            if (a->has_gripper) {                  /* :946-953 */
+                const int open = act[6] >= 0.0f;
+                a->pos_control[r * 9 + 7] = open ? a->gripper_upper[0] : a->gripper_lower[0];
+                a->pos_control[r * 9 + 8] = open ? a->gripper_upper[1] : a->gripper_lower[1];
+            }
+        }
+    return 0;
+}

@@ -421,3 +421,62 @@ def test_rollout_step_matches_oracle(rows, A, paired, done_prob):
     import rollout_harness as R
     blob = _rollout_blob(rows, A, 3, seed=rows % 97, done_prob=done_prob, paired=paired, boot=(rows % 2 == 0))
     R.compare(R.gpu_rollout(blob), R.oracle_rollout(blob), f"rows={rows}")
+
+
+# ---- MA Franka OSC torque pre-physics ------------------------------------------------------
+def test_franka_osc_matches_reference_golden():
+    """ige_franka_ma_pre_physics == the oracle bit for bit (same algorithm, no FMA contraction on either side), and
+    within the conditioning-aware bar of the reference's own torques (see test_oracle_osc_matches_reference_pre_physics)."""
+    import osc_harness as O
+    for path in O.golden_files():
+        blob = H.load_golden(path)
+        got, orc = O.gpu_osc(blob), O.oracle_osc(blob)
+        for k in ("out_actions", "out_pos_control"):
+            H.assert_equal(k, got[k], blob[k])
+        assert O.torque_error(got, blob) <= 1e-4, path
+        assert O.torque_error(got, orc) <= 1e-6, (path, O.torque_error(got, orc))
+
+
+@pytest.mark.parametrize("variant,n,A", [("pp", 8192, 2), ("reach", 1000, 3), ("collect", 37, 2)])
+def test_franka_osc_matches_oracle_full_size(variant, n, A):
+    """BASELINE.json configs[3] size (8192 envs x 2 agents) and ragged tiles, synthetic SPD mass matrices."""
+    import osc_harness as O
+    syn = H.pkg.synthetic
+    cfg = syn.franka_ma_cfg(variant, A, 2)
+    st = syn.make_state("franka_" + variant, n, seed=n, num_agents=A, num_targets=2)
+    rows = n * A
+    g = torch.Generator().manual_seed(n)
+    G = torch.randn((rows, 7, 7), generator=g)
+    mm = torch.diag_embed(torch.rand((rows, 7), generator=g) * 1.5 + 0.5) + 0.1 * G @ G.transpose(1, 2)
+    j = 0.2 * torch.randn((rows, 6, 7), generator=g)
+    j[:, :, :6] += torch.eye(6)
+    rb = np.array(st["_rigid_body_state"], np.float32)
+    rb[:, :, 7:] *= 0.05
+    blob = {"in_actions_raw": (torch.rand((rows, cfg["num_actions"]), generator=g) * 3 - 1.5).numpy(),
+            "in_mm": mm.numpy(), "in_j_eef": j.numpy(), "in_dof_state": np.array(st["_dof_state"], np.float32),
+            "in_rigid_body_state": rb, "in_pos_control": np.array(st["_pos_control"], np.float32),
+            "in_effort_control": np.array(st["_effort_control"], np.float32),
+            "cfg_variant": variant, "cfg_num_agents": A, "cfg_num_envs": n, "cfg_num_actions": cfg["num_actions"],
+            "cfg_eef_body_start": cfg["eef_body_start"], "cfg_eef_body_step": cfg["eef_body_step"],
+            "cfg_num_bodies": rb.shape[1], "cfg_kp": [150.0] * 6, "cfg_kd": (2 * np.sqrt(np.float32(150.0))).repeat(6),
+            "cfg_kp_null": [10.0] * 7, "cfg_kd_null": (2 * np.sqrt(np.float32(10.0))).repeat(7),
+            "cfg_cmd_limit": [0.1] * 6, "cfg_action_scale": 1.0,
+            "cfg_effort_limits": [87.0, 87.0, 87.0, 87.0, 12.0, 12.0, 12.0],
+            "cfg_default_dof_pos": syn.FRANKA_DEFAULT_DOF_POS[:7], "cfg_gripper_lower": syn.FRANKA_DOF_LOWER[-2:],
+            "cfg_gripper_upper": syn.FRANKA_DOF_UPPER[-2:]}
+    got, orc = O.gpu_osc(blob), O.oracle_osc(blob)
+    for k in ("out_actions", "out_pos_control"):
+        H.assert_equal(k, got[k], orc[k])
+    assert O.torque_error(got, orc) <= 1e-6
+    # the same call through the host mirror (FrankaMA.attach_dynamics + pre_physics_step)
+    env = H.build("franka_" + variant, st, "cuda:0", rand_mode="philox")
+    env._rigid_body_state.copy_(torch.from_numpy(rb))
+    env.clip_actions = 1.0
+    env.attach_dynamics(mm.to("cuda:0").contiguous(), j.to("cuda:0").contiguous(), cmd_limit=0.1)
+    env.pre_physics_step(torch.from_numpy(blob["in_actions_raw"]).to("cuda:0"))
+    torch.cuda.synchronize()
+    H.assert_equal("mirror actions", env.actions.cpu().numpy(), got["out_actions"])
+    H.assert_equal("mirror effort_control", env._effort_control.cpu().numpy(), got["out_effort_control"])
+    H.assert_equal("mirror pos_control", env._pos_control.cpu().numpy(), got["out_pos_control"])
+    truth = O.float64_truth(blob)   # as close to float64 as the reference's own fp32 lines are (2x + 1e-5)
+    assert O.torque_error(got, truth) <= 2.0 * O.torque_error(O.torch_fp32(blob), truth) + 1e-5

@@ -48,3 +48,24 @@ def test_oracle_rollout_matches_reference_play_steps():
     for path in files:
         blob = H.load_golden(path)
         R.compare(R.oracle_rollout(blob), blob, os.path.basename(path))
+
+
+def test_oracle_osc_matches_reference_pre_physics():
+    """the oracle's restatement of Franka*MA.pre_physics_step + _compute_osc_torques against the
+    reference's own output (tests/golden/gen_golden_osc.py).  Clamped actions and gripper targets bit-exact.  The
+    torques go through two matrix inverses (torch.inverse = LAPACK LU, here Gauss-Jordan): fp32 rounding is amplified
+    by the condition number, so the bar is 1e-4 * max(1, |ref|), AND the oracle must be as close to a float64
+    evaluation of the same formula as the reference's own fp32 result is (within 2x + 1e-5)."""
+    import osc_harness as O
+    files = O.golden_files()
+    assert len(files) >= 4
+    for path in files:
+        blob = H.load_golden(path)
+        got, truth = O.oracle_osc(blob), O.float64_truth(blob)
+        H.assert_equal("actions", got["out_actions"], blob["out_actions"])
+        H.assert_equal("pos_control", got["out_pos_control"], blob["out_pos_control"])
+        assert O.torque_error(got, blob) <= 1e-4, (path, O.torque_error(got, blob))
+        assert O.torque_error(got, truth) <= 2.0 * O.torque_error(blob, truth) + 1e-5
+        # untouched columns (6 of each arm, 7..8) keep their previous value: franka_PPMA.py:944 assigns [:, :6]
+        eff, ref = got["out_effort_control"].reshape(-1, 9), blob["out_effort_control"].reshape(-1, 9)
+        H.assert_equal("untouched effort columns", eff[:, 6:], ref[:, 6:])
