@@ -43,46 +43,74 @@ __device__ __forceinline__ float py_remainder(float a, float b) {  // torch.rema
     return m;
 }
 
-// coalesced copy of `count` floats (global, 16-B aligned base) into shared memory by one warp
-__device__ __forceinline__ void warp_copy(float *dst, const float *src, int count, int lane) {
+__device__ __forceinline__ void cp_async16(float *dst, const float *src) {
+    const uint32_t d = (uint32_t)__cvta_generic_to_shared(dst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(src) : "memory");
+}
+
+// one warp starts the coalesced copy of `count` floats (16-B aligned global base) into shared memory: 16-B chunks
+// asynchronously (LDGSTS), the tail of a ragged last tile synchronously
+__device__ __forceinline__ void warp_copy_async(float *dst, const float *src, int count, int lane) {
     const int v4 = count >> 2;
-    for (int i = lane; i < v4; i += 32) reinterpret_cast<float4 *>(dst)[i] = __ldg(reinterpret_cast<const float4 *>(src) + i);
+    for (int i = lane; i < v4; i += 32) cp_async16(dst + 4 * i, src + 4 * i);
     for (int i = (v4 << 2) + lane; i < count; i += 32) dst[i] = __ldg(src + i);
 }
 
+// the row's small inputs straight from global: clamped actions (vec_task.py:373 + :933) and eef_vel
+__device__ __forceinline__ void load_small(const IgeFrankaOscArgs &a, int r, bool ok, float (&act)[7], float (&ev)[6]) {
+#pragma unroll
+    for (int i = 0; i < 7; ++i) act[i] = 0.0f;
+#pragma unroll
+    for (int i = 0; i < 6; ++i) ev[i] = 0.0f;
+    if (!ok) return;
+    const int NA = a.num_actions;
+#pragma unroll
+    for (int i = 0; i < 7; ++i)
+        if (i < NA) {
+            const float x = __ldg(a.actions_in + (size_t)r * NA + i);
+            act[i] = fminf(fmaxf(x, -a.clip_actions), a.clip_actions);
+        }
+    const int e = r / a.num_agents, g = r - e * a.num_agents;
+    const float *p = a.rigid_body_state + ((size_t)e * a.num_bodies + a.eef_body_start + (size_t)g * a.eef_body_step) * 13 + 7;
+#pragma unroll
+    for (int i = 0; i < 6; ++i) ev[i] = __ldg(p + i);
+}
+
+// Software pipeline per warp: the tile's matrices move shared memory -> registers as soon as they land; the copy of
+// the warp's NEXT tile (and its small per-row inputs) is then issued into the same shared buffer and flies during the
+// ~2.6 k instructions of register arithmetic -- the register file is the second stage of the double buffer.
 __global__ void __launch_bounds__(kWarps * 32) franka_osc_kernel(IgeFrankaOscArgs a, int rows) {
     __shared__ __align__(16) float s_mm[kWarps][kTile * 49];
     __shared__ __align__(16) float s_j[kWarps][kTile * 42];
     __shared__ __align__(16) float s_ds[kWarps][kTile * 18];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int num_tiles = (rows + kTile - 1) / kTile;
-    for (int tile = blockIdx.x * kWarps + warp; tile < num_tiles; tile += gridDim.x * kWarps) {
+    const int stride = gridDim.x * kWarps;
+    int tile = blockIdx.x * kWarps + warp;
+    float act_n[7], ev_n[6];
+    auto issue = [&](int t) {
+        const int r0 = t * kTile, cnt = min(kTile, rows - r0);
+        warp_copy_async(s_mm[warp], a.mm + (size_t)r0 * 49, cnt * 49, lane);
+        warp_copy_async(s_j[warp], a.j_eef + (size_t)r0 * 42, cnt * 42, lane);
+        warp_copy_async(s_ds[warp], a.dof_state + (size_t)r0 * 18, cnt * 18, lane);
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        load_small(a, r0 + lane, lane < cnt, act_n, ev_n);
+    };
+    if (tile < num_tiles) issue(tile);
+    for (; tile < num_tiles; tile += stride) {
         const int r0 = tile * kTile;
         const int cnt = min(kTile, rows - r0);
-        warp_copy(s_mm[warp], a.mm + (size_t)r0 * 49, cnt * 49, lane);
-        warp_copy(s_j[warp], a.j_eef + (size_t)r0 * 42, cnt * 42, lane);
-        warp_copy(s_ds[warp], a.dof_state + (size_t)r0 * 18, cnt * 18, lane);
         const int r = r0 + lane;
         const bool ok = lane < cnt;
-        // per-row small inputs straight from global (issued before the shared-memory tile is consumed)
-        float act[7] = {0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f}, ev[6] = {0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f};
-        if (ok) {
-            const int NA = a.num_actions;
+        float act[7], ev[6], M[7][7], J[6][7], q[7], qd[7];
 #pragma unroll
-            for (int i = 0; i < 7; ++i)  // vec_task.py:373 + :933
-                if (i < NA) {
-                    const float x = __ldg(a.actions_in + (size_t)r * NA + i);
-                    act[i] = fminf(fmaxf(x, -a.clip_actions), a.clip_actions);
-                }
-            const int e = r / a.num_agents, g = r - e * a.num_agents;
-            const float *p = a.rigid_body_state + ((size_t)e * a.num_bodies + a.eef_body_start + (size_t)g * a.eef_body_step) * 13 + 7;
+        for (int i = 0; i < 7; ++i) act[i] = act_n[i];
 #pragma unroll
-            for (int i = 0; i < 6; ++i) ev[i] = __ldg(p + i);
-        }
+        for (int i = 0; i < 6; ++i) ev[i] = ev_n[i];
+        asm volatile("cp.async.wait_all;" ::: "memory");
         __syncwarp();
         if (ok) {
             const float *mrow = s_mm[warp] + lane * 49, *jrow = s_j[warp] + lane * 42, *ds = s_ds[warp] + lane * 18;
-            float M[7][7], J[6][7];
 #pragma unroll
             for (int i = 0; i < 7; ++i)
 #pragma unroll
@@ -91,6 +119,12 @@ __global__ void __launch_bounds__(kWarps * 32) franka_osc_kernel(IgeFrankaOscArg
             for (int i = 0; i < 6; ++i)
 #pragma unroll
                 for (int j = 0; j < 7; ++j) J[i][j] = jrow[i * 7 + j];
+#pragma unroll
+            for (int k = 0; k < 7; ++k) q[k] = ds[2 * k], qd[k] = ds[2 * k + 1];
+        }
+        __syncwarp();
+        if (tile + stride < num_tiles) issue(tile + stride);
+        if (ok) {
             float v[6], un[7], w[7];
 #pragma unroll
             for (int i = 0; i < 6; ++i) {  // :939, :913  kp * dpose - kd * eef_vel
@@ -99,10 +133,9 @@ __global__ void __launch_bounds__(kWarps * 32) franka_osc_kernel(IgeFrankaOscArg
             }
 #pragma unroll
             for (int k = 0; k < 7; ++k) {  // :920
-                const float q = ds[2 * k], qd = ds[2 * k + 1];
-                const float d0 = (a.default_dof_pos[k] - q) + kPi;
+                const float d0 = (a.default_dof_pos[k] - q[k]) + kPi;
                 const float wrap = py_remainder(d0, ige::kTwoPi) - kPi;
-                un[k] = a.kd_null[k] * (-qd) + a.kp_null[k] * wrap;
+                un[k] = a.kd_null[k] * (-qd[k]) + a.kp_null[k] * wrap;
             }
 #pragma unroll
             for (int i = 0; i < 7; ++i) {  // :922  u_null = mm @ u_null
