@@ -229,9 +229,15 @@ extern "C" int ige_franka_ma_pre_physics(const IgeFrankaOscArgs *a, void *stream
     if (rows > (1ll << 30)) return ige_fail(IGE_ESIZE, "too many agent rows");
     if (rows == 0) return IGE_OK;
     const int tiles = (int)((rows + kTile - 1) / kTile);
-    int dev = 0, sms = 148;
-    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    const int grid = min((tiles + kWarps - 1) / kWarps, sms * 8);
+    static int resident = 0;  // persistent grid: exactly the CTAs that fit on the device at once
+    if (resident == 0) {
+        int dev = 0, sms = 148, per_sm = 4;
+        if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, franka_osc_kernel, kWarps * 32, 0) != cudaSuccess || per_sm < 1)
+            per_sm = 4;
+        resident = sms * per_sm;
+    }
+    const int grid = min((tiles + kWarps - 1) / kWarps, resident);
     franka_osc_kernel<<<grid, kWarps * 32, 0, (cudaStream_t)stream>>>(*a, (int)rows);
     return ige_check_launch("ige_franka_ma_pre_physics");
 }
