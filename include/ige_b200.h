@@ -481,6 +481,52 @@ typedef struct IgeFrankaOscArgs {
 int ige_franka_ma_pre_physics(const IgeFrankaOscArgs *a, void *stream);
 
 /* ------------------------------------------------------------------------------------------
+ * Anymal (first of the remaining single-agent tasks) -- replaces
+ * Anymal.post_physics_step (tasks/anymal.py:231-240) incl. reset_idx (:277-304),
+ * compute_anymal_observations (:355-386) and compute_anymal_reward (:311-351), plus the step() epilogue
+ * (vec_task.py:396-404).  One launch; the reset list (ascending env ids == reset_buf.nonzero()) and each
+ * reset env's row in the injected uniforms come from an in-kernel chained scan.
+ * ------------------------------------------------------------------------------------------ */
+#define IGE_ANYMAL_DOF 12
+#define IGE_ANYMAL_MAX_KNEES 8
+typedef struct IgeAnymalParams {
+    int32_t num_envs, num_bodies;  /* rigid bodies per env (contact_forces rows) */
+    int32_t base_index, num_knees;
+    int32_t knee_indices[IGE_ANYMAL_MAX_KNEES];
+    float lin_vel_scale, ang_vel_scale, dof_pos_scale, dof_vel_scale;
+    float rew_lin_vel_xy, rew_ang_vel_z, rew_torque; /* rew_scales[...] already multiplied by dt (anymal.py:57-59) */
+    float max_episode_length;      /* int in the reference; compared as progress >= max - 1 */
+    float clip_obs;                /* cfg env.clipObservations; INFINITY = none */
+    float command_x_range[2], command_y_range[2], command_yaw_range[2];
+    float default_dof_pos[IGE_ANYMAL_DOF]; /* every row of self.default_dof_pos (anymal.py:132-138) */
+    int32_t rand_mode;             /* IGE_RAND_* */
+    int32_t _pad;
+    uint64_t seed;                 /* PHILOX */
+    uint64_t *step;                /* PHILOX: device counter, advanced by one per launch; NULL = 0 */
+    const float *u[5];             /* INJECTED, rows by reset rank: positions_offset (k,12), velocities (k,12),
+                                      commands x (k,1), y (k,1), yaw (k,1) -- the torch.rand calls of :282-302 */
+} IgeAnymalParams;
+
+typedef struct IgeAnymalBuffers {
+    const float *root_states;      /* (N, 13) */
+    float *dof_state;              /* (N, 12, 2) in/out: reset rows rewritten */
+    const float *contact_forces;   /* (N, num_bodies, 3) */
+    const float *torques;          /* (N, 12) */
+    const float *actions;          /* (N, 12) */
+    float *commands;               /* (N, 3) in/out: re-drawn on reset */
+    float *obs_buf;                /* (N, 48) out */
+    float *rew_buf;                /* (N) out */
+    int64_t *reset_buf, *progress_buf; /* (N) in/out */
+    float *obs_clamped;            /* optional (N, 48) */
+    uint8_t *timeout_buf;          /* optional (N) */
+    int32_t *reset_ids;            /* (N) out: ids of the envs reset in this step, ascending */
+    int32_t *reset_count;          /* [1] out */
+    uint32_t *scratch;             /* [ige_anymal_scratch_words(num_envs)] zeroed ONCE; left zero by every launch */
+} IgeAnymalBuffers;
+int ige_anymal_scratch_words(int32_t num_envs);
+int ige_anymal_post_physics(const IgeAnymalParams *p, const IgeAnymalBuffers *b, void *stream);
+
+/* ------------------------------------------------------------------------------------------
  * Library
  * ------------------------------------------------------------------------------------------ */
 int ige_version(void);

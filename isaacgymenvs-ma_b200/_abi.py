@@ -168,6 +168,21 @@ class IgeFrankaOscArgs(C.Structure):
                 ("dof_state", _p), ("rigid_body_state", _p), ("effort_control", _p), ("pos_control", _p)]
 
 
+class IgeAnymalParams(C.Structure):
+    _fields_ = [("num_envs", _i), ("num_bodies", _i), ("base_index", _i), ("num_knees", _i),
+                ("knee_indices", _i * 8), ("lin_vel_scale", _f), ("ang_vel_scale", _f), ("dof_pos_scale", _f),
+                ("dof_vel_scale", _f), ("rew_lin_vel_xy", _f), ("rew_ang_vel_z", _f), ("rew_torque", _f),
+                ("max_episode_length", _f), ("clip_obs", _f), ("command_x_range", _f * 2),
+                ("command_y_range", _f * 2), ("command_yaw_range", _f * 2), ("default_dof_pos", _f * 12),
+                ("rand_mode", _i), ("_pad", _i), ("seed", C.c_uint64), ("step", _p), ("u", _p * 5)]
+
+
+class IgeAnymalBuffers(C.Structure):
+    _fields_ = [("root_states", _p), ("dof_state", _p), ("contact_forces", _p), ("torques", _p), ("actions", _p),
+                ("commands", _p), ("obs_buf", _p), ("rew_buf", _p), ("reset_buf", _p), ("progress_buf", _p),
+                ("obs_clamped", _p), ("timeout_buf", _p), ("reset_ids", _p), ("reset_count", _p), ("scratch", _p)]
+
+
 def fill_array(carr, values):
     for i, v in enumerate(values):
         carr[i] = type(carr[0])(v) if isinstance(carr[0], int) else float(v)

@@ -22,6 +22,7 @@ _SIGS = {
     "ige_locomotion_pre_physics": (_abi.IgeActionForceArgs,),
     "ige_shadow_hand_pre_physics_targets": (_abi.IgeHandTargetArgs,),
     "ige_franka_ma_pre_physics": (_abi.IgeFrankaOscArgs,),
+    "ige_anymal_post_physics": (_abi.IgeAnymalParams, _abi.IgeAnymalBuffers),
     "ige_ma_rollout_step": (_abi.IgeRolloutStepArgs,),
     "ige_ma_discount_values": (_abi.IgeDiscountArgs,),
 }
@@ -48,6 +49,8 @@ def lib():
         l.ige_reset_list_scratch_words.argtypes = [C.c_int32]
         l.ige_rollout_scratch_words.restype = C.c_int
         l.ige_rollout_scratch_words.argtypes = [C.c_int32]
+        l.ige_anymal_scratch_words.restype = C.c_int
+        l.ige_anymal_scratch_words.argtypes = [C.c_int32]
         l.ige_set_use_tma.restype = None
         l.ige_set_use_tma.argtypes = [C.c_int]
         l.ige_set_fast_paths.restype = None
@@ -64,7 +67,7 @@ def lib():
 
 def exported_symbols():
     return ["ige_version", "ige_last_error_string", "ige_launch_count", "ige_compact_scratch_words",
-            "ige_reset_list_scratch_words", "ige_rollout_scratch_words", "ige_set_use_tma", "ige_set_fast_paths", *_SIGS.keys()]
+            "ige_reset_list_scratch_words", "ige_rollout_scratch_words", "ige_anymal_scratch_words", "ige_set_use_tma", "ige_set_fast_paths", *_SIGS.keys()]
 
 
 def call(name, *structs, stream=0):

@@ -1225,3 +1225,99 @@ int ige_oracle_franka_ma_pre_physics(const IgeFrankaOscArgs *a) {
         }
     return 0;
 }
+
+/* ------------------------------------------------------------------------------------------
+ * Anymal: tasks/anymal.py:231-240 post_physics_step, :277-304 reset_idx,
+ * :311-351 compute_anymal_reward, :355-386 compute_anymal_observations; epilogue vec_task.py:396-404.
+ * ------------------------------------------------------------------------------------------ */
+static float anymal_uniform(const IgeAnymalParams *p, int draw, int rank, int env, int cols, int j) {
+    if (p->rand_mode == IGE_RAND_PHILOX) {
+        IgeResetRand r;
+        memset(&r, 0, sizeof(r));
+        r.seed = p->seed; r.step = p->step;
+        return philox_uniform(&r, (uint32_t)env, (uint32_t)draw, (uint32_t)j);
+    }
+    return p->u[draw][(size_t)rank * cols + j];
+}
+/* torch_rand_float (utils/torch_jit_utils.py:216-218): (upper - lower) * rand + lower, scalars rounded to fp32 */
+static inline float rand_float(double lower, double upper, float u) {
+    const float t = (float)(upper - lower) * u;
+    return t + (float)lower;
+}
+
+int ige_oracle_anymal_post_physics(const IgeAnymalParams *p, const IgeAnymalBuffers *b) {
+    const int n = p->num_envs;
+    int rank = 0;
+    for (int e = 0; e < n; ++e) {
+        float *ds = b->dof_state + (size_t)e * 24;
+        float *cmd = b->commands + (size_t)e * 3;
+        int64_t progress = b->progress_buf[e] + 1;             /* :232 */
+        if (b->reset_buf[e] != 0) {                            /* :234-236 reset_idx */
+            for (int j = 0; j < 12; ++j) {
+                const float off = rand_float(0.5, 1.5, anymal_uniform(p, 0, rank, e, 12, j));   /* :282 */
+                const float vel = rand_float(-0.1, 0.1, anymal_uniform(p, 1, rank, e, 12, j));  /* :283 */
+                ds[2 * j] = p->default_dof_pos[j] * off;       /* :285 */
+                ds[2 * j + 1] = vel;                           /* :286 */
+            }
+            cmd[0] = rand_float(p->command_x_range[0], p->command_x_range[1], anymal_uniform(p, 2, rank, e, 1, 0));
+            cmd[1] = rand_float(p->command_y_range[0], p->command_y_range[1], anymal_uniform(p, 3, rank, e, 1, 0));
+            cmd[2] = rand_float(p->command_yaw_range[0], p->command_yaw_range[1], anymal_uniform(p, 4, rank, e, 1, 0));
+            progress = 0;                                      /* :303 */
+            b->reset_ids[rank++] = e;
+        }
+        const float *root = b->root_states + (size_t)e * 13;
+        const float *q = root + 3;
+        const float grav[3] = {0.0f, 0.0f, -1.0f};
+        float blv[3], bav[3], pg[3];
+        quat_rotate_impl(q, root + 7, 1, blv);                 /* :369-370 / :328-329 */
+        quat_rotate_impl(q, root + 10, 1, bav);
+        quat_rotate_impl(q, grav, 0, pg);                      /* :371 */
+        float *obs = b->obs_buf + (size_t)e * 48;
+        const float *act = b->actions + (size_t)e * 12;
+        for (int i = 0; i < 3; ++i) {
+            obs[i] = blv[i] * p->lin_vel_scale;
+            obs[3 + i] = bav[i] * p->ang_vel_scale;
+            obs[6 + i] = pg[i];
+            obs[9 + i] = cmd[i] * (i < 2 ? p->lin_vel_scale : p->ang_vel_scale);   /* :374 */
+        }
+        for (int j = 0; j < 12; ++j) {
+            obs[12 + j] = (ds[2 * j] - p->default_dof_pos[j]) * p->dof_pos_scale;  /* :372 */
+            obs[24 + j] = ds[2 * j + 1] * p->dof_vel_scale;
+            obs[36 + j] = act[j];
+        }
+        /* compute_anymal_reward :331-351 */
+        const float d0 = cmd[0] - blv[0], d1 = cmd[1] - blv[1], d2 = cmd[2] - bav[2];
+        const float sq[2] = {d0 * d0, d1 * d1};
+        const float lin_err = row_sum(sq, 2);
+        const float ang_err = d2 * d2;
+        const float r_lin = expf(-lin_err / 0.25f) * p->rew_lin_vel_xy;
+        const float r_ang = expf(-ang_err / 0.25f) * p->rew_ang_vel_z;
+        float tq2[12];
+        for (int j = 0; j < 12; ++j) { const float t = b->torques[(size_t)e * 12 + j]; tq2[j] = t * t; }
+        const float r_tq = row_sum(tq2, 12) * p->rew_torque;
+        float total = (r_lin + r_ang) + r_tq;
+        total = total < 0.0f ? 0.0f : total;                   /* torch.clip(total, 0., None) */
+        const float *cf = b->contact_forces + (size_t)e * p->num_bodies * 3;
+        int reset = norm3(cf[p->base_index * 3], cf[p->base_index * 3 + 1], cf[p->base_index * 3 + 2]) > 1.0f;
+        for (int k = 0; k < p->num_knees; ++k) {
+            const float *c = cf + p->knee_indices[k] * 3;
+            reset |= norm3(c[0], c[1], c[2]) > 1.0f;
+        }
+        const int time_out = (float)progress >= p->max_episode_length - 1.0f;     /* :348 */
+        reset |= time_out;
+        b->rew_buf[e] = total;
+        b->reset_buf[e] = reset;
+        b->progress_buf[e] = progress;
+        if (b->timeout_buf) b->timeout_buf[e] = (uint8_t)(time_out && reset);     /* vec_task.py:396 */
+        if (b->obs_clamped)
+            for (int j = 0; j < 48; ++j) {
+                float v = obs[j];
+                v = v < -p->clip_obs ? -p->clip_obs : v;
+                v = v > p->clip_obs ? p->clip_obs : v;
+                b->obs_clamped[(size_t)e * 48 + j] = v;
+            }
+    }
+    *b->reset_count = rank;
+    if (p->rand_mode == IGE_RAND_PHILOX && p->step) *p->step += 1;
+    return 0;
+}

@@ -480,3 +480,43 @@ def test_franka_osc_matches_oracle_full_size(variant, n, A):
     H.assert_equal("mirror pos_control", env._pos_control.cpu().numpy(), got["out_pos_control"])
     truth = O.float64_truth(blob)   # as close to float64 as the reference's own fp32 lines are (2x + 1e-5)
     assert O.torque_error(got, truth) <= 2.0 * O.torque_error(O.torch_fp32(blob), truth) + 1e-5
+
+
+# ---- Anymal --------------------------------------------------------------------------------
+def test_anymal_matches_reference_golden():
+    import anymal_harness as A
+    for path in A.golden_files():
+        blob = H.load_golden(path)
+        for s, ids, got, ref in A.run_fixture(blob, "cuda:0"):
+            H.assert_equal("reset_env_ids", ids, ref["reset_env_ids"])
+            A.compare(got, ref, f"{os.path.basename(path)} step{s}")
+
+
+@pytest.mark.parametrize("n,reset_prob,mode", [(16384, 0.02, "injected"), (16384, 0.02, "philox"), (4099, 1.0, "injected"),
+                                               (262144, 0.3, "philox"), (5, 0.5, "injected")])
+def test_anymal_matches_oracle(n, reset_prob, mode):
+    """CUDA vs oracle on the same seeded state over 3 chained steps: flags, progress, reset ids, reset rows bit-exact;
+    observations / rewards 1e-5 relative.  Philox mode: the oracle implements the same generator."""
+    import anymal_harness as A
+    sys_path = os.path.join(H.GOLDEN_DIR)
+    if sys_path not in __import__("sys").path:
+        __import__("sys").path.insert(0, sys_path)
+    import gen_golden_anymal_state as G
+    cfg = G.CFG
+    st0 = G.make_state(n, seed=n % 1013, reset_prob=reset_prob)
+    cpu, gpu = A.State(n, cfg["num_bodies"], "cpu"), A.State(n, cfg["num_bodies"], "cuda:0")
+    rng = np.random.Generator(np.random.PCG64(n))
+    for dev in (cpu, gpu):
+        dev.load(**{k: st0[k] for k in ("root_states", "dof_state", "contact_forces", "torques", "commands", "reset_buf",
+                                        "progress_buf")}, actions=np.clip(st0["actions"], -1, 1))
+    for step in range(3):
+        k = int((cpu.reset_buf != 0).sum())
+        rands = [rng.random(s, dtype=np.float32) for s in ((k, 12), (k, 12), (k, 1), (k, 1), (k, 1))] if mode == "injected" else None
+        ids_c, ids_g = cpu.step(cfg, rands, seed=77), gpu.step(cfg, rands, seed=77)
+        H.assert_equal("reset ids", ids_g, ids_c)
+        A.compare(gpu.outputs(), cpu.outputs(), f"n={n} step{step}")
+        assert int(gpu.scratch.abs().sum()) == 0, "scratch not restored"
+        assert int(gpu.rng_step) == int(cpu.rng_step)
+        G.advance(st0, rng)                       # new simulator state, identical on both sides
+        for dev in (cpu, gpu):
+            dev.load(**{k: st0[k] for k in ("root_states", "contact_forces", "torques")}, actions=np.clip(st0["actions"], -1, 1))

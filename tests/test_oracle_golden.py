@@ -69,3 +69,17 @@ def test_oracle_osc_matches_reference_pre_physics():
         # untouched columns (6 of each arm, 7..8) keep their previous value: franka_PPMA.py:944 assigns [:, :6]
         eff, ref = got["out_effort_control"].reshape(-1, 9), blob["out_effort_control"].reshape(-1, 9)
         H.assert_equal("untouched effort columns", eff[:, 6:], ref[:, 6:])
+
+
+def test_oracle_anymal_matches_reference_golden():
+    """the oracle against the reference's own VecTask.step outputs
+    (tests/golden/gen_golden_anymal.py): flags / progress / reset ids / reset rows bit-exact, obs and rewards 1e-5."""
+    import anymal_harness as A
+    files = A.golden_files()
+    assert len(files) >= 3
+    for path in files:
+        blob = H.load_golden(path)
+        for s, ids, got, ref in A.run_fixture(blob, "cpu"):
+            H.assert_equal("reset_env_ids", ids, ref["reset_env_ids"])
+            A.compare(got, ref, f"{os.path.basename(path)} step{s}")
+            assert H.bitexact_fraction(got["obs_buf"], ref["obs_buf"]) > 0.98
