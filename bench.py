@@ -34,14 +34,15 @@ from ige_loader import load_package  # noqa: E402
 
 # frozen algorithmic bytes per env-step (SURVEY.md 8d / BASELINE.md section 2)
 ALGO_BYTES = {"Cartpole": 68, "Ant": 556, "Humanoid": 940, "ShadowHand": 1732, "FrankaReachMA": 376,
-              "FrankaCollectMA": 488, "FrankaCombineMA": 692, "FrankaPPMA": 720}
+              "FrankaCollectMA": 488, "FrankaCombineMA": 692, "FrankaPPMA": 720, "Anymal": 544}
 ALGO_BYTES_EPILOGUE = {"Cartpole": 85, "Ant": 797, "Humanoid": 1373, "ShadowHand": 2577, "FrankaReachMA": 530,
-                       "FrankaCollectMA": 714, "FrankaCombineMA": 1078, "FrankaPPMA": 1122}
+                       "FrankaCollectMA": 714, "FrankaCombineMA": 1078, "FrankaPPMA": 1122, "Anymal": 737}
 KERNEL_NAME = {"Cartpole": "cartpole_post_physics_kernel", "Ant": "locomotion_pipelined_kernel<Ant>",
                "Humanoid": "locomotion_pipelined_kernel<Humanoid>",
                "ShadowHand": "shadow_hand_post_physics_kernel (+ shadow_hand_reset_kernel)",
                "FrankaReachMA": "franka_ma_kernel", "FrankaCollectMA": "franka_ma_kernel",
-               "FrankaCombineMA": "franka_ma_kernel (reset + compute)", "FrankaPPMA": "franka_ma_kernel (reset + compute)"}
+               "FrankaCombineMA": "franka_ma_kernel (reset + compute)", "FrankaPPMA": "franka_ma_kernel (reset + compute)",
+               "Anymal": "anymal_post_physics_kernel"}
 L2_BYTES = 126 * 1024 * 1024
 HORIZON = 16  # cfg/train/AntPPO.yaml:65 horizon_length -> one stats all-reduce per horizon
 

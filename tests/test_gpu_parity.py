@@ -520,3 +520,32 @@ def test_anymal_matches_oracle(n, reset_prob, mode):
         G.advance(st0, rng)                       # new simulator state, identical on both sides
         for dev in (cpu, gpu):
             dev.load(**{k: st0[k] for k in ("root_states", "contact_forces", "torques")}, actions=np.clip(st0["actions"], -1, 1))
+
+
+def test_anymal_mirror_step_matches_oracle():
+    """isaacgymenvs.make()-shaped entry -> Anymal.step(): the VecTask return tuple, the recorded indexed sim calls and
+    every buffer against the oracle driven from the same synthetic state (Philox reset noise on both sides)."""
+    import anymal_harness as A
+    n, seed = 3000, 5
+    st = H.pkg.synthetic.make_state("anymal", n, seed=seed, reset_prob=0.1)
+    env = H.pkg.factory.from_state("Anymal", st, "cuda:0", rand_mode="philox", seed=seed)
+    cfg = H.pkg.synthetic.ANYMAL_CFG
+    cpu = A.State(n, cfg["num_bodies"], "cpu")
+    cpu.load(**{k: st[k] for k in ("root_states", "dof_state", "contact_forces", "torques", "commands", "reset_buf",
+                                   "progress_buf")}, actions=np.clip(st["actions"], -1, 1))
+    ids_ref = cpu.step(cfg, None, seed=seed)
+    env.sim.record = True
+    obs_dict, rew, reset, extras = env.step(torch.from_numpy(st["actions"]).to("cuda:0"))
+    torch.cuda.synchronize()
+    ref = cpu.outputs()
+    k = int(env.reset_count)
+    H.assert_equal("reset ids", env.reset_env_ids[:k].cpu().numpy(), ids_ref)
+    got = {"obs_buf": env.obs_buf.cpu().numpy(), "rew_buf": rew.cpu().numpy(), "dof_state": env.dof_state.cpu().numpy(),
+           "commands": env.commands.cpu().numpy(), "obs_clamped": obs_dict["obs"].cpu().numpy(),
+           "reset_buf": reset.cpu().numpy(), "progress_buf": env.progress_buf.cpu().numpy(),
+           "time_outs": extras["time_outs"].cpu().numpy()}
+    A.compare(got, ref, "mirror")
+    names = [c[0] for c in env.sim.calls]
+    assert "set_actor_root_state_tensor_indexed" in names and "set_dof_state_tensor_indexed" in names
+    with pytest.raises(H.pkg._lib.IgeError):
+        H.pkg.factory.from_state("Anymal", st, "cpu").post_physics_step()
