@@ -29,7 +29,8 @@ class Anymal(VecTaskB200):
         self.max_episode_length = int(cfg["max_episode_length"])                  # anymal.py:95
         self.num_dof, self.num_bodies = 12, int(cfg["num_bodies"])
         self.base_index = int(cfg["base_index"])
-        self.knee_indices = torch.tensor(list(cfg["knee_indices"]), dtype=torch.long, device=dev)
+        self._knees = [int(k) for k in cfg["knee_indices"]]      # host copy: abi_structs() must not sync (graph capture)
+        self.knee_indices = torch.tensor(self._knees, dtype=torch.long, device=dev)
         t = sim.tensors
         self.root_states, self.dof_state = t["root_states"], t["dof_state"]       # anymal.py:121-126
         self.dof_pos = self.dof_state.view(n, self.num_dof, 2)[..., 0]
@@ -58,7 +59,7 @@ class Anymal(VecTaskB200):
     def abi_structs(self):
         p = _abi.IgeAnymalParams()
         p.num_envs, p.num_bodies, p.base_index = self.num_envs, self.num_bodies, self.base_index
-        knees = self.knee_indices.tolist()
+        knees = self._knees
         p.num_knees = len(knees)
         _abi.fill_array(p.knee_indices, knees)
         p.lin_vel_scale, p.ang_vel_scale = self.lin_vel_scale, self.ang_vel_scale
