@@ -91,3 +91,31 @@ def test_buffers_match_vec_task_contract():
     cp = pkg.make(0, "Cartpole", 16, "cpu")
     assert cp.obs_buf.shape == (16, 4) and cp.dof_state.shape == (32, 2)
     assert cp.dof_pos.data_ptr() == cp.dof_state.data_ptr()     # strided views, cartpole.py:53-54
+
+
+def test_bad_arguments_rejected_8f_entry_points(lib):
+    """The §8f entry points validate before launching (no GPU needed): negative IGE_E* codes -> IgeError."""
+    a = pkg._abi.IgeRolloutStepArgs()
+    a.num_rows, a.num_agents, a.meter_max_size = 8, 2, 100
+    with pytest.raises(pkg._lib.IgeError, match="non-NULL"):
+        pkg._lib.call("ige_ma_rollout_step", a)
+    a.num_agents = 0
+    with pytest.raises(pkg._lib.IgeError, match="num_agents"):
+        pkg._lib.call("ige_ma_rollout_step", a)
+    o = pkg._abi.IgeFrankaOscArgs()
+    o.num_envs, o.num_agents, o.num_actions, o.num_bodies = 4, 2, 5, 24
+    with pytest.raises(pkg._lib.IgeError, match="num_actions"):
+        pkg._lib.call("ige_franka_ma_pre_physics", o)
+    o.num_actions, o.eef_body_start, o.eef_body_step = 7, 20, 11
+    with pytest.raises(pkg._lib.IgeError, match="out of range"):
+        pkg._lib.call("ige_franka_ma_pre_physics", o)
+    p, b = pkg._abi.IgeAnymalParams(), pkg._abi.IgeAnymalBuffers()
+    p.num_envs, p.num_bodies, p.num_knees = 4, 17, 9
+    with pytest.raises(pkg._lib.IgeError, match="num_knees"):
+        pkg._lib.call("ige_anymal_post_physics", p, b)
+    p.num_knees = 4
+    with pytest.raises(pkg._lib.IgeError, match="NULL"):
+        pkg._lib.call("ige_anymal_post_physics", p, b)
+    assert lib.ige_anymal_scratch_words(16384) == 4 + 128 and lib.ige_rollout_scratch_words(16384) == 4 + 16
+    with pytest.raises(pkg._lib.IgeError, match="no CPU fallback"):
+        pkg.rollout.RolloutBookkeeperMA(16, 2, 4, "cpu")
