@@ -121,8 +121,9 @@ def build_replicas(pkg, task, num_envs, replicas, device, seed, fall_frac, fuse_
     return envs
 
 
-def capture(envs, fn):
-    """Capture fn(env) for every env of `envs`, in order, into one CUDA graph."""
+def capture(envs, fn, pre=None, post=None, error_mode="global"):
+    """Capture fn(env) for every env of `envs`, in order, into one CUDA graph.  `pre` / `post` run inside the
+    capture before / after the steps (the statistics branch forks and joins there)."""
     g = torch.cuda.CUDAGraph()
     s = torch.cuda.Stream()
     s.wait_stream(torch.cuda.current_stream())
@@ -131,10 +132,23 @@ def capture(envs, fn):
             fn(e)
     torch.cuda.current_stream().wait_stream(s)
     torch.cuda.synchronize()
-    with torch.cuda.graph(g):
+    with torch.cuda.graph(g, capture_error_mode=error_mode):
+        if pre is not None:
+            pre()
         for e in envs:
             fn(e)
+        if post is not None:
+            post()
     return g
+
+
+def bench_config(task, n, world):
+    """`config` of the JSON line -- the SAME dict for both arms (ours / --impl reference)."""
+    return {"workload": f"{task} post_physics_step num_envs={n} per GPU" +
+                        (" (BASELINE.json configs[1])" if task == "Ant" and n == 16384 else ""),
+            "task": task, "num_envs_per_gpu": n, "global_envs": n * world,
+            "parallelism": f"env-shard x{world}", "reset": "natural (2% fallen envs/step)",
+            "stats": f"episode-statistics all-reduce every {HORIZON} steps"}
 
 
 def run_ours(args):
@@ -155,36 +169,36 @@ def run_ours(args):
     algo = ALGO_BYTES[task]
     state_bytes = ALGO_BYTES_EPILOGUE[task] * n
     replicas = args.replicas or max(2 * HORIZON, -(-2 * L2_BYTES // state_bytes))
-    replicas = -(-replicas // HORIZON) * HORIZON
+    replicas = -(-replicas // (2 * HORIZON)) * (2 * HORIZON)      # an even number of horizons (double-buffered stats)
     envs = build_replicas(pkg, task, n, replicas, device, args.seed, args.fall_frac, False, rank)
     lib = pkg._lib
 
-    # ---- graphs: chunks of HORIZON consecutive replicas (one stats all-reduce per chunk) ----
-    chunks = [(capture(envs[i:i + HORIZON], lambda e: e.hot_step()), HORIZON)
-              for i in range(0, replicas, HORIZON)]
-    single = [(capture([e], lambda e: e.hot_step()), 1) for e in envs[:HORIZON]]
+    # ---- graphs: one per horizon = HORIZON consecutive replicas + (forked branch) the statistics snapshot and
+    #      NCCL all-reduce of the PREVIOUS horizon's accumulator; the remainder steps are one more graph ----
     reducer = pkg.distributed.StatsReducer(device)
-
-    def allreduce_stats():
-        # episode statistics: <= 16 floats, once per horizon, off the critical path
-        if dist is None:
-            return
-        reducer.start(lambda: envs[0].stats)      # side stream: the step stream never waits for the collective
+    reducer.warm()
+    n_chunks = replicas // HORIZON
+    for c in range(n_chunks):
+        for e in envs[c * HORIZON:(c + 1) * HORIZON]:
+            reducer.attach(e, c)
+    mode = "thread_local" if world > 1 else "global"   # NCCL's watchdog thread may touch the device during capture
+    chunks = [capture(envs[c * HORIZON:(c + 1) * HORIZON], lambda e: e.hot_step(),
+                      pre=lambda c=c: reducer.fork(reducer.rows[(c & 1) ^ 1]), post=reducer.join, error_mode=mode)
+              for c in range(n_chunks)]
+    full, rem = divmod(args.steps, HORIZON)
+    # the remainder continues with the replicas (and the accumulator) of the horizon that would come next
+    rem_envs = [envs[((full % n_chunks) * HORIZON + i) % replicas] for i in range(rem)]
+    rem_graph = capture(rem_envs, lambda e: e.hot_step(), error_mode=mode) if rem else None
 
     def timed(steps, warmup):
-        full, rem = divmod(steps, HORIZON)
         def body():
             for i in range(full):
-                chunks[i % len(chunks)][0].replay()
-                allreduce_stats()
-            for i in range(rem):
-                single[i][0].replay()
-            if dist is not None:
-                reducer.wait()          # the last horizon's collective ends inside the timed region
-        wfull = -(-warmup // HORIZON)
-        for i in range(max(wfull, 1)):
-            chunks[i % len(chunks)][0].replay()
-        allreduce_stats()
+                chunks[i % n_chunks].replay()
+            if rem_graph is not None:
+                rem_graph.replay()
+        w = max(-(-warmup // HORIZON), 3)
+        for i in range(w):
+            chunks[(i - w) % n_chunks].replay()      # ends on the last chunk: body() starts at chunk 0
         torch.cuda.synchronize()
         if dist is not None:
             dist.barrier()
@@ -196,7 +210,6 @@ def run_ours(args):
         t1.record()
         torch.cuda.synchronize()
         torch.cuda.cudart().cudaProfilerStop()
-        reducer.wait()
         if dist is not None:
             dist.barrier()
         torch.cuda.synchronize()
@@ -210,8 +223,7 @@ def run_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         elapsed = float(t.item())
     value = n * world * args.steps / elapsed
-    kernels_per_step = 1
-    gpu_launches = args.steps * kernels_per_step
+    gpu_launches = args.steps + full          # one fused step kernel per step + one statistics snapshot per horizon
 
     # ---- dominant kernel alone (roofline): fused kernel only, same rotation, CUDA events ----
     kgraph = capture(envs, lambda e: e.hot_step())
@@ -234,13 +246,13 @@ def run_ours(args):
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": elapsed / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"{task} post_physics_step num_envs={n} per GPU" +
-                               (" (BASELINE.json configs[1])" if task == "Ant" and n == 16384 else ""),
-                   "task": task, "num_envs_per_gpu": n, "global_envs": n * world,
-                   "parallelism": f"env-shard x{world}", "reset": "natural (2% fallen envs/step), in-kernel Philox",
-                   "l2": f"inputs larger than L2: rotating {replicas} state replicas = "
-                         f"{replicas * state_bytes / 2**20:.0f} MiB > 126 MiB L2",
-                   "launch": f"CUDA graph, {HORIZON} steps per graph; stats all-reduce every {HORIZON} steps"},
+        "config": bench_config(task, n, world),
+        "how": {"l2": f"inputs larger than L2: rotating {replicas} state replicas = "
+                      f"{replicas * state_bytes / 2**20:.0f} MiB > 126 MiB L2",
+                "launch": f"one CUDA graph per horizon of {HORIZON} steps; the statistics snapshot + NCCL all-reduce of "
+                          f"the previous horizon is a forked branch of the same graph ({reducer.collectives} collectives "
+                          f"captured, world={world}); remainder steps = one more graph",
+                "reset_noise": "in-kernel Philox"},
         "gpu_launches": gpu_launches,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": ncu_traffic(task, n), "peak_source": f"MEASURED_PEAKS.json hbm_gbs ({peak_kind})",
@@ -254,12 +266,12 @@ def run_ours(args):
     # keep sampling for >= 1 s of GPU load so that short runs still see clocks under load
     t_end = time.time() + max(0.0, 1.0 - (time.time() - clk.t0))
     while time.time() < t_end:
-        chunks[0][0].replay()
+        kgraph.replay()          # step kernels only: no collective, so ranks need not agree on the count
         torch.cuda.synchronize()
     clk.__exit__()
     out["clocks"] = clk.summary()
     if rank == 0 and world == 1 and not args.no_cpu:
-        out["cpu_baseline"] = cpu_baseline(pkg, args, seconds=args.cpu_seconds)
+        out["cpu_baseline"] = host_baselines(pkg, args, seconds=args.cpu_seconds)
     if rank == 0:
         print(json.dumps(out))
     if dist is not None:
@@ -412,8 +424,10 @@ def cpu_baseline(pkg, args, seconds=6.0, steps=None, warmup=3):
     from oracle import oracle
     task, n = args.task, args.num_envs
     cores = os.cpu_count() or 1
-    oracle.lib().ige_oracle_set_threads(cores)
     syn = pkg.factory._SYN_NAME[task]
+    if syn not in H.TASK_NAME:
+        return None
+    oracle.lib().ige_oracle_set_threads(cores)
     st = pkg.synthetic.make_state(syn, n, seed=args.seed, reset_prob=0.02, fall_frac=args.fall_frac)
     obj = H.build(syn, st, "cpu", rand_mode="philox", fuse_epilogue=False)
     for _ in range(warmup):
@@ -433,19 +447,98 @@ def cpu_baseline(pkg, args, seconds=6.0, steps=None, warmup=3):
                       f"{el:.1f} s", "ms_per_step": el / done * 1e3}
 
 
+def cpu_model():
+    try:
+        with open("/proc/cpuinfo") as f:
+            for line in f:
+                if line.startswith("model name"):
+                    return line.split(":", 1)[1].strip()
+    except OSError:
+        pass
+    return "unknown"
+
+
+def reference_torch_baseline(pkg, args, seconds=6.0, steps=None, warmup=5, threads=None):
+    """The reference's OWN implementation of the step on the host cores (north_star: "the reference torch path
+    ... sim_device=cpu pipeline=cpu"): the unmodified task class from the reference tree (/root/reference in the
+    build container, else the files tools/vendor_reference.py staged under oracle/_ref/), built around the same
+    synthetic state with a recording-free FakeGym (tests/ref_harness.py), its
+    ``post_physics_step()`` timed with time.perf_counter.  Returns None when the reference is not available."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import ref_shim
+    if not ref_shim.reference_available():
+        return None
+    import ref_harness
+    task, n = args.task, args.num_envs
+    syn = pkg.factory._SYN_NAME[task]
+    if syn not in ref_harness.BUILDERS:
+        return None
+    cores = threads or os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    st = pkg.synthetic.make_state(syn, n, seed=args.seed, reset_prob=0.02, fall_frac=args.fall_frac)
+    cfg = pkg.factory.task_cfg(task)
+    if syn.startswith("franka_"):
+        cfg = pkg.synthetic.franka_ma_cfg(syn[len("franka_"):], int(st["cfg_num_agents"]), int(st["cfg_num_targets"]))
+    obj = ref_harness.BUILDERS[syn](st, cfg)
+    obj.gym.record = False
+    if syn == "shadow_hand":       # its resets run in pre_physics_step (shadow_hand.py:670-682)
+        act = obj.actions.clone()
+
+        def step():
+            obj.pre_physics_step(act)
+            obj.post_physics_step()
+    else:
+        step = obj.post_physics_step
+    with torch.no_grad():
+        for _ in range(max(warmup, 3)):       # TorchScript's profiling executor specialises on the first calls
+            step()
+        done, t0 = 0, time.perf_counter()
+        while True:
+            step()
+            done += 1
+            if steps is not None:
+                if done >= steps:
+                    break
+            elif time.perf_counter() - t0 >= seconds:
+                break
+        el = time.perf_counter() - t0
+    return {"value": n * done / el, "unit": "env-steps/s", "cores": cores, "kind": "reference",
+            "cpu_model": cpu_model(), "torch_threads": torch.get_num_threads(),
+            "sample": f"{done} steps of the reference's own {task}.post_physics_step (unmodified "
+                      f"isaacgymenvs/tasks/{syn}.py on CPU torch {torch.__version__}, FakeGym, num_envs={n}), "
+                      f"{cores} threads, {el:.1f} s", "ms_per_step": el / done * 1e3,
+            "reference_root": os.path.relpath(ref_shim.REFERENCE_ROOT, ROOT) if ref_shim.REFERENCE_ROOT.startswith(ROOT)
+            else ref_shim.REFERENCE_ROOT}
+
+
+def host_baselines(pkg, args, seconds, steps=None, warmup=3):
+    """cpu_baseline object: the reference's torch path when available (kind "reference"), with the C port of
+    the oracle beside it as `cpu_port`; the port alone (kind "port") otherwise."""
+    port = cpu_baseline(pkg, args, seconds=seconds, steps=steps, warmup=warmup)
+    ref = reference_torch_baseline(pkg, args, seconds=seconds, steps=steps, warmup=max(warmup, 3))
+    if ref is None:
+        return port
+    if port is None:
+        return ref
+    one = reference_torch_baseline(pkg, args, seconds=min(seconds, 3.0), steps=None if steps is None else max(2, steps // 4),
+                                   warmup=3, threads=1)
+    ref["single_thread"] = {"value": one["value"], "ms_per_step": one["ms_per_step"]}
+    ref["cpu_port"] = port
+    return ref
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     pkg = load_package()
-    cb = cpu_baseline(pkg, args, steps=args.steps, warmup=max(args.warmup, 1))
     world = int(os.environ.get("WORLD_SIZE", "1"))
+    cb = host_baselines(pkg, args, seconds=args.cpu_seconds, steps=args.steps, warmup=max(args.warmup, 3))
     out = {"impl": "reference", "metric": "env-steps/sec (obs+reward+reset)", "value": cb["value"],
            "unit": "env-steps/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
            "ms_per_step": cb["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
            "dtype": "f32", "data": "synthetic",
-           "config": {"workload": f"{args.task} post_physics_step num_envs={args.num_envs} (CPU, host cores)",
-                      "task": args.task, "num_envs_per_gpu": args.num_envs},
+           "config": bench_config(args.task, args.num_envs, world),
            "cpu_baseline": cb,
            "e2e": {"value": cb["value"], "unit": "env-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
            "gpu_launches": 0}
@@ -463,7 +556,7 @@ def main():
     ap.add_argument("--replicas", type=int, default=0)
     ap.add_argument("--seed", type=int, default=0)
     ap.add_argument("--fall-frac", type=float, default=0.02)
-    ap.add_argument("--cpu-seconds", type=float, default=6.0)
+    ap.add_argument("--cpu-seconds", type=float, default=8.0)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-sweep", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")

@@ -527,6 +527,20 @@ int ige_anymal_scratch_words(int32_t num_envs);
 int ige_anymal_post_physics(const IgeAnymalParams *p, const IgeAnymalBuffers *b, void *stream);
 
 /* ------------------------------------------------------------------------------------------
+ * Episode statistics: fold the striped accumulator a step kernel adds into (Buffers.stats) into the
+ * <= IGE_NUM_STATS-float vector that is all-reduced across GPUs once per horizon (the
+ * reference keeps per-rank statistics, utils/rlgames_utils.py:89-107).  One tiny launch, off the step's
+ * critical path (the host double-buffers the accumulator, see distributed.StatsReducer).
+ * ------------------------------------------------------------------------------------------ */
+typedef struct IgeStatsSnapshotArgs {
+    float *stats;          /* [IGE_STATS_ROWS * IGE_STATS_STRIDE] accumulator rows */
+    float *out;            /* [IGE_NUM_STATS] column sums over the rows */
+    int32_t zero_stats;    /* != 0: leave the rows zeroed (a horizon's numbers never mix with the next one's) */
+    int32_t accumulate;    /* != 0: out += sums instead of out = sums */
+} IgeStatsSnapshotArgs;
+int ige_stats_snapshot(const IgeStatsSnapshotArgs *a, void *stream);
+
+/* ------------------------------------------------------------------------------------------
  * Library
  * ------------------------------------------------------------------------------------------ */
 int ige_version(void);

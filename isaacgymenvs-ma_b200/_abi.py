@@ -183,6 +183,10 @@ class IgeAnymalBuffers(C.Structure):
                 ("obs_clamped", _p), ("timeout_buf", _p), ("reset_ids", _p), ("reset_count", _p), ("scratch", _p)]
 
 
+class IgeStatsSnapshotArgs(C.Structure):
+    _fields_ = [("stats", _p), ("out", _p), ("zero_stats", _i), ("accumulate", _i)]
+
+
 def fill_array(carr, values):
     for i, v in enumerate(values):
         carr[i] = type(carr[0])(v) if isinstance(carr[0], int) else float(v)

@@ -25,6 +25,7 @@ _SIGS = {
     "ige_anymal_post_physics": (_abi.IgeAnymalParams, _abi.IgeAnymalBuffers),
     "ige_ma_rollout_step": (_abi.IgeRolloutStepArgs,),
     "ige_ma_discount_values": (_abi.IgeDiscountArgs,),
+    "ige_stats_snapshot": (_abi.IgeStatsSnapshotArgs,),
 }
 
 

@@ -50,42 +50,119 @@ def rank_seed(seed, rank):
 
 
 class StatsReducer:
-    """Sum all-reduce of the episode-statistics vector, off the step's critical path: the step
-    kernels keep adding into the env's accumulator while a snapshot is being reduced.
+    """Sum all-reduce of the episode-statistics vector, once per horizon, off the step's critical path.
 
-    On CUDA the snapshot and the NCCL all-reduce are issued on a SIDE stream that only waits for the step
-    stream's work up to now; the step stream never waits for the collective (a `work.wait()` on the step
-    stream put the ~15 us all-reduce latency into every horizon: 89 % weak-scaling efficiency at 2 GPUs).
-    ``wait()`` joins the side stream when the reduced numbers are actually needed."""
+    CUDA (the product path).  The accumulator the step kernels add into is DOUBLE-BUFFERED: horizon h adds
+    into ``rows[h & 1]`` while the previous horizon's ``rows[h & 1 ^ 1]`` is folded into the 16-float vector
+    (``ige_stats_snapshot``: column sums + re-zero, one tiny launch) and all-reduced over NCCL / NVLink.  Both
+    are issued by :meth:`fork` on a side stream and re-joined by :meth:`join`; called while a CUDA graph is being
+    captured they become a forked BRANCH of the horizon's graph, so a horizon costs the host exactly one graph
+    launch -- no Python, no ProcessGroup enqueue and no stream join between two step kernels (the eager
+    ``dist.all_reduce`` per horizon of round 1 held the host thread that feeds the step graphs for ~180 us:
+    49 % weak-scaling efficiency at the driver's 20-step window).  The collective overlaps the first steps
+    of the horizon; the reduced numbers lag by one horizon, which is what an asynchronous reduction means.
+
+    CPU (gloo, tests of the host logic): :meth:`start` with the 16-float vector, eager.
+    """
 
     def __init__(self, device):
         self.device = torch.device(device)
-        self.snap = torch.zeros(_abi.IGE_NUM_STATS, dtype=torch.float32, device=device)
-        self.side = torch.cuda.Stream(self.device) if self.device.type == "cuda" else None
+        self.cuda = self.device.type == "cuda"
+        self.reduced = torch.zeros(_abi.IGE_NUM_STATS, dtype=torch.float32, device=device)
+        self.snap = self.reduced          # round-1 name
+        n = _abi.IGE_STATS_ROWS * _abi.IGE_STATS_STRIDE
+        self.rows = [torch.zeros(n, dtype=torch.float32, device=device) for _ in range(2)] if self.cuda else None
+        self.side = torch.cuda.Stream(self.device) if self.cuda else None
+        self._free = torch.cuda.Event() if self.cuda else None     # the folded buffer is zeroed and reusable
         self._work = None
+        self._cur = 0
+        self.collectives = 0
+        if self.cuda:      # load the snapshot kernel now: its first launch must not happen inside a graph capture
+            with torch.cuda.device(self.device):
+                self._snapshot(self.rows[0])
+                torch.cuda.synchronize(self.device)
 
-    def start(self, stats_vector):
-        """`stats_vector`: the [IGE_NUM_STATS] tensor, or a callable returning it (evaluated on the side stream)."""
+    @staticmethod
+    def _multi():
         import torch.distributed as dist
-        multi = dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
-        if self.side is None:
-            self.snap.copy_(stats_vector() if callable(stats_vector) else stats_vector)
-            if multi:
-                self._work = dist.all_reduce(self.snap, op=dist.ReduceOp.SUM, async_op=True)
-            return
-        self.side.wait_stream(torch.cuda.current_stream(self.device))
+        return dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
+
+    # -- CUDA: graph-capturable pieces ---------------------------------------------------------------------
+    def attach(self, env, parity):
+        """Make `env`'s step kernels accumulate into rows[parity]."""
+        env.stats_rows = self.rows[parity & 1]
+
+    def warm(self):
+        """One eager collective so the NCCL communicator exists before any graph capture."""
+        if self._multi():
+            import torch.distributed as dist
+            dist.all_reduce(self.reduced, op=dist.ReduceOp.SUM)
+            torch.cuda.synchronize(self.device)
+            self.reduced.zero_()
+
+    def _snapshot(self, rows):
+        from . import _lib
+        a = _abi.IgeStatsSnapshotArgs()
+        a.stats, a.out, a.zero_stats, a.accumulate = rows.data_ptr(), self.reduced.data_ptr(), 1, 0
+        _lib.call("ige_stats_snapshot", a, stream=torch.cuda.current_stream(self.device).cuda_stream)
+
+    def issue(self, rows):
+        """Fold `rows` into the vector (re-zeroing them) and all-reduce it, on the CURRENT stream."""
+        self._snapshot(rows)
+        if not torch.cuda.is_current_stream_capturing():
+            self._free.record(torch.cuda.current_stream(self.device))
+        if self._multi():
+            import torch.distributed as dist
+            dist.all_reduce(self.reduced, op=dist.ReduceOp.SUM)     # NCCL, capturable; in place
+            self.collectives += 1
+
+    def fork(self, rows):
+        """Side branch: snapshot + all-reduce of `rows` (the PREVIOUS horizon's buffer).  Inside
+        ``torch.cuda.graph`` capture this forks the graph; pair with :meth:`join` before the capture ends."""
+        cur = torch.cuda.current_stream(self.device)
+        self.side.wait_stream(cur)
         with torch.cuda.stream(self.side):
-            self.snap.copy_(stats_vector() if callable(stats_vector) else stats_vector)
-            if multi:
-                dist.all_reduce(self.snap, op=dist.ReduceOp.SUM, async_op=True).wait()   # side stream waits, not the step's
+            self.issue(rows)
+
+    def join(self):
+        torch.cuda.current_stream(self.device).wait_stream(self.side)
+
+    # -- eager use -----------------------------------------------------------------------------------------
+    def start(self, stats):
+        """End of a horizon, eager.  `stats` is an env (CUDA: its accumulator is swapped for the spare buffer
+        and the full one is reduced on the side stream; the step stream only waits for the spare to be zeroed,
+        never for the collective) or the 16-float vector / a callable returning it (CPU, gloo)."""
+        import torch.distributed as dist
+        if self.cuda and hasattr(stats, "stats_rows"):
+            env = stats
+            full = env.stats_rows
+            if full is self.rows[0] or full is self.rows[1]:
+                self._cur = 0 if full is self.rows[0] else 1
+            else:                                  # first horizon of an env that owns its accumulator
+                self.rows[self._cur] = full
+            torch.cuda.current_stream(self.device).wait_event(self._free)   # spare buffer: zeroed long ago
+            env.stats_rows = self.rows[self._cur ^ 1]
+            self.fork(full)
+            return
+        vec = stats() if callable(stats) else stats
+        if self.cuda:
+            self.side.wait_stream(torch.cuda.current_stream(self.device))
+            with torch.cuda.stream(self.side):
+                self.reduced.copy_(vec)
+                if self._multi():
+                    dist.all_reduce(self.reduced, op=dist.ReduceOp.SUM)
+            return
+        self.reduced.copy_(vec)
+        if self._multi():
+            self._work = dist.all_reduce(self.reduced, op=dist.ReduceOp.SUM, async_op=True)
 
     def wait(self):
         if self._work is not None:
             self._work.wait()
             self._work = None
         if self.side is not None:
-            torch.cuda.current_stream(self.device).wait_stream(self.side)
-        return self.snap
+            self.join()
+        return self.reduced
 
     def result(self):
         v = self.wait().detach().cpu().tolist()

@@ -15,7 +15,22 @@ import os
 import sys
 import types
 
-REFERENCE_ROOT = os.environ.get("IGE_REFERENCE_ROOT", "/root/reference")
+_STAGED = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle", "_ref")
+
+
+def _pick_root():
+    """IGE_REFERENCE_ROOT, else /root/reference (build container), else the unmodified files staged under the
+    git-ignored oracle/_ref/ by tools/vendor_reference.py (this is what travels to the GPU box)."""
+    env = os.environ.get("IGE_REFERENCE_ROOT")
+    if env:
+        return env
+    for cand in ("/root/reference", _STAGED):
+        if os.path.isdir(os.path.join(cand, "isaacgymenvs", "tasks")):
+            return cand
+    return "/root/reference"
+
+
+REFERENCE_ROOT = _pick_root()
 
 
 def reference_available() -> bool:
@@ -83,7 +98,8 @@ def install():
     for name, rel in (("isaacgymenvs", "isaacgymenvs"),
                       ("isaacgymenvs.tasks", "isaacgymenvs/tasks"),
                       ("isaacgymenvs.tasks.base", "isaacgymenvs/tasks/base"),
-                      ("isaacgymenvs.utils", "isaacgymenvs/utils")):
+                      ("isaacgymenvs.utils", "isaacgymenvs/utils"),
+                      ("isaacgymenvs.learning", "isaacgymenvs/learning")):
         pkg = types.ModuleType(name)
         pkg.__path__ = [os.path.join(REFERENCE_ROOT, rel)]
         sys.modules[name] = pkg
@@ -100,13 +116,16 @@ class FakeGym:
     hold post-simulate state), set_*_indexed calls are *recorded* and never mutate anything
     (SURVEY.md section 8c)."""
 
-    def __init__(self):
+    def __init__(self, record=True):
         self.calls = []
+        self.record = record          # False: set_* calls are dropped (timed baseline runs)
 
     def __getattr__(self, name):
         if name.startswith("__"):
             raise AttributeError(name)
         if name.startswith("refresh_"):
+            return lambda *a, **k: None
+        if not self.record:
             return lambda *a, **k: None
 
         def rec(sim, *args):

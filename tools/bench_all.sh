@@ -1,13 +1,13 @@
 #!/bin/bash
 # Per-task bench lines (BASELINE.json configs[1..3] + the other tasks) -> gpurun_out/bench_tasks.jsonl
-out=gpurun_out/bench_tasks.jsonl; : > $out
+out=gpurun_out/${ROUND:-r2}_bench_tasks.jsonl; : > $out
 for spec in "Ant 16384" "Humanoid 32768" "ShadowHand 16384" "FrankaReachMA 8192" "FrankaCollectMA 8192" "FrankaCombineMA 8192" "FrankaPPMA 8192" "Cartpole 16384" "Humanoid 1048576" "ShadowHand 262144" "FrankaPPMA 262144" "Cartpole 4194304"; do
   set -- $spec
   timeout 300 python bench.py --task $1 --num-envs $2 --steps 512 --warmup 32 --no-sweep --no-cpu >> $out 2>gpurun_out/bench_$1_$2.err || echo "{\"task\": \"$1\", \"failed\": true}" >> $out
 done
 python - <<'PY'
 import json
-for l in open('gpurun_out/bench_tasks.jsonl'):
+for l in open("gpurun_out/" + __import__("os").environ.get("ROUND", "r2") + "_bench_tasks.jsonl"):
     d = json.loads(l)
     if d.get('failed'): print(d); continue
     c = d['config']; r = d['roofline']

@@ -1,0 +1,52 @@
+#!/bin/bash
+# One parametrised GPU-box script (replaces the per-lease gpu_round*.sh of round 1).
+#   bash tools/gpu.sh <action> [<action> ...]        actions run in order; logs go to gpurun_out/
+# actions:
+#   tests            pytest -m gpu (whole suite)            tests:<expr>   pytest -m gpu -k <expr>
+#   smoke            __graft_entry__.smoke()
+#   bench            default bench.py (driver's N=1 line)   ref            bench.py --impl reference
+#   driver           bench.py --steps 20 --warmup 5 (the driver's own command, N=1)
+#   scale:<N>        torchrun bench.py --gpus N --steps 20 --warmup 5 (+ a --steps 2048 line)
+#   tasks            per-task bench lines (tools/bench_all.sh)
+#   launches         ncu launch list of the default bench's timed region
+#   ncu:<Task>:<N>:<tag>   ncu --set full of one launch (tools/prof.py), summary into gpurun_out/
+#   sanitize         compute-sanitizer memcheck + racecheck over a reduced -m gpu selection
+#   floors           tools/floors.py (empty-launch / copy floors)
+mkdir -p gpurun_out
+R=${ROUND:-r2}
+for act in "$@"; do
+  IFS=: read -r a b c d <<< "$act"
+  case "$a" in
+    tests)
+      if [ -n "$b" ]; then python -m pytest tests -m gpu -x -q -k "$b" > gpurun_out/pytest_gpu_k.log 2>&1; echo "pytest -k '$b' rc=$?"; tail -5 gpurun_out/pytest_gpu_k.log
+      else python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -5 gpurun_out/pytest_gpu.log; fi ;;
+    smoke) python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?"; tail -3 gpurun_out/smoke.log ;;
+    bench) python bench.py > gpurun_out/${R}_bench_default.json 2> gpurun_out/bench_default.err; echo "bench rc=$?"; tail -2 gpurun_out/bench_default.err; cut -c1-1500 gpurun_out/${R}_bench_default.json ;;
+    driver) python bench.py --gpus 1 --steps 20 --warmup 5 > gpurun_out/${R}_bench_driver_n1.json 2> gpurun_out/bench_driver.err; echo "driver-bench rc=$?"; tail -2 gpurun_out/bench_driver.err; cut -c1-900 gpurun_out/${R}_bench_driver_n1.json ;;
+    ref) python bench.py --impl reference --steps 20 --warmup 5 > gpurun_out/${R}_bench_reference.json 2> gpurun_out/bench_reference.err; echo "ref rc=$?"; tail -2 gpurun_out/bench_reference.err; cut -c1-1200 gpurun_out/${R}_bench_reference.json ;;
+    scale)
+      for steps in 20 2048; do
+        python -m torch.distributed.run --nnodes=1 --nproc-per-node $b --master-addr 127.0.0.1 --master-port 29533 \
+          bench.py --gpus $b --steps $steps --warmup 5 --no-sweep > gpurun_out/${R}_bench_n${b}_s${steps}.json 2> gpurun_out/bench_n${b}_s${steps}.err
+        echo "scale N=$b steps=$steps rc=$?"; tail -3 gpurun_out/bench_n${b}_s${steps}.err | cut -c1-300; cut -c1-700 gpurun_out/${R}_bench_n${b}_s${steps}.json
+      done ;;
+    tasks) bash tools/bench_all.sh > gpurun_out/${R}_bench_tasks.txt 2>&1; cat gpurun_out/${R}_bench_tasks.txt ;;
+    launches)
+      ncu --profile-from-start off --metrics gpu__time_duration.sum --clock-control none -c 400 --csv \
+        --log-file gpurun_out/${R}_launches_bench.csv python bench.py --steps 64 --warmup 16 --no-sweep --no-cpu --no-e2e > gpurun_out/ncu_launch.log 2>&1
+      echo "ncu launches rc=$?" ;;
+    ncu)
+      timeout 400 ncu --set full --clock-control none --import-source on -s 2 -c 1 -f -o gpurun_out/${R}_prof_$d \
+        python tools/prof.py --task $b --num-envs $c --steps 4 --replicas 4 --hot > gpurun_out/ncu_$d.log 2>&1
+      echo "ncu $d rc=$?"; python tools/ncu_summary.py gpurun_out/${R}_prof_$d.ncu-rep > gpurun_out/${R}_ncu_full_$d.txt 2>&1; cat gpurun_out/${R}_ncu_full_$d.txt ;;
+    sanitize)
+      SEL="test_cuda_matches_reference_golden or test_reset_extremes or test_stats or test_reducer or rollout_golden or anymal_golden"
+      for tool in memcheck racecheck; do
+        timeout 1500 compute-sanitizer --tool $tool --error-exitcode 9 python -m pytest tests -m gpu -x -q -k "$SEL" > gpurun_out/${R}_sanitizer_$tool.log 2>&1
+        echo "compute-sanitizer $tool rc=$?"; tail -6 gpurun_out/${R}_sanitizer_$tool.log
+      done ;;
+    floors) python tools/floors.py > gpurun_out/${R}_floors.txt 2>&1; cat gpurun_out/${R}_floors.txt ;;
+    *) echo "unknown action $act" ;;
+  esac
+done
+ls -la gpurun_out | tail -30
