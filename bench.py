@@ -188,14 +188,14 @@ def run_ours(args):
     full, rem = divmod(args.steps, HORIZON)
     # the remainder continues with the replicas (and the accumulator) of the horizon that would come next
     rem_envs = [envs[((full % n_chunks) * HORIZON + i) % replicas] for i in range(rem)]
-    rem_graph = capture(rem_envs, lambda e: e.hot_step(), error_mode=mode) if rem else None
+    rem_graph = [capture(rem_envs, lambda e: e.hot_step(), error_mode=mode)] if rem else []
 
     def timed(steps, warmup):
         def body():
             for i in range(full):
                 chunks[i % n_chunks].replay()
-            if rem_graph is not None:
-                rem_graph.replay()
+            for g in rem_graph:
+                g.replay()
         w = max(-(-warmup // HORIZON), 3)
         for i in range(w):
             chunks[(i - w) % n_chunks].replay()      # ends on the last chunk: body() starts at chunk 0
@@ -273,10 +273,21 @@ def run_ours(args):
     if rank == 0 and world == 1 and not args.no_cpu:
         out["cpu_baseline"] = host_baselines(pkg, args, seconds=args.cpu_seconds)
     if rank == 0:
-        print(json.dumps(out))
+        print(json.dumps(out), flush=True)
     if dist is not None:
+        # NCCL keeps a reference per captured graph and ncclCommDestroy waits for them: drop the graphs that hold
+        # the captured all-reduce BEFORE tearing the process group down (a rank that skipped this hung forever in
+        # destroy_process_group after printing its line).  The timer is a last resort against a wedged teardown.
+        torch.cuda.synchronize()
+        chunks.clear()
+        rem_graph.clear()
+        import gc
+        gc.collect()
+        torch.cuda.synchronize()
+        threading.Timer(30.0, lambda: os._exit(0)).start()
         dist.barrier()
         dist.destroy_process_group()
+        os._exit(0)
 
 
 def _time_steps(step, steps, warmup, device, dist):

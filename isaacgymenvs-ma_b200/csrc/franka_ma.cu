@@ -441,316 +441,510 @@ __global__ void __launch_bounds__(NT) franka_ma_kernel(const __grid_constant__ I
 
 
 // ---------------------------------------------------------------------------------------------
-// Pair kernel: the shipped configuration of all four tasks (numAgents = numTargets = 2,
-// cfg/task/Franka*MA.yaml) with every per-env quantity in registers.
+// Rows kernel: the shipped configuration of all four tasks (numAgents = numTargets = 2,
+// cfg/task/Franka*MA.yaml), ONE launch for every variant.
 // ---------------------------------------------------------------------------------------------
-// Same thread-per-env ownership as franka_ma_kernel, but V / A / T / num_actions are compile-time: the
-// agent and cube loops unroll, nothing is indexed dynamically (the generic kernel keeps eef / cube /
-// fsm in local memory), and every load whose address depends only on the env index -- gripper, base and
-// contact rows, actions, the flags as 16-B vectors, the cross-env rows of compute_global_FSM -- is issued
-// before the reset section, so a step costs two dependent DRAM round trips (flags + state, then the cube
-// rows a reset may have rewritten) instead of one per stage.
+// One thread per AGENT ROW (row = env * 2 + agent; the two lanes of an env sit next to each other and trade the
+// partner's gripper / cube / FSM with shuffles), 32-env tiles, persistent CTAs over contiguous tile ranges:
+// BASELINE.json's 8192 x 2 configuration is 512 warps on 256 CTAs instead of 256 warps on 128 (round 1: 3 % of
+// the warp slots active), the per-thread dependent chain is half as long, and every load whose address depends
+// only on the row index is issued before anything is consumed.
+//
+// Resets happen in registers: the two lanes of a flagged env draw the env's uniforms (<= 6 Philox calls per
+// lane; injected mode: loads by reset rank), keep the new cube / destination rows for the arithmetic below and
+// write them out with fire-and-forget stores -- no thread ever re-reads a row its own launch rewrote.
+//
+// compute_global_FSM pairs flat row k with d_ecp[k] of a flatten()ed (2, N) stack (franka_PPMA.py:606), i.e.
+// row k needs the gripper and one cube of ANOTHER env j = k or k - N, whose cube row env j's own reset may be
+// rewriting in this very launch.  Round 1 ran the reset as a separate launch for that reason.  Here the reader
+// never looks at a row that is being rewritten: post-reset cube positions are a pure function of (env, draw,
+// step | reset rank), so it recomputes env j's when env j resets and reads memory when it does not.  "Does env j
+// reset" is taken from env j's ENTRY flags, which every CTA snapshots (a ballot per tile in shared memory) in
+// the prologue where it also counts its own flags for the reset list; the flags are only overwritten after the
+// launch epoch has advanced, i.e. after every CTA has finished that prologue (ige::list_cta_prefix: the last
+// CTA to take its ticket advances the epoch; all CTAs are co-resident).
+constexpr int RT_E = 32;                // envs per tile
+constexpr int RT_NT = 2 * RT_E;         // threads per CTA = rows per tile
+constexpr int RT_MAX_TILES = 96;        // tiles per CTA the prologue snapshot has room for
+
+// four consecutive uniforms j = 4 blk .. 4 blk + 3 of draw `draw` for env `env` (reset rank `rank`)
+__device__ __forceinline__ void ma_uniform4(const IgeMAResetRand &r, uint64_t step, int draw, int rank, int env, int cols,
+                                            int blk, float (&u)[4]) {
+    if (r.mode == IGE_RAND_PHILOX) {
+        uint32_t c[4] = {(uint32_t)env, ((uint32_t)draw << 16) | (uint32_t)blk, (uint32_t)step, (uint32_t)(step >> 32)};
+        ige::philox4x32_10(c, (uint32_t)r.seed, (uint32_t)(r.seed >> 32));
+#pragma unroll
+        for (int k = 0; k < 4; ++k) u[k] = (float)(c[k] >> 8) * (1.0f / 16777216.0f);
+    } else {
+        const float *src = r.u[draw] + (size_t)rank * cols + blk * 4;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) u[k] = blk * 4 + k < cols ? __ldg(src + k) : 0.0f;
+    }
+}
+
 template <int V>
-__global__ void __launch_bounds__(NT) franka_ma_pair_kernel(const __grid_constant__ IgeFrankaMAParams p,
-                                                            const __grid_constant__ IgeFrankaMABuffers b, const int phase,
-                                                            const int use_tma) {
+__global__ void __launch_bounds__(RT_NT) franka_ma_rows_kernel(const __grid_constant__ IgeFrankaMAParams p,
+                                                               const __grid_constant__ IgeFrankaMABuffers b,
+                                                               const int num_tiles, const int tiles_per_cta,
+                                                               const int use_tma) {
     constexpr int A = 2, T = 2;
     constexpr int NA = V == IGE_FRANKA_REACH ? 6 : 7;
     constexpr int NO = V == IGE_FRANKA_REACH ? 19 : V == IGE_FRANKA_COLLECT ? 28 : V == IGE_FRANKA_COMBINE ? 48 : 50;
     constexpr bool PAIRED = V == IGE_FRANKA_COMBINE || V == IGE_FRANKA_PP;
-    extern __shared__ __align__(128) float obs_tile[];  // TE * A * NO
+    constexpr bool MEANS = V != IGE_FRANKA_REACH;   // Reach logs no component means (franka_reach_MA.py:928-960)
+    __shared__ __align__(128) float obs_tile[2][RT_NT * NO];
+    __shared__ uint32_t s_pmask[PAIRED ? RT_MAX_TILES : 1][2];   // bit = "the partner env of this row resets in this launch"
+    __shared__ uint32_t s_own[RT_MAX_TILES];                      // reset ballot of my tiles
+    __shared__ uint64_t s_step;
     __shared__ int s_last;
-    __shared__ float s_u[NT / 32][32];
-    const int tid = threadIdx.x, lane = tid & 31;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int N = p.num_envs;
-    const int e0 = blockIdx.x * TE;
-    const int ne = min(TE, N - e0);
-    const int e = e0 + tid;
-    const bool valid = tid < ne;
-    const int ec = valid ? e : N - 1;   // clamped: invalid lanes load a real row and discard it
-    const uint64_t step = (p.rand.mode == IGE_RAND_PHILOX && p.rand.step)
-                              ? *reinterpret_cast<const volatile uint64_t *>(p.rand.step) : 0ull;
+    const int first = blockIdx.x * tiles_per_cta;
+    const int my_tiles = min(tiles_per_cta, num_tiles - first);
+    const bool emit = b.list.scratch != nullptr;
+    const int a = tid & 1;                     // my agent
+    auto partner_env = [&](int row, bool &first_half) {
+        first_half = row < N;
+        return first_half ? row : row - N;
+    };
 
-    // ---- loads that no reset can change ----
-    longlong2 prog = *reinterpret_cast<const longlong2 *>(b.progress_buf + (size_t)ec * A);
-    longlong2 rst = *reinterpret_cast<const longlong2 *>(b.reset_buf + (size_t)ec * A);
-    float eef[A][7], base[A][7], act[A][NA], cf[A][3], je[A][3];
-    if (phase != PH_RESET) {
-#pragma unroll
-        for (int a = 0; a < A; ++a) {
-            const float *r = body_row(p, b, ec, p.eef_body_start, p.eef_body_step, a);
-#pragma unroll
-            for (int i = 0; i < 7; ++i) eef[a][i] = __ldg(r + i);
-            if (V != IGE_FRANKA_REACH) {
-                const float *bs = body_row(p, b, ec, p.base_body_start, p.base_body_step, a);
-#pragma unroll
-                for (int i = 0; i < 7; ++i) base[a][i] = __ldg(bs + i);
+    // ---- prologue: step word, own-flag ballots (-> reset-list count), partner-reset ballots ----
+    if (tid == 0) s_step = (p.rand.mode == IGE_RAND_PHILOX && p.rand.step)
+                               ? *reinterpret_cast<const volatile uint64_t *>(p.rand.step) : 0ull;
+    int cnt = 0;
+    if (warp == 0) {
+        for (int t = 0; t < my_tiles; ++t) {
+            const int e = (first + t) * RT_E + lane;
+            bool f = false;
+            if (e < N) {
+                const longlong2 r = *reinterpret_cast<const longlong2 *>(b.reset_buf + (size_t)e * A);
+                f = r.x != 0 && r.y != 0;
             }
-            const float *ap = b.actions + ((size_t)ec * A + a) * NA;
-#pragma unroll
-            for (int j = 0; j < NA; ++j) act[a][j] = __ldg(ap + j);
-            if (V == IGE_FRANKA_REACH) {
-                const float *c = b.contact_forces + ((size_t)ec * p.num_bodies + p.hand_body_start + p.hand_body_step * a) * 3;
-#pragma unroll
-                for (int i = 0; i < 3; ++i) cf[a][i] = __ldg(c + i);
-            }
-            if (PAIRED) {  // compute_global_FSM's partner rows (franka_PPMA.py:597-611, see the header)
-                const size_t row = (size_t)ec * A + a;
-                const bool first_half = row < (size_t)N;
-                const int j = first_half ? (int)row : (int)(row - N);
-                const float *r2 = body_row(p, b, j, p.eef_body_start, p.eef_body_step, first_half ? 0 : 1);
-#pragma unroll
-                for (int i = 0; i < 3; ++i) je[a][i] = __ldg(r2 + i);
-            }
+            const uint32_t m = __ballot_sync(0xffffffffu, f);
+            if (lane == 0) s_own[t] = m;
+            cnt += __popc(m);
         }
-    }
-
-    // ---- post_physics_step :821-826: progress++, agent flags -> reset_idx (AND filter) ----
-    if (phase != PH_COMPUTE) {
-        const bool did_reset = valid && rst.x != 0 && rst.y != 0;
-        const uint32_t mask = __ballot_sync(0xffffffffu, did_reset);
-        if (b.list.scratch && lane == 0 && e < N) ige::publish_tile_mask(b.list, e >> 5, mask);
-        for (uint32_t m = mask; m; m &= m - 1)  // the warp resets its flagged envs one after the other, together
-            reset_env_coop(p, b, step, e - lane + __ffs(m) - 1, lane, s_u[tid >> 5]);
-        if (did_reset) { prog = make_longlong2(0, 0); rst = make_longlong2(0, 0); }
-        else { prog.x += 1; prog.y += 1; }
-        if (valid) *reinterpret_cast<longlong2 *>(b.progress_buf + (size_t)e * A) = prog;
-    }
-    if (phase == PH_RESET) {
-        if (b.list.scratch) ige::finish_reset_list(b.list, N, nullptr, lane == 0);
-        return;
-    }
-
-
-    // ---- rows a reset may have rewritten (own warp's writes are ordered by reset_env_coop's __syncwarp) ----
-    float cube[T][7], dest[A][3], sb[3], jc[A][3];
-#pragma unroll
-    for (int c = 0; c < T; ++c) {
-        const float *r = actor_row(p, b, ec, p.cube_actor_start + p.cube_actor_step * c);
-#pragma unroll
-        for (int i = 0; i < 7; ++i) cube[c][i] = r[i];
-    }
-    if (V == IGE_FRANKA_PP) {
-#pragma unroll
-        for (int a = 0; a < A; ++a) {
-            const float *d = actor_row(p, b, ec, p.dest_actor_start + p.dest_actor_step * a);
-#pragma unroll
-            for (int i = 0; i < 3; ++i) dest[a][i] = d[i];
-        }
-    }
-    if (V == IGE_FRANKA_COMBINE) {
-        const float *r = actor_row(p, b, ec, p.stack_base_actor);
-#pragma unroll
-        for (int i = 0; i < 3; ++i) sb[i] = r[i];
     }
     if (PAIRED) {
-#pragma unroll
-        for (int a = 0; a < A; ++a) {
-            const size_t row = (size_t)ec * A + a;
-            const bool first_half = row < (size_t)N;
-            const int j = first_half ? (int)row : (int)(row - N);
-            const float *r = actor_row(p, b, j, p.cube_actor_start + p.cube_actor_step * (first_half ? 1 : 0));
-#pragma unroll
-            for (int i = 0; i < 3; ++i) jc[a][i] = r[i];
+        // warp w snapshots the partner flags of rows [32 w, 32 w + 32) of every tile
+        for (int t = 0; t < my_tiles; ++t) {
+            const int row = ((first + t) * RT_E) * A + tid;
+            bool f = false;
+            if (row < N * A) {
+                bool fh;
+                const int j = partner_env(row, fh);
+                const longlong2 r = *reinterpret_cast<const longlong2 *>(b.reset_buf + (size_t)j * A);
+                f = r.x != 0 && r.y != 0;
+            }
+            const uint32_t m = __ballot_sync(0xffffffffu, f);
+            if (lane == 0) s_pmask[t][warp] = m;
         }
+    }
+    __syncthreads();   // every thread has read what it needs of the ENTRY flags and the step word
+    const uint64_t step = s_step;
+    uint64_t tag = 0;
+    int list_off = 0;
+    if (warp == 0 && emit) {
+        tag = *reinterpret_cast<const volatile uint64_t *>(b.list.scratch) + 1;
+        list_off = ige::list_cta_prefix(b.list, cnt, p.rand.step);   // every lane of warp 0 holds it
     }
 
     float comp[NC];
 #pragma unroll
     for (int i = 0; i < NC; ++i) comp[i] = 0.0f;
-    float st_rew = 0.f, st_done = 0.f, st_to = 0.f, st_len = 0.f;
-    if (valid) {
-        // _get_min_relative_pos (franka_reach_MA.py:521-531)
-        float ncube[A][3];
-        unsigned touched = 0u;
+    float st_rew = 0.f, st_done = 0.f, st_to = 0.f, st_len = 0.f, st_n = 0.f;
+    bool flags_open = !(PAIRED && emit);   // may reset_buf be overwritten yet?
+
+    for (int t = 0; t < my_tiles; ++t) {
+        const int e0 = (first + t) * RT_E;
+        const int ne = min(RT_E, N - e0);
+        const int e = e0 + (tid >> 1);
+        const bool valid = (tid >> 1) < ne;
+        const int ec = valid ? e : N - 1;          // clamped: invalid lanes load a real row and discard it
+        const size_t row = (size_t)ec * A + a;
+        float *otile = obs_tile[t & 1];
+
+        // ---- every load whose address depends only on the row ----
+        long long prog = b.progress_buf[row], rst = b.reset_buf[row];
+        float eef[7], base[7], act[NA], cf[3], cube[7], dest[3], sb[3], je[3], jc[3];
+        {
+            const float *r = body_row(p, b, ec, p.eef_body_start, p.eef_body_step, a);
 #pragma unroll
-        for (int a = 0; a < A; ++a) {
-            float best = 0.0f, bx = 0.f, by = 0.f, bz = 0.f;
-            int bi = 0;
-#pragma unroll
-            for (int c = 0; c < T; ++c) {
-                const float d = ige::norm3(cube[c][0] - eef[a][0], cube[c][1] - eef[a][1], cube[c][2] - eef[a][2]);
-                if (c == 0 || d < best) { best = d; bi = c; bx = cube[c][0]; by = cube[c][1]; bz = cube[c][2]; }
-            }
-            ncube[a][0] = bx; ncube[a][1] = by; ncube[a][2] = bz;
-            touched |= 1u << bi;
+            for (int i = 0; i < 7; ++i) eef[i] = __ldg(r + i);
         }
-        int fsm[A];
-        float md[A];
+        if (V != IGE_FRANKA_REACH) {
+            const float *r = body_row(p, b, ec, p.base_body_start, p.base_body_step, a);
+#pragma unroll
+            for (int i = 0; i < 7; ++i) base[i] = __ldg(r + i);
+        }
+        {
+            const float *r = b.actions + row * NA;
+#pragma unroll
+            for (int j = 0; j < NA; ++j) act[j] = __ldg(r + j);
+        }
+        if (V == IGE_FRANKA_REACH) {
+            const float *r = b.contact_forces + ((size_t)ec * p.num_bodies + p.hand_body_start + p.hand_body_step * a) * 3;
+#pragma unroll
+            for (int i = 0; i < 3; ++i) cf[i] = __ldg(r + i);
+        }
+        {
+            const float *r = actor_row(p, b, ec, p.cube_actor_start + p.cube_actor_step * a);   // cube `a` (pre-reset)
+#pragma unroll
+            for (int i = 0; i < 7; ++i) cube[i] = r[i];
+        }
+        if (V == IGE_FRANKA_PP) {
+            const float *r = actor_row(p, b, ec, p.dest_actor_start + p.dest_actor_step * a);
+#pragma unroll
+            for (int i = 0; i < 3; ++i) dest[i] = r[i];
+        }
+        if (V == IGE_FRANKA_COMBINE) {
+            const float *r = actor_row(p, b, ec, p.stack_base_actor);
+#pragma unroll
+            for (int i = 0; i < 3; ++i) sb[i] = r[i];
+        }
+        bool j_first = false, j_reset = false;
+        int j = 0;
+        if (PAIRED) {
+            j = partner_env((int)row, j_first);
+            j_reset = (s_pmask[t][warp] >> lane) & 1u;
+            const float *r = body_row(p, b, j, p.eef_body_start, p.eef_body_step, j_first ? 0 : 1);
+#pragma unroll
+            for (int i = 0; i < 3; ++i) je[i] = __ldg(r + i);
+            if (!j_reset) {   // env j keeps its cubes in this launch: nobody writes this row
+                const float *c = actor_row(p, b, j, p.cube_actor_start + p.cube_actor_step * (j_first ? 1 : 0));
+#pragma unroll
+                for (int i = 0; i < 3; ++i) jc[i] = c[i];
+            }
+        }
+
+        // ---- post_physics_step :821-826: progress++, agent flags -> reset_idx (AND filter) ----
+        const long long rst_o = __shfl_xor_sync(0xffffffffu, rst, 1);
+        const bool did_reset = valid && rst != 0 && rst_o != 0;
+        if (did_reset) {
+            const IgeMAResetRand &rr = p.rand;
+            const int rk = rr.env_rank ? __ldg(rr.env_rank + e) : 0;
+            float u0[4], u1[4], u3[4], u4[3][4];
+            ma_uniform4(rr, step, 0, rk, e, T, 0, u0);
+            ma_uniform4(rr, step, 1, rk, e, 2 * T, 0, u1);
+            if (PAIRED) ma_uniform4(rr, step, 3, rk, e, V == IGE_FRANKA_PP ? 2 * T : 2, 0, u3);
+#pragma unroll
+            for (int k = 0; k < 3; ++k) ma_uniform4(rr, step, 4, rk, e, 9, k, u4[k]);
+            // _reset_init_cube_state: cube `a` (franka_reach_MA.py:676-704)
+            cube[0] = p.cube_xy_center[0] + p.cube_xy_mult * (u1[2 * a] - 0.5f);
+            cube[1] = p.cube_xy_center[1] + p.cube_xy_mult * (u1[2 * a + 1] - 0.5f);
+            cube[2] = p.cube_z_base + u0[a] * p.cube_z_range;
+            cube[3] = cube[4] = cube[5] = 0.0f; cube[6] = 1.0f;
+            float *ci = b.init_cubeA_state + ((size_t)e * T + a) * 13;
+            float *cr = actor_row(p, b, e, p.cube_actor_start + p.cube_actor_step * a);
+#pragma unroll
+            for (int i = 0; i < 13; ++i) { const float v = i < 7 ? cube[i] : 0.0f; ci[i] = v; cr[i] = v; }
+            if (V == IGE_FRANKA_PP) {  // _reset_dest_cube_state franka_PPMA.py:862-895
+                dest[0] = p.aux_xy_center_x[a] + p.aux_xy_mult * (u3[2 * a] - 0.5f);
+                dest[1] = p.aux_xy_center_y + p.aux_xy_mult * (u3[2 * a + 1] - 0.5f);
+                dest[2] = p.aux_z_base + 0.0f;
+                float *dr = actor_row(p, b, e, p.dest_actor_start + p.dest_actor_step * a);
+#pragma unroll
+                for (int i = 0; i < 13; ++i) dr[i] = i < 3 ? dest[i] : (i == 6 ? 1.0f : 0.0f);
+            }
+            if (V == IGE_FRANKA_COMBINE) {  // _reset_stack_base_cube_state franka_combine_MA.py:885-908
+                sb[0] = p.aux_xy_center_x[0] + p.aux_xy_mult * (u3[0] - 0.5f);
+                sb[1] = p.aux_xy_center_y + p.aux_xy_mult * (u3[1] - 0.5f);
+                sb[2] = p.aux_z_base + 0.0f;
+                if (a == 0) {
+                    float *dr = actor_row(p, b, e, p.stack_base_actor);
+#pragma unroll
+                    for (int i = 0; i < 13; ++i) dr[i] = i < 3 ? sb[i] : (i == 6 ? 1.0f : 0.0f);
+                }
+            }
+            // arm `a`: the SAME joint sample is tiled over the arms (franka_reach_MA.py:638-656)
+#pragma unroll
+            for (int jj = 0; jj < 9; ++jj) {
+                float v = p.franka_default_dof_pos[jj] + p.dof_noise_mult * (u4[jj >> 2][jj & 3] - 0.5f);
+                v = fminf(v, p.franka_dof_upper[jj]);
+                v = fmaxf(v, p.franka_dof_lower[jj]);
+                const float pos = jj >= 7 ? p.franka_default_dof_pos[jj] : v;
+                const size_t k = (size_t)e * p.num_dofs + a * 9 + jj;
+                reinterpret_cast<float2 *>(b.dof_state)[k] = make_float2(pos, 0.0f);
+                b.pos_control[k] = pos;
+                b.effort_control[k] = 0.0f;
+            }
+            prog = 0; rst = 0;
+        } else {
+            prog += 1;
+        }
+        if (PAIRED && j_reset) {   // env j's cube (j_first ? 1 : 0) as env j's own reset writes it
+            const IgeMAResetRand &rr = p.rand;
+            const int rk = rr.env_rank ? __ldg(rr.env_rank + j) : 0;
+            const int c = j_first ? 1 : 0;
+            float u0[4], u1[4];
+            ma_uniform4(rr, step, 0, rk, j, T, 0, u0);
+            ma_uniform4(rr, step, 1, rk, j, 2 * T, 0, u1);
+            jc[0] = p.cube_xy_center[0] + p.cube_xy_mult * (u1[2 * c] - 0.5f);
+            jc[1] = p.cube_xy_center[1] + p.cube_xy_mult * (u1[2 * c + 1] - 0.5f);
+            jc[2] = p.cube_z_base + u0[c] * p.cube_z_range;
+        }
+
+        // ---- the partner lane's rows ----
+        float eef_o[7], cube_o[7], dest_o[3];
+#pragma unroll
+        for (int i = 0; i < 7; ++i) {
+            eef_o[i] = __shfl_xor_sync(0xffffffffu, eef[i], 1);
+            cube_o[i] = __shfl_xor_sync(0xffffffffu, cube[i], 1);
+        }
+        if (V == IGE_FRANKA_PP) {
+#pragma unroll
+            for (int i = 0; i < 3; ++i) dest_o[i] = __shfl_xor_sync(0xffffffffu, dest[i], 1);
+        }
+        // cube[0] / cube[1] in the reference's indexing
+        const float *c0 = a == 0 ? cube : cube_o, *c1 = a == 0 ? cube_o : cube;
+
+        // ---- _update_states / compute_FSM ----
+        float ncube[3];
+        int near;
+        {   // _get_min_relative_pos (franka_reach_MA.py:521-531): first minimum wins
+            const float d0 = ige::norm3(c0[0] - eef[0], c0[1] - eef[1], c0[2] - eef[2]);
+            const float d1 = ige::norm3(c1[0] - eef[0], c1[1] - eef[1], c1[2] - eef[2]);
+            near = d1 < d0 ? 1 : 0;
+            const float *nc = near ? c1 : c0;
+            ncube[0] = nc[0]; ncube[1] = nc[1]; ncube[2] = nc[2];
+        }
+        const int near_o = __shfl_xor_sync(0xffffffffu, near, 1);
+        const unsigned touched = (1u << near) | (1u << near_o);
+        int fsm = 0;
+        float md;
         const float on_th = (float)((double)p.cubeA_size * 0.5 * 0.9);
-#pragma unroll
-        for (int a = 0; a < A; ++a) {
-            const bool closed = act[a][NA - 1] < 0.0f;
-            int sx = 0;
-            if (V == IGE_FRANKA_REACH || V == IGE_FRANKA_COLLECT) {
-                const float *nc = ncube[a];
-                md[a] = ige::norm3(nc[0] - eef[a][0], nc[1] - eef[a][1], nc[2] - eef[a][2]);
-                if (V == IGE_FRANKA_COLLECT) {  // franka_collect_MA.py:549-606
-                    const bool close = md[a] <= on_th;
-                    const bool holding = close && closed;
-                    const bool high = (nc[2] - 1.05f) > (float)((double)p.wall_height + (double)p.cubeA_size / 2);
-                    const bool in_area = (nc[1] > (float)((double)p.wall_pos_y + (double)p.cubeA_size * 1.)) && (fabsf(nc[0]) < 0.6f);
-                    const bool low = (nc[2] - 1.05f) < (float)((double)p.wall_height / 2.);
-                    if (close) sx = 1;
-                    if (holding) sx = 2;
-                    if (holding && high) sx = 3;
-                    if (holding && in_area) sx = 4;
-                    if (holding && in_area && low) sx = 5;
-                    if (holding && in_area && low && !closed) sx = 6;
-                }
-            } else {  // Combine :565-611 / PP :561-595: own cube
-                md[a] = ige::norm3(cube[a][0] - eef[a][0], cube[a][1] - eef[a][1], cube[a][2] - eef[a][2]);
-                const bool on = md[a] <= on_th;
-                if (on) sx = 1;
-                if (on && closed) sx = 2;
-                if (V == IGE_FRANKA_PP) {
-                    const float dz = dest[a][2] - cube[a][2];
-                    const bool lifted = fabsf(dz) >= (float)(((double)p.dest_size + (double)p.cubeA_size) / 2.);
-                    const bool align = ige::norm2(dest[a][0] - cube[a][0], dest[a][1] - cube[a][1]) < (float)((0.05) * 0.5);
-                    const bool stackable = fabsf(dz) <= (float)((double)p.cubeA_size * 0.8660 + (double)p.dest_size / 2.);
-                    if (on && lifted) sx = 3;
-                    if (align) sx = 4;
-                    if (align && stackable) sx = 5;
-                    if (align && stackable && !closed) sx = 6;
-                }
+        const bool closed = act[NA - 1] < 0.0f;
+        if (V == IGE_FRANKA_REACH || V == IGE_FRANKA_COLLECT) {
+            md = ige::norm3(ncube[0] - eef[0], ncube[1] - eef[1], ncube[2] - eef[2]);
+            if (V == IGE_FRANKA_COLLECT) {  // franka_collect_MA.py:549-606
+                const bool close = md <= on_th;
+                const bool holding = close && closed;
+                const bool high = (ncube[2] - 1.05f) > (float)((double)p.wall_height + (double)p.cubeA_size / 2);
+                const bool in_area = (ncube[1] > (float)((double)p.wall_pos_y + (double)p.cubeA_size * 1.)) && (fabsf(ncube[0]) < 0.6f);
+                const bool low = (ncube[2] - 1.05f) < (float)((double)p.wall_height / 2.);
+                if (close) fsm = 1;
+                if (holding) fsm = 2;
+                if (holding && high) fsm = 3;
+                if (holding && in_area) fsm = 4;
+                if (holding && in_area && low) fsm = 5;
+                if (holding && in_area && low && !closed) fsm = 6;
             }
-            fsm[a] = sx;
+        } else {  // Combine :565-611 / PP :561-595: own cube
+            md = ige::norm3(cube[0] - eef[0], cube[1] - eef[1], cube[2] - eef[2]);
+            const bool on = md <= on_th;
+            if (on) fsm = 1;
+            if (on && closed) fsm = 2;
+            if (V == IGE_FRANKA_PP) {
+                const float dz = dest[2] - cube[2];
+                const bool lifted = fabsf(dz) >= (float)(((double)p.dest_size + (double)p.cubeA_size) / 2.);
+                const bool align = ige::norm2(dest[0] - cube[0], dest[1] - cube[1]) < (float)((0.05) * 0.5);
+                const bool stackable = fabsf(dz) <= (float)((double)p.cubeA_size * 0.8660 + (double)p.dest_size / 2.);
+                if (on && lifted) fsm = 3;
+                if (align) fsm = 4;
+                if (align && stackable) fsm = 5;
+                if (align && stackable && !closed) fsm = 6;
+            }
         }
+        const int fsm_o = __shfl_xor_sync(0xffffffffu, fsm, 1);
+        int gfsm = 0;
+        if (PAIRED) {  // compute_global_FSM franka_PPMA.py:597-611: eef[1] - eef[0] of my env, d_ecp of env j
+            const float *e0p = a == 0 ? eef : eef_o, *e1p = a == 0 ? eef_o : eef;
+            const bool grip = ige::norm3(e1p[0] - e0p[0], e1p[1] - e0p[1], e1p[2] - e0p[2]) <= 0.18f;
+            const bool cub = ige::norm3(je[0] - jc[0], je[1] - jc[1], je[2] - jc[2]) <= 0.18f;
+            gfsm = (grip || cub) ? -1 : 0;
+        }
+
+        // ---- compute_observations: my row of the tile ----
+        float *o = otile + tid * NO;
+        int n = 0;
+        if (V == IGE_FRANKA_REACH || V == IGE_FRANKA_COLLECT) {
 #pragma unroll
-        for (int a = 0; a < A; ++a) {
-            const size_t row = (size_t)e * A + a;
-            float *o = obs_tile + ((size_t)tid * A + a) * NO;
-            int gfsm = 0;
-            if (PAIRED) {  // compute_global_FSM franka_PPMA.py:597-611
-                const bool grip = ige::norm3(eef[1][0] - eef[0][0], eef[1][1] - eef[0][1], eef[1][2] - eef[0][2]) <= 0.18f;
-                const bool cub = ige::norm3(je[a][0] - jc[a][0], je[a][1] - jc[a][1], je[a][2] - jc[a][2]) <= 0.18f;
-                gfsm = (grip || cub) ? -1 : 0;
+            for (int i = 0; i < 3; ++i) o[n++] = c0[i];
+#pragma unroll
+            for (int i = 0; i < 3; ++i) o[n++] = c1[i];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) o[n++] = eef[3 + i];
+#pragma unroll
+            for (int i = 0; i < 3; ++i) o[n++] = eef[i];
+#pragma unroll
+            for (int i = 0; i < 3; ++i) o[n++] = ncube[i] - eef[i];
+            if (V == IGE_FRANKA_COLLECT) {
+#pragma unroll
+                for (int i = 0; i < 7; ++i) o[n++] = base[i];
             }
-            int n = 0;
-            if (V == IGE_FRANKA_REACH || V == IGE_FRANKA_COLLECT) {
 #pragma unroll
-                for (int c = 0; c < T; ++c) { o[n++] = cube[c][0]; o[n++] = cube[c][1]; o[n++] = cube[c][2]; }
+            for (int i = 0; i < 3; ++i) o[n++] = eef_o[i];
+            if (V == IGE_FRANKA_COLLECT) { o[n++] = (float)fsm; o[n++] = (float)fsm; }
+        } else {
 #pragma unroll
-                for (int i = 0; i < 4; ++i) o[n++] = eef[a][3 + i];
+            for (int i = 0; i < 4; ++i) o[n++] = cube[3 + i];
 #pragma unroll
-                for (int i = 0; i < 3; ++i) o[n++] = eef[a][i];
+            for (int i = 0; i < 4; ++i) o[n++] = cube_o[3 + i];
 #pragma unroll
-                for (int i = 0; i < 3; ++i) o[n++] = ncube[a][i] - eef[a][i];
-                if (V == IGE_FRANKA_COLLECT) {
+            for (int i = 0; i < 3; ++i) o[n++] = cube[i];
 #pragma unroll
-                    for (int i = 0; i < 7; ++i) o[n++] = base[a][i];
-                }
+            for (int i = 0; i < 3; ++i) o[n++] = cube_o[i];
+            float aux[3];
+            if (V == IGE_FRANKA_COMBINE) {
 #pragma unroll
-                for (int sft = 1; sft < A; ++sft) {
-                    const int q = (a + sft) % A;
-                    o[n++] = eef[q][0]; o[n++] = eef[q][1]; o[n++] = eef[q][2];
-                }
-                if (V == IGE_FRANKA_COLLECT) { o[n++] = (float)fsm[a]; o[n++] = (float)fsm[a]; }
+                for (int i = 0; i < 3; ++i) { aux[i] = sb[i]; o[n++] = sb[i]; }
             } else {
 #pragma unroll
-                for (int sft = 0; sft < T; ++sft) { const int q = (a + sft) % T;
+                for (int i = 0; i < 3; ++i) o[n++] = dest[i];
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) o[n++] = cube[q][3 + i]; }
+                for (int i = 0; i < 3; ++i) o[n++] = dest_o[i];
 #pragma unroll
-                for (int sft = 0; sft < T; ++sft) { const int q = (a + sft) % T; o[n++] = cube[q][0]; o[n++] = cube[q][1]; o[n++] = cube[q][2]; }
-                float aux[3];
-                if (V == IGE_FRANKA_COMBINE) {
-                    aux[0] = sb[0]; aux[1] = sb[1]; aux[2] = sb[2];
-                    o[n++] = aux[0]; o[n++] = aux[1]; o[n++] = aux[2];
-                } else {
-#pragma unroll
-                    for (int sft = 0; sft < T; ++sft) {
-                        const int q = (a + sft) % T;
-                        o[n++] = dest[q][0]; o[n++] = dest[q][1]; o[n++] = dest[q][2];
-                    }
-                    aux[0] = dest[a][0]; aux[1] = dest[a][1]; aux[2] = dest[a][2];
-                }
-#pragma unroll
-                for (int i = 0; i < 3; ++i) o[n++] = cube[a][i] - eef[a][i];
-#pragma unroll
-                for (int i = 0; i < 3; ++i) o[n++] = aux[i] - cube[a][i];
-#pragma unroll
-                for (int i = 0; i < 7; ++i) o[n++] = base[a][i];
-#pragma unroll
-                for (int sft = 0; sft < A; ++sft) { const int q = (a + sft) % A; o[n++] = eef[q][0]; o[n++] = eef[q][1]; o[n++] = eef[q][2]; }
-#pragma unroll
-                for (int sft = 0; sft < A; ++sft) { const int q = (a + sft) % A;
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) o[n++] = eef[q][3 + i]; }
-#pragma unroll
-                for (int sft = 0; sft < A; ++sft) o[n++] = pow2_small(fsm[(a + sft) % A]);
-                o[n++] = pow2_small(gfsm);
-                if (V == IGE_FRANKA_COMBINE) o[n++] = (a == A - 1) ? 1.0f : 0.0f;  // agent_idx :526-527
+                for (int i = 0; i < 3; ++i) aux[i] = dest[i];
             }
-            // ---- compute_franka_reward ----
-            float rewards;
-            float c10[NC];
 #pragma unroll
-            for (int i = 0; i < NC; ++i) c10[i] = 0.0f;
-            const float alast = act[a][NA - 1];
-            if (V == IGE_FRANKA_REACH) {  // franka_reach_MA.py:928-960
-                const float d = md[a];
-                const float dist_reward = 1.0f / (0.5f + d * d);
-                const float actions_cost = sum_sq_small(act[a], NA) * 0.01f;
-                rewards = dist_reward - actions_cost;
-                const int distinct = __popc(touched);  // mask.sum(dim=-1), franka_reach_MA.py:944-948
-                const float all_touched = ((float)distinct / (float)A) * 1.0f;
-                const float colliding = (ige::norm3(cf[a][0], cf[a][1], cf[a][2]) >= 0.1f ? 1.0f : 0.0f) * -10.0f;
-                rewards = rewards + (all_touched + colliding);
-            } else {
-                const float m = md[a];
-                const int sx = fsm[a];
-                c10[0] = sx == 0 ? expf(-5.0f * (m * m)) : 0.0f;
-                c10[1] = sx == 1 ? expf(-1.0f * alast) : 0.0f;
-                if (V == IGE_FRANKA_COLLECT) {  // franka_collect_MA.py:1082-1174
-                    const float *hc = ncube[a];
-                    c10[2] = sx == 2 ? (hc[2] - 1.05f) / (float)(0.3 + 0.025) : 0.0f;
-                    const float dy = fabsf(hc[1] - (float)(0.3 + 0.05 * 2.));
-                    c10[3] = sx == 3 ? expf(-5.0f * (dy * dy)) : 0.0f;
-                    const float dz = fabsf(hc[2] - (float)(0.3 / 2. + 1.05));
-                    c10[4] = sx == 4 ? expf(-5.0f * (dz * dz)) : 0.0f;
-                    c10[5] = sx == 5 ? expf(4.0f * alast) : 0.0f;
-                    c10[6] = sx == 6 ? 1.0f * 3.0f : 0.0f;
-                    c10[7] = (float)sx;
-                    rewards = c10[0] + c10[1] + c10[2] + c10[3] + c10[4] + c10[5] + c10[6] + c10[7] + c10[8] + 0.0f;
-                } else if (V == IGE_FRANKA_COMBINE) {  // franka_combine_MA.py:1080-1166
-                    float lift = fabsf(sb[2] - cube[a][2]) / (float)((0.05 + 0.05) * 0.5);
-                    lift = lift < 0.0f ? 0.0f : (lift > 1.0f ? 1.0f : lift);
-                    c10[2] = sx == 2 ? lift : 0.0f;
-                    c10[7] = (float)sx;
-                    rewards = c10[0] + c10[1] + c10[7];
-                } else {  // franka_PPMA.py:1082-1167
-                    const float rx = dest[a][0] - cube[a][0], ry = dest[a][1] - cube[a][1], rz = dest[a][2] - cube[a][2];
-                    float lift = fabsf(rz) / (float)((0.05 + 0.05) * 0.5);
-                    lift = lift < 0.0f ? 0.0f : (lift > 1.0f ? 1.0f : lift);
-                    c10[2] = sx == 2 ? lift : 0.0f;
-                    const float dt = ige::norm3(rx + 0.0f, ry + 0.0f, rz + 0.05f);
-                    c10[3] = sx == 3 ? expf(-3.0f * dt) : 0.0f;
-                    c10[4] = sx == 4 ? expf(-10.0f * dt) : 0.0f;
-                    c10[5] = sx == 5 ? expf(5.0f * alast) : 0.0f;
-                    c10[6] = sx == 6 ? tanhf(m) : 0.0f;
-                    c10[7] = (float)sx;
-                    c10[8] = (float)gfsm * 0.5f;
-                    rewards = c10[0] + c10[1] + c10[2] + c10[3] + c10[4] + c10[5] + c10[6] + c10[7] + c10[8] + c10[9];
-                }
+            for (int i = 0; i < 3; ++i) o[n++] = cube[i] - eef[i];
+#pragma unroll
+            for (int i = 0; i < 3; ++i) o[n++] = aux[i] - cube[i];
+#pragma unroll
+            for (int i = 0; i < 7; ++i) o[n++] = base[i];
+#pragma unroll
+            for (int i = 0; i < 3; ++i) o[n++] = eef[i];
+#pragma unroll
+            for (int i = 0; i < 3; ++i) o[n++] = eef_o[i];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) o[n++] = eef[3 + i];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) o[n++] = eef_o[3 + i];
+            o[n++] = pow2_small(fsm);
+            o[n++] = pow2_small(fsm_o);
+            o[n++] = pow2_small(gfsm);
+            if (V == IGE_FRANKA_COMBINE) o[n++] = (a == A - 1) ? 1.0f : 0.0f;  // agent_idx :526-527
+        }
+
+        // ---- compute_franka_reward ----
+        float rewards;
+        float c10[NC];
+#pragma unroll
+        for (int i = 0; i < NC; ++i) c10[i] = 0.0f;
+        const float alast = act[NA - 1];
+        if (V == IGE_FRANKA_REACH) {  // franka_reach_MA.py:928-960
+            const float dist_reward = 1.0f / (0.5f + md * md);
+            const float actions_cost = sum_sq_small(act, NA) * 0.01f;
+            rewards = dist_reward - actions_cost;
+            const float all_touched = ((float)__popc(touched) / (float)A) * 1.0f;   // mask.sum(dim=-1) :944-948
+            const float colliding = (ige::norm3(cf[0], cf[1], cf[2]) >= 0.1f ? 1.0f : 0.0f) * -10.0f;
+            rewards = rewards + (all_touched + colliding);
+        } else {
+            c10[0] = fsm == 0 ? expf(-5.0f * (md * md)) : 0.0f;
+            c10[1] = fsm == 1 ? expf(-1.0f * alast) : 0.0f;
+            if (V == IGE_FRANKA_COLLECT) {  // franka_collect_MA.py:1082-1174
+                c10[2] = fsm == 2 ? (ncube[2] - 1.05f) / (float)(0.3 + 0.025) : 0.0f;
+                const float dy = fabsf(ncube[1] - (float)(0.3 + 0.05 * 2.));
+                c10[3] = fsm == 3 ? expf(-5.0f * (dy * dy)) : 0.0f;
+                const float dz = fabsf(ncube[2] - (float)(0.3 / 2. + 1.05));
+                c10[4] = fsm == 4 ? expf(-5.0f * (dz * dz)) : 0.0f;
+                c10[5] = fsm == 5 ? expf(4.0f * alast) : 0.0f;
+                c10[6] = fsm == 6 ? 1.0f * 3.0f : 0.0f;
+                c10[7] = (float)fsm;
+                rewards = c10[0] + c10[1] + c10[2] + c10[3] + c10[4] + c10[5] + c10[6] + c10[7] + c10[8] + 0.0f;
+            } else if (V == IGE_FRANKA_COMBINE) {  // franka_combine_MA.py:1080-1166
+                float lift = fabsf(sb[2] - cube[2]) / (float)((0.05 + 0.05) * 0.5);
+                lift = lift < 0.0f ? 0.0f : (lift > 1.0f ? 1.0f : lift);
+                c10[2] = fsm == 2 ? lift : 0.0f;
+                c10[7] = (float)fsm;
+                rewards = c10[0] + c10[1] + c10[7];
+            } else {  // franka_PPMA.py:1082-1167
+                const float rx = dest[0] - cube[0], ry = dest[1] - cube[1], rz = dest[2] - cube[2];
+                float lift = fabsf(rz) / (float)((0.05 + 0.05) * 0.5);
+                lift = lift < 0.0f ? 0.0f : (lift > 1.0f ? 1.0f : lift);
+                c10[2] = fsm == 2 ? lift : 0.0f;
+                const float dt = ige::norm3(rx + 0.0f, ry + 0.0f, rz + 0.05f);
+                c10[3] = fsm == 3 ? expf(-3.0f * dt) : 0.0f;
+                c10[4] = fsm == 4 ? expf(-10.0f * dt) : 0.0f;
+                c10[5] = fsm == 5 ? expf(5.0f * alast) : 0.0f;
+                c10[6] = fsm == 6 ? tanhf(md) : 0.0f;
+                c10[7] = (float)fsm;
+                c10[8] = (float)gfsm * 0.5f;
+                rewards = c10[0] + c10[1] + c10[2] + c10[3] + c10[4] + c10[5] + c10[6] + c10[7] + c10[8] + c10[9];
             }
-            rewards = rewards < 0.0f ? 0.0f : rewards;  // torch.clip(rewards, 0., None)
+        }
+        rewards = rewards < 0.0f ? 0.0f : rewards;  // torch.clip(rewards, 0., None)
+        const bool late = (float)prog >= p.max_episode_length - 1.0f;
+        if (late) rst = 1;
+        const bool timeout = late && rst != 0;  // vec_task.py:396
+        if (valid) {
 #pragma unroll
             for (int i = 0; i < NC; ++i) comp[i] += c10[i];
-            long long reset = a == 0 ? rst.x : rst.y;
-            const long long progress = a == 0 ? prog.x : prog.y;
-            const bool late = (float)progress >= p.max_episode_length - 1.0f;
-            if (late) reset = 1;
-            if (a == 0) rst.x = reset; else rst.y = reset;
-            b.rew_buf[row] = rewards;
-            const bool timeout = late && reset != 0;  // vec_task.py:396
-            if (b.timeout_buf) b.timeout_buf[row] = timeout ? 1 : 0;
-            st_rew += rewards; st_done += reset != 0 ? 1.f : 0.f; st_to += timeout ? 1.f : 0.f;
-            st_len += reset != 0 ? (float)progress : 0.f;
+            st_n += 1.f; st_rew += rewards; st_done += rst != 0 ? 1.f : 0.f; st_to += timeout ? 1.f : 0.f;
+            st_len += rst != 0 ? (float)prog : 0.f;
         }
-        *reinterpret_cast<longlong2 *>(b.reset_buf + (size_t)e * A) = rst;
+
+        // ---- outputs.  The ENTRY flags of other CTAs' partner envs are only overwritten once every CTA has
+        //      snapshot them, i.e. once the launch epoch has advanced (see the header); by now it has ----
+        const int count = ne * A * NO;
+        const bool bulk = use_tma && (count % 4 == 0);
+        if (bulk) ige::fence_proxy_async();
+        if (!flags_open && tid == 0) {
+            const volatile uint64_t *sc = reinterpret_cast<const volatile uint64_t *>(b.list.scratch);
+            while (sc[0] < tag) { }
+        }
+        if (t >= 1 && tid == 0) ige::bulk_wait_read_all();  // tile t - 1 has left obs_tile[(t + 1) & 1]: free for tile t + 1
+        __syncthreads();
+        flags_open = true;
+        if (valid) {
+            b.rew_buf[row] = rewards;
+            b.reset_buf[row] = rst;
+            b.progress_buf[row] = prog;
+            if (b.timeout_buf) b.timeout_buf[row] = timeout ? 1 : 0;
+        }
+        float *dst = b.obs_buf + (size_t)e0 * A * NO;
+        if (bulk) {
+            if (tid == 0) { ige::bulk_s2g(dst, otile, (uint32_t)count * 4); ige::bulk_commit(); }
+        } else {
+            for (int i = tid; i < count; i += RT_NT) dst[i] = otile[i];
+        }
+        if (b.obs_clamped) {  // vec_task.py:404
+            float *dc = b.obs_clamped + (size_t)e0 * A * NO;
+            for (int i = tid; i < count; i += RT_NT) dc[i] = clampf(otile[i], p.clip_obs);
+        }
+        if (emit && warp == 0) {   // this tile's ids: lane l writes env e0 + l at its rank within the ballot
+            const uint32_t m = s_own[t];
+            if ((m >> lane) & 1u) b.list.ids[list_off + __popc(m & ((1u << lane) - 1u))] = e0 + lane;
+            list_off += __popc(m);
+        }
     }
-    franka_tile_out_and_reduce(p, b, obs_tile, &s_last, comp, st_rew, st_done, st_to, st_len, valid, phase, use_tma, A, NO);
+
+    // ---- reward-component sums (the .mean()s of extras) + statistics ----
+#pragma unroll
+    for (int i = 0; i < NC; ++i) comp[i] = ige::warp_sum(comp[i]);
+    if (lane < NC) {
+        float mine = 0.f;
+#pragma unroll
+        for (int i = 0; i < NC; ++i) if (lane == i) mine = comp[i];
+        if (MEANS) atomicAdd(b.reduce_scratch + lane, mine);
+        if (b.stats && MEANS) atomicAdd(b.stats + (blockIdx.x % IGE_STATS_ROWS) * IGE_STATS_STRIDE + IGE_STAT_TASK0 + lane, mine);
+    }
+    if (b.stats) {
+        const float v[5] = {st_n, st_rew, st_done, st_to, st_len};
+        const int slot[5] = {IGE_STAT_STEPS, IGE_STAT_REWARD, IGE_STAT_DONE, IGE_STAT_TIMEOUT, IGE_STAT_DONE_LENGTH};
+        ige::warp_stats_add<5>(b.stats, v, slot);
+    }
+    if (MEANS) {   // the CTA that retires last turns the component sums into the logged means
+        if (lane < NC) __threadfence();
+        __syncthreads();
+        if (tid == 0) {
+            unsigned *c = reinterpret_cast<unsigned *>(b.reduce_scratch + NC);
+            s_last = atomicAdd(c, 1u) == gridDim.x - 1;
+        }
+        __syncthreads();
+        if (s_last) {
+            __threadfence();
+            if (tid < NC) {
+                const float sum = __ldcg(b.reduce_scratch + tid);
+                if (b.reward_components) b.reward_components[tid] = sum / (float)((long long)N * A);
+                b.reduce_scratch[tid] = 0.0f;
+            }
+            if (tid == 0) b.reduce_scratch[NC] = 0.0f;
+        }
+    } else if (b.reward_components && blockIdx.x == 0 && tid < NC) {
+        b.reward_components[tid] = 0.0f;
+    }
+    if (tid == 0) ige::bulk_wait_read_all();  // the tiles must outlive the bulk stores' reads
 }
 }  // namespace
 
@@ -792,28 +986,48 @@ extern "C" int ige_franka_ma_post_physics(const IgeFrankaMAParams *p, const IgeF
     if (p->rand.mode == IGE_RAND_INJECTED && !p->rand.env_rank) return ige_fail(IGE_ENULL, "rand.env_rank is NULL (INJECTED mode)");
     if (p->rand.mode != IGE_RAND_INJECTED && p->rand.mode != IGE_RAND_PHILOX) return ige_fail(IGE_EPARAM, "rand.mode invalid");
     if (p->num_envs == 0) return IGE_OK;
+    cudaStream_t s = (cudaStream_t)stream;
+    static const int kPairObs[4] = {19, 28, 48, 50}, kPairActions[4] = {6, 7, 7, 7};
+    if (ige_fast_paths() && p->num_agents == 2 && p->num_targets == 2 && p->num_obs == kPairObs[p->variant] &&
+        p->num_actions == kPairActions[p->variant] && (!pair_only || b->list.scratch != nullptr)) {
+        // rows kernel: ONE launch for every variant (Combine / PP need the reset list's launch epoch, see its header)
+        typedef void (*Rows)(const IgeFrankaMAParams, const IgeFrankaMABuffers, const int, const int, const int);
+        static const Rows rows[4] = {franka_ma_rows_kernel<IGE_FRANKA_REACH>, franka_ma_rows_kernel<IGE_FRANKA_COLLECT>,
+                                     franka_ma_rows_kernel<IGE_FRANKA_COMBINE>, franka_ma_rows_kernel<IGE_FRANKA_PP>};
+        int dev = 0;
+        cudaGetDevice(&dev);
+        static int max_ctas[4][IGE_MAX_DEVICES];   // resident CTAs per variant and device (0 = not queried yet)
+        if (dev < 0 || dev >= IGE_MAX_DEVICES) return ige_fail(IGE_EPARAM, "device ordinal %d not supported", dev);
+        if (max_ctas[p->variant][dev] == 0) {
+            int sms = 0, per_sm = 0;
+            cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+            cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, rows[p->variant], RT_NT, 0);
+            if (e != cudaSuccess || per_sm < 1 || sms < 1)
+                return ige_fail(e != cudaSuccess ? (int)e : IGE_EPARAM, "ige_franka_ma_post_physics: occupancy query failed");
+            int m = sms * per_sm;
+            if (m > ige::kListMaxCtas) m = ige::kListMaxCtas;
+            max_ctas[p->variant][dev] = m;
+        }
+        const int tiles = (p->num_envs + RT_E - 1) / RT_E;
+        const int per_cta = (tiles + max_ctas[p->variant][dev] - 1) / max_ctas[p->variant][dev];
+        if (per_cta <= RT_MAX_TILES) {
+            const int grid = (tiles + per_cta - 1) / per_cta;   // <= resident capacity: all CTAs co-resident
+            rows[p->variant]<<<grid, RT_NT, 0, s>>>(*p, *b, tiles, per_cta, ige_use_tma());
+            return ige_check_launch("ige_franka_ma_post_physics");
+        }
+    }
     const size_t smem = (size_t)TE * p->num_agents * p->num_obs * sizeof(float);
     if (smem > 48 * 1024) {
         cudaError_t e = cudaFuncSetAttribute(franka_ma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return ige_fail((int)e, "cudaFuncSetAttribute(%zu): %s", smem, cudaGetErrorString(e));
     }
     const int grid = (p->num_envs + TE - 1) / TE;
-    cudaStream_t s = (cudaStream_t)stream;
-    typedef void (*Kernel)(const IgeFrankaMAParams, const IgeFrankaMABuffers, const int, const int);
-    Kernel k = franka_ma_kernel;
-    static const int kPairObs[4] = {19, 28, 48, 50}, kPairActions[4] = {6, 7, 7, 7};
-    if (ige_fast_paths() && p->num_agents == 2 && p->num_targets == 2 && p->num_obs == kPairObs[p->variant] &&
-        p->num_actions == kPairActions[p->variant]) {
-        static const Kernel pair[4] = {franka_ma_pair_kernel<IGE_FRANKA_REACH>, franka_ma_pair_kernel<IGE_FRANKA_COLLECT>,
-                                       franka_ma_pair_kernel<IGE_FRANKA_COMBINE>, franka_ma_pair_kernel<IGE_FRANKA_PP>};
-        k = pair[p->variant];
-    }
     if (pair_only) {
-        k<<<grid, NT, 0, s>>>(*p, *b, PH_RESET, ige_use_tma());
+        franka_ma_kernel<<<grid, NT, 0, s>>>(*p, *b, PH_RESET, ige_use_tma());
         if (int rc = ige_check_launch("ige_franka_ma_post_physics(reset)")) return rc;
-        k<<<grid, NT, smem, s>>>(*p, *b, PH_COMPUTE, ige_use_tma());
+        franka_ma_kernel<<<grid, NT, smem, s>>>(*p, *b, PH_COMPUTE, ige_use_tma());
     } else {
-        k<<<grid, NT, smem, s>>>(*p, *b, PH_FUSED, ige_use_tma());
+        franka_ma_kernel<<<grid, NT, smem, s>>>(*p, *b, PH_FUSED, ige_use_tma());
     }
     return ige_check_launch("ige_franka_ma_post_physics");
 }

@@ -18,6 +18,8 @@ int ige_check_launch(const char *what);
 extern "C" int ige_use_tma();  // 1 unless IGE_NO_TMA=1 / ige_set_use_tma(0)
 extern "C" int ige_fast_paths();  // 1 unless IGE_GENERIC=1 / ige_set_fast_paths(0)
 
+#define IGE_MAX_DEVICES 64   // per-device launch caches (occupancy, function attributes) are indexed by ordinal
+
 #define IGE_REQUIRE_PTR(ptr)                                                       \
     do {                                                                           \
         if ((ptr) == nullptr) return ige_fail(IGE_ENULL, "%s is NULL", #ptr);      \
@@ -285,6 +287,67 @@ constexpr int kListMaskBase = kListCounterWord + 4;       // 16-B aligned
 __host__ __device__ inline int reset_list_scratch_words(int num_envs) {
     return kListMaskBase + (((num_envs + 31) / 32 + 3) / 4) * 4;
 }
+// ---- persistent kernels: CTA-level look-back ---------------------------------------------------------------
+// CTA c owns a contiguous, ascending range of envs, so its reset ids form one contiguous run of the output
+// list that starts at the sum of the counts of the CTAs with a lower block index.  list_cta_prefix() is called
+// by ONE full warp per CTA, EARLY (right after the warp has counted its CTA's flags -- typically while the
+// CTA's first tile is still in flight), and returns that sum:
+//   1. publish {launch epoch + 1 : count} in this CTA's slot;
+//   2. take the "consumed the epoch and the Philox step word" ticket: every thread of the CTA must have READ the
+//      step word before the CTA barrier that precedes this call, so the CTA that draws the last ticket may open
+//      the next launch epoch and advance the step word at once -- nobody reads either word again in this launch
+//      (slot tags are compared with the register copy of the epoch);
+//   3. sum the predecessors' slots (batched polls, only unpublished slots are re-polled).
+// The caller's grid must not exceed the number of co-resident CTAs (every launcher caps it with the occupancy
+// API), so all predecessors are running and publish within their first microsecond -- the wait cannot deadlock,
+// whatever order the hardware dispatches CTAs in.  grid <= kListMaxCtas.
+__device__ __forceinline__ int list_cta_prefix(const IgeResetList &L, int cnt, uint64_t *step_word) {
+    volatile uint64_t *sc = reinterpret_cast<volatile uint64_t *>(L.scratch);
+    const int lane = threadIdx.x & 31;
+    const uint64_t tag = sc[0] + 1;  // launch epoch + 1 (the scratch starts zeroed)
+    unsigned ticket = 0;
+    if (lane == 0) {
+        sc[2 + blockIdx.x] = (tag << 32) | (uint32_t)cnt;
+        ticket = atomicInc(L.scratch + 2, gridDim.x - 1);
+    }
+    int sum = 0;
+    constexpr int LB = 8;
+    for (int c0 = lane; c0 < (int)blockIdx.x; c0 += 32 * LB) {
+        uint64_t v[LB];
+        bool ok;
+        do {
+            ok = true;
+#pragma unroll
+            for (int k = 0; k < LB; ++k) {
+                const int c = c0 + 32 * k;
+                v[k] = c < (int)blockIdx.x ? sc[2 + c] : (tag << 32);
+                ok &= (v[k] >> 32) == tag;
+            }
+        } while (!ok);
+#pragma unroll
+        for (int k = 0; k < LB; ++k) sum += (int)(uint32_t)v[k];
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    if (lane == 0) {
+        if (blockIdx.x == gridDim.x - 1) *L.count = sum + cnt;
+        if (ticket == gridDim.x - 1) {
+            sc[0] = sc[0] + 1;
+            if (step_word) *step_word += 1ull;
+        }
+    }
+    return sum;
+}
+// Ascending ids of one 32-env ballot `mask` whose first env is `base`, written from list position `off` on.
+// One lane per call (the caller distributes tiles over lanes); returns the next free position.
+__device__ __forceinline__ int list_emit_mask(const IgeResetList &L, int off, uint32_t mask, int base) {
+    while (mask) {
+        L.ids[off++] = base + __ffs(mask) - 1;
+        mask &= mask - 1;
+    }
+    return off;
+}
+
 // One thread publishes the ballot mask of 32-env tile `tile` (bit i = env tile*32+i was reset).
 // No fence here: finish_reset_list() fences once per publishing thread.
 __device__ __forceinline__ void publish_tile_mask(const IgeResetList &L, int tile, uint32_t mask) {

@@ -519,17 +519,22 @@ locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p,
     const int my_tiles = min(tiles_per_cta, num_tiles - first);
     const bool clamp_copy = b.obs_clamped != nullptr && p.clip_obs < INFINITY;
     const bool second_obs_copy = b.obs_clamped != nullptr && !clamp_copy;
-    const uint64_t step = ige::load_step(p.rand);
     auto tile_e0 = [&](int it) { return (first + it) * TE; };
     auto tile_ne = [&](int it) { return min(TE, p.num_envs - tile_e0(it)); };
 
     CLK(kstart);
+    // Philox step word: read by ONE thread and handed over through shared memory, so the load has completed
+    // (not merely been issued) when the CTA passes the barrier below -- the retirement ticket that lets the
+    // last CTA advance the word is taken right after it.
+    __shared__ uint64_t s_step;
     if (tid == 0) {
+        s_step = ige::load_step(p.rand);
 #pragma unroll
         for (int s = 0; s < IN_STAGES; ++s) ige::mbar_init(&full[s], 1);
         ige::fence_mbar_init();
     }
     __syncthreads();
+    const uint64_t step = s_step;
     // prologue: the first IN_STAGES tiles
     if (lane == 0 && role != REWARD)
         for (int k = 0; k < IN_STAGES && k < my_tiles; ++k)
@@ -543,14 +548,13 @@ locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p,
             n_reset = b.reset_buf[e]; n_progress = b.progress_buf[e];
             if (b.randomize_buf) n_rand = b.randomize_buf[e];
         }
-        // ---- reset index list, part 1 (while the role warps work on the first tile): count my resets
-        //      and publish the count early, so nobody has to wait for it later ----
+        // ---- reset index list (while the role warps work on the first tile): count my resets, publish the count
+        //      and sum the predecessor CTAs' counts -- this warp is idle until the first tile has been produced, so
+        //      the look-back costs nothing on the critical path (ige::list_cta_prefix) ----
         const bool emit = b.list.scratch != nullptr;
-        volatile uint64_t *sc = reinterpret_cast<volatile uint64_t *>(b.list.scratch);
-        uint64_t tag = 0;
-        int cnt = 0;
+        int sum = 0;
         if (emit) {
-            tag = sc[0] + 1;  // launch epoch + 1 (the scratch starts zeroed)
+            int cnt = 0;
             constexpr int PB = 8;            // flag loads in flight
             for (int it0 = 0; it0 < my_tiles; it0 += PB) {
                 long long f[PB];
@@ -562,7 +566,7 @@ locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p,
 #pragma unroll
                 for (int k = 0; k < PB; ++k) cnt += __popc(__ballot_sync(0xffffffffu, f[k] != 0));
             }
-            if (lane == 0) sc[2 + blockIdx.x] = (tag << 32) | (uint32_t)cnt;
+            sum = ige::list_cta_prefix(b.list, cnt, p.rand.step);
         }
         StatAcc st;
         uint32_t reg_mask = 0u;  // lane t: reset ballot of my tile t (t < 32)
@@ -605,36 +609,8 @@ locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p,
         }
         CLK(r3);
         if (b.stats) flush_stats(b.stats, st);
-        // ---- reset index list, part 2 (last thing this warp does): offset = sum of the predecessor CTAs'
-        //      counts, published long ago; then the ascending ids of my tiles ----
+        // ---- reset index list, part 3: the ascending ids of my tiles (stores only; nothing is waited for) ----
         if (emit) {
-            // Predecessors have lower block ids, so they were dispatched before this CTA: the wait cannot
-            // deadlock.  Loads go out in batches (no dependent chain); only unpublished slots are re-polled.
-            // Retirement ticket, issued now so that its round trip overlaps the polling below.  Every role
-            // warp of this CTA has passed its last barrier, i.e. has long consumed the epoch / Philox step.
-            unsigned ticket = 0;
-            if (lane == 0) ticket = atomicInc(b.list.scratch + 2, gridDim.x - 1);
-            int sum = 0;
-            constexpr int LB = 8;
-            for (int c0 = lane; c0 < (int)blockIdx.x; c0 += 32 * LB) {
-                uint64_t v[LB];
-                bool ok;
-                do {
-                    ok = true;
-#pragma unroll
-                    for (int k = 0; k < LB; ++k) {
-                        const int c = c0 + 32 * k;
-                        v[k] = c < (int)blockIdx.x ? sc[2 + c] : (tag << 32);
-                        ok &= (v[k] >> 32) == tag;
-                    }
-                } while (!ok);
-#pragma unroll
-                for (int k = 0; k < LB; ++k) sum += (int)(uint32_t)v[k];
-            }
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-            if (blockIdx.x == gridDim.x - 1 && lane == 0) *b.list.count = sum + cnt;
-            __syncwarp();
             // lane l expands tiles l, l + 32, ...: exclusive scan of the tile counts, then the set bits
             for (int t0 = 0; t0 < my_tiles; t0 += 32) {
                 const int t = t0 + lane;
@@ -646,18 +622,8 @@ locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p,
                     const int u = __shfl_up_sync(0xffffffffu, incl, o);
                     if (lane >= o) incl += u;
                 }
-                int off = sum + incl - c;
-                const int base = tile_e0(t);
-                while (m) {
-                    b.list.ids[off++] = base + __ffs(m) - 1;
-                    m &= m - 1;
-                }
+                ige::list_emit_mask(b.list, sum + incl - c, m, tile_e0(t));
                 sum += __shfl_sync(0xffffffffu, incl, 31);
-            }
-            // the CTA that retires last opens the next launch epoch and advances the Philox step word
-            if (lane == 0 && ticket == gridDim.x - 1) {
-                sc[0] = sc[0] + 1;
-                if (p.rand.step) *p.rand.step += 1ull;
             }
         }
         CLK(r4);

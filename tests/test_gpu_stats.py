@@ -43,6 +43,7 @@ def _horizon_graph(envs, reducer, parity, mode="global"):
     for e in envs:
         reducer.attach(e, parity)
         e.sim.record = False
+        e._constants()        # the per-task constants are validated with torch ops once: not inside a capture
     s = torch.cuda.Stream()
     s.wait_stream(torch.cuda.current_stream())
     g = torch.cuda.CUDAGraph()
@@ -150,6 +151,10 @@ def _nccl_worker(rank, world, port, q):
         gb.replay()
     torch.cuda.synchronize()
     q.put((rank, local_a, got, red.collectives))
+    del ga, gb                             # ncclCommDestroy waits for the graphs that captured its collectives
+    import gc
+    gc.collect()
+    torch.cuda.synchronize()
     torch.distributed.barrier()
     torch.distributed.destroy_process_group()
 
@@ -163,10 +168,15 @@ def test_nccl_allreduce_inside_horizon_graph():
     procs = [ctx.Process(target=_nccl_worker, args=(r, world, port, q)) for r in range(world)]
     for p in procs:
         p.start()
-    res = sorted((q.get(timeout=300) for _ in range(world)), key=lambda t: t[0])
-    for p in procs:
-        p.join(timeout=120)
-        assert p.exitcode == 0
+    try:
+        res = sorted((q.get(timeout=240) for _ in range(world)), key=lambda t: t[0])
+        for p in procs:
+            p.join(timeout=60)
+            assert p.exitcode == 0
+    finally:
+        for p in procs:
+            if p.is_alive():
+                p.kill()
     total = sum(r[1] for r in res)
     assert total[abi.STAT_STEPS] == sum(1024 * (r + 1) * 2 for r in range(world))
     for rank, _, got, ncoll in res:

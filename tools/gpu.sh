@@ -18,15 +18,15 @@ for act in "$@"; do
   IFS=: read -r a b c d <<< "$act"
   case "$a" in
     tests)
-      if [ -n "$b" ]; then python -m pytest tests -m gpu -x -q -k "$b" > gpurun_out/pytest_gpu_k.log 2>&1; echo "pytest -k '$b' rc=$?"; tail -5 gpurun_out/pytest_gpu_k.log
-      else python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -5 gpurun_out/pytest_gpu.log; fi ;;
-    smoke) python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?"; tail -3 gpurun_out/smoke.log ;;
-    bench) python bench.py > gpurun_out/${R}_bench_default.json 2> gpurun_out/bench_default.err; echo "bench rc=$?"; tail -2 gpurun_out/bench_default.err; cut -c1-1500 gpurun_out/${R}_bench_default.json ;;
-    driver) python bench.py --gpus 1 --steps 20 --warmup 5 > gpurun_out/${R}_bench_driver_n1.json 2> gpurun_out/bench_driver.err; echo "driver-bench rc=$?"; tail -2 gpurun_out/bench_driver.err; cut -c1-900 gpurun_out/${R}_bench_driver_n1.json ;;
-    ref) python bench.py --impl reference --steps 20 --warmup 5 > gpurun_out/${R}_bench_reference.json 2> gpurun_out/bench_reference.err; echo "ref rc=$?"; tail -2 gpurun_out/bench_reference.err; cut -c1-1200 gpurun_out/${R}_bench_reference.json ;;
+      if [ -n "$b" ]; then timeout 600 python -m pytest tests -m gpu -x -q -k "$b" > gpurun_out/pytest_gpu_k.log 2>&1; echo "pytest -k '$b' rc=$?"; tail -5 gpurun_out/pytest_gpu_k.log
+      else timeout 1500 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -5 gpurun_out/pytest_gpu.log; fi ;;
+    smoke) timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?"; tail -3 gpurun_out/smoke.log ;;
+    bench) timeout 600 python bench.py > gpurun_out/${R}_bench_default.json 2> gpurun_out/bench_default.err; echo "bench rc=$?"; tail -2 gpurun_out/bench_default.err; cut -c1-1500 gpurun_out/${R}_bench_default.json ;;
+    driver) timeout 300 python bench.py --gpus 1 --steps 20 --warmup 5 > gpurun_out/${R}_bench_driver_n1.json 2> gpurun_out/bench_driver.err; echo "driver-bench rc=$?"; tail -2 gpurun_out/bench_driver.err; cut -c1-900 gpurun_out/${R}_bench_driver_n1.json ;;
+    ref) timeout 300 python bench.py --impl reference --steps 20 --warmup 5 > gpurun_out/${R}_bench_reference.json 2> gpurun_out/bench_reference.err; echo "ref rc=$?"; tail -2 gpurun_out/bench_reference.err; cut -c1-1200 gpurun_out/${R}_bench_reference.json ;;
     scale)
       for steps in 20 2048; do
-        python -m torch.distributed.run --nnodes=1 --nproc-per-node $b --master-addr 127.0.0.1 --master-port 29533 \
+        timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $b --master-addr 127.0.0.1 --master-port 29533 \
           bench.py --gpus $b --steps $steps --warmup 5 --no-sweep > gpurun_out/${R}_bench_n${b}_s${steps}.json 2> gpurun_out/bench_n${b}_s${steps}.err
         echo "scale N=$b steps=$steps rc=$?"; tail -3 gpurun_out/bench_n${b}_s${steps}.err | cut -c1-300; cut -c1-700 gpurun_out/${R}_bench_n${b}_s${steps}.json
       done ;;
@@ -39,12 +39,25 @@ for act in "$@"; do
       timeout 400 ncu --set full --clock-control none --import-source on -s 2 -c 1 -f -o gpurun_out/${R}_prof_$d \
         python tools/prof.py --task $b --num-envs $c --steps 4 --replicas 4 --hot > gpurun_out/ncu_$d.log 2>&1
       echo "ncu $d rc=$?"; python tools/ncu_summary.py gpurun_out/${R}_prof_$d.ncu-rep > gpurun_out/${R}_ncu_full_$d.txt 2>&1; cat gpurun_out/${R}_ncu_full_$d.txt ;;
-    sanitize)
-      SEL="test_cuda_matches_reference_golden or test_reset_extremes or test_stats or test_reducer or rollout_golden or anymal_golden"
-      for tool in memcheck racecheck; do
-        timeout 1500 compute-sanitizer --tool $tool --error-exitcode 9 python -m pytest tests -m gpu -x -q -k "$SEL" > gpurun_out/${R}_sanitizer_$tool.log 2>&1
-        echo "compute-sanitizer $tool rc=$?"; tail -6 gpurun_out/${R}_sanitizer_$tool.log
-      done ;;
+    sanitize)   # sanitize:<memcheck|racecheck>  -- ONE tool per gpurun call (B200_PROFILING.md)
+      SEL="test_cuda_matches_reference_golden or test_reset_extremes or test_stats_snapshot or test_reducer_as_graph or rollout_golden or anymal_golden"
+      timeout 1500 compute-sanitizer --tool $b --error-exitcode 9 python -m pytest tests -m gpu -x -q -k "$SEL" > gpurun_out/${R}_sanitizer_$b.log 2>&1
+      echo "compute-sanitizer $b rc=$?"; tail -8 gpurun_out/${R}_sanitizer_$b.log ;;
+    roleclk)    # roleclk:<Task>:<N>  -- debug build with per-role cycle counters, then the normal build again
+      python isaacgymenvs-ma_b200/build.py -DIGE_ROLE_CLOCKS > gpurun_out/build_clk.log 2>&1
+      timeout 300 python tools/role_clocks.py --task $b --num-envs $c > gpurun_out/${R}_role_clocks_${b}_$c.txt 2>&1; cat gpurun_out/${R}_role_clocks_${b}_$c.txt
+      python isaacgymenvs-ma_b200/build.py > gpurun_out/build.log 2>&1 ;;
+    kern)       # kern:<Task>:<N>  -- kernel-only timing of one task (no e2e / sweep / cpu legs)
+      timeout 300 python bench.py --task $b --num-envs $c --steps 2048 --warmup 64 --no-e2e --no-sweep --no-cpu > gpurun_out/kern_${b}_$c.json 2> gpurun_out/kern_${b}_$c.err
+      echo "kern $b $c rc=$?"; python - <<PY
+import json
+try:
+    d = json.load(open("gpurun_out/kern_${b}_$c.json")); r = d["roofline"]
+    print(f"  ${b} N=$c: step {d['ms_per_step']*1e3:.2f} us  kernel {r['kernel_us']:.2f} us  frac {r['frac']:.3f}")
+except Exception as e:
+    print("  failed:", e); print(open("gpurun_out/kern_${b}_$c.err").read()[-800:])
+PY
+      ;;
     floors) python tools/floors.py > gpurun_out/${R}_floors.txt 2>&1; cat gpurun_out/${R}_floors.txt ;;
     *) echo "unknown action $act" ;;
   esac
