@@ -7,3 +7,4 @@ from .factory import make  # noqa: E402,F401
 from . import distributed  # noqa: E402,F401
 from . import host_pipeline  # noqa: E402,F401
 from . import rollout  # noqa: E402,F401
+from . import integration  # noqa: E402,F401

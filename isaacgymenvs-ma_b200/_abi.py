@@ -193,5 +193,6 @@ def fill_array(carr, values):
 
 
 def reset_list_scratch_words(num_envs):
-    """== ige_reset_list_scratch_words(): look-back slots + retirement counter + one mask word per 32 envs."""
-    return 2 * (2 + 2040) + 4 + (((num_envs + 31) // 32 + 3) // 4) * 4
+    """Words of IgeResetList.scratch for `num_envs` envs: asks the library (ige_reset_list_scratch_words)."""
+    from . import _lib
+    return int(_lib.lib().ige_reset_list_scratch_words(int(num_envs)))

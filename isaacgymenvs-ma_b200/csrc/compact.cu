@@ -109,7 +109,10 @@ __global__ void __launch_bounds__(kThreads) compact_resets_kernel(IgeCompactArgs
 }  // namespace
 
 // scratch words needed for `num_rows / group` envs
-extern "C" int ige_compact_scratch_words(int32_t num_envs) { return 2 + (num_envs + kChunk - 1) / kChunk; }
+extern "C" int ige_compact_scratch_words(int32_t num_envs) {
+    const int chunks = num_envs > 0 ? (num_envs + kChunk - 1) / kChunk : 1;   // an empty env set still launches one chunk
+    return 2 + chunks;
+}
 
 extern "C" int ige_compact_resets(const IgeCompactArgs *a, void *stream) {
     if (!a) return ige_fail(IGE_ENULL, "args is NULL");

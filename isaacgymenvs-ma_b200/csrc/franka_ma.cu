@@ -20,6 +20,10 @@
 // own launch first (grid-wide ordering by the stream); Reach / Collect are a single launch.
 #include "ige_common.cuh"
 
+#ifndef IGE_STAGE_ARGS
+#define IGE_STAGE_ARGS 0
+#endif
+
 namespace {
 
 constexpr int TE = 64;   // envs per CTA (two 32-env list tiles)
@@ -461,7 +465,7 @@ __global__ void __launch_bounds__(NT) franka_ma_kernel(const __grid_constant__ I
 // step | reset rank), so it recomputes env j's when env j resets and reads memory when it does not.  "Does env j
 // reset" is taken from env j's ENTRY flags, which every CTA snapshots (a ballot per tile in shared memory) in
 // the prologue where it also counts its own flags for the reset list; the flags are only overwritten after the
-// launch epoch has advanced, i.e. after every CTA has finished that prologue (ige::list_cta_prefix: the last
+// launch epoch has advanced, i.e. after every CTA has finished that prologue (ige::list_cta_publish: the last
 // CTA to take its ticket advances the epoch; all CTAs are co-resident).
 constexpr int RT_E = 32;                // envs per tile
 constexpr int RT_NT = 2 * RT_E;         // threads per CTA = rows per tile
@@ -483,10 +487,28 @@ __device__ __forceinline__ void ma_uniform4(const IgeMAResetRand &r, uint64_t st
 }
 
 template <int V>
-__global__ void __launch_bounds__(RT_NT) franka_ma_rows_kernel(const __grid_constant__ IgeFrankaMAParams p,
-                                                               const __grid_constant__ IgeFrankaMABuffers b,
+__global__ void __launch_bounds__(RT_NT) franka_ma_rows_kernel(const __grid_constant__ IgeFrankaMAParams p_in,
+                                                               const __grid_constant__ IgeFrankaMABuffers b_in,
                                                                const int num_tiles, const int tiles_per_cta,
                                                                const int use_tma) {
+#if IGE_STAGE_ARGS
+    // (experiment) kernel arguments -> shared memory once
+    __shared__ __align__(16) IgeFrankaMAParams p;
+    __shared__ __align__(16) IgeFrankaMABuffers b;
+    {
+        static_assert(sizeof(IgeFrankaMAParams) % 8 == 0 && sizeof(IgeFrankaMABuffers) % 8 == 0, "argument structs copy as 8-B words");
+        constexpr int WP = sizeof(IgeFrankaMAParams) / 8, WB = sizeof(IgeFrankaMABuffers) / 8;
+        const uint64_t *sp = reinterpret_cast<const uint64_t *>(&p_in), *sb = reinterpret_cast<const uint64_t *>(&b_in);
+        for (int w = threadIdx.x; w < WP + WB; w += blockDim.x) {
+            if (w < WB) reinterpret_cast<uint64_t *>(&b)[w] = sb[w];
+            else reinterpret_cast<uint64_t *>(&p)[w - WB] = sp[w - WB];
+        }
+    }
+    __syncthreads();
+#else
+    const IgeFrankaMAParams &p = p_in;
+    const IgeFrankaMABuffers &b = b_in;
+#endif
     constexpr int A = 2, T = 2;
     constexpr int NA = V == IGE_FRANKA_REACH ? 6 : 7;
     constexpr int NO = V == IGE_FRANKA_REACH ? 19 : V == IGE_FRANKA_COLLECT ? 28 : V == IGE_FRANKA_COMBINE ? 48 : 50;
@@ -542,12 +564,9 @@ __global__ void __launch_bounds__(RT_NT) franka_ma_rows_kernel(const __grid_cons
     }
     __syncthreads();   // every thread has read what it needs of the ENTRY flags and the step word
     const uint64_t step = s_step;
-    uint64_t tag = 0;
-    int list_off = 0;
-    if (warp == 0 && emit) {
-        tag = *reinterpret_cast<const volatile uint64_t *>(b.list.scratch) + 1;
-        list_off = ige::list_cta_prefix(b.list, cnt, p.rand.step);   // every lane of warp 0 holds it
-    }
+    ige::ListTag ltag{0, 0};
+    int list_off = -1;
+    if (warp == 0 && emit) ltag = ige::list_cta_publish(b.list, cnt);   // the ticket's round trip overlaps tile 0's loads
 
     float comp[NC];
 #pragma unroll
@@ -617,6 +636,11 @@ __global__ void __launch_bounds__(RT_NT) franka_ma_rows_kernel(const __grid_cons
             }
         }
 
+        // the launch epoch, for the flag gate below: loaded now so that its round trip overlaps the tile's loads
+        uint64_t gate = 0;
+        if (!flags_open && tid == 0) gate = *reinterpret_cast<const volatile uint64_t *>(b.list.scratch);
+        if (t == 0 && warp == 0 && emit) ige::list_cta_scan(b.list, ltag, p.rand.step);   // last CTA to arrive only
+
         // ---- post_physics_step :821-826: progress++, agent flags -> reset_idx (AND filter) ----
         const long long rst_o = __shfl_xor_sync(0xffffffffu, rst, 1);
         const bool did_reset = valid && rst != 0 && rst_o != 0;
@@ -630,17 +654,17 @@ __global__ void __launch_bounds__(RT_NT) franka_ma_rows_kernel(const __grid_cons
 #pragma unroll
             for (int k = 0; k < 3; ++k) ma_uniform4(rr, step, 4, rk, e, 9, k, u4[k]);
             // _reset_init_cube_state: cube `a` (franka_reach_MA.py:676-704)
-            cube[0] = p.cube_xy_center[0] + p.cube_xy_mult * (u1[2 * a] - 0.5f);
-            cube[1] = p.cube_xy_center[1] + p.cube_xy_mult * (u1[2 * a + 1] - 0.5f);
-            cube[2] = p.cube_z_base + u0[a] * p.cube_z_range;
+            cube[0] = p.cube_xy_center[0] + p.cube_xy_mult * ((a ? u1[2] : u1[0]) - 0.5f);
+            cube[1] = p.cube_xy_center[1] + p.cube_xy_mult * ((a ? u1[3] : u1[1]) - 0.5f);
+            cube[2] = p.cube_z_base + (a ? u0[1] : u0[0]) * p.cube_z_range;
             cube[3] = cube[4] = cube[5] = 0.0f; cube[6] = 1.0f;
             float *ci = b.init_cubeA_state + ((size_t)e * T + a) * 13;
             float *cr = actor_row(p, b, e, p.cube_actor_start + p.cube_actor_step * a);
 #pragma unroll
             for (int i = 0; i < 13; ++i) { const float v = i < 7 ? cube[i] : 0.0f; ci[i] = v; cr[i] = v; }
             if (V == IGE_FRANKA_PP) {  // _reset_dest_cube_state franka_PPMA.py:862-895
-                dest[0] = p.aux_xy_center_x[a] + p.aux_xy_mult * (u3[2 * a] - 0.5f);
-                dest[1] = p.aux_xy_center_y + p.aux_xy_mult * (u3[2 * a + 1] - 0.5f);
+                dest[0] = (a ? p.aux_xy_center_x[1] : p.aux_xy_center_x[0]) + p.aux_xy_mult * ((a ? u3[2] : u3[0]) - 0.5f);
+                dest[1] = p.aux_xy_center_y + p.aux_xy_mult * ((a ? u3[3] : u3[1]) - 0.5f);
                 dest[2] = p.aux_z_base + 0.0f;
                 float *dr = actor_row(p, b, e, p.dest_actor_start + p.dest_actor_step * a);
 #pragma unroll
@@ -679,9 +703,9 @@ __global__ void __launch_bounds__(RT_NT) franka_ma_rows_kernel(const __grid_cons
             float u0[4], u1[4];
             ma_uniform4(rr, step, 0, rk, j, T, 0, u0);
             ma_uniform4(rr, step, 1, rk, j, 2 * T, 0, u1);
-            jc[0] = p.cube_xy_center[0] + p.cube_xy_mult * (u1[2 * c] - 0.5f);
-            jc[1] = p.cube_xy_center[1] + p.cube_xy_mult * (u1[2 * c + 1] - 0.5f);
-            jc[2] = p.cube_z_base + u0[c] * p.cube_z_range;
+            jc[0] = p.cube_xy_center[0] + p.cube_xy_mult * ((c ? u1[2] : u1[0]) - 0.5f);
+            jc[1] = p.cube_xy_center[1] + p.cube_xy_mult * ((c ? u1[3] : u1[1]) - 0.5f);
+            jc[2] = p.cube_z_base + (c ? u0[1] : u0[0]) * p.cube_z_range;
         }
 
         // ---- the partner lane's rows ----
@@ -881,7 +905,7 @@ __global__ void __launch_bounds__(RT_NT) franka_ma_rows_kernel(const __grid_cons
         if (bulk) ige::fence_proxy_async();
         if (!flags_open && tid == 0) {
             const volatile uint64_t *sc = reinterpret_cast<const volatile uint64_t *>(b.list.scratch);
-            while (sc[0] < tag) { }
+            while (gate < ltag.tag) gate = sc[0];
         }
         if (t >= 1 && tid == 0) ige::bulk_wait_read_all();  // tile t - 1 has left obs_tile[(t + 1) & 1]: free for tile t + 1
         __syncthreads();
@@ -903,6 +927,7 @@ __global__ void __launch_bounds__(RT_NT) franka_ma_rows_kernel(const __grid_cons
             for (int i = tid; i < count; i += RT_NT) dc[i] = clampf(otile[i], p.clip_obs);
         }
         if (emit && warp == 0) {   // this tile's ids: lane l writes env e0 + l at its rank within the ballot
+            if (list_off < 0) list_off = ige::list_cta_prefix_wait(b.list, ltag);   // my CTA's slot: written long ago
             const uint32_t m = s_own[t];
             if ((m >> lane) & 1u) b.list.ids[list_off + __popc(m & ((1u << lane) - 1u))] = e0 + lane;
             list_off += __popc(m);

@@ -275,68 +275,129 @@ __device__ __forceinline__ void warp_stats_add(float *stats, const float (&v)[NS
 // reset index list (IgeResetList): tile masks -> ascending ids, by the CTA that retires last
 // ---------------------------------------------------------------------------------------------
 // Scratch layout (uint32 words, zeroed once by the caller).  Two emission schemes share it:
-//   persistent kernels (blocked tiles, CTA-level look-back):
-//     64-bit word 0 = launch epoch, word 1 = {unused, retirement counter}, words 2.. = per-CTA slots
-//     {epoch + 1 : count}, kListMaxCtas of them;
+//   persistent kernels (blocked tiles, one CTA scans the per-CTA counts):
+//     64-bit word 0 = launch epoch, word 1 = {unused, ticket counter}, then kListMaxCtas count slots
+//     {epoch + 1 : count} and kListMaxCtas prefix slots {epoch + 1 : exclusive prefix};
 //   one-tile-per-warp kernels (masks + last-CTA expansion): uint32 word kListCounterWord = retirement
 //     counter, ballot masks from kListMaskBase on.
 constexpr int kListMaxCtas = 2040;
-constexpr int kListCounterWord = 2 * (2 + kListMaxCtas);  // 4084
-constexpr int kListMaskBase = kListCounterWord + 4;       // 16-B aligned
+constexpr int kListCountBase = 2;                          // 64-bit word index
+constexpr int kListPrefixBase = 2 + kListMaxCtas;          // 64-bit word index
+constexpr int kListCounterWord = 2 * (2 + 2 * kListMaxCtas);
+constexpr int kListMaskBase = kListCounterWord + 4;        // 16-B aligned
 
 __host__ __device__ inline int reset_list_scratch_words(int num_envs) {
     return kListMaskBase + (((num_envs + 31) / 32 + 3) / 4) * 4;
 }
-// ---- persistent kernels: CTA-level look-back ---------------------------------------------------------------
+// ---- persistent kernels: one CTA scans the per-CTA counts ----------------------------------------------------
 // CTA c owns a contiguous, ascending range of envs, so its reset ids form one contiguous run of the output
-// list that starts at the sum of the counts of the CTAs with a lower block index.  list_cta_prefix() is called
-// by ONE full warp per CTA, EARLY (right after the warp has counted its CTA's flags -- typically while the
-// CTA's first tile is still in flight), and returns that sum:
-//   1. publish {launch epoch + 1 : count} in this CTA's slot;
-//   2. take the "consumed the epoch and the Philox step word" ticket: every thread of the CTA must have READ the
-//      step word before the CTA barrier that precedes this call, so the CTA that draws the last ticket may open
-//      the next launch epoch and advance the step word at once -- nobody reads either word again in this launch
-//      (slot tags are compared with the register copy of the epoch);
-//   3. sum the predecessors' slots (batched polls, only unpublished slots are re-polled).
+// list that starts at the sum of the counts of the CTAs with a lower block index.  Every CTA reading every
+// predecessor's slot is O(grid^2) loads on a few hot L2 lines (measured at 512 CTAs: 1.4 us at the tail of the
+// kernel, 3 us when polled early).  Instead, O(grid) traffic and no memory fence anywhere:
+//   list_cta_publish()  (one full warp per CTA, EARLY -- right after the warp counted its CTA's flags): store
+//     {launch epoch + 1 : count} in the CTA's count slot and take a ticket.  Returns at once; the ticket's round
+//     trip overlaps whatever the warp does next.
+//   list_cta_scan()  (same warp, a little later): the CTA that drew the LAST ticket opens the next launch epoch,
+//     advances the Philox step word, then reads all count slots (batched; a slot whose tag is still stale -- its
+//     store may trail its CTA's ticket -- is simply re-read), scans them and writes every CTA's exclusive prefix
+//     {epoch + 1 : prefix} plus the total.
+//     Epoch / step word: every thread of every CTA READ both before its CTA's ticket (the caller guarantees a CTA
+//     barrier between those reads and list_cta_publish), and nobody reads either again in this launch (tags are
+//     compared with the register copy), so the last ticket may advance them at once.
+//   list_cta_prefix_wait()  (LATE -- when the ids are about to be written): poll the CTA's OWN prefix slot; by
+//     then it has long been written.
 // The caller's grid must not exceed the number of co-resident CTAs (every launcher caps it with the occupancy
-// API), so all predecessors are running and publish within their first microsecond -- the wait cannot deadlock,
-// whatever order the hardware dispatches CTAs in.  grid <= kListMaxCtas.
-__device__ __forceinline__ int list_cta_prefix(const IgeResetList &L, int cnt, uint64_t *step_word) {
+// API): the scanner is the last CTA to ARRIVE, so nobody waits for a CTA that is not running yet, whatever order
+// the hardware dispatches CTAs in.  grid <= kListMaxCtas.
+#ifndef IGE_LIST_SCAN
+#define IGE_LIST_SCAN 1
+#endif
+struct ListTag {
+    uint64_t tag;      // launch epoch + 1
+    unsigned ticket;   // lane 0: this CTA's ticket (in flight until first use)
+};
+__device__ __forceinline__ ListTag list_cta_publish(const IgeResetList &L, int cnt) {
     volatile uint64_t *sc = reinterpret_cast<volatile uint64_t *>(L.scratch);
-    const int lane = threadIdx.x & 31;
-    const uint64_t tag = sc[0] + 1;  // launch epoch + 1 (the scratch starts zeroed)
+    const uint64_t tag = sc[0] + 1;  // (the scratch starts zeroed)
     unsigned ticket = 0;
-    if (lane == 0) {
-        sc[2 + blockIdx.x] = (tag << 32) | (uint32_t)cnt;
-        ticket = atomicInc(L.scratch + 2, gridDim.x - 1);
+    if ((threadIdx.x & 31) == 0) {
+        sc[kListCountBase + blockIdx.x] = (tag << 32) | (uint32_t)cnt;
+        ticket = atomicInc(L.scratch + 2, gridDim.x - 1u);
     }
-    int sum = 0;
-    constexpr int LB = 8;
-    for (int c0 = lane; c0 < (int)blockIdx.x; c0 += 32 * LB) {
+    return ListTag{tag, ticket};
+}
+__device__ __forceinline__ void list_cta_scan(const IgeResetList &L, const ListTag &t, uint64_t *step_word) {
+    volatile uint64_t *sc = reinterpret_cast<volatile uint64_t *>(L.scratch);
+    const int lane = threadIdx.x & 31, G = (int)gridDim.x;
+    if (__shfl_sync(0xffffffffu, t.ticket, 0) != (unsigned)G - 1u) return;
+    if (lane == 0) {   // every CTA has consumed the epoch and the step word
+        sc[0] = t.tag;
+        if (step_word) *step_word += 1ull;
+    }
+#if IGE_LIST_SCAN
+    int run = 0;
+    constexpr int LB = 8;   // chunks of 32 slots in flight
+    for (int c0 = 0; c0 < G; c0 += 32 * LB) {
         uint64_t v[LB];
         bool ok;
         do {
             ok = true;
 #pragma unroll
             for (int k = 0; k < LB; ++k) {
-                const int c = c0 + 32 * k;
-                v[k] = c < (int)blockIdx.x ? sc[2 + c] : (tag << 32);
-                ok &= (v[k] >> 32) == tag;
+                const int c = c0 + 32 * k + lane;
+                v[k] = c < G ? sc[kListCountBase + c] : (t.tag << 32);
+                ok &= (v[k] >> 32) == t.tag;
             }
-        } while (!ok);
+        } while (!__all_sync(0xffffffffu, ok));
 #pragma unroll
-        for (int k = 0; k < LB; ++k) sum += (int)(uint32_t)v[k];
-    }
+        for (int k = 0; k < LB; ++k) {
+            const int c = c0 + 32 * k + lane;
+            const int cnt = (int)(uint32_t)v[k];
+            int incl = cnt;
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-    if (lane == 0) {
-        if (blockIdx.x == gridDim.x - 1) *L.count = sum + cnt;
-        if (ticket == gridDim.x - 1) {
-            sc[0] = sc[0] + 1;
-            if (step_word) *step_word += 1ull;
+            for (int o = 1; o < 32; o <<= 1) {
+                const int u = __shfl_up_sync(0xffffffffu, incl, o);
+                if (lane >= o) incl += u;
+            }
+            if (c < G) sc[kListPrefixBase + c] = (t.tag << 32) | (uint32_t)(run + incl - cnt);
+            run += __shfl_sync(0xffffffffu, incl, 31);
         }
     }
-    return sum;
+    if (lane == 0) *L.count = run;
+#endif
+}
+// exclusive prefix of this CTA (number of ids emitted by the CTAs with a lower block index); full warp
+__device__ __forceinline__ int list_cta_prefix_wait(const IgeResetList &L, const ListTag &t) {
+    const volatile uint64_t *sc = reinterpret_cast<const volatile uint64_t *>(L.scratch);
+#if !IGE_LIST_SCAN
+    {   // (round-1 behaviour, kept for A/B timing) batched polls of every predecessor's count slot
+        const int lane = threadIdx.x & 31;
+        int sum = 0;
+        constexpr int LB = 8;
+        for (int c0 = lane; c0 < (int)blockIdx.x; c0 += 32 * LB) {
+            uint64_t v[LB];
+            bool ok;
+            do {
+                ok = true;
+#pragma unroll
+                for (int k = 0; k < LB; ++k) {
+                    const int c = c0 + 32 * k;
+                    v[k] = c < (int)blockIdx.x ? sc[kListCountBase + c] : (t.tag << 32);
+                    ok &= (v[k] >> 32) == t.tag;
+                }
+            } while (!ok);
+#pragma unroll
+            for (int k = 0; k < LB; ++k) sum += (int)(uint32_t)v[k];
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+        if (blockIdx.x == gridDim.x - 1 && lane == 0) *L.count = sum + (int)(uint32_t)sc[kListCountBase + blockIdx.x];
+        return sum;
+    }
+#endif
+    uint64_t v;
+    do { v = sc[kListPrefixBase + blockIdx.x]; } while ((v >> 32) != t.tag);
+    return (int)(uint32_t)v;
 }
 // Ascending ids of one 32-env ballot `mask` whose first env is `base`, written from list position `off` on.
 // One lane per call (the caller distributes tiles over lanes); returns the next free position.

@@ -35,6 +35,13 @@
 // (num_envs % 4 != 0) and the IGE_NO_TMA debug mode.
 #include "ige_common.cuh"
 
+#ifndef IGE_STAGE_ARGS
+#define IGE_STAGE_ARGS 0
+#endif
+#ifndef IGE_ARG_PREFETCH
+#define IGE_ARG_PREFETCH 0
+#endif
+
 namespace {
 
 #ifdef IGE_ROLE_CLOCKS  // debug build only (tools/role_clocks.py): where does each role warp spend its cycles
@@ -488,9 +495,43 @@ __device__ __forceinline__ void issue_tile_loads(int role, const IgeLocomotionBu
 // ---------------------------------------------------------------------------------------------
 template <int D, int NS, bool HUM, int NW_ELEM, int IN_STAGES>
 __global__ void __launch_bounds__(32 * (4 + NW_ELEM), HUM ? 3 : 6)  // shared memory allows 6 (Ant) / 3 (Humanoid) CTAs per SM
-locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p,
-                            const __grid_constant__ IgeLocomotionBuffers b, const int num_tiles,
+locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p_in,
+                            const __grid_constant__ IgeLocomotionBuffers b_in, const int num_tiles,
                             const int tiles_per_cta) {
+#if IGE_STAGE_ARGS
+    // (experiment) kernel arguments staged into shared memory once; later accesses are LDS instead of constant-bank
+    // operands
+    __shared__ __align__(16) IgeLocomotionParams p;
+    __shared__ __align__(16) IgeLocomotionBuffers b;
+    {
+        static_assert(sizeof(IgeLocomotionParams) % 8 == 0 && sizeof(IgeLocomotionBuffers) % 8 == 0, "argument structs copy as 8-B words");
+        constexpr int WP = sizeof(IgeLocomotionParams) / 8, WB = sizeof(IgeLocomotionBuffers) / 8;
+        const uint64_t *sp = reinterpret_cast<const uint64_t *>(&p_in), *sb = reinterpret_cast<const uint64_t *>(&b_in);
+        for (int w = threadIdx.x; w < WP + WB; w += blockDim.x) {
+            if (w < WB) reinterpret_cast<uint64_t *>(&b)[w] = sb[w];          // the pointers first: the tile loads need them
+            else reinterpret_cast<uint64_t *>(&p)[w - WB] = sp[w - WB];
+        }
+    }
+#else
+    const IgeLocomotionParams &p = p_in;
+    const IgeLocomotionBuffers &b = b_in;
+#endif
+#if IGE_ARG_PREFETCH
+    // Kernel arguments live in the constant bank.  At 16 k envs every CTA processes ONE tile, so every first touch
+    // of a 64-B argument line is a cold constant-cache miss inside some role's dependent chain.  Touch every line
+    // now, with independent loads whose misses overlap (and hide behind the mbarrier set-up / first tile load).
+    {
+        constexpr int LINES = (sizeof(IgeLocomotionParams) + sizeof(IgeLocomotionBuffers) + 63) / 64;
+        const uint32_t *a = reinterpret_cast<const uint32_t *>(&p_in);
+        uint32_t acc = 0;
+#pragma unroll
+        for (int l = 0; l < LINES; ++l) acc ^= a[l * 16 < (int)(sizeof(IgeLocomotionParams) / 4) ? l * 16 : 0];
+        const uint32_t *a2 = reinterpret_cast<const uint32_t *>(&b_in);
+#pragma unroll
+        for (int l = 0; l < (int)(sizeof(IgeLocomotionBuffers) + 63) / 64; ++l) acc ^= a2[l * 16];
+        if (acc == 0x9e3779b9u && num_tiles < 0) asm volatile("trap;");   // keeps the loads alive; never true
+    }
+#endif
     using L = Layout<D, NS, HUM>;
     constexpr int NUM_OBS = L::NUM_OBS;
     constexpr int NW = 4 + NW_ELEM;
@@ -507,34 +548,33 @@ locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p,
     uint64_t *full = reinterpret_cast<uint64_t *>(smem_raw + sizeof(In) * IN_STAGES + sizeof(Out) * 2);
     ResetStage<D> *stage = reinterpret_cast<ResetStage<D> *>(smem_raw + sizeof(In) * IN_STAGES + sizeof(Out) * 2 + kBarBytes);
     Handoff<D> *hand = reinterpret_cast<Handoff<D> *>(stage + 2);
-    // reset ballots of my tiles: the mask words of the list scratch (global; written and read back by the
-    // REWARD warp only, so they need no shared memory)
-    uint32_t *tile_masks = b.list.scratch ? b.list.scratch + ige::kListMaskBase + blockIdx.x * tiles_per_cta : nullptr;
-
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int role = (warp + (int)blockIdx.x) % NW;
     // blocked assignment: CTA c owns the contiguous tiles [c*K, c*K + my_tiles) -- its reset ids are then
     // one contiguous run of the output list
     const int first = blockIdx.x * tiles_per_cta;
     const int my_tiles = min(tiles_per_cta, num_tiles - first);
-    const bool clamp_copy = b.obs_clamped != nullptr && p.clip_obs < INFINITY;
-    const bool second_obs_copy = b.obs_clamped != nullptr && !clamp_copy;
-    auto tile_e0 = [&](int it) { return (first + it) * TE; };
-    auto tile_ne = [&](int it) { return min(TE, p.num_envs - tile_e0(it)); };
 
     CLK(kstart);
     // Philox step word: read by ONE thread and handed over through shared memory, so the load has completed
-    // (not merely been issued) when the CTA passes the barrier below -- the retirement ticket that lets the
-    // last CTA advance the word is taken right after it.
+    // (not merely been issued) when the CTA passes the barrier below -- the ticket that lets the last CTA
+    // advance the word (ige::list_cta_publish) is taken after it.
     __shared__ uint64_t s_step;
     if (tid == 0) {
-        s_step = ige::load_step(p.rand);
+        s_step = ige::load_step(p_in.rand);
 #pragma unroll
         for (int s = 0; s < IN_STAGES; ++s) ige::mbar_init(&full[s], 1);
         ige::fence_mbar_init();
     }
-    __syncthreads();
+    __syncthreads();   // staged arguments, step word and mbarriers are visible
     const uint64_t step = s_step;
+    // reset ballots of my tiles: the mask words of the list scratch (global; written and read back by the
+    // REWARD warp only, so they need no shared memory)
+    uint32_t *tile_masks = b.list.scratch ? b.list.scratch + ige::kListMaskBase + blockIdx.x * tiles_per_cta : nullptr;
+    const bool clamp_copy = b.obs_clamped != nullptr && p.clip_obs < INFINITY;
+    const bool second_obs_copy = b.obs_clamped != nullptr && !clamp_copy;
+    auto tile_e0 = [&](int it) { return (first + it) * TE; };
+    auto tile_ne = [&](int it) { return min(TE, p.num_envs - tile_e0(it)); };
     // prologue: the first IN_STAGES tiles
     if (lane == 0 && role != REWARD)
         for (int k = 0; k < IN_STAGES && k < my_tiles; ++k)
@@ -548,11 +588,10 @@ locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p,
             n_reset = b.reset_buf[e]; n_progress = b.progress_buf[e];
             if (b.randomize_buf) n_rand = b.randomize_buf[e];
         }
-        // ---- reset index list (while the role warps work on the first tile): count my resets, publish the count
-        //      and sum the predecessor CTAs' counts -- this warp is idle until the first tile has been produced, so
-        //      the look-back costs nothing on the critical path (ige::list_cta_prefix) ----
+        // ---- reset index list (while the role warps work on the first tile): count my resets and publish the
+        //      count; the CTA that publishes last scans all counts (ige::list_cta_publish) ----
         const bool emit = b.list.scratch != nullptr;
-        int sum = 0;
+        ige::ListTag ltag{0, 0};
         if (emit) {
             int cnt = 0;
             constexpr int PB = 8;            // flag loads in flight
@@ -566,7 +605,8 @@ locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p,
 #pragma unroll
                 for (int k = 0; k < PB; ++k) cnt += __popc(__ballot_sync(0xffffffffu, f[k] != 0));
             }
-            sum = ige::list_cta_prefix(b.list, cnt, p.rand.step);
+            ltag = ige::list_cta_publish(b.list, cnt);
+            ige::list_cta_scan(b.list, ltag, p.rand.step);   // (this warp is idle until the first tile is produced)
         }
         StatAcc st;
         uint32_t reg_mask = 0u;  // lane t: reset ballot of my tile t (t < 32)
@@ -609,8 +649,9 @@ locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p,
         }
         CLK(r3);
         if (b.stats) flush_stats(b.stats, st);
-        // ---- reset index list, part 3: the ascending ids of my tiles (stores only; nothing is waited for) ----
+        // ---- reset index list, part 2: the ascending ids of my tiles, from my prefix slot on (written long ago) ----
         if (emit) {
+            int sum = ige::list_cta_prefix_wait(b.list, ltag);
             // lane l expands tiles l, l + 32, ...: exclusive scan of the tile counts, then the set bits
             for (int t0 = 0; t0 < my_tiles; t0 += 32) {
                 const int t = t0 + lane;

@@ -59,9 +59,35 @@ def from_state(task, st, sim_device, rl_device=None, **kw):
     return obj
 
 
-def make(seed, task, num_envs, sim_device, rl_device=None, reset_prob=0.02, **kw):
-    """isaacgymenvs.make()-shaped entry point (isaacgymenvs/__init__.py:14-26) on synthetic state."""
+def make(seed, task, num_envs, sim_device, rl_device=None, graphics_device_id=-1, headless=False, multi_gpu=False,
+         virtual_screen_capture=False, force_render=True, cfg=None, reset_prob=0.02, **kw):
+    """``isaacgymenvs.make()`` (isaacgymenvs/__init__.py:14-26), same positional and keyword arguments, on synthetic
+    simulator state.  ``graphics_device_id``, ``headless``, ``virtual_screen_capture`` and ``force_render`` configure
+    the viewer / camera sensors, which do not exist here (no graphics stack, no PhysX): accepted and ignored.
+    ``multi_gpu``: as in utils/rlgames_utils.py:89-107, rank / device / seed come from the torchrun environment
+    (LOCAL_RANK -> cuda:<local_rank>, seed + rank); ``num_envs`` is per rank like the reference's.
+    ``cfg``: the hydra config of the reference; only ``cfg["task"]["env"]`` scalars that the mirrors know
+    (``numEnvs``, ``clipObservations``, ``clipActions``, ``episodeLength`` / ``maxEpisodeLength``) are honoured."""
+    del graphics_device_id, headless, virtual_screen_capture, force_render
+    if task not in task_map:
+        raise ValueError(f"unknown task {task!r}; the fused path covers {sorted(task_map)}")
+    if multi_gpu:
+        from . import distributed
+        rank, local_rank, _ = distributed.env_info()
+        seed = distributed.rank_seed(seed, rank)
+        sim_device = f"cuda:{local_rank}"
+        rl_device = f"cuda:{local_rank}"
+    overrides = {}
+    if cfg is not None:
+        env_cfg = dict((cfg.get("task", cfg) or {}).get("env", {}))
+        num_envs = int(env_cfg.get("numEnvs", num_envs))
+        for src, dst in (("clipObservations", "clip_obs"), ("clipActions", "clip_actions"),
+                         ("episodeLength", "max_episode_length"), ("maxEpisodeLength", "max_episode_length")):
+            if src in env_cfg:
+                overrides["cfg_" + dst] = np.asarray(env_cfg[src])
     st = synthetic.make_state(_SYN_NAME[task], num_envs, seed=seed, reset_prob=reset_prob)
+    if task not in _MA_TASKS:
+        st.update(overrides)
     kw.setdefault("seed", seed)
     return from_state(task, st, sim_device, rl_device=rl_device, **kw)
 

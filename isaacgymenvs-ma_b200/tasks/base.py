@@ -5,7 +5,8 @@ What is kept from the reference (so callers cannot tell the difference):
   * ``allocate_buffers`` shapes / dtypes (vec_task.py:302-326): obs_buf f32 (N, num_obs),
     rew_buf f32, reset_buf i64 = 1, timeout_buf, progress_buf i64, randomize_buf i64, extras.
   * ``step(actions) -> (obs_dict, rew, reset, extras)`` order of operations (vec_task.py:362-410).
-  * ``reset()`` / ``reset_done()`` (vec_task.py:428-457).
+  * ``reset()`` / ``reset_done()`` / ``reset_idx(env_ids)`` (vec_task.py:422-457; resets are deferred to the next
+    fused launch, see ``reset_idx``).
 What is different: the simulator.  Isaac Gym's PhysX binary is not available, so ``self.sim`` is a
 ``SyntheticSim`` that owns the gymtorch-layout tensors and *records* the ``set_*_indexed`` calls
 (the same role ``gym`` plays in the reference).  A real integration binds the same
@@ -68,6 +69,14 @@ class VecTaskB200:
         self.clip_obs = float(cfg.get("clip_obs", math.inf))
         self.clip_actions = float(cfg.get("clip_actions", math.inf))
         self.control_steps = 0
+        # vec_task.py:368-370, :399-400: domain-randomisation noise lambdas on actions / observations.  DR is outside
+        # the hot path and the fused step() epilogue produces the clamped observations inside
+        # the kernel, so a noise hook could not run between post_physics_step and the clamp: refuse instead of
+        # silently dropping it.
+        self.dr_randomizations = {}
+        if cfg.get("randomize") or cfg.get("dr_randomizations"):
+            raise NotImplementedError("domain randomisation (vec_task.py:368-370, :399-400, :528-) is not part of the "
+                                      "fused path; construct the task without `randomize`")
         self.rand_mode = rand_mode
         self.seed = int(seed)
         self.fuse_epilogue = fuse_epilogue
@@ -84,7 +93,7 @@ class VecTaskB200:
         self.reset_rank = torch.zeros(self.num_envs, dtype=torch.int32, device=dev)
         self.reset_count = torch.zeros(1, dtype=torch.int32, device=dev)
         self.rng_step = torch.zeros(1, dtype=torch.int64, device=dev)
-        words = 2 + (self.num_envs + 2047) // 2048   # == ige_compact_scratch_words(num_envs)
+        words = int(_lib.lib().ige_compact_scratch_words(self.num_envs * self.num_agents))
         self._compact_scratch = torch.zeros(words, dtype=torch.int32, device=dev)
         self._list_scratch = torch.zeros(_abi.reset_list_scratch_words(self.num_envs), dtype=torch.int32, device=dev)
         self.stats_rows = (torch.zeros(_abi.IGE_STATS_ROWS * _abi.IGE_STATS_STRIDE, dtype=torch.float32, device=dev)
@@ -217,6 +226,32 @@ class VecTaskB200:
         if self.num_states > 0:
             self.obs_dict["states"] = self.get_state()
         return self.obs_dict
+
+    def reset_idx(self, env_ids):
+        """vec_task.py:422-426 virtual.  The fused kernels run ``reset_idx`` for every flagged env INSIDE the next
+        ``post_physics_step`` (tasks that reset in pre-physics: inside ``pre_physics_step``), so resetting specific
+        envs means flagging them: the reset -- state rows, noise, cleared flags -- then happens in the same launch
+        as the observations, exactly where the reference's ``step()`` would run it."""
+        ids = torch.as_tensor(env_ids, device=self.device).long().flatten()
+        if self.num_agents > 1:      # agent-axis tasks: env e owns rows e*A .. e*A + A - 1 (franka_reach_MA.py:885-889)
+            ids = (ids[:, None] * self.num_agents + torch.arange(self.num_agents, device=self.device)[None, :]).flatten()
+        self.reset_buf[ids] = 1
+
+    def reset_done(self):
+        """vec_task.py:442-457: ``(obs_dict, done_env_ids)``; called by RLGPUEnv.reset_done
+        (utils/rlgames_utils.py:252-253).  ``done_env_ids`` are the rows whose ``reset_buf`` is set, as in the
+        reference; their reset is deferred to the next step's fused launch (see ``reset_idx``)."""
+        done_env_ids = self.reset_buf.nonzero(as_tuple=False).flatten()
+        if len(done_env_ids) > 0 and self.num_agents == 1:
+            self.reset_idx(done_env_ids)
+        self.obs_dict["obs"] = torch.clamp(self.obs_buf, -self.clip_obs, self.clip_obs).to(self.rl_device)
+        if self.num_states > 0:
+            self.obs_dict["states"] = self.get_state()
+        return self.obs_dict, done_env_ids
+
+    def get_number_of_agents(self):
+        """What RLGPUEnv.get_number_of_agents forwards to (utils/rlgames_utils.py:255-256): vec_task.py:102 num_agents."""
+        return self.num_agents
 
     # -- pipeline=cpu: simulator state lives in pinned host memory ------------------------------
     FUSED_ACTION_CLAMP = False

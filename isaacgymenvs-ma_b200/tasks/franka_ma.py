@@ -169,8 +169,11 @@ class FrankaMA(VecTaskB200):
 
     # -- pre_physics_step: operational-space torque controller --------------------------------
     EFFORT_LIMITS = [87.0, 87.0, 87.0, 87.0, 12.0, 12.0, 12.0]   # franka_description panda.urdf efforts (:339)
+    # controlType "osc" command limits, per axis (franka_reach_MA.py:219, franka_collect_MA.py:228,
+    # franka_combine_MA.py / franka_PPMA.py:234)
+    CMD_LIMIT = {"reach": [0.1, 0.1, 0.1, 0.5, 0.5, 0.5], "collect": [0.6] * 6, "combine": [0.55] * 6, "pp": [0.55] * 6}
 
-    def attach_dynamics(self, mm, j_eef, action_scale=1.0, cmd_limit=0.55, kp=150.0, kp_null=10.0,
+    def attach_dynamics(self, mm, j_eef, action_scale=1.0, cmd_limit=None, kp=150.0, kp_null=10.0,
                         effort_limits=None):
         """Bind the tensors ``_get_mm()`` / ``_get_j_eef()`` return (franka_PPMA.py:1041-1061: PhysX mass matrices
         (N*A, 7, 7) and end-effector Jacobians (N*A, 6, 7), stacked over agents) and the controller gains
@@ -183,7 +186,11 @@ class FrankaMA(VecTaskB200):
             raise _lib.IgeError("OSC pre-physics expects 9 DOFs per Franka (7 arm + 2 fingers)")
         self._mm, self._j_eef = mm, j_eef
         self.action_scale = float(action_scale)
-        self.cmd_limit = [float(cmd_limit)] * 6
+        if cmd_limit is None:
+            cmd_limit = self.CMD_LIMIT[self.variant]
+        self.cmd_limit = ([float(cmd_limit)] * 6 if isinstance(cmd_limit, (int, float)) else [float(x) for x in cmd_limit])
+        if len(self.cmd_limit) != 6:
+            raise ValueError("cmd_limit: a scalar or one value per Cartesian axis (6)")
         self.kp = [float(kp)] * 6
         self.kd = (2 * torch.sqrt(torch.tensor(self.kp))).tolist()            # :227
         self.kp_null = [float(kp_null)] * 7

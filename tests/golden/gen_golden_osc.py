@@ -19,6 +19,7 @@ import harness as H  # noqa: E402
 import ref_harness  # noqa: E402
 
 EFFORT_LIMITS = [87.0, 87.0, 87.0, 87.0, 12.0, 12.0, 12.0]
+REF_CMD_LIMIT = {"reach": [0.1, 0.1, 0.1, 0.5, 0.5, 0.5], "collect": [0.6] * 6, "combine": [0.55] * 6, "pp": [0.55] * 6}
 
 
 def synthetic_dynamics(rows, seed):
@@ -45,18 +46,20 @@ def generate(variant, n, A, seed):
     # gentle motion so that about half of the torques stay inside the effort limits (the clamp is tested either way)
     obj._rigid_body_state[:, :, 7:] *= 0.05
     obj._dof_state[..., 1] *= 0.05
-    obj.cmd_limit_value = 0.05 if seed % 2 == 0 else 0.55
     obj.kp = torch.tensor([150.0] * 6)
     obj.kd = 2 * torch.sqrt(obj.kp)
     obj.kp_null = torch.tensor([10.0] * 7)
     obj.kd_null = 2 * torch.sqrt(obj.kp_null)
-    obj.cmd_limit = torch.tensor([obj.cmd_limit_value] * 6).unsqueeze(0)
+    # the reference's own per-variant command limits (franka_reach_MA.py:219 is NOT uniform over the six axes;
+    # franka_collect_MA.py:228, franka_combine_MA.py / franka_PPMA.py:234)
+    obj.cmd_limit = torch.tensor(REF_CMD_LIMIT[variant]).unsqueeze(0)
     obj._franka_effort_limits = torch.tensor(EFFORT_LIMITS + [70.0, 70.0])
     obj._arm_control = obj._effort_control.view(-1, 9)[:, :7]
     obj._gripper_control = obj._pos_control.view(-1, 9)[:, -2:]
     obj.states["eef_vel"] = obj._eef_state[:, :, 7:]
     g = torch.Generator().manual_seed(seed + 7)
     raw = torch.rand((rows, cfg["num_actions"]), generator=g) * 3.0 - 1.5
+    raw[1::2, :6] *= 0.08      # every other row: small arm commands, so that a good share of the torques is NOT clamped
     actions = torch.clamp(raw, -1.0, 1.0)                             # VecTask.step, vec_task.py:373
     blob = {"in_actions_raw": raw.numpy().copy(), "in_mm": mm.numpy().copy(), "in_j_eef": j.numpy().copy(),
             "in_dof_state": obj._dof_state.numpy().copy(), "in_rigid_body_state": obj._rigid_body_state.numpy().copy(),

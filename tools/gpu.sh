@@ -36,7 +36,7 @@ for act in "$@"; do
         --log-file gpurun_out/${R}_launches_bench.csv python bench.py --steps 64 --warmup 16 --no-sweep --no-cpu --no-e2e > gpurun_out/ncu_launch.log 2>&1
       echo "ncu launches rc=$?" ;;
     ncu)
-      timeout 400 ncu --set full --clock-control none --import-source on -s 2 -c 1 -f -o gpurun_out/${R}_prof_$d \
+      timeout 400 ncu --set full --clock-control none --import-source on -k regex:"${KREGEX:-ige|locomotion|franka|shadow_hand|anymal|cartpole|rollout|task}" -s 2 -c 1 -f -o gpurun_out/${R}_prof_$d \
         python tools/prof.py --task $b --num-envs $c --steps 4 --replicas 4 --hot > gpurun_out/ncu_$d.log 2>&1
       echo "ncu $d rc=$?"; python tools/ncu_summary.py gpurun_out/${R}_prof_$d.ncu-rep > gpurun_out/${R}_ncu_full_$d.txt 2>&1; cat gpurun_out/${R}_ncu_full_$d.txt ;;
     sanitize)   # sanitize:<memcheck|racecheck>  -- ONE tool per gpurun call (B200_PROFILING.md)
@@ -58,6 +58,8 @@ except Exception as e:
     print("  failed:", e); print(open("gpurun_out/kern_${b}_$c.err").read()[-800:])
 PY
       ;;
+    build)      # build:<nvcc flags separated by commas>  -- rebuild the library on the box (experiments)
+      python isaacgymenvs-ma_b200/build.py ${b//,/ } > gpurun_out/build_$c.log 2>&1; echo "build [$b] rc=$?" ;;
     floors) python tools/floors.py > gpurun_out/${R}_floors.txt 2>&1; cat gpurun_out/${R}_floors.txt ;;
     *) echo "unknown action $act" ;;
   esac
