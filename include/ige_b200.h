@@ -527,6 +527,117 @@ int ige_anymal_scratch_words(int32_t num_envs);
 int ige_anymal_post_physics(const IgeAnymalParams *p, const IgeAnymalBuffers *b, void *stream);
 
 /* ------------------------------------------------------------------------------------------
+ * Remaining single-agent tasks.  One Args struct per task (scalars first, then the
+ * borrowed device pointers), two entry points for the tasks whose reset_idx runs in pre_physics_step.
+ * Every kernel that resets envs emits the ascending reset id list itself (IgeResetList) and advances
+ * rand.step once per launch.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct IgeTaskRand {
+    int32_t mode;          /* IGE_RAND_INJECTED | IGE_RAND_PHILOX */
+    int32_t _pad;
+    uint64_t seed;         /* PHILOX: key */
+    uint64_t *step;        /* PHILOX: device word mixed into the counter, advanced by one per resetting launch */
+    const int32_t *rank;   /* INJECTED: [N] exclusive prefix of the reset flag == row of env n in u[] */
+    const float *u[8];     /* INJECTED: the torch.rand draws of the reset path, in call order (shapes per task) */
+} IgeTaskRand;
+
+/* BallBalance -- tasks/ball_balance.py: pre_physics_step :410-430 (reset_idx :360-408 + position targets),
+ * post_physics_step :432-441 (compute_observations :330-345, compute_bbot_reward :460-476) and the step() epilogue.
+ * Reset draws (rows by reset rank, each (k,1)): u[0] dists, u[1] direction angle, u[2] horizontal speed,
+ * u[3] vertical speed (its value is multiplied by 5.0 - 5.0), u[4] height. */
+typedef struct IgeBallBalanceArgs {
+    int32_t num_envs;
+    float max_episode_length;        /* cfg env.maxEpisodeLength (500) */
+    float ball_radius;               /* 0.1 (:99 of _create_envs) */
+    float target_step;               /* float32(dt * actionSpeedScale): the Python double product of :421 */
+    float clip_obs;                  /* INFINITY = none */
+    float dof_lower[6], dof_upper[6];/* bbot_dof_lower / upper_limits */
+    IgeTaskRand rand;
+    float *root_states;              /* (N, 2, 13) actor 0 = balance bot, actor 1 = ball; reset rows rewritten */
+    float *dof_states;               /* (N, 6, 2) reset rows rewritten */
+    const float *sensor_tensor;      /* (N, 3, 6) force sensors (force xyz, torque xyz) */
+    const float *initial_root_states;/* (N, 2, 13) */
+    const float *initial_dof_states; /* (N, 6, 2) */
+    const float *actions;            /* (N, 3) as passed to pre_physics_step (already clamped by VecTask.step) */
+    float *dof_position_targets;     /* (N, 6) in/out */
+    float *obs_buf;                  /* (N, 24) */
+    float *rew_buf;
+    int64_t *reset_buf, *progress_buf;
+    float *obs_clamped;              /* optional */
+    uint8_t *timeout_buf;            /* optional */
+    IgeResetList list;               /* pre_physics: envs reset in this call */
+} IgeBallBalanceArgs;
+int ige_ball_balance_pre_physics(const IgeBallBalanceArgs *a, void *stream);
+int ige_ball_balance_post_physics(const IgeBallBalanceArgs *a, void *stream);
+
+/* Quadcopter -- tasks/quadcopter.py: pre_physics_step :301-331 (reset_idx :280-299 + DOF targets, thrusts, rotor
+ * forces), post_physics_step :333-341 (compute_observations :362-373, compute_quadcopter_reward :391-425).
+ * Reset draws: u[0], u[1], u[2] root x / y / z offsets (k,1); u[3] DOF positions (k,8). */
+typedef struct IgeQuadcopterArgs {
+    int32_t num_envs;
+    int32_t num_bodies;              /* rigid bodies per env in `forces` (9) */
+    float max_episode_length;
+    float dof_target_step;           /* float32(dt * 8 pi)   (:309-310) */
+    float thrust_step;               /* float32(dt * 200)    (:313-314) */
+    float clip_obs;
+    float dof_lower[8], dof_upper[8];
+    float thrust_lower[4], thrust_upper[4];
+    int32_t rotor_bodies[4];         /* forces[:, body, 2] = thrust (2, 4, 6, 8; :317-320) */
+    IgeTaskRand rand;
+    float *root_states;              /* (N, 13) reset rows rewritten */
+    float *dof_states;               /* (N, 8, 2) reset rows rewritten */
+    const float *initial_root_states, *initial_dof_states;
+    const float *actions;            /* (N, 12) */
+    float *dof_position_targets;     /* (N, 8) in/out */
+    float *thrusts;                  /* (N, 4) in/out */
+    float *forces;                   /* (N, num_bodies, 3) in/out */
+    float *obs_buf;                  /* (N, 21) */
+    float *rew_buf;
+    int64_t *reset_buf, *progress_buf;
+    float *obs_clamped;
+    uint8_t *timeout_buf;
+    IgeResetList list;
+} IgeQuadcopterArgs;
+int ige_quadcopter_pre_physics(const IgeQuadcopterArgs *a, void *stream);
+int ige_quadcopter_post_physics(const IgeQuadcopterArgs *a, void *stream);
+
+/* Ingenuity -- tasks/ingenuity.py: pre_physics_step :322-364 (set_targets :283-294 for progress % 500 == 0,
+ * reset_idx :296-320, rotor thrusts), post_physics_step :366-374 (compute_observations :396-401,
+ * compute_ingenuity_reward :420-455).
+ * Draws: u[0] (kt, 2) / u[1] (kt) set_targets of the envs with progress % 500 == 0 (rows by target_rank);
+ *        u[2] (k, 2) / u[3] (k) set_targets nested in reset_idx, u[4], u[5], u[6] (k,1) root x / y / z offsets
+ *        (rows by rand.rank). */
+typedef struct IgeIngenuityArgs {
+    int32_t num_envs;
+    int32_t num_bodies;              /* rigid bodies per env in `forces` (6) */
+    float max_episode_length;
+    float dt;
+    float thrust_upper_limit;        /* 2000 */
+    float thrust_lateral_component;  /* 0.2 */
+    float clip_obs;
+    int32_t _pad;
+    IgeTaskRand rand;
+    const int32_t *target_rank;      /* INJECTED: [N] exclusive prefix of (progress_buf % 500 == 0) */
+    float *root_tensor;              /* (N, 2, 13) actor 0 = copter, actor 1 = target marker */
+    float *dof_states;               /* (N, 4, 2): rotor velocities of ALL envs are re-set whenever any env resets (:299-300) */
+    const float *initial_root_states;/* (N, 13) copter rows */
+    const float *actions;            /* (N, 6) */
+    float *target_root_positions;    /* (N, 3) in/out */
+    float *thrusts;                  /* (N, 2, 3) */
+    float *forces;                   /* (N, num_bodies, 3) */
+    float *obs_buf;                  /* (N, 13) */
+    float *rew_buf;
+    int64_t *reset_buf, *progress_buf;
+    float *obs_clamped;
+    uint8_t *timeout_buf;
+    int64_t *actor_dirty;            /* optional (N * 2): 0/1 per actor row to hand to set_actor_root_state_tensor_indexed
+                                        (== the sorted unique() of :341 once compacted) */
+    IgeResetList list;               /* envs reset in this call (== reset_buf.nonzero()) */
+} IgeIngenuityArgs;
+int ige_ingenuity_pre_physics(const IgeIngenuityArgs *a, void *stream);
+int ige_ingenuity_post_physics(const IgeIngenuityArgs *a, void *stream);
+
+/* ------------------------------------------------------------------------------------------
  * Episode statistics: fold the striped accumulator a step kernel adds into (Buffers.stats) into the
  * <= IGE_NUM_STATS-float vector that is all-reduced across GPUs once per horizon (the
  * reference keeps per-rank statistics, utils/rlgames_utils.py:89-107).  One tiny launch, off the step's

@@ -183,6 +183,38 @@ class IgeAnymalBuffers(C.Structure):
                 ("obs_clamped", _p), ("timeout_buf", _p), ("reset_ids", _p), ("reset_count", _p), ("scratch", _p)]
 
 
+class IgeTaskRand(C.Structure):
+    _fields_ = [("mode", _i), ("_pad", _i), ("seed", C.c_uint64), ("step", _p), ("rank", _p), ("u", _p * 8)]
+
+
+class IgeBallBalanceArgs(C.Structure):
+    _fields_ = [("num_envs", _i), ("max_episode_length", _f), ("ball_radius", _f), ("target_step", _f),
+                ("clip_obs", _f), ("dof_lower", _f * 6), ("dof_upper", _f * 6), ("rand", IgeTaskRand),
+                ("root_states", _p), ("dof_states", _p), ("sensor_tensor", _p), ("initial_root_states", _p),
+                ("initial_dof_states", _p), ("actions", _p), ("dof_position_targets", _p), ("obs_buf", _p),
+                ("rew_buf", _p), ("reset_buf", _p), ("progress_buf", _p), ("obs_clamped", _p), ("timeout_buf", _p),
+                ("list", IgeResetList)]
+
+
+class IgeQuadcopterArgs(C.Structure):
+    _fields_ = [("num_envs", _i), ("num_bodies", _i), ("max_episode_length", _f), ("dof_target_step", _f),
+                ("thrust_step", _f), ("clip_obs", _f), ("dof_lower", _f * 8), ("dof_upper", _f * 8),
+                ("thrust_lower", _f * 4), ("thrust_upper", _f * 4), ("rotor_bodies", _i * 4), ("rand", IgeTaskRand),
+                ("root_states", _p), ("dof_states", _p), ("initial_root_states", _p), ("initial_dof_states", _p),
+                ("actions", _p), ("dof_position_targets", _p), ("thrusts", _p), ("forces", _p), ("obs_buf", _p),
+                ("rew_buf", _p), ("reset_buf", _p), ("progress_buf", _p), ("obs_clamped", _p), ("timeout_buf", _p),
+                ("list", IgeResetList)]
+
+
+class IgeIngenuityArgs(C.Structure):
+    _fields_ = [("num_envs", _i), ("num_bodies", _i), ("max_episode_length", _f), ("dt", _f),
+                ("thrust_upper_limit", _f), ("thrust_lateral_component", _f), ("clip_obs", _f), ("_pad", _i),
+                ("rand", IgeTaskRand), ("target_rank", _p), ("root_tensor", _p), ("dof_states", _p),
+                ("initial_root_states", _p), ("actions", _p), ("target_root_positions", _p), ("thrusts", _p),
+                ("forces", _p), ("obs_buf", _p), ("rew_buf", _p), ("reset_buf", _p), ("progress_buf", _p),
+                ("obs_clamped", _p), ("timeout_buf", _p), ("actor_dirty", _p), ("list", IgeResetList)]
+
+
 class IgeStatsSnapshotArgs(C.Structure):
     _fields_ = [("stats", _p), ("out", _p), ("zero_stats", _i), ("accumulate", _i)]
 

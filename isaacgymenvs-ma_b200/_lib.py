@@ -25,6 +25,12 @@ _SIGS = {
     "ige_anymal_post_physics": (_abi.IgeAnymalParams, _abi.IgeAnymalBuffers),
     "ige_ma_rollout_step": (_abi.IgeRolloutStepArgs,),
     "ige_ma_discount_values": (_abi.IgeDiscountArgs,),
+    "ige_ball_balance_pre_physics": (_abi.IgeBallBalanceArgs,),
+    "ige_ball_balance_post_physics": (_abi.IgeBallBalanceArgs,),
+    "ige_quadcopter_pre_physics": (_abi.IgeQuadcopterArgs,),
+    "ige_quadcopter_post_physics": (_abi.IgeQuadcopterArgs,),
+    "ige_ingenuity_pre_physics": (_abi.IgeIngenuityArgs,),
+    "ige_ingenuity_post_physics": (_abi.IgeIngenuityArgs,),
     "ige_stats_snapshot": (_abi.IgeStatsSnapshotArgs,),
 }
 

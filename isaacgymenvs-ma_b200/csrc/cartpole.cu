@@ -62,7 +62,7 @@ __global__ void __launch_bounds__(kThreads) cartpole_post_physics_kernel(IgeCart
     }
     if (b.list.scratch) {  // warp == one 32-env tile of the reset list
         const uint32_t mask = __ballot_sync(0xffffffffu, was_reset);
-        if ((threadIdx.x & 31) == 0 && e < p.num_envs) ige::publish_tile_mask(b.list, e >> 5, mask);
+        if ((threadIdx.x & 31) == 0 && e < p.num_envs) ige::publish_tile_mask(b.list, p.num_envs, e >> 5, mask);
     }
     }
     if (b.stats) {

@@ -220,7 +220,7 @@ __global__ void __launch_bounds__(NT) franka_ma_kernel(const __grid_constant__ I
     }
     if (phase != PH_COMPUTE) {
         const uint32_t mask = __ballot_sync(0xffffffffu, did_reset);
-        if (b.list.scratch && lane == 0 && e < N) ige::publish_tile_mask(b.list, e >> 5, mask);
+        if (b.list.scratch && lane == 0 && e < N) ige::publish_tile_mask(b.list, N, e >> 5, mask);
         for (uint32_t m = mask; m; m &= m - 1)  // the warp resets its flagged envs one after the other, together
             reset_env_coop(p, b, step, e - lane + __ffs(m) - 1, lane, s_u[tid >> 5]);
     }

@@ -172,8 +172,10 @@ __device__ __forceinline__ float row_sum(F elem) {
 // ---------------------------------------------------------------------------------------------
 // Philox4x32-10 counter-based RNG (production reset noise; the oracle has the same function)
 // ---------------------------------------------------------------------------------------------
+// (the rounds stay a LOOP: unrolled, every inlined call was 1.7 KB of code that only reset rows execute, and the
+// step kernels are instruction-fetch bound at small env counts -- 32 KB L1.5 instruction cache per SM)
 __device__ __forceinline__ void philox4x32_10(uint32_t c[4], uint32_t k0, uint32_t k1) {
-#pragma unroll
+#pragma unroll 1
     for (int r = 0; r < 10; ++r) {
         const uint32_t hi0 = __umulhi(0xD2511F53u, c[0]), lo0 = 0xD2511F53u * c[0];
         const uint32_t hi1 = __umulhi(0xCD9E8D57u, c[2]), lo1 = 0xCD9E8D57u * c[2];
@@ -286,8 +288,11 @@ constexpr int kListPrefixBase = 2 + kListMaxCtas;          // 64-bit word index
 constexpr int kListCounterWord = 2 * (2 + 2 * kListMaxCtas);
 constexpr int kListMaskBase = kListCounterWord + 4;        // 16-B aligned
 
+// uint32 words of the tagged tile slots (scheme 3 below): one 64-bit slot per 32-env tile, from kListMaskBase on;
+// the plain ballot masks of the one-tile-per-warp kernels follow them
+__host__ __device__ inline int list_slot_words(int num_envs) { return 2 * ((((num_envs + 31) / 32 + 3) / 4) * 4); }
 __host__ __device__ inline int reset_list_scratch_words(int num_envs) {
-    return kListMaskBase + (((num_envs + 31) / 32 + 3) / 4) * 4;
+    return kListMaskBase + list_slot_words(num_envs) + (((num_envs + 31) / 32 + 3) / 4) * 4;
 }
 // ---- persistent kernels: one CTA scans the per-CTA counts ----------------------------------------------------
 // CTA c owns a contiguous, ascending range of envs, so its reset ids form one contiguous run of the output
@@ -409,10 +414,155 @@ __device__ __forceinline__ int list_emit_mask(const IgeResetList &L, int off, ui
     return off;
 }
 
+// ---- persistent kernels, scheme 3: tagged tile slots, one scanner CTA, no worker ever waits -------------------
+// Any cross-CTA hand-off costs L2 round trips (~0.7 us each on B200).  Schemes that make every CTA wait for a prefix
+// put three or four of them, chained, at the tail of a 5-8 us kernel.  Here the workers only STORE:
+//   worker, per 32-env tile:  list_publish_slot(): one 64-bit store {launch epoch + 1 : ballot of the entry flags}
+//     as soon as the tile's flags are in registers.  Fire and forget -- no ticket, no fence, no poll.
+//   scanner = one extra CTA (the last block index):  list_scanner_cta() polls the slots in tile order (the worker
+//     CTAs take tile = block + k * workers, so consecutive tiles are published at about the same time), scans the
+//     popcounts and writes the ascending ids itself; after the last slot it stores the count, opens the next epoch
+//     and advances the Philox step word.  The ids of a run of tiles are complete about one L2 round trip after its
+//     last slot was published, i.e. while the workers are still storing that tile's outputs.
+// Nobody waits for the scanner, so the grid needs no co-residency guarantee (the launchers still keep
+// workers + 1 <= resident CTAs so that the scanner starts with the kernel).  Epoch / step word: every worker CTA read
+// both before its first publish (the caller guarantees a CTA barrier in between), and the scanner advances them only
+// after it has seen every slot of this launch.
+__device__ __forceinline__ uint32_t list_epoch_tag(const IgeResetList &L) {
+    return (uint32_t)(*reinterpret_cast<const volatile uint64_t *>(L.scratch)) + 1u;
+}
+__device__ __forceinline__ void list_publish_slot(const IgeResetList &L, uint32_t tag, int tile, uint32_t mask) {
+    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(__cvta_generic_to_global(
+                     reinterpret_cast<uint64_t *>(L.scratch + kListMaskBase) + tile)), "l"(((uint64_t)tag << 32) | mask) : "memory");
+}
+// entry flag of env `e` as published by its owner (cross-CTA read of ENTRY flags without touching reset_buf, which
+// the owner may already have overwritten); spins until the owner's slot of this launch is there
+__device__ __forceinline__ bool list_slot_bit(const IgeResetList &L, uint32_t tag, int e) {
+    const volatile uint64_t *slots = reinterpret_cast<const volatile uint64_t *>(L.scratch + kListMaskBase);
+    uint64_t v;
+    do { v = slots[e >> 5]; } while ((uint32_t)(v >> 32) != tag);
+    return ((uint32_t)v >> (e & 31)) & 1u;
+}
+// The scanner works in UNITS of 256 consecutive tiles: lane l owns the 8 contiguous slots [8 l, 8 l + 8) (four 16-B
+// loads, all in flight), so ONE warp scan of the lane totals orders the whole unit.  Unit u belongs to warp
+// u % (T / 32): T / 32 units are polled concurrently (under load an L2 round trip is 1-3 us; a scanner with one unit
+// in flight falls behind the workers at 1M envs).  The running offset passes from unit to unit through one 64-bit
+// shared-memory word, BEFORE the unit's ids are written.  The code is kept SMALL on purpose: the scanner shares
+// its SM's instruction cache with five worker CTAs, and a long unrolled scan measured 11 us per unit in fetch
+// stalls alone.
+// Slot accesses are gpu-scope relaxed (volatile would be system-scope strong accesses through generic addressing).
+constexpr int kListUnitSlots = 8;                       // per lane
+constexpr int kListUnitTiles = 32 * kListUnitSlots;     // per unit
+__device__ __forceinline__ uint64_t ld_relaxed_gpu_u64(const uint64_t *p) {
+    uint64_t v;
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(__cvta_generic_to_global(p)) : "memory");
+    return v;
+}
+__device__ __forceinline__ void ld_relaxed_gpu_2xu64(const uint64_t *p, uint64_t &a, uint64_t &b) {
+    asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(a), "=l"(b) : "l"(__cvta_generic_to_global(p)) : "memory");
+}
+#ifdef IGE_SCAN_DEBUG
+// [0][0] = min worker start, [0][1] = max worker end, [0][2] = scanner start; [1 + u][..] per unit: poll start,
+// polls, all valid, chain passed, ids written, scanned, spun
+__device__ unsigned long long g_scan_dbg[80][8];
+__device__ __forceinline__ unsigned long long gtime() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
+#define SCAN_DBG(u, k, v) do { if ((threadIdx.x & 31) == 0 && (u) < 79) g_scan_dbg[1 + (u)][k] = (v); } while (0)
+#else
+#define SCAN_DBG(u, k, v) do { } while (0)
+#endif
+template <int T>
+static __device__ __noinline__ int list_scanner_cta(const IgeResetList L, const int num_tiles, uint64_t *step_word) {
+    constexpr int S = kListUnitSlots, W = T / 32;
+    __shared__ volatile unsigned long long s_chain;   // {units done : ids so far}
+    if (threadIdx.x == 0) s_chain = 0ull;
+    __syncthreads();
+#ifdef IGE_SCAN_DEBUG
+    if (threadIdx.x == 0) g_scan_dbg[0][2] = gtime();
+#endif
+#if !defined(IGE_EXP_SCAN_NOP)
+    // (the slot region is padded to a multiple of 4 tiles and zeroed once: slots past num_tiles are never valid, so
+    // they are not loaded)
+    const uint64_t *slots = reinterpret_cast<const uint64_t *>(L.scratch + kListMaskBase);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t tag = (uint32_t)ld_relaxed_gpu_u64(reinterpret_cast<const uint64_t *>(L.scratch)) + 1u;
+    const uint64_t done = (uint64_t)tag << 32;   // value of a slot with no reset (also stands in for slots past the end)
+    const int units = (num_tiles + kListUnitTiles - 1) / kListUnitTiles;
+#pragma unroll 1
+    for (int u = warp; u < units; u += W) {
+        const int lo = u * kListUnitTiles + lane * S;
+        uint64_t v[S];
+        int polls = 0;
+        (void)polls;
+        SCAN_DBG(u, 0, gtime());
+#pragma unroll
+        for (int i = 0; i < S; ++i) v[i] = (lo + i < num_tiles) ? 0ull : done;
+        for (;;) {   // (re-)load ALL stale pairs per spin: independent loads, one round trip per spin
+            bool ok = true;
+#pragma unroll
+            for (int i = 0; i < S; i += 2)
+                if ((uint32_t)(v[i] >> 32) != tag || (uint32_t)(v[i + 1] >> 32) != tag) {
+                    if (lo + i + 1 < num_tiles) ld_relaxed_gpu_2xu64(slots + lo + i, v[i], v[i + 1]);
+                    else v[i] = ld_relaxed_gpu_u64(slots + lo + i);   // odd tail (lo + i < num_tiles here)
+                    ok = false;
+                }
+            if (ok) break;
+            ++polls;
+        }
+        __syncwarp();
+        SCAN_DBG(u, 1, (unsigned long long)polls);
+        SCAN_DBG(u, 2, gtime());
+        int cnt = 0;
+#pragma unroll
+        for (int i = 0; i < S; ++i) cnt += __popc((uint32_t)v[i]);
+        int incl = cnt;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += t;
+        }
+        int run = 0;
+        SCAN_DBG(u, 5, gtime());
+        if (lane == 31) {   // incl == the unit's total.  Hand-off word: ONE 64-bit shared-memory word, so no fence
+            unsigned long long w;
+            do { w = s_chain; } while ((int)(w >> 32) != u);
+            SCAN_DBG(u, 6, gtime());
+            run = (int)(uint32_t)w;
+            s_chain = ((unsigned long long)(u + 1) << 32) | (uint32_t)(run + incl);
+            if (u == units - 1) {   // every slot of this launch has been seen
+                *L.count = run + incl;
+                *reinterpret_cast<volatile uint64_t *>(L.scratch) = tag;
+                if (step_word) *step_word += 1ull;
+            }
+        }
+        run = __shfl_sync(0xffffffffu, run, 31);
+        SCAN_DBG(u, 3, gtime());
+        int off = run + incl - cnt;
+        if (cnt > 0) {
+#pragma unroll
+            for (int i = 0; i < S; ++i) {
+                uint32_t m = (uint32_t)v[i];
+                const int e0 = (lo + i) * 32;
+#pragma unroll 1
+                while (m) {   // (not unrolled: the compiler's 4x unrolling of these 8 loops was 16 KB of code)
+                    L.ids[off++] = e0 + __ffs(m) - 1;
+                    m &= m - 1;
+                }
+            }
+        }
+        __syncwarp();
+        SCAN_DBG(u, 4, gtime());
+    }
+#else
+    if (threadIdx.x == 0) { *L.count = 0; *reinterpret_cast<volatile uint64_t *>(L.scratch) += 1; if (step_word) *step_word += 1ull; }
+#endif
+    __syncthreads();
+    return (int)(uint32_t)s_chain;   // number of ids (same value in every thread)
+}
+
 // One thread publishes the ballot mask of 32-env tile `tile` (bit i = env tile*32+i was reset).
 // No fence here: finish_reset_list() fences once per publishing thread.
-__device__ __forceinline__ void publish_tile_mask(const IgeResetList &L, int tile, uint32_t mask) {
-    L.scratch[kListMaskBase + tile] = mask;
+__device__ __forceinline__ void publish_tile_mask(const IgeResetList &L, int num_envs, int tile, uint32_t mask) {
+    L.scratch[kListMaskBase + list_slot_words(num_envs) + tile] = mask;
 }
 // finish_reset_list() is called by EVERY thread of EVERY CTA once, after the CTA's masks are published
 // (`i_published`: this thread wrote masks).  The CTA that arrives last expands all masks (blocked
@@ -424,7 +574,7 @@ static __device__ __noinline__ void expand_reset_list(const IgeResetList L, cons
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nthr = blockDim.x, nwarps = (nthr + 31) >> 5;
     __threadfence();
     const int tiles4 = ((num_envs + 31) / 32 + 3) / 4;
-    const uint4 *m4 = reinterpret_cast<const uint4 *>(L.scratch + kListMaskBase);
+    const uint4 *m4 = reinterpret_cast<const uint4 *>(L.scratch + kListMaskBase + list_slot_words(num_envs));
     const int per = (tiles4 + nthr - 1) / nthr;
     const int lo = min(tiles4, tid * per), hi = min(tiles4, lo + per);
     constexpr int B = 4;  // loads in flight per thread

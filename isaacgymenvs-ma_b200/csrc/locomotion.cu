@@ -41,6 +41,12 @@
 #ifndef IGE_ARG_PREFETCH
 #define IGE_ARG_PREFETCH 0
 #endif
+#ifndef IGE_EXP_NOCOMPUTE
+#define IGE_EXP_NOCOMPUTE 0
+#endif
+#ifndef IGE_EXP_NOREWARD
+#define IGE_EXP_NOREWARD 0
+#endif
 
 namespace {
 
@@ -497,41 +503,9 @@ template <int D, int NS, bool HUM, int NW_ELEM, int IN_STAGES>
 __global__ void __launch_bounds__(32 * (4 + NW_ELEM), HUM ? 3 : 6)  // shared memory allows 6 (Ant) / 3 (Humanoid) CTAs per SM
 locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p_in,
                             const __grid_constant__ IgeLocomotionBuffers b_in, const int num_tiles,
-                            const int tiles_per_cta) {
-#if IGE_STAGE_ARGS
-    // (experiment) kernel arguments staged into shared memory once; later accesses are LDS instead of constant-bank
-    // operands
-    __shared__ __align__(16) IgeLocomotionParams p;
-    __shared__ __align__(16) IgeLocomotionBuffers b;
-    {
-        static_assert(sizeof(IgeLocomotionParams) % 8 == 0 && sizeof(IgeLocomotionBuffers) % 8 == 0, "argument structs copy as 8-B words");
-        constexpr int WP = sizeof(IgeLocomotionParams) / 8, WB = sizeof(IgeLocomotionBuffers) / 8;
-        const uint64_t *sp = reinterpret_cast<const uint64_t *>(&p_in), *sb = reinterpret_cast<const uint64_t *>(&b_in);
-        for (int w = threadIdx.x; w < WP + WB; w += blockDim.x) {
-            if (w < WB) reinterpret_cast<uint64_t *>(&b)[w] = sb[w];          // the pointers first: the tile loads need them
-            else reinterpret_cast<uint64_t *>(&p)[w - WB] = sp[w - WB];
-        }
-    }
-#else
+                            const int workers) {
     const IgeLocomotionParams &p = p_in;
     const IgeLocomotionBuffers &b = b_in;
-#endif
-#if IGE_ARG_PREFETCH
-    // Kernel arguments live in the constant bank.  At 16 k envs every CTA processes ONE tile, so every first touch
-    // of a 64-B argument line is a cold constant-cache miss inside some role's dependent chain.  Touch every line
-    // now, with independent loads whose misses overlap (and hide behind the mbarrier set-up / first tile load).
-    {
-        constexpr int LINES = (sizeof(IgeLocomotionParams) + sizeof(IgeLocomotionBuffers) + 63) / 64;
-        const uint32_t *a = reinterpret_cast<const uint32_t *>(&p_in);
-        uint32_t acc = 0;
-#pragma unroll
-        for (int l = 0; l < LINES; ++l) acc ^= a[l * 16 < (int)(sizeof(IgeLocomotionParams) / 4) ? l * 16 : 0];
-        const uint32_t *a2 = reinterpret_cast<const uint32_t *>(&b_in);
-#pragma unroll
-        for (int l = 0; l < (int)(sizeof(IgeLocomotionBuffers) + 63) / 64; ++l) acc ^= a2[l * 16];
-        if (acc == 0x9e3779b9u && num_tiles < 0) asm volatile("trap;");   // keeps the loads alive; never true
-    }
-#endif
     using L = Layout<D, NS, HUM>;
     constexpr int NUM_OBS = L::NUM_OBS;
     constexpr int NW = 4 + NW_ELEM;
@@ -550,10 +524,18 @@ locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p_in,
     Handoff<D> *hand = reinterpret_cast<Handoff<D> *>(stage + 2);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int role = (warp + (int)blockIdx.x) % NW;
-    // blocked assignment: CTA c owns the contiguous tiles [c*K, c*K + my_tiles) -- its reset ids are then
-    // one contiguous run of the output list
-    const int first = blockIdx.x * tiles_per_cta;
-    const int my_tiles = min(tiles_per_cta, num_tiles - first);
+    // Reset index list: the workers only publish their tiles' entry-flag ballots; the extra last CTA turns them
+    // into the ascending id list (ige::list_scanner_cta) -- no worker ever waits for another CTA.
+    if ((int)blockIdx.x >= workers) {
+        ige::list_scanner_cta<32 * NW>(b_in.list, num_tiles, p_in.rand.step);
+        return;
+    }
+#ifdef IGE_SCAN_DEBUG
+    if (threadIdx.x == 0) atomicMin(&ige::g_scan_dbg[0][0], ige::gtime());
+#endif
+    // strided assignment: worker c owns tiles c, c + workers, ... -- the slots of one scanner round are published
+    // at about the same time
+    const int my_tiles = (num_tiles - (int)blockIdx.x + workers - 1) / workers;
 
     CLK(kstart);
     // Philox step word: read by ONE thread and handed over through shared memory, so the load has completed
@@ -568,12 +550,9 @@ locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p_in,
     }
     __syncthreads();   // staged arguments, step word and mbarriers are visible
     const uint64_t step = s_step;
-    // reset ballots of my tiles: the mask words of the list scratch (global; written and read back by the
-    // REWARD warp only, so they need no shared memory)
-    uint32_t *tile_masks = b.list.scratch ? b.list.scratch + ige::kListMaskBase + blockIdx.x * tiles_per_cta : nullptr;
     const bool clamp_copy = b.obs_clamped != nullptr && p.clip_obs < INFINITY;
     const bool second_obs_copy = b.obs_clamped != nullptr && !clamp_copy;
-    auto tile_e0 = [&](int it) { return (first + it) * TE; };
+    auto tile_e0 = [&](int it) { return ((int)blockIdx.x + it * workers) * TE; };
     auto tile_ne = [&](int it) { return min(TE, p.num_envs - tile_e0(it)); };
     // prologue: the first IN_STAGES tiles
     if (lane == 0 && role != REWARD)
@@ -588,28 +567,16 @@ locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p_in,
             n_reset = b.reset_buf[e]; n_progress = b.progress_buf[e];
             if (b.randomize_buf) n_rand = b.randomize_buf[e];
         }
-        // ---- reset index list (while the role warps work on the first tile): count my resets and publish the
-        //      count; the CTA that publishes last scans all counts (ige::list_cta_publish) ----
+        // reset index list: tile 0's ballot goes out as soon as its flags are here, tile it + 1's at the end of
+        // iteration it (its flags were prefetched at the top of the iteration)
         const bool emit = b.list.scratch != nullptr;
-        ige::ListTag ltag{0, 0};
+        uint32_t ltag = 0u;
         if (emit) {
-            int cnt = 0;
-            constexpr int PB = 8;            // flag loads in flight
-            for (int it0 = 0; it0 < my_tiles; it0 += PB) {
-                long long f[PB];
-#pragma unroll
-                for (int k = 0; k < PB; ++k) {
-                    const int e = tile_e0(it0 + k) + lane;
-                    f[k] = (it0 + k < my_tiles && e < p.num_envs) ? b.reset_buf[e] : 0;
-                }
-#pragma unroll
-                for (int k = 0; k < PB; ++k) cnt += __popc(__ballot_sync(0xffffffffu, f[k] != 0));
-            }
-            ltag = ige::list_cta_publish(b.list, cnt);
-            ige::list_cta_scan(b.list, ltag, p.rand.step);   // (this warp is idle until the first tile is produced)
+            ltag = ige::list_epoch_tag(b.list);
+            const uint32_t mask = __ballot_sync(0xffffffffu, n_reset != 0);
+            if (lane == 0) ige::list_publish_slot(b.list, ltag, tile_e0(0) / TE, mask);
         }
         StatAcc st;
-        uint32_t reg_mask = 0u;  // lane t: reset ballot of my tile t (t < 32)
         long long k_work = 0, k_bar = 0;
         (void)k_work; (void)k_bar;
         CLK(rp);
@@ -621,11 +588,6 @@ locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p_in,
                 if (b.randomize_buf) n_rand = b.randomize_buf[e];
             } else {
                 n_reset = 0;  // lanes past the end of a partial tile must not leak stale flags
-            }
-            if (emit) {
-                const uint32_t mask = __ballot_sync(0xffffffffu, reset != 0);
-                if (it < 32) { if (lane == it) reg_mask = mask; }  // the first 32 ballots never leave the warp
-                else if (lane == 0) tile_masks[it] = mask;
             }
             CLK(r0);
             __syncthreads();  // barrier #it: the role warps have produced tile `it`
@@ -641,32 +603,22 @@ locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p_in,
                 atomicAdd(&g_role_clk[5][7], (unsigned long long)(last > r0 ? last - r0 : 0));       // REWARD idle before the barrier
             }
 #endif
+#if !IGE_EXP_NOREWARD
             if (lane < tile_ne(it))
                 role_reward<D, NS, HUM>(p, b, out[it & 1].obs + lane * NUM_OBS, hand[it & 1], lane, tile_e0(it) + lane,
                                     reset, progress, randomize, st);
+#else
+            if (lane < tile_ne(it)) { b.rew_buf[tile_e0(it) + lane] = (float)(reset + progress + randomize); }
+#endif
+            if (emit && it + 1 < my_tiles) {
+                const uint32_t mask = __ballot_sync(0xffffffffu, n_reset != 0);
+                if (lane == 0) ige::list_publish_slot(b.list, ltag, tile_e0(it + 1) / TE, mask);
+            }
             CLK(r2);
             CLK_ADD(k_bar, r0, r1); CLK_ADD(k_work, r1, r2);
         }
         CLK(r3);
         if (b.stats) flush_stats(b.stats, st);
-        // ---- reset index list, part 2: the ascending ids of my tiles, from my prefix slot on (written long ago) ----
-        if (emit) {
-            int sum = ige::list_cta_prefix_wait(b.list, ltag);
-            // lane l expands tiles l, l + 32, ...: exclusive scan of the tile counts, then the set bits
-            for (int t0 = 0; t0 < my_tiles; t0 += 32) {
-                const int t = t0 + lane;
-                uint32_t m = t >= my_tiles ? 0u : (t0 == 0 ? reg_mask : __ldcg(tile_masks + t));
-                const int c = __popc(m);
-                int incl = c;
-#pragma unroll
-                for (int o = 1; o < 32; o <<= 1) {
-                    const int u = __shfl_up_sync(0xffffffffu, incl, o);
-                    if (lane >= o) incl += u;
-                }
-                ige::list_emit_mask(b.list, sum + incl - c, m, tile_e0(t));
-                sum += __shfl_sync(0xffffffffu, incl, 31);
-            }
-        }
         CLK(r4);
         CLK_FLUSH(REWARD, 1, k_work); CLK_FLUSH(REWARD, 2, k_bar); CLK_FLUSH(REWARD, 3, r4 - r3);
         CLK_FLUSH(REWARD, 0, rp - kstart); CLK_FLUSH(REWARD, 4, r4 - kstart); CLK_FLUSH(REWARD, 7, my_tiles);
@@ -705,6 +657,7 @@ locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p_in,
             CLK(c1);
             float *obs_row = out[o].obs + lane * NUM_OBS;
             const float *root = in[s].root + lane * 13;
+#if !IGE_EXP_NOCOMPUTE   // (timing experiment: the data-movement skeleton alone)
             if (role == HEADING) {
                 if (lane < ne)
                     role_heading<D, NUM_OBS>(p, root, was_reset, stage[o].xy[lane * 2], stage[o].xy[lane * 2 + 1], pot_in,
@@ -717,6 +670,10 @@ locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p_in,
                 role_elem<D, NS, HUM, NW_ELEM>(p, b, in[s], out[o].obs, hand[o], elem, ne, e0, step, m_cur, stage[o].pos);
             }
             if (role < REWARD) stream_columns<D, NS, HUM>(p, in[s], out[o].obs, role, 3, lane, ne);
+#else
+            hout.prev = hout.pot = root[0]; hout.up[0] = hout.up[1] = hout.up[2] = hout.hd[0] = hout.hd[1] = hout.hd[2] = pot_in;
+            (void)obs_row; (void)was_reset;
+#endif
             ige::fence_proxy_async();  // obs tile -> visible to the bulk-store (async) proxy
             // out[o ^ 1] is rewritten right after this barrier: its store (tile it - 1, issued by this
             // same thread one iteration ago) must have finished reading shared memory
@@ -756,6 +713,9 @@ locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p_in,
         CLK_FLUSH(min(role, 4), 3, c5 - c4); CLK_FLUSH(min(role, 4), 7, my_tiles);
         CLK_FLUSH(min(role, 4), 4, k_issue); CLK_FLUSH(min(role, 4), 5, c5 - cbeg); CLK_FLUSH(min(role, 4), 6, cbeg - kstart);
     }
+#ifdef IGE_SCAN_DEBUG
+    if ((threadIdx.x & 31) == 0) atomicMax(&ige::g_scan_dbg[0][1], ige::gtime());
+#endif
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -824,7 +784,7 @@ locomotion_tile_kernel(const __grid_constant__ IgeLocomotionParams p, const __gr
     if (role == REWARD) {
         if (b.list.scratch && emit_mode == EMIT_MASKS) {  // sole kernel of the step: masks, expanded below
             const uint32_t mask = __ballot_sync(0xffffffffu, reset != 0);
-            if (lane == 0) ige::publish_tile_mask(b.list, blockIdx.x + tile_offset, mask);
+            if (lane == 0) ige::publish_tile_mask(b.list, p.num_envs, blockIdx.x + tile_offset, mask);
         }
         if (b.list.scratch && emit_mode == EMIT_APPEND) {  // the one ragged tile after the pipelined kernel
             const uint32_t mask = __ballot_sync(0xffffffffu, reset != 0);
@@ -892,19 +852,21 @@ int launch(const IgeLocomotionParams *p, const IgeLocomotionBuffers *b, cudaStre
                             (sizeof(uint64_t) * IN_STAGES + 15) / 16 * 16 + sizeof(ResetStage<D>) * 2 +
                             sizeof(Handoff<D>) * 2;
     auto kern = locomotion_pipelined_kernel<D, NS, HUM, NW_ELEM, IN_STAGES>;
-    static int max_ctas = 0;  // resident CTAs on the current device (per template instance)
-    if (max_ctas == 0) {
+    static int cap[IGE_MAX_DEVICES];  // resident CTAs per device (per template instance)
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= IGE_MAX_DEVICES) return ige_fail(IGE_EPARAM, "%s: device ordinal %d not supported", name, dev);
+    if (cap[dev] == 0) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return ige_fail((int)e, "%s: cudaFuncSetAttribute(smem=%zu): %s", name, smem, cudaGetErrorString(e));
-        int dev = 0, sms = 0, per_sm = 0;
-        cudaGetDevice(&dev);
+        int sms = 0, per_sm = 0;
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
         e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, NT, smem);
         if (e != cudaSuccess || per_sm < 1 || sms < 1)
             return ige_fail(e != cudaSuccess ? (int)e : IGE_EPARAM, "%s: occupancy query failed", name);
-        max_ctas = sms * per_sm;
-        if (max_ctas > ige::kListMaxCtas) max_ctas = ige::kListMaxCtas;
+        cap[dev] = sms * per_sm;
     }
+    const int max_ctas = cap[dev];
     const int n = p->num_envs;
     const int full_tiles = n / TE, rem = n % TE;
     const bool tma = use_tma() != 0;
@@ -917,9 +879,11 @@ int launch(const IgeLocomotionParams *p, const IgeLocomotionBuffers *b, cudaStre
         fallback_tiles = full_tiles + (rem > 0 ? 1 : 0);
     }
     if (pipelined_tiles > 0) {
-        const int per_cta = (pipelined_tiles + max_ctas - 1) / max_ctas;   // contiguous tiles per CTA
-        const int grid = (pipelined_tiles + per_cta - 1) / per_cta;        // <= max_ctas: all CTAs co-resident
-        kern<<<grid, NT, smem, stream>>>(*p, *b, pipelined_tiles, per_cta);
+        // workers (+ the scanner CTA of the reset list) <= resident CTAs, balanced tile counts
+        const int scanner = b->list.scratch ? 1 : 0;
+        const int per_cta = (pipelined_tiles + (max_ctas - scanner) - 1) / (max_ctas - scanner);
+        const int workers = (pipelined_tiles + per_cta - 1) / per_cta;
+        kern<<<workers + scanner, NT, smem, stream>>>(*p, *b, pipelined_tiles, workers);
         if (int rc = ige_check_launch(name)) return rc;
     }
     if (fallback_tiles > 0) {  // TMA mode: at most the one ragged tile, whose ids come last -> append
@@ -937,6 +901,20 @@ extern "C" int ige_debug_role_clocks(unsigned long long *out, int reset) {
     cudaDeviceSynchronize();
     if (out) cudaMemcpyFromSymbol(out, g_role_clk, sizeof(unsigned long long) * 64);
     if (reset) { unsigned long long z[64] = {0}; cudaMemcpyToSymbol(g_role_clk, z, sizeof(z)); }
+    return 0;
+}
+#endif
+
+#ifdef IGE_SCAN_DEBUG
+extern "C" int ige_debug_scan(unsigned long long *out, int reset) {
+    cudaDeviceSynchronize();
+    if (out) cudaMemcpyFromSymbol(out, ige::g_scan_dbg, sizeof(unsigned long long) * 80 * 8);
+    if (reset) {
+        static unsigned long long z[80 * 8];
+        for (int i = 0; i < 80 * 8; ++i) z[i] = 0;
+        z[0] = ~0ull;
+        cudaMemcpyToSymbol(ige::g_scan_dbg, z, sizeof(z));
+    }
     return 0;
 }
 #endif

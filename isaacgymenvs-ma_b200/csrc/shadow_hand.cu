@@ -175,7 +175,7 @@ __global__ void __launch_bounds__(128) shadow_hand_reset_kernel(const __grid_con
         hand_reset_env_coop(p, b, step, e - lane + src, __shfl_sync(0xffffffffu, rk, src), lane, s_u[threadIdx.x >> 5]);
     }
     if (b.list.scratch) {  // reset list == reset_buf.nonzero() at entry
-        if (lane == 0 && e < p.num_envs) ige::publish_tile_mask(b.list, e >> 5, mask);
+        if (lane == 0 && e < p.num_envs) ige::publish_tile_mask(b.list, p.num_envs, e >> 5, mask);
         ige::finish_reset_list(b.list, p.num_envs, nullptr, lane == 0);
     }
 }

@@ -14,12 +14,17 @@ _SIM_TENSORS = {
     "ShadowHand": ["dof_state", "root_state_tensor", "rigid_body_states", "vec_sensor_tensor", "dof_force_tensor"],
 }
 _SIM_TENSORS["Anymal"] = ["root_states", "dof_state", "contact_forces", "torques"]
+_SIM_TENSORS.update({"BallBalance": ["root_states", "dof_states", "sensor_tensor"], "Quadcopter": ["root_states", "dof_states"],
+                     "Ingenuity": ["root_tensor", "dof_states"]})
 _MA_TASKS = {"FrankaReachMA": "reach", "FrankaCollectMA": "collect", "FrankaCombineMA": "combine", "FrankaPPMA": "pp"}
 for _t in _MA_TASKS:
     _SIM_TENSORS[_t] = ["_rigid_body_state", "_root_state", "_dof_state", "_contact_forces"]
 _CFGS = {"Cartpole": synthetic.CARTPOLE_CFG, "Ant": synthetic.ANT_CFG, "Humanoid": synthetic.HUMANOID_CFG,
-         "ShadowHand": synthetic.SHADOW_HAND_CFG, "Anymal": synthetic.ANYMAL_CFG}
-_SYN_NAME = {"Cartpole": "cartpole", "Ant": "ant", "Humanoid": "humanoid", "ShadowHand": "shadow_hand", "Anymal": "anymal"}
+         "ShadowHand": synthetic.SHADOW_HAND_CFG, "Anymal": synthetic.ANYMAL_CFG,
+         "BallBalance": synthetic.BALL_BALANCE_CFG, "Quadcopter": synthetic.QUADCOPTER_CFG,
+         "Ingenuity": synthetic.INGENUITY_CFG}
+_SYN_NAME = {"Cartpole": "cartpole", "Ant": "ant", "Humanoid": "humanoid", "ShadowHand": "shadow_hand", "Anymal": "anymal",
+             "BallBalance": "ball_balance", "Quadcopter": "quadcopter", "Ingenuity": "ingenuity"}
 for _t, _v in _MA_TASKS.items():
     _SYN_NAME[_t] = "franka_" + _v
 

@@ -254,9 +254,112 @@ def advance_anymal(st, g):
     st["actions"] = g.uniform(-1.5, 1.5, st["actions"].shape).astype(np.float32)
 
 
-MAKERS = {"cartpole": make_cartpole, "ant": make_ant, "humanoid": make_humanoid, "anymal": make_anymal}
+# ---------------------------------------------------------------------------------------------
+# BallBalance / Quadcopter / Ingenuity (reference: tasks/ball_balance.py, quadcopter.py, ingenuity.py and their
+# cfg/task/*.yaml) -- SURVEY.md 8f row 2.  These reset in PRE-physics position: a state holds what
+# pre_physics_step reads (flags, targets, thrusts) and the post-simulate tensors post_physics_step reads.
+# ---------------------------------------------------------------------------------------------
+BALL_BALANCE_CFG = dict(num_obs=24, num_actions=3, dt=0.01, action_speed_scale=20, max_episode_length=500,
+                        clip_obs=5.0, clip_actions=1.0, ball_radius=0.1,
+                        # generated MJCF (ball_balance.py:195-214): upper leg -45..45 deg, lower leg -70..90 deg
+                        dof_lower=[-45 * _DEG, -70 * _DEG] * 3, dof_upper=[45 * _DEG, 90 * _DEG] * 3)
+QUADCOPTER_CFG = dict(num_obs=21, num_actions=12, dt=0.01, max_episode_length=500, clip_obs=5.0, clip_actions=1.0,
+                      num_bodies=9, rotor_bodies=[2, 4, 6, 8], max_thrust=2.0,
+                      dof_lower=[-30 * _DEG] * 8, dof_upper=[30 * _DEG] * 8)      # quadcopter.py:180,199
+INGENUITY_CFG = dict(num_obs=13, num_actions=6, dt=0.01, max_episode_length=2000, clip_obs=5.0, clip_actions=1.0,
+                     num_bodies=6, thrust_upper_limit=2000.0, thrust_lateral_component=0.2)   # ingenuity.py:90-92
+
+
+def _root_rows(g, n, pos_scale, z_lo, z_hi):
+    root = np.zeros((n, 13), F32)
+    root[:, 0:2] = pos_scale * g.standard_normal((n, 2))
+    root[:, 2] = g.uniform(z_lo, z_hi, n)
+    root[:, 3:7] = _unit_quats(g, n)
+    root[:, 7:13] = g.standard_normal((n, 6))
+    return root.astype(F32)
+
+
+def make_ball_balance(num_envs, seed=0, reset_prob=0.02, fall_frac=None):
+    n, g, cfg = num_envs, _rng(seed), BALL_BALANCE_CFG
+    root = np.zeros((n, 2, 13), F32)
+    root[:, 0, 2], root[:, 0, 6] = 0.62, 1.0                                        # tray pose
+    root[:, 1] = _root_rows(g, n, 0.3, 0.05 if fall_frac is None else 0.2 - 0.5 * fall_frac, 2.0)
+    init_root = root.copy()
+    init_root[:, 1] = _root_rows(g, n, 0.1, 0.9, 1.1)
+    dof = (g.standard_normal((n, 6, 2)) * np.array([0.4, 2.0])).astype(F32)
+    lo, hi = np.array(cfg["dof_lower"]), np.array(cfg["dof_upper"])
+    return {
+        "root_states": root, "dof_states": dof, "sensor_tensor": (30.0 * g.standard_normal((n, 3, 6))).astype(F32),
+        "initial_root_states": init_root, "initial_dof_states": (0.05 * g.standard_normal((n, 6, 2))).astype(F32),
+        "dof_position_targets": g.uniform(1.2 * lo, 1.2 * hi, (n, 6)).astype(F32),   # some beyond the limits
+        "actions": g.uniform(-1.5, 1.5, (n, 3)).astype(F32),
+        "reset_buf": _resets(g, n, reset_prob), "progress_buf": _progress(g, n, cfg["max_episode_length"]),
+    }
+
+
+def advance_ball_balance(st, g):
+    n = st["reset_buf"].shape[0]
+    st["root_states"][:, 1] = _root_rows(g, n, 0.3, 0.05, 2.0)
+    st["dof_states"] = (st["dof_states"] + 0.1 * g.standard_normal(st["dof_states"].shape)).astype(F32)
+    st["sensor_tensor"] = (30.0 * g.standard_normal(st["sensor_tensor"].shape)).astype(F32)
+    st["actions"] = g.uniform(-1.5, 1.5, st["actions"].shape).astype(F32)
+
+
+def make_quadcopter(num_envs, seed=0, reset_prob=0.02, fall_frac=None):
+    n, g, cfg = num_envs, _rng(seed), QUADCOPTER_CFG
+    init_root = np.zeros((n, 13), F32)
+    init_root[:, 2], init_root[:, 6] = 1.0, 1.0
+    forces = np.zeros((n, cfg["num_bodies"], 3), F32)
+    forces[:, cfg["rotor_bodies"], 2] = g.uniform(0, 2, (n, 4))
+    return {
+        "root_states": _root_rows(g, n, 1.2, 0.1, 2.5), "dof_states": (g.standard_normal((n, 8, 2)) * np.array([0.3, 2.0])).astype(F32),
+        "initial_root_states": init_root, "initial_dof_states": np.zeros((n, 8, 2), F32),
+        "dof_position_targets": g.uniform(-0.7, 0.7, (n, 8)).astype(F32), "thrusts": g.uniform(-0.2, 2.2, (n, 4)).astype(F32),
+        "forces": forces, "actions": g.uniform(-1.5, 1.5, (n, 12)).astype(F32),
+        "reset_buf": _resets(g, n, reset_prob), "progress_buf": _progress(g, n, cfg["max_episode_length"]),
+    }
+
+
+def advance_quadcopter(st, g):
+    n = st["reset_buf"].shape[0]
+    st["root_states"] = _root_rows(g, n, 1.2, 0.1, 2.5)
+    st["dof_states"] = (st["dof_states"] + 0.1 * g.standard_normal(st["dof_states"].shape)).astype(F32)
+    st["actions"] = g.uniform(-1.5, 1.5, st["actions"].shape).astype(F32)
+
+
+def make_ingenuity(num_envs, seed=0, reset_prob=0.02, fall_frac=None):
+    n, g, cfg = num_envs, _rng(seed), INGENUITY_CFG
+    root = np.zeros((n, 2, 13), F32)
+    root[:, 0] = _root_rows(g, n, 3.0, 0.2, 3.0)
+    root[:, 1, 6] = 1.0
+    tgt = np.concatenate([g.uniform(-5, 5, (n, 2)), g.uniform(1, 2, (n, 1))], 1).astype(F32)
+    root[:, 1, 0:3] = tgt + np.array([0, 0, 0.4], F32)
+    init_root = np.zeros((n, 13), F32)
+    init_root[:, 2], init_root[:, 6] = 1.0, 1.0
+    progress = _progress(g, n, cfg["max_episode_length"])
+    retarget = g.random(n) < 0.05
+    progress[retarget] = 500 * g.integers(0, 4, int(retarget.sum()))             # progress % 500 == 0 rows (ingenuity.py:325)
+    return {
+        "root_tensor": root, "dof_states": (g.standard_normal((n, 4, 2)) * np.array([0.3, 30.0])).astype(F32),
+        "initial_root_states": init_root, "target_root_positions": tgt,
+        "thrusts": g.standard_normal((n, 2, 3)).astype(F32), "forces": g.standard_normal((n, cfg["num_bodies"], 3)).astype(F32),
+        "actions": g.uniform(-1.5, 1.5, (n, 6)).astype(F32),
+        "reset_buf": _resets(g, n, reset_prob), "progress_buf": progress,
+    }
+
+
+def advance_ingenuity(st, g):
+    n = st["reset_buf"].shape[0]
+    st["root_tensor"][:, 0] = _root_rows(g, n, 3.0, 0.2, 3.0)
+    st["dof_states"] = (st["dof_states"] + 0.1 * g.standard_normal(st["dof_states"].shape)).astype(F32)
+    st["actions"] = g.uniform(-1.5, 1.5, st["actions"].shape).astype(F32)
+
+
+MAKERS = {"cartpole": make_cartpole, "ant": make_ant, "humanoid": make_humanoid, "anymal": make_anymal,
+          "ball_balance": make_ball_balance, "quadcopter": make_quadcopter, "ingenuity": make_ingenuity}
 ADVANCERS = {"cartpole": advance_cartpole, "ant": advance_ant, "humanoid": advance_humanoid,
-             "anymal": advance_anymal}
+             "anymal": advance_anymal, "ball_balance": advance_ball_balance, "quadcopter": advance_quadcopter,
+             "ingenuity": advance_ingenuity}
 
 
 def make_state(task, num_envs, seed=0, reset_prob=0.02, **kw):

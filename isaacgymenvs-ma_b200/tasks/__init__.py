@@ -10,8 +10,10 @@ from .cartpole import Cartpole  # noqa: F401
 from .locomotion import Ant, Humanoid  # noqa: F401
 from .shadow_hand import ShadowHand  # noqa: F401
 from .anymal import Anymal  # noqa: F401
+from .small import BallBalance, Ingenuity, Quadcopter  # noqa: F401
 from .franka_ma import FrankaCollectMA, FrankaCombineMA, FrankaPPMA, FrankaReachMA  # noqa: F401
 
 task_map = {"Cartpole": Cartpole, "Ant": Ant, "Humanoid": Humanoid, "ShadowHand": ShadowHand,
             "FrankaReachMA": FrankaReachMA, "FrankaCollectMA": FrankaCollectMA, "FrankaCombineMA": FrankaCombineMA,
-            "FrankaPPMA": FrankaPPMA, "Anymal": Anymal}
+            "FrankaPPMA": FrankaPPMA, "Anymal": Anymal, "BallBalance": BallBalance, "Quadcopter": Quadcopter,
+            "Ingenuity": Ingenuity}

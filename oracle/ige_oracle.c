@@ -1321,3 +1321,264 @@ int ige_oracle_anymal_post_physics(const IgeAnymalParams *p, const IgeAnymalBuff
     if (p->rand_mode == IGE_RAND_PHILOX && p->step) *p->step += 1;
     return 0;
 }
+
+/* ------------------------------------------------------------------------------------------
+ * Remaining single-agent tasks: BallBalance, Quadcopter, Ingenuity.
+ * These reset in PRE-physics position, so each has a pre_physics and a post_physics restatement.
+ * ------------------------------------------------------------------------------------------ */
+static float task_uniform(const IgeTaskRand *r, const int32_t *rank, int draw, int env, int cols, int j) {
+    if (r->mode == IGE_RAND_PHILOX) {
+        IgeResetRand rr;
+        memset(&rr, 0, sizeof(rr));
+        rr.seed = r->seed; rr.step = r->step;
+        return philox_uniform(&rr, (uint32_t)env, (uint32_t)draw, (uint32_t)j);
+    }
+    return r->u[draw][(size_t)rank[env] * cols + j];
+}
+static void task_list(const IgeResetList *l, const IgeTaskRand *r, const int64_t *reset_buf, int n) {
+    emit_reset_list(l, reset_buf, n, 1);
+}
+static void task_advance(const IgeResetList *l, const IgeTaskRand *r) {
+    if (l->scratch && r->step) *r->step += 1;
+}
+static inline float tensor_clamp1(float t, float lo, float hi) { return fmaxf(fminf(t, hi), lo); } /* utils/torch_jit_utils.py:228-230 */
+static inline float clamp_obs1(float x, float c) { return fminf(fmaxf(x, -c), c); }
+
+/* tasks/ball_balance.py:410-430 pre_physics_step (+ reset_idx :360-408) */
+int ige_oracle_ball_balance_pre_physics(const IgeBallBalanceArgs *a) {
+    const int n = a->num_envs;
+    task_list(&a->list, &a->rand, a->reset_buf, n);
+    for (int e = 0; e < n; ++e) {
+        const int flagged = a->reset_buf[e] != 0;
+        float *tg = a->dof_position_targets + (size_t)e * 6;
+        if (flagged) {
+            float *root = a->root_states + (size_t)e * 26, *ball = root + 13;
+            memcpy(root, a->initial_root_states + (size_t)e * 26, 26 * sizeof(float));              /* :364 */
+            const float dists = rand_float(0.001, 0.5, task_uniform(&a->rand, a->rand.rank, 0, e, 1, 0));   /* :373 */
+            const float angle = rand_float(-M_PI, M_PI, task_uniform(&a->rand, a->rand.rank, 1, e, 1, 0)); /* :374, torch_jit_utils.py:222-225 */
+            const float dc = cosf(angle), ds = sinf(angle);
+            const float hx = dists * dc, hy = dists * ds;                                            /* :375 */
+            const float speedscales = (dists - 0.001f) / (float)(0.5 - 0.001);                       /* :377 */
+            const float hspeeds = rand_float(0.0, 5.0, task_uniform(&a->rand, a->rand.rank, 2, e, 1, 0));   /* :378 */
+            const float hs = -speedscales * hspeeds;                                                 /* :379 */
+            const float vspeed = -rand_float(5.0, 5.0, task_uniform(&a->rand, a->rand.rank, 3, e, 1, 0));   /* :380 */
+            const float height = rand_float(1.0, 2.0, task_uniform(&a->rand, a->rand.rank, 4, e, 1, 0));    /* :383 */
+            ball[0] = hx; ball[1] = hy; ball[2] = height;
+            ball[3] = 0.f; ball[4] = 0.f; ball[5] = 0.f; ball[6] = 1.f;                              /* :385-386 */
+            ball[7] = hs * dc; ball[8] = hs * ds; ball[9] = vspeed;
+            ball[10] = ball[11] = ball[12] = 0.f;                                                    /* :390 */
+            memcpy(a->dof_states + (size_t)e * 12, a->initial_dof_states + (size_t)e * 12, 12 * sizeof(float)); /* :398 */
+            a->reset_buf[e] = 0;
+            a->progress_buf[e] = 0;
+        }
+        for (int k = 0; k < 3; ++k) tg[2 * k + 1] += a->target_step * a->actions[(size_t)e * 3 + k];  /* :421 */
+        for (int j = 0; j < 6; ++j) {
+            tg[j] = tensor_clamp1(tg[j], a->dof_lower[j], a->dof_upper[j]);                          /* :422 */
+            if (flagged) tg[j] = 0.0f;                                                               /* :425 */
+        }
+    }
+    task_advance(&a->list, &a->rand);
+    return 0;
+}
+
+/* tasks/ball_balance.py:432-441 post_physics_step; compute_observations :336-349; compute_bbot_reward :460-476 */
+int ige_oracle_ball_balance_post_physics(const IgeBallBalanceArgs *a) {
+    for (int e = 0; e < a->num_envs; ++e) {
+        const int64_t progress = a->progress_buf[e] + 1;
+        const float *dof = a->dof_states + (size_t)e * 12, *ball = a->root_states + (size_t)e * 26 + 13;
+        const float *sens = a->sensor_tensor + (size_t)e * 18;
+        float *obs = a->obs_buf + (size_t)e * 24;
+        for (int k = 0; k < 3; ++k) {
+            obs[k] = dof[2 * (2 * k + 1)];
+            obs[3 + k] = dof[2 * (2 * k + 1) + 1];
+            obs[6 + k] = ball[k];
+            obs[9 + k] = ball[7 + k];
+            obs[12 + k] = sens[6 * k] / 20.0f;
+            obs[15 + k] = sens[6 * k + 3] / 20.0f;
+            obs[18 + k] = sens[6 * k + 4] / 20.0f;
+            obs[21 + k] = sens[6 * k + 5] / 20.0f;
+        }
+        if (a->obs_clamped)
+            for (int i = 0; i < 24; ++i) a->obs_clamped[(size_t)e * 24 + i] = clamp_obs1(obs[i], a->clip_obs);
+        const float zz = ball[2] - 0.7f;
+        const float ball_dist = sqrtf((ball[0] * ball[0] + zz * zz) + ball[1] * ball[1]);
+        const float ball_speed = sqrtf((ball[7] * ball[7] + ball[8] * ball[8]) + ball[9] * ball[9]);
+        const float pos_reward = 1.0f / (1.0f + ball_dist), speed_reward = 1.0f / (1.0f + ball_speed);
+        int64_t reset = a->reset_buf[e];
+        const int late = (float)progress >= a->max_episode_length - 1.0f;
+        if (late) reset = 1;
+        if (ball[2] < (float)((double)a->ball_radius * 1.5)) reset = 1;
+        a->rew_buf[e] = pos_reward * speed_reward;
+        a->reset_buf[e] = reset;
+        a->progress_buf[e] = progress;
+        if (a->timeout_buf) a->timeout_buf[e] = (late && reset != 0) ? 1 : 0;                       /* vec_task.py:396 */
+    }
+    return 0;
+}
+
+/* tasks/quadcopter.py:301-331 pre_physics_step (+ reset_idx :280-299) */
+int ige_oracle_quadcopter_pre_physics(const IgeQuadcopterArgs *a) {
+    const int n = a->num_envs, nb = a->num_bodies;
+    task_list(&a->list, &a->rand, a->reset_buf, n);
+    for (int e = 0; e < n; ++e) {
+        const int flagged = a->reset_buf[e] != 0;
+        float *tg = a->dof_position_targets + (size_t)e * 8, *th = a->thrusts + (size_t)e * 4;
+        float *f = a->forces + (size_t)e * nb * 3, *dof = a->dof_states + (size_t)e * 16;
+        const float *act = a->actions + (size_t)e * 12;
+        if (flagged) {
+            float *root = a->root_states + (size_t)e * 13;
+            memcpy(root, a->initial_root_states + (size_t)e * 13, 13 * sizeof(float));                      /* :288 */
+            root[0] += rand_float(-1.5, 1.5, task_uniform(&a->rand, a->rand.rank, 0, e, 1, 0));              /* :289 */
+            root[1] += rand_float(-1.5, 1.5, task_uniform(&a->rand, a->rand.rank, 1, e, 1, 0));
+            root[2] += rand_float(-0.2, 1.5, task_uniform(&a->rand, a->rand.rank, 2, e, 1, 0));
+            for (int j = 0; j < 8; ++j) {
+                dof[2 * j] = rand_float(-0.2, 0.2, task_uniform(&a->rand, a->rand.rank, 3, e, 8, j));        /* :294 */
+                dof[2 * j + 1] = 0.0f;                                                                       /* :295 */
+            }
+            a->reset_buf[e] = 0;
+            a->progress_buf[e] = 0;
+        }
+        for (int j = 0; j < 8; ++j) {
+            tg[j] += a->dof_target_step * act[j];                                                            /* :310 */
+            tg[j] = tensor_clamp1(tg[j], a->dof_lower[j], a->dof_upper[j]);                                  /* :311 */
+        }
+        for (int k = 0; k < 4; ++k) {
+            th[k] += a->thrust_step * act[8 + k];                                                            /* :314 */
+            th[k] = tensor_clamp1(th[k], a->thrust_lower[k], a->thrust_upper[k]);                            /* :315 */
+            f[a->rotor_bodies[k] * 3 + 2] = th[k];                                                           /* :317-320 */
+        }
+        if (flagged) {                                                                                       /* :323-325 */
+            for (int k = 0; k < 4; ++k) th[k] = 0.0f;
+            for (int i = 0; i < nb * 3; ++i) f[i] = 0.0f;
+            for (int j = 0; j < 8; ++j) tg[j] = dof[2 * j];
+        }
+    }
+    task_advance(&a->list, &a->rand);
+    return 0;
+}
+
+/* reward terms shared by compute_quadcopter_reward (quadcopter.py:391-425) and compute_ingenuity_reward
+ * (ingenuity.py:420-455); quat_axis(q, 2) = quat_rotate(q, z) (utils/torch_jit_utils.py:280-284) */
+static float copter_reward(const float *root, float target_dist, float up_scale) {
+    const float pos_reward = 1.0f / (1.0f + target_dist * target_dist);
+    const float z[3] = {0.0f, 0.0f, 1.0f};
+    float ups[3];
+    quat_rotate_impl(root + 3, z, 0, ups);
+    const float tiltage = fabsf(1.0f - ups[2]);
+    const float up_reward = up_scale / (1.0f + tiltage * tiltage);
+    const float spinnage = fabsf(root[12]);
+    const float spinnage_reward = 1.0f / (1.0f + spinnage * spinnage);
+    return pos_reward + pos_reward * (up_reward + spinnage_reward);
+}
+
+/* tasks/quadcopter.py:333-341 post_physics_step; compute_observations :359-370 */
+int ige_oracle_quadcopter_post_physics(const IgeQuadcopterArgs *a) {
+    const float pi_f = 3.14159274101257324219f;
+    for (int e = 0; e < a->num_envs; ++e) {
+        const int64_t progress = a->progress_buf[e] + 1;
+        const float *root = a->root_states + (size_t)e * 13, *dof = a->dof_states + (size_t)e * 16;
+        float *obs = a->obs_buf + (size_t)e * 21;
+        obs[0] = (0.0f - root[0]) / 3.0f;
+        obs[1] = (0.0f - root[1]) / 3.0f;
+        obs[2] = (1.0f - root[2]) / 3.0f;
+        for (int i = 0; i < 4; ++i) obs[3 + i] = root[3 + i];
+        for (int i = 0; i < 3; ++i) { obs[7 + i] = root[7 + i] / 2.0f; obs[10 + i] = root[10 + i] / pi_f; }
+        for (int j = 0; j < 8; ++j) obs[13 + j] = dof[2 * j];
+        if (a->obs_clamped)
+            for (int i = 0; i < 21; ++i) a->obs_clamped[(size_t)e * 21 + i] = clamp_obs1(obs[i], a->clip_obs);
+        const float dz = 1.0f - root[2];
+        const float target_dist = sqrtf((root[0] * root[0] + root[1] * root[1]) + dz * dz);
+        const int die = target_dist > 3.0f || root[2] < 0.3f;
+        const int late = (float)progress >= a->max_episode_length - 1.0f;
+        const int64_t reset = (late || die) ? 1 : 0;
+        a->rew_buf[e] = copter_reward(root, target_dist, 1.0f);
+        a->reset_buf[e] = reset;
+        a->progress_buf[e] = progress;
+        if (a->timeout_buf) a->timeout_buf[e] = (late && reset != 0) ? 1 : 0;
+    }
+    return 0;
+}
+
+/* tasks/ingenuity.py:322-364 pre_physics_step (set_targets :283-294, reset_idx :296-320) */
+static void ingenuity_set_target(const IgeIngenuityArgs *a, int e, float ux, float uy, float uz) {
+    float *t = a->target_root_positions + (size_t)e * 3, *marker = a->root_tensor + (size_t)e * 26 + 13;
+    t[0] = ux * 10.0f - 5.0f;                                                                                /* :286 */
+    t[1] = uy * 10.0f - 5.0f;
+    t[2] = uz + 1.0f;                                                                                        /* :287 */
+    marker[0] = t[0]; marker[1] = t[1]; marker[2] = t[2] + 0.4f;                                             /* :288-290 */
+}
+int ige_oracle_ingenuity_pre_physics(const IgeIngenuityArgs *a) {
+    const int n = a->num_envs, nb = a->num_bodies;
+    task_list(&a->list, &a->rand, a->reset_buf, n);
+    int any = 0;
+    for (int e = 0; e < n; ++e) any |= a->reset_buf[e] != 0;
+    if (any)                                                                                                 /* :299-300 */
+        for (int e = 0; e < n; ++e) {
+            a->dof_states[(size_t)e * 8 + 3] = -50.0f;
+            a->dof_states[(size_t)e * 8 + 7] = 50.0f;
+        }
+    for (int e = 0; e < n; ++e) {
+        const int flagged = a->reset_buf[e] != 0;
+        const int retarget = a->progress_buf[e] % 500 == 0;                                                  /* :325 */
+        if (retarget)
+            ingenuity_set_target(a, e, task_uniform(&a->rand, a->target_rank, 0, e, 2, 0),
+                                 task_uniform(&a->rand, a->target_rank, 0, e, 2, 1),
+                                 task_uniform(&a->rand, a->target_rank, 1, e, 1, 0));
+        if (flagged) {
+            float *root = a->root_tensor + (size_t)e * 26;
+            ingenuity_set_target(a, e, task_uniform(&a->rand, a->rand.rank, 2, e, 2, 0),
+                                 task_uniform(&a->rand, a->rand.rank, 2, e, 2, 1),
+                                 task_uniform(&a->rand, a->rand.rank, 3, e, 1, 0));                          /* :304 */
+            memcpy(root, a->initial_root_states + (size_t)e * 13, 13 * sizeof(float));                       /* :308 */
+            root[0] += rand_float(-1.5, 1.5, task_uniform(&a->rand, a->rand.rank, 4, e, 1, 0));
+            root[1] += rand_float(-1.5, 1.5, task_uniform(&a->rand, a->rand.rank, 5, e, 1, 0));
+            root[2] += rand_float(-0.2, 1.5, task_uniform(&a->rand, a->rand.rank, 6, e, 1, 0));
+            a->reset_buf[e] = 0;
+            a->progress_buf[e] = 0;
+        }
+        if (a->actor_dirty) {                                                                                /* :334, :341 */
+            a->actor_dirty[(size_t)e * 2] = flagged ? 1 : 0;
+            a->actor_dirty[(size_t)e * 2 + 1] = (flagged || retarget) ? 1 : 0;
+        }
+        const float *act = a->actions + (size_t)e * 6;
+        float *th = a->thrusts + (size_t)e * 6, *f = a->forces + (size_t)e * nb * 3;
+        for (int r = 0; r < 2; ++r) {                                                                        /* :345-355 */
+            const float vert = fminf(fmaxf(act[3 * r + 2] * 2000.0f, -a->thrust_upper_limit), a->thrust_upper_limit);
+            th[3 * r + 2] = a->dt * vert;
+            th[3 * r] = th[3 * r + 2] * fminf(fmaxf(act[3 * r], -a->thrust_lateral_component), a->thrust_lateral_component);
+            th[3 * r + 1] = th[3 * r + 2] * fminf(fmaxf(act[3 * r + 1], -a->thrust_lateral_component), a->thrust_lateral_component);
+        }
+        for (int i = 0; i < 3; ++i) { f[3 + i] = th[i]; f[9 + i] = th[3 + i]; }                              /* :357-358 */
+        if (flagged) {                                                                                       /* :361-362 */
+            for (int i = 0; i < 6; ++i) th[i] = 0.0f;
+            for (int i = 0; i < nb * 3; ++i) f[i] = 0.0f;
+        }
+    }
+    task_advance(&a->list, &a->rand);
+    return 0;
+}
+
+/* tasks/ingenuity.py:366-374 post_physics_step; compute_observations :396-401 */
+int ige_oracle_ingenuity_post_physics(const IgeIngenuityArgs *a) {
+    const float pi_f = 3.14159274101257324219f;
+    for (int e = 0; e < a->num_envs; ++e) {
+        const int64_t progress = a->progress_buf[e] + 1;
+        const float *root = a->root_tensor + (size_t)e * 26, *tgt = a->target_root_positions + (size_t)e * 3;
+        float *obs = a->obs_buf + (size_t)e * 13;
+        for (int i = 0; i < 3; ++i) obs[i] = (tgt[i] - root[i]) / 3.0f;
+        for (int i = 0; i < 4; ++i) obs[3 + i] = root[3 + i];
+        for (int i = 0; i < 3; ++i) { obs[7 + i] = root[7 + i] / 2.0f; obs[10 + i] = root[10 + i] / pi_f; }
+        if (a->obs_clamped)
+            for (int i = 0; i < 13; ++i) a->obs_clamped[(size_t)e * 13 + i] = clamp_obs1(obs[i], a->clip_obs);
+        const float dx = tgt[0] - root[0], dy = tgt[1] - root[1], dz = tgt[2] - root[2];
+        const float target_dist = sqrtf((dx * dx + dy * dy) + dz * dz);                                      /* :424 sum(-1) */
+        const int die = target_dist > 8.0f || root[2] < 0.5f;
+        const int late = (float)progress >= a->max_episode_length - 1.0f;
+        const int64_t reset = (late || die) ? 1 : 0;
+        a->rew_buf[e] = copter_reward(root, target_dist, 5.0f);
+        a->reset_buf[e] = reset;
+        a->progress_buf[e] = progress;
+        if (a->timeout_buf) a->timeout_buf[e] = (late && reset != 0) ? 1 : 0;
+    }
+    return 0;
+}

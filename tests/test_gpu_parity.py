@@ -549,3 +549,113 @@ def test_anymal_mirror_step_matches_oracle():
     assert "set_actor_root_state_tensor_indexed" in names and "set_dof_state_tensor_indexed" in names
     with pytest.raises(H.pkg._lib.IgeError):
         H.pkg.factory.from_state("Anymal", st, "cpu").post_physics_step()
+
+
+# ---- BallBalance / Quadcopter / Ingenuity (reset in pre-physics position) --------------------
+SMALL_TASKS = ["ball_balance", "quadcopter", "ingenuity"]
+# reset rows / targets / thrusts / forces: copies and a few fp32 ops of the injected draws -> bit-exact against the
+# oracle; BallBalance's ball rows go through cosf / sinf (CUDA libm vs glibc differ in the last ulp)
+SMALL_EXACT = {t: tuple(n for n in ("root_states", "root_tensor", "dof_states", "dof_position_targets", "thrusts", "forces",
+                                    "target_root_positions") if not (t == "ball_balance" and n == "root_states"))
+               for t in SMALL_TASKS}
+
+
+@pytest.mark.parametrize("task", SMALL_TASKS)
+def test_small_task_matches_reference_golden(task):
+    """CUDA pre_physics / post_physics against the reference's own VecTask.step outputs (gen_golden_small.py)."""
+    import small_harness as S
+    files = S.golden_files(task)
+    assert len(files) >= 3
+    for path in files:
+        blob = H.load_golden(path)
+        for s, phase, got, ref in S.run_fixture(blob, task, "cuda:0"):
+            exact = tuple(n for n in SMALL_EXACT[task])
+            S.compare(got, ref, f"{os.path.basename(path)} step{s} {phase}", exact_float=exact)
+
+
+@pytest.mark.parametrize("task", SMALL_TASKS)
+@pytest.mark.parametrize("n,reset_prob,mode", [(16384, 0.02, "injected"), (16384, 0.02, "philox"), (4099, 1.0, "injected"),
+                                               (262144, 0.3, "philox"), (1000, 0.0, "injected"), (33, 0.5, "injected"),
+                                               (1, 1.0, "philox")])
+def test_small_task_matches_oracle(task, n, reset_prob, mode):
+    """CUDA vs oracle on the same seeded state over 3 chained control steps (pre -> new simulator state -> post):
+    ids / flags / counters bit-exact, reset rows bit-exact, observations / rewards 1e-5 relative.  Philox mode: the
+    oracle implements the same counter-based generator, so the noise itself is compared too."""
+    import small_harness as S
+    syn = H.pkg.synthetic
+    st = syn.make_state(task, n, seed=n % 1013 + 3, reset_prob=reset_prob)
+    cpu, gpu = S.State(task, n, "cpu"), S.State(task, n, "cuda:0")
+    rng = np.random.Generator(np.random.PCG64(n + 17))
+    for dev in (cpu, gpu):
+        dev.load_state(st)
+    total_resets = 0
+    for step in range(3):
+        k = int((cpu.reset_buf != 0).sum())
+        kt = int((cpu.progress_buf % 500 == 0).sum()) if task == "ingenuity" else 0
+        rands = S.np_draws(task, rng, k, kt) if mode == "injected" else None
+        ids_c, ids_g = cpu.pre(rands, seed=91), gpu.pre(rands, seed=91)
+        assert len(ids_c) == k
+        total_resets += k
+        H.assert_equal(f"{task} reset ids step{step}", ids_g, ids_c)
+        names = S.PRE_OUT[task] + ("reset_buf", "progress_buf") + (("actor_dirty",) if task == "ingenuity" else ())
+        S.compare(gpu.get(names), cpu.get(names), f"{task} n={n} step{step} pre", exact_float=SMALL_EXACT[task])
+        assert int(gpu.rng_step) == int(cpu.rng_step) == (step + 1 if mode == "philox" else 0)
+        syn.advance_physics(task, st, rng)                      # the simulator's new state, identical on both sides
+        for dev in (cpu, gpu):
+            dev.load(**{name: st[name] for name in S.PHYS[task]})
+            dev.post()
+        names = S.POST_OUT + ("reset_buf", "progress_buf", "time_outs")
+        S.compare(gpu.get(names), cpu.get(names), f"{task} n={n} step{step} post")
+        for dev in (cpu, gpu):                                  # next actions
+            dev.load(actions=np.clip(st["actions"], -1, 1))
+    if reset_prob > 0 and n > 100:
+        assert total_resets > 0
+
+
+@pytest.mark.parametrize("task", SMALL_TASKS)
+def test_small_task_mirror_step(task):
+    """factory.make()-shaped entry -> <Task>.step(): the VecTask return tuple, the recorded indexed sim calls and every
+    buffer against the oracle driven from the same synthetic state (Philox reset noise on both sides)."""
+    import small_harness as S
+    name = {"ball_balance": "BallBalance", "quadcopter": "Quadcopter", "ingenuity": "Ingenuity"}[task]
+    n, seed = 3000, 5
+    st = H.pkg.synthetic.make_state(task, n, seed=seed, reset_prob=0.1)
+    env = H.pkg.factory.from_state(name, st, "cuda:0", rand_mode="philox", seed=seed)
+    cpu = S.State(task, n, "cpu")
+    cpu.load_state(st)
+    ids_ref = cpu.pre(None, seed=seed)
+    cpu.post()
+    env.sim.record = True
+    obs_dict, rew, reset, extras = env.step(torch.from_numpy(st["actions"]).to("cuda:0"))
+    torch.cuda.synchronize()
+    k = int(env.reset_count)
+    H.assert_equal("reset ids", env.reset_env_ids[:k].cpu().numpy(), ids_ref)
+    got = {"obs_buf": env.obs_buf.cpu().numpy(), "rew_buf": rew.cpu().numpy(), "obs_clamped": obs_dict["obs"].cpu().numpy(),
+           "reset_buf": reset.cpu().numpy(), "progress_buf": env.progress_buf.cpu().numpy(),
+           "time_outs": extras["time_outs"].cpu().numpy().astype(np.uint8)}
+    for t in S.PRE_OUT[task]:
+        got[t] = getattr(env, t).cpu().numpy()
+    S.compare(got, cpu.get(tuple(got)), f"{task} mirror", exact_float=SMALL_EXACT[task])
+    names = [c[0] for c in env.sim.calls]
+    assert "set_dof_state_tensor_indexed" in names and "set_actor_root_state_tensor_indexed" in names
+    with pytest.raises(H.pkg._lib.IgeError):
+        H.pkg.factory.from_state(name, st, "cpu").post_physics_step()
+
+
+def test_small_task_argument_checks():
+    """No reset list: BallBalance / Quadcopter still step (rand.step is then not advanced); Ingenuity refuses, because
+    the rotor speeds of all envs depend on the list's total (ingenuity.py:299-300)."""
+    import small_harness as S
+    for task in ("ball_balance", "quadcopter"):
+        st = H.pkg.synthetic.make_state(task, 2048, seed=1, reset_prob=0.1)
+        a, b = S.State(task, 2048, "cuda:0"), S.State(task, 2048, "cpu")
+        for dev in (a, b):
+            dev.load_state(st)
+            dev.emit_list = False
+            dev.pre(None, seed=3)
+        S.compare(a.get(S.PRE_OUT[task]), b.get(S.PRE_OUT[task]), f"{task} no list", exact_float=SMALL_EXACT[task])
+        assert int(a.rng_step) == 0
+    ing = S.State("ingenuity", 64, "cuda:0")
+    ing.emit_list = False
+    with pytest.raises(H.pkg._lib.IgeError):
+        ing.pre(None)

@@ -83,3 +83,32 @@ def test_oracle_anymal_matches_reference_golden():
             H.assert_equal("reset_env_ids", ids, ref["reset_env_ids"])
             A.compare(got, ref, f"{os.path.basename(path)} step{s}")
             assert H.bitexact_fraction(got["obs_buf"], ref["obs_buf"]) > 0.98
+
+
+# reset rows, targets, thrusts and forces are plain copies / a few fp32 ops of injected draws: bit-exact -- except
+# BallBalance's ball rows, which go through cos / sin of the drawn direction (torch CPU = Sleef, libm and CUDA differ
+# from it in the last ulp)
+SMALL_EXACT = {t: tuple(n for n in ("root_states", "root_tensor", "dof_states", "dof_position_targets", "thrusts", "forces",
+                                    "target_root_positions") if not (t == "ball_balance" and n == "root_states"))
+               for t in ("ball_balance", "quadcopter", "ingenuity")}
+
+
+@pytest.mark.parametrize("task", ["ball_balance", "quadcopter", "ingenuity"])
+def test_oracle_small_tasks_match_reference_golden(task):
+    """SURVEY.md 8f row 2 (BallBalance / Quadcopter / Ingenuity): the oracle's pre_physics and post_physics halves
+    against the reference's own VecTask.step (tests/golden/gen_golden_small.py, gym.simulate hooked to snapshot the
+    pre-physics writes): ids / flags / counters and every reset row bit-exact, obs and rewards within 1e-5."""
+    import small_harness as S
+    files = S.golden_files(task)
+    assert len(files) >= 3
+    resets = timeouts = 0
+    for path in files:
+        blob = H.load_golden(path)
+        for s, phase, got, ref in S.run_fixture(blob, task, "cpu"):
+            S.compare(got, ref, f"{os.path.basename(path)} step{s} {phase}", exact_float=SMALL_EXACT[task])
+            if phase == "pre":
+                resets += len(got["reset_env_ids"])
+            else:
+                timeouts += int(got["time_outs"].sum())
+                assert H.bitexact_fraction(got["obs_buf"], ref["obs_buf"]) > 0.98
+    assert resets > 50 and timeouts > 0

@@ -47,8 +47,12 @@ for act in "$@"; do
       python isaacgymenvs-ma_b200/build.py -DIGE_ROLE_CLOCKS > gpurun_out/build_clk.log 2>&1
       timeout 300 python tools/role_clocks.py --task $b --num-envs $c > gpurun_out/${R}_role_clocks_${b}_$c.txt 2>&1; cat gpurun_out/${R}_role_clocks_${b}_$c.txt
       python isaacgymenvs-ma_b200/build.py > gpurun_out/build.log 2>&1 ;;
-    kern)       # kern:<Task>:<N>  -- kernel-only timing of one task (no e2e / sweep / cpu legs)
-      timeout 300 python bench.py --task $b --num-envs $c --steps 2048 --warmup 64 --no-e2e --no-sweep --no-cpu > gpurun_out/kern_${b}_$c.json 2> gpurun_out/kern_${b}_$c.err
+    scandbg)    # scandbg:<Task>:<N>  -- debug build with the scanner timeline, then the normal build again
+      python isaacgymenvs-ma_b200/build.py -DIGE_SCAN_DEBUG > gpurun_out/build_scan.log 2>&1
+      timeout 300 python tools/scan_debug.py --task $b --num-envs $c > gpurun_out/${R}_scan_debug_${b}_$c.txt 2>&1; cat gpurun_out/${R}_scan_debug_${b}_$c.txt
+      python isaacgymenvs-ma_b200/build.py > gpurun_out/build.log 2>&1 ;;
+    kern)       # kern:<Task>:<N>[:ENV=VAL,...]  -- kernel-only timing of one task (no e2e / sweep / cpu legs)
+      env ${d//,/ } timeout 300 python bench.py --task $b --num-envs $c --steps 2048 --warmup 64 --no-e2e --no-sweep --no-cpu > gpurun_out/kern_${b}_$c.json 2> gpurun_out/kern_${b}_$c.err
       echo "kern $b $c rc=$?"; python - <<PY
 import json
 try:
