@@ -638,6 +638,96 @@ int ige_ingenuity_pre_physics(const IgeIngenuityArgs *a, void *stream);
 int ige_ingenuity_post_physics(const IgeIngenuityArgs *a, void *stream);
 
 /* ------------------------------------------------------------------------------------------
+ * Single-agent Franka cube tasks: FrankaReach (the fork's FSM lifting task,
+ * tasks/franka_reach.py), FrankaCubeStack2 (the fork's 7-state stacking FSM, tasks/franka_cube_stack2.py) and
+ * FrankaCubeStack (NVIDIA's original, tasks/franka_cube_stack.py).  One entry point replaces post_physics_step
+ * (franka_reach.py:695-704, franka_cube_stack2.py:707-716, franka_cube_stack.py:657-665): progress++, reset_idx
+ * (:479-535 / :501-558 / :458-514 with _reset_init_cube_state), _update_states + FSM (:410-458 / :408-466 / :416-433),
+ * compute_observations, compute_franka_reward (:877-928 / :774-850 / :698-747) and the step() epilogue.
+ *
+ * torch.rand draws of reset_idx, rows by reset rank (slot = index into rand.u[], -1 = the variant does not draw it):
+ *   draw_slot[0] cubeB z (k)   [1] cubeB xy (k,2)   [2] cubeB yaw (k)   [3] cubeA z (k)   [4] cubeA xy (k,2)
+ *   [5] cubeA yaw (k)   [6] franka joints (k,9).
+ * FrankaCubeStack re-samples cubeA's xy until it clears cubeB (check_valid, up to 100 tries, :567-585): in INJECTED
+ * mode u[draw_slot[4]] holds the ACCEPTED sample of each env; in PHILOX mode the kernel runs the retry loop itself.
+ * ------------------------------------------------------------------------------------------ */
+#define IGE_FRANKA_SA_REACH 0
+#define IGE_FRANKA_SA_STACK2 1
+#define IGE_FRANKA_SA_STACK 2
+#define IGE_FRANKA_SA_COMPONENTS 12
+/* reward_components[]: Reach     0 r/state0, 1 r/state1, 2 r/state2, 7 r/state, 8 mean_cube_height
+ *                      Stack2    0..6 r/state0, r/state1, r/state2, r/stat3, r/stat4, r/stat5, r/state6, 7 r/state,
+ *                                8 mean_cube_height, 9 target_dist          (means over the envs of this launch) */
+typedef struct IgeFrankaSAArgs {
+    int32_t variant;                 /* IGE_FRANKA_SA_* */
+    int32_t num_envs;
+    int32_t num_bodies, num_actors;  /* rows per env of rigid_body_state / root_state */
+    int32_t eef_body, lf_body, rf_body;  /* panda_grip_site / leftfinger_tip / rightfinger_tip handles (:355-362) */
+    int32_t cubeA_actor, cubeB_actor;
+    int32_t draw_slot[7];
+    float max_episode_length, clip_obs;
+    float cubeA_size, cubeB_size, table_height;
+    float cube_xy_center[2], cube_xy_mult;   /* float32(table xy), float32(2 * startPositionNoise) */
+    float cubeA_z_base, cubeB_z_base, cube_z_range;  /* z = base + rand * range (range 0: no draw) */
+    float cube_yaw_mult;             /* float32(2 * startRotationNoise); 0 = no rotation draw */
+    float dof_noise_mult;            /* float32(frankaDofNoise * 2) */
+    float min_dist;                  /* Stack: collision-free distance of the two cubes (:550-553) */
+    float r_dist_scale, r_lift_scale, r_align_scale, r_stack_scale;   /* Stack reward_settings */
+    float default_dof_pos[9], dof_lower[9], dof_upper[9];
+    IgeTaskRand rand;
+    const float *rigid_body_state;   /* (N, num_bodies, 13) */
+    float *root_state;               /* (N, num_actors, 13) cube rows rewritten by the reset */
+    float *dof_state;                /* (N, 9, 2) reset rows rewritten */
+    const float *actions;            /* (N, 7) */
+    float *pos_control, *effort_control;         /* (N, 9) reset rows rewritten */
+    float *init_cubeA_state, *init_cubeB_state;  /* (N, 13); cubeB unused by Reach */
+    float *obs_buf;                  /* (N, 14 | 21 | 19) */
+    float *rew_buf;
+    int64_t *reset_buf, *progress_buf;
+    float *obs_clamped;              /* optional */
+    uint8_t *timeout_buf;            /* optional */
+    float *reward_components;        /* optional [IGE_FRANKA_SA_COMPONENTS] */
+    float *reduce_scratch;           /* [IGE_FRANKA_SA_COMPONENTS + 2], zeroed once */
+    IgeResetList list;
+} IgeFrankaSAArgs;
+int ige_franka_sa_post_physics(const IgeFrankaSAArgs *a, void *stream);
+
+/* FrankaCabinet -- tasks/franka_cabinet.py: pre_physics_step :417-425 (DOF position targets) and post_physics_step
+ * :427-436 (reset_idx :385-415, compute_observations :352-383 with compute_grasp_transforms :554-567,
+ * compute_franka_reward :475-551) + the step() epilogue.  Reset draw: u[0] (k, 9) franka joints. */
+typedef struct IgeFrankaCabinetArgs {
+    int32_t num_envs;
+    int32_t num_bodies, num_actors, num_dofs;   /* per env: rigid bodies, actors (2 + num_props), DOFs (9 + 4) */
+    int32_t num_props;
+    int32_t hand_body, drawer_body, lfinger_body, rfinger_body;
+    float max_episode_length, clip_obs;
+    float dof_vel_scale, target_step;  /* target_step = float32(dt) applied as speed_scale * dt * action * action_scale */
+    float action_scale;
+    float dist_reward_scale, rot_reward_scale, around_handle_reward_scale, open_reward_scale;
+    float finger_dist_reward_scale, action_penalty_scale, distX_offset;
+    float franka_local_grasp_pos[3], franka_local_grasp_rot[4];
+    float drawer_local_grasp_pos[3], drawer_local_grasp_rot[4];
+    float gripper_forward_axis[3], drawer_inward_axis[3], gripper_up_axis[3], drawer_up_axis[3];
+    float default_dof_pos[9], dof_lower[9], dof_upper[9], dof_speed_scales[9];
+    IgeTaskRand rand;
+    const float *rigid_body_states;  /* (N, num_bodies, 13) */
+    float *root_state_tensor;        /* (N, num_actors, 13) prop rows rewritten by the reset */
+    const float *default_prop_states;/* (N, num_props, 13) */
+    float *dof_state;                /* (N, num_dofs, 2): franka 0..8, cabinet 9..12; reset rows rewritten */
+    const float *actions;            /* (N, 9) */
+    float *franka_dof_targets;       /* (N, num_dofs) */
+    float *franka_grasp_pos, *franka_grasp_rot, *drawer_grasp_pos, *drawer_grasp_rot;   /* optional (N,3)/(N,4) outputs */
+    float *obs_buf;                  /* (N, 23) */
+    float *rew_buf;
+    int64_t *reset_buf, *progress_buf;
+    float *obs_clamped;
+    uint8_t *timeout_buf;
+    IgeResetList list;
+} IgeFrankaCabinetArgs;
+int ige_franka_cabinet_pre_physics(const IgeFrankaCabinetArgs *a, void *stream);
+int ige_franka_cabinet_post_physics(const IgeFrankaCabinetArgs *a, void *stream);
+
+/* ------------------------------------------------------------------------------------------
  * Episode statistics: fold the striped accumulator a step kernel adds into (Buffers.stats) into the
  * <= IGE_NUM_STATS-float vector that is all-reduced across GPUs once per horizon (the
  * reference keeps per-rank statistics, utils/rlgames_utils.py:89-107).  One tiny launch, off the step's

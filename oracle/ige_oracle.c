@@ -1582,3 +1582,296 @@ int ige_oracle_ingenuity_post_physics(const IgeIngenuityArgs *a) {
     }
     return 0;
 }
+
+/* ------------------------------------------------------------------------------------------
+ * Single-agent Franka cube tasks: FrankaReach, FrankaCubeStack2, FrankaCubeStack.
+ * Reference: tasks/franka_reach.py, tasks/franka_cube_stack2.py, tasks/franka_cube_stack.py.
+ * ------------------------------------------------------------------------------------------ */
+static float sa_uniform(const IgeFrankaSAArgs *a, int which, int e, int cols, int j) {
+    return task_uniform(&a->rand, a->rand.rank, a->draw_slot[which], e, cols, j);
+}
+/* axisangle2quat((0, 0, az)) followed by quat_mul(., (0,0,0,1)): franka_reach.py:18-49, :626-629 */
+static void sa_yaw_quat(float az, float *q) {
+    const float angle = norm3(0.0f, 0.0f, az);
+    float aa[4] = {0.0f, 0.0f, 0.0f, 1.0f};
+    if (angle > 1e-6f) {
+        const float s = sinf(angle / 2.0f);
+        aa[0] = 0.0f * s / angle; aa[1] = 0.0f * s / angle; aa[2] = az * s / angle;
+        aa[3] = cosf(angle / 2.0f);
+    }
+    const float ident[4] = {0.0f, 0.0f, 0.0f, 1.0f};
+    quat_mul(aa, ident, q);
+}
+/* _reset_init_cube_state for one env (franka_reach.py:538-632, franka_cube_stack2.py:557-647,
+ * franka_cube_stack.py:516-599); which: 0 = cubeB, 1 = cubeA.  other_xy: the other cube's fresh init xy (Stack). */
+static void sa_sample_cube(const IgeFrankaSAArgs *a, int e, int which, const float *other_xy, float *row) {
+    const int base = which ? 3 : 0;
+    memset(row, 0, 13 * sizeof(float));
+    row[2] = which ? a->cubeA_z_base : a->cubeB_z_base;
+    if (a->cube_z_range != 0.0f) row[2] = row[2] + sa_uniform(a, base + 0, e, 1, 0) * a->cube_z_range;
+    row[6] = 1.0f;
+    float ux = sa_uniform(a, base + 1, e, 2, 0), uy = sa_uniform(a, base + 1, e, 2, 1);
+    row[0] = a->cube_xy_center[0] + a->cube_xy_mult * (ux - 0.5f);
+    row[1] = a->cube_xy_center[1] + a->cube_xy_mult * (uy - 0.5f);
+    if (which && a->variant == IGE_FRANKA_SA_STACK && a->rand.mode == IGE_RAND_PHILOX) {
+        /* check_valid: re-sample while the cubes would touch (:567-585); INJECTED mode is handed the accepted sample */
+        for (int t = 1; t < 100 && norm2(row[0] - other_xy[0], row[1] - other_xy[1]) < a->min_dist; ++t) {
+            IgeTaskRand r = a->rand;
+            ux = task_uniform(&r, r.rank, 8 + t, e, 2, 0); uy = task_uniform(&r, r.rank, 8 + t, e, 2, 1);
+            row[0] = a->cube_xy_center[0] + a->cube_xy_mult * (ux - 0.5f);
+            row[1] = a->cube_xy_center[1] + a->cube_xy_mult * (uy - 0.5f);
+        }
+    }
+    if (a->cube_yaw_mult > 0.0f) sa_yaw_quat(a->cube_yaw_mult * (sa_uniform(a, base + 2, e, 1, 0) - 0.5f), row + 3);
+}
+
+int ige_oracle_franka_sa_post_physics(const IgeFrankaSAArgs *a) {
+    const int n = a->num_envs, V = a->variant;
+    const int nobs = V == IGE_FRANKA_SA_REACH ? 14 : (V == IGE_FRANKA_SA_STACK2 ? 21 : 19);
+    double comp[IGE_FRANKA_SA_COMPONENTS];
+    memset(comp, 0, sizeof(comp));
+    task_list(&a->list, &a->rand, a->reset_buf, n);
+    for (int e = 0; e < n; ++e) {
+        int64_t progress = a->progress_buf[e] + 1;
+        int64_t reset = a->reset_buf[e];
+        float *cubeA = a->root_state + ((size_t)e * a->num_actors + a->cubeA_actor) * 13;
+        float *cubeB = a->root_state + ((size_t)e * a->num_actors + a->cubeB_actor) * 13;
+        float *dof = a->dof_state + (size_t)e * 18;
+        if (reset != 0) { /* reset_idx */
+            float row[13], bxy[2] = {0.0f, 0.0f};
+            if (V != IGE_FRANKA_SA_REACH) { /* cube B first, then A */
+                sa_sample_cube(a, e, 0, bxy, row);
+                memcpy(a->init_cubeB_state + (size_t)e * 13, row, sizeof(row));
+                memcpy(cubeB, row, sizeof(row));
+                bxy[0] = row[0]; bxy[1] = row[1];
+            }
+            sa_sample_cube(a, e, 1, bxy, row);
+            memcpy(a->init_cubeA_state + (size_t)e * 13, row, sizeof(row));
+            memcpy(cubeA, row, sizeof(row));
+            for (int j = 0; j < 9; ++j) {
+                float v = a->default_dof_pos[j] + a->dof_noise_mult * (sa_uniform(a, 6, e, 9, j) - 0.5f);
+                v = tensor_clamp1(v, a->dof_lower[j], a->dof_upper[j]);
+                if (j >= 7) v = a->default_dof_pos[j];
+                dof[2 * j] = v; dof[2 * j + 1] = 0.0f;
+                a->pos_control[(size_t)e * 9 + j] = v;
+                a->effort_control[(size_t)e * 9 + j] = 0.0f;
+            }
+            progress = 0; reset = 0;
+        }
+        /* _update_states */
+        const float *rb = a->rigid_body_state + (size_t)e * a->num_bodies * 13;
+        const float *eef = rb + (size_t)a->eef_body * 13;
+        const float rel[3] = {cubeA[0] - eef[0], cubeA[1] - eef[1], cubeA[2] - eef[2]};
+        const float a2b[3] = {cubeB[0] - cubeA[0], cubeB[1] - cubeA[1], cubeB[2] - cubeA[2]};
+        const float height = cubeA[2] - a->table_height;
+        const float qg[2] = {dof[14], dof[16]};
+        const float agrip = a->actions[(size_t)e * 7 + 6];
+        const float d = norm3(rel[0], rel[1], rel[2]);
+        float *obs = a->obs_buf + (size_t)e * nobs;
+        float reward;
+        if (V == IGE_FRANKA_SA_STACK) {
+            const float *lf = rb + (size_t)a->lf_body * 13, *rf = rb + (size_t)a->rf_body * 13;
+            int k = 0;
+            for (int i = 0; i < 4; ++i) obs[k++] = cubeA[3 + i];
+            for (int i = 0; i < 3; ++i) obs[k++] = cubeA[i];
+            for (int i = 0; i < 3; ++i) obs[k++] = a2b[i];
+            for (int i = 0; i < 3; ++i) obs[k++] = eef[i];
+            for (int i = 0; i < 4; ++i) obs[k++] = eef[3 + i];
+            obs[k++] = qg[0]; obs[k++] = qg[1];
+            /* compute_franka_reward franka_cube_stack.py:698-747 */
+            const float target_height = a->cubeB_size + a->cubeA_size / 2.0f;
+            const float d_lf = norm3(cubeA[0] - lf[0], cubeA[1] - lf[1], cubeA[2] - lf[2]);
+            const float d_rf = norm3(cubeA[0] - rf[0], cubeA[1] - rf[1], cubeA[2] - rf[2]);
+            float dist_reward = 1.0f - tanhf(10.0f * ((d + d_lf) + d_rf) / 3.0f);
+            const int lifted = (height - a->cubeA_size) > 0.04f;
+            const float d_ab = norm3(a2b[0] + 0.0f, a2b[1] + 0.0f, a2b[2] + (a->cubeA_size + a->cubeB_size) / 2.0f);
+            const float align_reward = (1.0f - tanhf(10.0f * d_ab)) * (lifted ? 1.0f : 0.0f);
+            dist_reward = fmaxf(dist_reward, align_reward);
+            const int stack = (norm2(a2b[0], a2b[1]) < 0.02f) && (fabsf(height - target_height) < 0.02f) && (d > 0.04f);
+            reward = stack ? a->r_stack_scale * 1.0f
+                           : (a->r_dist_scale * dist_reward + a->r_lift_scale * (lifted ? 1.0f : 0.0f)) + a->r_align_scale * align_reward;
+            if (stack) reset = 1;
+        } else {
+            /* FSM franka_reach.py:410-430 / franka_cube_stack2.py:408-439 */
+            const int on = d <= (a->cubeA_size / 2.0f) * 0.9f;
+            const int closed = agrip < 0.0f;
+            int fsm = 0;
+            if (on) fsm = 1;
+            if (on && closed) fsm = 2;
+            float tdist = 0.0f, tdist2 = 0.0f;
+            if (V == IGE_FRANKA_SA_STACK2) {
+                const int lifted = height >= (a->cubeB_size + a->cubeA_size * 0.5f);
+                if (on && closed && lifted) fsm = 3;
+                const int aligned = norm2(a2b[0], a2b[1]) <= a->cubeA_size * 0.5f;
+                if (aligned) fsm = 4;
+                const int super_close = norm3(a2b[0], a2b[1], a2b[2]) < (a->cubeA_size * 0.7071f + a->cubeB_size * 0.5f);
+                if (aligned && super_close) fsm = 5;
+                if (aligned && super_close && !closed) fsm = 6;
+            }
+            int k = 0;
+            for (int i = 0; i < 4; ++i) obs[k++] = eef[3 + i];
+            for (int i = 0; i < 3; ++i) obs[k++] = eef[i];
+            for (int i = 0; i < 3; ++i) obs[k++] = rel[i];
+            obs[k++] = height;
+            if (V == IGE_FRANKA_SA_STACK2) {
+                for (int i = 0; i < 4; ++i) obs[k++] = cubeA[3 + i];
+                for (int i = 0; i < 3; ++i) obs[k++] = a2b[i];
+            }
+            obs[k++] = qg[0]; obs[k++] = qg[1];
+            obs[k++] = pow2_small(fsm);
+            const float dist_reward = 1.0f / (0.5f + d * d) * 0.5f;
+            const float sf = (float)fsm;
+            if (V == IGE_FRANKA_SA_REACH) { /* franka_reach.py:877-928 */
+                const float s0 = (dist_reward + tanhf(agrip * 3.0f)) / 2.0f;
+                const float s1 = (dist_reward + tanhf(-agrip * 3.0f)) / 2.0f;
+                const float s2 = expf(2.5f * height) - 1.0f;
+                reward = fsm == 0 ? s0 : 0.0f;
+                reward += s1;
+                reward += fsm == 1 ? s1 : 0.0f;
+                reward += fsm == 2 ? s2 : 0.0f;
+                reward += sf;
+                comp[0] += s0; comp[1] += s1; comp[2] += s2; comp[7] += sf; comp[8] += height;
+            } else { /* franka_cube_stack2.py:774-850 */
+                const float s0 = dist_reward;
+                const float s1 = (dist_reward + fmaxf(tanhf(-agrip * 3.0f), 0.0f)) / 2.0f;
+                const float s2 = fsm == 2 ? fminf(height / 0.095f, 1.0f) : 0.0f;
+                const float off = (a->cubeA_size + a->cubeB_size) / 2.0f;
+                const float tz = a2b[2] + off;
+                tdist = norm3(a2b[0], a2b[1], tz);
+                tdist2 = norm3(a2b[0], a2b[1], tz + off); /* the debug block adds the offset once more (:752-756) */
+                const float s3 = tanhf(5.0f * -tdist) + 1.0f;
+                const float s4 = tanhf(6.0f * -tdist) + 1.0f;
+                const float s5 = tanhf(agrip * 7.0f) + 1.0f;
+                const float s6 = tanhf(7.0f * d);
+                reward = fsm == 0 ? s0 : 0.0f;
+                reward += fsm == 1 ? s1 : 0.0f;
+                reward += fsm == 2 ? s2 : 0.0f;
+                reward += fsm == 3 ? s3 : 0.0f;
+                reward += fsm == 4 ? s4 : 0.0f;
+                reward += fsm == 5 ? s5 : 0.0f;
+                reward += fsm == 6 ? s6 + 10.0f : 0.0f;
+                reward += sf;
+                comp[0] += s0; comp[1] += s1; comp[2] += s2; comp[3] += s3; comp[4] += s4; comp[5] += s5; comp[6] += s6;
+                comp[7] += sf; comp[8] += height; comp[9] += tdist2;
+            }
+            reward = fmaxf(reward, 0.0f);
+        }
+        const int late = (float)progress >= a->max_episode_length - 1.0f;
+        if (late) reset = 1;
+        if (a->obs_clamped)
+            for (int i = 0; i < nobs; ++i) a->obs_clamped[(size_t)e * nobs + i] = clamp_obs1(obs[i], a->clip_obs);
+        a->rew_buf[e] = reward;
+        a->reset_buf[e] = reset;
+        a->progress_buf[e] = progress;
+        if (a->timeout_buf) a->timeout_buf[e] = (late && reset != 0) ? 1 : 0;
+    }
+    if (a->reward_components)
+        for (int i = 0; i < IGE_FRANKA_SA_COMPONENTS; ++i) a->reward_components[i] = n ? (float)(comp[i] / n) : 0.0f;
+    task_advance(&a->list, &a->rand);
+    return 0;
+}
+
+/* ------------------------------------------------------------------------------------------
+ * FrankaCabinet: tasks/franka_cabinet.py
+ * ------------------------------------------------------------------------------------------ */
+/* utils/torch_jit_utils.py:71-77 quat_apply */
+static void quat_apply3(const float *q, const float *b, float *out) {
+    float t[3], c2[3];
+    cross3(q, b, t);
+    for (int i = 0; i < 3; ++i) t[i] = t[i] * 2.0f;
+    cross3(q, t, c2);
+    for (int i = 0; i < 3; ++i) out[i] = (b[i] + q[3] * t[i]) + c2[i];
+}
+int ige_oracle_franka_cabinet_pre_physics(const IgeFrankaCabinetArgs *a) { /* :417-425 */
+    for (int e = 0; e < a->num_envs; ++e)
+        for (int j = 0; j < 9; ++j) {
+            float *t = a->franka_dof_targets + (size_t)e * a->num_dofs + j;
+            const float v = *t + a->dof_speed_scales[j] * a->target_step * a->actions[(size_t)e * 9 + j] * a->action_scale;
+            *t = tensor_clamp1(v, a->dof_lower[j], a->dof_upper[j]);
+        }
+    return 0;
+}
+int ige_oracle_franka_cabinet_post_physics(const IgeFrankaCabinetArgs *a) { /* :427-436 */
+    const int n = a->num_envs, D = a->num_dofs;
+    task_list(&a->list, &a->rand, a->reset_buf, n);
+    for (int e = 0; e < n; ++e) {
+        int64_t progress = a->progress_buf[e] + 1;
+        int64_t reset = a->reset_buf[e];
+        float *dof = a->dof_state + (size_t)e * D * 2;
+        if (reset != 0) { /* reset_idx :385-415 */
+            for (int j = 0; j < 9; ++j) {
+                float v = a->default_dof_pos[j] + 0.25f * (task_uniform(&a->rand, a->rand.rank, 0, e, 9, j) - 0.5f);
+                v = tensor_clamp1(v, a->dof_lower[j], a->dof_upper[j]);
+                dof[2 * j] = v; dof[2 * j + 1] = 0.0f;
+                a->franka_dof_targets[(size_t)e * D + j] = v;
+            }
+            for (int j = 9; j < D; ++j) { dof[2 * j] = 0.0f; dof[2 * j + 1] = 0.0f; }
+            if (a->num_props > 0)
+                memcpy(a->root_state_tensor + ((size_t)e * a->num_actors + 2) * 13,
+                       a->default_prop_states + (size_t)e * a->num_props * 13, (size_t)a->num_props * 13 * sizeof(float));
+            progress = 0; reset = 0;
+        }
+        const float *rb = a->rigid_body_states + (size_t)e * a->num_bodies * 13;
+        const float *hand = rb + (size_t)a->hand_body * 13, *drawer = rb + (size_t)a->drawer_body * 13;
+        const float *lf = rb + (size_t)a->lfinger_body * 13, *rf = rb + (size_t)a->rfinger_body * 13;
+        float fg_rot[4], fg_pos[3], dg_rot[4], dg_pos[3], t3[3];
+        quat_mul(hand + 3, a->franka_local_grasp_rot, fg_rot); /* tf_combine :148-149 */
+        quat_apply3(hand + 3, a->franka_local_grasp_pos, t3);
+        for (int i = 0; i < 3; ++i) fg_pos[i] = t3[i] + hand[i];
+        quat_mul(drawer + 3, a->drawer_local_grasp_rot, dg_rot);
+        quat_apply3(drawer + 3, a->drawer_local_grasp_pos, t3);
+        for (int i = 0; i < 3; ++i) dg_pos[i] = t3[i] + drawer[i];
+        if (a->franka_grasp_pos) memcpy(a->franka_grasp_pos + (size_t)e * 3, fg_pos, sizeof(fg_pos));
+        if (a->franka_grasp_rot) memcpy(a->franka_grasp_rot + (size_t)e * 4, fg_rot, sizeof(fg_rot));
+        if (a->drawer_grasp_pos) memcpy(a->drawer_grasp_pos + (size_t)e * 3, dg_pos, sizeof(dg_pos));
+        if (a->drawer_grasp_rot) memcpy(a->drawer_grasp_rot + (size_t)e * 4, dg_rot, sizeof(dg_rot));
+        float *obs = a->obs_buf + (size_t)e * 23;
+        for (int j = 0; j < 9; ++j) {
+            obs[j] = 2.0f * (dof[2 * j] - a->dof_lower[j]) / (a->dof_upper[j] - a->dof_lower[j]) - 1.0f; /* :378-379 */
+            obs[9 + j] = dof[2 * j + 1] * a->dof_vel_scale;
+        }
+        for (int i = 0; i < 3; ++i) obs[18 + i] = dg_pos[i] - fg_pos[i];
+        const float cab_pos = dof[2 * 12], cab_vel = dof[2 * 12 + 1]; /* cabinet_dof_*[:, 3] */
+        obs[21] = cab_pos; obs[22] = cab_vel;
+        /* compute_franka_reward :475-551 */
+        const float d = norm3(fg_pos[0] - dg_pos[0], fg_pos[1] - dg_pos[1], fg_pos[2] - dg_pos[2]);
+        float dist_reward = 1.0f / (1.0f + d * d);
+        dist_reward *= dist_reward;
+        if (d <= 0.02f) dist_reward = dist_reward * 2.0f;
+        float ax1[3], ax2[3], ax3[3], ax4[3];
+        quat_apply3(fg_rot, a->gripper_forward_axis, ax1);
+        quat_apply3(dg_rot, a->drawer_inward_axis, ax2);
+        quat_apply3(fg_rot, a->gripper_up_axis, ax3);
+        quat_apply3(dg_rot, a->drawer_up_axis, ax4);
+        const float dot1 = dot3(ax1, ax2), dot2 = dot3(ax3, ax4);
+        const float sg1 = (float)((dot1 > 0.0f) - (dot1 < 0.0f)), sg2 = (float)((dot2 > 0.0f) - (dot2 < 0.0f));
+        const float rot_reward = 0.5f * (sg1 * (dot1 * dot1) + sg2 * (dot2 * dot2));
+        const int around = lf[2] > dg_pos[2] && rf[2] < dg_pos[2];
+        const float around_handle_reward = around ? 0.0f + 0.5f : 0.0f;
+        const float lfd = fabsf(lf[2] - dg_pos[2]), rfd = fabsf(rf[2] - dg_pos[2]);
+        const float finger_dist_reward = around ? (0.04f - lfd) + (0.04f - rfd) : 0.0f;
+        float sq[9];
+        for (int j = 0; j < 9; ++j) { const float x = a->actions[(size_t)e * 9 + j]; sq[j] = x * x; }
+        const float action_penalty = row_sum(sq, 9);
+        const float open_reward = cab_pos * around_handle_reward + cab_pos;
+        float rew = ((((a->dist_reward_scale * dist_reward + a->rot_reward_scale * rot_reward) +
+                       a->around_handle_reward_scale * around_handle_reward) + a->open_reward_scale * open_reward) +
+                     a->finger_dist_reward_scale * finger_dist_reward) - a->action_penalty_scale * action_penalty;
+        if (cab_pos > 0.01f) rew = rew + 0.5f;
+        if (cab_pos > 0.2f) rew = rew + around_handle_reward;
+        if (cab_pos > 0.39f) rew = rew + (2.0f * around_handle_reward);
+        if (lf[0] < dg_pos[0] - a->distX_offset) rew = -1.0f;
+        if (rf[0] < dg_pos[0] - a->distX_offset) rew = -1.0f;
+        if (cab_pos > 0.39f) reset = 1;
+        const int late = (float)progress >= a->max_episode_length - 1.0f;
+        if (late) reset = 1;
+        if (a->obs_clamped)
+            for (int i = 0; i < 23; ++i) a->obs_clamped[(size_t)e * 23 + i] = clamp_obs1(obs[i], a->clip_obs);
+        a->rew_buf[e] = rew;
+        a->reset_buf[e] = reset;
+        a->progress_buf[e] = progress;
+        if (a->timeout_buf) a->timeout_buf[e] = (late && reset != 0) ? 1 : 0;
+    }
+    task_advance(&a->list, &a->rand);
+    return 0;
+}
