@@ -8,6 +8,8 @@ IGE_STATS_ROWS = 32
 IGE_STATS_STRIDE = 32
 IGE_RAND_INJECTED = 0
 IGE_RAND_PHILOX = 1
+IGE_FRANKA_SA_REACH, IGE_FRANKA_SA_STACK2, IGE_FRANKA_SA_STACK = 0, 1, 2
+IGE_FRANKA_SA_COMPONENTS = 12
 
 IGE_OK, IGE_ENULL, IGE_EALIGN, IGE_ESIZE, IGE_EPARAM = 0, -1, -2, -3, -4
 
@@ -213,6 +215,39 @@ class IgeIngenuityArgs(C.Structure):
                 ("initial_root_states", _p), ("actions", _p), ("target_root_positions", _p), ("thrusts", _p),
                 ("forces", _p), ("obs_buf", _p), ("rew_buf", _p), ("reset_buf", _p), ("progress_buf", _p),
                 ("obs_clamped", _p), ("timeout_buf", _p), ("actor_dirty", _p), ("list", IgeResetList)]
+
+
+class IgeFrankaSAArgs(C.Structure):
+    _fields_ = [("variant", _i), ("num_envs", _i), ("num_bodies", _i), ("num_actors", _i), ("eef_body", _i),
+                ("lf_body", _i), ("rf_body", _i), ("cubeA_actor", _i), ("cubeB_actor", _i), ("draw_slot", _i * 7),
+                ("max_episode_length", _f), ("clip_obs", _f), ("cubeA_size", _f), ("cubeB_size", _f),
+                ("table_height", _f), ("cube_xy_center", _f * 2), ("cube_xy_mult", _f), ("cubeA_z_base", _f),
+                ("cubeB_z_base", _f), ("cube_z_range", _f), ("cube_yaw_mult", _f), ("dof_noise_mult", _f),
+                ("min_dist", _f), ("r_dist_scale", _f), ("r_lift_scale", _f), ("r_align_scale", _f),
+                ("r_stack_scale", _f), ("default_dof_pos", _f * 9), ("dof_lower", _f * 9), ("dof_upper", _f * 9),
+                ("rand", IgeTaskRand), ("rigid_body_state", _p), ("root_state", _p), ("dof_state", _p),
+                ("actions", _p), ("pos_control", _p), ("effort_control", _p), ("init_cubeA_state", _p),
+                ("init_cubeB_state", _p), ("obs_buf", _p), ("rew_buf", _p), ("reset_buf", _p), ("progress_buf", _p),
+                ("obs_clamped", _p), ("timeout_buf", _p), ("reward_components", _p), ("reduce_scratch", _p),
+                ("list", IgeResetList)]
+
+
+class IgeFrankaCabinetArgs(C.Structure):
+    _fields_ = [("num_envs", _i), ("num_bodies", _i), ("num_actors", _i), ("num_dofs", _i), ("num_props", _i),
+                ("hand_body", _i), ("drawer_body", _i), ("lfinger_body", _i), ("rfinger_body", _i),
+                ("max_episode_length", _f), ("clip_obs", _f), ("dof_vel_scale", _f), ("target_step", _f),
+                ("action_scale", _f), ("dist_reward_scale", _f), ("rot_reward_scale", _f),
+                ("around_handle_reward_scale", _f), ("open_reward_scale", _f), ("finger_dist_reward_scale", _f),
+                ("action_penalty_scale", _f), ("distX_offset", _f), ("franka_local_grasp_pos", _f * 3),
+                ("franka_local_grasp_rot", _f * 4), ("drawer_local_grasp_pos", _f * 3),
+                ("drawer_local_grasp_rot", _f * 4), ("gripper_forward_axis", _f * 3), ("drawer_inward_axis", _f * 3),
+                ("gripper_up_axis", _f * 3), ("drawer_up_axis", _f * 3), ("default_dof_pos", _f * 9),
+                ("dof_lower", _f * 9), ("dof_upper", _f * 9), ("dof_speed_scales", _f * 9), ("rand", IgeTaskRand),
+                ("rigid_body_states", _p), ("root_state_tensor", _p), ("default_prop_states", _p), ("dof_state", _p),
+                ("actions", _p), ("franka_dof_targets", _p), ("franka_grasp_pos", _p), ("franka_grasp_rot", _p),
+                ("drawer_grasp_pos", _p), ("drawer_grasp_rot", _p), ("obs_buf", _p), ("rew_buf", _p),
+                ("reset_buf", _p), ("progress_buf", _p), ("obs_clamped", _p), ("timeout_buf", _p),
+                ("list", IgeResetList)]
 
 
 class IgeStatsSnapshotArgs(C.Structure):

@@ -31,6 +31,9 @@ _SIGS = {
     "ige_quadcopter_post_physics": (_abi.IgeQuadcopterArgs,),
     "ige_ingenuity_pre_physics": (_abi.IgeIngenuityArgs,),
     "ige_ingenuity_post_physics": (_abi.IgeIngenuityArgs,),
+    "ige_franka_sa_post_physics": (_abi.IgeFrankaSAArgs,),
+    "ige_franka_cabinet_pre_physics": (_abi.IgeFrankaCabinetArgs,),
+    "ige_franka_cabinet_post_physics": (_abi.IgeFrankaCabinetArgs,),
     "ige_stats_snapshot": (_abi.IgeStatsSnapshotArgs,),
 }
 

@@ -16,6 +16,10 @@ _SIM_TENSORS = {
 _SIM_TENSORS["Anymal"] = ["root_states", "dof_state", "contact_forces", "torques"]
 _SIM_TENSORS.update({"BallBalance": ["root_states", "dof_states", "sensor_tensor"], "Quadcopter": ["root_states", "dof_states"],
                      "Ingenuity": ["root_tensor", "dof_states"]})
+_SA_TASKS = {"FrankaReach": "reach", "FrankaCubeStack2": "stack2", "FrankaCubeStack": "stack"}
+for _t in _SA_TASKS:
+    _SIM_TENSORS[_t] = ["rigid_body_state", "root_state", "dof_state"]
+_SIM_TENSORS["FrankaCabinet"] = ["rigid_body_states", "root_state_tensor", "dof_state"]
 _MA_TASKS = {"FrankaReachMA": "reach", "FrankaCollectMA": "collect", "FrankaCombineMA": "combine", "FrankaPPMA": "pp"}
 for _t in _MA_TASKS:
     _SIM_TENSORS[_t] = ["_rigid_body_state", "_root_state", "_dof_state", "_contact_forces"]
@@ -27,11 +31,17 @@ _SYN_NAME = {"Cartpole": "cartpole", "Ant": "ant", "Humanoid": "humanoid", "Shad
              "BallBalance": "ball_balance", "Quadcopter": "quadcopter", "Ingenuity": "ingenuity"}
 for _t, _v in _MA_TASKS.items():
     _SYN_NAME[_t] = "franka_" + _v
+for _t, _v in _SA_TASKS.items():
+    _SYN_NAME[_t] = "franka_sa_" + _v
+_SYN_NAME["FrankaCabinet"] = "franka_cabinet"
+_CFGS["FrankaCabinet"] = synthetic.FRANKA_CABINET_CFG
 
 
 def task_cfg(task):
     if task in _MA_TASKS:
         return synthetic.franka_ma_cfg(_MA_TASKS[task])
+    if task in _SA_TASKS:
+        return synthetic.franka_sa_cfg(_SA_TASKS[task])
     return dict(_CFGS[task])
 
 
@@ -51,7 +61,7 @@ def from_state(task, st, sim_device, rl_device=None, **kw):
     for k in list(st):                      # per-state config overrides travel with the state dict
         if k.startswith("cfg_"):
             v = st[k]
-            if task not in _MA_TASKS:
+            if task not in _MA_TASKS and task not in _SA_TASKS:
                 cfg[k[4:]] = v.item() if v.shape == () and v.dtype.kind in "iuf" else str(v)
     tensors = {k: torch.from_numpy(np.ascontiguousarray(st[k])).to(dev) for k in _SIM_TENSORS[task]}
     sim = SyntheticSim(tensors)

@@ -633,3 +633,159 @@ for _v in FRANKA_VARIANTS:
     MAKERS["franka_" + _v] = (lambda v: (lambda num_envs, seed=0, reset_prob=0.02, **kw: make_franka_ma(
         v, num_envs, seed=seed, reset_prob=reset_prob, **kw)))(_v)
     ADVANCERS["franka_" + _v] = _advance_franka
+
+
+# ---------------------------------------------------------------------------------------------
+# Single-agent Franka tasks (reference: tasks/franka_reach.py, franka_cube_stack2.py,
+# franka_cube_stack.py, franka_cabinet.py and their cfg/task/*.yaml)
+# ---------------------------------------------------------------------------------------------
+FRANKA_SA_VARIANTS = ("reach", "stack2", "stack")
+FRANKA_SA_NUM_OBS = {"reach": 14, "stack2": 21, "stack": 19}
+
+
+def franka_sa_cfg(variant):
+    """Layout + parameters of FrankaReach / FrankaCubeStack2 / FrankaCubeStack.  Actor order of one env: franka
+    (17 links), table, table stand, cubeA[, cubeB] (franka_reach.py:300-330, franka_cube_stack2.py:303-330)."""
+    two = variant != "reach"
+    return dict(
+        variant=variant, num_obs=FRANKA_SA_NUM_OBS[variant], num_actions=7,
+        max_episode_length=300 if variant == "stack" else 150, clip_obs=5.0, clip_actions=1.0,
+        start_position_noise=0.25, start_rotation_noise=0.785, franka_dof_noise=0.25,
+        cubeA_size=0.05, cubeB_size=0.07, table_surface_pos=(0.0, 0.0, 1.025),
+        rand_z_range=0.0 if variant == "stack" else 0.5,
+        r_dist_scale=0.1, r_lift_scale=1.5, r_align_scale=2.0, r_stack_scale=16.0,
+        num_actors=5 if two else 4, num_bodies=FRANKA_LINKS + (4 if two else 3), num_dofs=9,
+        eef_body=FRANKA_LINK_GRIP_SITE, lf_body=15, rf_body=16, cubeA_actor=3, cubeB_actor=4 if two else 3)
+
+
+def _franka_sa_sim_draw(st, g, cfg):
+    n, v = st["progress_buf"].shape[0], cfg["variant"]
+    nb, na = cfg["num_bodies"], cfg["num_actors"]
+    rb = np.zeros((n, nb, 13), F32)
+    rb[:, :, 0:2] = g.uniform(-0.5, 0.5, (n, nb, 2))
+    rb[:, :, 2] = g.uniform(1.0, 1.6, (n, nb))
+    rb[:, :, 3:7] = _rand_unit_quats(g, n * nb).reshape(n, nb, 4)
+    rb[:, :, 7:13] = g.standard_normal((n, nb, 6))
+    root = np.zeros((n, na, 13), F32)
+    root[:, :, 6] = 1.0
+    A = root[:, cfg["cubeA_actor"]]
+    A[:, 0:2] = g.uniform(-0.25, 0.25, (n, 2))
+    A[:, 2] = 1.05 + g.uniform(0.0, 0.5, n)
+    A[:, 3:7] = _rand_unit_quats(g, n)
+    A[:, 7:13] = g.normal(0, 0.2, (n, 6))
+    if v != "reach":
+        B = root[:, cfg["cubeB_actor"]]
+        B[:, 0:2] = g.uniform(-0.25, 0.25, (n, 2))
+        B[:, 2] = 1.06 + g.uniform(0.0, 0.05, n)
+        B[:, 3:7] = _rand_unit_quats(g, n)
+        # cube A hovering over / resting on cube B: FSM states 4-6 of Stack2, the stack success of Stack
+        near = g.random(n) < 0.45
+        off = np.zeros((n, 3), F32)
+        off[:, 0:2] = g.uniform(-0.03, 0.03, (n, 2))
+        off[:, 2] = g.uniform(0.03, 0.12, n)
+        exact = g.random(n) < 0.4
+        off[exact, 0:2] = g.uniform(-0.012, 0.012, (int(exact.sum()), 2))
+        off[exact, 2] = 0.06 + g.uniform(-0.004, 0.004, int(exact.sum()))
+        A[near, 0:3] = (B[:, 0:3] + off)[near]
+        rest = near & exact & (g.random(n) < 0.5)          # cube B on the table, A on top: |height - target| < 0.02
+        B[rest, 2] = 1.025 + 0.035
+        A[rest, 2] = 1.025 + 0.07 + 0.025 + g.uniform(-0.01, 0.01, int(rest.sum()))
+    on = g.random(n) < 0.4                                 # gripper on the cube: FSM >= 1
+    rb[on, cfg["eef_body"], 0:3] = (A[:, 0:3] + g.uniform(-0.018, 0.018, (n, 3)).astype(F32))[on]
+    for b in (cfg["lf_body"], cfg["rf_body"]):
+        rb[:, b, 0:3] = rb[:, cfg["eef_body"], 0:3] + g.uniform(-0.05, 0.05, (n, 3)).astype(F32)
+    st["rigid_body_state"], st["root_state"] = rb, root
+    dof = np.zeros((n, 9, 2), F32)
+    dof[:, :, 0] = g.uniform(FRANKA_DOF_LOWER, FRANKA_DOF_UPPER, (n, 9))
+    dof[:, :, 1] = g.normal(0, 1, (n, 9))
+    st["dof_state"] = dof
+    st["actions"] = g.uniform(-1.3, 1.3, (n, 7)).astype(F32)
+
+
+def make_franka_sa(variant, num_envs, seed=0, reset_prob=0.02, fall_frac=None):
+    cfg, g, n = franka_sa_cfg(variant), _rng(seed), num_envs
+    st = {"cfg_variant": np.array(variant), "progress_buf": _progress(g, n, cfg["max_episode_length"]),
+          "reset_buf": _resets(g, n, reset_prob)}
+    _franka_sa_sim_draw(st, g, cfg)
+    st["pos_control"] = g.normal(0, 1, (n, 9)).astype(F32)
+    st["effort_control"] = g.normal(0, 1, (n, 9)).astype(F32)
+    st["init_cubeA_state"] = np.zeros((n, 13), F32)
+    st["init_cubeB_state"] = np.zeros((n, 13), F32)
+    return st
+
+
+def _advance_franka_sa(st, g):
+    _franka_sa_sim_draw(st, g, franka_sa_cfg(str(st["cfg_variant"])))
+
+
+for _v in FRANKA_SA_VARIANTS:
+    MAKERS["franka_sa_" + _v] = (lambda v: (lambda num_envs, seed=0, reset_prob=0.02, **kw: make_franka_sa(
+        v, num_envs, seed=seed, reset_prob=reset_prob, **kw)))(_v)
+    ADVANCERS["franka_sa_" + _v] = _advance_franka_sa
+
+# franka_panda.urdf (11 bodies, 9 DOFs) + sektion_cabinet_2.urdf (5 bodies, 4 DOFs) + props; franka_cabinet.py:139-330
+FRANKA_CABINET_CFG = dict(
+    num_obs=23, num_actions=9, max_episode_length=500, clip_obs=5.0, clip_actions=1.0, dt=0.0166,
+    action_scale=7.5, dof_vel_scale=0.1, dist_reward_scale=2.0, rot_reward_scale=0.5, around_handle_reward_scale=0.25,
+    open_reward_scale=7.5, finger_dist_reward_scale=5.0, action_penalty_scale=0.01, distX_offset=0.04,
+    num_props=16, num_dofs=13, num_bodies=11 + 5 + 16, num_actors=2 + 16,
+    hand_body=8, lfinger_body=9, rfinger_body=10, drawer_body=11 + 3,
+    default_dof_pos=[1.157, -1.066, -0.155, -2.239, -1.841, 1.003, 0.469, 0.035, 0.035],   # franka_cabinet.py:110
+    dof_speed_scales=[1.0] * 7 + [0.1, 0.1],                                                # :253-254
+    # compute_grasp_transforms inputs (:300-326): grasp pose between the finger pads, drawer handle offset
+    franka_local_grasp_pos=[0.0, 0.04, 0.0584], franka_local_grasp_rot=[0.0, 0.0, 0.0, 1.0],
+    drawer_local_grasp_pos=[0.3, 0.01, 0.0], drawer_local_grasp_rot=[0.0, 0.0, 0.0, 1.0],
+    gripper_forward_axis=[0, 0, 1], drawer_inward_axis=[-1, 0, 0], gripper_up_axis=[0, 1, 0], drawer_up_axis=[0, 0, 1])
+
+
+def _franka_cabinet_sim_draw(st, g):
+    cfg, n = FRANKA_CABINET_CFG, st["progress_buf"].shape[0]
+    nb = cfg["num_bodies"]
+    rb = np.zeros((n, nb, 13), F32)
+    rb[:, :, 0:3] = g.uniform(-0.6, 0.6, (n, nb, 3)) + np.array([0, 0, 0.6], F32)
+    rb[:, :, 3:7] = _rand_unit_quats(g, n * nb).reshape(n, nb, 4)
+    rb[:, :, 7:13] = g.standard_normal((n, nb, 6))
+    # half of the hands sit at the drawer handle with a nearly aligned gripper (around-handle / finger terms)
+    near = g.random(n) < 0.5
+    k = int(near.sum())
+    small = np.zeros((k, 4), F32)
+    small[:, 0:3] = g.normal(0, 0.05, (k, 3))
+    small[:, 3] = 1.0
+    small /= np.linalg.norm(small, axis=1, keepdims=True)
+    rb[near, cfg["drawer_body"], 3:7] = small
+    rb[near, cfg["hand_body"], 0:3] = rb[near, cfg["drawer_body"], 0:3] + np.array([0.3, 0.0, -0.05], F32) + \
+        g.normal(0, 0.03, (k, 3)).astype(F32)
+    for b, dz in ((cfg["lfinger_body"], 0.03), (cfg["rfinger_body"], -0.03)):
+        rb[near, b, 0:3] = rb[near, cfg["drawer_body"], 0:3] + np.array([0.3, 0.01, dz], F32) + \
+            g.normal(0, 0.02, (k, 3)).astype(F32)
+    st["rigid_body_states"] = rb
+    root = np.zeros((n, cfg["num_actors"], 13), F32)
+    root[:, :, 0:3] = g.uniform(-1, 1, (n, cfg["num_actors"], 3))
+    root[:, :, 6] = 1.0
+    st["root_state_tensor"] = root
+    dof = np.zeros((n, cfg["num_dofs"], 2), F32)
+    dof[:, :9, 0] = g.uniform(FRANKA_DOF_LOWER, FRANKA_DOF_UPPER, (n, 9))
+    dof[:, 9:, 0] = g.uniform(0.0, 0.45, (n, 4))                  # drawer opening straddles 0.01 / 0.2 / 0.39
+    dof[:, :, 1] = g.normal(0, 1, (n, cfg["num_dofs"]))
+    st["dof_state"] = dof
+    st["actions"] = g.uniform(-1.3, 1.3, (n, 9)).astype(F32)
+
+
+def make_franka_cabinet(num_envs, seed=0, reset_prob=0.02, fall_frac=None):
+    cfg, g, n = FRANKA_CABINET_CFG, _rng(seed), num_envs
+    st = {"progress_buf": _progress(g, n, cfg["max_episode_length"]), "reset_buf": _resets(g, n, reset_prob)}
+    _franka_cabinet_sim_draw(st, g)
+    st["default_prop_states"] = g.uniform(-1, 1, (n, cfg["num_props"], 13)).astype(F32)
+    lo, hi = FRANKA_DOF_LOWER, FRANKA_DOF_UPPER
+    tg = np.zeros((n, cfg["num_dofs"]), F32)
+    tg[:, :9] = g.uniform(lo - 0.05, hi + 0.05, (n, 9))
+    st["franka_dof_targets"] = tg
+    return st
+
+
+def _advance_franka_cabinet(st, g):
+    _franka_cabinet_sim_draw(st, g)
+
+
+MAKERS["franka_cabinet"] = make_franka_cabinet
+ADVANCERS["franka_cabinet"] = _advance_franka_cabinet

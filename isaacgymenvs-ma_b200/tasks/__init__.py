@@ -11,9 +11,11 @@ from .locomotion import Ant, Humanoid  # noqa: F401
 from .shadow_hand import ShadowHand  # noqa: F401
 from .anymal import Anymal  # noqa: F401
 from .small import BallBalance, Ingenuity, Quadcopter  # noqa: F401
+from .franka_sa import FrankaCabinet, FrankaCubeStack, FrankaCubeStack2, FrankaReach  # noqa: F401
 from .franka_ma import FrankaCollectMA, FrankaCombineMA, FrankaPPMA, FrankaReachMA  # noqa: F401
 
 task_map = {"Cartpole": Cartpole, "Ant": Ant, "Humanoid": Humanoid, "ShadowHand": ShadowHand,
             "FrankaReachMA": FrankaReachMA, "FrankaCollectMA": FrankaCollectMA, "FrankaCombineMA": FrankaCombineMA,
             "FrankaPPMA": FrankaPPMA, "Anymal": Anymal, "BallBalance": BallBalance, "Quadcopter": Quadcopter,
-            "Ingenuity": Ingenuity}
+            "Ingenuity": Ingenuity, "FrankaReach": FrankaReach, "FrankaCubeStack2": FrankaCubeStack2,
+            "FrankaCubeStack": FrankaCubeStack, "FrankaCabinet": FrankaCabinet}

@@ -659,3 +659,95 @@ def test_small_task_argument_checks():
     ing.emit_list = False
     with pytest.raises(H.pkg._lib.IgeError):
         ing.pre(None)
+
+
+# ------------------------------------------------------------------------------------------------------------
+# FrankaReach / FrankaCubeStack2 / FrankaCubeStack / FrankaCabinet (csrc/franka_sa.cu)
+# ------------------------------------------------------------------------------------------------------------
+FRANKA_SA_TASKS = ["franka_sa_reach", "franka_sa_stack2", "franka_sa_stack", "franka_cabinet"]
+
+
+@pytest.mark.parametrize("task", FRANKA_SA_TASKS)
+def test_franka_sa_matches_reference_golden(task):
+    """CUDA post_physics (+ FrankaCabinet pre_physics) against the reference's own VecTask.step outputs
+    (gen_golden_franka_sa.py): ids / flags / counters / reset DOF rows bit-exact, obs / rewards / component means 1e-5."""
+    import franka_sa_harness as F
+    files = F.golden_files(task)
+    assert len(files) >= 3
+    for path in files:
+        blob = H.load_golden(path)
+        for s, got, ref in F.run_fixture(blob, task, "cuda:0"):
+            F.compare(got, ref, f"{os.path.basename(path)} step{s}")
+
+
+@pytest.mark.parametrize("task", FRANKA_SA_TASKS)
+@pytest.mark.parametrize("n,reset_prob,mode", [(16384, 0.02, "injected"), (16384, 0.02, "philox"), (4099, 1.0, "injected"),
+                                               (262144, 0.3, "philox"), (1000, 0.0, "injected"), (33, 0.5, "philox"),
+                                               (1, 1.0, "philox")])
+def test_franka_sa_matches_oracle(task, n, reset_prob, mode):
+    """CUDA vs oracle on the same seeded state over 3 chained control steps: ids / flags / counters bit-exact, reset
+    rows bit-exact (cube quaternions 1e-5: sinf / cosf), observations / rewards 1e-5.  Philox mode: the oracle
+    implements the same counter-based generator (FrankaCubeStack: including the check_valid retry draws)."""
+    import franka_sa_harness as F
+    syn = H.pkg.synthetic
+    st = syn.make_state(task, n, seed=n % 1013 + 5, reset_prob=reset_prob)
+    cpu, gpu = F.State(task, n, "cpu"), F.State(task, n, "cuda:0")
+    rng = np.random.Generator(np.random.PCG64(n + 29))
+    for dev in (cpu, gpu):
+        dev.load_state(st)
+    total = 0
+    for step in range(3):
+        k = int((cpu.reset_buf != 0).sum())
+        total += k
+        rands = F.np_draws(task, rng, k) if mode == "injected" else None
+        for dev in (cpu, gpu):
+            dev.pre()
+        ids_c, ids_g = cpu.post(rands, seed=77), gpu.post(rands, seed=77)
+        assert len(ids_c) == k
+        H.assert_equal(f"{task} reset ids step{step}", ids_g, ids_c)
+        names = F.OUT[task] + ("reset_buf", "progress_buf", "time_outs")
+        F.compare(gpu.get(names), cpu.get(names), f"{task} n={n} step{step}")
+        if task in ("franka_sa_reach", "franka_sa_stack2"):
+            H.assert_float_close(f"{task} reward components", gpu.reward_components.cpu().numpy(),
+                                 cpu.reward_components.numpy(), rtol=2e-4)   # fp32 atomics vs fp64 sums
+        assert int(gpu.rng_step) == int(cpu.rng_step) == (step + 1 if mode == "philox" else 0)
+        syn.advance_physics(task, st, rng)
+        for dev in (cpu, gpu):
+            dev.load(**{name: st[name] for name in F.PHYS[task]})
+            dev.load(actions=np.clip(st["actions"], -1, 1))
+    if reset_prob > 0 and n > 100:
+        assert total > 0
+
+
+@pytest.mark.parametrize("task,name", [("franka_sa_reach", "FrankaReach"), ("franka_sa_stack2", "FrankaCubeStack2"),
+                                       ("franka_sa_stack", "FrankaCubeStack"), ("franka_cabinet", "FrankaCabinet")])
+def test_franka_sa_mirror_step(task, name):
+    """factory.from_state() -> <Task>.step(): the VecTask return tuple, the recorded indexed sim calls and every buffer
+    against the oracle driven from the same synthetic state (Philox reset noise on both sides)."""
+    import franka_sa_harness as F
+    n, seed = 3000, 7
+    st = H.pkg.synthetic.make_state(task, n, seed=seed, reset_prob=0.1)
+    env = H.pkg.factory.from_state(name, st, "cuda:0", rand_mode="philox", seed=seed)
+    cpu = F.State(task, n, "cpu")
+    cpu.load_state(st)
+    cpu.pre()
+    ids_ref = cpu.post(None, seed=seed)
+    env.sim.record = True
+    obs_dict, rew, reset, extras = env.step(torch.from_numpy(st["actions"]).to("cuda:0"))
+    torch.cuda.synchronize()
+    k = int(env.reset_count)
+    H.assert_equal("reset ids", env.reset_env_ids[:k].cpu().numpy(), ids_ref)
+    got = {"obs_buf": env.obs_buf.cpu().numpy(), "rew_buf": rew.cpu().numpy(), "obs_clamped": obs_dict["obs"].cpu().numpy(),
+           "reset_buf": reset.cpu().numpy(), "progress_buf": env.progress_buf.cpu().numpy(),
+           "time_outs": extras["time_outs"].cpu().numpy().astype(np.uint8)}
+    if task == "franka_cabinet":
+        got.update(dof_state=env.dof_state.cpu().numpy(), franka_dof_targets=env.franka_dof_targets.cpu().numpy(),
+                   root_state_tensor=env.root_state_tensor.cpu().numpy())
+    else:
+        got.update(dof_state=env._dof_state.cpu().numpy(), root_state=env._root_state.cpu().numpy(),
+                   pos_control=env._pos_control.cpu().numpy(), init_cubeA_state=env._init_cubeA_state.cpu().numpy())
+    F.compare(got, cpu.get(tuple(got)), f"{task} mirror")
+    names = [c[0] for c in env.sim.calls]
+    assert "set_dof_state_tensor_indexed" in names and "set_actor_root_state_tensor_indexed" in names
+    with pytest.raises(H.pkg._lib.IgeError):
+        H.pkg.factory.from_state(name, st, "cpu").post_physics_step()
