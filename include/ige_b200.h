@@ -196,6 +196,12 @@ int ige_humanoid_post_physics(const IgeLocomotionParams *p, const IgeLocomotionB
 #define IGE_HAND_OBS_FULL_NO_VEL 1  /* 77  (:499-510) */
 #define IGE_HAND_OBS_FULL 2         /* 157 (:511-526) */
 #define IGE_HAND_OBS_FULL_STATE 3   /* 211 (:557-584) */
+/* AllegroHand (tasks/allegro_hand.py): same entry points, 16 DOFs / 16 actions, no fingertip or
+ * force-sensor segments; reset_idx (:507-573), reset_target_pose (:491-505) and compute_hand_reward (:664-729) are
+ * ShadowHand's.  The asymmetric states_buf is then the 88-wide full_state layout (:452-469). */
+#define IGE_HAND_OBS_ALLEGRO_FULL_NO_VEL 4  /* 50  (allegro_hand.py:439-449) */
+#define IGE_HAND_OBS_ALLEGRO_FULL 5         /* 72  (:450-465) */
+#define IGE_HAND_OBS_ALLEGRO_FULL_STATE 6   /* 88  (:470-489) */
 #define IGE_HAND_NUM_FINGERTIPS 5
 
 /* Uniforms of the four torch.rand draws of the pre-physics reset, in the reference's order:

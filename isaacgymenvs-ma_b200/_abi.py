@@ -70,6 +70,7 @@ class IgeLocomotionBuffers(C.Structure):
 
 
 IGE_HAND_OBS = {"openai": 0, "full_no_vel": 1, "full": 2, "full_state": 3}
+IGE_HAND_OBS_ALLEGRO = {"full_no_vel": 4, "full": 5, "full_state": 6}
 
 
 class IgeHandResetRand(C.Structure):

@@ -3,7 +3,7 @@
 // One thread per env; per env the whole state is ONE 16-byte dof_state row (cart pos, cart vel,
 // pole pos, pole vel), so a warp reads 512 contiguous bytes with one LDG.128 per thread and writes
 // obs the same way.  Algorithmic traffic 68 B/env: HBM-bound, no staging needed.
-// The grid is capped at the resident capacity (148 SMs x 8 CTAs) and the warps stride over the
+// The grid is capped at the resident capacity (SM count x 8 CTAs) and the warps stride over the
 // 32-env tiles: statistics and the retirement ticket are then a few atomics per CTA, not per 128 envs
 // (32 k CTAs bumping one counter serialised 4 M-env launches to 20 % of the HBM roofline).
 #include "ige_common.cuh"
@@ -11,7 +11,7 @@
 namespace {
 
 constexpr int kThreads = 256;
-constexpr int kMaxCtas = 148 * 8;
+constexpr int kCtasPerSm = 8;   // 8 x 256 threads = the SM's 2048 thread slots
 
 __global__ void __launch_bounds__(kThreads) cartpole_post_physics_kernel(IgeCartpoleParams p, IgeCartpoleBuffers b) {
     const uint64_t step = ige::load_step(p.rand);
@@ -87,7 +87,13 @@ extern "C" int ige_cartpole_post_physics(const IgeCartpoleParams *p, const IgeCa
     if (int rc = ige_check_list(b->list)) return rc;
     if (int rc = ige_check_rand(p->rand)) return rc;
     if (p->num_envs == 0) return IGE_OK;
-    const int grid = min((p->num_envs + kThreads - 1) / kThreads, kMaxCtas);
+    static int sms[IGE_MAX_DEVICES];
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= IGE_MAX_DEVICES) return ige_fail(IGE_EPARAM, "device ordinal %d not supported", dev);
+    if (sms[dev] == 0 && (cudaDeviceGetAttribute(&sms[dev], cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms[dev] < 1))
+        sms[dev] = 1;
+    const int grid = min((p->num_envs + kThreads - 1) / kThreads, sms[dev] * kCtasPerSm);
     cartpole_post_physics_kernel<<<grid, kThreads, 0, (cudaStream_t)stream>>>(*p, *b);
     return ige_check_launch("ige_cartpole_post_physics");
 }

@@ -14,7 +14,7 @@
 namespace {
 
 constexpr int kThreads = 256;
-constexpr int kMaxCtas = 148 * 8;
+constexpr int kCtasPerSm = 8;
 
 __device__ __forceinline__ float clamp_sym(float x, float c) { return fminf(fmaxf(x, -c), c); }  // torch.clamp
 
@@ -81,8 +81,14 @@ __global__ void __launch_bounds__(kThreads) hand_targets_kernel(const __grid_con
 }
 
 int grid_for(long long items) {
-    long long g = (items + kThreads - 1) / kThreads;
-    return (int)(g < 1 ? 1 : (g > kMaxCtas ? kMaxCtas : g));
+    static int sms = 0;   // grid-stride cap: SM count x 8 CTAs
+    if (sms == 0) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms < 1) sms = 1;
+    }
+    const long long g = (items + kThreads - 1) / kThreads, cap = (long long)sms * kCtasPerSm;
+    return (int)(g < 1 ? 1 : (g > cap ? cap : g));
 }
 
 }  // namespace

@@ -29,7 +29,7 @@ enum Seg { SEG_DOF_POS, SEG_DOF_VEL, SEG_DOF_FORCE, SEG_OBJ_POSE, SEG_OBJ_POS, S
            SEG_GOAL_POSE, SEG_QUAT_DIFF, SEG_FT_STATE, SEG_FT_POS, SEG_SENSORS, SEG_ACTIONS, SEG_END };
 struct SegEntry { int kind, off; };
 // shadow_hand.py:473-584
-__constant__ SegEntry kLayout[4][12] = {
+__constant__ SegEntry kLayout[7][12] = {
     {{SEG_FT_POS, 0}, {SEG_OBJ_POS, 15}, {SEG_QUAT_DIFF, 18}, {SEG_ACTIONS, 22}, {SEG_END, 42}},
     {{SEG_DOF_POS, 0}, {SEG_OBJ_POSE, 24}, {SEG_GOAL_POSE, 31}, {SEG_QUAT_DIFF, 38}, {SEG_FT_POS, 42}, {SEG_ACTIONS, 57},
      {SEG_END, 77}},
@@ -37,8 +37,21 @@ __constant__ SegEntry kLayout[4][12] = {
      {SEG_GOAL_POSE, 61}, {SEG_QUAT_DIFF, 68}, {SEG_FT_STATE, 72}, {SEG_ACTIONS, 137}, {SEG_END, 157}},
     {{SEG_DOF_POS, 0}, {SEG_DOF_VEL, 24}, {SEG_DOF_FORCE, 48}, {SEG_OBJ_POSE, 72}, {SEG_OBJ_LINVEL, 79},
      {SEG_OBJ_ANGVEL, 82}, {SEG_GOAL_POSE, 85}, {SEG_QUAT_DIFF, 92}, {SEG_FT_STATE, 96}, {SEG_SENSORS, 161},
-     {SEG_ACTIONS, 191}, {SEG_END, 211}}};
-__host__ __device__ constexpr int hand_num_obs(int type) { return type == 0 ? 42 : type == 1 ? 77 : type == 2 ? 157 : 211; }
+     {SEG_ACTIONS, 191}, {SEG_END, 211}},
+    // AllegroHand (allegro_hand.py:439-489): 16 DOFs, 16 actions, no fingertip / sensor segments
+    {{SEG_DOF_POS, 0}, {SEG_OBJ_POSE, 16}, {SEG_GOAL_POSE, 23}, {SEG_QUAT_DIFF, 30}, {SEG_ACTIONS, 34}, {SEG_END, 50}},
+    {{SEG_DOF_POS, 0}, {SEG_DOF_VEL, 16}, {SEG_OBJ_POSE, 32}, {SEG_OBJ_LINVEL, 39}, {SEG_OBJ_ANGVEL, 42},
+     {SEG_GOAL_POSE, 45}, {SEG_QUAT_DIFF, 52}, {SEG_ACTIONS, 56}, {SEG_END, 72}},
+    {{SEG_DOF_POS, 0}, {SEG_DOF_VEL, 16}, {SEG_DOF_FORCE, 32}, {SEG_OBJ_POSE, 48}, {SEG_OBJ_LINVEL, 55},
+     {SEG_OBJ_ANGVEL, 58}, {SEG_GOAL_POSE, 61}, {SEG_QUAT_DIFF, 68}, {SEG_ACTIONS, 72}, {SEG_END, 88}}};
+__host__ __device__ constexpr int hand_num_obs(int type) {
+    return type == 0 ? 42 : type == 1 ? 77 : type == 2 ? 157 : type == 3 ? 211 : type == 4 ? 50 : type == 5 ? 72 : 88;
+}
+// layout of the asymmetric states_buf: the hand's own full_state (shadow_hand.py:529-556, allegro_hand.py:452-469)
+__host__ __device__ constexpr int hand_state_layout(int type) {
+    return type >= IGE_HAND_OBS_ALLEGRO_FULL_NO_VEL ? IGE_HAND_OBS_ALLEGRO_FULL_STATE : IGE_HAND_OBS_FULL_STATE;
+}
+__host__ __device__ constexpr bool hand_is_allegro(int type) { return type >= IGE_HAND_OBS_ALLEGRO_FULL_NO_VEL; }
 
 __device__ __forceinline__ float clampf(float x, float c) { return x < -c ? -c : (x > c ? c : x); }
 
@@ -297,8 +310,9 @@ __global__ void __launch_bounds__(NT) shadow_hand_post_physics_kernel(const __gr
                                                                       const int expected_ctas) {
     extern __shared__ __align__(128) float smem[];
     const int nobs = hand_num_obs(p.obs_type);
+    const int slay = hand_state_layout(p.obs_type), nst = hand_num_obs(slay);
     float *obs_tile = smem;                                             // TE * nobs
-    float *st_tile = smem + ((TE * nobs + 31) / 32) * 32;               // TE * 211 when asymmetric
+    float *st_tile = smem + ((TE * nobs + 31) / 32) * 32;               // TE * (211 | 88) when asymmetric
     __shared__ int s_last;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int e0 = (tile0 + blockIdx.x) * TE;
@@ -306,7 +320,7 @@ __global__ void __launch_bounds__(NT) shadow_hand_post_physics_kernel(const __gr
     const bool bulk = use_tma && (ne % 4 == 0);
 
     fill_tile(p, b, p.obs_type, nobs, obs_tile, e0, ne);
-    if (p.asymmetric_obs) fill_tile(p, b, IGE_HAND_OBS_FULL_STATE, MAX_OBS, st_tile, e0, ne);
+    if (p.asymmetric_obs) fill_tile(p, b, slay, nst, st_tile, e0, ne);
 
     // ---- warp 0: per-env object / goal math, reward, flags (compute_hand_reward :746-800) ----
     int my_resets = 0;
@@ -326,7 +340,7 @@ __global__ void __launch_bounds__(NT) shadow_hand_post_physics_kernel(const __gr
             ige::quat_conjugate(goal + 3, conj);
             ige::quat_mul(obj + 3, conj, qd);
             fill_env_segments(p, p.obs_type, nobs, obs_tile + lane * nobs, obj, goal, qd);
-            if (p.asymmetric_obs) fill_env_segments(p, IGE_HAND_OBS_FULL_STATE, MAX_OBS, st_tile + lane * MAX_OBS, obj, goal, qd);
+            if (p.asymmetric_obs) fill_env_segments(p, slay, nst, st_tile + lane * nst, obj, goal, qd);
 
             long long progress = b.progress_buf[e] + 1;  // :711
             if (b.randomize_buf) b.randomize_buf[e] += 1;
@@ -398,8 +412,8 @@ __global__ void __launch_bounds__(NT) shadow_hand_post_physics_kernel(const __gr
     store_tile(b.obs_buf + (size_t)e0 * nobs, b.obs_clamped ? b.obs_clamped + (size_t)e0 * nobs : nullptr, obs_tile,
                ne * nobs, p.clip_obs, bulk);
     if (p.asymmetric_obs)
-        store_tile(b.states_buf + (size_t)e0 * MAX_OBS, b.states_clamped ? b.states_clamped + (size_t)e0 * MAX_OBS : nullptr,
-                   st_tile, ne * MAX_OBS, p.clip_obs, bulk);
+        store_tile(b.states_buf + (size_t)e0 * nst, b.states_clamped ? b.states_clamped + (size_t)e0 * nst : nullptr,
+                   st_tile, ne * nst, p.clip_obs, bulk);
     if (bulk && tid == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
 
     finish_hand_reduction(p, b, expected_ctas, &s_last);
@@ -416,21 +430,23 @@ __global__ void __launch_bounds__(NT) shadow_hand_post_physics_kernel(const __gr
 // only then scatters them into the shared (32 x num_obs) tile, so a tile costs two dependent DRAM
 // round trips (object_indices -> object row is the second) instead of ~12.  Per-CTA partial sums stay in
 // registers across tiles: 3 global atomics per CTA, not per tile.
-constexpr int FD = 24, FA = 20, FS = 30, FT_N = 5;
+// AllegroHand (layouts 4-6) is the same kernel instantiated with 16 DOFs / 16 actions and no sensor / fingertip columns.
+constexpr int FS = 30, FT_N = 5;
 constexpr int kFastCtasPerSm = 4;
 constexpr int FNT = 256;       // threads per CTA of the fast kernel
 constexpr int CT = FNT - 32;   // element threads (warp 0 is the env warp)
-// column-owner mapping: SUB threads share a column and split the 32 envs of the tile between them
-constexpr int DSUB = CT / FD, SSUB = CT / FS;
-constexpr int KD = (TE + DSUB - 1) / DSUB, KS = (TE + SSUB - 1) / SSUB;   // loads per thread: DOF rows, sensor floats
-static_assert(TE * FD / 4 <= CT && TE * FA / 4 <= CT, "fast kernel: one vector per thread for force / actions");
+__host__ __device__ constexpr int fast_dofs(int layout) { return hand_is_allegro(layout) ? 16 : 24; }
+__host__ __device__ constexpr int fast_actions(int layout) { return hand_is_allegro(layout) ? 16 : 20; }
 struct SegOff { int dof_pos, dof_vel, dof_force, ft_state, ft_pos, sensors, actions; };
-// element-segment offsets of the four layouts (shadow_hand.py:473-584; same numbers as kLayout), compile-time
+// element-segment offsets of the layouts (shadow_hand.py:473-584, allegro_hand.py:439-489; same numbers as kLayout)
 __host__ __device__ constexpr SegOff seg_offsets(int layout) {
     return layout == 0 ? SegOff{-1, -1, -1, -1, 0, -1, 22}
          : layout == 1 ? SegOff{0, -1, -1, -1, 42, -1, 57}
          : layout == 2 ? SegOff{0, 24, -1, 72, -1, -1, 137}
-                       : SegOff{0, 24, 48, 96, -1, 161, 191};
+         : layout == 3 ? SegOff{0, 24, 48, 96, -1, 161, 191}
+         : layout == 4 ? SegOff{0, -1, -1, -1, -1, -1, 34}
+         : layout == 5 ? SegOff{0, 16, -1, -1, -1, -1, 56}
+                       : SegOff{0, 16, 32, -1, -1, -1, 72};
 }
 
 template <int LAYOUT, bool ASYM>
@@ -440,26 +456,34 @@ shadow_hand_post_physics_fast_kernel(const __grid_constant__ IgeShadowHandParams
                                      const int expected_ctas) {
     extern __shared__ __align__(128) float smem[];
     constexpr int nobs = hand_num_obs(LAYOUT);
+    constexpr int FD = fast_dofs(LAYOUT), FA = fast_actions(LAYOUT);
+    constexpr int SLAY = hand_state_layout(LAYOUT), NST = hand_num_obs(SLAY);   // states_buf: 211 | 88 wide
+    // column-owner mapping: SUB threads share a column and split the 32 envs of the tile between them
+    constexpr int DSUB = CT / FD, SSUB = CT / FS;
+    constexpr int KD = (TE + DSUB - 1) / DSUB, KS = (TE + SSUB - 1) / SSUB;   // loads per thread: DOF rows, sensor floats
+    static_assert(TE * FD / 4 <= CT && TE * FA / 4 <= CT && FD % 4 == 0 && FA % 4 == 0,
+                  "fast kernel: one vector per thread for force / actions");
     float *obs_tile = smem;                                   // TE * nobs
-    float *st_tile = smem + ((TE * nobs + 31) / 32) * 32;     // TE * 211 when asymmetric
+    float *st_tile = smem + ((TE * nobs + 31) / 32) * 32;     // TE * NST when asymmetric
     __shared__ int s_last;
     __shared__ float s_lo[FD], s_hi[FD], s_rspan[FD];
     __shared__ int s_ft[FT_N];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     constexpr bool asym = ASYM;
     constexpr SegOff oo = seg_offsets(LAYOUT);
-    constexpr SegOff so = seg_offsets(IGE_HAND_OBS_FULL_STATE);   // states_buf
+    constexpr SegOff so = seg_offsets(SLAY);   // states_buf
     constexpr bool need_dof = oo.dof_pos >= 0 || oo.dof_vel >= 0 || asym;
     constexpr bool need_force = oo.dof_force >= 0 || asym;
-    constexpr bool need_sens = oo.sensors >= 0 || asym;
-    constexpr bool ft_full = oo.ft_state >= 0 || asym;
+    constexpr bool need_sens = oo.sensors >= 0 || (asym && so.sensors >= 0);
+    constexpr bool need_ft = oo.ft_state >= 0 || oo.ft_pos >= 0 || (asym && so.ft_state >= 0);
+    constexpr bool ft_full = oo.ft_state >= 0 || (asym && so.ft_state >= 0);
     constexpr int FTW = ft_full ? 65 : 15, FTC = ft_full ? 13 : 3;   // fingertip block: 5 x (13 | 3) floats per env
     constexpr int FSUB = CT / FTW, KF = (TE + FSUB - 1) / FSUB;
     if (tid < FD) {
         const float lo = p.dof_lower[tid], hi = p.dof_upper[tid];
         s_lo[tid] = lo; s_hi[tid] = hi; s_rspan[tid] = 1.0f / (hi - lo);
     }
-    if (tid < FT_N) s_ft[tid] = p.fingertip_handles[tid];
+    if (need_ft && tid < FT_N) s_ft[tid] = p.fingertip_handles[tid];
     __syncthreads();
 
     int acc_resets = 0;                      // warp 0, lane == env: partial sums over this CTA's tiles
@@ -489,7 +513,7 @@ shadow_hand_post_physics_fast_kernel(const __grid_constant__ IgeShadowHandParams
             ige::quat_conjugate(goal + 3, conj);
             ige::quat_mul(obj + 3, conj, qd);
             fill_env_segments(p, LAYOUT, nobs, obs_tile + lane * nobs, obj, goal, qd);
-            if (asym) fill_env_segments(p, IGE_HAND_OBS_FULL_STATE, MAX_OBS, st_tile + lane * MAX_OBS, obj, goal, qd);
+            if (asym) fill_env_segments(p, SLAY, NST, st_tile + lane * NST, obj, goal, qd);
         } else {
             // ---- element warps: every load of the tile first, then the scatter into the row-major tile(s).
             //      Each thread owns ONE column of a segment and walks the envs with a fixed stride, so addresses
@@ -515,7 +539,7 @@ shadow_hand_post_physics_fast_kernel(const __grid_constant__ IgeShadowHandParams
                 for (int k = 0; k < KS; ++k) { const int le = ssub + k * SSUB; if (le < TE) sv[k] = __ldg(src + le * FS); }
             }
             if (ct < TE * FA / 4) ac = __ldg(reinterpret_cast<const float4 *>(b.actions + (size_t)e0 * FA) + ct);
-            if (fsub < FSUB) {
+            if (need_ft && fsub < FSUB) {
                 const int f = fc / FTC, kk = fc - f * FTC;
                 const int estride = p.num_bodies * 13;
                 const float *src = b.rigid_body_states + (size_t)e0 * estride + s_ft[f] * 13 + kk;
@@ -533,18 +557,18 @@ shadow_hand_post_physics_fast_kernel(const __grid_constant__ IgeShadowHandParams
                         const float uv = p.vel_obs_scale * dv[k].y;
                         if (oo.dof_pos >= 0) obs_tile[le * nobs + oo.dof_pos + dj] = up;
                         if (oo.dof_vel >= 0) obs_tile[le * nobs + oo.dof_vel + dj] = uv;
-                        if (asym) { st_tile[le * MAX_OBS + so.dof_pos + dj] = up; st_tile[le * MAX_OBS + so.dof_vel + dj] = uv; }
+                        if (asym) { st_tile[le * NST + so.dof_pos + dj] = up; st_tile[le * NST + so.dof_vel + dj] = uv; }
                     }
                 }
             }
             if (need_force && ct < TE * FD / 4) {
                 const float v[4] = {fo.x, fo.y, fo.z, fo.w};
-                const int i = ct * 4, le = i / FD, j = i - le * FD;   // 24 % 4 == 0: one env per vector
+                const int i = ct * 4, le = i / FD, j = i - le * FD;   // FD % 4 == 0: one env per vector
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
                     const float x = p.force_torque_obs_scale * v[q];
                     if (oo.dof_force >= 0) obs_tile[le * nobs + oo.dof_force + j + q] = x;
-                    if (asym) st_tile[le * MAX_OBS + so.dof_force + j + q] = x;
+                    if (asym) st_tile[le * NST + so.dof_force + j + q] = x;
                 }
             }
             if (need_sens && ssub < SSUB) {
@@ -554,7 +578,7 @@ shadow_hand_post_physics_fast_kernel(const __grid_constant__ IgeShadowHandParams
                     if (le < TE) {
                         const float x = p.force_torque_obs_scale * sv[k];
                         if (oo.sensors >= 0) obs_tile[le * nobs + oo.sensors + sj] = x;
-                        if (asym) st_tile[le * MAX_OBS + so.sensors + sj] = x;
+                        if (asym && so.sensors >= 0) st_tile[le * NST + so.sensors + sj] = x;
                     }
                 }
             }
@@ -564,10 +588,10 @@ shadow_hand_post_physics_fast_kernel(const __grid_constant__ IgeShadowHandParams
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
                     obs_tile[le * nobs + oo.actions + j + q] = v[q];
-                    if (asym) st_tile[le * MAX_OBS + so.actions + j + q] = v[q];
+                    if (asym) st_tile[le * NST + so.actions + j + q] = v[q];
                 }
             }
-            if (fsub < FSUB) {
+            if (need_ft && fsub < FSUB) {
                 const int f = fc / FTC, kk = fc - f * FTC;
 #pragma unroll
                 for (int k = 0; k < KF; ++k) {
@@ -576,7 +600,7 @@ shadow_hand_post_physics_fast_kernel(const __grid_constant__ IgeShadowHandParams
                         if (ft_full) {
                             if (oo.ft_state >= 0) obs_tile[le * nobs + oo.ft_state + fc] = ft[k];
                             if (oo.ft_pos >= 0 && kk < 3) obs_tile[le * nobs + oo.ft_pos + f * 3 + kk] = ft[k];
-                            if (asym) st_tile[le * MAX_OBS + so.ft_state + fc] = ft[k];
+                            if (asym && so.ft_state >= 0) st_tile[le * NST + so.ft_state + fc] = ft[k];
                         } else {
                             obs_tile[le * nobs + oo.ft_pos + fc] = ft[k];
                         }
@@ -589,7 +613,7 @@ shadow_hand_post_physics_fast_kernel(const __grid_constant__ IgeShadowHandParams
         // ---- tile out (warp 1 issues the bulk stores; warp 0 goes on with the reward) ----
         if (tid == 32) {
             ige::bulk_s2g(b.obs_buf + (size_t)e0 * nobs, obs_tile, (uint32_t)(TE * nobs) * 4);
-            if (asym) ige::bulk_s2g(b.states_buf + (size_t)e0 * MAX_OBS, st_tile, (uint32_t)(TE * MAX_OBS) * 4);
+            if (asym) ige::bulk_s2g(b.states_buf + (size_t)e0 * NST, st_tile, (uint32_t)(TE * NST) * 4);
             ige::bulk_commit();
         }
         if (warp == 0) {  // compute_hand_reward :746-800
@@ -634,8 +658,8 @@ shadow_hand_post_physics_fast_kernel(const __grid_constant__ IgeShadowHandParams
             for (int i = tid; i < TE * nobs; i += FNT) dc[i] = clampf(obs_tile[i], p.clip_obs);
         }
         if (asym && b.states_clamped) {
-            float *dc = b.states_clamped + (size_t)e0 * MAX_OBS;
-            for (int i = tid; i < TE * MAX_OBS; i += FNT) dc[i] = clampf(st_tile[i], p.clip_obs);
+            float *dc = b.states_clamped + (size_t)e0 * NST;
+            for (int i = tid; i < TE * NST; i += FNT) dc[i] = clampf(st_tile[i], p.clip_obs);
         }
         if (tid == 32) ige::bulk_wait_read_all();
         __syncthreads();  // the tile may be overwritten
@@ -661,11 +685,14 @@ shadow_hand_post_physics_fast_kernel(const __grid_constant__ IgeShadowHandParams
 
 typedef void (*HandFastKernel)(const IgeShadowHandParams, const IgeShadowHandBuffers, const int, const int);
 HandFastKernel fast_kernel(int layout, bool asym) {
-    static const HandFastKernel table[8] = {
+    static const HandFastKernel table[14] = {
         shadow_hand_post_physics_fast_kernel<0, false>, shadow_hand_post_physics_fast_kernel<0, true>,
         shadow_hand_post_physics_fast_kernel<1, false>, shadow_hand_post_physics_fast_kernel<1, true>,
         shadow_hand_post_physics_fast_kernel<2, false>, shadow_hand_post_physics_fast_kernel<2, true>,
-        shadow_hand_post_physics_fast_kernel<3, false>, shadow_hand_post_physics_fast_kernel<3, true>};
+        shadow_hand_post_physics_fast_kernel<3, false>, shadow_hand_post_physics_fast_kernel<3, true>,
+        shadow_hand_post_physics_fast_kernel<4, false>, shadow_hand_post_physics_fast_kernel<4, true>,   // AllegroHand
+        shadow_hand_post_physics_fast_kernel<5, false>, shadow_hand_post_physics_fast_kernel<5, true>,
+        shadow_hand_post_physics_fast_kernel<6, false>, shadow_hand_post_physics_fast_kernel<6, true>};
     return table[layout * 2 + (asym ? 1 : 0)];
 }
 
@@ -675,8 +702,8 @@ int check(const IgeShadowHandParams *p, const IgeShadowHandBuffers *b) {
     if (p->num_hand_dofs < 1 || p->num_hand_dofs > IGE_MAX_DOF || p->num_dofs_per_env < p->num_hand_dofs)
         return ige_fail(IGE_ESIZE, "num_hand_dofs=%d num_dofs_per_env=%d invalid", p->num_hand_dofs, p->num_dofs_per_env);
     if (p->num_actions < 1 || p->num_actions > IGE_MAX_DOF) return ige_fail(IGE_ESIZE, "num_actions=%d invalid", p->num_actions);
-    if (p->obs_type < 0 || p->obs_type > 3) return ige_fail(IGE_EPARAM, "obs_type=%d invalid", p->obs_type);
-    for (int f = 0; f < IGE_HAND_NUM_FINGERTIPS; ++f)
+    if (p->obs_type < 0 || p->obs_type > IGE_HAND_OBS_ALLEGRO_FULL_STATE) return ige_fail(IGE_EPARAM, "obs_type=%d invalid", p->obs_type);
+    for (int f = 0; f < IGE_HAND_NUM_FINGERTIPS && !hand_is_allegro(p->obs_type); ++f)
         if (p->fingertip_handles[f] < 0 || p->fingertip_handles[f] >= p->num_bodies)
             return ige_fail(IGE_ESIZE, "fingertip_handles[%d]=%d outside [0, %d)", f, p->fingertip_handles[f], p->num_bodies);
     IGE_REQUIRE_PTR(b->dof_state);
@@ -711,22 +738,24 @@ extern "C" int ige_shadow_hand_reset(const IgeShadowHandParams *p, const IgeShad
 
 extern "C" int ige_shadow_hand_post_physics(const IgeShadowHandParams *p, const IgeShadowHandBuffers *b, void *stream) {
     if (int rc = check(p, b)) return rc;
-    IGE_REQUIRE_PTR(b->rigid_body_states);
+    const bool allegro = hand_is_allegro(p->obs_type);
+    if (!allegro) IGE_REQUIRE_PTR(b->rigid_body_states);
     IGE_REQUIRE_PTR(b->actions);
     IGE_REQUIRE_PTR(b->obs_buf);
     IGE_REQUIRE_PTR(b->rew_buf);
     IGE_REQUIRE_PTR(b->consecutive_successes);
     if (!b->reduce_scratch) return ige_fail(IGE_ENULL, "reduce_scratch is NULL");
-    const bool need_full = p->obs_type == IGE_HAND_OBS_FULL_STATE || p->asymmetric_obs;
+    const bool need_full = p->obs_type == IGE_HAND_OBS_FULL_STATE || p->obs_type == IGE_HAND_OBS_ALLEGRO_FULL_STATE || p->asymmetric_obs;
     if (need_full) {
-        IGE_REQUIRE_PTR(b->vec_sensor_tensor);
+        if (!allegro) IGE_REQUIRE_PTR(b->vec_sensor_tensor);
         IGE_REQUIRE_PTR(b->dof_force_tensor);
     }
     if (p->asymmetric_obs) IGE_REQUIRE_PTR(b->states_buf);
     IGE_OPTIONAL_PTR(b->obs_clamped);
     if (p->num_envs == 0) return IGE_OK;
     const int nobs = hand_num_obs(p->obs_type);
-    const size_t smem = (size_t)(((TE * nobs + 31) / 32) * 32 + (p->asymmetric_obs ? TE * MAX_OBS : 0)) * sizeof(float);
+    const int nst = hand_num_obs(hand_state_layout(p->obs_type));
+    const size_t smem = (size_t)(((TE * nobs + 31) / 32) * 32 + (p->asymmetric_obs ? TE * nst : 0)) * sizeof(float);
     static bool attr_set = false;
     if (!attr_set) {
         cudaError_t e = cudaFuncSetAttribute(shadow_hand_post_physics_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -736,7 +765,7 @@ extern "C" int ige_shadow_hand_post_physics(const IgeShadowHandParams *p, const 
     }
     static bool fast_attr_set = false;
     if (!fast_attr_set) {
-        for (int i = 0; i < 8; ++i) {
+        for (int i = 0; i < 14; ++i) {
             cudaError_t e = cudaFuncSetAttribute(fast_kernel(i >> 1, i & 1), cudaFuncAttributeMaxDynamicSharedMemorySize,
                                                  (int)((TE * MAX_OBS + 32 + TE * MAX_OBS) * sizeof(float)));
             if (e != cudaSuccess) return ige_fail((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
@@ -745,12 +774,19 @@ extern "C" int ige_shadow_hand_post_physics(const IgeShadowHandParams *p, const 
     }
     const int tiles = (p->num_envs + TE - 1) / TE;
     cudaStream_t s = (cudaStream_t)stream;
-    const bool standard = p->num_hand_dofs == FD && p->num_dofs_per_env == FD && p->num_actions == FA && ige_use_tma() &&
+    const int fd = fast_dofs(p->obs_type), fa = fast_actions(p->obs_type);
+    const bool standard = p->num_hand_dofs == fd && p->num_dofs_per_env == fd && p->num_actions == fa && ige_use_tma() &&
                           ige_fast_paths();
     if (standard) {
         // full tiles: persistent fast kernel; a ragged last tile (num_envs % 32) goes through the generic one
         const int full = p->num_envs / TE, ragged = tiles - full;
-        const int grid = full < 148 * kFastCtasPerSm ? full : 148 * kFastCtasPerSm;
+        static int sms = 0;
+        if (sms == 0) {
+            int dev = 0;
+            cudaGetDevice(&dev);
+            if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms < 1) sms = 1;
+        }
+        const int grid = full < sms * kFastCtasPerSm ? full : sms * kFastCtasPerSm;
         if (full > 0) {
             fast_kernel(p->obs_type, p->asymmetric_obs != 0)<<<grid, FNT, smem, s>>>(*p, *b, full, grid + ragged);
             if (int rc = ige_check_launch("ige_shadow_hand_post_physics(fast)")) return rc;

@@ -13,6 +13,7 @@ _SIM_TENSORS = {
     "Humanoid": ["root_states", "dof_state", "vec_sensor_tensor", "dof_force_tensor"],
     "ShadowHand": ["dof_state", "root_state_tensor", "rigid_body_states", "vec_sensor_tensor", "dof_force_tensor"],
 }
+_SIM_TENSORS["AllegroHand"] = list(_SIM_TENSORS["ShadowHand"])
 _SIM_TENSORS["Anymal"] = ["root_states", "dof_state", "contact_forces", "torques"]
 _SIM_TENSORS.update({"BallBalance": ["root_states", "dof_states", "sensor_tensor"], "Quadcopter": ["root_states", "dof_states"],
                      "Ingenuity": ["root_tensor", "dof_states"]})
@@ -35,6 +36,8 @@ for _t, _v in _SA_TASKS.items():
     _SYN_NAME[_t] = "franka_sa_" + _v
 _SYN_NAME["FrankaCabinet"] = "franka_cabinet"
 _CFGS["FrankaCabinet"] = synthetic.FRANKA_CABINET_CFG
+_SYN_NAME["AllegroHand"] = "allegro_hand"
+_CFGS["AllegroHand"] = synthetic.ALLEGRO_HAND_CFG
 
 
 def task_cfg(task):

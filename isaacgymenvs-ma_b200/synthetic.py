@@ -385,15 +385,20 @@ SHADOW_HAND_CFG = dict(
     fingertip_handles=(7, 11, 15, 20, 25),
     obs_type="full_state", asymmetric_obs=False)
 SHADOW_HAND_NUM_OBS = {"openai": 42, "full_no_vel": 77, "full": 157, "full_state": 211}
+# AllegroHand (tasks/allegro_hand.py; cfg/task/AllegroHand.yaml): ShadowHand's reset / reward code on a 16-DOF hand with all
+# joints actuated, no fingertip or force-sensor observations (allegro_hand.py:108-126, :439-489)
+ALLEGRO_HAND_CFG = dict(SHADOW_HAND_CFG, hand="allegro", num_hand_dofs=16, num_actions=16, num_fingertips=0, num_bodies=8,
+                        fingertip_handles=(0, 0, 0, 0, 0), num_states_full=88)
+ALLEGRO_HAND_NUM_OBS = {"full_no_vel": 50, "full": 72, "full_state": 88}
 # the 20 actuated of the 24 hand DOFs (coupled distal joints are passive in the MJCF)
 SHADOW_HAND_ACTUATED = (0, 1, 2, 3, 4, 6, 7, 8, 10, 11, 12, 14, 15, 16, 17, 19, 20, 21, 22, 23)
 
 
-def _shadow_limits():
+def _shadow_limits(d=24):
     r = _rng(424242)
     lo = r.uniform(-0.8, 0.0, 24).astype(F32)
     hi = r.uniform(0.5, 1.6, 24).astype(F32)
-    return lo, hi
+    return lo[:d].copy(), hi[:d].copy()
 
 
 def _quat_mul_np(a, b):
@@ -434,14 +439,15 @@ def _shadow_sim_draw(st, rng, cfg):
     rb[:, :, 3:7] = _rand_unit_quats(rng, n * b).reshape(n, b, 4)
     rb[:, :, 7:13] = rng.standard_normal((n, b, 6))
     st["rigid_body_states"] = rb
-    st["vec_sensor_tensor"] = rng.normal(0.0, 0.3, (n, cfg["num_fingertips"] * 6)).astype(F32)
+    st["vec_sensor_tensor"] = rng.normal(0.0, 0.3, (n, max(cfg["num_fingertips"], 1) * 6)).astype(F32)
     st["dof_force_tensor"] = rng.normal(0.0, 0.3, (n, d)).astype(F32)
     st["actions"] = rng.uniform(-1.0, 1.0, (n, cfg["num_actions"])).astype(F32)
 
 
 def make_shadow_hand(num_envs, seed=0, reset_prob=0.02, fall_frac=None, obs_type=None, asymmetric_obs=None,
-                     max_consecutive_successes=None, goal_reset_prob=0.05):
-    cfg = dict(SHADOW_HAND_CFG)
+                     max_consecutive_successes=None, goal_reset_prob=0.05, base_cfg=None):
+    cfg = dict(base_cfg or SHADOW_HAND_CFG)
+    allegro = cfg.get("hand") == "allegro"
     if obs_type is not None:
         cfg["obs_type"] = obs_type
     if asymmetric_obs is not None:
@@ -452,7 +458,7 @@ def make_shadow_hand(num_envs, seed=0, reset_prob=0.02, fall_frac=None, obs_type
     n, d = num_envs, cfg["num_hand_dofs"]
     st = {"cfg_obs_type": np.array(cfg["obs_type"]), "cfg_asymmetric_obs": np.array(int(cfg["asymmetric_obs"])),
           "cfg_max_consecutive_successes": np.array(int(cfg["max_consecutive_successes"]))}
-    lo, hi = _shadow_limits()
+    lo, hi = _shadow_limits(d)
     st["shadow_hand_dof_lower_limits"], st["shadow_hand_dof_upper_limits"] = lo, hi
     st["shadow_hand_dof_default_pos"] = np.zeros(d, F32)
     st["shadow_hand_dof_default_vel"] = np.zeros(d, F32)
@@ -475,7 +481,7 @@ def make_shadow_hand(num_envs, seed=0, reset_prob=0.02, fall_frac=None, obs_type
     st["object_indices"] = (3 * np.arange(n) + 1).astype(I64)
     st["goal_object_indices"] = (3 * np.arange(n) + 2).astype(I64)
     st["fingertip_handles"] = np.array(cfg["fingertip_handles"], I64)
-    st["actuated_dof_indices"] = np.array(SHADOW_HAND_ACTUATED, I64)
+    st["actuated_dof_indices"] = np.arange(d, dtype=I64) if allegro else np.array(SHADOW_HAND_ACTUATED, I64)
     st["progress_buf"] = _progress(rng, n, cfg["max_episode_length"])
     st["reset_buf"] = _resets(rng, n, reset_prob)
     st["reset_goal_buf"] = _resets(rng, n, goal_reset_prob if reset_prob < 1.0 else 1.0)
@@ -487,9 +493,9 @@ def make_shadow_hand(num_envs, seed=0, reset_prob=0.02, fall_frac=None, obs_type
     st["rb_forces"] = rng.normal(0, 1, (n, cfg["num_bodies"], 3)).astype(F32)
     st["random_force_prob"] = rng.uniform(0.001, 0.1, n).astype(F32)
     _shadow_sim_draw(st, rng, cfg)
-    nobs = SHADOW_HAND_NUM_OBS[cfg["obs_type"]]
+    nobs = (ALLEGRO_HAND_NUM_OBS if allegro else SHADOW_HAND_NUM_OBS)[cfg["obs_type"]]
     st["obs_buf"] = np.zeros((n, nobs), F32)
-    st["states_buf"] = np.zeros((n, 211 if cfg["asymmetric_obs"] else 0), F32)
+    st["states_buf"] = np.zeros((n, (88 if allegro else 211) if cfg["asymmetric_obs"] else 0), F32)
     st["rew_buf"] = np.zeros(n, F32)
     return st
 
@@ -498,8 +504,18 @@ def advance_shadow_hand(st, rng):
     _shadow_sim_draw(st, rng, SHADOW_HAND_CFG)
 
 
+def make_allegro_hand(num_envs, seed=0, reset_prob=0.02, **kw):
+    return make_shadow_hand(num_envs, seed=seed, reset_prob=reset_prob, base_cfg=ALLEGRO_HAND_CFG, **kw)
+
+
+def advance_allegro_hand(st, rng):
+    _shadow_sim_draw(st, rng, ALLEGRO_HAND_CFG)
+
+
 MAKERS["shadow_hand"] = make_shadow_hand
 ADVANCERS["shadow_hand"] = advance_shadow_hand
+MAKERS["allegro_hand"] = make_allegro_hand
+ADVANCERS["allegro_hand"] = advance_allegro_hand
 
 
 # ---------------------------------------------------------------------------------------------

@@ -8,7 +8,7 @@ into the C ABI (libige_b200.so).  ``task_map`` mirrors ``isaacgym_task_map``
 from .base import SyntheticSim, VecTaskB200  # noqa: F401
 from .cartpole import Cartpole  # noqa: F401
 from .locomotion import Ant, Humanoid  # noqa: F401
-from .shadow_hand import ShadowHand  # noqa: F401
+from .shadow_hand import AllegroHand, ShadowHand  # noqa: F401
 from .anymal import Anymal  # noqa: F401
 from .small import BallBalance, Ingenuity, Quadcopter  # noqa: F401
 from .franka_sa import FrankaCabinet, FrankaCubeStack, FrankaCubeStack2, FrankaReach  # noqa: F401
@@ -18,4 +18,4 @@ task_map = {"Cartpole": Cartpole, "Ant": Ant, "Humanoid": Humanoid, "ShadowHand"
             "FrankaReachMA": FrankaReachMA, "FrankaCollectMA": FrankaCollectMA, "FrankaCombineMA": FrankaCombineMA,
             "FrankaPPMA": FrankaPPMA, "Anymal": Anymal, "BallBalance": BallBalance, "Quadcopter": Quadcopter,
             "Ingenuity": Ingenuity, "FrankaReach": FrankaReach, "FrankaCubeStack2": FrankaCubeStack2,
-            "FrankaCubeStack": FrankaCubeStack, "FrankaCabinet": FrankaCabinet}
+            "FrankaCubeStack": FrankaCubeStack, "FrankaCabinet": FrankaCabinet, "AllegroHand": AllegroHand}

@@ -14,13 +14,16 @@ NUM_OBS = {"openai": 42, "full_no_vel": 77, "full": 157, "full_state": 211}
 
 class ShadowHand(VecTaskB200):
     FUSED_ACTION_CLAMP = True
+    NUM_OBS = NUM_OBS
+    NUM_STATES = 211
+    OBS_IDS = _abi.IGE_HAND_OBS
 
     def __init__(self, cfg, sim, device, **kw):
         cfg = dict(cfg)
         self.obs_type = cfg["obs_type"]
         self.asymmetric_obs = bool(cfg["asymmetric_obs"])
-        cfg["num_obs"] = NUM_OBS[self.obs_type]            # shadow_hand.py:109-133
-        cfg["num_states"] = 211 if self.asymmetric_obs else 0
+        cfg["num_obs"] = self.NUM_OBS[self.obs_type]       # shadow_hand.py:109-133, allegro_hand.py:108-126
+        cfg["num_states"] = self.NUM_STATES if self.asymmetric_obs else 0
         super().__init__(cfg, sim, device, **kw)
         for k in ("dist_reward_scale", "rot_reward_scale", "rot_eps", "action_penalty_scale", "reach_goal_bonus",
                   "fall_dist", "fall_penalty", "success_tolerance", "av_factor", "vel_obs_scale",
@@ -85,7 +88,7 @@ class ShadowHand(VecTaskB200):
         p.num_envs = self.num_envs
         p.num_hand_dofs, p.num_dofs_per_env = self.num_shadow_hand_dofs, self.num_dofs
         p.num_bodies, p.num_actions = self.num_bodies, self.num_actions
-        p.obs_type = _abi.IGE_HAND_OBS[self.obs_type]
+        p.obs_type = self.OBS_IDS[self.obs_type]
         p.asymmetric_obs = int(self.asymmetric_obs)
         p.ignore_z_rot = int(self.ignore_z)
         p.max_consecutive_successes = self.max_consecutive_successes
@@ -221,3 +224,14 @@ class ShadowHand(VecTaskB200):
         _lib.call("ige_shadow_hand_post_physics", p, b, stream=self._stream())
         # shadow_hand.py:424 `.mean()` of the 1-element tensor == the element: a 0-dim view, no extra kernel
         self.extras["consecutive_successes"] = self.consecutive_successes.reshape(())
+
+
+class AllegroHand(ShadowHand):
+    """AllegroHand mirror (reference: isaacgymenvs/tasks/allegro_hand.py) -- SURVEY.md 8f row 2.  ``reset_idx``
+    (:507-573), ``reset_target_pose`` (:491-505), the action -> target arithmetic (:590-606) and ``compute_hand_reward``
+    (:664-729) are ShadowHand's lines on a 16-DOF hand whose joints are all actuated; the observation layouts
+    (:439-489: 50 / 72 / 88 wide, no fingertip or force-sensor segments) are three more instantiations of the same
+    kernels (csrc/shadow_hand.cu, IGE_HAND_OBS_ALLEGRO_*)."""
+    NUM_OBS = {"full_no_vel": 50, "full": 72, "full_state": 88}
+    NUM_STATES = 88
+    OBS_IDS = _abi.IGE_HAND_OBS_ALLEGRO

@@ -574,7 +574,7 @@ int ige_oracle_shadow_hand_reset(const IgeShadowHandParams *p, const IgeShadowHa
 /* observation row layouts, shadow_hand.py:473-584 */
 enum { SEG_DOF_POS, SEG_DOF_VEL, SEG_DOF_FORCE, SEG_OBJ_POSE, SEG_OBJ_POS, SEG_OBJ_LINVEL, SEG_OBJ_ANGVEL,
        SEG_GOAL_POSE, SEG_QUAT_DIFF, SEG_FT_STATE, SEG_FT_POS, SEG_SENSORS, SEG_ACTIONS, SEG_END };
-static const int HAND_LAYOUT[4][12][2] = {
+static const int HAND_LAYOUT[7][12][2] = {
     /* openai 42 */ {{SEG_FT_POS, 0}, {SEG_OBJ_POS, 15}, {SEG_QUAT_DIFF, 18}, {SEG_ACTIONS, 22}, {SEG_END, 42}},
     /* full_no_vel 77 */ {{SEG_DOF_POS, 0}, {SEG_OBJ_POSE, 24}, {SEG_GOAL_POSE, 31}, {SEG_QUAT_DIFF, 38}, {SEG_FT_POS, 42},
                           {SEG_ACTIONS, 57}, {SEG_END, 77}},
@@ -582,7 +582,15 @@ static const int HAND_LAYOUT[4][12][2] = {
                     {SEG_GOAL_POSE, 61}, {SEG_QUAT_DIFF, 68}, {SEG_FT_STATE, 72}, {SEG_ACTIONS, 137}, {SEG_END, 157}},
     /* full_state 211 */ {{SEG_DOF_POS, 0}, {SEG_DOF_VEL, 24}, {SEG_DOF_FORCE, 48}, {SEG_OBJ_POSE, 72}, {SEG_OBJ_LINVEL, 79},
                           {SEG_OBJ_ANGVEL, 82}, {SEG_GOAL_POSE, 85}, {SEG_QUAT_DIFF, 92}, {SEG_FT_STATE, 96}, {SEG_SENSORS, 161},
-                          {SEG_ACTIONS, 191}, {SEG_END, 211}}};
+                          {SEG_ACTIONS, 191}, {SEG_END, 211}},
+    /* AllegroHand full_no_vel 50 (allegro_hand.py:439-449) */
+    {{SEG_DOF_POS, 0}, {SEG_OBJ_POSE, 16}, {SEG_GOAL_POSE, 23}, {SEG_QUAT_DIFF, 30}, {SEG_ACTIONS, 34}, {SEG_END, 50}},
+    /* AllegroHand full 72 (:450-465) */
+    {{SEG_DOF_POS, 0}, {SEG_DOF_VEL, 16}, {SEG_OBJ_POSE, 32}, {SEG_OBJ_LINVEL, 39}, {SEG_OBJ_ANGVEL, 42},
+     {SEG_GOAL_POSE, 45}, {SEG_QUAT_DIFF, 52}, {SEG_ACTIONS, 56}, {SEG_END, 72}},
+    /* AllegroHand full_state 88 (:470-489; also the asymmetric states_buf :452-469) */
+    {{SEG_DOF_POS, 0}, {SEG_DOF_VEL, 16}, {SEG_DOF_FORCE, 32}, {SEG_OBJ_POSE, 48}, {SEG_OBJ_LINVEL, 55},
+     {SEG_OBJ_ANGVEL, 58}, {SEG_GOAL_POSE, 61}, {SEG_QUAT_DIFF, 68}, {SEG_ACTIONS, 72}, {SEG_END, 88}}};
 
 static void hand_fill_row(const IgeShadowHandParams *p, const IgeShadowHandBuffers *b, int e, int layout, float *row,
                           const float *quat_diff) {
@@ -631,6 +639,9 @@ static int hand_num_obs(int layout) {
 int ige_oracle_shadow_hand_post_physics(const IgeShadowHandParams *p, const IgeShadowHandBuffers *b) {
     const int n = p->num_envs, na = p->num_actions;
     const int num_obs = hand_num_obs(p->obs_type);
+    /* the asymmetric states_buf: ShadowHand 211-wide full_state (:529-556), AllegroHand 88-wide (allegro_hand.py:452-469) */
+    const int st_layout = p->obs_type >= IGE_HAND_OBS_ALLEGRO_FULL_NO_VEL ? IGE_HAND_OBS_ALLEGRO_FULL_STATE : IGE_HAND_OBS_FULL_STATE;
+    const int num_st = hand_num_obs(st_layout);
     float tol = p->success_tolerance;
     if (p->ignore_z_rot) tol = 2.0f * tol; /* :758-759 */
     int64_t num_resets = 0;
@@ -648,7 +659,7 @@ int ige_oracle_shadow_hand_post_physics(const IgeShadowHandParams *p, const IgeS
         quat_mul(obj + 3, conj, quat_diff);
         float *obs = b->obs_buf + (size_t)e * num_obs;
         hand_fill_row(p, b, e, p->obs_type, obs, quat_diff);
-        if (p->asymmetric_obs) hand_fill_row(p, b, e, IGE_HAND_OBS_FULL_STATE, b->states_buf + (size_t)e * 211, quat_diff);
+        if (p->asymmetric_obs) hand_fill_row(p, b, e, st_layout, b->states_buf + (size_t)e * num_st, quat_diff);
         /* compute_hand_reward :746-800 */
         float goal_dist = norm3(obj[0] - goal[0], obj[1] - goal[1], obj[2] - goal[2]);
         float qn = norm3(quat_diff[0], quat_diff[1], quat_diff[2]);
@@ -685,10 +696,10 @@ int ige_oracle_shadow_hand_post_physics(const IgeShadowHandParams *p, const IgeS
                 b->obs_clamped[(size_t)e * num_obs + j] = v;
             }
         if (b->states_clamped && p->asymmetric_obs)
-            for (int j = 0; j < 211; ++j) {
-                float v = b->states_buf[(size_t)e * 211 + j];
+            for (int j = 0; j < num_st; ++j) {
+                float v = b->states_buf[(size_t)e * num_st + j];
                 v = v < -p->clip_obs ? -p->clip_obs : v; v = v > p->clip_obs ? p->clip_obs : v;
-                b->states_clamped[(size_t)e * 211 + j] = v;
+                b->states_clamped[(size_t)e * num_st + j] = v;
             }
         s_rew += reward; s_done += resets != 0; s_to += timeout; s_len += resets != 0 ? (double)progress : 0.0;
     }

@@ -23,7 +23,7 @@ pkg = load_package()
 syn = pkg.synthetic
 
 CFGS = {"cartpole": syn.CARTPOLE_CFG, "ant": syn.ANT_CFG, "humanoid": syn.HUMANOID_CFG,
-        "shadow_hand": syn.SHADOW_HAND_CFG}
+        "shadow_hand": syn.SHADOW_HAND_CFG, "allegro_hand": syn.ALLEGRO_HAND_CFG}
 for _v in syn.FRANKA_VARIANTS:
     CFGS["franka_" + _v] = None     # built per fixture: synthetic.franka_ma_cfg(variant, A, T)
 
@@ -41,6 +41,9 @@ FIXTURES = [
     ("shadow_hand", 48, 3, 0.1, 2, dict(obs_type="full_no_vel")),
     ("shadow_hand", 48, 4, 0.1, 2, dict(obs_type="full", max_consecutive_successes=3)),
     ("shadow_hand", 48, 5, 0.0, 2, dict(obs_type="full_state", goal_reset_prob=0.2)),   # goal-only resets
+    ("allegro_hand", 48, 0, 0.1, 3, dict(obs_type="full_state")),
+    ("allegro_hand", 40, 1, 1.0, 2, dict(obs_type="full", asymmetric_obs=True)),
+    ("allegro_hand", 40, 2, 0.1, 2, dict(obs_type="full_no_vel", max_consecutive_successes=3, goal_reset_prob=0.2)),
     ("franka_reach", 64, 0, 0.1, 3, {}),
     ("franka_reach", 32, 1, 1.0, 2, {}),                          # first step resets every env (vec_task.py:317)
     ("franka_reach", 32, 2, 0.3, 2, dict(ragged_flags=True)),     # AND filter: partially flagged envs do not reset

@@ -19,7 +19,8 @@ from oracle import oracle  # noqa: E402
 GOLDEN_DIR = os.path.join(ROOT, "tests", "golden")
 RTOL = 1e-5   # north_star: observations and rewards within 1e-5 relative in fp32
 
-TASK_NAME = {"cartpole": "Cartpole", "ant": "Ant", "humanoid": "Humanoid", "shadow_hand": "ShadowHand",
+HAND_TASKS = ("shadow_hand", "allegro_hand")
+TASK_NAME = {"cartpole": "Cartpole", "ant": "Ant", "humanoid": "Humanoid", "shadow_hand": "ShadowHand", "allegro_hand": "AllegroHand",
              "franka_reach": "FrankaReachMA", "franka_collect": "FrankaCollectMA",
              "franka_combine": "FrankaCombineMA", "franka_pp": "FrankaPPMA"}
 MA_TASKS = ["franka_reach", "franka_collect", "franka_combine", "franka_pp"]
@@ -36,15 +37,16 @@ INT_OUT = {
 }
 _HAND_FLOAT = ["obs_buf", "rew_buf", "successes", "consecutive_successes", "goal_states", "root_state_tensor",
                "dof_state", "prev_targets", "cur_targets", "rb_forces", "random_force_prob"]
-FLOAT_OUT["shadow_hand"] = _HAND_FLOAT
-INT_OUT["shadow_hand"] = ["reset_buf", "reset_goal_buf", "progress_buf", "randomize_buf"]
+for _t in HAND_TASKS:
+    FLOAT_OUT[_t] = _HAND_FLOAT
+    INT_OUT[_t] = ["reset_buf", "reset_goal_buf", "progress_buf", "randomize_buf"]
 for _t in MA_TASKS:
     FLOAT_OUT[_t] = ["obs_buf", "rew_buf", "_root_state", "_dof_state", "_pos_control", "_effort_control",
                      "_init_cubeA_state"]
     INT_OUT[_t] = ["reset_buf", "progress_buf"]
 BITEXACT_FLOAT = {"cartpole": ["dof_state"], "ant": ["potentials", "prev_potentials", "dof_state"],
                   "humanoid": ["potentials", "prev_potentials", "dof_state"],
-                  "shadow_hand": ["successes", "rb_forces"]}
+                  "shadow_hand": ["successes", "rb_forces"], "allegro_hand": ["successes", "rb_forces"]}
 for _t in MA_TASKS:
     BITEXACT_FLOAT[_t] = ["_root_state", "_dof_state", "_pos_control", "_effort_control", "_init_cubeA_state"]
 
@@ -74,7 +76,7 @@ def step_outputs(blob, s):
 
 def step_rands(blob, s):
     named = {k.split("/rand")[1]: blob[k] for k in blob if k.startswith(f"step{s}/rand") and k[-1] in "ABCD"}
-    if named or str(blob.get("meta_task", "")) == "shadow_hand":
+    if named or str(blob.get("meta_task", "")) in HAND_TASKS:
         return named
     out = []
     i = 0
@@ -178,7 +180,7 @@ def cuda_step_ma(obj, rands=None):
 def oracle_step(task, obj, rands=None):
     """One post_physics_step of the CPU oracle on a mirror object whose tensors live on the CPU."""
     assert obj.device.type == "cpu"
-    if task == "shadow_hand":
+    if task in HAND_TASKS:
         return oracle_step_hand(obj, rands)
     if task in MA_TASKS:
         return oracle_step_ma(obj, rands)
@@ -197,7 +199,7 @@ def oracle_step(task, obj, rands=None):
 
 def cuda_step(task, obj, rands=None):
     """One post_physics_step of the product CUDA path; returns the reset id list it emitted."""
-    if task == "shadow_hand":
+    if task in HAND_TASKS:
         return cuda_step_hand(obj, rands)
     if task in MA_TASKS:
         return cuda_step_ma(obj, rands)
@@ -217,6 +219,7 @@ def get(obj, name):
 
 
 HAND_QD_OFFSET = {"openai": 18, "full_no_vel": 38, "full": 68, "full_state": 92}
+ALLEGRO_QD_OFFSET = {"full_no_vel": 30, "full": 52, "full_state": 68}
 
 
 def hand_reward_slack(obj, ref_obs):
@@ -225,7 +228,7 @@ def hand_reward_slack(obj, ref_obs):
     difference in the object quaternion (e.g. libm vs CUDA sinf/cosf in the reset of THIS step -- torch
     CPU vs torch CUDA differ the same way) moves the reward by more than 1e-5.  The slack is the change
     of the rotation term under a +-2 ulp perturbation of |q_xyz|; it is ~0 everywhere else."""
-    off = HAND_QD_OFFSET[obj.obs_type]
+    off = (ALLEGRO_QD_OFFSET if obj.num_shadow_hand_dofs == 16 else HAND_QD_OFFSET)[obj.obs_type]
     qd = np.asarray(ref_obs, dtype=np.float64)[:, off:off + 3]
     qn = np.sqrt((qd ** 2).sum(-1))
     eps, scale = obj.rot_eps, abs(obj.rot_reward_scale)
@@ -271,11 +274,11 @@ def compare_outputs(task, obj, ref_out, check_epilogue=True, bitexact=()):
     for name in INT_OUT[task]:
         assert_equal(name, get(obj, name), ref_out[name])
     for name in FLOAT_OUT[task]:
-        slack = hand_reward_slack(obj, ref_out["obs_buf"]) if (task == "shadow_hand" and name == "rew_buf") else None
+        slack = hand_reward_slack(obj, ref_out["obs_buf"]) if (task in HAND_TASKS and name == "rew_buf") else None
         assert_float_close(name, get(obj, name), ref_out[name], slack=slack)
     for name in bitexact:
         assert_equal(name + " (bit-exact)", get(obj, name).view(np.uint32), np.asarray(ref_out[name]).view(np.uint32))
-    if task == "shadow_hand" and obj.asymmetric_obs:
+    if task in HAND_TASKS and obj.asymmetric_obs:
         assert_float_close("states_buf", get(obj, "states_buf"), ref_out["states_buf"])
         if check_epilogue and obj.fuse_epilogue and "states_clamped" in ref_out:
             assert_float_close("states_clamped", obj.states_clamped.detach().cpu().numpy(), ref_out["states_clamped"])
@@ -292,7 +295,7 @@ def compare_outputs(task, obj, ref_out, check_epilogue=True, bitexact=()):
 
 def snapshot(task, obj):
     out = {n: get(obj, n).copy() for n in INT_OUT[task] + FLOAT_OUT[task]}
-    if task == "shadow_hand" and obj.asymmetric_obs:
+    if task in HAND_TASKS and obj.asymmetric_obs:
         out["states_buf"] = get(obj, "states_buf").copy()
         if obj.fuse_epilogue:
             out["states_clamped"] = obj.states_clamped.detach().cpu().numpy().copy()

@@ -103,13 +103,15 @@ def build_humanoid(st, cfg):
 
 
 def build_shadow_hand(st, cfg):
-    mod = ref_shim.ref_module("tasks.shadow_hand")
+    allegro = cfg.get("hand") == "allegro"
+    mod = ref_shim.ref_module("tasks.allegro_hand" if allegro else "tasks.shadow_hand")
+    cls = mod.AllegroHand if allegro else mod.ShadowHand
     n = st["progress_buf"].shape[0]
     d = cfg["num_hand_dofs"]
     obs_type = str(st["cfg_obs_type"])
     asym = bool(int(st["cfg_asymmetric_obs"]))
-    obj = mod.ShadowHand.__new__(mod.ShadowHand)
-    _common(obj, cfg, n, st["obs_buf"].shape[1], cfg["num_actions"], num_states=211 if asym else 0)
+    obj = cls.__new__(cls)
+    _common(obj, cfg, n, st["obs_buf"].shape[1], cfg["num_actions"], num_states=(88 if allegro else 211) if asym else 0)
     obj.obs_type, obj.asymmetric_obs = obs_type, asym
     obj.object_type = "block"
     obj.up_axis_idx = 2
@@ -212,7 +214,7 @@ def build_franka_ma(st, cfg):
 
 
 BUILDERS = {"cartpole": build_cartpole, "ant": build_ant, "humanoid": build_humanoid,
-            "shadow_hand": build_shadow_hand}
+            "shadow_hand": build_shadow_hand, "allegro_hand": build_shadow_hand}
 for _v in ("reach", "collect", "combine", "pp"):
     BUILDERS["franka_" + _v] = build_franka_ma
 
@@ -249,6 +251,8 @@ SIM_INPUTS = {
 
 SIM_INPUTS["shadow_hand"] = ["dof_state", "root_state_tensor", "rigid_body_states", "vec_sensor_tensor",
                              "dof_force_tensor", "actions"]
+OUTPUTS["allegro_hand"], SIM_INPUTS["allegro_hand"] = OUTPUTS["shadow_hand"], SIM_INPUTS["shadow_hand"]
+HAND_TASKS = ("shadow_hand", "allegro_hand")
 for _v in ("reach", "collect", "combine", "pp"):
     OUTPUTS["franka_" + _v] = ["obs_buf", "rew_buf", "reset_buf", "progress_buf", "_root_state", "_dof_state",
                                "_pos_control", "_effort_control", "_init_cubeA_state"]
@@ -287,7 +291,7 @@ def run_reference_step(task, obj, st, cfg, torch_seed):
     if task.startswith("franka_"):
         return _run_reference_step_ma(task, obj, st, cfg, torch_seed)
     reset_ids = obj.reset_buf.nonzero(as_tuple=False).flatten().clone()
-    goal_ids = obj.reset_goal_buf.nonzero(as_tuple=False).flatten().clone() if task == "shadow_hand" else None
+    goal_ids = obj.reset_goal_buf.nonzero(as_tuple=False).flatten().clone() if task in HAND_TASKS else None
     if task == "cartpole":
         actions = torch.zeros(n, 1)
     else:
@@ -298,7 +302,7 @@ def run_reference_step(task, obj, st, cfg, torch_seed):
     # regenerate the uniforms reset_idx consumed (same seed, same call shapes, same order)
     k = int(reset_ids.numel())
     rands = []
-    if task == "shadow_hand":
+    if task in HAND_TASKS:
         torch.manual_seed(torch_seed)
         rands = {name: torch.rand(*shape).numpy() for name, shape in
                  shadow_hand_rand_shapes(int(goal_ids.numel()), k, cfg)}

@@ -19,13 +19,13 @@ DOFS = {"cartpole": 2, "ant": 8, "humanoid": 21}
 def _make_rands(task, ref, rng):
     """Uniforms for one step in the shapes / order the reference's reset path draws them."""
     k = int((H.get(ref, "reset_buf") != 0).sum())
-    if task == "shadow_hand":
+    if task in H.HAND_TASKS:
         kg = int((H.get(ref, "reset_goal_buf") != 0).sum())
         out = {}
         if kg:
             out["A"] = rng.random((kg, 4), dtype=np.float32)
         if k:
-            out["B"] = rng.random((k, 53), dtype=np.float32)
+            out["B"] = rng.random((k, 2 * ref.num_shadow_hand_dofs + 5), dtype=np.float32)
             out["C"] = rng.random((k, 4), dtype=np.float32)
             out["D"] = rng.random((k,), dtype=np.float32)
         return out
@@ -43,7 +43,7 @@ def _set_tma(on):
     lib.ige_set_use_tma(C.c_int(1 if on else 0))
 
 
-@pytest.mark.parametrize("task", ["cartpole", "ant", "humanoid", "shadow_hand"] + H.MA_TASKS)
+@pytest.mark.parametrize("task", ["cartpole", "ant", "humanoid", "shadow_hand", "allegro_hand"] + H.MA_TASKS)
 def test_cuda_matches_reference_golden(task):
     for path in H.golden_files(task):
         blob = H.load_golden(path)
@@ -70,7 +70,7 @@ def _oracle_vs_cuda(task, n, seed, reset_prob, steps=3, tma=True, rand_mode="inj
                 cur.update({k: st[k] for k in st if k not in cur})
                 cur["progress_buf"] = H.get(ref, "progress_buf")
                 H.pkg.synthetic.advance_physics(task, cur, phys)
-                if task == "shadow_hand":
+                if task in H.HAND_TASKS:
                     cur["goal_states"] = H.get(ref, "goal_states")
                 if task in H.MA_TASKS:
                     for kk in ("cfg_variant", "cfg_num_agents", "cfg_num_targets"):
@@ -154,6 +154,31 @@ def test_shadow_hand_max_consecutive_successes_and_extremes():
 
 def test_shadow_hand_philox():
     _oracle_vs_cuda("shadow_hand", 4096, 21, 0.25, steps=3, rand_mode="philox")
+
+
+# AllegroHand: the ShadowHand kernels instantiated for 16 DOFs / 16 actions and the three
+# allegro_hand.py observation layouts (50 / 72 / 88 wide), default cfg size, asymmetric 88-wide states
+def test_allegro_hand_16384_full_state():
+    _oracle_vs_cuda("allegro_hand", 16384, 0, 0.02)
+
+
+@pytest.mark.parametrize("obs_type", ["full_no_vel", "full", "full_state"])
+@pytest.mark.parametrize("asym", [False, True])
+def test_allegro_hand_obs_types(obs_type, asym):
+    _oracle_vs_cuda("allegro_hand", 2052, 3, 0.2, steps=2, obs_type=obs_type, asymmetric_obs=asym)
+
+
+def test_allegro_hand_ragged_generic_philox_extremes():
+    _oracle_vs_cuda("allegro_hand", 1000, 5, 0.3, steps=2)
+    _oracle_vs_cuda("allegro_hand", 37, 5, 0.3, steps=2, tma=False)
+    _oracle_vs_cuda("allegro_hand", 4096, 21, 0.25, steps=3, rand_mode="philox")
+    _oracle_vs_cuda("allegro_hand", 2048, 7, 1.0, steps=2, max_consecutive_successes=3)
+    _oracle_vs_cuda("allegro_hand", 2048, 8, 0.0, steps=2, goal_reset_prob=0.3)
+    _set_fast(False)
+    try:
+        _oracle_vs_cuda("allegro_hand", 2052, 3, 0.2, steps=2, obs_type="full", asymmetric_obs=True)
+    finally:
+        _set_fast(True)
 
 
 def test_shadow_hand_sim_call_lists():

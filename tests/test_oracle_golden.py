@@ -19,7 +19,7 @@ def _run_fixture(task, path):
         ids = H.oracle_step(task, obj, H.step_rands(blob, s))
         ref = H.step_outputs(blob, s)
         H.assert_equal("reset_env_ids", ids.numpy(), ref["reset_env_ids"])
-        if task != "shadow_hand" and task not in H.MA_TASKS:   # (actor-id lists: checked in the GPU tests)
+        if task not in H.HAND_TASKS and task not in H.MA_TASKS:   # (actor-id lists: checked in the GPU tests)
             for cname, idx in H.step_call_indices(blob, s):
                 H.assert_equal(f"{cname} indices", ids.numpy(), idx)
         H.compare_outputs(task, obj, ref, bitexact=H.BITEXACT_FLOAT[task])
@@ -28,7 +28,7 @@ def _run_fixture(task, path):
     return worst
 
 
-@pytest.mark.parametrize("task", ["cartpole", "ant", "humanoid", "shadow_hand"] + H.MA_TASKS)
+@pytest.mark.parametrize("task", ["cartpole", "ant", "humanoid", "shadow_hand", "allegro_hand"] + H.MA_TASKS)
 def test_oracle_matches_reference_golden(task):
     files = H.golden_files(task)
     assert files, f"no golden fixtures for {task}"
@@ -36,7 +36,7 @@ def test_oracle_matches_reference_golden(task):
         worst = _run_fixture(task, path)
         # the restatement is op-for-op: everything but libm-vs-sleef transcendentals is bit-exact
         # (ShadowHand's reward goes through asin(): libm and torch's vectorised asin differ in the last ulp)
-        assert worst["rew_buf"] > (0.5 if task == "shadow_hand" else 0.9), worst
+        assert worst["rew_buf"] > (0.5 if task in H.HAND_TASKS else 0.9), worst
 
 
 def test_oracle_rollout_matches_reference_play_steps():
