@@ -34,15 +34,26 @@ from ige_loader import load_package  # noqa: E402
 
 # frozen algorithmic bytes per env-step (SURVEY.md 8d / BASELINE.md section 2)
 ALGO_BYTES = {"Cartpole": 68, "Ant": 556, "Humanoid": 940, "ShadowHand": 1732, "FrankaReachMA": 376,
-              "FrankaCollectMA": 488, "FrankaCombineMA": 692, "FrankaPPMA": 720, "Anymal": 544}
+              "FrankaCollectMA": 488, "FrankaCombineMA": 692, "FrankaPPMA": 720, "Anymal": 544,
+              # SURVEY 8f row 2 (compulsory bytes of the reset + obs + reward + done launches)
+              "AllegroHand": 748, "BallBalance": 360, "Quadcopter": 396, "Ingenuity": 248, "FrankaReach": 160,
+              "FrankaCubeStack2": 200, "FrankaCubeStack": 216, "FrankaCabinet": 380}
 ALGO_BYTES_EPILOGUE = {"Cartpole": 85, "Ant": 797, "Humanoid": 1373, "ShadowHand": 2577, "FrankaReachMA": 530,
-                       "FrankaCollectMA": 714, "FrankaCombineMA": 1078, "FrankaPPMA": 1122, "Anymal": 737}
+                       "FrankaCollectMA": 714, "FrankaCombineMA": 1078, "FrankaPPMA": 1122, "Anymal": 737,
+                       "AllegroHand": 1101, "BallBalance": 457, "Quadcopter": 481, "Ingenuity": 301, "FrankaReach": 217,
+                       "FrankaCubeStack2": 285, "FrankaCubeStack": 293, "FrankaCabinet": 473}
 KERNEL_NAME = {"Cartpole": "cartpole_post_physics_kernel", "Ant": "locomotion_pipelined_kernel<Ant>",
                "Humanoid": "locomotion_pipelined_kernel<Humanoid>",
                "ShadowHand": "shadow_hand_post_physics_kernel (+ shadow_hand_reset_kernel)",
                "FrankaReachMA": "franka_ma_kernel", "FrankaCollectMA": "franka_ma_kernel",
                "FrankaCombineMA": "franka_ma_kernel (reset + compute)", "FrankaPPMA": "franka_ma_kernel (reset + compute)",
-               "Anymal": "anymal_post_physics_kernel"}
+               "Anymal": "anymal_post_physics_kernel",
+               "AllegroHand": "shadow_hand_post_physics_fast_kernel<6> (+ shadow_hand_reset_kernel)",
+               "BallBalance": "ball_balance_pre_kernel + ball_balance_post_kernel",
+               "Quadcopter": "quadcopter_pre_kernel + quadcopter_post_kernel",
+               "Ingenuity": "ingenuity_pre_kernel + ingenuity_post_kernel", "FrankaReach": "franka_sa_kernel<0>",
+               "FrankaCubeStack2": "franka_sa_kernel<1>", "FrankaCubeStack": "franka_sa_kernel<2>",
+               "FrankaCabinet": "franka_cabinet_post_kernel"}
 L2_BYTES = 126 * 1024 * 1024
 HORIZON = 16  # cfg/train/AntPPO.yaml:65 horizon_length -> one stats all-reduce per horizon
 
@@ -175,15 +186,17 @@ def run_ours(args):
 
     # ---- graphs: one per horizon = HORIZON consecutive replicas + (forked branch) the statistics snapshot and
     #      NCCL all-reduce of the PREVIOUS horizon's accumulator; the remainder steps are one more graph ----
-    reducer = pkg.distributed.StatsReducer(device)
+    reducer = pkg.distributed.StatsReducer(device, mode=None if args.stats_reduce in ("auto", "none") else args.stats_reduce)
     reducer.warm()
+    use_branch = args.stats_reduce != "none"
     n_chunks = replicas // HORIZON
     for c in range(n_chunks):
         for e in envs[c * HORIZON:(c + 1) * HORIZON]:
             reducer.attach(e, c)
     mode = "thread_local" if world > 1 else "global"   # NCCL's watchdog thread may touch the device during capture
     chunks = [capture(envs[c * HORIZON:(c + 1) * HORIZON], lambda e: e.hot_step(),
-                      pre=lambda c=c: reducer.fork(reducer.rows[(c & 1) ^ 1]), post=reducer.join, error_mode=mode)
+                      pre=(lambda c=c: reducer.fork(reducer.rows[(c & 1) ^ 1])) if use_branch else None,
+                      post=reducer.join if use_branch else None, error_mode=mode)
               for c in range(n_chunks)]
     full, rem = divmod(args.steps, HORIZON)
     # the remainder continues with the replicas (and the accumulator) of the horizon that would come next
@@ -249,9 +262,15 @@ def run_ours(args):
         "config": bench_config(task, n, world),
         "how": {"l2": f"inputs larger than L2: rotating {replicas} state replicas = "
                       f"{replicas * state_bytes / 2**20:.0f} MiB > 126 MiB L2",
-                "launch": f"one CUDA graph per horizon of {HORIZON} steps; the statistics snapshot + NCCL all-reduce of "
-                          f"the previous horizon is a forked branch of the same graph ({reducer.collectives} collectives "
-                          f"captured, world={world}); remainder steps = one more graph",
+                "launch": f"one CUDA graph per horizon of {HORIZON} steps; the fold + all-reduce of the previous horizon's "
+                          f"statistics is a forked branch of the same graph ({reducer.collectives} collectives captured, "
+                          f"world={world}); remainder steps = one more graph",
+                "stats_reduce": ("none (diagnostic)" if not use_branch else
+                                 {"peer": "ige_stats_exchange: one kernel, fold + NVLink peer-mailbox all-reduce",
+                                  "nccl": "ige_stats_snapshot + ncclAllReduce captured in the branch"
+                                          + (f" (peer mapping unavailable: {reducer.peer_error})"
+                                             if getattr(reducer, "peer_error", None) else ""),
+                                  "local": "ige_stats_snapshot (single rank)"}[reducer.mode]),
                 "reset_noise": "in-kernel Philox"},
         "gpu_launches": gpu_launches,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
@@ -263,6 +282,7 @@ def run_ours(args):
         out["e2e"] = run_e2e(pkg, args, device, dist=dist, world=world)   # collective: every rank runs it
     if rank == 0 and world == 1 and not args.no_sweep:
         out["sweep"] = run_sweep(pkg, args, device, peak)
+        out["variants"] = run_variants(pkg, args, device, peak)
     # keep sampling for >= 1 s of GPU load so that short runs still see clocks under load
     t_end = time.time() + max(0.0, 1.0 - (time.time() - clk.t0))
     while time.time() < t_end:
@@ -285,6 +305,7 @@ def run_ours(args):
         gc.collect()
         torch.cuda.synchronize()
         threading.Timer(30.0, lambda: os._exit(0)).start()
+        reducer.close()
         dist.barrier()
         dist.destroy_process_group()
         os._exit(0)
@@ -426,6 +447,47 @@ def run_sweep(pkg, args, device, peak):
         del envs, g
         torch.cuda.empty_cache()
     return res
+
+
+def run_variants(pkg, args, device, peak):
+    """SURVEY.md 8d timing-method items beside the headline (cold L2, natural reset rate): the same kernel with its
+    state resident in L2 (one replica replayed: 13 MB at Ant 16384 << 126 MB) and at the worst-case reset rate
+    p = 1.0 (every env below the termination height: each step flags every env, the next one resets it)."""
+    task, n = args.task, args.num_envs
+    out = {}
+
+    def timed(envs, loops):
+        g = capture(envs, lambda e: e.hot_step())
+        for _ in range(3):
+            g.replay()
+        torch.cuda.synchronize()
+        a, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(loops):
+            g.replay()
+        b_.record()
+        torch.cuda.synchronize()
+        return a.elapsed_time(b_) * 1e-3 / (loops * len(envs))
+
+    def row(t, note):
+        gbs = ALGO_BYTES[task] * n / t / 1e9
+        return {"kernel_us": t * 1e6, "achieved_gbs": gbs, "frac": gbs / peak, "env_steps_per_s": n / t, "how": note}
+
+    warm = build_replicas(pkg, task, n, 1, device, args.seed + 9, args.fall_frac, False, 0)
+    out["warm_l2"] = row(timed(warm * 16, 64), "one state replica replayed back to back: inputs and outputs stay in L2")
+    del warm
+    reps = max(2, min(32, -(-2 * L2_BYTES // (ALGO_BYTES_EPILOGUE[task] * n))))
+    try:
+        envs = build_replicas(pkg, task, n, reps, device, args.seed + 11, 1.0, False, 0)
+        for e in envs:
+            e.reset_buf.fill_(1)
+        out["reset_p1.0"] = row(timed(envs, max(1, 512 // reps)),
+                                "cold L2, every env flagged every step (fall_frac = 1.0): reset_idx runs for all envs")
+        del envs
+    except Exception as exc:          # tasks whose synthetic maker has no fall knob
+        out["reset_p1.0"] = {"unavailable": str(exc)[:120]}
+    torch.cuda.empty_cache()
+    return out
 
 
 def cpu_baseline(pkg, args, seconds=6.0, steps=None, warmup=3):
@@ -571,6 +633,8 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-sweep", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--stats-reduce", default="auto", choices=["auto", "peer", "nccl", "none"],
+                    help="multi-GPU statistics all-reduce: peer-mailbox kernel (default), NCCL, or none (diagnostic)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -748,6 +748,47 @@ typedef struct IgeStatsSnapshotArgs {
 int ige_stats_snapshot(const IgeStatsSnapshotArgs *a, void *stream);
 
 /* ------------------------------------------------------------------------------------------
+ * Statistics all-reduce fused with the horizon fold, over NVLink / NVSwitch peer memory.
+ *
+ * ONE single-CTA kernel per horizon: fold the accumulator rows into the 16-float vector (as ige_stats_snapshot),
+ * STORE the vector into the mailbox of every rank (peer-mapped device memory: the stores travel over NVLink), wait
+ * until every rank's vector of this epoch has landed in the LOCAL mailbox, sum the slots in rank order (identical
+ * bits on every rank) into `out`.  Every mailbox word is 64 bits, {epoch : float}, written with one store -- a word
+ * whose epoch matches is complete, so no fence and no separate flag travel over the link (the LL idea of NCCL).
+ * The mailbox is double-buffered by epoch parity; a rank can only be one exchange ahead of any other, because it
+ * needs that rank's vector of the previous epoch first.  The kernel polls local memory only, takes no SM resources
+ * to speak of (IGE_NUM_STATS * world threads) and is CUDA-graph capturable: as a forked branch of the horizon graph
+ * it costs the step stream nothing.  Replaces torch.distributed.all_reduce of the reference's statistics
+ * (utils/rlgames_utils.py:89-107 keeps them per rank; rl_games sums them with NCCL) -- NCCL stays the bootstrap
+ * (handle exchange, barriers) and the selectable fallback (IGE_STATS_REDUCE=nccl).
+ *
+ * Mailbox memory comes from ige_mailbox_create (cudaMalloc + zero fill + cudaIpcGetMemHandle); the 64-byte handles are
+ * exchanged by the host (one all-gather at start-up) and opened with ige_mailbox_open.
+ * ------------------------------------------------------------------------------------------ */
+#define IGE_MAX_RANKS 16
+#define IGE_IPC_HANDLE_BYTES 64
+typedef struct IgeStatsExchangeArgs {
+    float *stats;                       /* [IGE_STATS_ROWS * IGE_STATS_STRIDE] accumulator rows of the finished horizon */
+    float *out;                         /* [IGE_NUM_STATS] sum over all ranks */
+    float *local;                       /* optional [IGE_NUM_STATS]: this rank's own folded vector */
+    uint64_t *mailbox[IGE_MAX_RANKS];   /* mailbox[r]: rank r's mailbox as mapped into THIS process (own: the local one) */
+    uint64_t *epoch;                    /* device word, starts at 0; advanced by the kernel (graph replays count themselves) */
+    int32_t *error;                     /* device word: set to 1 + the first missing rank when the wait timed out */
+    int32_t rank, world;
+    int32_t zero_stats;                 /* != 0: leave the rows zeroed */
+    uint32_t timeout_ms;                /* give up waiting for a peer after this long (0 = 2000 ms) */
+} IgeStatsExchangeArgs;
+int ige_stats_exchange(const IgeStatsExchangeArgs *a, void *stream);
+/* bytes of one rank's mailbox for `world` ranks */
+uint64_t ige_mailbox_bytes(int32_t world);
+/* allocate + zero this rank's mailbox on the current device; `handle` receives the IPC handle to send to the peers */
+int ige_mailbox_create(int32_t world, void **mailbox, unsigned char handle[IGE_IPC_HANDLE_BYTES]);
+/* map a peer's mailbox (enables peer access to its device on first use) */
+int ige_mailbox_open(const unsigned char handle[IGE_IPC_HANDLE_BYTES], void **mailbox);
+int ige_mailbox_close(void *peer_mailbox);      /* cudaIpcCloseMemHandle */
+int ige_mailbox_destroy(void *own_mailbox);     /* cudaFree */
+
+/* ------------------------------------------------------------------------------------------
  * Library
  * ------------------------------------------------------------------------------------------ */
 int ige_version(void);

@@ -251,6 +251,15 @@ class IgeFrankaCabinetArgs(C.Structure):
                 ("list", IgeResetList)]
 
 
+IGE_MAX_RANKS = 16
+IGE_IPC_HANDLE_BYTES = 64
+
+
+class IgeStatsExchangeArgs(C.Structure):
+    _fields_ = [("stats", _p), ("out", _p), ("local", _p), ("mailbox", _p * IGE_MAX_RANKS), ("epoch", _p),
+                ("error", _p), ("rank", _i), ("world", _i), ("zero_stats", _i), ("timeout_ms", C.c_uint32)]
+
+
 class IgeStatsSnapshotArgs(C.Structure):
     _fields_ = [("stats", _p), ("out", _p), ("zero_stats", _i), ("accumulate", _i)]
 

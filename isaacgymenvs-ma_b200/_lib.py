@@ -34,6 +34,7 @@ _SIGS = {
     "ige_franka_sa_post_physics": (_abi.IgeFrankaSAArgs,),
     "ige_franka_cabinet_pre_physics": (_abi.IgeFrankaCabinetArgs,),
     "ige_franka_cabinet_post_physics": (_abi.IgeFrankaCabinetArgs,),
+    "ige_stats_exchange": (_abi.IgeStatsExchangeArgs,),
     "ige_stats_snapshot": (_abi.IgeStatsSnapshotArgs,),
 }
 
@@ -61,6 +62,16 @@ def lib():
         l.ige_rollout_scratch_words.argtypes = [C.c_int32]
         l.ige_anymal_scratch_words.restype = C.c_int
         l.ige_anymal_scratch_words.argtypes = [C.c_int32]
+        l.ige_mailbox_bytes.restype = C.c_uint64
+        l.ige_mailbox_bytes.argtypes = [C.c_int32]
+        l.ige_mailbox_create.restype = C.c_int
+        l.ige_mailbox_create.argtypes = [C.c_int32, C.POINTER(C.c_void_p), C.c_char_p]
+        l.ige_mailbox_open.restype = C.c_int
+        l.ige_mailbox_open.argtypes = [C.c_char_p, C.POINTER(C.c_void_p)]
+        l.ige_mailbox_close.restype = C.c_int
+        l.ige_mailbox_close.argtypes = [C.c_void_p]
+        l.ige_mailbox_destroy.restype = C.c_int
+        l.ige_mailbox_destroy.argtypes = [C.c_void_p]
         l.ige_set_use_tma.restype = None
         l.ige_set_use_tma.argtypes = [C.c_int]
         l.ige_set_fast_paths.restype = None
@@ -77,7 +88,8 @@ def lib():
 
 def exported_symbols():
     return ["ige_version", "ige_last_error_string", "ige_launch_count", "ige_compact_scratch_words",
-            "ige_reset_list_scratch_words", "ige_rollout_scratch_words", "ige_anymal_scratch_words", "ige_set_use_tma", "ige_set_fast_paths", *_SIGS.keys()]
+            "ige_reset_list_scratch_words", "ige_rollout_scratch_words", "ige_anymal_scratch_words", "ige_set_use_tma", "ige_set_fast_paths",
+            "ige_mailbox_bytes", "ige_mailbox_create", "ige_mailbox_open", "ige_mailbox_close", "ige_mailbox_destroy", *_SIGS.keys()]
 
 
 def call(name, *structs, stream=0):

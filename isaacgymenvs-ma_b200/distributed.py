@@ -62,12 +62,24 @@ class StatsReducer:
     49 % weak-scaling efficiency at the driver's 20-step window).  The collective overlaps the first steps
     of the horizon; the reduced numbers lag by one horizon, which is what an asynchronous reduction means.
 
+    The collective itself (``mode``):
+      * ``"peer"`` (default for world > 1 on CUDA): ``ige_stats_exchange`` -- ONE single-CTA kernel that folds the
+        rows, stores the vector into every rank's mailbox over NVLink peer memory (cudaIpc-mapped, 64-bit
+        {epoch : float} words) and sums the local mailbox in rank order.  An NCCL kernel in the branch held SM
+        resources next to the resident-capacity step grid for its whole wait (measured: 0.90 weak-scaling efficiency
+        at the driver's 20-step window); this kernel is 512 threads polling local memory.  The process group (NCCL)
+        is only the bootstrap: one all-gather of the 64-byte IPC handles and a barrier.
+      * ``"nccl"`` (``IGE_STATS_REDUCE=nccl``, or when peer mapping is unavailable): snapshot kernel +
+        ``dist.all_reduce`` captured in the branch.
+
     CPU (gloo, tests of the host logic): :meth:`start` with the 16-float vector, eager.
     """
 
-    def __init__(self, device):
+    def __init__(self, device, mode=None):
         self.device = torch.device(device)
         self.cuda = self.device.type == "cuda"
+        self.mode = "local"
+        self._mailboxes, self._own_mailbox = [], None
         self.reduced = torch.zeros(_abi.IGE_NUM_STATS, dtype=torch.float32, device=device)
         self.snap = self.reduced          # round-1 name
         n = _abi.IGE_STATS_ROWS * _abi.IGE_STATS_STRIDE
@@ -81,6 +93,88 @@ class StatsReducer:
             with torch.cuda.device(self.device):
                 self._snapshot(self.rows[0])
                 torch.cuda.synchronize(self.device)
+            if self._multi():
+                want = mode or os.environ.get("IGE_STATS_REDUCE", "peer")
+                self.mode = "nccl"
+                if want == "peer":
+                    self._setup_peer()
+
+    # -- peer-memory mailboxes (ige_stats_exchange) ----------------------------------------------------------
+    def _setup_peer(self):
+        """Allocate this rank's mailbox, all-gather the IPC handles, map every peer's mailbox.  Falls back to the
+        NCCL collective (with a note in ``self.peer_error``) if any rank cannot map any peer."""
+        import ctypes as C
+        import torch.distributed as dist
+        from . import _lib
+        lib = _lib.lib()
+        rank, world = dist.get_rank(), dist.get_world_size()
+        self.peer_error = None
+        own, handle = C.c_void_p(), C.create_string_buffer(_abi.IGE_IPC_HANDLE_BYTES)
+        ok = world <= _abi.IGE_MAX_RANKS
+        with torch.cuda.device(self.device):
+            if ok and lib.ige_mailbox_create(world, C.byref(own), handle) != 0:
+                ok, self.peer_error = False, lib.ige_last_error_string().decode()
+            handles = [None] * world
+            dist.all_gather_object(handles, (bool(ok), handle.raw))
+            ptrs = [None] * world
+            if all(h[0] for h in handles):
+                for r, (_, raw) in enumerate(handles):
+                    if r == rank:
+                        ptrs[r] = own.value
+                        continue
+                    p = C.c_void_p()
+                    if lib.ige_mailbox_open(raw, C.byref(p)) != 0:
+                        ok, self.peer_error = False, lib.ige_last_error_string().decode()
+                        break
+                    ptrs[r] = p.value
+            else:
+                ok = False
+            flags = [None] * world
+            dist.all_gather_object(flags, bool(ok))
+            if all(flags):
+                self._own_mailbox, self._mailboxes = own.value, ptrs
+                self.epoch = torch.zeros(1, dtype=torch.int64, device=self.device)
+                self.error = torch.zeros(1, dtype=torch.int32, device=self.device)
+                self.local = torch.zeros(_abi.IGE_NUM_STATS, dtype=torch.float32, device=self.device)
+                self.rank, self.world = rank, world
+                self.mode = "peer"
+                self._exchange(self.rows[0])            # first launch outside any capture; also checks the mapping
+                torch.cuda.synchronize(self.device)
+                if int(self.error.item()) != 0:
+                    raise RuntimeError(f"ige_stats_exchange: rank {int(self.error.item()) - 1} never answered")
+                self.reduced.zero_()
+            else:
+                for r, p in enumerate(ptrs):
+                    if p and r != rank:
+                        lib.ige_mailbox_close(p)
+                if own.value:
+                    lib.ige_mailbox_destroy(own)
+            dist.barrier()
+
+    def _exchange(self, rows):
+        from . import _lib
+        a = _abi.IgeStatsExchangeArgs()
+        a.stats, a.out, a.local = rows.data_ptr(), self.reduced.data_ptr(), self.local.data_ptr()
+        for r, p in enumerate(self._mailboxes):
+            a.mailbox[r] = p
+        a.epoch, a.error = self.epoch.data_ptr(), self.error.data_ptr()
+        a.rank, a.world, a.zero_stats, a.timeout_ms = self.rank, self.world, 1, 2000
+        _lib.call("ige_stats_exchange", a, stream=torch.cuda.current_stream(self.device).cuda_stream)
+
+    def close(self):
+        """Unmap the peers' mailboxes and free our own (after a barrier: nobody may still be storing into it)."""
+        if self.mode != "peer" or self._own_mailbox is None:
+            return
+        import torch.distributed as dist
+        from . import _lib
+        lib = _lib.lib()
+        torch.cuda.synchronize(self.device)
+        dist.barrier()
+        for r, p in enumerate(self._mailboxes):
+            if r != self.rank:
+                lib.ige_mailbox_close(p)
+        lib.ige_mailbox_destroy(self._own_mailbox)
+        self._own_mailbox, self._mailboxes, self.mode = None, [], "nccl"
 
     @staticmethod
     def _multi():
@@ -94,7 +188,7 @@ class StatsReducer:
 
     def warm(self):
         """One eager collective so the NCCL communicator exists before any graph capture."""
-        if self._multi():
+        if self._multi() and self.mode != "peer":
             import torch.distributed as dist
             dist.all_reduce(self.reduced, op=dist.ReduceOp.SUM)
             torch.cuda.synchronize(self.device)
@@ -108,6 +202,12 @@ class StatsReducer:
 
     def issue(self, rows):
         """Fold `rows` into the vector (re-zeroing them) and all-reduce it, on the CURRENT stream."""
+        if self.mode == "peer":
+            self._exchange(rows)
+            if not torch.cuda.is_current_stream_capturing():
+                self._free.record(torch.cuda.current_stream(self.device))
+            self.collectives += 1
+            return
         self._snapshot(rows)
         if not torch.cuda.is_current_stream_capturing():
             self._free.record(torch.cuda.current_stream(self.device))

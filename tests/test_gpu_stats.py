@@ -121,7 +121,7 @@ def _free_port():
         return s.getsockname()[1]
 
 
-def _nccl_worker(rank, world, port, q):
+def _nccl_worker(rank, world, port, q, mode="nccl"):
     os.environ.update(RANK=str(rank), LOCAL_RANK=str(rank), WORLD_SIZE=str(world), MASTER_ADDR="127.0.0.1",
                       MASTER_PORT=str(port))
     import harness as H2
@@ -129,7 +129,8 @@ def _nccl_worker(rank, world, port, q):
     torch.cuda.set_device(dev)
     d = H2.pkg.distributed
     d.init_process_group(dev)
-    red = d.StatsReducer(dev)
+    red = d.StatsReducer(dev, mode=mode)
+    assert red.mode == mode, (red.mode, getattr(red, "peer_error", None))
     red.warm()
     _make_envs(64, 1, 0, dev)[0].hot_step()     # load the step kernel outside any capture
     torch.cuda.synchronize()
@@ -151,21 +152,27 @@ def _nccl_worker(rank, world, port, q):
         gb.replay()
     torch.cuda.synchronize()
     q.put((rank, local_a, got, red.collectives))
+    if mode == "peer":
+        assert int(red.error.item()) == 0
     del ga, gb                             # ncclCommDestroy waits for the graphs that captured its collectives
     import gc
     gc.collect()
     torch.cuda.synchronize()
+    red.close()
     torch.distributed.barrier()
     torch.distributed.destroy_process_group()
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs >= 2 GPUs")
-def test_nccl_allreduce_inside_horizon_graph():
+@pytest.mark.parametrize("mode", ["peer", "nccl"])
+def test_allreduce_inside_horizon_graph(mode):
+    """2 GPUs: the statistics all-reduce captured as a branch of the horizon graph -- over NVLink peer mailboxes
+    (ige_stats_exchange, the default) or NCCL -- equals the sum of the per-rank vectors."""
     world = 2
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_nccl_worker, args=(r, world, port, q)) for r in range(world)]
+    procs = [ctx.Process(target=_nccl_worker, args=(r, world, port, q, mode)) for r in range(world)]
     for p in procs:
         p.start()
     try:
@@ -182,3 +189,70 @@ def test_nccl_allreduce_inside_horizon_graph():
     for rank, _, got, ncoll in res:
         np.testing.assert_allclose(got, total, rtol=1e-5, atol=1e-3, err_msg=f"rank {rank}")
         assert ncoll == 2                  # one collective captured per horizon graph
+
+
+def _peer_worker_one_gpu(rank, world, port, q):
+    """Both ranks on cuda:0 (gloo bootstrap): exercises the IPC mapping, the {epoch : float} protocol, the parity
+    double-buffering and graph replays of ige_stats_exchange without needing a second GPU."""
+    os.environ.update(RANK=str(rank), LOCAL_RANK="0", WORLD_SIZE=str(world), MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    import torch.distributed as dist
+    import harness as H2
+    dev = torch.device("cuda", 0)
+    torch.cuda.set_device(dev)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    red = H2.pkg.distributed.StatsReducer(dev, mode="peer")
+    assert red.mode == "peer", getattr(red, "peer_error", None)
+    rows = red.rows[0]
+    view = rows.view(abi.IGE_STATS_ROWS, abi.IGE_STATS_STRIDE)
+    results = []
+    for it in range(4):                                   # eager exchanges: both parities, twice
+        view[:, :abi.IGE_NUM_STATS] = float(rank + 1) * (it + 1)
+        red.issue(rows)
+        torch.cuda.synchronize()
+        results.append(red.reduced.cpu().numpy().copy())
+        assert float(view[:, :abi.IGE_NUM_STATS].abs().sum()) == 0.0          # re-zeroed
+    # captured: fill + exchange in one graph, replayed (the kernel counts its own epochs)
+    fill = torch.full((abi.IGE_STATS_ROWS, abi.IGE_NUM_STATS), float(10 * (rank + 1)), device=dev)
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.stream(s):
+        with torch.cuda.graph(g, stream=s, capture_error_mode="thread_local"):
+            view[:, :abi.IGE_NUM_STATS].copy_(fill)
+            red.fork(rows)
+            red.join()
+    for _ in range(7):
+        g.replay()
+    torch.cuda.synchronize()
+    results.append(red.reduced.cpu().numpy().copy())
+    q.put((rank, results, int(red.epoch.item()), int(red.error.item())))
+    del g
+    red.close()
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_peer_exchange_two_processes_one_gpu():
+    world = 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_peer_worker_one_gpu, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    try:
+        res = sorted((q.get(timeout=240) for _ in range(world)), key=lambda t: t[0])
+        for p in procs:
+            p.join(timeout=60)
+            assert p.exitcode == 0
+    finally:
+        for p in procs:
+            if p.is_alive():
+                p.kill()
+    R = abi.IGE_STATS_ROWS
+    for rank, results, epoch, err in res:
+        assert err == 0 and epoch == 1 + 4 + 7          # set-up probe + eager + graph replays
+        for it in range(4):
+            np.testing.assert_array_equal(results[it], np.full(abi.IGE_NUM_STATS, R * 3.0 * (it + 1), np.float32))
+        np.testing.assert_array_equal(results[4], np.full(abi.IGE_NUM_STATS, R * 30.0, np.float32))
+    np.testing.assert_array_equal(res[0][1][4], res[1][1][4])       # identical bits on every rank
