@@ -801,6 +801,9 @@ void ige_set_use_tma(int on);
 /* Debug knob: 0 = take the generic any-shape kernels instead of the shape-specialised fast paths (ShadowHand with
  * 24 DOFs / 20 actions, Franka MA with 2 agents / 2 targets); also IGE_GENERIC=1.  Results are identical. */
 void ige_set_fast_paths(int on);
+/* Debug knob: 0 = launch the kernels fully stream-serialised instead of with programmatic dependent launch (each
+ * kernel waits for its predecessor's completion before its first memory access either way); also IGE_PDL=0. */
+void ige_set_use_pdl(int on);
 
 #ifdef __cplusplus
 }

@@ -31,6 +31,7 @@ __device__ __forceinline__ void philox4(const IgeAnymalParams &p, uint64_t step,
 }
 
 __global__ void __launch_bounds__(kThreads) anymal_post_physics_kernel(IgeAnymalParams p, IgeAnymalBuffers b, int num_chunks) {
+    ige::pdl_prologue();   // PDL: let the next kernel in; wait for the previous one before touching memory
     __shared__ int s_warp[kThreads / 32];
     __shared__ int s_prefix, s_last;
     uint32_t *scratch = b.scratch;
@@ -254,6 +255,6 @@ extern "C" int ige_anymal_post_physics(const IgeAnymalParams *p, const IgeAnymal
         !b->reset_ids || !b->reset_count || !b->scratch)
         return ige_fail(IGE_ENULL, "root_states / contact_forces / commands / rew / flags / reset list / scratch must be non-NULL");
     const int num_chunks = p->num_envs == 0 ? 1 : (p->num_envs + kThreads - 1) / kThreads;
-    anymal_post_physics_kernel<<<num_chunks, kThreads, 0, (cudaStream_t)stream>>>(*p, *b, num_chunks);
+ige_launch(anymal_post_physics_kernel, num_chunks, kThreads, 0, (cudaStream_t)stream, *p, *b, num_chunks);
     return ige_check_launch("ige_anymal_post_physics");
 }

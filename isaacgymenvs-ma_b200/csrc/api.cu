@@ -41,3 +41,14 @@ extern "C" int ige_fast_paths() {
     }
     return g_fast_paths;
 }
+
+// Debug knob: 0 = plain stream-serialised launches instead of programmatic dependent launch (also IGE_PDL=0).
+static int g_use_pdl = -1;
+extern "C" void ige_set_use_pdl(int on) { g_use_pdl = on ? 1 : 0; }
+extern "C" int ige_use_pdl() {
+    if (g_use_pdl < 0) {
+        const char *e = getenv("IGE_PDL");
+        g_use_pdl = (e && e[0] == '0') ? 0 : 1;
+    }
+    return g_use_pdl;
+}

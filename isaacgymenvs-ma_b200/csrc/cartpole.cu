@@ -14,6 +14,7 @@ constexpr int kThreads = 256;
 constexpr int kCtasPerSm = 8;   // 8 x 256 threads = the SM's 2048 thread slots
 
 __global__ void __launch_bounds__(kThreads) cartpole_post_physics_kernel(IgeCartpoleParams p, IgeCartpoleBuffers b) {
+    ige::pdl_prologue();   // PDL: let the next kernel in; wait for the previous one before touching memory
     const uint64_t step = ige::load_step(p.rand);
     float st_rew = 0.f, st_done = 0.f, st_to = 0.f, st_len = 0.f, st_n = 0.f;
     const int stride = gridDim.x * kThreads;
@@ -94,6 +95,6 @@ extern "C" int ige_cartpole_post_physics(const IgeCartpoleParams *p, const IgeCa
     if (sms[dev] == 0 && (cudaDeviceGetAttribute(&sms[dev], cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms[dev] < 1))
         sms[dev] = 1;
     const int grid = min((p->num_envs + kThreads - 1) / kThreads, sms[dev] * kCtasPerSm);
-    cartpole_post_physics_kernel<<<grid, kThreads, 0, (cudaStream_t)stream>>>(*p, *b);
+ige_launch(cartpole_post_physics_kernel, grid, kThreads, 0, (cudaStream_t)stream, *p, *b);
     return ige_check_launch("ige_cartpole_post_physics");
 }

@@ -20,6 +20,7 @@ constexpr int kChunk = kThreads * kItems;
 constexpr uint32_t kFlagAgg = 1u << 30, kFlagPrefix = 2u << 30, kValMask = (1u << 30) - 1;
 
 __global__ void __launch_bounds__(kThreads) compact_resets_kernel(IgeCompactArgs a, int num_chunks) {
+    ige::pdl_prologue();   // PDL: let the next kernel in; wait for the previous one before touching memory
     uint32_t *scratch = a.scratch;
     __shared__ int s_chunk;
     __shared__ int s_warp[kThreads / 32];
@@ -123,7 +124,7 @@ extern "C" int ige_compact_resets(const IgeCompactArgs *a, void *stream) {
     const int n = a->num_rows / a->group;
     if (n > (1 << 30) - 1) return ige_fail(IGE_ESIZE, "too many envs");
     const int num_chunks = n == 0 ? 1 : (n + kChunk - 1) / kChunk;
-    compact_resets_kernel<<<num_chunks, kThreads, 0, (cudaStream_t)stream>>>(*a, num_chunks);
+ige_launch(compact_resets_kernel, num_chunks, kThreads, 0, (cudaStream_t)stream, *a, num_chunks);
     return ige_check_launch("ige_compact_resets");
 }
 

@@ -195,6 +195,7 @@ __device__ __forceinline__ void franka_tile_out_and_reduce(const IgeFrankaMAPara
 __global__ void __launch_bounds__(NT) franka_ma_kernel(const __grid_constant__ IgeFrankaMAParams p,
                                                        const __grid_constant__ IgeFrankaMABuffers b, const int phase,
                                                        const int use_tma) {
+    ige::pdl_prologue();   // PDL: let the next kernel in; wait for the previous one before touching memory
     extern __shared__ __align__(128) float obs_tile[];  // TE * A * num_obs
     __shared__ int s_last;
     __shared__ float s_u[NT / 32][32];
@@ -461,15 +462,16 @@ __global__ void __launch_bounds__(NT) franka_ma_kernel(const __grid_constant__ I
 // compute_global_FSM pairs flat row k with d_ecp[k] of a flatten()ed (2, N) stack (franka_PPMA.py:606), i.e.
 // row k needs the gripper and one cube of ANOTHER env j = k or k - N, whose cube row env j's own reset may be
 // rewriting in this very launch.  Round 1 ran the reset as a separate launch for that reason.  Here the reader
-// never looks at a row that is being rewritten: post-reset cube positions are a pure function of (env, draw,
-// step | reset rank), so it recomputes env j's when env j resets and reads memory when it does not.  "Does env j
-// reset" is taken from env j's ENTRY flags, which every CTA snapshots (a ballot per tile in shared memory) in
-// the prologue where it also counts its own flags for the reset list; the flags are only overwritten after the
-// launch epoch has advanced, i.e. after every CTA has finished that prologue (ige::list_cta_publish: the last
-// CTA to take its ticket advances the epoch; all CTAs are co-resident).
+// never uses a row that is being rewritten: post-reset cube positions are a pure function of (env, draw,
+// step | reset rank), so it recomputes env j's when env j resets and uses memory when it does not.  "Does env j
+// reset" comes from the reset-list SLOT of env j's tile ({launch tag : entry-flag ballot}, ige::list_publish_slot),
+// which its owner CTA publishes in its prologue -- for ALL of its tiles, before it waits for anybody's slot, so the
+// cross-CTA waits cannot form a cycle -- and never from reset_buf, which the owner is free to overwrite at once.
+// The ascending reset id list is written by one extra scanner CTA from the same slots (ige::list_scanner_cta); no
+// worker waits for a prefix, a ticket or an epoch.  The loads of a CTA's first tile are issued BEFORE that prologue:
+// the flag round trip, the slot round trip and the tile's DRAM round trip overlap instead of following each other.
 constexpr int RT_E = 32;                // envs per tile
 constexpr int RT_NT = 2 * RT_E;         // threads per CTA = rows per tile
-constexpr int RT_MAX_TILES = 96;        // tiles per CTA the prologue snapshot has room for
 
 // four consecutive uniforms j = 4 blk .. 4 blk + 3 of draw `draw` for env `env` (reset rank `rank`)
 __device__ __forceinline__ void ma_uniform4(const IgeMAResetRand &r, uint64_t step, int draw, int rank, int env, int cols,
@@ -490,7 +492,8 @@ template <int V>
 __global__ void __launch_bounds__(RT_NT) franka_ma_rows_kernel(const __grid_constant__ IgeFrankaMAParams p_in,
                                                                const __grid_constant__ IgeFrankaMABuffers b_in,
                                                                const int num_tiles, const int tiles_per_cta,
-                                                               const int use_tma) {
+                                                               const int use_tma, const int workers) {
+    ige::pdl_trigger();   // PDL (ige_common.cuh): the next step's grid may be scheduled behind this one
 #if IGE_STAGE_ARGS
     // (experiment) kernel arguments -> shared memory once
     __shared__ __align__(16) IgeFrankaMAParams p;
@@ -515,9 +518,8 @@ __global__ void __launch_bounds__(RT_NT) franka_ma_rows_kernel(const __grid_cons
     constexpr bool PAIRED = V == IGE_FRANKA_COMBINE || V == IGE_FRANKA_PP;
     constexpr bool MEANS = V != IGE_FRANKA_REACH;   // Reach logs no component means (franka_reach_MA.py:928-960)
     __shared__ __align__(128) float obs_tile[2][RT_NT * NO];
-    __shared__ uint32_t s_pmask[PAIRED ? RT_MAX_TILES : 1][2];   // bit = "the partner env of this row resets in this launch"
-    __shared__ uint32_t s_own[RT_MAX_TILES];                      // reset ballot of my tiles
     __shared__ uint64_t s_step;
+    __shared__ uint32_t s_tag;
     __shared__ int s_last;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int N = p.num_envs;
@@ -530,62 +532,29 @@ __global__ void __launch_bounds__(RT_NT) franka_ma_rows_kernel(const __grid_cons
         return first_half ? row : row - N;
     };
 
-    // ---- prologue: step word, own-flag ballots (-> reset-list count), partner-reset ballots ----
-    if (tid == 0) s_step = (p.rand.mode == IGE_RAND_PHILOX && p.rand.step)
-                               ? *reinterpret_cast<const volatile uint64_t *>(p.rand.step) : 0ull;
-    int cnt = 0;
-    if (warp == 0) {
-        for (int t = 0; t < my_tiles; ++t) {
-            const int e = (first + t) * RT_E + lane;
-            bool f = false;
-            if (e < N) {
-                const longlong2 r = *reinterpret_cast<const longlong2 *>(b.reset_buf + (size_t)e * A);
-                f = r.x != 0 && r.y != 0;
-            }
-            const uint32_t m = __ballot_sync(0xffffffffu, f);
-            if (lane == 0) s_own[t] = m;
-            cnt += __popc(m);
-        }
+    ige::pdl_wait();   // global memory from here on
+    if ((int)blockIdx.x >= workers) {   // the scanner CTA: slots -> ascending id list, count, launch tag, Philox step
+        ige::list_scanner_cta<RT_NT>(b_in.list, num_tiles, p_in.rand.step);
+        return;
     }
-    if (PAIRED) {
-        // warp w snapshots the partner flags of rows [32 w, 32 w + 32) of every tile
-        for (int t = 0; t < my_tiles; ++t) {
-            const int row = ((first + t) * RT_E) * A + tid;
-            bool f = false;
-            if (row < N * A) {
-                bool fh;
-                const int j = partner_env(row, fh);
-                const longlong2 r = *reinterpret_cast<const longlong2 *>(b.reset_buf + (size_t)j * A);
-                f = r.x != 0 && r.y != 0;
-            }
-            const uint32_t m = __ballot_sync(0xffffffffu, f);
-            if (lane == 0) s_pmask[t][warp] = m;
-        }
+    if (tid == 0) {
+        s_step = (p.rand.mode == IGE_RAND_PHILOX && p.rand.step) ? *reinterpret_cast<const volatile uint64_t *>(p.rand.step) : 0ull;
+        s_tag = emit ? ige::list_epoch_tag(b.list) : 0u;
     }
-    __syncthreads();   // every thread has read what it needs of the ENTRY flags and the step word
-    const uint64_t step = s_step;
-    ige::ListTag ltag{0, 0};
-    int list_off = -1;
-    if (warp == 0 && emit) ltag = ige::list_cta_publish(b.list, cnt);   // the ticket's round trip overlaps tile 0's loads
 
-    float comp[NC];
-#pragma unroll
-    for (int i = 0; i < NC; ++i) comp[i] = 0.0f;
-    float st_rew = 0.f, st_done = 0.f, st_to = 0.f, st_len = 0.f, st_n = 0.f;
-    bool flags_open = !(PAIRED && emit);   // may reset_buf be overwritten yet?
-
-    for (int t = 0; t < my_tiles; ++t) {
+    // registers of one tile's row-indexed loads
+    long long prog = 0, rst = 0;
+    float eef[7], base[7], act[NA], cf[3], cube[7], dest[3], sb[3], je[3], jc[3];
+    bool j_first = false;
+    int j = 0;
+    // ---- every load whose address depends only on the row (issued for tile 0 before the prologue below) ----
+    auto load_tile = [&](int t) {
         const int e0 = (first + t) * RT_E;
         const int ne = min(RT_E, N - e0);
-        const int e = e0 + (tid >> 1);
-        const bool valid = (tid >> 1) < ne;
-        const int ec = valid ? e : N - 1;          // clamped: invalid lanes load a real row and discard it
+        const int ec = (tid >> 1) < ne ? e0 + (tid >> 1) : N - 1;   // clamped: invalid lanes load a real row and discard it
         const size_t row = (size_t)ec * A + a;
-        float *otile = obs_tile[t & 1];
-
-        // ---- every load whose address depends only on the row ----
-        long long prog = b.progress_buf[row], rst = b.reset_buf[row];
-        float eef[7], base[7], act[NA], cf[3], cube[7], dest[3], sb[3], je[3], jc[3];
+        prog = b.progress_buf[row];
+        rst = b.reset_buf[row];
         {
             const float *r = body_row(p, b, ec, p.eef_body_start, p.eef_body_step, a);
 #pragma unroll
@@ -599,7 +568,7 @@ __global__ void __launch_bounds__(RT_NT) franka_ma_rows_kernel(const __grid_cons
         {
             const float *r = b.actions + row * NA;
 #pragma unroll
-            for (int j = 0; j < NA; ++j) act[j] = __ldg(r + j);
+            for (int jj = 0; jj < NA; ++jj) act[jj] = __ldg(r + jj);
         }
         if (V == IGE_FRANKA_REACH) {
             const float *r = b.contact_forces + ((size_t)ec * p.num_bodies + p.hand_body_start + p.hand_body_step * a) * 3;
@@ -621,25 +590,51 @@ __global__ void __launch_bounds__(RT_NT) franka_ma_rows_kernel(const __grid_cons
 #pragma unroll
             for (int i = 0; i < 3; ++i) sb[i] = r[i];
         }
-        bool j_first = false, j_reset = false;
-        int j = 0;
         if (PAIRED) {
             j = partner_env((int)row, j_first);
-            j_reset = (s_pmask[t][warp] >> lane) & 1u;
             const float *r = body_row(p, b, j, p.eef_body_start, p.eef_body_step, j_first ? 0 : 1);
 #pragma unroll
             for (int i = 0; i < 3; ++i) je[i] = __ldg(r + i);
-            if (!j_reset) {   // env j keeps its cubes in this launch: nobody writes this row
-                const float *c = actor_row(p, b, j, p.cube_actor_start + p.cube_actor_step * (j_first ? 1 : 0));
+            // env j's cube row: used only when env j does NOT reset in this launch (then nobody writes the row; a value
+            // read while env j's owner rewrites it is discarded below)
+            const volatile float *c = actor_row(p, b, j, p.cube_actor_start + p.cube_actor_step * (j_first ? 1 : 0));
 #pragma unroll
-                for (int i = 0; i < 3; ++i) jc[i] = c[i];
-            }
+            for (int i = 0; i < 3; ++i) jc[i] = c[i];
         }
+    };
+    if (my_tiles > 0) load_tile(0);
 
-        // the launch epoch, for the flag gate below: loaded now so that its round trip overlaps the tile's loads
-        uint64_t gate = 0;
-        if (!flags_open && tid == 0) gate = *reinterpret_cast<const volatile uint64_t *>(b.list.scratch);
-        if (t == 0 && warp == 0 && emit) ige::list_cta_scan(b.list, ltag, p.rand.step);   // last CTA to arrive only
+    // ---- prologue: the entry-flag ballot of EVERY tile of this CTA goes out before the CTA waits for anybody ----
+    __syncthreads();   // step word and launch tag were read before this CTA's first publish
+    const uint64_t step = s_step;
+    const uint32_t ltag = s_tag;
+    if (emit && warp == 0) {
+        for (int t = 0; t < my_tiles; ++t) {
+            const int e = (first + t) * RT_E + lane;
+            bool f = false;
+            if (e < N) {
+                const longlong2 r = *reinterpret_cast<const longlong2 *>(b.reset_buf + (size_t)e * A);
+                f = r.x != 0 && r.y != 0;
+            }
+            const uint32_t m = __ballot_sync(0xffffffffu, f);
+            if (lane == 0) ige::list_publish_slot(b.list, ltag, first + t, m);
+        }
+    }
+
+    float comp[NC];
+#pragma unroll
+    for (int i = 0; i < NC; ++i) comp[i] = 0.0f;
+    float st_rew = 0.f, st_done = 0.f, st_to = 0.f, st_len = 0.f, st_n = 0.f;
+    for (int t = 0; t < my_tiles; ++t) {
+        const int e0 = (first + t) * RT_E;
+        const int ne = min(RT_E, N - e0);
+        const int e = e0 + (tid >> 1);
+        const bool valid = (tid >> 1) < ne;
+        const int ec = valid ? e : N - 1;
+        const size_t row = (size_t)ec * A + a;
+        float *otile = obs_tile[t & 1];
+        // does the partner env reset in this launch?  Its owner's slot (published in that CTA's prologue)
+        const bool j_reset = PAIRED && ige::list_slot_bit(b.list, ltag, j);
 
         // ---- post_physics_step :821-826: progress++, agent flags -> reset_idx (AND filter) ----
         const long long rst_o = __shfl_xor_sync(0xffffffffu, rst, 1);
@@ -903,13 +898,8 @@ __global__ void __launch_bounds__(RT_NT) franka_ma_rows_kernel(const __grid_cons
         const int count = ne * A * NO;
         const bool bulk = use_tma && (count % 4 == 0);
         if (bulk) ige::fence_proxy_async();
-        if (!flags_open && tid == 0) {
-            const volatile uint64_t *sc = reinterpret_cast<const volatile uint64_t *>(b.list.scratch);
-            while (gate < ltag.tag) gate = sc[0];
-        }
         if (t >= 1 && tid == 0) ige::bulk_wait_read_all();  // tile t - 1 has left obs_tile[(t + 1) & 1]: free for tile t + 1
         __syncthreads();
-        flags_open = true;
         if (valid) {
             b.rew_buf[row] = rewards;
             b.reset_buf[row] = rst;
@@ -926,12 +916,7 @@ __global__ void __launch_bounds__(RT_NT) franka_ma_rows_kernel(const __grid_cons
             float *dc = b.obs_clamped + (size_t)e0 * A * NO;
             for (int i = tid; i < count; i += RT_NT) dc[i] = clampf(otile[i], p.clip_obs);
         }
-        if (emit && warp == 0) {   // this tile's ids: lane l writes env e0 + l at its rank within the ballot
-            if (list_off < 0) list_off = ige::list_cta_prefix_wait(b.list, ltag);   // my CTA's slot: written long ago
-            const uint32_t m = s_own[t];
-            if ((m >> lane) & 1u) b.list.ids[list_off + __popc(m & ((1u << lane) - 1u))] = e0 + lane;
-            list_off += __popc(m);
-        }
+        if (t + 1 < my_tiles) load_tile(t + 1);   // (every register of tile t is dead by now)
     }
 
     // ---- reward-component sums (the .mean()s of extras) + statistics ----
@@ -954,7 +939,7 @@ __global__ void __launch_bounds__(RT_NT) franka_ma_rows_kernel(const __grid_cons
         __syncthreads();
         if (tid == 0) {
             unsigned *c = reinterpret_cast<unsigned *>(b.reduce_scratch + NC);
-            s_last = atomicAdd(c, 1u) == gridDim.x - 1;
+            s_last = atomicAdd(c, 1u) == (unsigned)workers - 1u;
         }
         __syncthreads();
         if (s_last) {
@@ -1016,7 +1001,7 @@ extern "C" int ige_franka_ma_post_physics(const IgeFrankaMAParams *p, const IgeF
     if (ige_fast_paths() && p->num_agents == 2 && p->num_targets == 2 && p->num_obs == kPairObs[p->variant] &&
         p->num_actions == kPairActions[p->variant] && (!pair_only || b->list.scratch != nullptr)) {
         // rows kernel: ONE launch for every variant (Combine / PP need the reset list's launch epoch, see its header)
-        typedef void (*Rows)(const IgeFrankaMAParams, const IgeFrankaMABuffers, const int, const int, const int);
+        typedef void (*Rows)(const IgeFrankaMAParams, const IgeFrankaMABuffers, const int, const int, const int, const int);
         static const Rows rows[4] = {franka_ma_rows_kernel<IGE_FRANKA_REACH>, franka_ma_rows_kernel<IGE_FRANKA_COLLECT>,
                                      franka_ma_rows_kernel<IGE_FRANKA_COMBINE>, franka_ma_rows_kernel<IGE_FRANKA_PP>};
         int dev = 0;
@@ -1034,12 +1019,12 @@ extern "C" int ige_franka_ma_post_physics(const IgeFrankaMAParams *p, const IgeF
             max_ctas[p->variant][dev] = m;
         }
         const int tiles = (p->num_envs + RT_E - 1) / RT_E;
-        const int per_cta = (tiles + max_ctas[p->variant][dev] - 1) / max_ctas[p->variant][dev];
-        if (per_cta <= RT_MAX_TILES) {
-            const int grid = (tiles + per_cta - 1) / per_cta;   // <= resident capacity: all CTAs co-resident
-            rows[p->variant]<<<grid, RT_NT, 0, s>>>(*p, *b, tiles, per_cta, ige_use_tma());
-            return ige_check_launch("ige_franka_ma_post_physics");
-        }
+        const int scanner = b->list.scratch ? 1 : 0;
+        const int cap = max_ctas[p->variant][dev] - scanner > 0 ? max_ctas[p->variant][dev] - scanner : 1;
+        const int per_cta = (tiles + cap - 1) / cap;
+        const int workers = (tiles + per_cta - 1) / per_cta;   // workers + scanner <= resident capacity: all CTAs co-resident
+        ige_launch(rows[p->variant], workers + scanner, RT_NT, 0, s, *p, *b, tiles, per_cta, ige_use_tma(), workers);
+        return ige_check_launch("ige_franka_ma_post_physics");
     }
     const size_t smem = (size_t)TE * p->num_agents * p->num_obs * sizeof(float);
     if (smem > 48 * 1024) {
@@ -1048,11 +1033,11 @@ extern "C" int ige_franka_ma_post_physics(const IgeFrankaMAParams *p, const IgeF
     }
     const int grid = (p->num_envs + TE - 1) / TE;
     if (pair_only) {
-        franka_ma_kernel<<<grid, NT, 0, s>>>(*p, *b, PH_RESET, ige_use_tma());
+        ige_launch(franka_ma_kernel, grid, NT, 0, s, *p, *b, (int)PH_RESET, ige_use_tma());
         if (int rc = ige_check_launch("ige_franka_ma_post_physics(reset)")) return rc;
-        franka_ma_kernel<<<grid, NT, smem, s>>>(*p, *b, PH_COMPUTE, ige_use_tma());
+        ige_launch(franka_ma_kernel, grid, NT, smem, s, *p, *b, (int)PH_COMPUTE, ige_use_tma());
     } else {
-        franka_ma_kernel<<<grid, NT, smem, s>>>(*p, *b, PH_FUSED, ige_use_tma());
+        ige_launch(franka_ma_kernel, grid, NT, smem, s, *p, *b, (int)PH_FUSED, ige_use_tma());
     }
     return ige_check_launch("ige_franka_ma_post_physics");
 }

@@ -80,6 +80,7 @@ __device__ __forceinline__ void load_small(const IgeFrankaOscArgs &a, int r, boo
 // the warp's NEXT tile (and its small per-row inputs) is then issued into the same shared buffer and flies during the
 // ~2.6 k instructions of register arithmetic -- the register file is the second stage of the double buffer.
 __global__ void __launch_bounds__(kWarps * 32) franka_osc_kernel(IgeFrankaOscArgs a, int rows) {
+    ige::pdl_prologue();   // PDL: let the next kernel in; wait for the previous one before touching memory
     __shared__ __align__(16) float s_mm[kWarps][kTile * 49];
     __shared__ __align__(16) float s_j[kWarps][kTile * 42];
     __shared__ __align__(16) float s_ds[kWarps][kTile * 18];
@@ -238,6 +239,6 @@ extern "C" int ige_franka_ma_pre_physics(const IgeFrankaOscArgs *a, void *stream
         resident = sms * per_sm;
     }
     const int grid = min((tiles + kWarps - 1) / kWarps, resident);
-    franka_osc_kernel<<<grid, kWarps * 32, 0, (cudaStream_t)stream>>>(*a, (int)rows);
+ige_launch(franka_osc_kernel, grid, kWarps * 32, 0, (cudaStream_t)stream, *a, (int)rows);
     return ige_check_launch("ige_franka_ma_pre_physics");
 }

@@ -101,6 +101,7 @@ __device__ __forceinline__ void sample_cube(const IgeFrankaSAArgs &a, uint64_t s
 
 template <int V>
 __global__ void __launch_bounds__(kTaskThreads) franka_sa_kernel(const __grid_constant__ IgeFrankaSAArgs a, const int workers) {
+    ige::pdl_prologue();   // PDL: let the next kernel in; wait for the previous one before touching memory
     constexpr int NOBS = V == IGE_FRANKA_SA_REACH ? 14 : (V == IGE_FRANKA_SA_STACK2 ? 21 : 19);
     constexpr int NC = IGE_FRANKA_SA_COMPONENTS;
     float comp[NC];
@@ -303,6 +304,7 @@ __device__ __forceinline__ void quat_apply3(const float *q, const float *b, floa
 }
 
 __global__ void __launch_bounds__(kTaskThreads) franka_cabinet_pre_kernel(const __grid_constant__ IgeFrankaCabinetArgs a) {
+    ige::pdl_prologue();   // PDL: let the next kernel in; wait for the previous one before touching memory
     const int total = a.num_envs * 9;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {   // :417-425
         const int e = i / 9, j = i - e * 9;
@@ -314,6 +316,7 @@ __global__ void __launch_bounds__(kTaskThreads) franka_cabinet_pre_kernel(const 
 
 __global__ void __launch_bounds__(kTaskThreads) franka_cabinet_post_kernel(const __grid_constant__ IgeFrankaCabinetArgs a,
                                                                            const int workers) {
+    ige::pdl_prologue();   // PDL: let the next kernel in; wait for the previous one before touching memory
     ige::task_reset_skeleton(a.num_envs, workers, a.reset_buf, a.list, a.rand, [&](int e, bool flagged, uint64_t step) {
         const int D = a.num_dofs;
         long long progress = a.progress_buf[e] + 1;
@@ -440,7 +443,7 @@ template <class K, class Args>
 int launch_workers(K kernel, const Args *a, void *stream, const char *name) {
     int workers = 0;
     if (int rc = ige_task_grid(kernel, a->num_envs, &workers, name)) return rc;
-    kernel<<<workers + (a->list.scratch ? 1 : 0), kTaskThreads, 0, (cudaStream_t)stream>>>(*a, workers);
+ige_launch(kernel, workers + (a->list.scratch ? 1 : 0), kTaskThreads, 0, (cudaStream_t)stream, *a, workers);
     return ige_check_launch(name);
 }
 
@@ -504,7 +507,7 @@ extern "C" int ige_franka_cabinet_pre_physics(const IgeFrankaCabinetArgs *a, voi
     }
     int g = (a->num_envs * 9 + kTaskThreads - 1) / kTaskThreads;
     g = g > sms * 16 ? sms * 16 : g;
-    franka_cabinet_pre_kernel<<<g, kTaskThreads, 0, (cudaStream_t)stream>>>(*a);
+ige_launch(franka_cabinet_pre_kernel, g, kTaskThreads, 0, (cudaStream_t)stream, *a);
     return ige_check_launch(name);
 }
 

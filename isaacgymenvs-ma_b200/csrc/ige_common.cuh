@@ -18,6 +18,8 @@ int ige_check_launch(const char *what);
 extern "C" int ige_use_tma();  // 1 unless IGE_NO_TMA=1 / ige_set_use_tma(0)
 extern "C" int ige_fast_paths();  // 1 unless IGE_GENERIC=1 / ige_set_fast_paths(0)
 
+extern "C" int ige_use_pdl();  // 1 unless IGE_PDL=0 / ige_set_use_pdl(0)
+
 #define IGE_MAX_DEVICES 64   // per-device launch caches (occupancy, function attributes) are indexed by ordinal
 
 #define IGE_REQUIRE_PTR(ptr)                                                       \
@@ -50,6 +52,41 @@ static inline int ige_check_list(const IgeResetList &l) {
 }
 
 #ifdef __CUDACC__
+// ---------------------------------------------------------------------------------------------
+// Programmatic dependent launch (PDL).  A step is ONE short kernel (5-15 us at BASELINE.json's sizes) and steps
+// follow each other on a stream or in a CUDA graph: fully serialised, every kernel pays the grid launch latency
+// and its own prologue (~1 us) on top of its work.  Every kernel of the library therefore
+//   * executes griddepcontrol.launch_dependents first (the next kernel's CTAs may be scheduled as soon as all of this
+//     kernel's CTAs are resident; they then sit in griddepcontrol.wait and issue nothing), and
+//   * executes griddepcontrol.wait BEFORE its first global-memory access: it returns once the previous kernel has
+//     completed and its writes are visible, so the data dependence between consecutive steps is fully kept; what
+//     overlaps is launch latency, argument fetch, barrier / shared-memory set-up;
+// and is launched through ige_launch(), which sets cudaLaunchAttributeProgrammaticStreamSerialization (captured into
+// CUDA graphs as a programmatic edge).  A kernel launched without the attribute executes both instructions as
+// no-ops.  The in-kernel spin-wait protocols are unaffected: a dependent grid is only scheduled once EVERY CTA of
+// its predecessor is resident or done, so it can never take a slot a running kernel is still waiting for.
+// ---------------------------------------------------------------------------------------------
+namespace ige {
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_prologue() { pdl_trigger(); pdl_wait(); }
+}  // namespace ige
+template <typename... KArgs, typename... Args>
+static inline cudaError_t ige_launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                                     Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = ige_use_pdl() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+
 // ---------------------------------------------------------------------------------------------
 // device math (reference: isaacgymenvs/utils/torch_jit_utils.py)
 // ---------------------------------------------------------------------------------------------

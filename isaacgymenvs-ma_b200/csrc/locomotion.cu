@@ -504,6 +504,7 @@ __global__ void __launch_bounds__(32 * (4 + NW_ELEM), HUM ? 3 : 6)  // shared me
 locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p_in,
                             const __grid_constant__ IgeLocomotionBuffers b_in, const int num_tiles,
                             const int workers) {
+    ige::pdl_trigger();   // PDL (ige_common.cuh): the next step's grid may be scheduled behind this one
     const IgeLocomotionParams &p = p_in;
     const IgeLocomotionBuffers &b = b_in;
     using L = Layout<D, NS, HUM>;
@@ -527,6 +528,7 @@ locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p_in,
     // Reset index list: the workers only publish their tiles' entry-flag ballots; the extra last CTA turns them
     // into the ascending id list (ige::list_scanner_cta) -- no worker ever waits for another CTA.
     if ((int)blockIdx.x >= workers) {
+        ige::pdl_wait();
         ige::list_scanner_cta<32 * NW>(b_in.list, num_tiles, p_in.rand.step);
         return;
     }
@@ -543,12 +545,13 @@ locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p_in,
     // advance the word (ige::list_cta_publish) is taken after it.
     __shared__ uint64_t s_step;
     if (tid == 0) {
-        s_step = ige::load_step(p_in.rand);
 #pragma unroll
         for (int s = 0; s < IN_STAGES; ++s) ige::mbar_init(&full[s], 1);
         ige::fence_mbar_init();
     }
-    __syncthreads();   // staged arguments, step word and mbarriers are visible
+    ige::pdl_wait();   // everything above overlapped the previous kernel's tail; global memory from here on
+    if (tid == 0) s_step = ige::load_step(p_in.rand);
+    __syncthreads();   // step word and mbarriers are visible
     const uint64_t step = s_step;
     const bool clamp_copy = b.obs_clamped != nullptr && p.clip_obs < INFINITY;
     const bool second_obs_copy = b.obs_clamped != nullptr && !clamp_copy;
@@ -724,7 +727,8 @@ locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p_in,
 template <int D, int NS, bool HUM, int NW_ELEM>
 __global__ void __launch_bounds__(32 * (4 + NW_ELEM))
 locomotion_tile_kernel(const __grid_constant__ IgeLocomotionParams p, const __grid_constant__ IgeLocomotionBuffers b,
-                       const int tile_offset, const int emit_mode) {
+                       const int tile_offset, const int emit_mode, const int step_bias) {
+    ige::pdl_prologue();   // PDL: let the next kernel in; wait for the previous one before touching memory
     using L = Layout<D, NS, HUM>;
     constexpr int NUM_OBS = L::NUM_OBS;
     constexpr int NW = 4 + NW_ELEM;
@@ -736,7 +740,9 @@ locomotion_tile_kernel(const __grid_constant__ IgeLocomotionParams p, const __gr
     const int role = (warp + (int)blockIdx.x) % NW;
     const int e0 = (blockIdx.x + tile_offset) * TE;
     const int ne = min(TE, p.num_envs - e0);
-    const uint64_t step = ige::load_step(p.rand);
+    // step_bias = 1: this launch follows the pipelined kernel of the SAME step, whose scanner CTA has already advanced
+    // the Philox step word
+    const uint64_t step = ige::load_step(p.rand) - (uint64_t)step_bias;
 
     coop_copy(in.root, b.root_states + (size_t)e0 * 13, ne * 13);
     coop_copy(in.dof, (const float *)b.dof_state + (size_t)e0 * D * 2, ne * D * 2);
@@ -883,12 +889,13 @@ int launch(const IgeLocomotionParams *p, const IgeLocomotionBuffers *b, cudaStre
         const int scanner = b->list.scratch ? 1 : 0;
         const int per_cta = (pipelined_tiles + (max_ctas - scanner) - 1) / (max_ctas - scanner);
         const int workers = (pipelined_tiles + per_cta - 1) / per_cta;
-        kern<<<workers + scanner, NT, smem, stream>>>(*p, *b, pipelined_tiles, workers);
+ige_launch(kern, workers + scanner, NT, smem, stream, *p, *b, pipelined_tiles, workers);
         if (int rc = ige_check_launch(name)) return rc;
     }
     if (fallback_tiles > 0) {  // TMA mode: at most the one ragged tile, whose ids come last -> append
-        locomotion_tile_kernel<D, NS, HUM, NW_ELEM><<<fallback_tiles, NT, 0, stream>>>(
-            *p, *b, fallback_offset, pipelined_tiles == 0 ? EMIT_MASKS : EMIT_APPEND);
+ige_launch(locomotion_tile_kernel<D, NS, HUM, NW_ELEM>, fallback_tiles, NT, 0, stream, *p, *b, fallback_offset,
+                   pipelined_tiles == 0 ? (int)EMIT_MASKS : (int)EMIT_APPEND,
+                   (pipelined_tiles > 0 && b->list.scratch && p->rand.mode == IGE_RAND_PHILOX && p->rand.step) ? 1 : 0);
         if (int rc = ige_check_launch(name)) return rc;
     }
     return IGE_OK;

@@ -19,6 +19,7 @@ constexpr int kCtasPerSm = 8;
 __device__ __forceinline__ float clamp_sym(float x, float c) { return fminf(fmaxf(x, -c), c); }  // torch.clamp
 
 __global__ void __launch_bounds__(kThreads) action_force_kernel(const __grid_constant__ IgeActionForceArgs a) {
+    ige::pdl_prologue();   // PDL: let the next kernel in; wait for the previous one before touching memory
     __shared__ float s_gear[IGE_MAX_DOF];
     if (threadIdx.x < IGE_MAX_DOF) s_gear[threadIdx.x] = a.gears[threadIdx.x];
     __syncthreads();
@@ -50,6 +51,7 @@ __global__ void __launch_bounds__(kThreads) action_force_kernel(const __grid_con
 }
 
 __global__ void __launch_bounds__(kThreads) hand_targets_kernel(const __grid_constant__ IgeHandTargetArgs a) {
+    ige::pdl_prologue();   // PDL: let the next kernel in; wait for the previous one before touching memory
     __shared__ float s_lo[IGE_MAX_DOF], s_hi[IGE_MAX_DOF];
     __shared__ int s_dof[IGE_MAX_DOF];
     if (threadIdx.x < IGE_MAX_DOF) {
@@ -102,7 +104,7 @@ extern "C" int ige_locomotion_pre_physics(const IgeActionForceArgs *a, void *str
     IGE_REQUIRE_PTR(a->forces);
     if (a->actions_in == a->actions) return ige_fail(IGE_EPARAM, "actions_in must not alias actions");
     if (a->num_envs == 0) return IGE_OK;
-    action_force_kernel<<<grid_for((long long)a->num_envs * a->num_dof / 4), kThreads, 0, (cudaStream_t)stream>>>(*a);
+ige_launch(action_force_kernel, grid_for((long long)a->num_envs * a->num_dof / 4), kThreads, 0, (cudaStream_t)stream, *a);
     return ige_check_launch("ige_locomotion_pre_physics");
 }
 
@@ -120,6 +122,6 @@ extern "C" int ige_shadow_hand_pre_physics_targets(const IgeHandTargetArgs *a, v
     IGE_REQUIRE_PTR(a->cur_targets);
     if (a->actions_in == a->actions) return ige_fail(IGE_EPARAM, "actions_in must not alias actions");
     if (a->num_envs == 0) return IGE_OK;
-    hand_targets_kernel<<<grid_for((long long)a->num_envs * a->num_actions), kThreads, 0, (cudaStream_t)stream>>>(*a);
+ige_launch(hand_targets_kernel, grid_for((long long)a->num_envs * a->num_actions), kThreads, 0, (cudaStream_t)stream, *a);
     return ige_check_launch("ige_shadow_hand_pre_physics_targets");
 }

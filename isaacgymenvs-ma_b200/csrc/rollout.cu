@@ -39,6 +39,7 @@ __device__ __forceinline__ uint32_t poll(const uint32_t *p) { return *reinterpre
 // Chunk c is CTA c (CTAs are dispatched in block-index order, so a CTA's predecessors are always running or done --
 // the same assumption as the reset list of the locomotion kernel); slots: scratch[2 + c], retirement counter: scratch[1].
 __global__ void __launch_bounds__(kThreads) ma_rollout_step_kernel(IgeRolloutStepArgs a, int num_chunks, int vec) {
+    ige::pdl_prologue();   // PDL: let the next kernel in; wait for the previous one before touching memory
     uint32_t *scratch = a.scratch;
     __shared__ int s_last;
     __shared__ int s_warp[kThreads / 32];
@@ -234,6 +235,7 @@ __global__ void __launch_bounds__(kThreads) ma_rollout_step_kernel(IgeRolloutSte
 
 // thread per row, backwards over the horizon; every (t, rows) slab is read/written coalesced
 __global__ void __launch_bounds__(256) ma_discount_values_kernel(IgeDiscountArgs a) {
+    ige::pdl_prologue();   // PDL: let the next kernel in; wait for the previous one before touching memory
     const int r = blockIdx.x * blockDim.x + threadIdx.x;
     if (r >= a.num_rows) return;
     const size_t n = (size_t)a.num_rows;
@@ -284,7 +286,7 @@ extern "C" int ige_ma_rollout_step(const IgeRolloutStepArgs *a, void *stream) {
     if (!a->done_rows || !a->done_count || !a->meter_mean || !a->meter_size || !a->reduce_scratch || !a->scratch)
         return ige_fail(IGE_ENULL, "done_rows / done_count / meter_* / reduce_scratch / scratch must be non-NULL");
     const int num_chunks = a->num_rows == 0 ? 1 : (a->num_rows + kChunk - 1) / kChunk;
-    ma_rollout_step_kernel<<<num_chunks, kThreads, 0, (cudaStream_t)stream>>>(*a, num_chunks, vec);
+ige_launch(ma_rollout_step_kernel, num_chunks, kThreads, 0, (cudaStream_t)stream, *a, num_chunks, vec);
     return ige_check_launch("ige_ma_rollout_step");
 }
 
@@ -294,6 +296,6 @@ extern "C" int ige_ma_discount_values(const IgeDiscountArgs *a, void *stream) {
     if (!a->dones || !a->last_values || !a->mb_dones || !a->mb_values || !a->mb_rewards || !a->mb_returns)
         return ige_fail(IGE_ENULL, "dones / last_values / mb_* must be non-NULL");
     if (a->num_rows == 0 || a->horizon == 0) return IGE_OK;
-    ma_discount_values_kernel<<<(a->num_rows + 255) / 256, 256, 0, (cudaStream_t)stream>>>(*a);
+ige_launch(ma_discount_values_kernel, (a->num_rows + 255) / 256, 256, 0, (cudaStream_t)stream, *a);
     return ige_check_launch("ige_ma_discount_values");
 }

@@ -166,6 +166,7 @@ __device__ void hand_reset_env_coop(const IgeShadowHandParams &p, const IgeShado
 
 __global__ void __launch_bounds__(128) shadow_hand_reset_kernel(const __grid_constant__ IgeShadowHandParams p,
                                                                 const __grid_constant__ IgeShadowHandBuffers b) {
+    ige::pdl_prologue();   // PDL: let the next kernel in; wait for the previous one before touching memory
     __shared__ float s_u[4][2 * IGE_MAX_DOF + 8];
     const int e = blockIdx.x * blockDim.x + threadIdx.x, lane = threadIdx.x & 31;
     const IgeHandResetRand &r = p.rand;
@@ -308,6 +309,7 @@ __global__ void __launch_bounds__(NT) shadow_hand_post_physics_kernel(const __gr
                                                                       const __grid_constant__ IgeShadowHandBuffers b,
                                                                       const int use_tma, const int tile0,
                                                                       const int expected_ctas) {
+    ige::pdl_prologue();   // PDL: let the next kernel in; wait for the previous one before touching memory
     extern __shared__ __align__(128) float smem[];
     const int nobs = hand_num_obs(p.obs_type);
     const int slay = hand_state_layout(p.obs_type), nst = hand_num_obs(slay);
@@ -454,6 +456,7 @@ __global__ void __launch_bounds__(FNT, kFastCtasPerSm)
 shadow_hand_post_physics_fast_kernel(const __grid_constant__ IgeShadowHandParams p,
                                      const __grid_constant__ IgeShadowHandBuffers b, const int num_tiles,
                                      const int expected_ctas) {
+    ige::pdl_prologue();   // PDL: let the next kernel in; wait for the previous one before touching memory
     extern __shared__ __align__(128) float smem[];
     constexpr int nobs = hand_num_obs(LAYOUT);
     constexpr int FD = fast_dofs(LAYOUT), FA = fast_actions(LAYOUT);
@@ -732,7 +735,7 @@ extern "C" int ige_shadow_hand_reset(const IgeShadowHandParams *p, const IgeShad
     if (p->rand.mode != IGE_RAND_INJECTED && p->rand.mode != IGE_RAND_PHILOX) return ige_fail(IGE_EPARAM, "rand.mode invalid");
     if (p->num_envs == 0) return IGE_OK;
     const int grid = (p->num_envs + 127) / 128;
-    shadow_hand_reset_kernel<<<grid, 128, 0, (cudaStream_t)stream>>>(*p, *b);
+ige_launch(shadow_hand_reset_kernel, grid, 128, 0, (cudaStream_t)stream, *p, *b);
     return ige_check_launch("ige_shadow_hand_reset");
 }
 
@@ -788,13 +791,13 @@ extern "C" int ige_shadow_hand_post_physics(const IgeShadowHandParams *p, const 
         }
         const int grid = full < sms * kFastCtasPerSm ? full : sms * kFastCtasPerSm;
         if (full > 0) {
-            fast_kernel(p->obs_type, p->asymmetric_obs != 0)<<<grid, FNT, smem, s>>>(*p, *b, full, grid + ragged);
+ige_launch(fast_kernel(p->obs_type, p->asymmetric_obs != 0), grid, FNT, smem, s, *p, *b, full, grid + ragged);
             if (int rc = ige_check_launch("ige_shadow_hand_post_physics(fast)")) return rc;
         }
         if (ragged == 0) return IGE_OK;
-        shadow_hand_post_physics_kernel<<<ragged, NT, smem, s>>>(*p, *b, ige_use_tma(), full, grid + ragged);
+ige_launch(shadow_hand_post_physics_kernel, ragged, NT, smem, s, *p, *b, ige_use_tma(), full, grid + ragged);
     } else {
-        shadow_hand_post_physics_kernel<<<tiles, NT, smem, s>>>(*p, *b, ige_use_tma(), 0, tiles);
+ige_launch(shadow_hand_post_physics_kernel, tiles, NT, smem, s, *p, *b, ige_use_tma(), 0, tiles);
     }
     return ige_check_launch("ige_shadow_hand_post_physics");
 }

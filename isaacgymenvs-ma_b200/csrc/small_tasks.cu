@@ -25,6 +25,7 @@ __device__ __forceinline__ float tensor_clampf(float t, float lo, float hi) { re
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kTaskThreads) ball_balance_pre_kernel(const __grid_constant__ IgeBallBalanceArgs a,
                                                                         const int workers) {
+    ige::pdl_prologue();   // PDL: let the next kernel in; wait for the previous one before touching memory
     ige::task_reset_skeleton(a.num_envs, workers, a.reset_buf, a.list, a.rand, [&](int e, bool flagged, uint64_t step) {
         float tg[6], act[3];
 #pragma unroll
@@ -73,6 +74,7 @@ __global__ void __launch_bounds__(kTaskThreads) ball_balance_pre_kernel(const __
 }
 
 __global__ void __launch_bounds__(kTaskThreads) ball_balance_post_kernel(const __grid_constant__ IgeBallBalanceArgs a) {
+    ige::pdl_prologue();   // PDL: let the next kernel in; wait for the previous one before touching memory
     for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < a.num_envs; e += gridDim.x * blockDim.x) {
         const long long progress = a.progress_buf[e] + 1;   // :434
         long long reset = a.reset_buf[e];
@@ -133,6 +135,7 @@ __global__ void __launch_bounds__(kTaskThreads) ball_balance_post_kernel(const _
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kTaskThreads) quadcopter_pre_kernel(const __grid_constant__ IgeQuadcopterArgs a,
                                                                       const int workers) {
+    ige::pdl_prologue();   // PDL: let the next kernel in; wait for the previous one before touching memory
     ige::task_reset_skeleton(a.num_envs, workers, a.reset_buf, a.list, a.rand, [&](int e, bool flagged, uint64_t step) {
         float tg[8], th[4], act[12], pos[8];
 #pragma unroll
@@ -208,6 +211,7 @@ __device__ __forceinline__ float copter_reward(const float *root, float target_d
 }
 
 __global__ void __launch_bounds__(kTaskThreads) quadcopter_post_kernel(const __grid_constant__ IgeQuadcopterArgs a) {
+    ige::pdl_prologue();   // PDL: let the next kernel in; wait for the previous one before touching memory
     for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < a.num_envs; e += gridDim.x * blockDim.x) {
         const long long progress = a.progress_buf[e] + 1;   // :335
         float root[13], obs[21];
@@ -258,6 +262,7 @@ __device__ __forceinline__ void ingenuity_set_target(const IgeIngenuityArgs &a, 
 
 __global__ void __launch_bounds__(kTaskThreads) ingenuity_pre_kernel(const __grid_constant__ IgeIngenuityArgs a,
                                                                      const int workers) {
+    ige::pdl_prologue();   // PDL: let the next kernel in; wait for the previous one before touching memory
     ige::task_reset_skeleton(
         a.num_envs, workers, a.reset_buf, a.list, a.rand,
         [&](int e, bool flagged, uint64_t step) {
@@ -322,6 +327,7 @@ __global__ void __launch_bounds__(kTaskThreads) ingenuity_pre_kernel(const __gri
 }
 
 __global__ void __launch_bounds__(kTaskThreads) ingenuity_post_kernel(const __grid_constant__ IgeIngenuityArgs a) {
+    ige::pdl_prologue();   // PDL: let the next kernel in; wait for the previous one before touching memory
     for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < a.num_envs; e += gridDim.x * blockDim.x) {
         const long long progress = a.progress_buf[e] + 1;   // :368
         float root[13], tgt[3], obs[13];
@@ -378,7 +384,7 @@ template <class K, class Args>
 int launch_pre(K kernel, const Args *a, void *stream, const char *name) {
     int workers = 0;
     if (int rc = ige_task_grid(kernel, a->num_envs, &workers, name)) return rc;
-    kernel<<<workers + (a->list.scratch ? 1 : 0), kTaskThreads, 0, (cudaStream_t)stream>>>(*a, workers);
+ige_launch(kernel, workers + (a->list.scratch ? 1 : 0), kTaskThreads, 0, (cudaStream_t)stream, *a, workers);
     return ige_check_launch(name);
 }
 
@@ -404,7 +410,7 @@ extern "C" int ige_ball_balance_post_physics(const IgeBallBalanceArgs *a, void *
     IGE_REQUIRE_PTR(a->rew_buf);
     IGE_OPTIONAL_PTR(a->obs_clamped);
     if (a->num_envs == 0) return IGE_OK;
-    ball_balance_post_kernel<<<post_grid(a->num_envs), kTaskThreads, 0, (cudaStream_t)stream>>>(*a);
+ige_launch(ball_balance_post_kernel, post_grid(a->num_envs), kTaskThreads, 0, (cudaStream_t)stream, *a);
     return ige_check_launch("ige_ball_balance_post_physics");
 }
 
@@ -431,7 +437,7 @@ extern "C" int ige_quadcopter_post_physics(const IgeQuadcopterArgs *a, void *str
     IGE_REQUIRE_PTR(a->rew_buf);
     IGE_OPTIONAL_PTR(a->obs_clamped);
     if (a->num_envs == 0) return IGE_OK;
-    quadcopter_post_kernel<<<post_grid(a->num_envs), kTaskThreads, 0, (cudaStream_t)stream>>>(*a);
+ige_launch(quadcopter_post_kernel, post_grid(a->num_envs), kTaskThreads, 0, (cudaStream_t)stream, *a);
     return ige_check_launch("ige_quadcopter_post_physics");
 }
 
@@ -460,6 +466,6 @@ extern "C" int ige_ingenuity_post_physics(const IgeIngenuityArgs *a, void *strea
     IGE_REQUIRE_PTR(a->rew_buf);
     IGE_OPTIONAL_PTR(a->obs_clamped);
     if (a->num_envs == 0) return IGE_OK;
-    ingenuity_post_kernel<<<post_grid(a->num_envs), kTaskThreads, 0, (cudaStream_t)stream>>>(*a);
+ige_launch(ingenuity_post_kernel, post_grid(a->num_envs), kTaskThreads, 0, (cudaStream_t)stream, *a);
     return ige_check_launch("ige_ingenuity_post_physics");
 }

@@ -18,6 +18,7 @@ static_assert(IGE_STATS_ROWS >= IGE_MAX_RANKS, "stats_exchange_kernel: one threa
 
 __global__ void __launch_bounds__(IGE_STATS_ROWS * IGE_NUM_STATS)
 stats_snapshot_kernel(float *__restrict__ rows, float *__restrict__ out, const int zero_rows, const int accumulate) {
+    ige::pdl_prologue();   // PDL: let the next kernel in; wait for the previous one before touching memory
     __shared__ float s[IGE_STATS_ROWS][IGE_NUM_STATS + 1];
     const int r = threadIdx.x / IGE_NUM_STATS, c = threadIdx.x % IGE_NUM_STATS;
     s[r][c] = __ldcg(rows + r * IGE_STATS_STRIDE + c);   // atomics land in L2
@@ -50,6 +51,7 @@ __device__ __forceinline__ uint64_t global_ns() {
 }
 
 __global__ void __launch_bounds__(IGE_STATS_ROWS * IGE_NUM_STATS) stats_exchange_kernel(const __grid_constant__ IgeStatsExchangeArgs a) {
+    ige::pdl_prologue();   // PDL: let the next kernel in; wait for the previous one before touching memory
     __shared__ float s[IGE_STATS_ROWS][IGE_NUM_STATS + 1];
     __shared__ float s_vec[IGE_NUM_STATS];
     __shared__ float s_peer[IGE_MAX_RANKS][IGE_NUM_STATS];
@@ -158,7 +160,7 @@ extern "C" int ige_stats_exchange(const IgeStatsExchangeArgs *a, void *stream) {
     for (int r = 0; r < a->world; ++r)
         if (!a->mailbox[r] || (reinterpret_cast<uintptr_t>(a->mailbox[r]) & 7u))
             return ige_fail(IGE_ENULL, "ige_stats_exchange: mailbox[%d] is NULL / misaligned", r);
-    stats_exchange_kernel<<<1, IGE_STATS_ROWS * IGE_NUM_STATS, 0, (cudaStream_t)stream>>>(*a);
+ige_launch(stats_exchange_kernel, 1, IGE_STATS_ROWS * IGE_NUM_STATS, 0, (cudaStream_t)stream, *a);
     return ige_check_launch("ige_stats_exchange");
 }
 
@@ -166,7 +168,7 @@ extern "C" int ige_stats_snapshot(const IgeStatsSnapshotArgs *a, void *stream) {
     if (!a) return ige_fail(IGE_ENULL, "args is NULL");
     IGE_REQUIRE_PTR(a->stats);
     IGE_REQUIRE_PTR(a->out);
-    stats_snapshot_kernel<<<1, IGE_STATS_ROWS * IGE_NUM_STATS, 0, (cudaStream_t)stream>>>(a->stats, a->out, a->zero_stats,
+ige_launch(stats_snapshot_kernel, 1, IGE_STATS_ROWS * IGE_NUM_STATS, 0, (cudaStream_t)stream, a->stats, a->out, a->zero_stats,
                                                                                            a->accumulate);
     return ige_check_launch("ige_stats_snapshot");
 }

@@ -235,8 +235,11 @@ def hand_reward_slack(obj, ref_obs):
 
     def rot_rew(q):
         return scale / (np.abs(2.0 * np.arcsin(np.clip(q, 0.0, 1.0))) + eps)
-    d = 2.4e-7 * np.maximum(qn, 1e-3)
+    d = 4.8e-7 * np.maximum(qn, 1e-3)          # +-4 ulp of |q_xyz| (sinf / cosf / sqrt chain of the re-drawn quaternion)
     return np.maximum(np.abs(rot_rew(qn + d) - rot_rew(qn)), np.abs(rot_rew(qn - d) - rot_rew(qn)))
+
+
+SLACK_USED = {"rows": 0, "of": 0}      # how many reward rows needed the carve-out (reported by the tests)
 
 
 def assert_float_close(name, got, ref, rtol=RTOL, slack=None):
@@ -247,6 +250,11 @@ def assert_float_close(name, got, ref, rtol=RTOL, slack=None):
     bound = rtol * np.maximum(1.0, np.abs(ref))
     if slack is not None:
         bound = bound + np.asarray(slack, dtype=np.float64).reshape(-1)
+    if slack is not None:               # the carve-out must stay a carve-out: count the rows that needed it
+        used = int((err > rtol * np.maximum(1.0, np.abs(ref))).sum())
+        SLACK_USED["rows"] += used
+        SLACK_USED["of"] += int(err.size)
+        assert used <= max(2, err.size // 500), f"{name}: {used}/{err.size} rows needed the conditioning slack (> 0.2 %)"
     bad = ~(err <= bound)
     if bad.any():
         i = int(np.argmax(err / bound))

@@ -65,6 +65,8 @@ def test_oracle_osc_matches_reference_pre_physics():
         H.assert_equal("actions", got["out_actions"], blob["out_actions"])
         H.assert_equal("pos_control", got["out_pos_control"], blob["out_pos_control"])
         assert O.torque_error(got, blob) <= 1e-4, (path, O.torque_error(got, blob))
+        over, rows = O.rows_over(got, blob)
+        print(f"{os.path.basename(path)}: {over} of {rows} agent rows beyond 1e-5 of the reference's fp32 torques")
         assert O.torque_error(got, truth) <= 2.0 * O.torque_error(blob, truth) + 1e-5
         # untouched columns (6 of each arm, 7..8) keep their previous value: franka_PPMA.py:944 assigns [:, :6]
         eff, ref = got["out_effort_control"].reshape(-1, 9), blob["out_effort_control"].reshape(-1, 9)

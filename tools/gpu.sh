@@ -19,7 +19,7 @@ for act in "$@"; do
   case "$a" in
     tests)
       if [ -n "$b" ]; then timeout 600 python -m pytest tests -m gpu -x -q -k "$b" > gpurun_out/pytest_gpu_k.log 2>&1; echo "pytest -k '$b' rc=$?"; tail -5 gpurun_out/pytest_gpu_k.log
-      else timeout 1500 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -5 gpurun_out/pytest_gpu.log; fi ;;
+      else timeout 1500 python -m pytest tests -m gpu --maxfail=25 -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -5 gpurun_out/pytest_gpu.log; fi ;;
     smoke) timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?"; tail -3 gpurun_out/smoke.log ;;
     bench) timeout 600 python bench.py > gpurun_out/${R}_bench_default.json 2> gpurun_out/bench_default.err; echo "bench rc=$?"; tail -2 gpurun_out/bench_default.err; cut -c1-1500 gpurun_out/${R}_bench_default.json ;;
     driver) timeout 300 python bench.py --gpus 1 --steps 20 --warmup 5 > gpurun_out/${R}_bench_driver_n1.json 2> gpurun_out/bench_driver.err; echo "driver-bench rc=$?"; tail -2 gpurun_out/bench_driver.err; cut -c1-900 gpurun_out/${R}_bench_driver_n1.json ;;
