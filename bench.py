@@ -171,6 +171,7 @@ def run_ours(args):
         raise SystemExit("bench.py needs a CUDA device: the post-physics kernels have no CPU fallback")
     torch.cuda.set_device(local_rank)
     device = torch.device("cuda", local_rank)
+    numa_node = pkg.distributed.bind_to_gpu_numa_node(local_rank)   # before any pinned arena exists
     dist = None
     if world > 1:
         import torch.distributed as dist
@@ -271,7 +272,9 @@ def run_ours(args):
                                           + (f" (peer mapping unavailable: {reducer.peer_error})"
                                              if getattr(reducer, "peer_error", None) else ""),
                                   "local": "ige_stats_snapshot (single rank)"}[reducer.mode]),
-                "reset_noise": "in-kernel Philox"},
+                "reset_noise": "in-kernel Philox",
+                "pdl": "programmatic dependent launch: on" if lib.lib().ige_use_pdl() else "programmatic dependent launch: off",
+                "host_numa_node": numa_node},
         "gpu_launches": gpu_launches,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": ncu_traffic(task, n), "peak_source": f"MEASURED_PEAKS.json hbm_gbs ({peak_kind})",

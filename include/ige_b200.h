@@ -804,6 +804,8 @@ void ige_set_fast_paths(int on);
 /* Debug knob: 0 = launch the kernels fully stream-serialised instead of with programmatic dependent launch (each
  * kernel waits for its predecessor's completion before its first memory access either way); also IGE_PDL=0. */
 void ige_set_use_pdl(int on);
+/* PCI bus id ("0000:1b:00.0") of CUDA device `device` (host NUMA placement of pinned arenas, one rank per GPU). */
+int ige_device_pci_bus_id(int device, char *out, int len);
 
 #ifdef __cplusplus
 }

@@ -74,6 +74,8 @@ def lib():
         l.ige_mailbox_destroy.argtypes = [C.c_void_p]
         l.ige_set_use_tma.restype = None
         l.ige_set_use_tma.argtypes = [C.c_int]
+        l.ige_device_pci_bus_id.restype = C.c_int
+        l.ige_device_pci_bus_id.argtypes = [C.c_int, C.c_char_p, C.c_int]
         l.ige_set_use_pdl.restype = None
         l.ige_set_use_pdl.argtypes = [C.c_int]
         l.ige_set_fast_paths.restype = None
@@ -90,7 +92,7 @@ def lib():
 
 def exported_symbols():
     return ["ige_version", "ige_last_error_string", "ige_launch_count", "ige_compact_scratch_words",
-            "ige_reset_list_scratch_words", "ige_rollout_scratch_words", "ige_anymal_scratch_words", "ige_set_use_tma", "ige_set_fast_paths", "ige_set_use_pdl",
+            "ige_reset_list_scratch_words", "ige_rollout_scratch_words", "ige_anymal_scratch_words", "ige_set_use_tma", "ige_set_fast_paths", "ige_set_use_pdl", "ige_device_pci_bus_id",
             "ige_mailbox_bytes", "ige_mailbox_create", "ige_mailbox_open", "ige_mailbox_close", "ige_mailbox_destroy", *_SIGS.keys()]
 
 

@@ -52,3 +52,12 @@ extern "C" int ige_use_pdl() {
     }
     return g_use_pdl;
 }
+
+// PCI bus id ("0000:1b:00.0") of a device: the host side binds each rank to its GPU's NUMA node before it allocates
+// pinned arenas (distributed.bind_to_gpu_numa_node).
+extern "C" int ige_device_pci_bus_id(int device, char *out, int len) {
+    if (!out || len < 16) return ige_fail(IGE_ENULL, "ige_device_pci_bus_id: buffer too small");
+    cudaError_t e = cudaDeviceGetPCIBusId(out, len, device);
+    if (e != cudaSuccess) { cudaGetLastError(); return ige_fail((int)e, "cudaDeviceGetPCIBusId: %s", cudaGetErrorString(e)); }
+    return IGE_OK;
+}
