@@ -464,14 +464,17 @@ __global__ void __launch_bounds__(NT) franka_ma_kernel(const __grid_constant__ I
 // rewriting in this very launch.  Round 1 ran the reset as a separate launch for that reason.  Here the reader
 // never uses a row that is being rewritten: post-reset cube positions are a pure function of (env, draw,
 // step | reset rank), so it recomputes env j's when env j resets and uses memory when it does not.  "Does env j
-// reset" comes from the reset-list SLOT of env j's tile ({launch tag : entry-flag ballot}, ige::list_publish_slot),
-// which its owner CTA publishes in its prologue -- for ALL of its tiles, before it waits for anybody's slot, so the
-// cross-CTA waits cannot form a cycle -- and never from reset_buf, which the owner is free to overwrite at once.
-// The ascending reset id list is written by one extra scanner CTA from the same slots (ige::list_scanner_cta); no
-// worker waits for a prefix, a ticket or an epoch.  The loads of a CTA's first tile are issued BEFORE that prologue:
-// the flag round trip, the slot round trip and the tile's DRAM round trip overlap instead of following each other.
+// reset" is env j's ENTRY flag, which every CTA snapshots for all of its rows in its prologue (a ballot per tile in
+// shared memory) BEFORE it publishes its reset-list slots ({launch tag : entry-flag ballot}, ige::list_publish_slot).
+// The ascending reset id list is written by one extra scanner CTA from those slots (ige::list_scanner_cta); once it
+// has seen every CTA's slots it stores the launch tag, and only then -- one tile of work later, so the poll never
+// actually spins -- do the workers overwrite reset_buf.  No worker waits for a prefix or a ticket.  (Polling the
+// partner's SLOT instead of snapshotting its flag was measured: 16 k threads spinning on a few L2 lines cost
+// +1.4 us.)  The loads of a CTA's first tile are issued BEFORE the prologue: the flag round trip and the tile's
+// DRAM round trip overlap instead of following each other.
 constexpr int RT_E = 32;                // envs per tile
 constexpr int RT_NT = 2 * RT_E;         // threads per CTA = rows per tile
+constexpr int RT_MAX_TILES = 96;        // tiles per CTA the partner-flag snapshot of Combine / PP has room for
 
 // four consecutive uniforms j = 4 blk .. 4 blk + 3 of draw `draw` for env `env` (reset rank `rank`)
 __device__ __forceinline__ void ma_uniform4(const IgeMAResetRand &r, uint64_t step, int draw, int rank, int env, int cols,
@@ -520,6 +523,7 @@ __global__ void __launch_bounds__(RT_NT) franka_ma_rows_kernel(const __grid_cons
     __shared__ __align__(128) float obs_tile[2][RT_NT * NO];
     __shared__ uint64_t s_step;
     __shared__ uint32_t s_tag;
+    __shared__ uint32_t s_pmask[PAIRED ? RT_MAX_TILES : 1][2];   // bit = "the partner env of this row resets in this launch"
     __shared__ int s_last;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int N = p.num_envs;
@@ -604,8 +608,24 @@ __global__ void __launch_bounds__(RT_NT) franka_ma_rows_kernel(const __grid_cons
     };
     if (my_tiles > 0) load_tile(0);
 
-    // ---- prologue: the entry-flag ballot of EVERY tile of this CTA goes out before the CTA waits for anybody ----
-    __syncthreads();   // step word and launch tag were read before this CTA's first publish
+    // ---- prologue.  Combine / PP: snapshot the ENTRY flags of the partner envs of every row of every tile (warp w
+    //      takes rows [32 w, 32 w + 32) of each tile).  Only then are this CTA's slots published, and reset_buf is
+    //      not overwritten by anybody before the scanner has seen EVERY CTA's slots (the gate below) ----
+    if (PAIRED) {
+        for (int t = 0; t < my_tiles; ++t) {
+            const int row = ((first + t) * RT_E) * A + tid;
+            bool f = false;
+            if (row < N * A) {
+                bool fh;
+                const int pj = partner_env(row, fh);
+                const longlong2 r = *reinterpret_cast<const longlong2 *>(b.reset_buf + (size_t)pj * A);
+                f = r.x != 0 && r.y != 0;
+            }
+            const uint32_t m = __ballot_sync(0xffffffffu, f);
+            if (lane == 0) s_pmask[t][warp] = m;
+        }
+    }
+    __syncthreads();   // step word, launch tag and every partner flag were read before this CTA's first publish
     const uint64_t step = s_step;
     const uint32_t ltag = s_tag;
     if (emit && warp == 0) {
@@ -625,6 +645,7 @@ __global__ void __launch_bounds__(RT_NT) franka_ma_rows_kernel(const __grid_cons
 #pragma unroll
     for (int i = 0; i < NC; ++i) comp[i] = 0.0f;
     float st_rew = 0.f, st_done = 0.f, st_to = 0.f, st_len = 0.f, st_n = 0.f;
+    bool flags_open = !PAIRED;   // may reset_buf be overwritten yet?
     for (int t = 0; t < my_tiles; ++t) {
         const int e0 = (first + t) * RT_E;
         const int ne = min(RT_E, N - e0);
@@ -633,8 +654,7 @@ __global__ void __launch_bounds__(RT_NT) franka_ma_rows_kernel(const __grid_cons
         const int ec = valid ? e : N - 1;
         const size_t row = (size_t)ec * A + a;
         float *otile = obs_tile[t & 1];
-        // does the partner env reset in this launch?  Its owner's slot (published in that CTA's prologue)
-        const bool j_reset = PAIRED && ige::list_slot_bit(b.list, ltag, j);
+        const bool j_reset = PAIRED && ((s_pmask[PAIRED ? t : 0][warp] >> lane) & 1u);   // does the partner env reset in this launch?
 
         // ---- post_physics_step :821-826: progress++, agent flags -> reset_idx (AND filter) ----
         const long long rst_o = __shfl_xor_sync(0xffffffffu, rst, 1);
@@ -898,8 +918,15 @@ __global__ void __launch_bounds__(RT_NT) franka_ma_rows_kernel(const __grid_cons
         const int count = ne * A * NO;
         const bool bulk = use_tma && (count % 4 == 0);
         if (bulk) ige::fence_proxy_async();
+        if (!flags_open && tid == 0) {
+            // the gate: the scanner CTA stores the launch tag once it has seen the slots of EVERY CTA, i.e. once every
+            // CTA is past its partner-flag snapshot.  By now (one tile of work later) it has long done so.
+            const uint64_t *sc = reinterpret_cast<const uint64_t *>(b.list.scratch);
+            while ((uint32_t)ige::ld_relaxed_gpu_u64(sc) != ltag) __nanosleep(100);
+        }
         if (t >= 1 && tid == 0) ige::bulk_wait_read_all();  // tile t - 1 has left obs_tile[(t + 1) & 1]: free for tile t + 1
         __syncthreads();
+        flags_open = true;
         if (valid) {
             b.rew_buf[row] = rewards;
             b.reset_buf[row] = rst;
@@ -1022,9 +1049,11 @@ extern "C" int ige_franka_ma_post_physics(const IgeFrankaMAParams *p, const IgeF
         const int scanner = b->list.scratch ? 1 : 0;
         const int cap = max_ctas[p->variant][dev] - scanner > 0 ? max_ctas[p->variant][dev] - scanner : 1;
         const int per_cta = (tiles + cap - 1) / cap;
-        const int workers = (tiles + per_cta - 1) / per_cta;   // workers + scanner <= resident capacity: all CTAs co-resident
-        ige_launch(rows[p->variant], workers + scanner, RT_NT, 0, s, *p, *b, tiles, per_cta, ige_use_tma(), workers);
-        return ige_check_launch("ige_franka_ma_post_physics");
+        if (!pair_only || per_cta <= RT_MAX_TILES) {
+            const int workers = (tiles + per_cta - 1) / per_cta;   // workers + scanner <= resident capacity: all CTAs co-resident
+            ige_launch(rows[p->variant], workers + scanner, RT_NT, 0, s, *p, *b, tiles, per_cta, ige_use_tma(), workers);
+            return ige_check_launch("ige_franka_ma_post_physics");
+        }
     }
     const size_t smem = (size_t)TE * p->num_agents * p->num_obs * sizeof(float);
     if (smem > 48 * 1024) {
