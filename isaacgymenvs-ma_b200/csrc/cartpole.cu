@@ -14,7 +14,7 @@ constexpr int kThreads = 256;
 constexpr int kCtasPerSm = 8;   // 8 x 256 threads = the SM's 2048 thread slots
 
 __global__ void __launch_bounds__(kThreads) cartpole_post_physics_kernel(IgeCartpoleParams p, IgeCartpoleBuffers b) {
-    ige::pdl_prologue();   // PDL: let the next kernel in; wait for the previous one before touching memory
+    ige::pdl_prologue_early();   // PDL: let the next kernel in; wait for the previous one before touching memory
     const uint64_t step = ige::load_step(p.rand);
     float st_rew = 0.f, st_done = 0.f, st_to = 0.f, st_len = 0.f, st_n = 0.f;
     const int stride = gridDim.x * kThreads;

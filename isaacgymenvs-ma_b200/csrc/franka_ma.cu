@@ -496,7 +496,6 @@ __global__ void __launch_bounds__(RT_NT) franka_ma_rows_kernel(const __grid_cons
                                                                const __grid_constant__ IgeFrankaMABuffers b_in,
                                                                const int num_tiles, const int tiles_per_cta,
                                                                const int use_tma, const int workers) {
-    ige::pdl_trigger();   // PDL (ige_common.cuh): the next step's grid may be scheduled behind this one
 #if IGE_STAGE_ARGS
     // (experiment) kernel arguments -> shared memory once
     __shared__ __align__(16) IgeFrankaMAParams p;
@@ -538,6 +537,7 @@ __global__ void __launch_bounds__(RT_NT) franka_ma_rows_kernel(const __grid_cons
 
     ige::pdl_wait();   // global memory from here on
     if ((int)blockIdx.x >= workers) {   // the scanner CTA: slots -> ascending id list, count, launch tag, Philox step
+        ige::pdl_trigger();
         ige::list_scanner_cta<RT_NT>(b_in.list, num_tiles, p_in.rand.step);
         return;
     }
@@ -945,6 +945,7 @@ __global__ void __launch_bounds__(RT_NT) franka_ma_rows_kernel(const __grid_cons
         }
         if (t + 1 < my_tiles) load_tile(t + 1);   // (every register of tile t is dead by now)
     }
+    ige::pdl_trigger();   // PDL: the next step's grid may be scheduled behind this CTA's tail (ige_common.cuh)
 
     // ---- reward-component sums (the .mean()s of extras) + statistics ----
 #pragma unroll

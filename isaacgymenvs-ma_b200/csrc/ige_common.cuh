@@ -56,8 +56,9 @@ static inline int ige_check_list(const IgeResetList &l) {
 // Programmatic dependent launch (PDL).  A step is ONE short kernel (5-15 us at BASELINE.json's sizes) and steps
 // follow each other on a stream or in a CUDA graph: fully serialised, every kernel pays the grid launch latency
 // and its own prologue (~1 us) on top of its work.  Every kernel of the library therefore
-//   * executes griddepcontrol.launch_dependents first (the next kernel's CTAs may be scheduled as soon as all of this
-//     kernel's CTAs are resident; they then sit in griddepcontrol.wait and issue nothing), and
+//   * executes griddepcontrol.launch_dependents (at the top or after its main loop, see pdl_prologue below): the next
+//     kernel's CTAs may be scheduled as soon as all of this kernel's CTAs have done so; they then sit in
+//     griddepcontrol.wait and issue nothing, and
 //   * executes griddepcontrol.wait BEFORE its first global-memory access: it returns once the previous kernel has
 //     completed and its writes are visible, so the data dependence between consecutive steps is fully kept; what
 //     overlaps is launch latency, argument fetch, barrier / shared-memory set-up;
@@ -69,7 +70,15 @@ static inline int ige_check_list(const IgeResetList &l) {
 namespace ige {
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
-__device__ __forceinline__ void pdl_prologue() { pdl_trigger(); pdl_wait(); }
+// Where a kernel triggers matters (measured, profiles/r2_pdl_trigger.txt): triggering at the very top lets the grids of
+// the next 3-4 steps pile up resident behind the running one; their shared-memory reservations shrink the running
+// kernel's L1, which the kernels that gather 28-byte pieces of 52-byte rows through L1 pay for (Franka PP 8192 x 2:
+// 12.4 -> 16.5 us, Quadcopter 11.0 -> 15.2 us), while the TMA-staged locomotion kernel and Cartpole gain (Ant 16 384:
+// 6.54 -> 5.98 us).  Policy: locomotion / Cartpole trigger at the top; every other kernel waits at the top and triggers
+// after its main loop (explicitly before its tail, or implicitly by exiting), so at most ONE dependent grid is resident
+// and only during the tail.
+__device__ __forceinline__ void pdl_prologue() { pdl_wait(); }
+__device__ __forceinline__ void pdl_prologue_early() { pdl_trigger(); pdl_wait(); }
 }  // namespace ige
 template <typename... KArgs, typename... Args>
 static inline cudaError_t ige_launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,

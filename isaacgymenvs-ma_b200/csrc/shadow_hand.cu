@@ -668,6 +668,7 @@ shadow_hand_post_physics_fast_kernel(const __grid_constant__ IgeShadowHandParams
         __syncthreads();  // the tile may be overwritten
     }
 
+    ige::pdl_trigger();   // PDL: main loop done
     // ---- per-CTA sums -> global; last CTA: consecutive_successes (:798), re-arm, advance Philox ----
     if (warp == 0) {
         const int cta_resets = __reduce_add_sync(0xffffffffu, acc_resets);

@@ -50,6 +50,7 @@ __device__ __forceinline__ void task_reset_skeleton(int num_envs, int workers, c
                                                     const IgeResetList &L, const IgeTaskRand &rand, EnvFn env,
                                                     TailFn tail = TailFn()) {
     if ((int)blockIdx.x >= workers) {
+        pdl_trigger();
         tail(list_scanner_cta<kTaskThreads>(L, (num_envs + 31) / 32, rand.step));
         return;
     }
@@ -71,6 +72,7 @@ __device__ __forceinline__ void task_reset_skeleton(int num_envs, int workers, c
         if (emit && lane == 0 && e < num_envs) list_publish_slot(L, tag, e >> 5, m);
         if (e < num_envs) env(e, f, step);
     }
+    pdl_trigger();   // main loop done: the next kernel's grid may be scheduled behind this one's tail
 }
 
 }  // namespace ige

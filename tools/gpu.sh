@@ -30,6 +30,22 @@ for act in "$@"; do
           bench.py --gpus $b --steps $steps --warmup 5 --no-sweep > gpurun_out/${R}_bench_n${b}_s${steps}.json 2> gpurun_out/bench_n${b}_s${steps}.err
         echo "scale N=$b steps=$steps rc=$?"; tail -3 gpurun_out/bench_n${b}_s${steps}.err | cut -c1-300; cut -c1-700 gpurun_out/${R}_bench_n${b}_s${steps}.json
       done ;;
+    scalemodes)   # scalemodes:<N>  -- the driver's 20-step window with each statistics-reduction mode (+ none = no branch)
+      for mode in peer nccl none; do
+        for rep in 1 2; do
+        timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $b --master-addr 127.0.0.1 --master-port 29544 \
+          bench.py --gpus $b --steps 20 --warmup 5 --no-sweep --no-e2e --no-cpu --stats-reduce $mode > gpurun_out/${R}_bench_n${b}_s20_${mode}_$rep.json 2> gpurun_out/bench_n${b}_${mode}.err
+        echo "scale N=$b mode=$mode rep=$rep rc=$?"; tail -2 gpurun_out/bench_n${b}_${mode}.err | cut -c1-300
+        python - <<PY
+import json
+try:
+    d = json.loads(open("gpurun_out/${R}_bench_n${b}_s20_${mode}_$rep.json").read().strip().splitlines()[-1])
+    print(f"   ms_per_step {d['ms_per_step']*1e3:.3f} us  value {d['value']/1e9:.3f} G  kernel_us {d['roofline']['kernel_us']:.2f}  reduce: {d['how']['stats_reduce'][:60]}")
+except Exception as e:
+    print("   failed:", e)
+PY
+        done
+      done ;;
     tasks) bash tools/bench_all.sh > gpurun_out/${R}_bench_tasks.txt 2>&1; cat gpurun_out/${R}_bench_tasks.txt ;;
     launches)
       ncu --profile-from-start off --metrics gpu__time_duration.sum --clock-control none -c 400 --csv \
