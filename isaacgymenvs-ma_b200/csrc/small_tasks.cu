@@ -263,9 +263,15 @@ __device__ __forceinline__ void ingenuity_set_target(const IgeIngenuityArgs &a, 
 __global__ void __launch_bounds__(kTaskThreads) ingenuity_pre_kernel(const __grid_constant__ IgeIngenuityArgs a,
                                                                      const int workers) {
     ige::pdl_prologue();   // PDL: let the next kernel in; wait for the previous one before touching memory
-    ige::task_reset_skeleton(
+    ige::task_reset_skeleton<true>(
         a.num_envs, workers, a.reset_buf, a.list, a.rand,
-        [&](int e, bool flagged, uint64_t step) {
+        [&](int e, bool flagged, uint64_t step, bool chunk_any) {
+            // :299-300 re-sets the rotor speeds of ALL envs whenever ANY env resets.  A chunk that holds a flagged env
+            // knows the answer and writes its own envs here; the scanner CTA (below) covers the chunks that hold none.
+            if (chunk_any) {
+                a.dof_states[(size_t)e * 8 + 3] = -50.0f;
+                a.dof_states[(size_t)e * 8 + 7] = 50.0f;
+            }
             float *copter = a.root_tensor + (size_t)e * 26, *marker = copter + 13;
             const bool retarget = a.progress_buf[e] % 500 == 0;   // :325 (progress is read before reset_idx zeroes it)
             if (retarget)
@@ -317,11 +323,19 @@ __global__ void __launch_bounds__(kTaskThreads) ingenuity_pre_kernel(const __gri
             for (int i = 0; i < 3; ++i)
                 reinterpret_cast<float2 *>(a.thrusts + (size_t)e * 6)[i] = make_float2(th[2 * i], th[2 * i + 1]);
         },
-        [&](int total) {   // :299-300: the rotor speeds of ALL envs, whenever ANY env resets
+        [&](int total) {   // :299-300 for the 128-env chunks without a flagged env (their 4 slots are all zero)
             if (total == 0) return;
-            for (int e = threadIdx.x; e < a.num_envs; e += kTaskThreads) {
-                a.dof_states[(size_t)e * 8 + 3] = -50.0f;
-                a.dof_states[(size_t)e * 8 + 7] = 50.0f;
+            const uint64_t *slots = reinterpret_cast<const uint64_t *>(a.list.scratch + ige::kListMaskBase);
+            const int tiles = (a.num_envs + 31) / 32;
+            for (int c = 0; c * kTaskThreads < a.num_envs; ++c) {
+                uint32_t m = 0u;
+                for (int t = 4 * c; t < 4 * c + 4 && t < tiles; ++t) m |= (uint32_t)ige::ld_relaxed_gpu_u64(slots + t);
+                if (m != 0u) continue;
+                const int e = c * kTaskThreads + threadIdx.x;
+                if (e < a.num_envs) {
+                    a.dof_states[(size_t)e * 8 + 3] = -50.0f;
+                    a.dof_states[(size_t)e * 8 + 7] = 50.0f;
+                }
             }
         });
 }

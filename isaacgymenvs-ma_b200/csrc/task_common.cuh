@@ -45,7 +45,8 @@ __device__ __forceinline__ float rand_span(double lower, double upper, float u) 
 //   `tail(total)`: run by every thread of the scanner CTA once the list is complete (total = number of resets) --
 //   for the rare cross-env side effect (Ingenuity re-sets the rotor speed of ALL envs when any env resets).
 struct NoTail { __device__ void operator()(int) const {} };
-template <class EnvFn, class TailFn = NoTail>
+//   CHUNK_ANY: env() additionally receives "some env of this CTA's current 128-env chunk is flagged" (a CTA-wide OR).
+template <bool CHUNK_ANY = false, class EnvFn, class TailFn = NoTail>
 __device__ __forceinline__ void task_reset_skeleton(int num_envs, int workers, const int64_t *reset_buf,
                                                     const IgeResetList &L, const IgeTaskRand &rand, EnvFn env,
                                                     TailFn tail = TailFn()) {
@@ -70,7 +71,12 @@ __device__ __forceinline__ void task_reset_skeleton(int num_envs, int workers, c
         const bool f = e < num_envs && reset_buf[e] != 0;
         const uint32_t m = __ballot_sync(0xffffffffu, f);
         if (emit && lane == 0 && e < num_envs) list_publish_slot(L, tag, e >> 5, m);
-        if (e < num_envs) env(e, f, step);
+        if constexpr (CHUNK_ANY) {
+            const bool any = __syncthreads_or(f ? 1 : 0) != 0;
+            if (e < num_envs) env(e, f, step, any);
+        } else {
+            if (e < num_envs) env(e, f, step);
+        }
     }
     pdl_trigger();   // main loop done: the next kernel's grid may be scheduled behind this one's tail
 }

@@ -232,8 +232,10 @@ def _peer_worker_one_gpu(rank, world, port, q):
     dist.destroy_process_group()
 
 
-def test_peer_exchange_two_processes_one_gpu():
-    world = 2
+@pytest.mark.parametrize("world", [2, 4])
+def test_peer_exchange_processes_on_one_gpu(world):
+    """world ranks on ONE GPU (gloo bootstrap): IPC mapping, {epoch : float} protocol, parity double-buffering, graph
+    replays of ige_stats_exchange; the reduced vector is the sum over ranks and bit-identical on every rank."""
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
@@ -250,9 +252,10 @@ def test_peer_exchange_two_processes_one_gpu():
             if p.is_alive():
                 p.kill()
     R = abi.IGE_STATS_ROWS
+    tri = world * (world + 1) / 2.0                     # sum over ranks of (rank + 1)
     for rank, results, epoch, err in res:
         assert err == 0 and epoch == 1 + 4 + 7          # set-up probe + eager + graph replays
         for it in range(4):
-            np.testing.assert_array_equal(results[it], np.full(abi.IGE_NUM_STATS, R * 3.0 * (it + 1), np.float32))
-        np.testing.assert_array_equal(results[4], np.full(abi.IGE_NUM_STATS, R * 30.0, np.float32))
-    np.testing.assert_array_equal(res[0][1][4], res[1][1][4])       # identical bits on every rank
+            np.testing.assert_array_equal(results[it], np.full(abi.IGE_NUM_STATS, R * tri * (it + 1), np.float32))
+        np.testing.assert_array_equal(results[4], np.full(abi.IGE_NUM_STATS, R * 10.0 * tri, np.float32))
+        np.testing.assert_array_equal(results[4], res[0][1][4])     # identical bits on every rank
