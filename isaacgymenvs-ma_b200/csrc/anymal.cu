@@ -36,10 +36,13 @@ __global__ void __launch_bounds__(kThreads) anymal_post_physics_kernel(IgeAnymal
     __shared__ int s_prefix, s_last;
     uint32_t *scratch = b.scratch;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int chunk = blockIdx.x;
+    const uint64_t step = (p.rand_mode == IGE_RAND_PHILOX && p.step) ? *reinterpret_cast<const volatile uint64_t *>(p.step) : 0ull;
+    // Chunks are taken in ascending order by a grid that fits on the device at once (the launcher caps it): the look-back
+    // below only ever waits for a chunk with a LOWER index, which a resident CTA is processing or has processed --
+    // whatever order the hardware dispatches CTAs in.
+    for (int chunk = blockIdx.x; chunk < num_chunks; chunk += gridDim.x) {
     const int e = chunk * kThreads + tid;
     const bool ok = e < p.num_envs;
-    const uint64_t step = (p.rand_mode == IGE_RAND_PHILOX && p.step) ? *reinterpret_cast<const volatile uint64_t *>(p.step) : 0ull;
 
     // ---- every load whose address depends only on the env index, up front ----
     long long reset_in = 0, progress = 0;
@@ -231,6 +234,8 @@ __global__ void __launch_bounds__(kThreads) anymal_post_physics_kernel(IgeAnymal
             if (p.rand_mode == IGE_RAND_PHILOX && p.step) *p.step = step + 1;
         }
     }
+    __syncthreads();   // s_warp / s_prefix / s_last are reused by the next chunk
+    }
 }
 
 }  // namespace
@@ -255,6 +260,18 @@ extern "C" int ige_anymal_post_physics(const IgeAnymalParams *p, const IgeAnymal
         !b->reset_ids || !b->reset_count || !b->scratch)
         return ige_fail(IGE_ENULL, "root_states / contact_forces / commands / rew / flags / reset list / scratch must be non-NULL");
     const int num_chunks = p->num_envs == 0 ? 1 : (p->num_envs + kThreads - 1) / kThreads;
-ige_launch(anymal_post_physics_kernel, num_chunks, kThreads, 0, (cudaStream_t)stream, *p, *b, num_chunks);
+    static int cap[IGE_MAX_DEVICES];   // resident CTAs per device
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= IGE_MAX_DEVICES) return ige_fail(IGE_EPARAM, "device ordinal %d not supported", dev);
+    if (cap[dev] == 0) {
+        int sms = 0, per_sm = 0;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, anymal_post_physics_kernel, kThreads, 0);
+        if (e != cudaSuccess || per_sm < 1 || sms < 1) return ige_fail(e != cudaSuccess ? (int)e : IGE_EPARAM, "ige_anymal_post_physics: occupancy query failed");
+        cap[dev] = sms * per_sm;
+    }
+    const int grid = num_chunks < cap[dev] ? num_chunks : cap[dev];
+    ige_launch(anymal_post_physics_kernel, grid, kThreads, 0, (cudaStream_t)stream, *p, *b, num_chunks);
     return ige_check_launch("ige_anymal_post_physics");
 }

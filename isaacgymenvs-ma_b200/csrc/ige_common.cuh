@@ -81,8 +81,8 @@ __device__ __forceinline__ void pdl_prologue() { pdl_wait(); }
 __device__ __forceinline__ void pdl_prologue_early() { pdl_trigger(); pdl_wait(); }
 }  // namespace ige
 template <typename... KArgs, typename... Args>
-static inline cudaError_t ige_launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
-                                     Args... args) {
+static inline cudaError_t ige_launch_opt(bool pdl, void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem,
+                                         cudaStream_t stream, Args... args) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = grid;
     cfg.blockDim = block;
@@ -92,8 +92,13 @@ static inline cudaError_t ige_launch(void (*kernel)(KArgs...), dim3 grid, dim3 b
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
-    cfg.numAttrs = ige_use_pdl() ? 1 : 0;
+    cfg.numAttrs = (pdl && ige_use_pdl()) ? 1 : 0;
     return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+template <typename... KArgs, typename... Args>
+static inline cudaError_t ige_launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                                     Args... args) {
+    return ige_launch_opt(true, kernel, grid, block, smem, stream, args...);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -259,6 +264,9 @@ __device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
 }
 __device__ __forceinline__ void fence_mbar_init() {
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar) {   // release.cta: earlier shared-memory stores are visible to waiters
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 __device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)

@@ -540,19 +540,21 @@ locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p_in,
     const int my_tiles = (num_tiles - (int)blockIdx.x + workers - 1) / workers;
 
     CLK(kstart);
-    // Philox step word: read by ONE thread and handed over through shared memory, so the load has completed
-    // (not merely been issued) when the CTA passes the barrier below -- the ticket that lets the last CTA
-    // advance the word (ige::list_cta_publish) is taken after it.
+    // Philox step word: read by ONE thread (lane 0 of the REWARD warp, which also publishes the CTA's reset-list
+    // slots: its load has COMPLETED before its first publish, and the scanner CTA advances the word only after it
+    // has seen every slot) and handed to the ELEM warps through shared memory + an mbarrier.  The tile loads below
+    // are issued without waiting for it: only the reset path consumes it, one DRAM round trip later.
     __shared__ uint64_t s_step;
+    __shared__ __align__(8) uint64_t s_step_bar;
     if (tid == 0) {
 #pragma unroll
         for (int s = 0; s < IN_STAGES; ++s) ige::mbar_init(&full[s], 1);
+        ige::mbar_init(&s_step_bar, 1);
         ige::fence_mbar_init();
     }
+    __syncthreads();   // mbarriers are visible (no global memory touched yet)
     ige::pdl_wait();   // everything above overlapped the previous kernel's tail; global memory from here on
-    if (tid == 0) s_step = ige::load_step(p_in.rand);
-    __syncthreads();   // step word and mbarriers are visible
-    const uint64_t step = s_step;
+
     const bool clamp_copy = b.obs_clamped != nullptr && p.clip_obs < INFINITY;
     const bool second_obs_copy = b.obs_clamped != nullptr && !clamp_copy;
     auto tile_e0 = [&](int it) { return ((int)blockIdx.x + it * workers) * TE; };
@@ -574,8 +576,12 @@ locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p_in,
         // iteration it (its flags were prefetched at the top of the iteration)
         const bool emit = b.list.scratch != nullptr;
         uint32_t ltag = 0u;
+        if (emit) ltag = ige::list_epoch_tag(b.list);
+        if (lane == 0) {   // (both words were READ -- their values used -- before the publish below)
+            s_step = ige::load_step(p_in.rand);
+            ige::mbar_arrive(&s_step_bar);
+        }
         if (emit) {
-            ltag = ige::list_epoch_tag(b.list);
             const uint32_t mask = __ballot_sync(0xffffffffu, n_reset != 0);
             if (lane == 0) ige::list_publish_slot(b.list, ltag, tile_e0(0) / TE, mask);
         }
@@ -640,6 +646,9 @@ locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p_in,
         if (role == HEADING && lane < tile_ne(0)) n_pot = b.potentials[tile_e0(0) + lane];
         uint32_t m_cur = __ballot_sync(0xffffffffu, load_flag(0) != 0), m_next = 0u;
         prefetch_reset<D, NS, HUM, NW_ELEM>(b, elem, role, lane, tile_e0(0), m_cur, stage[0]);
+        if (role >= ELEM0) {   // the Philox step word (reset path only): handed over by the REWARD warp, long before tile 0 lands
+            ige::mbar_wait(&s_step_bar, 0);
+        }
         long long k_load = 0, k_work = 0, k_bar = 0, k_issue = 0;
         (void)k_load; (void)k_work; (void)k_bar; (void)k_issue;
         CLK(cbeg);
@@ -670,7 +679,8 @@ locomotion_pipelined_kernel(const __grid_constant__ IgeLocomotionParams p_in,
             } else if (role == ANGLES) {
                 if (lane < ne) role_angles<HUM>(p, root, obs_row);
             } else {
-                role_elem<D, NS, HUM, NW_ELEM>(p, b, in[s], out[o].obs, hand[o], elem, ne, e0, step, m_cur, stage[o].pos);
+                role_elem<D, NS, HUM, NW_ELEM>(p, b, in[s], out[o].obs, hand[o], elem, ne, e0,
+                                               *reinterpret_cast<const volatile uint64_t *>(&s_step), m_cur, stage[o].pos);
             }
             if (role < REWARD) stream_columns<D, NS, HUM>(p, in[s], out[o].obs, role, 3, lane, ne);
 #else

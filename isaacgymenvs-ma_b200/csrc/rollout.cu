@@ -46,15 +46,17 @@ __global__ void __launch_bounds__(kThreads) ma_rollout_step_kernel(IgeRolloutSte
     __shared__ int s_prefix;
     __shared__ float s_sum[kThreads / 32][3];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int chunk = blockIdx.x;
     const int n = a.num_rows;
-    const int base = chunk * kChunk + tid * kItems;
-    const bool full = vec && base + kItems <= n;  // vec: every stream is 16-B aligned (host-checked)
-    const bool boot = a.value_bootstrap != 0;
     // meter state: fetched now by the three threads that may need it at the very end (hides a cold DRAM round trip)
     float mt_mean = 0.0f;
     int mt_size = 0;
     if (tid < 3) mt_mean = a.meter_mean[tid], mt_size = a.meter_size[tid];
+    // Chunks in ascending order over a grid that fits on the device at once (capped by the launcher): the look-back only
+    // waits for LOWER chunk indices, which resident CTAs are processing or have processed, whatever the dispatch order.
+    for (int chunk = blockIdx.x; chunk < num_chunks; chunk += gridDim.x) {
+    const int base = chunk * kChunk + tid * kItems;
+    const bool full = vec && base + kItems <= n;  // vec: every stream is 16-B aligned (host-checked)
+    const bool boot = a.value_bootstrap != 0;
 
     float rew[kItems], val[kItems], cr[kItems], cs[kItems], cl[kItems];
     long long dn[kItems];
@@ -231,6 +233,8 @@ __global__ void __launch_bounds__(kThreads) ma_rollout_step_kernel(IgeRolloutSte
         for (int i = tid; i < num_chunks; i += kThreads) scratch[2 + i] = 0u;
         if (tid == 0) scratch[1] = 0u;
     }
+    __syncthreads();   // the shared scratch is reused by the next chunk
+    }
 }
 
 // thread per row, backwards over the horizon; every (t, rows) slab is read/written coalesced
@@ -286,7 +290,19 @@ extern "C" int ige_ma_rollout_step(const IgeRolloutStepArgs *a, void *stream) {
     if (!a->done_rows || !a->done_count || !a->meter_mean || !a->meter_size || !a->reduce_scratch || !a->scratch)
         return ige_fail(IGE_ENULL, "done_rows / done_count / meter_* / reduce_scratch / scratch must be non-NULL");
     const int num_chunks = a->num_rows == 0 ? 1 : (a->num_rows + kChunk - 1) / kChunk;
-ige_launch(ma_rollout_step_kernel, num_chunks, kThreads, 0, (cudaStream_t)stream, *a, num_chunks, vec);
+    static int cap[IGE_MAX_DEVICES];   // resident CTAs per device
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= IGE_MAX_DEVICES) return ige_fail(IGE_EPARAM, "device ordinal %d not supported", dev);
+    if (cap[dev] == 0) {
+        int sms = 0, per_sm = 0;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ma_rollout_step_kernel, kThreads, 0);
+        if (e != cudaSuccess || per_sm < 1 || sms < 1) return ige_fail(e != cudaSuccess ? (int)e : IGE_EPARAM, "ige_ma_rollout_step: occupancy query failed");
+        cap[dev] = sms * per_sm;
+    }
+    const int grid = num_chunks < cap[dev] ? num_chunks : cap[dev];
+    ige_launch(ma_rollout_step_kernel, grid, kThreads, 0, (cudaStream_t)stream, *a, num_chunks, vec);
     return ige_check_launch("ige_ma_rollout_step");
 }
 

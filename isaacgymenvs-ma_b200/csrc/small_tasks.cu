@@ -326,15 +326,23 @@ __global__ void __launch_bounds__(kTaskThreads) ingenuity_pre_kernel(const __gri
         [&](int total) {   // :299-300 for the 128-env chunks without a flagged env (their 4 slots are all zero)
             if (total == 0) return;
             const uint64_t *slots = reinterpret_cast<const uint64_t *>(a.list.scratch + ige::kListMaskBase);
-            const int tiles = (a.num_envs + 31) / 32;
-            for (int c = 0; c * kTaskThreads < a.num_envs; ++c) {
-                uint32_t m = 0u;
-                for (int t = 4 * c; t < 4 * c + 4 && t < tiles; ++t) m |= (uint32_t)ige::ld_relaxed_gpu_u64(slots + t);
-                if (m != 0u) continue;
-                const int e = c * kTaskThreads + threadIdx.x;
-                if (e < a.num_envs) {
-                    a.dof_states[(size_t)e * 8 + 3] = -50.0f;
-                    a.dof_states[(size_t)e * 8 + 7] = 50.0f;
+            const int tiles = (a.num_envs + 31) / 32, chunks = (a.num_envs + kTaskThreads - 1) / kTaskThreads;
+            const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+            // warp w looks at 32 chunks at a time (lane = chunk: its four slots, independent loads), then writes the
+            // envs of the few empty ones together
+            for (int c0 = warp * 32; c0 < chunks; c0 += kTaskThreads) {
+                const int c = c0 + lane;
+                uint32_t m = 1u;
+                if (c < chunks) {
+                    m = 0u;
+                    for (int t = 4 * c; t < 4 * c + 4 && t < tiles; ++t) m |= (uint32_t)ige::ld_relaxed_gpu_u64(slots + t);
+                }
+                for (uint32_t em = __ballot_sync(0xffffffffu, m == 0u); em; em &= em - 1) {
+                    const int base = (c0 + __ffs(em) - 1) * kTaskThreads;
+                    for (int e = base + lane; e < base + kTaskThreads && e < a.num_envs; e += 32) {
+                        a.dof_states[(size_t)e * 8 + 3] = -50.0f;
+                        a.dof_states[(size_t)e * 8 + 7] = 50.0f;
+                    }
                 }
             }
         });
