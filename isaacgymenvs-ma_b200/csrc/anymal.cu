@@ -30,17 +30,23 @@ __device__ __forceinline__ void philox4(const IgeAnymalParams &p, uint64_t step,
     for (int i = 0; i < 4; ++i) out[i] = (float)(c[i] >> 8) * (1.0f / 16777216.0f);
 }
 
-__global__ void __launch_bounds__(kThreads) anymal_post_physics_kernel(IgeAnymalParams p, IgeAnymalBuffers b, int num_chunks) {
+__global__ void __launch_bounds__(kThreads) anymal_post_physics_kernel(IgeAnymalParams p, IgeAnymalBuffers b, int num_chunks, int use_ticket) {
     ige::pdl_prologue();   // PDL: let the next kernel in; wait for the previous one before touching memory
     __shared__ int s_warp[kThreads / 32];
     __shared__ int s_prefix, s_last;
     uint32_t *scratch = b.scratch;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint64_t step = (p.rand_mode == IGE_RAND_PHILOX && p.step) ? *reinterpret_cast<const volatile uint64_t *>(p.step) : 0ull;
-    // Chunks are taken in ascending order by a grid that fits on the device at once (the launcher caps it): the look-back
-    // below only ever waits for a chunk with a LOWER index, which a resident CTA is processing or has processed --
-    // whatever order the hardware dispatches CTAs in.
-    for (int chunk = blockIdx.x; chunk < num_chunks; chunk += gridDim.x) {
+    // The look-back below only ever waits for a chunk with a LOWER index, so chunk indices must be handed out in an order
+    // that guarantees those chunks are running or done, whatever order the hardware dispatches CTAs in: when the grid fits
+    // on the device at once (the launcher checks) chunk = block index is safe and free; otherwise chunks are taken from an
+    // atomic ticket (one L2 round trip per CTA, hidden by the oversubscribed grid).
+    __shared__ int s_chunk;
+    if (use_ticket) {
+        if (tid == 0) s_chunk = (int)atomicAdd(&scratch[0], 1u);
+        __syncthreads();
+    }
+    for (int chunk = use_ticket ? s_chunk : (int)blockIdx.x; chunk < num_chunks; chunk += use_ticket ? num_chunks : (int)gridDim.x) {
     const int e = chunk * kThreads + tid;
     const bool ok = e < p.num_envs;
 
@@ -230,6 +236,7 @@ __global__ void __launch_bounds__(kThreads) anymal_post_physics_kernel(IgeAnymal
     if (s_last) {
         for (int i = tid; i < num_chunks; i += kThreads) scratch[2 + i] = 0u;
         if (tid == 0) {
+            scratch[0] = 0u;
             scratch[1] = 0u;
             if (p.rand_mode == IGE_RAND_PHILOX && p.step) *p.step = step + 1;
         }
@@ -271,7 +278,7 @@ extern "C" int ige_anymal_post_physics(const IgeAnymalParams *p, const IgeAnymal
         if (e != cudaSuccess || per_sm < 1 || sms < 1) return ige_fail(e != cudaSuccess ? (int)e : IGE_EPARAM, "ige_anymal_post_physics: occupancy query failed");
         cap[dev] = sms * per_sm;
     }
-    const int grid = num_chunks < cap[dev] ? num_chunks : cap[dev];
-    ige_launch(anymal_post_physics_kernel, grid, kThreads, 0, (cudaStream_t)stream, *p, *b, num_chunks);
+    ige_launch(anymal_post_physics_kernel, num_chunks, kThreads, 0, (cudaStream_t)stream, *p, *b, num_chunks,
+               num_chunks > cap[dev] ? 1 : 0);
     return ige_check_launch("ige_anymal_post_physics");
 }

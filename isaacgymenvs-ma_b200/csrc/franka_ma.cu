@@ -540,7 +540,8 @@ __global__ void __launch_bounds__(RT_NT) franka_ma_rows_kernel(const __grid_cons
     ige::pdl_wait();   // global memory from here on
     if ((int)blockIdx.x >= workers) {   // the scanner CTA: slots -> ascending id list, count, launch tag, Philox step
         ige::pdl_trigger();
-        ige::list_scanner_cta<RT_NT>(b_in.list, num_tiles, p_in.rand.step);
+        if (num_tiles <= 2 * 32 * ige::kListUnitSlots) ige::list_scanner_cta<RT_NT>(b_in.list, num_tiles, p_in.rand.step);
+        else ige::list_scanner_cta<RT_NT, 32>(b_in.list, num_tiles, p_in.rand.step);   // large env counts: 1024-tile units
         return;
     }
     if (tid == 0) {

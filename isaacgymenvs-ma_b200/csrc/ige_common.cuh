@@ -524,9 +524,12 @@ __device__ __forceinline__ unsigned long long gtime() { unsigned long long t; as
 #else
 #define SCAN_DBG(u, k, v) do { } while (0)
 #endif
-template <int T>
+// S = slots per lane (unit = 32 S tiles).  CTAs with few warps (T = 64: the Franka MA rows kernel) take a larger S so that
+// large env counts do not queue up behind two units in flight (262 144 envs x 2 agents: 195 -> see DESIGN.md us).
+template <int T, int S = kListUnitSlots>
 static __device__ __noinline__ int list_scanner_cta(const IgeResetList L, const int num_tiles, uint64_t *step_word) {
-    constexpr int S = kListUnitSlots, W = T / 32;
+    constexpr int W = T / 32;
+    constexpr int kUnitTiles = 32 * S;
     __shared__ volatile unsigned long long s_chain;   // {units done : ids so far}
     if (threadIdx.x == 0) s_chain = 0ull;
     __syncthreads();
@@ -540,10 +543,10 @@ static __device__ __noinline__ int list_scanner_cta(const IgeResetList L, const 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t tag = (uint32_t)ld_relaxed_gpu_u64(reinterpret_cast<const uint64_t *>(L.scratch)) + 1u;
     const uint64_t done = (uint64_t)tag << 32;   // value of a slot with no reset (also stands in for slots past the end)
-    const int units = (num_tiles + kListUnitTiles - 1) / kListUnitTiles;
+    const int units = (num_tiles + kUnitTiles - 1) / kUnitTiles;
 #pragma unroll 1
     for (int u = warp; u < units; u += W) {
-        const int lo = u * kListUnitTiles + lane * S;
+        const int lo = u * kUnitTiles + lane * S;
         uint64_t v[S];
         int polls = 0;
         (void)polls;

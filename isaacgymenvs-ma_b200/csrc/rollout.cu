@@ -38,7 +38,7 @@ __device__ __forceinline__ uint32_t poll(const uint32_t *p) { return *reinterpre
 
 // Chunk c is CTA c (CTAs are dispatched in block-index order, so a CTA's predecessors are always running or done --
 // the same assumption as the reset list of the locomotion kernel); slots: scratch[2 + c], retirement counter: scratch[1].
-__global__ void __launch_bounds__(kThreads) ma_rollout_step_kernel(IgeRolloutStepArgs a, int num_chunks, int vec) {
+__global__ void __launch_bounds__(kThreads) ma_rollout_step_kernel(IgeRolloutStepArgs a, int num_chunks, int vec, int use_ticket) {
     ige::pdl_prologue();   // PDL: let the next kernel in; wait for the previous one before touching memory
     uint32_t *scratch = a.scratch;
     __shared__ int s_last;
@@ -51,9 +51,16 @@ __global__ void __launch_bounds__(kThreads) ma_rollout_step_kernel(IgeRolloutSte
     float mt_mean = 0.0f;
     int mt_size = 0;
     if (tid < 3) mt_mean = a.meter_mean[tid], mt_size = a.meter_size[tid];
-    // Chunks in ascending order over a grid that fits on the device at once (capped by the launcher): the look-back only
-    // waits for LOWER chunk indices, which resident CTAs are processing or have processed, whatever the dispatch order.
-    for (int chunk = blockIdx.x; chunk < num_chunks; chunk += gridDim.x) {
+    // The look-back below only ever waits for a chunk with a LOWER index, so chunk indices must be handed out in an order
+    // that guarantees those chunks are running or done, whatever order the hardware dispatches CTAs in: when the grid fits
+    // on the device at once (the launcher checks) chunk = block index is safe and free; otherwise chunks are taken from an
+    // atomic ticket (one L2 round trip per CTA, hidden by the oversubscribed grid).
+    __shared__ int s_chunk;
+    if (use_ticket) {
+        if (tid == 0) s_chunk = (int)atomicAdd(&scratch[0], 1u);
+        __syncthreads();
+    }
+    for (int chunk = use_ticket ? s_chunk : (int)blockIdx.x; chunk < num_chunks; chunk += use_ticket ? num_chunks : (int)gridDim.x) {
     const int base = chunk * kChunk + tid * kItems;
     const bool full = vec && base + kItems <= n;  // vec: every stream is 16-B aligned (host-checked)
     const bool boot = a.value_bootstrap != 0;
@@ -231,7 +238,7 @@ __global__ void __launch_bounds__(kThreads) ma_rollout_step_kernel(IgeRolloutSte
             a.reduce_scratch[tid] = 0.0;
         }
         for (int i = tid; i < num_chunks; i += kThreads) scratch[2 + i] = 0u;
-        if (tid == 0) scratch[1] = 0u;
+        if (tid == 0) { scratch[0] = 0u; scratch[1] = 0u; }
     }
     __syncthreads();   // the shared scratch is reused by the next chunk
     }
@@ -301,8 +308,8 @@ extern "C" int ige_ma_rollout_step(const IgeRolloutStepArgs *a, void *stream) {
         if (e != cudaSuccess || per_sm < 1 || sms < 1) return ige_fail(e != cudaSuccess ? (int)e : IGE_EPARAM, "ige_ma_rollout_step: occupancy query failed");
         cap[dev] = sms * per_sm;
     }
-    const int grid = num_chunks < cap[dev] ? num_chunks : cap[dev];
-    ige_launch(ma_rollout_step_kernel, grid, kThreads, 0, (cudaStream_t)stream, *a, num_chunks, vec);
+    ige_launch(ma_rollout_step_kernel, num_chunks, kThreads, 0, (cudaStream_t)stream, *a, num_chunks, vec,
+               num_chunks > cap[dev] ? 1 : 0);
     return ige_check_launch("ige_ma_rollout_step");
 }
 
