@@ -778,3 +778,44 @@ def test_franka_sa_mirror_step(task, name):
     assert "set_dof_state_tensor_indexed" in names and "set_actor_root_state_tensor_indexed" in names
     with pytest.raises(H.pkg._lib.IgeError):
         H.pkg.factory.from_state(name, st, "cpu").post_physics_step()
+
+
+# ------------------------------------------------------------------------------------------------------------
+# Out-of-bounds evidence without compute-sanitizer (closed on this pool): every tensor a task owns is re-homed into
+# a buffer with sentinel-filled guard regions on both sides; after two steps the guards must be untouched and the
+# outputs must still equal the oracle's.
+# ------------------------------------------------------------------------------------------------------------
+def _guarded(t, guards):
+    g = 64                                                  # elements: keeps 16-B (and 256-B) alignment for every dtype
+    big = torch.empty(t.numel() + 2 * g, dtype=t.dtype, device=t.device)
+    sentinel = {torch.float32: 12345.5, torch.int64: -77, torch.int32: -77, torch.uint8: 0xA5, torch.bool: True}[t.dtype]
+    big.fill_(sentinel)
+    guards.append((big, g, sentinel))
+    return big[g:g + t.numel()].view(t.shape)
+
+
+@pytest.mark.parametrize("task,n,kw", [("ant", 1000, {}), ("ant", 4099, {}), ("humanoid", 1000, {}), ("cartpole", 1000, {}),
+                                       ("franka_pp", 1000, {}), ("franka_reach", 999, {}), ("shadow_hand", 1000, {}),
+                                       ("shadow_hand", 70, dict(obs_type="openai", asymmetric_obs=True)),
+                                       ("allegro_hand", 1000, {})])
+def test_guard_regions_untouched(task, n, kw):
+    st = H.pkg.synthetic.make_state(task, n, seed=13, reset_prob=0.3, **kw)
+    ref = H.build(task, {k: v.copy() for k, v in st.items()}, "cpu", rand_mode="philox", seed=13)
+    gpu = H.build(task, {k: v.copy() for k, v in st.items()}, "cuda:0", rand_mode="philox", seed=13)
+    names = [k for k, v in vars(gpu).items()
+             if isinstance(v, torch.Tensor) and v.is_cuda and v.numel() > 0 and v.is_contiguous() and v.storage_offset() == 0
+             and v.untyped_storage().nbytes() == v.numel() * v.element_size() and v.dtype in
+             (torch.float32, torch.int64, torch.int32, torch.uint8, torch.bool) and not k.startswith("_list") and
+             not k.startswith("_compact") and k not in ("stats_rows", "_reduce_scratch", "rng_step")]
+    guards = []
+    gpu._rehome(names, lambda t: _guarded(t, guards))
+    assert len(guards) >= 8
+    for _ in range(2):
+        ids_ref, ids_gpu = H.oracle_step(task, ref), H.cuda_step(task, gpu)
+        torch.cuda.synchronize()
+        H.assert_equal("reset ids", ids_gpu.cpu().numpy(), ids_ref.numpy())
+        H.compare_outputs(task, gpu, H.snapshot(task, ref), bitexact=H.BITEXACT_FLOAT[task])
+    for big, g, sentinel in guards:
+        lo, hi = big[:g].cpu(), big[-g:].cpu()
+        want = torch.full_like(lo, sentinel)
+        assert torch.equal(lo, want) and torch.equal(hi, want), f"{task}: a guard region of a {tuple(big.shape)} {big.dtype} buffer was written"
