@@ -107,9 +107,10 @@ class RolloutBookkeeperMA:
                 time_outs = time_outs.view(torch.uint8)
             elif time_outs.dtype != torch.uint8:
                 time_outs = time_outs.to(torch.uint8)
-            values = values.reshape(-1)
-            if values.dtype != torch.float32 or values.device != self.device or time_outs.device != self.device:
-                raise _lib.IgeError("values / time_outs: wrong dtype or device")
+            values, time_outs = values.reshape(-1), time_outs.reshape(-1)
+            for name, t, dt in (("values", values, torch.float32), ("time_outs", time_outs, torch.uint8)):
+                if t.device != self.device or t.dtype != dt or not t.is_contiguous() or t.numel() != self.num_rows:
+                    raise _lib.IgeError(f"{name}: expected a contiguous {dt} tensor of {self.num_rows} rows on {self.device}")
             a.time_outs, a.values = time_outs.data_ptr(), values.data_ptr()
         a.mb_rewards = self.mb_rewards[n].data_ptr()
         a.dones_out = self._mb_dones[n + 1].data_ptr()

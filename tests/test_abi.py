@@ -119,3 +119,45 @@ def test_bad_arguments_rejected_8f_entry_points(lib):
     assert lib.ige_anymal_scratch_words(16384) == 4 + 128 and lib.ige_rollout_scratch_words(16384) == 4 + 16
     with pytest.raises(pkg._lib.IgeError, match="no CPU fallback"):
         pkg.rollout.RolloutBookkeeperMA(16, 2, 4, "cpu")
+
+
+def test_every_task_of_the_map_constructs_with_the_reference_shapes():
+    """isaacgym_task_map names on the path (tasks/__init__.py:67-100) -> mirrors whose contract buffers have the
+    reference's shapes (numObservations of each task's __init__, agent-axis rows = env * A + agent)."""
+    want = {"Cartpole": 4, "Ant": 60, "Humanoid": 108, "ShadowHand": 211, "AllegroHand": 88, "Anymal": 48,
+            "BallBalance": 24, "Quadcopter": 21, "Ingenuity": 13, "FrankaReach": 14, "FrankaCubeStack2": 21,
+            "FrankaCubeStack": 19, "FrankaCabinet": 23, "FrankaReachMA": 19, "FrankaCollectMA": 28,
+            "FrankaCombineMA": 48, "FrankaPPMA": 50}
+    assert set(want) == set(pkg.tasks.task_map)
+    for task, nobs in want.items():
+        env = pkg.make(0, task, 32, "cpu", graphics_device_id=0, headless=True, multi_gpu=False,
+                       virtual_screen_capture=False, force_render=False)      # the reference's own keyword set
+        rows = 32 * env.num_agents
+        assert env.obs_buf.shape == (rows, nobs), task
+        assert env.reset_buf.shape == (rows,) and env.reset_buf.dtype == torch.long, task
+        assert env.get_number_of_agents() == (2 if task.endswith("MA") else 1), task
+        obs, ids = env.reset_done()
+        assert obs["obs"].shape == (rows, nobs)
+
+
+def test_oracle_philox_is_a_pure_function_of_seed_env_step():
+    """Production reset noise (Philox4x32-10 keyed by seed, counter = env, draw, step): two oracle runs from the same
+    state agree bit for bit, the step word advances once per call, a different seed gives different rows."""
+    import franka_sa_harness as F
+    st = pkg.synthetic.make_state("franka_sa_stack", 257, seed=3, reset_prob=0.5)
+    outs = []
+    for seed in (5, 5, 6):
+        s = F.State("franka_sa_stack", 257, "cpu")
+        s.load_state(st)
+        s.post(None, seed=seed)
+        assert int(s.rng_step) == 1
+        outs.append(s.get(("root_state", "dof_state", "init_cubeA_state")))
+    for k in outs[0]:
+        assert (outs[0][k] == outs[1][k]).all()
+    assert not (outs[0]["dof_state"] == outs[2]["dof_state"]).all()
+    # FrankaCubeStack: the re-sampled cube A never ends up closer to cube B than the collision-free distance (:550-585)
+    import numpy as np
+    g = s.get(("init_cubeA_state", "init_cubeB_state"))
+    flagged = st["reset_buf"] != 0
+    d = np.linalg.norm(g["init_cubeA_state"][flagged, :2] - g["init_cubeB_state"][flagged, :2], axis=1)
+    assert flagged.sum() > 50 and (d >= np.float32(0.12) * np.float32(np.sqrt(2)) - 1e-6).all()
