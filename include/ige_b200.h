@@ -301,12 +301,6 @@ int ige_shadow_hand_post_physics(const IgeShadowHandParams *p, const IgeShadowHa
 #define IGE_FRANKA_PP 3
 #define IGE_MA_MAX_AGENTS 4
 #define IGE_MA_NUM_COMPONENTS 10
-/* reduce_scratch of the Franka MA entry point: 32 words (component sums of the generic kernel, retirement counter) followed
- * by IGE_MA_REDUCE_ROWS striped rows of IGE_MA_REDUCE_STRIDE floats: the rows kernel adds CTA c's partial sums into row
- * c % ROWS (one 128-B line per row: thousands of atomics on ONE line serialise in L2 -- measured ~2 us at 8192 x 2). */
-#define IGE_MA_REDUCE_ROWS 32
-#define IGE_MA_REDUCE_STRIDE 32
-#define IGE_MA_REDUCE_WORDS (32 + IGE_MA_REDUCE_ROWS * IGE_MA_REDUCE_STRIDE)
 
 /* Uniforms of reset_idx, in the reference's torch.rand order (k = #envs whose agents are ALL flagged):
  *   u[0] (k, T)     cube z         u[1] (k, T, 2)  cube xy      (_reset_init_cube_state)
@@ -365,7 +359,7 @@ typedef struct IgeFrankaMABuffers {
     float *obs_clamped;            /* optional */
     uint8_t *timeout_buf;          /* optional */
     float *stats;                  /* optional; TASK0.. = component SUMS (what the multi-GPU all-reduce needs) */
-    float *reduce_scratch;         /* [IGE_MA_REDUCE_WORDS] zeroed once: component sums + retirement counter; restored by every launch */
+    float *reduce_scratch;         /* [IGE_MA_NUM_COMPONENTS + 2] zeroed once: component sums + retirement counter */
     IgeResetList list;             /* ENV ids that were reset (all agents flagged) */
 } IgeFrankaMABuffers;
 

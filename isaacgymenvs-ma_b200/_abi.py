@@ -107,7 +107,6 @@ class IgeShadowHandBuffers(C.Structure):
 IGE_FRANKA_VARIANT = {"reach": 0, "collect": 1, "combine": 2, "pp": 3}
 IGE_MA_MAX_AGENTS = 4
 IGE_MA_NUM_COMPONENTS = 10
-IGE_MA_REDUCE_WORDS = 32 + 32 * 32
 
 
 class IgeMAResetRand(C.Structure):

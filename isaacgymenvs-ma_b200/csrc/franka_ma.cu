@@ -959,7 +959,7 @@ __global__ void __launch_bounds__(RT_NT) franka_ma_rows_kernel(const __grid_cons
         float mine = 0.f;
 #pragma unroll
         for (int i = 0; i < NC; ++i) if (lane == i) mine = comp[i];
-        if (MEANS) atomicAdd(b.reduce_scratch + 32 + (blockIdx.x % IGE_MA_REDUCE_ROWS) * IGE_MA_REDUCE_STRIDE + lane, mine);
+        if (MEANS) atomicAdd(b.reduce_scratch + lane, mine);
         if (b.stats && MEANS) atomicAdd(b.stats + (blockIdx.x % IGE_STATS_ROWS) * IGE_STATS_STRIDE + IGE_STAT_TASK0 + lane, mine);
     }
     if (b.stats) {
@@ -978,14 +978,9 @@ __global__ void __launch_bounds__(RT_NT) franka_ma_rows_kernel(const __grid_cons
         if (s_last) {
             __threadfence();
             if (tid < NC) {
-                float *rows = b.reduce_scratch + 32 + tid;
-                float v[IGE_MA_REDUCE_ROWS];
-#pragma unroll
-                for (int r = 0; r < IGE_MA_REDUCE_ROWS; ++r) v[r] = __ldcg(rows + r * IGE_MA_REDUCE_STRIDE);   // all loads in flight
-                float sum = 0.0f;
-#pragma unroll
-                for (int r = 0; r < IGE_MA_REDUCE_ROWS; ++r) { sum += v[r]; rows[r * IGE_MA_REDUCE_STRIDE] = 0.0f; }
+                const float sum = __ldcg(b.reduce_scratch + tid);
                 if (b.reward_components) b.reward_components[tid] = sum / (float)((long long)N * A);
+                b.reduce_scratch[tid] = 0.0f;
             }
             if (tid == 0) b.reduce_scratch[NC] = 0.0f;
         }

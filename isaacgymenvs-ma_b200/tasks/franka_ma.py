@@ -58,7 +58,7 @@ class FrankaMA(VecTaskB200):
         self.num_dofs = self._dof_state.shape[1]
         self.actions = torch.zeros((n * a, self.num_actions), device=dev)
         self.reward_components = torch.zeros(_abi.IGE_MA_NUM_COMPONENTS, device=dev)
-        self._reduce_scratch = torch.zeros(_abi.IGE_MA_REDUCE_WORDS, device=dev)
+        self._reduce_scratch = torch.zeros(_abi.IGE_MA_NUM_COMPONENTS + 2, device=dev)
         self._global_indices = torch.arange(n * cfg["num_actors"], dtype=torch.int32, device=dev).view(n, -1)
         self._u = [None] * 5
         self._p_static = None
