@@ -789,6 +789,24 @@ int ige_mailbox_close(void *peer_mailbox);      /* cudaIpcCloseMemHandle */
 int ige_mailbox_destroy(void *own_mailbox);     /* cudaFree */
 
 /* ------------------------------------------------------------------------------------------
+ * Helper probe (test hook for SURVEY.md 8a row a12): evaluates the device versions of the utils/torch_jit_utils.py helpers
+ * the kernels are built from on arbitrary inputs, one row per thread.  out row (IGE_PROBE_COLS floats):
+ *   0..3  quat_mul(q, q2) :41-62        4..6  quat_rotate(q, v) :80-90      7..9  quat_rotate_inverse(q, v) :93-103
+ *   10..12 normalize(v) :65-67          13,14 get_euler_xyz roll, yaw :175-195   15 normalize_angle(v.x) :126-128
+ *   16..19 quat_conjugate(q) :106-110   20 norm(v) (torch.norm dim=-1)      21 dot(q.xyz, v) (bmm 1x3 3x1 :88-89)
+ *   22 unscale(v.x, v.y, v.z) :238-240  23 remainder(v.x, 2 pi) (the `%` of :195)
+ * ------------------------------------------------------------------------------------------ */
+#define IGE_PROBE_COLS 24
+typedef struct IgeHelperProbeArgs {
+    int32_t n;
+    int32_t _pad;
+    const float *q, *q2;   /* (n, 4) xyzw */
+    const float *v;        /* (n, 3) */
+    float *out;            /* (n, IGE_PROBE_COLS) */
+} IgeHelperProbeArgs;
+int ige_debug_helper_probe(const IgeHelperProbeArgs *a, void *stream);
+
+/* ------------------------------------------------------------------------------------------
  * Library
  * ------------------------------------------------------------------------------------------ */
 int ige_version(void);

@@ -260,6 +260,13 @@ class IgeStatsExchangeArgs(C.Structure):
                 ("error", _p), ("rank", _i), ("world", _i), ("zero_stats", _i), ("timeout_ms", C.c_uint32)]
 
 
+IGE_PROBE_COLS = 24
+
+
+class IgeHelperProbeArgs(C.Structure):
+    _fields_ = [("n", _i), ("_pad", _i), ("q", _p), ("q2", _p), ("v", _p), ("out", _p)]
+
+
 class IgeStatsSnapshotArgs(C.Structure):
     _fields_ = [("stats", _p), ("out", _p), ("zero_stats", _i), ("accumulate", _i)]
 

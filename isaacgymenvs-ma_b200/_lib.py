@@ -35,6 +35,7 @@ _SIGS = {
     "ige_franka_cabinet_pre_physics": (_abi.IgeFrankaCabinetArgs,),
     "ige_franka_cabinet_post_physics": (_abi.IgeFrankaCabinetArgs,),
     "ige_stats_exchange": (_abi.IgeStatsExchangeArgs,),
+    "ige_debug_helper_probe": (_abi.IgeHelperProbeArgs,),
     "ige_stats_snapshot": (_abi.IgeStatsSnapshotArgs,),
 }
 

@@ -82,6 +82,31 @@ __global__ void __launch_bounds__(kThreads) hand_targets_kernel(const __grid_con
     }
 }
 
+// the device helpers on their own (include/ige_b200.h, IgeHelperProbeArgs)
+__global__ void __launch_bounds__(kThreads) helper_probe_kernel(const __grid_constant__ IgeHelperProbeArgs a) {
+    ige::pdl_prologue();
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < a.n; i += gridDim.x * blockDim.x) {
+        float q[4], q2[4], v[3], o[IGE_PROBE_COLS];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) { q[k] = a.q[(size_t)i * 4 + k]; q2[k] = a.q2[(size_t)i * 4 + k]; }
+#pragma unroll
+        for (int k = 0; k < 3; ++k) v[k] = a.v[(size_t)i * 3 + k];
+        ige::quat_mul(q, q2, o);
+        ige::quat_rotate<false>(q, v, o + 4);
+        ige::quat_rotate<true>(q, v, o + 7);
+        ige::normalize3(v, o + 10);
+        ige::euler_roll_yaw(q, o[13], o[14]);
+        o[15] = ige::normalize_angle(v[0]);
+        ige::quat_conjugate(q, o + 16);
+        o[20] = ige::norm3(v[0], v[1], v[2]);
+        o[21] = ige::dot3(q, v);
+        o[22] = (2.0f * v[0] - v[2] - v[1]) / (v[2] - v[1]);   // unscale(x, lower, upper), torch_jit_utils.py:238-240
+        o[23] = ige::py_remainder(v[0], ige::kTwoPi);
+#pragma unroll
+        for (int k = 0; k < IGE_PROBE_COLS; ++k) a.out[(size_t)i * IGE_PROBE_COLS + k] = o[k];
+    }
+}
+
 int grid_for(long long items) {
     static int sms = 0;   // grid-stride cap: SM count x 8 CTAs
     if (sms == 0) {
@@ -124,4 +149,13 @@ extern "C" int ige_shadow_hand_pre_physics_targets(const IgeHandTargetArgs *a, v
     if (a->num_envs == 0) return IGE_OK;
 ige_launch(hand_targets_kernel, grid_for((long long)a->num_envs * a->num_actions), kThreads, 0, (cudaStream_t)stream, *a);
     return ige_check_launch("ige_shadow_hand_pre_physics_targets");
+}
+
+extern "C" int ige_debug_helper_probe(const IgeHelperProbeArgs *a, void *stream) {
+    if (!a) return ige_fail(IGE_ENULL, "args is NULL");
+    if (a->n < 0) return ige_fail(IGE_ESIZE, "n < 0");
+    if (!a->q || !a->q2 || !a->v || !a->out) return ige_fail(IGE_ENULL, "q / q2 / v / out must be non-NULL");
+    if (a->n == 0) return IGE_OK;
+    ige_launch(helper_probe_kernel, grid_for(a->n), kThreads, 0, (cudaStream_t)stream, *a);
+    return ige_check_launch("ige_debug_helper_probe");
 }

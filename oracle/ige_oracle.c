@@ -1886,3 +1886,25 @@ int ige_oracle_franka_cabinet_post_physics(const IgeFrankaCabinetArgs *a) { /* :
     task_advance(&a->list, &a->rand);
     return 0;
 }
+
+/* ------------------------------------------------------------------------------------------
+ * Helper probe: the helpers above on arbitrary inputs, same columns as the device probe.
+ * ------------------------------------------------------------------------------------------ */
+int ige_oracle_debug_helper_probe(const IgeHelperProbeArgs *a) {
+    for (int i = 0; i < a->n; ++i) {
+        const float *q = a->q + (size_t)i * 4, *q2 = a->q2 + (size_t)i * 4, *v = a->v + (size_t)i * 3;
+        float *o = a->out + (size_t)i * IGE_PROBE_COLS;
+        quat_mul(q, q2, o);
+        quat_rotate_impl(q, v, 0, o + 4);
+        quat_rotate_impl(q, v, 1, o + 7);
+        normalize3(v, o + 10);
+        euler_roll_yaw(q, &o[13], &o[14]);
+        o[15] = normalize_angle(v[0]);
+        quat_conjugate(q, o + 16);
+        o[20] = norm3(v[0], v[1], v[2]);
+        o[21] = dot3(q, v);
+        o[22] = (2.0f * v[0] - v[2] - v[1]) / (v[2] - v[1]);
+        o[23] = py_remainder(v[0], 6.28318530717958647692f);
+    }
+    return 0;
+}
