@@ -71,3 +71,34 @@ def test_oracle_matches_reference_8f_row2_at_16384(task):
         blob = G.generate(task, 16384, 23, 0.02, 2)
         for s, phase, got, ref in S.run_fixture(blob, task, "cpu"):
             S.compare(got, ref, f"{task} 16384 step{s} {phase}", exact_float=SMALL_EXACT[task])
+
+
+def test_oracle_matches_reference_anymal_osc_rollout_at_size():
+    """The remaining 8f rows at C4-sized inputs: Anymal 16384 envs (VecTask.step), the OSC pre_physics_step of FrankaPPMA at
+    8192 x 2 agent rows, A2CAgentMA.play_steps on 8192 x 2 rows -- reference run in memory, oracle replays."""
+    import os
+    import sys
+    sys.path.insert(0, os.path.join(H.ROOT, "tests", "golden"))
+    import anymal_harness as A
+    import gen_golden_anymal as GA
+    blob = GA.generate(16384, 31, 0.02, 2)
+    for s, ids, got, ref in A.run_fixture(blob, "cpu"):
+        H.assert_equal("anymal reset_env_ids", ids, ref["reset_env_ids"])
+        A.compare(got, ref, f"anymal 16384 step{s}")
+    import gen_golden_osc as GO
+    import osc_harness as O
+    blob = GO.generate("pp", 8192, 2, 7)
+    got, truth = O.oracle_osc(blob), O.float64_truth(blob)
+    H.assert_equal("osc actions", got["out_actions"], blob["out_actions"])
+    H.assert_equal("osc pos_control", got["out_pos_control"], blob["out_pos_control"])
+    assert O.torque_error(got, truth) <= 2.0 * O.torque_error(blob, truth) + 1e-5    # as close to float64 as the reference's fp32
+    over, rows = O.rows_over(got, blob)
+    print(f"OSC pp 8192x2: {over} of {rows} agent rows beyond 1e-5 of the reference's fp32 torques")
+    import gen_golden_rollout as GR
+    import rollout_harness as R
+    cls = GR.load_reference_agent()
+    case = dict(GR.CASES[0])
+    case.pop("name")
+    case.update(num_envs=8192, A=2)
+    blob = GR.run_case(cls, **case)
+    R.compare(R.oracle_rollout(blob), blob, "rollout 8192x2")
