@@ -819,3 +819,33 @@ def test_guard_regions_untouched(task, n, kw):
         lo, hi = big[:g].cpu(), big[-g:].cpu()
         want = torch.full_like(lo, sentinel)
         assert torch.equal(lo, want) and torch.equal(hi, want), f"{task}: a guard region of a {tuple(big.shape)} {big.dtype} buffer was written"
+
+
+# ------------------------------------------------------------------------------------------------------------
+# Size-independent property at BASELINE.json's full sizes: environments are independent units, so
+# permuting the envs of the input state permutes every per-env output -- bit for bit, whatever tile / CTA / lane an
+# env lands in.  (No entry flags: a step without resets consumes no noise.)
+# ------------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("task,n", [("ant", 16384), ("humanoid", 32768), ("cartpole", 16384), ("ant", 4099)])
+def test_env_permutation_equivariance(task, n):
+    syn = H.pkg.synthetic
+    st = syn.make_state(task, n, seed=41, reset_prob=0.0)
+    st["reset_buf"][:] = 0
+    perm = np.random.Generator(np.random.PCG64(9)).permutation(n)
+    per_env = {k: v for k, v in st.items() if isinstance(v, np.ndarray) and v.ndim >= 1 and v.shape[0] >= n and v.shape[0] % n == 0}
+    st_p = dict(st)
+    for k, v in per_env.items():                         # (N, ...) rows, or (N * D, 2) DOF rows: D consecutive rows per env
+        st_p[k] = np.ascontiguousarray(v.reshape(n, v.shape[0] // n, -1)[perm].reshape(v.shape))
+    a = H.build(task, st, "cuda:0", rand_mode="philox", seed=1)
+    b = H.build(task, st_p, "cuda:0", rand_mode="philox", seed=1)
+    for o in (a, b):
+        ids = H.cuda_step(task, o)
+        assert ids.numel() == 0
+    torch.cuda.synchronize()
+    for name in H.INT_OUT[task] + [x for x in H.FLOAT_OUT[task] if x != "dof_state"] + ["obs_clamped", "time_outs"]:
+        ga, gb = H.get(a, name), H.get(b, name)
+        if ga.shape[0] != n:
+            continue
+        H.assert_equal(f"{task} {name} under an env permutation", gb.view(np.uint8) if gb.dtype == bool else gb,
+                       (ga[perm]).view(np.uint8) if ga.dtype == bool else ga[perm])
+    assert int((H.get(a, "reset_buf") != 0).sum()) > 0      # some envs terminated: the flags took part in the comparison
