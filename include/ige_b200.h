@@ -11,7 +11,8 @@
  *   - extern "C", plain pointers and sizes, no C++/torch types, never throws, never exits.
  *   - All pointers are DEVICE pointers borrowed for the duration of the call; the launch is
  *     asynchronous on `stream` (a cudaStream_t passed as void*); the callee never allocates,
- *     frees or synchronises.  The call is CUDA-graph capturable.
+ *     frees or synchronises.  The call is CUDA-graph capturable (ige_compact_resets_static: see its own
+ *     comment instead).
  *   - Layouts are the gymtorch layouts, unchanged: root / rigid-body rows = 13 floats
  *     (pos3, quat xyzw 4, linvel3, angvel3), DOF rows = (pos, vel), force sensors = 6 floats,
  *     contact forces = 3 floats; reset/progress/randomize flags are int64 (vec_task.py:317-324).
@@ -107,6 +108,23 @@ typedef struct IgeCompactArgs {
 
 int ige_compact_scratch_words(int32_t num_envs);
 int ige_compact_resets(const IgeCompactArgs *args, void *stream);
+
+/* No counterpart in the reference (which lets torch allocate whatever nonzero() needs): the same compaction for a
+ * caller that cannot provide `scratch`.  Meant for plug-ins living inside someone else's memory budget -- a simulator
+ * that pre-sized its GPU heap, a trainer whose caching allocator owns the card up to a hard cap, a foreign-language
+ * binding without a CUDA runtime -- which hold only the tensors they were given and cannot cudaMalloc the look-back
+ * words.  The words live in an 8200-byte __device__ array inside the library (held by every GPU that loads it, until
+ * process exit), so:
+ *   - args->scratch is ignored; num_rows / group must be <= IGE_COMPACT_STATIC_MAX_ENVS, larger -> IGE_ESIZE;
+ *   - the call allocates and frees nothing; it enqueues a small cudaMemsetAsync of the words it will use (the
+ *     array keeps the previous call's contents) and one kernel, both on `stream`;
+ *   - all calls on a device share the array: calls that may overlap on the GPU (two streams, two threads) race and
+ *     give wrong ids -- keep them on one stream or otherwise ordered;
+ *   - the first call on each device also resolves the array's device address (cudaGetSymbolAddress, with that
+ *     device current).  Treat it as set-up: make it once per device before any stream capture begins.
+ * Outputs are identical to ige_compact_resets. */
+#define IGE_COMPACT_STATIC_MAX_ENVS 4194304
+int ige_compact_resets_static(const IgeCompactArgs *args, void *stream);
 
 /* ------------------------------------------------------------------------------------------
  * Cartpole -- replaces Cartpole.post_physics_step (tasks/cartpole.py:165-173) incl. reset_idx

@@ -10,6 +10,8 @@
 // One launch, chained-scan with decoupled look-back: chunk order is taken from an atomic ticket so
 // a waiting CTA's predecessors are always already running; the last CTA to finish zeroes the
 // scratch again, so the launch is re-playable inside a CUDA graph with no memset node.
+#include <mutex>
+
 #include "ige_common.cuh"
 
 namespace {
@@ -129,3 +131,78 @@ ige_launch(compact_resets_kernel, num_chunks, kThreads, 0, (cudaStream_t)stream,
 }
 
 extern "C" int ige_reset_list_scratch_words(int32_t num_envs) { return ige::reset_list_scratch_words(num_envs); }
+
+// ---------------------------------------------------------------------------------------------
+// ige_compact_resets_static -- the same compaction for callers that have no way to hand us scratch words.
+//
+// Who that is: a plug-in running inside a host process whose device memory belongs to somebody else.  A simulator
+// that sized its GPU heap at start-up, a trainer that gave the whole card to a caching allocator with a hard cap, or a
+// binding written in a language with no CUDA runtime of its own only owns the tensors it was handed: the flags going
+// in and the id list coming out.  It cannot call cudaMalloc for a few look-back words (no budget left, no runtime
+// handle, or a control loop that cannot afford cudaMalloc's device-wide synchronisation), and ige_compact_resets
+// insists on a caller-owned scratch buffer.  This variant keeps the look-back words in the library image instead:
+// a file-scope __device__ array, present once on every GPU that loads the library, from load until the process exits
+// (kStaticWords * 4 = 8200 bytes).  The price is a size limit (IGE_COMPACT_STATIC_MAX_ENVS envs) and that every call
+// on a device goes through the one array: two calls whose kernels can be on the GPU at the same time (different
+// streams, different host threads) corrupt each other's prefix sums.  Serialise them, or use ige_compact_resets.
+//
+// The array's C++ name is only a handle on the host side; the kernel needs the device address behind it, which
+// cudaGetSymbolAddress returns for the CURRENT device.  It is looked up the first time the entry point runs on a
+// device and remembered per device ordinal.  That first call is therefore a set-up call (it may make the runtime
+// load the module): make it once per device, outside any stream capture, before the calls that matter.
+// Nothing here calls cudaMalloc / cudaFree or any library routine that allocates.
+// ---------------------------------------------------------------------------------------------
+namespace {
+constexpr int kStaticMaxEnvs = IGE_COMPACT_STATIC_MAX_ENVS;
+constexpr int kStaticMaxChunks = (kStaticMaxEnvs + kChunk - 1) / kChunk;
+constexpr int kStaticWords = 2 + kStaticMaxChunks;   // ticket, retirement counter, one look-back slot per chunk
+constexpr int kStaticMaxDevices = 64;
+}  // namespace
+
+static __device__ __align__(256) uint32_t g_compact_static_scratch[kStaticWords];
+
+static std::mutex g_static_scratch_mu;
+static uint32_t *g_static_scratch_addr[kStaticMaxDevices] = {};   // device address of the array, per device ordinal
+
+extern "C" int ige_compact_resets_static(const IgeCompactArgs *a, void *stream) {
+    if (!a) return ige_fail(IGE_ENULL, "args is NULL");
+    if (a->num_rows < 0 || a->group < 1 || a->num_rows % a->group != 0)
+        return ige_fail(IGE_ESIZE, "num_rows=%d group=%d invalid", a->num_rows, a->group);
+    if (!a->reset_buf || !a->reset_ids || !a->count)
+        return ige_fail(IGE_ENULL, "reset_buf / reset_ids / count must be non-NULL");
+    const int n = a->num_rows / a->group;
+    if (n > kStaticMaxEnvs)
+        return ige_fail(IGE_ESIZE,
+                        "ige_compact_resets_static: %d envs exceed the built-in scratch (IGE_COMPACT_STATIC_MAX_ENVS = %d); "
+                        "use ige_compact_resets with caller-owned scratch",
+                        n, kStaticMaxEnvs);
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) { cudaGetLastError(); return ige_fail((int)e, "cudaGetDevice: %s", cudaGetErrorString(e)); }
+    if (dev < 0 || dev >= kStaticMaxDevices)
+        return ige_fail(IGE_EPARAM, "ige_compact_resets_static: device ordinal %d outside [0, %d)", dev, kStaticMaxDevices);
+    uint32_t *scratch = nullptr;
+    {
+        std::lock_guard<std::mutex> lock(g_static_scratch_mu);
+        scratch = g_static_scratch_addr[dev];
+        if (!scratch) {   // first call on this device: resolve the symbol while this device is current
+            e = cudaGetSymbolAddress((void **)&scratch, g_compact_static_scratch);
+            if (e != cudaSuccess || !scratch) {
+                cudaGetLastError();
+                return ige_fail(e != cudaSuccess ? (int)e : IGE_EPARAM, "cudaGetSymbolAddress(compact scratch) on device %d: %s",
+                                dev, cudaGetErrorString(e));
+            }
+            g_static_scratch_addr[dev] = scratch;
+        }
+    }
+    const int num_chunks = n == 0 ? 1 : (n + kChunk - 1) / kChunk;
+    // The array still holds whatever the previous call left.  The kernel hands it back zeroed, but a launch that was
+    // cut short would not have; the words this launch reads must be zero, so clear exactly those, in stream order.
+    e = cudaMemsetAsync(scratch, 0, sizeof(uint32_t) * (size_t)(2 + num_chunks), (cudaStream_t)stream);
+    if (e != cudaSuccess) { cudaGetLastError(); return ige_fail((int)e, "cudaMemsetAsync(compact scratch): %s", cudaGetErrorString(e)); }
+    IgeCompactArgs k = *a;
+    k.scratch = scratch;   // whatever the caller put there is ignored
+    // plain stream-ordered launch (no programmatic dependent launch): the kernel must not start before the clear above
+    ige_launch_opt(false, compact_resets_kernel, num_chunks, kThreads, 0, (cudaStream_t)stream, k, num_chunks);
+    return ige_check_launch("ige_compact_resets_static");
+}
