@@ -33,6 +33,10 @@ class FusedLocomotionMixin:
         if dev.type != "cuda":
             raise _lib.IgeError("the fused post_physics_step needs sim_device=cuda tensors; there is no CPU path")
         self._ige_entry, sensors = self._IGE_ENTRY[int(self.num_dof)]
+        # The gym API takes gymtorch-unwrapped tensors, never torch tensors (ant.py:265-271).  isaacgym is already
+        # imported by the reference module that defines the class this mixin is bound to.
+        import importlib
+        self._ige_unwrap = importlib.import_module("isaacgym.gymtorch").unwrap_tensor
         lib = _lib.lib()
         i32 = dict(dtype=torch.int32, device=dev)
         self.reset_env_ids = torch.zeros(n, **i32)
@@ -108,9 +112,10 @@ class FusedLocomotionMixin:
         self._ige_keep = keep                                     # alive until the stream has consumed them
         k = int(self.reset_count.item())                          # ant.py:292 (the gym API needs a host integer)
         if k > 0:                                                 # ant.py:263-271: ids are int32, ascending
-            ids = self.reset_env_ids[:k]
-            self.gym.set_actor_root_state_tensor_indexed(self.sim, self.initial_root_states, ids, k)
-            self.gym.set_dof_state_tensor_indexed(self.sim, self.dof_state, ids, k)
+            unwrap = self._ige_unwrap
+            ids = unwrap(self.reset_env_ids[:k])
+            self.gym.set_actor_root_state_tensor_indexed(self.sim, unwrap(self.initial_root_states), ids, k)
+            self.gym.set_dof_state_tensor_indexed(self.sim, unwrap(self.dof_state), ids, k)
         if hasattr(self, "compute_true_objective") and int(self.num_dof) == 8:
             self.extras["true_objective"] = self.root_states[:, 7]   # ant.py:245-250
 

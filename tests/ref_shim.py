@@ -61,6 +61,18 @@ class _Anything:
         return _Anything(self._name + "." + name)
 
 
+class Unwrapped:
+    """What the stub ``gymtorch.unwrap_tensor`` returns: a marker around the torch tensor.  The real
+    ``gymapi.Gym`` methods take these descriptors and reject torch tensors; FakeGym does the same, so a
+    binding that forgets ``unwrap_tensor`` fails here too instead of only under Isaac Gym."""
+
+    def __init__(self, tensor):
+        import torch
+        if not isinstance(tensor, torch.Tensor):
+            raise TypeError(f"gymtorch.unwrap_tensor expects a torch tensor, got {type(tensor).__name__}")
+        self.tensor = tensor
+
+
 def install():
     """Idempotently install the stubs; returns the dict of stub modules."""
     if "isaacgym" in sys.modules and getattr(sys.modules["isaacgym"], "_ige_stub", False):
@@ -77,7 +89,7 @@ def install():
     gymutil = _Permissive("isaacgym.gymutil")
     gymtorch.__all__ = []            # ant.py:35 does `from isaacgym.gymtorch import *`
     gymtorch.wrap_tensor = lambda t: t
-    gymtorch.unwrap_tensor = lambda t: t
+    gymtorch.unwrap_tensor = Unwrapped   # FakeGym(strict) refuses bare torch tensors, as the real gym API does
     ig.gymapi, ig.gymtorch, ig.gymutil = gymapi, gymtorch, gymutil
     sys.modules.update({"isaacgym": ig, "isaacgym.gymapi": gymapi,
                         "isaacgym.gymtorch": gymtorch, "isaacgym.gymutil": gymutil})
@@ -119,6 +131,10 @@ class FakeGym:
     def __init__(self, record=True):
         self.calls = []
         self.record = record          # False: set_* calls are dropped (timed baseline runs)
+        # True: a bare torch tensor in a set_* call raises, as under the real gym API.  Opt-in, because some
+        # reference tasks pass the descriptor they got from gym.acquire_* (ball_balance.py:397), which the
+        # harness also models as a torch tensor.
+        self.strict = False
 
     def __getattr__(self, name):
         if name.startswith("__"):
@@ -132,6 +148,10 @@ class FakeGym:
             import torch
             saved = []
             for a in args:
+                if self.strict and isinstance(a, torch.Tensor):
+                    raise TypeError(f"gym.{name}: got a torch tensor; pass gymtorch.unwrap_tensor(t) (ant.py:265-271)")
+                if isinstance(a, Unwrapped):
+                    a = a.tensor
                 if isinstance(a, torch.Tensor) and a.dtype == torch.int32:
                     saved.append(a.clone())
                 elif isinstance(a, torch.Tensor):

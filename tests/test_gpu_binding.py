@@ -63,6 +63,7 @@ def test_fused_post_physics_under_reference_step(task, n):
     st = syn.make_state(task, n, seed=11, reset_prob=0.05)
     ref = _build(task, ref_cls, st, cfg)                                              # un-patched, CPU
     fused = _to_device(_build(task, fused_cls, st, cfg), n, d)                        # patched, CUDA
+    ref.gym.strict = fused.gym.strict = True      # bare torch tensors in gym.set_* calls raise (ant.py:265-271 wraps them)
     fused.ige_rand_mode = "injected"
     # the reference draws its reset noise from torch's CPU generator: draw the same stream, then move it over
     fused.ige_draw_reset_uniforms = lambda k: tuple(torch.rand((k, d)).to(DEV) for _ in range(2))
