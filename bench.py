@@ -71,8 +71,9 @@ class ClockSampler:
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
-    def __init__(self, gpu_index):
+    def __init__(self, gpu_index, enabled=True):
         self.idx, self.samples, self._stop, self._t = gpu_index, [], threading.Event(), None
+        self.enabled = enabled
 
     def _once(self):
         try:
@@ -90,11 +91,14 @@ class ClockSampler:
 
     def __enter__(self):
         self.t0 = time.time()
-        self._t = threading.Thread(target=self._run, daemon=True)
-        self._t.start()
+        if self.enabled:
+            self._t = threading.Thread(target=self._run, daemon=True)
+            self._t.start()
         return self
 
     def __exit__(self, *a):
+        if not self.enabled:
+            return
         self._stop.set()
         self._t.join(timeout=10)
         if not self.samples:
@@ -153,6 +157,41 @@ def capture(envs, fn, pre=None, post=None, error_mode="global"):
     return g
 
 
+def check_stats_reduce(pkg, reducer, chunks, dist, world, device):
+    """Does the statistics all-reduce the timed graphs carry (peer-mailbox kernel or NCCL) really SUM over ranks?
+    One horizon is accumulated (graph 0), its per-rank column sums are read back, the next graph folds and reduces
+    it, and the result is compared with the float64 sum of all ranks' vectors gathered over plain NCCL -- a path
+    that shares nothing with ige_stats_exchange.  Bar: 1e-5 relative (fp32 sums of <= 32 rows x N ranks)."""
+    abi = pkg._abi
+    torch.cuda.synchronize()
+    for r in reducer.rows:
+        r.zero_()
+    chunks[0].replay()                       # accumulates horizon A into rows[0] (and folds the zeroed rows[1])
+    torch.cuda.synchronize()
+    local = reducer.rows[0].view(abi.IGE_STATS_ROWS, abi.IGE_STATS_STRIDE)[:, :abi.IGE_NUM_STATS].double().sum(0)
+    chunks[1].replay()                       # folds + all-reduces horizon A
+    torch.cuda.synchronize()
+    got = reducer.reduced.double().clone()
+    err = None
+    try:
+        reducer.check_error()
+    except RuntimeError as e:
+        err = str(e)
+    want = local.clone()
+    if dist is not None:
+        parts = [torch.zeros_like(local) for _ in range(world)]
+        dist.all_gather(parts, local)
+        want = torch.stack(parts).sum(0)
+    rel = float(((got - want).abs() / want.abs().clamp_min(1.0)).max())
+    ok = err is None and rel <= 1e-5 and float(want[0]) > 0
+    if dist is not None:                     # the line says ok only if EVERY rank's vector checked out
+        flag = torch.tensor([1.0 if ok else 0.0], device=device)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        ok = bool(flag.item() > 0.5)
+    return {"ok": ok, "ranks": world, "mode": reducer.mode, "max_rel_err": rel, "error": err,
+            "steps_summed": float(want[0]), "reward_sum": float(want[1])}   # IGE_STAT_STEPS, IGE_STAT_REWARD
+
+
 def bench_config(task, n, world):
     """`config` of the JSON line -- the SAME dict for both arms (ours / --impl reference)."""
     return {"workload": f"{task} post_physics_step num_envs={n} per GPU" +
@@ -204,8 +243,29 @@ def run_ours(args):
     rem_envs = [envs[((full % n_chunks) * HORIZON + i) % replicas] for i in range(rem)]
     rem_graph = [capture(rem_envs, lambda e: e.hot_step(), error_mode=mode)] if rem else []
 
+    # Short runs (the driver's 20-step window is ~120 us): ALL timed steps in ONE graph launch, so a rank's host
+    # jitter is paid once, not once per horizon graph -- the MAX over ranks of several back-to-back launches was what
+    # kept the 8-GPU curve under 0.95 in round 2.  Long runs keep one graph per horizon (launch cost amortised).
+    whole = None
+    if args.steps <= 8 * HORIZON:
+        whole = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(whole, capture_error_mode=mode):
+            for i in range(full):
+                c = i % n_chunks
+                if use_branch:
+                    reducer.fork(reducer.rows[(c & 1) ^ 1])
+                for e in envs[c * HORIZON:(c + 1) * HORIZON]:
+                    e.hot_step()
+                if use_branch:
+                    reducer.join()
+            for e in rem_envs:
+                e.hot_step()
+
     def timed(steps, warmup):
         def body():
+            if whole is not None:
+                whole.replay()
+                return
             for i in range(full):
                 chunks[i % n_chunks].replay()
             for g in rem_graph:
@@ -213,6 +273,9 @@ def run_ours(args):
         w = max(-(-warmup // HORIZON), 3)
         for i in range(w):
             chunks[(i - w) % n_chunks].replay()      # ends on the last chunk: body() starts at chunk 0
+        if whole is not None:                        # the first launch of an instantiated graph uploads it: not timed
+            for _ in range(max(3, -(-warmup // max(steps, 1)))):
+                whole.replay()
         torch.cuda.synchronize()
         if dist is not None:
             dist.barrier()
@@ -229,8 +292,11 @@ def run_ours(args):
         torch.cuda.synchronize()
         return t0.elapsed_time(t1) * 1e-3
 
-    clk = ClockSampler(local_rank)
+    # Clocks: ONE sampler per box (local rank 0 forks nvidia-smi at 10 Hz for its own GPU); in round 2 every rank did,
+    # 8 subprocess trains contending for the driver lock and the cores that issue the launches inside a 120-us window.
+    clk = ClockSampler(local_rank, enabled=(local_rank == 0))
     clk.__enter__()
+    time.sleep(0.5)          # the first nvidia-smi fork is over before the timed window opens
     elapsed = timed(args.steps, args.warmup)
     if dist is not None:
         t = torch.tensor([elapsed], device=device, dtype=torch.float64)
@@ -238,6 +304,7 @@ def run_ours(args):
         elapsed = float(t.item())
     value = n * world * args.steps / elapsed
     gpu_launches = args.steps + full          # one fused step kernel per step + one statistics snapshot per horizon
+    stats_check = check_stats_reduce(pkg, reducer, chunks, dist, world, device) if use_branch else None
 
     # ---- dominant kernel alone (roofline): fused kernel only, same rotation, CUDA events ----
     kgraph = capture(envs, lambda e: e.hot_step())
@@ -276,6 +343,7 @@ def run_ours(args):
                 "pdl": "programmatic dependent launch: on" if lib.lib().ige_use_pdl() else "programmatic dependent launch: off",
                 "host_numa_node": numa_node},
         "gpu_launches": gpu_launches,
+        "stats_check": stats_check,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": ncu_traffic(task, n), "peak_source": f"MEASURED_PEAKS.json hbm_gbs ({peak_kind})",
                      "kernel": KERNEL_NAME[task], "kernel_us": kernel_s * 1e6,
@@ -493,13 +561,37 @@ def run_variants(pkg, args, device, peak):
     return out
 
 
+_FULL_AFFINITY = os.sched_getaffinity(0) if hasattr(os, "sched_getaffinity") else None   # before any NUMA binding
+
+
+class host_affinity:
+    """The CPU baselines get every core this process started with: run_ours() narrows the process to the GPU's NUMA
+    node (distributed.bind_to_gpu_numa_node) for the pinned arenas, which must not shrink the reference's thread
+    pool and understate it.  Restores the narrowed mask on exit."""
+
+    def __enter__(self):
+        self.saved = os.sched_getaffinity(0) if _FULL_AFFINITY is not None else None
+        if self.saved is not None and self.saved != _FULL_AFFINITY:
+            os.sched_setaffinity(0, _FULL_AFFINITY)
+        return self
+
+    def __exit__(self, *exc):
+        if self.saved is not None and self.saved != _FULL_AFFINITY:
+            os.sched_setaffinity(0, self.saved)
+
+
+def host_cores():
+    """Threads a CPU baseline may really use: the affinity mask, not the machine's core count."""
+    return len(os.sched_getaffinity(0)) if _FULL_AFFINITY is not None else (os.cpu_count() or 1)
+
+
 def cpu_baseline(pkg, args, seconds=6.0, steps=None, warmup=3):
     """The CPU port (oracle/ige_oracle.c, plain C + pthreads) of the same step on the host cores."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import harness as H
     from oracle import oracle
     task, n = args.task, args.num_envs
-    cores = os.cpu_count() or 1
+    cores = host_cores()
     syn = pkg.factory._SYN_NAME[task]
     if syn not in H.TASK_NAME:
         return None
@@ -534,7 +626,7 @@ def cpu_model():
     return "unknown"
 
 
-def reference_torch_baseline(pkg, args, seconds=6.0, steps=None, warmup=5, threads=None):
+def reference_torch_baseline(pkg, args, seconds=6.0, steps=None, warmup=5, threads=None, windows=1):
     """The reference's OWN implementation of the step on the host cores (north_star: "the reference torch path
     ... sim_device=cpu pipeline=cpu"): the unmodified task class from the reference tree (/root/reference in the
     build container, else the files tools/vendor_reference.py staged under oracle/_ref/), built around the same
@@ -549,7 +641,7 @@ def reference_torch_baseline(pkg, args, seconds=6.0, steps=None, warmup=5, threa
     syn = pkg.factory._SYN_NAME[task]
     if syn not in ref_harness.BUILDERS:
         return None
-    cores = threads or os.cpu_count() or 1
+    cores = threads or host_cores()
     torch.set_num_threads(cores)
     st = pkg.synthetic.make_state(syn, n, seed=args.seed, reset_prob=0.02, fall_frac=args.fall_frac)
     cfg = pkg.factory.task_cfg(task)
@@ -568,17 +660,28 @@ def reference_torch_baseline(pkg, args, seconds=6.0, steps=None, warmup=5, threa
     with torch.no_grad():
         for _ in range(max(warmup, 3)):       # TorchScript's profiling executor specialises on the first calls
             step()
-        done, t0 = 0, time.perf_counter()
-        while True:
-            step()
-            done += 1
-            if steps is not None:
-                if done >= steps:
+        def window():
+            done, t0 = 0, time.perf_counter()
+            while True:
+                step()
+                done += 1
+                if steps is not None:
+                    if done >= steps:
+                        break
+                elif time.perf_counter() - t0 >= seconds:
                     break
-            elif time.perf_counter() - t0 >= seconds:
-                break
-        el = time.perf_counter() - t0
-    return {"value": n * done / el, "unit": "env-steps/s", "cores": cores, "kind": "reference",
+            return done, time.perf_counter() - t0
+        done, el = window()
+        # A 20-step window is ~90 ms of CPU time and swings by +-25 % run to run.  With `windows` > 1 the same K-step
+        # window is repeated (while a window stays under 10 s) and the MEDIAN window is reported.
+        extra = {}
+        if windows > 1 and steps is not None and el < 10.0:
+            runs = [(done, el)] + [window() for _ in range(windows - 1)]
+            per_window = sorted(n * d / t for d, t in runs)
+            extra = {"windows": len(runs), "first_window_value": n * done / el, "min_window_value": per_window[0],
+                     "max_window_value": per_window[-1], "value_is": f"median of {len(runs)} windows of {steps} steps"}
+            done, el = sorted(runs, key=lambda r: r[1] / r[0])[len(runs) // 2]
+    return {**extra, "value": n * done / el, "unit": "env-steps/s", "cores": cores, "kind": "reference",
             "cpu_model": cpu_model(), "torch_threads": torch.get_num_threads(),
             "sample": f"{done} steps of the reference's own {task}.post_physics_step (unmodified "
                       f"isaacgymenvs/tasks/{syn}.py on CPU torch {torch.__version__}, FakeGym, num_envs={n}), "
@@ -590,14 +693,15 @@ def reference_torch_baseline(pkg, args, seconds=6.0, steps=None, warmup=5, threa
 def host_baselines(pkg, args, seconds, steps=None, warmup=3):
     """cpu_baseline object: the reference's torch path when available (kind "reference"), with the C port of
     the oracle beside it as `cpu_port`; the port alone (kind "port") otherwise."""
-    port = cpu_baseline(pkg, args, seconds=seconds, steps=steps, warmup=warmup)
-    ref = reference_torch_baseline(pkg, args, seconds=seconds, steps=steps, warmup=max(warmup, 3))
-    if ref is None:
-        return port
-    if port is None:
-        return ref
-    one = reference_torch_baseline(pkg, args, seconds=min(seconds, 3.0), steps=None if steps is None else max(2, steps // 4),
-                                   warmup=3, threads=1)
+    with host_affinity():
+        port = cpu_baseline(pkg, args, seconds=seconds, steps=steps, warmup=warmup)
+        ref = reference_torch_baseline(pkg, args, seconds=seconds, steps=steps, warmup=max(warmup, 3))
+        if ref is None:
+            return port
+        if port is None:
+            return ref
+        one = reference_torch_baseline(pkg, args, seconds=min(seconds, 3.0), steps=None if steps is None else max(2, steps // 4),
+                                       warmup=3, threads=1)
     ref["single_thread"] = {"value": one["value"], "ms_per_step": one["ms_per_step"]}
     ref["cpu_port"] = port
     return ref
@@ -609,12 +713,20 @@ def run_reference(args):
         return
     pkg = load_package()
     world = int(os.environ.get("WORLD_SIZE", "1"))
-    cb = host_baselines(pkg, args, seconds=args.cpu_seconds, steps=args.steps, warmup=max(args.warmup, 3))
+    # The reference arm runs the reference and nothing of this repository: no C port beside it (building the port's
+    # CPU mirror asks libige_b200.so for scratch sizes, which put the library into this process's maps), only rank 0's
+    # 16 384-env shard whatever N is (stated in config.reference_arm_envs).  The port is the fallback when the
+    # reference tree is absent.
+    with host_affinity():
+        cb = reference_torch_baseline(pkg, args, seconds=args.cpu_seconds, steps=args.steps, warmup=max(args.warmup, 3),
+                                      windows=5)
+    if cb is None:
+        cb = host_baselines(pkg, args, seconds=args.cpu_seconds, steps=args.steps, warmup=max(args.warmup, 3))
     out = {"impl": "reference", "metric": "env-steps/sec (obs+reward+reset)", "value": cb["value"],
            "unit": "env-steps/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
            "ms_per_step": cb["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
            "dtype": "f32", "data": "synthetic",
-           "config": bench_config(args.task, args.num_envs, world),
+           "config": {**bench_config(args.task, args.num_envs, world), "reference_arm_envs": args.num_envs},
            "cpu_baseline": cb,
            "e2e": {"value": cb["value"], "unit": "env-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
            "gpu_launches": 0}

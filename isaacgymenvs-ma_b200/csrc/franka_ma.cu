@@ -1040,6 +1040,7 @@ extern "C" int ige_franka_ma_post_physics(const IgeFrankaMAParams *p, const IgeF
         int dev = 0;
         cudaGetDevice(&dev);
         static int max_ctas[4][IGE_MAX_DEVICES];   // resident CTAs per variant and device (0 = not queried yet)
+        static int ctas_per_sm[4][IGE_MAX_DEVICES];
         if (dev < 0 || dev >= IGE_MAX_DEVICES) return ige_fail(IGE_EPARAM, "device ordinal %d not supported", dev);
         if (max_ctas[p->variant][dev] == 0) {
             int sms = 0, per_sm = 0;
@@ -1049,11 +1050,17 @@ extern "C" int ige_franka_ma_post_physics(const IgeFrankaMAParams *p, const IgeF
                 return ige_fail(e != cudaSuccess ? (int)e : IGE_EPARAM, "ige_franka_ma_post_physics: occupancy query failed");
             int m = sms * per_sm;
             if (m > ige::kListMaxCtas) m = ige::kListMaxCtas;
+            ctas_per_sm[p->variant][dev] = per_sm;
             max_ctas[p->variant][dev] = m;
         }
         const int tiles = (p->num_envs + RT_E - 1) / RT_E;
         const int scanner = b->list.scratch ? 1 : 0;
-        const int cap = max_ctas[p->variant][dev] - scanner > 0 ? max_ctas[p->variant][dev] - scanner : 1;
+        // Combine / PP: workers wait for the scanner's gate and the scanner waits for every worker, so ALL CTAs must be
+        // resident together.  The occupancy figure is that of an otherwise empty GPU; a kernel of another stream (the
+        // statistics exchange polling its peers, an NCCL kernel) may hold a slot.  Keep one SM's worth of CTAs free.
+        const int headroom = pair_only ? ctas_per_sm[p->variant][dev] : 0;
+        const int avail = max_ctas[p->variant][dev] - headroom - scanner;
+        const int cap = avail > 0 ? avail : 1;
         const int per_cta = (tiles + cap - 1) / cap;
         if (!pair_only || per_cta <= RT_MAX_TILES) {
             const int workers = (tiles + per_cta - 1) / per_cta;   // workers + scanner <= resident capacity: all CTAs co-resident

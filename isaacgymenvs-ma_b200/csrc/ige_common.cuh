@@ -478,8 +478,12 @@ __device__ __forceinline__ int list_emit_mask(const IgeResetList &L, int off, ui
 //     popcounts and writes the ascending ids itself; after the last slot it stores the count, opens the next epoch
 //     and advances the Philox step word.  The ids of a run of tiles are complete about one L2 round trip after its
 //     last slot was published, i.e. while the workers are still storing that tile's outputs.
-// Nobody waits for the scanner, so the grid needs no co-residency guarantee (the launchers still keep
-// workers + 1 <= resident CTAs so that the scanner starts with the kernel).  Epoch / step word: every worker CTA read
+// In this basic form nobody waits for the scanner, so the grid needs no co-residency guarantee (the launchers still
+// keep workers + 1 <= resident CTAs so that the scanner starts with the kernel).  EXCEPTION: the paired Franka rows
+// kernel (Combine / PP, franka_ma.cu) adds a gate -- its workers DO wait for the scanner's epoch store before they
+// overwrite the entry flags, and the scanner waits for every worker's slots -- so that caller needs every CTA
+// resident at once; its launcher keeps one SM's worth of CTAs free for kernels of other streams (statistics
+// exchange, NCCL) that may be resident beside it.  Epoch / step word: every worker CTA read
 // both before its first publish (the caller guarantees a CTA barrier in between), and the scanner advances them only
 // after it has seen every slot of this launch.
 __device__ __forceinline__ uint32_t list_epoch_tag(const IgeResetList &L) {

@@ -107,10 +107,20 @@ class StatsReducer:
       * ``"nccl"`` (``IGE_STATS_REDUCE=nccl``, or when peer mapping is unavailable): snapshot kernel +
         ``dist.all_reduce`` captured in the branch.
 
+    A rank that does not push within ``timeout_ms`` is NOT waited for any longer: the kernel substitutes zeros and
+    records ``rank + 1`` in ``self.error`` -- unlike NCCL, which would block.  The default is therefore long
+    (``IGE_STATS_TIMEOUT_MS``, 10 minutes: a checkpoint save or an evaluation pause on one rank must not drop its
+    horizon), and :meth:`check_error` / :meth:`result` raise when it happened, so ranks never continue silently with
+    different vectors.  Tests pass a short ``timeout_ms``.
+
     CPU (gloo, tests of the host logic): :meth:`start` with the 16-float vector, eager.
     """
 
-    def __init__(self, device, mode=None):
+    def __init__(self, device, mode=None, timeout_ms=None):
+        self.timeout_ms = int(timeout_ms if timeout_ms is not None else os.environ.get("IGE_STATS_TIMEOUT_MS", 600000))
+        if not 0 < self.timeout_ms < 2 ** 32:
+            raise ValueError(f"timeout_ms={self.timeout_ms} outside (0, 2^32)")
+        self.error = None
         self.device = torch.device(device)
         self.cuda = self.device.type == "cuda"
         self.mode = "local"
@@ -173,10 +183,16 @@ class StatsReducer:
                 self.local = torch.zeros(_abi.IGE_NUM_STATS, dtype=torch.float32, device=self.device)
                 self.rank, self.world = rank, world
                 self.mode = "peer"
-                self._exchange(self.rows[0])            # first launch outside any capture; also checks the mapping
+                self._exchange(self.rows[0], timeout_ms=min(self.timeout_ms, 30000))   # first launch outside any capture; also checks the mapping
                 torch.cuda.synchronize(self.device)
-                if int(self.error.item()) != 0:
-                    raise RuntimeError(f"ige_stats_exchange: rank {int(self.error.item()) - 1} never answered")
+                missing = int(self.error.item())
+                self.error.zero_()
+                answers = [None] * world
+                dist.all_gather_object(answers, missing)     # every rank learns of a failure: all raise, nobody is left in the barrier
+                if any(answers):
+                    bad = sorted({m - 1 for m in answers if m})
+                    raise RuntimeError(f"ige_stats_exchange: rank(s) {bad} never answered the first exchange "
+                                       f"(seen by rank(s) {[r for r, m in enumerate(answers) if m]})")
                 self.reduced.zero_()
             else:
                 for r, p in enumerate(ptrs):
@@ -186,14 +202,14 @@ class StatsReducer:
                     lib.ige_mailbox_destroy(own)
             dist.barrier()
 
-    def _exchange(self, rows):
+    def _exchange(self, rows, timeout_ms=None):
         from . import _lib
         a = _abi.IgeStatsExchangeArgs()
         a.stats, a.out, a.local = rows.data_ptr(), self.reduced.data_ptr(), self.local.data_ptr()
         for r, p in enumerate(self._mailboxes):
             a.mailbox[r] = p
         a.epoch, a.error = self.epoch.data_ptr(), self.error.data_ptr()
-        a.rank, a.world, a.zero_stats, a.timeout_ms = self.rank, self.world, 1, 2000
+        a.rank, a.world, a.zero_stats, a.timeout_ms = self.rank, self.world, 1, int(timeout_ms or self.timeout_ms)
         _lib.call("ige_stats_exchange", a, stream=torch.cuda.current_stream(self.device).cuda_stream)
 
     def close(self):
@@ -299,8 +315,20 @@ class StatsReducer:
             self.join()
         return self.reduced
 
+    def check_error(self):
+        """Peer mode: raise if an exchange since the last check gave up on a rank (its statistics were replaced by
+        zeros and the ranks' vectors may differ).  Synchronises with the device; clears the flag."""
+        if self.mode != "peer" or self.error is None:
+            return
+        missing = int(self.error.item())
+        if missing:
+            self.error.zero_()
+            raise RuntimeError(f"ige_stats_exchange: rank {missing - 1} did not push its statistics within "
+                               f"{self.timeout_ms} ms; this horizon's reduced vector is incomplete on rank {self.rank}")
+
     def result(self):
         v = self.wait().detach().cpu().tolist()
+        self.check_error()
         out = dict(zip(STAT_NAMES, v))
         steps, done = max(out["steps"], 1.0), max(out["done"], 1.0)
         out["mean_reward"] = out["reward_sum"] / steps

@@ -225,7 +225,23 @@ def _peer_worker_one_gpu(rank, world, port, q):
         g.replay()
     torch.cuda.synchronize()
     results.append(red.reduced.cpu().numpy().copy())
-    q.put((rank, results, int(red.epoch.item()), int(red.error.item())))
+    epoch, err = int(red.epoch.item()), int(red.error.item())
+    # a rank that is late beyond timeout_ms: the others give up on it (zeros in its place) and check_error() says so
+    import time
+    red.timeout_ms = 300
+    dist.barrier()
+    if rank == 1:
+        time.sleep(2.0)
+    view[:, :abi.IGE_NUM_STATS] = 1.0
+    red.issue(rows)
+    torch.cuda.synchronize()
+    late = None
+    try:
+        red.check_error()
+    except RuntimeError as e:
+        late = str(e)
+    red.check_error()                                     # the flag was cleared by the raise
+    q.put((rank, results, epoch, err, late, red.reduced.cpu().numpy().copy()))
     del g
     red.close()
     dist.barrier()
@@ -253,8 +269,14 @@ def test_peer_exchange_processes_on_one_gpu(world):
                 p.kill()
     R = abi.IGE_STATS_ROWS
     tri = world * (world + 1) / 2.0                     # sum over ranks of (rank + 1)
-    for rank, results, epoch, err in res:
+    for rank, results, epoch, err, late, late_vec in res:
         assert err == 0 and epoch == 1 + 4 + 7          # set-up probe + eager + graph replays
+        if rank == 1:                                   # the late rank finds everybody's slots already filled
+            assert late is None
+            np.testing.assert_array_equal(late_vec, np.full(abi.IGE_NUM_STATS, R * world, np.float32))
+        else:                                           # the others report it instead of continuing silently
+            assert late is not None and "rank 1 did not push" in late, late
+            np.testing.assert_array_equal(late_vec, np.full(abi.IGE_NUM_STATS, R * (world - 1), np.float32))
         for it in range(4):
             np.testing.assert_array_equal(results[it], np.full(abi.IGE_NUM_STATS, R * tri * (it + 1), np.float32))
         np.testing.assert_array_equal(results[4], np.full(abi.IGE_NUM_STATS, R * 10.0 * tri, np.float32))
