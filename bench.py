@@ -480,8 +480,51 @@ def run_e2e(pkg, args, device, dist=None, world=1):
                 "wall_ms_per_step": wall / args.steps * 1e3, "h2d_bytes_per_step": pipe.h2d_bytes_per_step,
                 "d2h_bytes_per_step": pipe.d2h_bytes_per_step, "results_on_host_ok": ok}
             del pipe
+    # ---- the floor of this box: nothing but the copies.  One pinned buffer of the staged mode's H2D bytes and one of
+    #      its D2H bytes per step, the two directions streaming concurrently on their own streams, all ranks at once.
+    #      This is what an ideal pipeline (H2D of step t+1 || kernel of t || D2H of t-1) would cost on this host. ----
+    nb_in, nb_out = res["staged"]["h2d_bytes_per_step"], res["staged"]["d2h_bytes_per_step"]
+    h_in = torch.empty(nb_in, dtype=torch.uint8).pin_memory()
+    h_out = torch.empty(nb_out, dtype=torch.uint8).pin_memory()
+    d_in = torch.empty(nb_in, dtype=torch.uint8, device=device)
+    d_out = torch.zeros(nb_out, dtype=torch.uint8, device=device)
+    s_in, s_out = torch.cuda.Stream(device), torch.cuda.Stream(device)
+
+    def copies_only(k):
+        cur = torch.cuda.current_stream(device)
+        s_in.wait_stream(cur)
+        s_out.wait_stream(cur)
+        with torch.cuda.stream(s_in):
+            for _ in range(k):
+                d_in.copy_(h_in, non_blocking=True)
+        with torch.cuda.stream(s_out):
+            for _ in range(k):
+                h_out.copy_(d_out, non_blocking=True)
+        cur.wait_stream(s_in)
+        cur.wait_stream(s_out)
+
+    copies_only(max(3, args.warmup))
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    f0.record()
+    copies_only(args.steps)
+    f1.record()
+    torch.cuda.synchronize()
+    floor_s = f0.elapsed_time(f1) * 1e-3
+    if dist is not None:
+        t = torch.tensor([floor_s], device=device, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        floor_s = float(t.item())
+    floor_ms = floor_s / args.steps * 1e3
     best = max(res, key=lambda k: res[k]["value"])
     out = dict(res[best])
+    out.update({"pcie_floor_ms": floor_ms,
+                "pcie_floor": f"{nb_in} B H2D || {nb_out} B D2H per step, cudaMemcpyAsync only, {world} rank(s) at once: "
+                              f"{nb_in / floor_ms / 1e6:.1f} + {nb_out / floor_ms / 1e6:.1f} GB/s per GPU",
+                "vs_pcie_floor": res[best]["ms_per_step"] / floor_ms,
+                "staged_ms_per_step": res["staged"]["ms_per_step"]})     # the SAME mode at every N, next to best-of
     out.update({"unit": "env-steps/s", "mode": best, "modes": res,
                 "api": f"{task}.post_physics_step() (ctypes -> C ABI), pinned host buffers; "
                        + {"mapped": "map_host_sim(): the kernel reads/writes pinned host memory over PCIe",
