@@ -228,11 +228,13 @@ def run_ours(args):
     #      NCCL all-reduce of the PREVIOUS horizon's accumulator; the remainder steps are one more graph ----
     reducer = pkg.distributed.StatsReducer(device, mode=None if args.stats_reduce in ("auto", "none") else args.stats_reduce)
     reducer.warm()
-    use_branch = args.stats_reduce != "none"
+    # tasks whose kernels have no statistics accumulator (ACCUMULATES_STATS False) get no reduction branch
+    use_branch = args.stats_reduce != "none" and envs[0].ACCUMULATES_STATS
     n_chunks = replicas // HORIZON
     for c in range(n_chunks):
         for e in envs[c * HORIZON:(c + 1) * HORIZON]:
-            reducer.attach(e, c)
+            if use_branch:
+                reducer.attach(e, c)
     mode = "thread_local" if world > 1 else "global"   # NCCL's watchdog thread may touch the device during capture
     chunks = [capture(envs[c * HORIZON:(c + 1) * HORIZON], lambda e: e.hot_step(),
                       pre=(lambda c=c: reducer.fork(reducer.rows[(c & 1) ^ 1])) if use_branch else None,
@@ -333,7 +335,7 @@ def run_ours(args):
                 "launch": f"one CUDA graph per horizon of {HORIZON} steps; the fold + all-reduce of the previous horizon's "
                           f"statistics is a forked branch of the same graph ({reducer.collectives} collectives captured, "
                           f"world={world}); remainder steps = one more graph",
-                "stats_reduce": ("none (diagnostic)" if not use_branch else
+                "stats_reduce": ("none (diagnostic, or a task without an accumulator)" if not use_branch else
                                  {"peer": "ige_stats_exchange: one kernel, fold + NVLink peer-mailbox all-reduce",
                                   "nccl": "ige_stats_snapshot + ncclAllReduce captured in the branch"
                                           + (f" (peer mapping unavailable: {reducer.peer_error})"

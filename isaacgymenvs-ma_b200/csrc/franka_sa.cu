@@ -499,12 +499,7 @@ extern "C" int ige_franka_cabinet_pre_physics(const IgeFrankaCabinetArgs *a, voi
     IGE_REQUIRE_PTR(a->actions);
     IGE_REQUIRE_PTR(a->franka_dof_targets);
     if (a->num_envs == 0) return IGE_OK;
-    static int sms = 0;
-    if (sms == 0) {
-        int dev = 0;
-        cudaGetDevice(&dev);
-        if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms < 1) sms = 1;
-    }
+    const int sms = ige_current_device_sms();
     int g = (a->num_envs * 9 + kTaskThreads - 1) / kTaskThreads;
     g = g > sms * 16 ? sms * 16 : g;
 ige_launch(franka_cabinet_pre_kernel, g, kTaskThreads, 0, (cudaStream_t)stream, *a);

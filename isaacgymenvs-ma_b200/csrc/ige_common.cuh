@@ -80,6 +80,25 @@ __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;"
 __device__ __forceinline__ void pdl_prologue() { pdl_wait(); }
 __device__ __forceinline__ void pdl_prologue_early() { pdl_trigger(); pdl_wait(); }
 }  // namespace ige
+// SM count of the CURRENT device, cached per device ordinal (a process may drive several GPUs: a single cached value
+// would size grids of device 1 with device 0's count).  *dev_out (optional) receives the ordinal, -1 if out of range.
+static inline int ige_current_device_sms(int *dev_out = nullptr) {
+    static int sms_of[IGE_MAX_DEVICES];
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= IGE_MAX_DEVICES) {
+        if (dev_out) *dev_out = -1;
+        int sms = 0;
+        if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev < 0 ? 0 : dev) != cudaSuccess || sms < 1) sms = 1;
+        return sms;
+    }
+    if (dev_out) *dev_out = dev;
+    if (sms_of[dev] == 0) {
+        int sms = 0;
+        if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms < 1) sms = 1;
+        sms_of[dev] = sms;
+    }
+    return sms_of[dev];
+}
 template <typename... KArgs, typename... Args>
 static inline cudaError_t ige_launch_opt(bool pdl, void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem,
                                          cudaStream_t stream, Args... args) {

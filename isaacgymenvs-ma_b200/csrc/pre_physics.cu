@@ -108,12 +108,7 @@ __global__ void __launch_bounds__(kThreads) helper_probe_kernel(const __grid_con
 }
 
 int grid_for(long long items) {
-    static int sms = 0;   // grid-stride cap: SM count x 8 CTAs
-    if (sms == 0) {
-        int dev = 0;
-        cudaGetDevice(&dev);
-        if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms < 1) sms = 1;
-    }
+    const int sms = ige_current_device_sms();   // grid-stride cap: SM count x 8 CTAs
     const long long g = (items + kThreads - 1) / kThreads, cap = (long long)sms * kCtasPerSm;
     return (int)(g < 1 ? 1 : (g > cap ? cap : g));
 }

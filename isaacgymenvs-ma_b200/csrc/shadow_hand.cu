@@ -760,14 +760,18 @@ extern "C" int ige_shadow_hand_post_physics(const IgeShadowHandParams *p, const 
     const int nobs = hand_num_obs(p->obs_type);
     const int nst = hand_num_obs(hand_state_layout(p->obs_type));
     const size_t smem = (size_t)(((TE * nobs + 31) / 32) * 32 + (p->asymmetric_obs ? TE * nst : 0)) * sizeof(float);
-    static bool attr_set = false;
+    // function attributes are per device (context): one flag per ordinal, not one per process
+    int attr_dev = -1;
+    ige_current_device_sms(&attr_dev);
+    if (attr_dev < 0) return ige_fail(IGE_EPARAM, "ige_shadow_hand_post_physics: device ordinal not supported");
+    static bool attr_set_of[IGE_MAX_DEVICES], fast_attr_set_of[IGE_MAX_DEVICES];
+    bool &attr_set = attr_set_of[attr_dev], &fast_attr_set = fast_attr_set_of[attr_dev];
     if (!attr_set) {
         cudaError_t e = cudaFuncSetAttribute(shadow_hand_post_physics_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              (int)((TE * MAX_OBS + 32 + TE * MAX_OBS) * sizeof(float)));
         if (e != cudaSuccess) return ige_fail((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
         attr_set = true;
     }
-    static bool fast_attr_set = false;
     if (!fast_attr_set) {
         for (int i = 0; i < 14; ++i) {
             cudaError_t e = cudaFuncSetAttribute(fast_kernel(i >> 1, i & 1), cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -784,12 +788,7 @@ extern "C" int ige_shadow_hand_post_physics(const IgeShadowHandParams *p, const 
     if (standard) {
         // full tiles: persistent fast kernel; a ragged last tile (num_envs % 32) goes through the generic one
         const int full = p->num_envs / TE, ragged = tiles - full;
-        static int sms = 0;
-        if (sms == 0) {
-            int dev = 0;
-            cudaGetDevice(&dev);
-            if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms < 1) sms = 1;
-        }
+        const int sms = ige_current_device_sms();
         const int grid = full < sms * kFastCtasPerSm ? full : sms * kFastCtasPerSm;
         if (full > 0) {
 ige_launch(fast_kernel(p->obs_type, p->asymmetric_obs != 0), grid, FNT, smem, s, *p, *b, full, grid + ragged);

@@ -392,12 +392,7 @@ int check_common(const Args *a, const char *name) {
     return ige_check_list(a->list);
 }
 int post_grid(int n) {   // grid-stride kernels: at most 16 CTAs per SM
-    static int sms = 0;
-    if (sms == 0) {
-        int dev = 0;
-        cudaGetDevice(&dev);
-        if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms < 1) sms = 1;
-    }
+    const int sms = ige_current_device_sms();
     const int g = (n + kTaskThreads - 1) / kTaskThreads;
     return g < 1 ? 1 : (g > sms * 16 ? sms * 16 : g);
 }

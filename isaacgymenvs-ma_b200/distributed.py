@@ -235,7 +235,16 @@ class StatsReducer:
     # -- CUDA: graph-capturable pieces ---------------------------------------------------------------------
     def attach(self, env, parity):
         """Make `env`'s step kernels accumulate into rows[parity]."""
+        self._require_accumulator(env)
         env.stats_rows = self.rows[parity & 1]
+
+    @staticmethod
+    def _require_accumulator(env):
+        """Tasks whose C ABI has no `stats` pointer (Anymal, BallBalance, Quadcopter, Ingenuity, the single-agent Franka
+        tasks) never write the accumulator: reducing it would ship zeros that look like statistics."""
+        if not getattr(env, "ACCUMULATES_STATS", True) or getattr(env, "stats_rows", 0) is None:
+            raise ValueError(f"{type(env).__name__} has no episode-statistics accumulator (its step kernels take no "
+                             "`stats` pointer, or it was built with accumulate_stats=False): nothing to reduce")
 
     def warm(self):
         """One eager collective so the NCCL communicator exists before any graph capture."""
@@ -286,6 +295,7 @@ class StatsReducer:
         import torch.distributed as dist
         if self.cuda and hasattr(stats, "stats_rows"):
             env = stats
+            self._require_accumulator(env)
             full = env.stats_rows
             if full is self.rows[0] or full is self.rows[1]:
                 self._cur = 0 if full is self.rows[0] else 1

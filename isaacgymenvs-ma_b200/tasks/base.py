@@ -52,6 +52,10 @@ class SyntheticSim:
 class VecTaskB200:
     """Mirror of Env + VecTask (vec_task.py:67-133, 207-457) minus viewer / DR / sim creation."""
 
+    # True for the task classes whose step kernels add into the episode-statistics accumulator (`stats` in their
+    # C-ABI buffers struct: Cartpole, Ant / Humanoid, ShadowHand / AllegroHand, Franka*MA).
+    ACCUMULATES_STATS = False
+
     num_agents = 1
 
     def __init__(self, cfg, sim: SyntheticSim, device, rl_device=None, rand_mode="philox", seed=0,
@@ -96,8 +100,10 @@ class VecTaskB200:
         words = int(_lib.lib().ige_compact_scratch_words(self.num_envs * self.num_agents))
         self._compact_scratch = torch.zeros(words, dtype=torch.int32, device=dev)
         self._list_scratch = torch.zeros(_abi.reset_list_scratch_words(self.num_envs), dtype=torch.int32, device=dev)
+        # only the tasks whose C ABI carries a `stats` pointer accumulate (ACCUMULATES_STATS); for the others the
+        # accumulator is None rather than a buffer of zeros that would be all-reduced as if it meant something
         self.stats_rows = (torch.zeros(_abi.IGE_STATS_ROWS * _abi.IGE_STATS_STRIDE, dtype=torch.float32, device=dev)
-                           if accumulate_stats else None)
+                           if accumulate_stats and self.ACCUMULATES_STATS else None)
         self._u0 = self._u1 = None
 
     @property

@@ -6,6 +6,7 @@ from .base import VecTaskB200, _ptr
 
 
 class Cartpole(VecTaskB200):
+    ACCUMULATES_STATS = True
     def __init__(self, cfg, sim, device, **kw):
         cfg = dict(cfg)
         cfg.setdefault("num_obs", 4)          # cartpole.py:46

@@ -18,6 +18,7 @@ LOGGED = {"reach": [], "collect": list(range(9)), "combine": [0, 1, 2, 7], "pp":
 
 
 class FrankaMA(VecTaskB200):
+    ACCUMULATES_STATS = True
     VARIANT = None
 
     def __init__(self, cfg, sim, device, **kw):

@@ -6,6 +6,7 @@ from .base import VecTaskB200, _ptr
 
 
 class _Locomotion(VecTaskB200):
+    ACCUMULATES_STATS = True
     ENTRY = None
     HAS_DOF_FORCE = False
     SENSORS = 0

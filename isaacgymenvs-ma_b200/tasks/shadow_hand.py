@@ -13,6 +13,7 @@ NUM_OBS = {"openai": 42, "full_no_vel": 77, "full": 157, "full_state": 211}
 
 
 class ShadowHand(VecTaskB200):
+    ACCUMULATES_STATS = True
     FUSED_ACTION_CLAMP = True
     NUM_OBS = NUM_OBS
     NUM_STATES = 211

@@ -73,3 +73,21 @@ def test_sharded_stats_allreduce_matches_single_process():
     np.testing.assert_allclose(out["done"], want[H.pkg._abi.STAT_DONE], rtol=0, atol=0)
     np.testing.assert_allclose(out["timeout"], want[H.pkg._abi.STAT_TIMEOUT], rtol=0, atol=0)
     np.testing.assert_allclose(out["task0"], want[H.pkg._abi.STAT_TASK0], rtol=1e-4)
+
+
+def test_reducer_refuses_tasks_without_accumulator():
+    """Anymal / BallBalance / ... take no `stats` pointer in their C ABI: StatsReducer must say so instead of
+    all-reducing a vector of zeros (and instead of crashing on a None accumulator)."""
+    import pytest
+    pkg = H.pkg
+    red = pkg.distributed.StatsReducer("cpu")
+
+    class NoStats:
+        ACCUMULATES_STATS = False
+        stats_rows = None
+
+    with pytest.raises(ValueError, match="no episode-statistics accumulator"):
+        red.attach(NoStats(), 0)
+    tm = pkg.tasks.task_map
+    assert all(tm[k].ACCUMULATES_STATS for k in ("Cartpole", "Ant", "Humanoid", "ShadowHand", "AllegroHand", "FrankaPPMA"))
+    assert not any(tm[k].ACCUMULATES_STATS for k in ("Anymal", "BallBalance", "Quadcopter", "Ingenuity", "FrankaCabinet"))
