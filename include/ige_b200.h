@@ -127,6 +127,41 @@ int ige_compact_resets(const IgeCompactArgs *args, void *stream);
 int ige_compact_resets_static(const IgeCompactArgs *args, void *stream);
 
 /* ------------------------------------------------------------------------------------------
+ * Observation / action noise of VecTask.step -- replaces dr_randomizations['actions']['noise_lambda'](actions)
+ * (vec_task.py:373-374) and dr_randomizations['observations']['noise_lambda'](self.obs_buf) (:399-400), i.e. the
+ * closures of apply_randomizations (vec_task.py:675-685 gaussian, :703-711 uniform), fused with the clamp that
+ * follows in step() (:376 actions, :404 observations):
+ *     noise = (corr * corr_scale + corr_shift) + draw * scale + shift;   y = x + noise | x * noise
+ * gaussian: (corr_scale, corr_shift, scale, shift) = (var_corr, mu_corr, var, mu), draw = randn_like(x);
+ * uniform:  (hi_corr - lo_corr, lo_corr, hi - lo, lo), draw = rand_like(x).  `corr` is the per-tensor N(0,1) sample
+ * the reference draws on the first call and keeps in params['corr'].  The schedule (sched_scaling, :651-673) is
+ * host arithmetic on those four numbers, done by the caller.
+ * ------------------------------------------------------------------------------------------ */
+#define IGE_NOISE_ADDITIVE 0
+#define IGE_NOISE_SCALING 1
+#define IGE_NOISE_GAUSSIAN 0
+#define IGE_NOISE_UNIFORM 1
+typedef struct IgeNoiseArgs {
+    int64_t count;         /* elements of the tensor */
+    int32_t operation;     /* IGE_NOISE_ADDITIVE / IGE_NOISE_SCALING */
+    int32_t distribution;  /* IGE_NOISE_GAUSSIAN / IGE_NOISE_UNIFORM (PHILOX: which draw the kernel makes) */
+    int32_t rand_mode;     /* IGE_RAND_INJECTED: `draw` (and `corr`) come from the caller; IGE_RAND_PHILOX: in-kernel */
+    int32_t init_corr;     /* PHILOX only: != 0 -> this launch also draws `corr` (N(0,1)) and stores it (first call) */
+    float corr_scale, corr_shift, scale, shift;
+    float clip;            /* clamp(y, +-clip) -> y_clamped; INFINITY = none */
+    uint32_t stream;       /* PHILOX: distinguishes tensors that share seed and step (0 = actions, 1 = observations) */
+    uint64_t seed;         /* PHILOX key */
+    const uint64_t *step;  /* PHILOX: device word mixed into the counter (NULL = 0); not advanced by this kernel */
+    const float *x;        /* [count] the tensor (actions / obs_buf) */
+    float *y;              /* [count] out, may alias x */
+    float *y_clamped;      /* [count] out, optional */
+    float *corr;           /* [count] in (out when init_corr) */
+    const float *draw;     /* [count] INJECTED: randn_like / rand_like of the reference */
+} IgeNoiseArgs;
+
+int ige_dr_noise(const IgeNoiseArgs *args, void *stream);
+
+/* ------------------------------------------------------------------------------------------
  * Cartpole -- replaces Cartpole.post_physics_step (tasks/cartpole.py:165-173) incl. reset_idx
  * (:144-157), compute_observations (:131-142), compute_cartpole_reward (:180-196).
  * ------------------------------------------------------------------------------------------ */

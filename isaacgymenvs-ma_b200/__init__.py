@@ -8,3 +8,4 @@ from . import distributed  # noqa: E402,F401
 from . import host_pipeline  # noqa: E402,F401
 from . import rollout  # noqa: E402,F401
 from . import integration  # noqa: E402,F401
+from . import dr_noise  # noqa: E402,F401

@@ -34,6 +34,17 @@ class IgeCompactArgs(C.Structure):
                 ("reset_rank", _p), ("count", _p), ("scratch", _p)]
 
 
+IGE_NOISE_ADDITIVE, IGE_NOISE_SCALING = 0, 1
+IGE_NOISE_GAUSSIAN, IGE_NOISE_UNIFORM = 0, 1
+
+
+class IgeNoiseArgs(C.Structure):
+    _fields_ = [("count", C.c_int64), ("operation", _i), ("distribution", _i), ("rand_mode", _i), ("init_corr", _i),
+                ("corr_scale", _f), ("corr_shift", _f), ("scale", _f), ("shift", _f), ("clip", _f),
+                ("stream", C.c_uint32), ("seed", C.c_uint64), ("step", _p), ("x", _p), ("y", _p),
+                ("y_clamped", _p), ("corr", _p), ("draw", _p)]
+
+
 class IgeCartpoleParams(C.Structure):
     _fields_ = [("num_envs", _i), ("reset_dist", _f), ("max_episode_length", _f), ("clip_obs", _f),
                 ("rand", IgeResetRand)]

@@ -14,6 +14,7 @@ _lib = None
 _SIGS = {
     "ige_compact_resets": (_abi.IgeCompactArgs,),
     "ige_compact_resets_static": (_abi.IgeCompactArgs,),
+    "ige_dr_noise": (_abi.IgeNoiseArgs,),
     "ige_cartpole_post_physics": (_abi.IgeCartpoleParams, _abi.IgeCartpoleBuffers),
     "ige_ant_post_physics": (_abi.IgeLocomotionParams, _abi.IgeLocomotionBuffers),
     "ige_humanoid_post_physics": (_abi.IgeLocomotionParams, _abi.IgeLocomotionBuffers),

@@ -52,10 +52,14 @@ def sim_tensor_names(task):
     return list(_SIM_TENSORS[task])
 
 
-def from_state(task, st, sim_device, rl_device=None, **kw):
-    """Construct the mirror of `task` around an existing synthetic state dict (numpy arrays)."""
+def from_state(task, st, sim_device, rl_device=None, dr_randomizations=None, **kw):
+    """Construct the mirror of `task` around an existing synthetic state dict (numpy arrays).
+    ``dr_randomizations``: the reference's ``task.randomization_params`` dict; only its ``observations`` / ``actions``
+    noise entries (and ``frequency``) are part of the fused path (tasks/base.py)."""
     dev = torch.device(sim_device)
     cfg = task_cfg(task)
+    if dr_randomizations:
+        cfg["dr_randomizations"] = dict(dr_randomizations)
     if task in _MA_TASKS:
         cfg = synthetic.franka_ma_cfg(_MA_TASKS[task], int(st["cfg_num_agents"]), int(st["cfg_num_targets"]))
         cfg["num_envs"] = int(st["progress_buf"].shape[0]) // cfg["num_agents"]
@@ -97,6 +101,9 @@ def make(seed, task, num_envs, sim_device, rl_device=None, graphics_device_id=-1
         rl_device = f"cuda:{local_rank}"
     overrides = {}
     if cfg is not None:
+        task_cfg_in = cfg.get("task", cfg) or {}
+        if task_cfg_in.get("task", {}).get("randomize") and "dr_randomizations" not in kw:   # ant.py:48-49
+            kw["dr_randomizations"] = task_cfg_in["task"].get("randomization_params", {})
         env_cfg = dict((cfg.get("task", cfg) or {}).get("env", {}))
         num_envs = int(env_cfg.get("numEnvs", num_envs))
         for src, dst in (("clipObservations", "clip_obs"), ("clipActions", "clip_actions"),

@@ -73,14 +73,19 @@ class VecTaskB200:
         self.clip_obs = float(cfg.get("clip_obs", math.inf))
         self.clip_actions = float(cfg.get("clip_actions", math.inf))
         self.control_steps = 0
-        # vec_task.py:368-370, :399-400: domain-randomisation noise lambdas on actions / observations.  DR is outside
-        # the hot path and the fused step() epilogue produces the clamped observations inside
-        # the kernel, so a noise hook could not run between post_physics_step and the clamp: refuse instead of
-        # silently dropping it.
+        # vec_task.py:373-374, :399-400: the noise lambdas on actions / observations are part of step() and run as one
+        # CUDA launch each, fused with the clamp that follows (dr_noise.NoiseLambda -> ige_dr_noise).  Everything else
+        # in the randomisation config (sim_params, actor_params: vec_task.py:715-) re-parameterises the simulator and
+        # is outside the hot path: refused rather than silently dropped.
         self.dr_randomizations = {}
-        if cfg.get("randomize") or cfg.get("dr_randomizations"):
-            raise NotImplementedError("domain randomisation (vec_task.py:368-370, :399-400, :528-) is not part of the "
-                                      "fused path; construct the task without `randomize`")
+        self._dr_spec = cfg.get("dr_randomizations") or {}
+        extra = sorted(k for k in self._dr_spec if k not in ("frequency", "observations", "actions"))
+        if cfg.get("randomize") and not self._dr_spec:
+            raise NotImplementedError("`randomize` without `dr_randomizations`: only the observation / action noise "
+                                      "of step() (vec_task.py:373-374, :399-400) is part of the fused path")
+        if extra:
+            raise NotImplementedError(f"domain randomisation of {extra} (vec_task.py:715-) is simulator set-up, not part "
+                                      "of the fused path; only `observations` / `actions` noise is supported")
         self.rand_mode = rand_mode
         self.seed = int(seed)
         self.fuse_epilogue = fuse_epilogue
@@ -105,6 +110,16 @@ class VecTaskB200:
         self.stats_rows = (torch.zeros(_abi.IGE_STATS_ROWS * _abi.IGE_STATS_STRIDE, dtype=torch.float32, device=dev)
                            if accumulate_stats and self.ACCUMULATES_STATS else None)
         self._u0 = self._u1 = None
+        self.last_step, self.last_rand_step = 0, 0
+        for tensor_id, name in enumerate(("actions", "observations")):
+            if self._dr_spec.get(name):
+                from ..dr_noise import NoiseLambda
+                clip = self.clip_actions if name == "actions" else self.clip_obs
+                self.dr_randomizations[name] = {"noise_lambda": NoiseLambda(
+                    self._dr_spec[name], dev, clip=clip, tensor_id=tensor_id, seed=self.seed, step=self.rng_step,
+                    rand_mode=rand_mode)}
+        if self.dr_randomizations.get("observations") and self.obs_clamped is None:
+            self.obs_clamped = torch.zeros_like(self.obs_buf)
 
     @property
     def stats(self):
@@ -202,13 +217,36 @@ class VecTaskB200:
     # -- vec_task.py:362-410 -------------------------------------------------------------------
     def step(self, actions):
         # vec_task.py:373; tasks whose pre-physics kernel clamps itself (FUSED_ACTION_CLAMP) skip the extra pass
-        action_tensor = actions if self.FUSED_ACTION_CLAMP else torch.clamp(actions, -self.clip_actions, self.clip_actions)
+        act_noise = self.dr_randomizations.get("actions")
+        if act_noise:                                   # vec_task.py:373-376: noise, then the clamp, one launch
+            if self.control_steps - self.last_rand_step >= self._dr_spec.get("frequency", 1) or self.control_steps == 0:
+                self.last_rand_step = self.control_steps          # apply_randomizations re-derives the schedule
+                for d in self.dr_randomizations.values():
+                    d["noise_lambda"].set_schedule(self.control_steps)
+            lam = act_noise["noise_lambda"]
+            actions = actions.to(self.device, torch.float32).contiguous()
+            clamped = torch.empty_like(actions)
+            noisy = lam(actions, out_clamped=clamped, **self._dr_draws("actions", actions))
+            action_tensor = noisy if self.FUSED_ACTION_CLAMP else clamped
+        else:
+            action_tensor = actions if self.FUSED_ACTION_CLAMP else torch.clamp(actions, -self.clip_actions, self.clip_actions)
         self.pre_physics_step(action_tensor)
         for _ in range(self.control_freq_inv):
             self.sim.simulate()
         self.post_physics_step()
         self.control_steps += 1
-        if self.fuse_epilogue:
+        obs_noise = self.dr_randomizations.get("observations")
+        if obs_noise:                                   # vec_task.py:399-404: obs_buf <- noise(obs_buf); obs = clamp(obs_buf)
+            if not act_noise and (self.control_steps - 1 - self.last_rand_step >= self._dr_spec.get("frequency", 1)
+                                  or self.control_steps == 1):
+                self.last_rand_step = self.control_steps - 1
+                obs_noise["noise_lambda"].set_schedule(self.control_steps - 1)
+            obs_noise["noise_lambda"](self.obs_buf, out=self.obs_buf, out_clamped=self.obs_clamped,
+                                      **self._dr_draws("observations", self.obs_buf))
+            self.timeout_buf = (self.timeout_bool if self.fuse_epilogue else
+                                (self.progress_buf >= self.max_episode_length - 1) & (self.reset_buf != 0))
+            obs = self.obs_clamped
+        elif self.fuse_epilogue:
             # produced by the same kernel launch (obs_clamped / timeout_bool outputs)
             self.timeout_buf = self.timeout_bool
             obs = self.obs_clamped
@@ -220,6 +258,18 @@ class VecTaskB200:
         if self.num_states > 0:
             self.obs_dict["states"] = self.get_state()
         return self.obs_dict, self.rew_buf.to(self.rl_device), self.reset_buf.to(self.rl_device), self.extras
+
+    def _dr_draws(self, name, tensor):
+        """injected parity mode: the draws the reference's closure would make, in its order -- on the first call
+        ``corr = randn_like`` (vec_task.py:678-679), then ``randn_like`` / ``rand_like`` (:684 / :710)."""
+        if self.rand_mode != "injected":
+            return {}
+        lam = self.dr_randomizations[name]["noise_lambda"]
+        kw = {}
+        if lam.corr is None:
+            kw["corr"] = torch.randn(tensor.shape)
+        kw["draw"] = torch.randn(tensor.shape) if lam.spec["distribution"] == "gaussian" else torch.rand(tensor.shape)
+        return kw
 
     def get_state(self):
         return torch.clamp(self.states_buf, -self.clip_obs, self.clip_obs).to(self.rl_device)

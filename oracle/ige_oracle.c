@@ -215,6 +215,63 @@ static void parallel_ranges(range_fn fn, const void *p, const void *b, int n, do
 }
 
 /* ------------------------------------------------------------------------------------------
+ * Observation / action noise lambdas (vec_task.py:373-374, :399-400; closures :675-685 gaussian, :703-711 uniform)
+ * + the clamp of step() (:376 / :404).  Restated op by op in float32, the order torch evaluates
+ *   op(tensor, corr * s_c + m_c  +  draw * s + m):   t1 = corr*s_c; t1 += m_c; t2 = draw*s; n = t1 + t2; n += m.
+ * INJECTED mode takes the reference's own randn_like / rand_like draws; PHILOX mode restates the kernel's generator
+ * (uniforms as the reset noise, normals by Box-Muller) so the two can be compared.
+ * ------------------------------------------------------------------------------------------ */
+static void noise_u4(const IgeNoiseArgs *a, uint64_t step, uint32_t block4, uint32_t stream, float u[4]) {
+    uint32_t c[4] = {block4, stream, (uint32_t)step, (uint32_t)(step >> 32)};
+    philox4x32_10(c, (uint32_t)a->seed, (uint32_t)(a->seed >> 32));
+    for (int k = 0; k < 4; ++k) u[k] = (float)(c[k] >> 8) * (1.0f / 16777216.0f);
+}
+static void noise_n4(const IgeNoiseArgs *a, uint64_t step, uint32_t block4, uint32_t stream, float z[4]) {
+    float u[4];
+    noise_u4(a, step, block4, stream, u);
+    for (int k = 0; k < 2; ++k) {
+        volatile float l = logf(1.0f - u[2 * k]);
+        volatile float m2 = -2.0f * l;
+        float r = sqrtf(m2);
+        volatile float t = 6.28318530717958647692f * u[2 * k + 1];
+        volatile float zc = r * cosf(t), zs = r * sinf(t);
+        z[2 * k] = zc;
+        z[2 * k + 1] = zs;
+    }
+}
+int ige_oracle_dr_noise(const IgeNoiseArgs *a) {
+    const uint64_t step = (a->rand_mode == IGE_RAND_PHILOX && a->step) ? *a->step : 0;
+    for (int64_t q = 0; q * 4 < a->count; ++q) {
+        float corr4[4], draw4[4];
+        if (a->rand_mode == IGE_RAND_PHILOX) {
+            if (a->init_corr) noise_n4(a, step, (uint32_t)q, 2u * a->stream + 1u, corr4);
+            if (a->distribution == IGE_NOISE_GAUSSIAN) noise_n4(a, step, (uint32_t)q, 2u * a->stream, draw4);
+            else noise_u4(a, step, (uint32_t)q, 2u * a->stream, draw4);
+        }
+        for (int k = 0; k < 4 && q * 4 + k < a->count; ++k) {
+            const int64_t i = q * 4 + k;
+            if (a->rand_mode == IGE_RAND_PHILOX && a->init_corr) a->corr[i] = corr4[k];
+            const float corr = a->corr[i];
+            const float draw = a->rand_mode == IGE_RAND_PHILOX ? draw4[k] : a->draw[i];
+            volatile float t1 = corr * a->corr_scale;     /* volatile: no contraction into fma */
+            volatile float c = t1 + a->corr_shift;
+            volatile float t2 = draw * a->scale;
+            volatile float n0 = c + t2;
+            volatile float n = n0 + a->shift;
+            const float x = a->x[i];
+            volatile float y = a->operation == IGE_NOISE_SCALING ? x * n : x + n;
+            a->y[i] = y;
+            if (a->y_clamped) {
+                float yc = y;
+                if (yc == yc) { yc = yc < -a->clip ? -a->clip : yc; yc = yc > a->clip ? a->clip : yc; }
+                a->y_clamped[i] = yc;
+            }
+        }
+    }
+    return 0;
+}
+
+/* ------------------------------------------------------------------------------------------
  * reset_buf.nonzero() with the multi-agent AND filter (franka_reach_MA.py:875-884)
  * ------------------------------------------------------------------------------------------ */
 int ige_oracle_compact_resets(const IgeCompactArgs *a) {
